@@ -1,0 +1,107 @@
+// C-ABI entry points of libftb200.so that own state: handle lifetime and plan tables.
+// (Stateless kernels export their own extern "C" wrappers next to the kernel.)
+#include "ftb_internal.h"
+
+using namespace ftb;
+
+extern "C" int ftb_version(void) { return FTB_VERSION; }
+
+extern "C" const char* ftb_error_string(int code) {
+  switch (code) {
+    case 0: return "ok";
+    case FTB_E_ARG: return "invalid argument (null pointer / bad size / bad enum)";
+    case FTB_E_ALIGN: return "pointer or leading dimension not 16-byte aligned";
+    case FTB_E_SHAPE: return "shape not supported by the sm_100a kernels";
+    case FTB_E_PLAN: return "unknown plan id";
+    case FTB_E_DRIVER: return "cuTensorMapEncodeTiled unavailable (no CUDA driver)";
+    case FTB_E_RESIDENT: return "persistent recurrence grid does not fit on the device";
+    default: break;
+  }
+  if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));
+  return "unknown ftb error";
+}
+
+extern "C" int ftb_create(int device, ftb_handle* out) {
+  if (!out) return FTB_E_ARG;
+  cudaError_t ce = cudaSetDevice(device);
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  cudaDeviceProp prop;
+  ce = cudaGetDeviceProperties(&prop, device);
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  if (prop.major != 10) return FTB_E_SHAPE;          // sm_100a only: no fallback path
+  ftb_context* c = new ftb_context();
+  c->device = device;
+  c->num_sms = prop.multiProcessorCount;
+  *out = c;
+  return 0;
+}
+
+extern "C" int ftb_destroy(ftb_handle h) {
+  if (!h) return FTB_E_ARG;
+  for (auto& kv : h->gemm_plans) cudaFree(kv.second.dev);
+  for (auto& kv : h->rnn_plans) {
+    cudaFree(kv.second.dev);
+    cudaFree(kv.second.counters);
+  }
+  delete h;
+  return 0;
+}
+
+extern "C" int64_t ftb_launch_count(ftb_handle h) { return h ? h->launches : -1; }
+
+extern "C" int ftb_gemm_plan_create(ftb_handle h, const ftb_gemm_problem* problems, int nproblems, int* plan_out) {
+  if (!h || !plan_out) return FTB_E_ARG;
+  GemmPlan plan;
+  const int rc = gemm_plan_build(problems, nproblems, &plan);
+  if (rc) return rc;
+  const int id = h->next_plan++;
+  h->gemm_plans[id] = plan;
+  *plan_out = id;
+  return 0;
+}
+
+extern "C" int ftb_gemm_plan_run(ftb_handle h, int plan, int impl, void* stream) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->gemm_plans.find(plan);
+  if (it == h->gemm_plans.end()) return FTB_E_PLAN;
+  h->launches += 1;
+  return gemm_plan_launch(it->second, impl, h->num_sms, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ftb_gemm_plan_destroy(ftb_handle h, int plan) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->gemm_plans.find(plan);
+  if (it == h->gemm_plans.end()) return FTB_E_PLAN;
+  cudaFree(it->second.dev);
+  h->gemm_plans.erase(it);
+  return 0;
+}
+
+extern "C" int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems, int nproblems, int* plan_out) {
+  if (!h || !plan_out) return FTB_E_ARG;
+  RnnPlan plan;
+  const int rc = rnn_plan_build(problems, nproblems, h->num_sms, &plan);
+  if (rc) return rc;
+  const int id = h->next_plan++;
+  h->rnn_plans[id] = plan;
+  *plan_out = id;
+  return 0;
+}
+
+extern "C" int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->rnn_plans.find(plan);
+  if (it == h->rnn_plans.end()) return FTB_E_PLAN;
+  h->launches += static_cast<int64_t>(it->second.launches.size());
+  return rnn_plan_launch(it->second, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ftb_rnn_plan_destroy(ftb_handle h, int plan) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->rnn_plans.find(plan);
+  if (it == h->rnn_plans.end()) return FTB_E_PLAN;
+  cudaFree(it->second.dev);
+  cudaFree(it->second.counters);
+  h->rnn_plans.erase(it);
+  return 0;
+}

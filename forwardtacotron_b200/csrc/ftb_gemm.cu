@@ -1,0 +1,440 @@
+// K1/K2: persistent, warp-specialised implicit-GEMM convolution / linear kernel for sm_100a.
+//
+//   warp 0      : TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
+//   warp 1      : MMA issuer     (one elected lane, tcgen05.mma kind::tf32, fp32 accum in TMEM)
+//   warps 2..5  : epilogue       (tcgen05.ld -> fused ReLU/BN-affine/maxpool/highway -> global)
+//
+// A convolution with k taps is k shifted GEMMs over the same channel-last activation
+// matrix: tap j loads the A tile at row (m0 + tap0 + j).  Sentence edges need no masks
+// because the padded-flat layout keeps >= 8 zero rows between sentences and TMA zero-fills
+// rows outside the tensor (include/ftb200.h).  Two 256-column TMEM accumulators let the
+// epilogue of tile i overlap the MMAs of tile i+1.
+//
+// Precision: operands are fp32 in memory, pre-rounded to tf32 (cvt.rna) by their
+// producers, so the tensor core's mantissa truncation is exact; accumulation is fp32.
+#include <cstdio>
+
+#include "ftb_internal.h"
+#include "ftb_ptx.cuh"
+
+namespace ftb {
+
+constexpr int BM = 128;                 // tile rows  (UMMA M)
+constexpr int BK = 32;                  // fp32 elements per k-block = 128 B = one swizzle row
+constexpr int UMMA_K = 8;               // tf32: 32 bytes per MMA
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = BM * BK * 4;        // 16 KB
+constexpr int B_STAGE_BYTES = 256 * BK * 4;       // 32 KB (bn <= 256)
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int TMEM_COLS = 512;          // 2 accumulators x 256 fp32 columns
+constexpr int NUM_THREADS = 192;
+constexpr int EPI_THREADS = 128;
+constexpr int CHUNK = 16;               // columns per tcgen05.ld
+
+struct SmemTail {
+  uint64_t full[STAGES];
+  uint64_t empty[STAGES];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+  uint32_t pad;
+  float exch[2][4][CHUNK];              // maxpool: last row of each 32-row group, double buffered
+};
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + sizeof(SmemTail) + 1024;   // +1024: manual alignment
+
+struct TileCoord {
+  const GemmProblemDev* p;
+  int m0, n0;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const GemmProblemDev* probs, int nprob, int tile) {
+  int pi = 0;
+  while (pi + 1 < nprob && tile >= probs[pi + 1].tile_base) ++pi;
+  const GemmProblemDev* p = probs + pi;
+  const int local = tile - p->tile_base;
+  const int nt = local % p->n_tiles;
+  const int mt = local / p->n_tiles;
+  return {p, mt * p->m_step + p->m_shift, nt * p->bn};
+}
+
+// ------------------------------------------------------------------------------------------
+// Epilogue math shared by the tensor-core kernel and the SIMT cross-check kernel.
+__device__ __forceinline__ float epi_affine(const GemmProblemDev* p, float acc, int n) {
+  float v = acc + (p->bias0 ? __ldg(p->bias0 + n) : 0.0f);
+  if (p->flags & FTB_F_RELU) v = fmaxf(v, 0.0f);
+  const float s = p->scale ? __ldg(p->scale + n) : 1.0f;
+  const float b = p->shift ? __ldg(p->shift + n) : 0.0f;
+  return v * s + b;     // contracted to one FMA: y = relu(acc)*s + b, s/b precomputed on the host
+}
+__device__ __forceinline__ float epi_highway(float x1, float x2, float x) {
+  const float g = 1.0f / (1.0f + expf(-x2));
+  return g * fmaxf(x1, 0.0f) + (1.0f - g) * x;
+}
+__device__ __forceinline__ float epi_finish(const GemmProblemDev* p, float v) {
+  return (p->flags & FTB_F_ROUND_TF32) ? round_tf32(v) : v;
+}
+
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  SmemTail* tail = reinterpret_cast<SmemTail*>(smem + STAGES * STAGE_BYTES);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&tail->full[s], 1);
+      mbar_init(&tail->empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tail->tmem_full[b], 1);
+      mbar_init(&tail->tmem_empty[b], 4);       // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {                              // whole warp: .sync.aligned
+    tmem_alloc(&tail->tmem_base, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tail->tmem_base;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const GemmProblemDev* last_p = nullptr;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(probs, nprob, tile);
+        const GemmProblemDev* p = tc.p;
+        const uint32_t tx = A_STAGE_BYTES + static_cast<uint32_t>(p->bn) * BK * 4;
+        if (p != last_p) {
+          tma_desc_fence_acquire(&p->tm_a);
+          tma_desc_fence_acquire(&p->tm_w);
+          last_p = p;
+        }
+        for (int tap = 0; tap < p->taps; ++tap) {
+          for (int kb = 0; kb < p->kblocks; ++kb) {
+            mbar_wait(&tail->empty[stage], phase ^ 1u);
+            uint8_t* sa = smem + stage * STAGE_BYTES;
+            uint8_t* sb = sa + A_STAGE_BYTES;
+            mbar_expect_tx(&tail->full[stage], tx);
+            tma_load_2d(sa, &p->tm_a, &tail->full[stage], kb * BK, tc.m0 + p->tap0 + tap);
+            tma_load_2d(sb, &p->tm_w, &tail->full[stage], kb * BK, tap * p->w_tap_rows + tc.n0);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const TileCoord tc = decode_tile(probs, nprob, tile);
+        const GemmProblemDev* p = tc.p;
+        const int buf = it & 1;
+        mbar_wait(&tail->tmem_empty[buf], ((it >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * 256;
+        const uint32_t idesc = umma_idesc_tf32(BM, p->bn);
+        const int kiters = p->taps * p->kblocks;
+        for (int ki = 0; ki < kiters; ++ki) {
+          mbar_wait(&tail->full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint64_t da = umma_desc_sw128(sa);
+          const uint64_t db = umma_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // +32 bytes per UMMA_K step inside the 128-byte swizzle row: +2 in (addr >> 4) units
+            umma_tf32(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&tail->empty[stage]);     // frees the smem slot when these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(&tail->tmem_full[buf]);     // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int g = warp & 3;                       // TMEM lane quarter this warp may read
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const TileCoord tc = decode_tile(probs, nprob, tile);
+      const GemmProblemDev* p = tc.p;
+      const int buf = it & 1;
+      mbar_wait(&tail->tmem_full[buf], (it >> 1) & 1u);
+      tc_fence_after();
+
+      const int lrow = g * 32 + lane;
+      const long long r = static_cast<long long>(tc.m0) + lrow;
+      int t = 0, b = 0;
+      bool valid = (r >= 0) && (r < p->rows);
+      if (valid) {
+        b = static_cast<int>(r / p->seq_stride);
+        t = static_cast<int>(r - static_cast<long long>(b) * p->seq_stride);
+        valid = t < p->seq_len;
+      }
+      const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(g * 32) << 16);
+      const int N = p->n;
+
+      if (p->epilogue == FTB_EPI_HIGHWAY) {
+        const int U = p->bn >> 1;
+        const int units = N >> 1;
+        const int u0 = tc.n0 >> 1;
+        for (int j0 = 0; j0 < U; j0 += CHUNK) {
+          float x1[CHUNK], x2[CHUNK];
+          tmem_ld_32x16(taddr + j0, x1);
+          tmem_ld_32x16(taddr + U + j0, x2);
+          tmem_ld_wait();
+          if (valid) {
+            const int u = u0 + j0;
+            const float* res = p->residual + r * p->res_ld + u;
+            float* o = p->out + r * p->out_ld + p->out_col0 + u;
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 4) {
+              const float4 xr = *reinterpret_cast<const float4*>(res + j);
+              const float xs[4] = {xr.x, xr.y, xr.z, xr.w};
+              float y[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float a1 = x1[j + q] + __ldg(p->bias0 + u + j + q);
+                const float a2 = x2[j + q] + __ldg(p->bias0 + units + u + j + q);
+                y[q] = epi_finish(p, epi_highway(a1, a2, xs[q]));
+              }
+              *reinterpret_cast<float4*>(o + j) = make_float4(y[0], y[1], y[2], y[3]);
+            }
+          }
+        }
+      } else {
+        const bool pool = (p->epilogue == FTB_EPI_MAXPOOL);
+        int chunk_i = 0;
+        for (int c0 = 0; c0 < p->bn; c0 += CHUNK, ++chunk_i) {
+          float v[CHUNK];
+          tmem_ld_32x16(taddr + c0, v);
+          tmem_ld_wait();
+          const int nb = tc.n0 + c0;
+#pragma unroll
+          for (int j = 0; j < CHUNK; ++j) v[j] = (nb + j < N) ? epi_affine(p, v[j], nb + j) : 0.0f;
+          bool store = valid;
+          if (pool) {
+            float (*ex)[CHUNK] = tail->exch[chunk_i & 1];
+            if (lane == 31) {
+#pragma unroll
+              for (int j = 0; j < CHUNK; ++j) ex[g][j] = v[j];
+            }
+            named_bar_sync(1, EPI_THREADS);
+#pragma unroll
+            for (int j = 0; j < CHUNK; ++j) {
+              float prev = __shfl_up_sync(0xffffffffu, v[j], 1);
+              if (lane == 0) prev = (g > 0) ? ex[g - 1][j] : v[j];
+              v[j] = (t == 0) ? v[j] : fmaxf(v[j], prev);
+            }
+            store = valid && (lrow >= 1);           // tile row 0 is the halo row of this tile
+          }
+          if (store) {
+            if (p->residual) {
+              const float* res = p->residual + r * p->res_ld + nb;
+#pragma unroll
+              for (int j = 0; j < CHUNK; ++j)
+                if (nb + j < N) v[j] += __ldg(res + j);
+            }
+            if (p->out_t) {
+              float* ot = p->out_t + (static_cast<long long>(b) * N + nb) * p->seq_len + t;
+#pragma unroll
+              for (int j = 0; j < CHUNK; ++j)
+                if (nb + j < N) ot[static_cast<long long>(j) * p->seq_len] = v[j];
+            }
+            if (p->out) {
+              float* o = p->out + r * p->out_ld + p->out_col0 + nb;
+              if (nb + CHUNK <= N) {
+#pragma unroll
+                for (int j = 0; j < CHUNK; j += 4)
+                  *reinterpret_cast<float4*>(o + j) =
+                      make_float4(epi_finish(p, v[j]), epi_finish(p, v[j + 1]), epi_finish(p, v[j + 2]),
+                                  epi_finish(p, v[j + 3]));
+              } else {
+#pragma unroll
+                for (int j = 0; j < CHUNK; ++j)
+                  if (nb + j < N) o[j] = epi_finish(p, v[j]);
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tail->tmem_empty[buf]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Plain fp32 SIMT kernel over the same problem records: one thread per output element.
+// TEST-ONLY cross-check for the descriptor/swizzle/pipeline logic above (impl = 1).
+__device__ __forceinline__ float simt_acc(const GemmProblemDev* p, long long r, int wrow) {
+  float acc = 0.0f;
+  for (int tap = 0; tap < p->taps; ++tap) {
+    const long long ra = r + p->tap0 + tap;
+    if (ra < 0 || ra >= p->rows) continue;
+    const float* a = p->a + ra * p->lda;
+    const float* w = p->w + (static_cast<long long>(tap) * p->w_tap_rows + wrow) * p->cin;
+    for (int c = 0; c < p->cin; ++c) acc = fmaf(a[c], w[c], acc);
+  }
+  return acc;
+}
+
+__global__ void conv_gemm_simt_kernel(const GemmProblemDev* __restrict__ probs, int nprob) {
+  const GemmProblemDev* p = probs + blockIdx.y;
+  const int N = (p->epilogue == FTB_EPI_HIGHWAY) ? p->n / 2 : p->n;
+  const long long total = p->rows * N;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / N;
+    const int n = static_cast<int>(i - r * N);
+    const int b = static_cast<int>(r / p->seq_stride);
+    const int t = static_cast<int>(r - static_cast<long long>(b) * p->seq_stride);
+    if (t >= p->seq_len) continue;
+    float v;
+    if (p->epilogue == FTB_EPI_HIGHWAY) {
+      const int U = p->bn / 2;
+      const int tile = n / U, j = n % U;
+      const float x1 = simt_acc(p, r, tile * p->bn + j) + p->bias0[n];
+      const float x2 = simt_acc(p, r, tile * p->bn + U + j) + p->bias0[N + n];
+      v = epi_highway(x1, x2, p->residual[r * p->res_ld + n]);
+    } else {
+      v = epi_affine(p, simt_acc(p, r, n), n);
+      if (p->epilogue == FTB_EPI_MAXPOOL && t > 0) v = fmaxf(v, epi_affine(p, simt_acc(p, r - 1, n), n));
+      if (p->residual) v += p->residual[r * p->res_ld + n];
+      if (p->out_t) p->out_t[(static_cast<long long>(b) * N + n) * p->seq_len + t] = v;
+    }
+    if (p->out) p->out[r * p->out_ld + p->out_col0 + n] = epi_finish(p, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Host side: tensor maps and plans.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D fp32 row-major [rows, cols] (leading dimension ld floats), box {32, box_rows}, 128B swizzle.
+static int make_map(CUtensorMap* m, const float* base, long long rows, int cols, int ld, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return FTB_E_DRIVER;
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult res = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return res == CUDA_SUCCESS ? 0 : FTB_E_SHAPE;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* plan) {
+  if (!problems || nproblems < 1 || nproblems > FTB_MAX_PROBLEMS) return FTB_E_ARG;
+  std::vector<GemmProblemDev> host(nproblems);
+  int tile_base = 0;
+  long long simt_elems = 0;
+  for (int i = 0; i < nproblems; ++i) {
+    const ftb_gemm_problem& q = problems[i];
+    GemmProblemDev& d = host[i];
+    if (!q.a || !q.w || (!q.out && !q.out_t)) return FTB_E_ARG;
+    if (q.rows < 1 || q.cin < 1 || q.taps < 1 || q.n < 1) return FTB_E_ARG;
+    if (q.bn < 16 || q.bn > 256 || (q.bn % 16) != 0) return FTB_E_SHAPE;
+    if (q.w_tap_rows < q.n || (q.w_tap_rows % q.bn) != 0) return FTB_E_SHAPE;
+    if ((q.lda % 4) != 0 || (q.cin % 4) != 0 || q.cin > q.lda) return FTB_E_ALIGN;
+    if (!aligned16(q.a) || !aligned16(q.w)) return FTB_E_ALIGN;
+    if (q.out && (!aligned16(q.out) || (q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0)) return FTB_E_ALIGN;
+    if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
+    if (q.rows != static_cast<long long>(q.batch) * q.seq_stride) return FTB_E_ARG;
+    if (q.epilogue == FTB_EPI_HIGHWAY) {
+      if (!q.residual || !q.bias0 || !q.out || (q.n % 2) != 0 || (q.bn % 32) != 0 || (q.n % q.bn) != 0)
+        return FTB_E_SHAPE;
+      if ((q.res_ld % 4) != 0 || !aligned16(q.residual)) return FTB_E_ALIGN;
+    } else if (q.epilogue != FTB_EPI_AFFINE && q.epilogue != FTB_EPI_MAXPOOL) {
+      return FTB_E_ARG;
+    }
+    d.a = q.a; d.w = q.w; d.bias0 = q.bias0; d.scale = q.scale; d.shift = q.shift;
+    d.residual = q.residual; d.out = q.out; d.out_t = q.out_t;
+    d.rows = q.rows; d.lda = q.lda; d.cin = q.cin; d.taps = q.taps; d.tap0 = q.tap0;
+    d.w_tap_rows = q.w_tap_rows; d.n = q.n; d.bn = q.bn; d.epilogue = q.epilogue; d.flags = q.flags;
+    d.res_ld = q.res_ld; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
+    d.batch = q.batch; d.seq_len = q.seq_len; d.seq_stride = q.seq_stride;
+    d.kblocks = (q.cin + BK - 1) / BK;
+    d.n_tiles = (q.n + q.bn - 1) / q.bn;
+    if (q.epilogue == FTB_EPI_MAXPOOL) {
+      d.m_step = BM - 1; d.m_shift = -1;
+    } else {
+      d.m_step = BM; d.m_shift = 0;
+    }
+    d.m_tiles = static_cast<int>((q.rows + d.m_step - 1) / d.m_step);
+    d.tile_base = tile_base;
+    tile_base += d.m_tiles * d.n_tiles;
+    int rc = make_map(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM);
+    if (rc) return rc;
+    rc = make_map(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, q.bn);
+    if (rc) return rc;
+    const long long e = q.rows * q.n;
+    if (e > simt_elems) simt_elems = e;
+  }
+  GemmProblemDev* dev = nullptr;
+  cudaError_t ce = cudaMalloc(&dev, sizeof(GemmProblemDev) * nproblems);
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  ce = cudaMemcpy(dev, host.data(), sizeof(GemmProblemDev) * nproblems, cudaMemcpyHostToDevice);
+  if (ce != cudaSuccess) { cudaFree(dev); return static_cast<int>(ce); }
+  plan->dev = dev; plan->nprob = nproblems; plan->total_tiles = tile_base; plan->simt_elems = simt_elems;
+  return 0;
+}
+
+int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t stream) {
+  if (impl == 1) {
+    long long blocks = (plan.simt_elems + 255) / 256;
+    if (blocks > 65535) blocks = 65535;
+    if (blocks < 1) blocks = 1;
+    dim3 grid(static_cast<unsigned>(blocks), static_cast<unsigned>(plan.nprob));
+    conv_gemm_simt_kernel<<<grid, 256, 0, stream>>>(plan.dev, plan.nprob);
+    return static_cast<int>(cudaGetLastError());
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t ce = cudaFuncSetAttribute(conv_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (ce != cudaSuccess) return static_cast<int>(ce);
+    attr_set = true;
+  }
+  const int grid = plan.total_tiles < num_sms ? plan.total_tiles : num_sms;
+  conv_gemm_tc_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(plan.dev, plan.nprob, plan.total_tiles);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace ftb

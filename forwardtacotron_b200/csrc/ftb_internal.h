@@ -1,0 +1,91 @@
+// Internal declarations shared by the kernel translation units and the C-ABI layer.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <map>
+#include <vector>
+
+#include "../../include/ftb200.h"
+
+namespace ftb {
+
+// ------------------------------------------------------------------ conv-GEMM (ftb_gemm.cu)
+// Device-resident problem record.  CUtensorMap needs 64-byte alignment; the struct is
+// padded to a multiple of 128 bytes and stored in a cudaMalloc'd array.
+struct alignas(128) GemmProblemDev {
+  CUtensorMap tm_a;      // A [rows, cin] fp32, box {32, 128}, SWIZZLE_128B
+  CUtensorMap tm_w;      // W [taps*w_tap_rows, cin] fp32, box {32, bn}, SWIZZLE_128B
+  const float* a;
+  const float* w;
+  const float* bias0;
+  const float* scale;
+  const float* shift;
+  const float* residual;
+  float* out;
+  float* out_t;
+  long long rows;
+  int lda, cin, taps, tap0, w_tap_rows, n, bn, epilogue, flags;
+  int res_ld, out_ld, out_col0;
+  int batch, seq_len, seq_stride;
+  int kblocks;           // ceil(cin / 32)
+  int m_tiles, n_tiles;  // tile grid of this problem
+  int m_step, m_shift;   // tile i covers rows [i*m_step + m_shift, +128)
+  int tile_base;         // first global tile id
+  int pad_[3];
+};
+
+struct GemmPlan {
+  GemmProblemDev* dev = nullptr;
+  int nprob = 0;
+  int total_tiles = 0;
+  long long simt_elems = 0;   // max rows*n over problems (SIMT cross-check grid)
+};
+
+int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* plan);
+int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t stream);
+
+// ------------------------------------------------------------------ recurrences (ftb_rnn.cu)
+struct RnnProblemDev {
+  const float* xproj;
+  const float* w_hh;
+  const float* b_hh;
+  float* out;
+  int cell, hidden, batch, seq_len, seq_stride, out_ld, out_col0;
+  int gates;             // 3 or 4
+  int units_per_cta;     // hidden units owned by one CTA
+  int slices;            // hidden / units_per_cta
+  int batch_per_cta;     // batch columns handled by one CTA (multiple of 8)
+  int bgroups;           // ceil(batch / batch_per_cta)
+  int cta_base;          // first CTA of this part inside its launch
+  int ctas;              // 2 * bgroups * slices
+  int group_base;        // first barrier-counter index (one per (dir, bgroup))
+  int b_begin, b_end;    // batch columns covered by this part (a problem too large for one
+                         // co-resident grid is split into parts that run in successive launches)
+};
+
+struct RnnLaunch {
+  int first = 0, count = 0;           // parts [first, first+count) of RnnPlan::dev
+  int ctas = 0;
+};
+
+struct RnnPlan {
+  RnnProblemDev* dev = nullptr;       // all parts of all launches
+  unsigned int* counters = nullptr;   // one counter per barrier group, zeroed on the stream before each run
+  int ngroups = 0;
+  std::vector<RnnLaunch> launches;
+};
+
+int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan);
+int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream);
+
+}  // namespace ftb
+
+struct ftb_context {
+  int device = 0;
+  int num_sms = 0;
+  int64_t launches = 0;
+  int next_plan = 1;
+  std::map<int, ftb::GemmPlan> gemm_plans;
+  std::map<int, ftb::RnnPlan> rnn_plans;
+};

@@ -1,0 +1,201 @@
+// K5/K6: duration rounding + warp-scan cumsum, and the LengthRegulator gather with the
+// pitch/energy projection add fused into the source read.  HBM-bound integer/copy work:
+// 128-bit accesses, one warp per output row, no tensor cores.
+#include "ftb_internal.h"
+#include "ftb_ptx.cuh"
+
+namespace ftb {
+
+constexpr int SCAN_THREADS = 1024;
+
+// One block per sentence.  Every block recomputes the batch-global fallback predicate
+// (`torch.sum(dur_hat.long()) <= 0`, forward_tacotron.py:176; B*T is a few thousand floats,
+// L2-resident) so no grid-wide dependency is needed.
+__global__ void __launch_bounds__(SCAN_THREADS)
+lr_scan_kernel(float* __restrict__ dur, int batch, int T, int apply_fallback, int32_t* __restrict__ cum,
+               int32_t* __restrict__ lens, int32_t* __restrict__ meta) {
+  __shared__ long long red[32];
+  __shared__ int warp_tot[32];
+  __shared__ int carry_s;
+  __shared__ int flag_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+
+  // ---- fallback predicate: sum over the WHOLE batch of trunc-toward-zero(dur)
+  int flag = 0;
+  if (apply_fallback) {
+    long long s = 0;
+    const long long total = static_cast<long long>(batch) * T;
+    for (long long i = tid; i < total; i += SCAN_THREADS) s += static_cast<long long>(dur[i]);   // (long) truncates
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    if (warp == 0) {
+      long long v = red[lane];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) flag_s = (v <= 0) ? 1 : 0;
+    }
+    __syncthreads();
+    flag = flag_s;
+  }
+  // dur itself is NOT rewritten here: another block may still be summing it.  The in-place
+  // fill/clamp the reference performs is done by lr_finalize_kernel in the next launch.
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+
+  float* d = dur + static_cast<long long>(b) * T;
+  int32_t* c = cum + static_cast<long long>(b) * T;
+  for (int base = 0; base < T; base += SCAN_THREADS) {
+    const int t = base + tid;
+    int rep = 0;
+    if (t < T) {
+      float v = flag ? 2.0f : d[t];
+      if (v < 0.0f) v = 0.0f;                       // dur[dur < 0] = 0      (common_layers.py:18)
+      rep = static_cast<int>(__fadd_rn(v, 0.5f));    // (dur + 0.5).long()    (common_layers.py:21)
+    }
+    int x = rep;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_tot[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      warp_tot[lane] = w;                            // inclusive over warps
+    }
+    __syncthreads();
+    const int before = carry_s + (warp > 0 ? warp_tot[warp - 1] : 0);
+    if (t < T) c[t] = before + x;
+    __syncthreads();
+    if (tid == 0) carry_s += warp_tot[31];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int len = carry_s;
+    lens[b] = len;
+    atomicMax(meta + 0, len);
+    atomicAdd(meta + 2, len);
+    if (b == 0) meta[1] = flag;
+  }
+}
+
+// In-place part of the reference semantics, run after every block of lr_scan_kernel is done:
+// the fallback fill (forward_tacotron.py:177) and the clamp (common_layers.py:18) -- the tensor
+// returned under 'dur' is this one.
+__global__ void lr_finalize_kernel(float* __restrict__ dur, long long n, const int32_t* __restrict__ meta) {
+  const int flag = meta[1];
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = flag ? 2.0f : dur[i];
+    if (v < 0.0f) v = 0.0f;
+    dur[i] = v;
+  }
+}
+
+struct GatherArgs {
+  ftb_lr_gather_args a;
+};
+
+// One warp per output row (b, m).
+__global__ void __launch_bounds__(256)
+lr_gather_kernel(const GatherArgs g) {
+  const ftb_lr_gather_args& a = g.a;
+  const int lane = threadIdx.x & 31;
+  const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
+  if (row >= static_cast<long long>(a.batch) * a.M) return;
+  const int b = static_cast<int>(row / a.M);
+  const int m = static_cast<int>(row - static_cast<long long>(b) * a.M);
+  const int C = a.c1 + a.c2;
+  float* o = a.out + (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
+  const int len = a.lens[b];
+  if (m >= len) {                                   // pad_sequence(padding_value=0.)
+    for (int c = lane * 4; c < C; c += 128) *reinterpret_cast<float4*>(o + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.idx && lane == 0) a.idx[row] = -1;
+    return;
+  }
+  // searchsorted(cum, m, right): first t with cum[t] > m
+  const int32_t* cum = a.cum + static_cast<long long>(b) * a.T;
+  int lo = 0, hi = a.T - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(cum + mid) > m) hi = mid; else lo = mid + 1;
+  }
+  const int t = lo;
+  if (a.idx && lane == 0) a.idx[row] = t;
+
+  const float* xs = a.x + (static_cast<long long>(b) * a.x_stride + t) * a.x_ld;
+  float pm = 0.f, p0 = 0.f, pp = 0.f, em = 0.f, e0 = 0.f, ep = 0.f;
+  const bool proj = (a.pitch != nullptr);
+  if (proj) {
+    const float* pr = a.pitch + static_cast<long long>(b) * a.T;
+    const float* er = a.energy + static_cast<long long>(b) * a.T;
+    p0 = pr[t]; e0 = er[t];
+    if (t > 0) { pm = pr[t - 1]; em = er[t - 1]; }
+    if (t + 1 < a.T) { pp = pr[t + 1]; ep = er[t + 1]; }
+  }
+  for (int c = lane * 4; c < C; c += 128) {
+    float4 v;
+    if (c < a.c1) v = *reinterpret_cast<const float4*>(xs + c);
+    else v = *reinterpret_cast<const float4*>(a.extra + static_cast<long long>(b) * a.c2 + (c - a.c1));
+    if (proj) {
+      float* vv = reinterpret_cast<float*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float* wp = a.wp + (c + j) * 3;
+        const float* we = a.we + (c + j) * 3;
+        // Conv1d(1->C, k=3, pad=1) + bias, scaled add (forward_tacotron.py:214-220)
+        const float pc = __fadd_rn(__fmaf_rn(wp[2], pp, __fmaf_rn(wp[1], p0, __fmul_rn(wp[0], pm))), a.bp[c + j]);
+        const float ec = __fadd_rn(__fmaf_rn(we[2], ep, __fmaf_rn(we[1], e0, __fmul_rn(we[0], em))), a.be[c + j]);
+        vv[j] = __fadd_rn(__fadd_rn(vv[j], __fmul_rn(pc, a.ps)), __fmul_rn(ec, a.es));
+      }
+    }
+    if (a.round_tf32) {
+      v.x = round_tf32(v.x); v.y = round_tf32(v.y); v.z = round_tf32(v.z); v.w = round_tf32(v.w);
+    }
+    *reinterpret_cast<float4*>(o + c) = v;
+  }
+}
+
+}  // namespace ftb
+
+using namespace ftb;
+
+extern "C" int ftb_lr_scan(ftb_handle h, float* dur, int batch, int T, int apply_fallback, int32_t* cum,
+                           int32_t* lens, int32_t* meta, void* stream) {
+  if (!h || !dur || !cum || !lens || !meta || batch < 1 || T < 1) return FTB_E_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t ce = cudaMemsetAsync(meta, 0, 4 * sizeof(int32_t), st);
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  lr_scan_kernel<<<batch, SCAN_THREADS, 0, st>>>(dur, batch, T, apply_fallback, cum, lens, meta);
+  const long long n = static_cast<long long>(batch) * T;
+  int blocks = static_cast<int>((n + 255) / 256);
+  if (blocks > 1184) blocks = 1184;
+  lr_finalize_kernel<<<blocks, 256, 0, st>>>(dur, n, meta);
+  h->launches += 2;
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void* stream) {
+  if (!h || !args || !args->x || !args->cum || !args->lens || !args->out) return FTB_E_ARG;
+  const ftb_lr_gather_args& a = *args;
+  if (a.batch < 1 || a.T < 1 || a.M < 0) return FTB_E_ARG;
+  if ((a.c1 % 4) || (a.c2 % 4) || (a.x_ld % 4) || (a.out_ld % 4)) return FTB_E_ALIGN;
+  if ((reinterpret_cast<uintptr_t>(a.x) | reinterpret_cast<uintptr_t>(a.out)) & 15u) return FTB_E_ALIGN;
+  if (a.c2 > 0 && (!a.extra || (reinterpret_cast<uintptr_t>(a.extra) & 15u))) return FTB_E_ARG;
+  if (a.pitch && (!a.energy || !a.wp || !a.bp || !a.we || !a.be)) return FTB_E_ARG;
+  if (a.M == 0) return 0;
+  GatherArgs g{a};
+  const long long rows = static_cast<long long>(a.batch) * a.M;
+  lr_gather_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(g);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}

@@ -1,0 +1,102 @@
+// Small glue kernels: embedding gather into the padded-flat layout, predictor head
+// (row dot products), arg-max over a tiny class axis.  All are bandwidth/latency trivial
+// next to the GEMMs and recurrences; one warp per row, coalesced accesses.
+#include "ftb_internal.h"
+#include "ftb_ptx.cuh"
+
+namespace ftb {
+
+__global__ void __launch_bounds__(256)
+embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
+             const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
+             const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
+             float* __restrict__ out, int out_ld, int round) {
+  const int lane = threadIdx.x & 31;
+  const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
+  if (row >= static_cast<long long>(batch) * T) return;
+  const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
+  float* o = out + (static_cast<long long>(b) * seq_stride + t) * out_ld;
+  const float* s1 = table + tok[row] * e1;
+  for (int c = lane; c < e1; c += 32) o[c] = round ? round_tf32(s1[c]) : s1[c];
+  if (e2 > 0) {
+    const float* s2 = table2 + tok2[row] * e2;
+    for (int c = lane; c < e2; c += 32) o[e1 + c] = round ? round_tf32(s2[c]) : s2[c];
+  }
+  if (e3 > 0) {
+    const float* s3 = extra + static_cast<long long>(b) * e3;
+    for (int c = lane; c < e3; c += 32) o[e1 + e2 + c] = round ? round_tf32(s3[c]) : s3[c];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+rowdot_kernel(const float* __restrict__ x, int x_ld, int k, const float* __restrict__ w,
+              const float* __restrict__ bias, int n_out, float inv_alpha, int batch, int T, int seq_stride,
+              float* __restrict__ y) {
+  const int lane = threadIdx.x & 31;
+  const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
+  if (row >= static_cast<long long>(batch) * T) return;
+  const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
+  const float* xr = x + (static_cast<long long>(b) * seq_stride + t) * x_ld;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int c = lane; c < k; c += 32) {
+    const float xv = xr[c];
+#pragma unroll
+    for (int o = 0; o < 4; ++o)
+      if (o < n_out) acc[o] = fmaf(xv, __ldg(w + o * k + c), acc[o]);
+  }
+#pragma unroll
+  for (int o = 0; o < 4; ++o) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
+  }
+  if (lane == 0) {
+    for (int o = 0; o < n_out; ++o) y[row * n_out + o] = (acc[o] + bias[o]) * inv_alpha;
+  }
+}
+
+__global__ void argmax_kernel(const float* __restrict__ x, long long n, int c, int64_t* __restrict__ out) {
+  const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  const float* r = x + i * c;
+  int best = 0;
+  float bv = r[0];
+  for (int j = 1; j < c; ++j) {
+    if (r[j] > bv) { bv = r[j]; best = j; }     // first maximum wins, like torch.argmax
+  }
+  out[i] = best;
+}
+
+}  // namespace ftb
+
+using namespace ftb;
+
+extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1, const int64_t* tok2,
+                         const float* table2, int e2, const float* extra, int e3, int batch, int T, int seq_stride,
+                         float* out, int out_ld, int round_tf32, void* stream) {
+  if (!h || !tok || !table || !out || e1 < 1 || batch < 1 || T < 1) return FTB_E_ARG;
+  if (e2 > 0 && (!tok2 || !table2)) return FTB_E_ARG;
+  if (e3 > 0 && !extra) return FTB_E_ARG;
+  if (e1 + e2 + e3 > out_ld || seq_stride < T) return FTB_E_ARG;
+  const long long rows = static_cast<long long>(batch) * T;
+  embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, round_tf32);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int ftb_rowdot(ftb_handle h, const float* x, int x_ld, int k, const float* w, const float* bias,
+                          int n_out, float inv_alpha, int batch, int T, int seq_stride, float* y, void* stream) {
+  if (!h || !x || !w || !bias || !y || n_out < 1 || n_out > 4 || k < 1 || batch < 1 || T < 1) return FTB_E_ARG;
+  const long long rows = static_cast<long long>(batch) * T;
+  rowdot_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, x_ld, k, w, bias, n_out, inv_alpha, batch, T, seq_stride, y);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int ftb_argmax_lastdim(ftb_handle h, const float* x, int64_t n, int c, int64_t* out, void* stream) {
+  if (!h || !x || !out || n < 1 || c < 1 || c > 8) return FTB_E_ARG;
+  argmax_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, c, out);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}

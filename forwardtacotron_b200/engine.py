@@ -1,0 +1,201 @@
+"""Launch programs for the mel-synthesis path: buffers + plans built once per shape.
+
+A `Program` is an ordered list of native launches (GEMM plans, recurrence plans, glue
+kernels) over a fixed set of device buffers in the padded-flat channel-last layout
+(include/ftb200.h).  Independent layers that are ready at the same time are grouped into
+ONE persistent GEMM launch (e.g. the three predictors' first convolutions and the 16 bank
+convolutions), so the SMs see a few hundred tiles per launch instead of ~100.
+"""
+from typing import Callable, Dict, List, Optional
+
+import torch
+
+from . import runtime as rt
+from .pack import PackedGemm, PackedRnn
+
+
+class Geometry:
+    """Row geometry of a [batch, seq_len, C] activation in the padded-flat layout."""
+
+    def __init__(self, batch: int, seq_len: int):
+        self.batch, self.seq_len = batch, seq_len
+        self.stride = rt.seq_stride(seq_len)
+        self.rows = batch * self.stride
+
+
+class Program:
+    def __init__(self, handle: rt.Handle, geo: Geometry):
+        self.h, self.geo = handle, geo
+        self.device = handle.device
+        self.bufs: Dict[str, torch.Tensor] = {}
+        self.steps: List[Callable[[], None]] = []
+        self._gemm_plans: List[int] = []
+        self._rnn_plans: List[int] = []
+        self._pending: List[rt.GemmProblem] = []
+        self._keep: list = []                         # tensors the plans point into
+
+    # ---- buffers ---------------------------------------------------------------------------
+    def buf(self, name: str, cols: int) -> torch.Tensor:
+        """Zero-initialised [rows, cols] activation; gap rows are never written so they stay zero."""
+        if name not in self.bufs:
+            self.bufs[name] = torch.zeros((self.geo.rows, cols), dtype=torch.float32, device=self.device)
+        b = self.bufs[name]
+        assert b.shape[1] == cols, (name, b.shape, cols)
+        return b
+
+    def dense(self, name: str, shape, dtype=torch.float32) -> torch.Tensor:
+        if name not in self.bufs:
+            self.bufs[name] = torch.zeros(shape, dtype=dtype, device=self.device)
+        return self.bufs[name]
+
+    def view(self, name: str) -> torch.Tensor:
+        """[batch, seq_len, C] view of a padded-flat buffer (valid rows only)."""
+        b = self.bufs[name]
+        g = self.geo
+        return b.view(g.batch, g.stride, b.shape[1])[:, :g.seq_len]
+
+    # ---- GEMM problems: queued, then flushed as one persistent launch ------------------------
+    def gemm(self, a: torch.Tensor, w: PackedGemm, out: Optional[torch.Tensor], *, out_col0: int = 0,
+             epilogue: int = rt.EPI_AFFINE, round_out: bool = True, residual: Optional[torch.Tensor] = None,
+             out_t: Optional[torch.Tensor] = None, cin: Optional[int] = None):
+        g = self.geo
+        p = rt.GemmProblem()
+        p.a, p.rows, p.lda = a.data_ptr(), g.rows, a.shape[1]
+        p.cin = cin if cin is not None else w.cin
+        assert p.cin == w.cin and p.cin <= a.shape[1], (p.cin, w.cin, a.shape)
+        p.w, p.taps, p.tap0, p.w_tap_rows = w.w.data_ptr(), w.taps, w.tap0, w.n_pad
+        p.n, p.bn, p.epilogue = w.n, w.bn, epilogue
+        p.flags = (rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out else 0)
+        p.bias0, p.scale, p.shift = rt.ptr(w.bias0), rt.ptr(w.scale), rt.ptr(w.shift)
+        p.residual = rt.ptr(residual)
+        p.res_ld = residual.shape[1] if residual is not None else 0
+        p.out = rt.ptr(out)
+        p.out_ld = out.shape[1] if out is not None else 0
+        p.out_col0 = out_col0
+        p.out_t = rt.ptr(out_t)
+        p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
+        self._pending.append(p)
+        self._keep += [a, w, out, residual, out_t]
+
+    def flush(self):
+        """Close the current group: everything queued since the last flush runs as one launch."""
+        if not self._pending:
+            return
+        # heaviest tiles first (tile cost ~ taps*cin*bn) for the static round-robin scheduler
+        probs = sorted(self._pending, key=lambda q: -(q.taps * q.cin * q.bn))
+        self._pending = []
+        for i in range(0, len(probs), 32):
+            plan = self.h.gemm_plan(probs[i:i + 32])
+            self._gemm_plans.append(plan)
+            self.steps.append(lambda plan=plan: self.h.gemm_run(plan))
+
+    def rnn(self, specs):
+        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one cooperative launch."""
+        self.flush()
+        g = self.geo
+        probs = []
+        for r, xproj, out, col0 in specs:
+            p = rt.RnnProblem()
+            p.cell, p.hidden = r.cell, r.hidden
+            p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
+            p.xproj, p.w_hh, p.b_hh = xproj.data_ptr(), r.w_hh.data_ptr(), r.b_hh.data_ptr()
+            p.out, p.out_ld, p.out_col0 = out.data_ptr(), out.shape[1], col0
+            probs.append(p)
+            self._keep += [r, xproj, out]
+        plan = self.h.rnn_plan(probs)
+        self._rnn_plans.append(plan)
+        self.steps.append(lambda plan=plan: self.h.rnn_run(plan))
+
+    def call(self, fn: Callable[[], None]):
+        self.flush()
+        self.steps.append(fn)
+
+    def run(self):
+        for s in self.steps:
+            s()
+
+    def close(self):
+        for p in self._gemm_plans:
+            self.h.gemm_destroy(p)
+        for p in self._rnn_plans:
+            self.h.rnn_destroy(p)
+        self._gemm_plans, self._rnn_plans, self.steps = [], [], []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# -------------------------------------------------------------------------------------------
+# Layer groups.  Each `stage_*` function queues the GEMMs of ONE dependency level; the caller
+# interleaves levels of independent branches and flushes between levels.
+# -------------------------------------------------------------------------------------------
+
+class CbhgPack:
+    """Packed weights of one CBHG (common_layers.py:60-124)."""
+
+    def __init__(self, bank: List[PackedGemm], proj1: PackedGemm, proj2: PackedGemm, pre_highway: PackedGemm,
+                 highways: List[PackedGemm], rnn: PackedRnn, in_channels: int, channels: int):
+        self.bank, self.proj1, self.proj2 = bank, proj1, proj2
+        self.pre_highway, self.highways, self.rnn = pre_highway, highways, rnn
+        self.in_channels, self.channels = in_channels, channels
+
+
+def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torch.Tensor, out_col0: int = 0):
+    """Returns the list of per-level closures for one CBHG over input buffer x [rows, in_channels];
+    level i may be queued only after level i-1 has been flushed.  The last entry runs the BiGRU."""
+    K = len(c.bank)
+    ch = c.channels
+    bank = prog.buf(f'{tag}.bank', K * ch)
+    p1 = prog.buf(f'{tag}.proj1', c.proj1.n)
+    p2 = prog.buf(f'{tag}.proj2', c.proj2.n)
+    hw = [prog.buf(f'{tag}.hw0', ch), prog.buf(f'{tag}.hw1', ch)]
+    xp = prog.buf(f'{tag}.xproj', c.rnn.ih.n)
+    levels = []
+
+    def l_bank():   # conv bank k=1..K, each trimmed to L, ReLU->BN, + MaxPool1d(2,1,1)[:L] fused (:97-105)
+        for k, w in enumerate(c.bank):
+            prog.gemm(x, w, bank, out_col0=k * ch, epilogue=rt.EPI_MAXPOOL)
+    levels.append(l_bank)
+    levels.append(lambda: prog.gemm(bank, c.proj1, p1))                               # :109
+    levels.append(lambda: prog.gemm(p1, c.proj2, p2, residual=x))                     # :111-114
+    levels.append(lambda: prog.gemm(p2, c.pre_highway, hw[0]))                        # :118
+    for i, w in enumerate(c.highways):                                                # :119-120
+        levels.append(lambda i=i, w=w: prog.gemm(hw[i & 1], w, hw[(i + 1) & 1], epilogue=rt.EPI_HIGHWAY,
+                                                 residual=hw[i & 1]))
+    last = hw[len(c.highways) & 1]
+    levels.append(lambda: prog.gemm(last, c.rnn.ih, xp, round_out=False))             # W_ih half of :123
+    return levels, (c.rnn, xp, out, out_col0)
+
+
+class PredictorPack:
+    """Packed weights of one SeriesPredictor (forward_tacotron.py:14-39 and the multi variants)."""
+
+    def __init__(self, convs: List[PackedGemm], rnn: PackedRnn, lin_w: torch.Tensor, lin_b: torch.Tensor):
+        self.convs, self.rnn = convs, rnn
+        self.lin_w = lin_w.detach().float().contiguous()
+        self.lin_b = lin_b.detach().float().contiguous()
+
+
+def predictor_levels(prog: Program, tag: str, p: PredictorPack, emb: torch.Tensor):
+    ch = p.convs[0].n
+    c = [prog.buf(f'{tag}.c0', ch), prog.buf(f'{tag}.c1', ch)]
+    xp = prog.buf(f'{tag}.xproj', p.rnn.ih.n)
+    h = prog.buf(f'{tag}.h', 2 * p.rnn.hidden)
+    levels = [lambda: prog.gemm(emb, p.convs[0], c[0]),
+              lambda: prog.gemm(c[0], p.convs[1], c[1]),
+              lambda: prog.gemm(c[1], p.convs[2], c[0]),
+              lambda: prog.gemm(c[0], p.rnn.ih, xp, round_out=False)]
+    return levels, (p.rnn, xp, h, 0), h
+
+
+def run_levels(prog: Program, branches: List[list]):
+    """Queue level i of every branch, flush, then level i+1, ...  (branches are independent)."""
+    depth = max(len(b) for b in branches)
+    for i in range(depth):
+        for b in branches:
+            if i < len(b):
+                b[i]()
+        prog.flush()

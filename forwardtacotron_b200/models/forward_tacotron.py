@@ -1,0 +1,245 @@
+"""ForwardTacotron with the single-pass inference path on sm_100a kernels.
+
+Drop-in for the reference's `models/forward_tacotron.py`: same constructor kwargs
+(forward_tacotron.py:44-69), same state_dict (322 entries), same `generate` / `forward` /
+`from_config` / `from_checkpoint` / `get_step` surface.  `generate()` and `_generate_mel()`
+run entirely on libftb200.so (there is no PyTorch fallback on that path); the training-mode
+`forward(batch)` stays stock PyTorch over the very same parameters.
+"""
+from pathlib import Path
+from typing import Any, Callable, Dict, Union
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
+
+from .. import engine as eng
+from .. import pack as pk
+from .. import runtime as rt
+from ..configs import NUM_CHARS
+from . import _accel
+from .common_layers import CBHG, BatchNormConv, LengthRegulator
+
+
+class SeriesPredictor(nn.Module):
+    """embedding -> 3x BatchNormConv(k=5) -> BiGRU -> Linear(1) -> /alpha."""
+
+    def __init__(self, num_chars, emb_dim=64, conv_dims=256, rnn_dims=64, dropout=0.5):
+        super().__init__()
+        self.embedding = nn.Embedding(num_chars, emb_dim)
+        dims = [emb_dim, conv_dims, conv_dims, conv_dims]
+        self.convs = nn.ModuleList([BatchNormConv(dims[i], dims[i + 1], 5, relu=True) for i in range(3)])
+        self.rnn = nn.GRU(conv_dims, rnn_dims, batch_first=True, bidirectional=True)
+        self.lin = nn.Linear(2 * rnn_dims, 1)
+        self.dropout = dropout
+
+    def forward(self, x: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
+        y = self.embedding(x).transpose(1, 2)
+        for conv in self.convs:
+            y = F.dropout(conv(y), p=self.dropout, training=self.training)
+        y = self.rnn(y.transpose(1, 2))[0]
+        return self.lin(y) / alpha
+
+
+class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
+
+    def __init__(self,
+                 embed_dims: int, series_embed_dims: int, num_chars: int,
+                 durpred_conv_dims: int, durpred_rnn_dims: int, durpred_dropout: float,
+                 pitch_conv_dims: int, pitch_rnn_dims: int, pitch_dropout: float, pitch_strength: float,
+                 energy_conv_dims: int, energy_rnn_dims: int, energy_dropout: float, energy_strength: float,
+                 rnn_dims: int, prenet_dims: int, prenet_k: int, postnet_num_highways: int,
+                 prenet_dropout: float, postnet_dims: int, postnet_k: int, prenet_num_highways: int,
+                 postnet_dropout: float, n_mels: int, padding_value=-11.5129):
+        super().__init__()
+        self.rnn_dims = rnn_dims
+        self.padding_value = padding_value
+        self.n_mels = n_mels
+        self.embedding = nn.Embedding(num_chars, embed_dims)
+        self.lr = LengthRegulator()
+        self.dur_pred = SeriesPredictor(num_chars, series_embed_dims, durpred_conv_dims, durpred_rnn_dims,
+                                        durpred_dropout)
+        self.pitch_pred = SeriesPredictor(num_chars, series_embed_dims, pitch_conv_dims, pitch_rnn_dims,
+                                          pitch_dropout)
+        self.energy_pred = SeriesPredictor(num_chars, series_embed_dims, energy_conv_dims, energy_rnn_dims,
+                                           energy_dropout)
+        self.prenet = CBHG(K=prenet_k, in_channels=embed_dims, channels=prenet_dims,
+                           proj_channels=[prenet_dims, embed_dims], num_highways=prenet_num_highways,
+                           dropout=prenet_dropout)
+        self.lstm = nn.LSTM(2 * prenet_dims, rnn_dims, batch_first=True, bidirectional=True)
+        self.lin = nn.Linear(2 * rnn_dims, n_mels)
+        self.register_buffer('step', torch.zeros(1, dtype=torch.long))
+        self.postnet = CBHG(K=postnet_k, in_channels=n_mels, channels=postnet_dims,
+                            proj_channels=[postnet_dims, n_mels], num_highways=postnet_num_highways,
+                            dropout=postnet_dropout)
+        self.post_proj = nn.Linear(2 * postnet_dims, n_mels, bias=False)
+        self.pitch_strength = pitch_strength
+        self.energy_strength = energy_strength
+        self.pitch_proj = nn.Conv1d(1, 2 * prenet_dims, kernel_size=3, padding=1)
+        self.energy_proj = nn.Conv1d(1, 2 * prenet_dims, kernel_size=3, padding=1)
+
+    def __repr__(self):
+        return f'ForwardTacotron, num params: {sum(int(np.prod(p.size())) for p in self.parameters())}'
+
+    def get_step(self) -> int:
+        return self.step.data.item()
+
+    # ------------------------------------------------------------------ training path (stock torch)
+    def forward(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        x, mel_len = batch['x'], batch['mel_len']
+        target_len = batch['mel'].size(2)
+        if self.training:
+            self.step += 1
+        dur_hat = self.dur_pred(x).squeeze(-1)
+        pitch_hat = self.pitch_pred(x).transpose(1, 2)
+        energy_hat = self.energy_pred(x).transpose(1, 2)
+
+        h = self.prenet(self.embedding(x).transpose(1, 2))
+        h = h + self.pitch_proj(batch['pitch'].unsqueeze(1)).transpose(1, 2) * self.pitch_strength
+        h = h + self.energy_proj(batch['energy'].unsqueeze(1)).transpose(1, 2) * self.energy_strength
+        h = self.lr(h, batch['dur'])
+        packed = pack_padded_sequence(h, lengths=mel_len.cpu(), enforce_sorted=False, batch_first=True)
+        h, _ = pad_packed_sequence(self.lstm(packed)[0], padding_value=self.padding_value, batch_first=True)
+        mel = self.lin(h).transpose(1, 2)
+        mel_post = self.post_proj(self.postnet(mel)).transpose(1, 2)
+        return {'mel': self._pad(mel, target_len), 'mel_post': self._pad(mel_post, target_len),
+                'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat}
+
+    def _pad(self, x: torch.Tensor, max_len: int) -> torch.Tensor:
+        x = x[:, :, :max_len]
+        return F.pad(x, [0, max_len - x.size(2), 0, 0], 'constant', self.padding_value)
+
+    # ------------------------------------------------------------------ accelerated inference path
+    def _build_packs(self) -> dict:
+        return {
+            'embedding': pk.round_tf32(self.embedding.weight),
+            'dur': _accel.pack_predictor(self.dur_pred), 'dur_emb': pk.round_tf32(self.dur_pred.embedding.weight),
+            'pitch': _accel.pack_predictor(self.pitch_pred),
+            'pitch_emb': pk.round_tf32(self.pitch_pred.embedding.weight),
+            'energy': _accel.pack_predictor(self.energy_pred),
+            'energy_emb': pk.round_tf32(self.energy_pred.embedding.weight),
+            'prenet': _accel.pack_cbhg(self.prenet),
+            'lstm': pk.PackedRnn(self.lstm),
+            'lin': pk.pack_linear(self.lin.weight, self.lin.bias),
+            'postnet': _accel.pack_cbhg(self.postnet),
+            'post_proj': pk.pack_linear(self.post_proj.weight),
+            'pitch_proj': (self.pitch_proj.weight.detach().float().reshape(-1, 3).contiguous(),
+                           self.pitch_proj.bias.detach().float().contiguous()),
+            'energy_proj': (self.energy_proj.weight.detach().float().reshape(-1, 3).contiguous(),
+                            self.energy_proj.bias.detach().float().contiguous()),
+        }
+
+    def _token_program(self, st: dict, batch: int, T: int, predictors: bool, prenet: bool) -> eng.Program:
+        """Phoneme-side program: (optionally) the three SeriesPredictors and the embedding + CBHG prenet,
+        level-interleaved so each persistent GEMM launch carries every branch's ready layer."""
+        packs, h = st['packs'], st['handle']
+        geo = eng.Geometry(batch, T)
+        prog = eng.Program(h, geo)
+        tok = prog.dense('tok', (batch, T), torch.int64)
+        branches, grus, heads = [], [], []
+        if predictors:
+            for name in ('dur', 'pitch', 'energy'):
+                p = packs[name]
+                emb = prog.buf(f'{name}.emb', packs[name + '_emb'].shape[1])
+                prog.call(lambda emb=emb, name=name: h.embed(tok, packs[name + '_emb'], emb, emb.shape[1],
+                                                             batch, T, geo.stride))
+                levels, gru, hbuf = eng.predictor_levels(prog, name, p, emb)
+                branches.append(levels)
+                grus.append(gru)
+                heads.append((name, p, hbuf))
+        if prenet:
+            emb = prog.buf('emb', packs['embedding'].shape[1])
+            prog.call(lambda: h.embed(tok, packs['embedding'], emb, emb.shape[1], batch, T, geo.stride))
+            out = prog.buf('prenet.h', 2 * packs['prenet'].rnn.hidden)
+            levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out)
+            branches.append(levels)
+            grus.append(gru)
+        eng.run_levels(prog, branches)
+        prog.rnn(grus)
+        for name, p, hbuf in heads:
+            y = prog.dense(f'{name}.y', (batch, T))
+            prog.call(lambda p=p, hbuf=hbuf, y=y, name=name: h.rowdot(
+                hbuf, hbuf.shape[1], hbuf.shape[1], p.lin_w, p.lin_b, 1,
+                (1.0 / prog.alpha) if name == 'dur' else 1.0, batch, T, geo.stride, y))
+        prog.alpha = 1.0
+        return prog
+
+    def generate(self,
+                 x: torch.Tensor,
+                 alpha=1.0,
+                 pitch_function: Callable[[torch.Tensor], torch.Tensor] = lambda x: x,
+                 energy_function: Callable[[torch.Tensor], torch.Tensor] = lambda x: x) -> Dict[str, torch.Tensor]:
+        self.eval()
+        self._check_tokens(x)
+        with torch.no_grad():
+            st = self._accel_state(x.device)
+            B, T = x.shape
+            prog = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True, True))
+            prog.bufs['tok'].copy_(x)
+            prog.alpha = float(alpha)
+            prog.run()
+            dur_hat = prog.bufs['dur.y'].clone()                               # [B,T]  (dur_pred(x)/alpha).squeeze(2)
+            scan = _accel.length_regulate(st['handle'], dur_hat, apply_fallback=True)   # :176-177 (+ LR clamp)
+            pitch_hat = pitch_function(prog.bufs['pitch.y'].clone().unsqueeze(1))       # [B,1,T]
+            energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
+            return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
+
+    def _generate_mel(self, x: torch.Tensor, dur_hat: torch.Tensor, pitch_hat: torch.Tensor,
+                      energy_hat: torch.Tensor) -> Dict[str, torch.Tensor]:
+        """Teacher-forced entry (forward_tacotron.py:205-234): durations/pitch/energy supplied by the caller."""
+        self._check_tokens(x)
+        with torch.no_grad():
+            st = self._accel_state(x.device)
+            B, T = x.shape
+            prog = self._program(st, ('prenet', B, T), lambda: self._token_program(st, B, T, False, True))
+            prog.bufs['tok'].copy_(x)
+            prog.run()
+            if not (dur_hat.is_cuda and dur_hat.dtype == torch.float32 and dur_hat.is_contiguous()):
+                raise RuntimeError('_generate_mel(): dur_hat must be a contiguous fp32 CUDA tensor [B,T]')
+            scan = _accel.length_regulate(st['handle'], dur_hat, apply_fallback=False)
+            return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
+
+    def _mel_from_prenet(self, st, tok_prog, dur_hat, pitch_hat, energy_hat, scan) -> Dict[str, torch.Tensor]:
+        packs, h = st['packs'], st['handle']
+        cum, lens, M, total = scan
+        B, T = dur_hat.shape
+        if M <= 0:
+            raise RuntimeError('generate(): all rounded durations are zero -- nothing to synthesise')
+        pre = tok_prog.bufs['prenet.h']
+        C = pre.shape[1]
+        prog = self._program(st, ('frame', B, M), lambda: _accel.build_frame_program(h, packs, B, M, C, self.n_mels))
+        pitch = pitch_hat.reshape(B, T).to(torch.float32).contiguous()
+        energy = energy_hat.reshape(B, T).to(torch.float32).contiguous()
+        g = rt.LrGatherArgs()
+        g.x, g.x_stride, g.x_ld, g.c1 = pre.data_ptr(), tok_prog.geo.stride, C, C
+        g.extra, g.c2 = None, 0
+        g.pitch, g.energy = pitch.data_ptr(), energy.data_ptr()
+        (wp, bp), (we, be) = packs['pitch_proj'], packs['energy_proj']
+        g.wp, g.bp, g.ps = wp.data_ptr(), bp.data_ptr(), float(self.pitch_strength)
+        g.we, g.be, g.es = we.data_ptr(), be.data_ptr(), float(self.energy_strength)
+        g.cum, g.lens = cum.data_ptr(), lens.data_ptr()
+        g.batch, g.T, g.M = B, T, M
+        lr = prog.bufs['lr']
+        g.out, g.out_stride, g.out_ld = lr.data_ptr(), prog.geo.stride, C
+        g.idx, g.round_tf32 = None, 1
+        h.lr_gather(g)                                                        # :214-222
+        prog.run()                                                            # :224-231
+        return {'mel': prog.bufs['mel'].clone(), 'mel_post': prog.bufs['mel_post'].clone(), 'dur': dur_hat,
+                'pitch': pitch_hat, 'energy': energy_hat}
+
+    # ------------------------------------------------------------------ construction helpers
+    @classmethod
+    def from_config(cls, config: Dict[str, Any]) -> 'ForwardTacotron':
+        kwargs = config['forward_tacotron']['model']
+        kwargs['num_chars'] = NUM_CHARS
+        kwargs['n_mels'] = config['dsp']['num_mels']
+        return cls(**kwargs)
+
+    @classmethod
+    def from_checkpoint(cls, path: Union[Path, str]) -> 'ForwardTacotron':
+        ckpt = torch.load(path, map_location=torch.device('cpu'))
+        model = cls.from_config(ckpt['config'])
+        model.load_state_dict(ckpt['model'])
+        return model

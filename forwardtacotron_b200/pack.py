@@ -1,0 +1,97 @@
+"""Weight repacking: torch parameters -> the layouts libftb200.so consumes.
+
+Derived, cached data only: the nn.Parameters stay the source of truth (state_dict keys are
+unchanged) and a pack is rebuilt whenever the parameters' versions change.
+All GEMM operands are rounded to tf32 (round-to-nearest, ties away: what cvt.rna.tf32.f32
+does) here, once, so the tensor core's operand truncation is exact.
+"""
+from typing import Optional
+
+import torch
+
+BN_EPS = 1e-5
+
+
+def round_tf32(t: torch.Tensor) -> torch.Tensor:
+    """fp32 -> nearest tf32 (10-bit mantissa), ties away from zero; bit-identical to cvt.rna.tf32.f32
+    for finite inputs."""
+    i = t.detach().contiguous().to(torch.float32).view(torch.int32)
+    return ((i + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+def ceil_to(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def pick_bn(n: int) -> int:
+    """N-tile width of the tcgen05 kernel: multiple of 16, at most 256."""
+    return min(256, ceil_to(n, 16))
+
+
+class PackedGemm:
+    """A conv / linear weight as [taps][n_pad][cin] (K-major, tf32-rounded) + epilogue vectors."""
+
+    def __init__(self, w: torch.Tensor, taps: int, tap0: int, n: int, bn: int,
+                 bias0: Optional[torch.Tensor] = None, scale: Optional[torch.Tensor] = None,
+                 shift: Optional[torch.Tensor] = None, relu: bool = False):
+        self.w, self.taps, self.tap0, self.n, self.bn = w, taps, tap0, n, bn
+        self.n_pad = w.shape[1]
+        self.cin = w.shape[2]
+        self.bias0, self.scale, self.shift, self.relu = bias0, scale, shift, relu
+
+
+def _f(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    return None if t is None else t.detach().to(torch.float32).contiguous()
+
+
+def pack_conv(weight: torch.Tensor, bias: Optional[torch.Tensor] = None, bn: Optional[int] = None,
+              scale=None, shift=None, relu=False) -> PackedGemm:
+    """Conv1d weight [Cout, Cin, k] (padding k//2, common_layers.py:50) -> taps x [Cout_pad, Cin]."""
+    cout, cin, k = weight.shape
+    bn = bn or pick_bn(cout)
+    n_pad = ceil_to(cout, bn)
+    w = weight.new_zeros((k, n_pad, cin), dtype=torch.float32)
+    w[:, :cout, :] = weight.detach().permute(2, 0, 1)
+    return PackedGemm(round_tf32(w), k, -(k // 2), cout, bn, _f(bias), _f(scale), _f(shift), relu)
+
+
+def pack_bn_conv(conv_w, gamma, beta, mean, var, relu: bool, bn: Optional[int] = None) -> PackedGemm:
+    """BatchNormConv (conv -> ReLU? -> BN eval, common_layers.py:54-57): BN becomes the per-channel
+    affine y = v*s + b applied AFTER the ReLU in the epilogue (it cannot be folded into the weights
+    when relu=True)."""
+    s = gamma.detach().float() / torch.sqrt(var.detach().float() + BN_EPS)
+    b = beta.detach().float() - mean.detach().float() * s
+    return pack_conv(conv_w, None, bn, s, b, relu)
+
+
+def pack_linear(weight: torch.Tensor, bias: Optional[torch.Tensor] = None, bn: Optional[int] = None,
+                relu=False) -> PackedGemm:
+    return pack_conv(weight.detach().unsqueeze(2), bias, bn, None, None, relu)
+
+
+def pack_highway(w1, b1, w2, b2, bn: int = 256) -> PackedGemm:
+    """HighwayNetwork (common_layers.py:27-40) as ONE GEMM with N = 2*units: N-tile i holds
+    [W1 rows | W2 rows] of units [i*bn/2, (i+1)*bn/2) so both halves of a unit land in one TMEM tile."""
+    units, k = w1.shape
+    u = bn // 2
+    assert units % u == 0, 'highway width must be a multiple of bn/2'
+    blocks = []
+    for i in range(units // u):
+        blocks += [w1.detach()[i * u:(i + 1) * u], w2.detach()[i * u:(i + 1) * u]]
+    w = torch.cat(blocks, dim=0).unsqueeze(0).float()
+    bias = torch.cat([b1.detach(), b2.detach()]).float().contiguous()
+    return PackedGemm(round_tf32(w), 1, 0, 2 * units, bn, bias)
+
+
+class PackedRnn:
+    """Bidirectional GRU/LSTM: input projection as one GEMM over both directions, W_hh resident."""
+
+    def __init__(self, rnn: torch.nn.RNNBase):
+        p = dict(rnn.named_parameters())
+        self.cell = 1 if isinstance(rnn, torch.nn.LSTM) else 0
+        self.hidden = rnn.hidden_size
+        w_ih = torch.cat([p['weight_ih_l0'], p['weight_ih_l0_reverse']], dim=0)
+        b_ih = torch.cat([p['bias_ih_l0'], p['bias_ih_l0_reverse']], dim=0)
+        self.ih = pack_linear(w_ih, b_ih)
+        self.w_hh = round_tf32(torch.stack([p['weight_hh_l0'], p['weight_hh_l0_reverse']]))
+        self.b_hh = torch.stack([p['bias_hh_l0'], p['bias_hh_l0_reverse']]).detach().float().contiguous()

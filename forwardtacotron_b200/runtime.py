@@ -1,0 +1,197 @@
+"""ctypes binding of libftb200.so (include/ftb200.h) and the per-device handle.
+
+This module is the ONLY place that touches the native library.  There is no CPU or
+PyTorch fallback: if the library is missing, or the device is not sm_100, every entry
+raises (north_star: "no CPU fallback").  PyTorch is used for device memory and streams only.
+"""
+import ctypes as C
+import os
+from typing import Dict, List, Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libftb200.so')
+
+EPI_AFFINE, EPI_MAXPOOL, EPI_HIGHWAY = 0, 1, 2
+F_RELU, F_ROUND = 1, 2
+CELL_GRU, CELL_LSTM = 0, 1
+SEQ_GAP = 8          # zero rows between sentences in the padded-flat layout (>= largest conv reach)
+
+_fp = C.c_void_p
+
+
+class GemmProblem(C.Structure):
+    _fields_ = [('a', _fp), ('rows', C.c_int64), ('lda', C.c_int32), ('cin', C.c_int32),
+                ('w', _fp), ('taps', C.c_int32), ('tap0', C.c_int32), ('w_tap_rows', C.c_int32),
+                ('n', C.c_int32), ('bn', C.c_int32), ('epilogue', C.c_int32), ('flags', C.c_int32),
+                ('bias0', _fp), ('scale', _fp), ('shift', _fp), ('residual', _fp), ('res_ld', C.c_int32),
+                ('out', _fp), ('out_ld', C.c_int32), ('out_col0', C.c_int32),
+                ('out_t', _fp), ('batch', C.c_int32), ('seq_len', C.c_int32), ('seq_stride', C.c_int32)]
+
+
+class RnnProblem(C.Structure):
+    _fields_ = [('cell', C.c_int32), ('hidden', C.c_int32), ('batch', C.c_int32), ('seq_len', C.c_int32),
+                ('seq_stride', C.c_int32), ('xproj', _fp), ('w_hh', _fp), ('b_hh', _fp), ('out', _fp),
+                ('out_ld', C.c_int32), ('out_col0', C.c_int32)]
+
+
+class LrGatherArgs(C.Structure):
+    _fields_ = [('x', _fp), ('x_stride', C.c_int32), ('x_ld', C.c_int32), ('c1', C.c_int32),
+                ('extra', _fp), ('c2', C.c_int32),
+                ('pitch', _fp), ('energy', _fp),
+                ('wp', _fp), ('bp', _fp), ('ps', C.c_float),
+                ('we', _fp), ('be', _fp), ('es', C.c_float),
+                ('cum', _fp), ('lens', _fp),
+                ('batch', C.c_int32), ('T', C.c_int32), ('M', C.c_int32),
+                ('out', _fp), ('out_stride', C.c_int32), ('out_ld', C.c_int32),
+                ('idx', _fp), ('round_tf32', C.c_int32)]
+
+
+# every symbol include/ftb200.h declares (tests check that the .so exports all of them)
+SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
+           'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy',
+           'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy',
+           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_embed', 'ftb_rowdot', 'ftb_argmax_lastdim',
+           'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha']
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """dlopen the in-tree library; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f'{LIB_PATH} not found: build it with `python -m forwardtacotron_b200.build` '
+                           '(there is no CPU fallback for the mel-synthesis path)')
+    lib = C.CDLL(LIB_PATH)
+    lib.ftb_error_string.restype = C.c_char_p
+    lib.ftb_launch_count.restype = C.c_int64
+    lib.ftb_launch_count.argtypes = [_fp]
+    lib.ftb_create.argtypes = [C.c_int, C.POINTER(_fp)]
+    lib.ftb_destroy.argtypes = [_fp]
+    lib.ftb_gemm_plan_create.argtypes = [_fp, C.POINTER(GemmProblem), C.c_int, C.POINTER(C.c_int)]
+    lib.ftb_gemm_plan_run.argtypes = [_fp, C.c_int, C.c_int, _fp]
+    lib.ftb_gemm_plan_destroy.argtypes = [_fp, C.c_int]
+    lib.ftb_rnn_plan_create.argtypes = [_fp, C.POINTER(RnnProblem), C.c_int, C.POINTER(C.c_int)]
+    lib.ftb_rnn_plan_run.argtypes = [_fp, C.c_int, _fp]
+    lib.ftb_rnn_plan_destroy.argtypes = [_fp, C.c_int]
+    lib.ftb_lr_scan.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
+    lib.ftb_lr_gather.argtypes = [_fp, C.POINTER(LrGatherArgs), _fp]
+    lib.ftb_embed.argtypes = [_fp, _fp, _fp, C.c_int, _fp, _fp, C.c_int, _fp, C.c_int,
+                              C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, _fp]
+    lib.ftb_rowdot.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_float,
+                               C.c_int, C.c_int, C.c_int, _fp, _fp]
+    lib.ftb_argmax_lastdim.argtypes = [_fp, _fp, C.c_int64, C.c_int, _fp, _fp]
+    lib.ftb_add_layernorm.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp,
+                                      C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
+    lib.ftb_posenc.argtypes = [_fp, _fp, _fp, _fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
+                               _fp, C.c_int, _fp]
+    lib.ftb_mha.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
+    _lib = lib
+    return lib
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def seq_stride(seq_len: int) -> int:
+    """Rows per sentence in the padded-flat layout (include/ftb200.h)."""
+    return seq_len + SEQ_GAP
+
+
+class Handle:
+    """One ftb_handle per CUDA device; raises RuntimeError on any non-zero status."""
+
+    _per_device: Dict[int, 'Handle'] = {}
+
+    def __init__(self, device: torch.device):
+        if device.type != 'cuda':
+            raise RuntimeError('forwardtacotron_b200 runs on CUDA (sm_100a) only; got device ' + str(device))
+        self.lib = load_library()
+        self.device = device
+        self.index = device.index if device.index is not None else torch.cuda.current_device()
+        h = _fp()
+        self.check(self.lib.ftb_create(self.index, C.byref(h)))
+        self.h = h
+        self.impl = int(os.environ.get('FTB_GEMM_IMPL', '0'))    # 1 = SIMT cross-check kernel (tests only)
+
+    @classmethod
+    def get(cls, device: torch.device) -> 'Handle':
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        if idx not in cls._per_device:
+            cls._per_device[idx] = Handle(torch.device('cuda', idx))
+        return cls._per_device[idx]
+
+    def check(self, code: int):
+        if code != 0:
+            msg = self.lib.ftb_error_string(code).decode()
+            raise RuntimeError(f'libftb200: {msg} (code {code})')
+
+    def stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def launch_count(self) -> int:
+        return int(self.lib.ftb_launch_count(self.h))
+
+    # ---- plans -----------------------------------------------------------------------------
+    def gemm_plan(self, problems: List[GemmProblem]) -> int:
+        arr = (GemmProblem * len(problems))(*problems)
+        pid = C.c_int()
+        self.check(self.lib.ftb_gemm_plan_create(self.h, arr, len(problems), C.byref(pid)))
+        return pid.value
+
+    def gemm_run(self, plan: int, impl: Optional[int] = None):
+        self.check(self.lib.ftb_gemm_plan_run(self.h, plan, self.impl if impl is None else impl, self.stream()))
+
+    def gemm_destroy(self, plan: int):
+        self.check(self.lib.ftb_gemm_plan_destroy(self.h, plan))
+
+    def rnn_plan(self, problems: List[RnnProblem]) -> int:
+        arr = (RnnProblem * len(problems))(*problems)
+        pid = C.c_int()
+        self.check(self.lib.ftb_rnn_plan_create(self.h, arr, len(problems), C.byref(pid)))
+        return pid.value
+
+    def rnn_run(self, plan: int):
+        self.check(self.lib.ftb_rnn_plan_run(self.h, plan, self.stream()))
+
+    def rnn_destroy(self, plan: int):
+        self.check(self.lib.ftb_rnn_plan_destroy(self.h, plan))
+
+    # ---- stateless kernels -------------------------------------------------------------------
+    def lr_scan(self, dur, batch, T, apply_fallback, cum, lens, meta):
+        self.check(self.lib.ftb_lr_scan(self.h, ptr(dur), batch, T, int(apply_fallback), ptr(cum), ptr(lens),
+                                        ptr(meta), self.stream()))
+
+    def lr_gather(self, args: LrGatherArgs):
+        self.check(self.lib.ftb_lr_gather(self.h, C.byref(args), self.stream()))
+
+    def embed(self, tok, table, out, out_ld, batch, T, stride, tok2=None, table2=None, extra=None, round_tf32=True):
+        e1 = table.shape[1]
+        e2 = table2.shape[1] if table2 is not None else 0
+        e3 = extra.shape[1] if extra is not None else 0
+        self.check(self.lib.ftb_embed(self.h, ptr(tok), ptr(table), e1, ptr(tok2), ptr(table2), e2, ptr(extra), e3,
+                                      batch, T, stride, ptr(out), out_ld, int(round_tf32), self.stream()))
+
+    def rowdot(self, x, x_ld, k, w, bias, n_out, inv_alpha, batch, T, stride, y):
+        self.check(self.lib.ftb_rowdot(self.h, ptr(x), x_ld, k, ptr(w), ptr(bias), n_out, float(inv_alpha),
+                                       batch, T, stride, ptr(y), self.stream()))
+
+    def argmax(self, x, n, c, out):
+        self.check(self.lib.ftb_argmax_lastdim(self.h, ptr(x), n, c, ptr(out), self.stream()))
+
+    def add_layernorm(self, x, res, ld, e, g, b, g2, b2, batch, L, stride, out, round_tf32=True):
+        self.check(self.lib.ftb_add_layernorm(self.h, ptr(x), ptr(res), ld, e, ptr(g), ptr(b), ptr(g2), ptr(b2),
+                                              batch, L, stride, ptr(out), int(round_tf32), self.stream()))
+
+    def posenc(self, tok, table, x_in, pe, scale, e, batch, L, stride, out, round_tf32=True):
+        self.check(self.lib.ftb_posenc(self.h, ptr(tok), ptr(table), ptr(x_in), ptr(pe), ptr(scale), e, batch, L,
+                                       stride, ptr(out), int(round_tf32), self.stream()))
+
+    def mha(self, qkv, e, heads, key_tok, batch, L, stride, out, round_tf32=True):
+        self.check(self.lib.ftb_mha(self.h, ptr(qkv), e, heads, ptr(key_tok), batch, L, stride, ptr(out),
+                                    int(round_tf32), self.stream()))

@@ -1,0 +1,215 @@
+/* ftb200.h -- C ABI of libftb200.so, the sm_100a kernel library behind
+ * forwardtacotron_b200.models.*.generate().
+ *
+ * The reference (ziyaad30/ForwardTacotron) has no FFI layer of its own: its hot path
+ * calls torch.nn modules.  Each entry point below therefore names the reference call
+ * site(s) (file:line under the reference tree) whose arithmetic it replaces; the Python
+ * side that binds them with ctypes is forwardtacotron_b200/runtime.py and the stub a
+ * reference maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless noted;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - return 0 = OK, <0 = invalid argument (FTB_E_*), >0 = a cudaError_t value;
+ *   - no entry point synchronises, allocates per call, or throws; plans own their
+ *     descriptors (tensor maps, barrier counters) and are created once per shape;
+ *   - one handle per device, calls on one handle are not thread safe.
+ *
+ * Activation layout ("padded-flat, channel-last"): a [batch, seq_len, C] fp32 tensor is
+ * stored as rows r = b*seq_stride + t (seq_stride >= seq_len + 8), C contiguous; the
+ * rows with t in [seq_len, seq_stride) are ZERO and are never written by any kernel, so
+ * convolution taps that reach across a sentence edge read zero padding exactly like
+ * nn.Conv1d(padding=k//2) (common_layers.py:50).
+ */
+#ifndef FTB200_H_
+#define FTB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FTB_VERSION 100
+
+#define FTB_E_ARG      (-1)   /* null pointer / bad size / bad enum                     */
+#define FTB_E_ALIGN    (-2)   /* pointer or leading dimension not 16-byte aligned        */
+#define FTB_E_SHAPE    (-3)   /* shape not supported by the sm_100a kernels              */
+#define FTB_E_PLAN     (-4)   /* unknown plan id                                         */
+#define FTB_E_DRIVER   (-5)   /* cuTensorMapEncodeTiled unavailable (no driver)          */
+#define FTB_E_RESIDENT (-6)   /* persistent recurrence grid does not fit on the device   */
+
+typedef struct ftb_context* ftb_handle;
+
+int ftb_version(void);
+const char* ftb_error_string(int code);
+int ftb_create(int device, ftb_handle* out);
+int ftb_destroy(ftb_handle h);
+/* number of kernels launched through this handle since creation (bench.py's gpu_launches) */
+int64_t ftb_launch_count(ftb_handle h);
+
+/* ------------------------------------------------------------------------------------
+ * K1/K2  implicit-GEMM convolution / linear with fused epilogue   (tcgen05 + TMEM + TMA)
+ *
+ * Replaces: nn.Conv1d + F.relu + nn.BatchNorm1d(eval) in BatchNormConv.forward
+ * (models/common_layers.py:54-57), the CBHG bank/cat/MaxPool1d (common_layers.py:97-105),
+ * conv_project1/2 + residual (:109-114), pre_highway Linear (:118), HighwayNetwork.forward
+ * (:35-40), the W_ih half of nn.GRU / nn.LSTM (common_layers.py:123,
+ * forward_tacotron.py:37,224), self.lin / self.post_proj (forward_tacotron.py:226,230) and
+ * the FFT-block Conv1d/Linear layers (common_layers.py:173-181).
+ *
+ *   acc[r, n] = sum_{j<taps} sum_{c<cin} A[r + tap0 + j, c] * W[j*w_tap_rows + n, c]
+ *   (rows outside [0, rows) read as zero; tf32 operands, fp32 accumulation)
+ *
+ *   FTB_EPI_AFFINE : v = acc + bias0[n]; if RELU v = max(v,0); v = v*scale[n] + shift[n];
+ *                    v += residual[r, n]
+ *   FTB_EPI_MAXPOOL: y = AFFINE(acc); v[r] = (t == 0) ? y[r] : max(y[r-1], y[r])
+ *                    (MaxPool1d(2,1,1)[:, :, :L], common_layers.py:105)
+ *   FTB_EPI_HIGHWAY: n = 2*units; W rows of N-tile i are [W1 rows | W2 rows] of units
+ *                    [i*bn/2, (i+1)*bn/2); bias0 = [b1 | b2];
+ *                    g = sigmoid(x2); v = g*relu(x1) + (1-g)*residual[r, u]
+ *   Only rows with (r % seq_stride) < seq_len are stored; null bias0/scale/shift mean 0/1/0.
+ * ------------------------------------------------------------------------------------ */
+enum { FTB_EPI_AFFINE = 0, FTB_EPI_MAXPOOL = 1, FTB_EPI_HIGHWAY = 2 };
+enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2 };
+
+typedef struct {
+  const float* a;        /* [rows, lda] activations (tf32-rounded by their producer)         */
+  int64_t rows;          /* batch * seq_stride                                               */
+  int32_t lda;           /* floats, multiple of 4                                            */
+  int32_t cin;           /* reduction extent per tap (<= lda)                                */
+  const float* w;        /* packed [taps][w_tap_rows][cin] fp32, tf32-rounded                 */
+  int32_t taps, tap0;    /* tap j reads row r + tap0 + j   (tap0 = -(k/2))                   */
+  int32_t w_tap_rows;    /* rows per tap in w (n rounded up to a multiple of bn)             */
+  int32_t n;             /* output channels (HIGHWAY: 2*units)                               */
+  int32_t bn;            /* N tile: multiple of 16, 16..256                                  */
+  int32_t epilogue;      /* FTB_EPI_*                                                        */
+  int32_t flags;         /* FTB_F_*                                                          */
+  const float* bias0;    /* [n] or null                                                      */
+  const float* scale;    /* [n] or null                                                      */
+  const float* shift;    /* [n] or null                                                      */
+  const float* residual; /* [rows, res_ld] or null                                           */
+  int32_t res_ld;
+  float* out;            /* [rows, out_ld], written at columns out_col0 + n; may be null      */
+  int32_t out_ld, out_col0;
+  float* out_t;          /* optional [batch, n, seq_len] transposed, never rounded; or null  */
+  int32_t batch, seq_len, seq_stride;
+} ftb_gemm_problem;
+
+/* A plan = up to FTB_MAX_PROBLEMS independent problems run by ONE persistent launch. */
+#define FTB_MAX_PROBLEMS 32
+int ftb_gemm_plan_create(ftb_handle h, const ftb_gemm_problem* problems, int nproblems, int* plan_out);
+/* impl: 0 = tcgen05/TMA kernel (the product path); 1 = plain SIMT fp32 cross-check kernel
+ * (test-only: same problems, no tensor cores, used by tests to bisect descriptor bugs).   */
+int ftb_gemm_plan_run(ftb_handle h, int plan, int impl, void* stream);
+int ftb_gemm_plan_destroy(ftb_handle h, int plan);
+
+/* ------------------------------------------------------------------------------------
+ * K3/K4  persistent bidirectional GRU / LSTM recurrence
+ *
+ * Replaces: the time loop of nn.GRU (common_layers.py:123; forward_tacotron.py:37) and
+ * nn.LSTM (forward_tacotron.py:224), batch_first, bidirectional, h0 = c0 = 0, run over the
+ * full padded length (no packing in generate()).  xproj holds W_ih x + b_ih for
+ * [forward | reverse] (K2 output); W_hh stays resident in registers for all steps; one
+ * group barrier per time step; h_t is published through `out`, which is also the layer output.
+ *   GRU  (r,z,n): r = s(xr + Whr h + bhr); z = s(xz + Whz h + bhz);
+ *                 n = tanh(xn + r*(Whn h + bhn)); h' = (1-z)*n + z*h
+ *   LSTM (i,f,g,o): c' = s(f)*c + s(i)*tanh(g); h' = s(o)*tanh(c')
+ * ------------------------------------------------------------------------------------ */
+enum { FTB_CELL_GRU = 0, FTB_CELL_LSTM = 1 };
+
+typedef struct {
+  int32_t cell;          /* FTB_CELL_*                                                       */
+  int32_t hidden;        /* H: 64, 128, 256 or 512                                           */
+  int32_t batch, seq_len, seq_stride;
+  const float* xproj;    /* [batch*seq_stride, 2*g*H], g = 3 (GRU) / 4 (LSTM)                */
+  const float* w_hh;     /* [2][g*H][H] fp32, tf32-rounded (weight_hh_l0, weight_hh_l0_reverse) */
+  const float* b_hh;     /* [2][g*H]                                                         */
+  float* out;            /* [batch*seq_stride, out_ld]; fwd h at out_col0, bwd at out_col0+H; tf32-rounded */
+  int32_t out_ld, out_col0;
+} ftb_rnn_problem;
+
+#define FTB_MAX_RNN_PROBLEMS 8
+int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems, int nproblems, int* plan_out);
+int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream);
+int ftb_rnn_plan_destroy(ftb_handle h, int plan);
+
+/* ------------------------------------------------------------------------------------
+ * K5/K6  duration rounding + LengthRegulator gather (+ fused pitch/energy projection add)
+ *
+ * Replaces: `if sum(dur.long()) <= 0: fill_(dur, 2.)` (forward_tacotron.py:176-177),
+ * LengthRegulator.forward (common_layers.py:17-24) and the pitch/energy Conv1d(1->C,k=3)
+ * projections + scaled adds (forward_tacotron.py:214-220).
+ *
+ * ftb_lr_scan : clamps dur in place (dur[dur<0]=0), applies the batch-global fallback,
+ *               rep = trunc(dur + 0.5f) (fp32 add), per-sentence inclusive scan.
+ *               Outputs cum [batch, T] int32, lens [batch] int32, and meta[0] = max len,
+ *               meta[1] = fallback flag, meta[2] = total frames (host reads meta once).
+ * ftb_lr_gather: out[b*out_stride + m, :] = src(b, idx) for m < lens[b], where
+ *               src(b,t) = x[b*x_stride + t, :C1] ++ extra[b, :C2]  (speaker embedding tail)
+ *                          + ps*(wp (*) pitch)[t] + es*(we (*) energy)[t]   (3-tap, zero padded)
+ *               rows m in [lens[b], M) are written as 0.0; also writes idx [batch, M] (-1 = pad).
+ *               The gathered rows are bit-exact copies of src; src itself is fp32 FMA-free
+ *               arithmetic in the reference's operation order.
+ * ------------------------------------------------------------------------------------ */
+int ftb_lr_scan(ftb_handle h, float* dur, int batch, int T, int apply_fallback,
+                int32_t* cum, int32_t* lens, int32_t* meta, void* stream);
+
+typedef struct {
+  const float* x; int32_t x_stride /*rows per sentence*/, x_ld, c1;
+  const float* extra; int32_t c2;                 /* [batch, c2] appended channels, or null  */
+  const float* pitch; const float* energy;        /* [batch, T] or null (then no projection) */
+  const float* wp; const float* bp; float ps;     /* [C,3], [C], strength                    */
+  const float* we; const float* be; float es;
+  const int32_t* cum; const int32_t* lens;
+  int32_t batch, T, M;
+  float* out; int32_t out_stride /*rows per sentence*/, out_ld;
+  int32_t* idx;                                   /* [batch, M] or null                      */
+  int32_t round_tf32;
+} ftb_lr_gather_args;
+int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Small glue kernels
+ * ------------------------------------------------------------------------------------ */
+/* nn.Embedding (forward_tacotron.py:31,210) (+ concatenated conditioning embedding and speaker
+ * vector, multi_forward_tacotron.py:40-42,82-86) into the padded-flat layout:
+ * out[b*seq_stride+t, :] = table[tok[b,t], :e1] ++ table2[tok2[b,t], :e2] ++ extra[b, :e3]. */
+int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1,
+              const int64_t* tok2, const float* table2, int e2,
+              const float* extra, int e3,
+              int batch, int T, int seq_stride, float* out, int out_ld, int round_tf32, void* stream);
+
+/* Predictor head: y[b,t,o] = (dot(x[b*seq_stride+t, :k], w[o,:]) + bias[o]) * inv_alpha
+ * (self.lin + `/ alpha`, forward_tacotron.py:38-39).  n_out <= 4.  y is dense [batch, T, n_out]. */
+int ftb_rowdot(ftb_handle h, const float* x, int x_ld, int k, const float* w, const float* bias,
+               int n_out, float inv_alpha, int batch, int T, int seq_stride, float* y, void* stream);
+
+/* argmax over the last axis of [n, c] (c <= 8) -> int64 (multi_forward_tacotron.py:252, per (b,t)). */
+int ftb_argmax_lastdim(ftb_handle h, const float* x, int64_t n, int c, int64_t* out, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * K7/K8  FFT-block pieces (FastPitch, common_layers.py:127-223)
+ * ------------------------------------------------------------------------------------ */
+/* y = LayerNorm(x (+ res)) * gamma + beta, eps = 1e-5, over the last axis e (<= 1024), only
+ * valid rows; optional second LayerNorm chained (the ForwardTransformer's final norm).   */
+int ftb_add_layernorm(ftb_handle h, const float* x, const float* res, int ld, int e,
+                      const float* gamma, const float* beta,
+                      const float* gamma2, const float* beta2,
+                      int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
+
+/* x[b,t,:] = emb[tok[b,t], :] + scale * pe[t, :]   (PositionalEncoding, common_layers.py:143-145);
+ * tok == null: in-place x += scale*pe over an existing activation (post-LR postnet input). */
+int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, const float* x_in, const float* pe,
+               const float* scale_ptr, int e, int batch, int seq_len, int seq_stride,
+               float* out, int round_tf32, void* stream);
+
+/* 2..8-head self attention over qkv [rows, 3e] (packed in_proj output), softmax over keys with
+ * optional key padding (tok[b,s] == 0 masked, common_layers.py:232-233); out [rows, e]. */
+int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const int64_t* key_tok,
+            int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FTB200_H_ */

@@ -40,9 +40,20 @@ Identity = lambda t: t  # noqa: E731
 _QUANT: Callable[[torch.Tensor], torch.Tensor] = Identity
 
 
-def set_operand_rounding(fn: Optional[Callable[[torch.Tensor], torch.Tensor]]) -> None:
-    global _QUANT
+_QUANT_REC: Optional[Callable[[torch.Tensor], torch.Tensor]] = None   # None: follow _QUANT
+
+
+def set_operand_rounding(fn: Optional[Callable[[torch.Tensor], torch.Tensor]],
+                         recurrent: Optional[Callable[[torch.Tensor], torch.Tensor]] = None) -> None:
+    """`fn` rounds the operands of every feed-forward contraction; `recurrent` (default: same
+    as fn) those of the h @ W_hh^T products inside the GRU/LSTM time loops."""
+    global _QUANT, _QUANT_REC
     _QUANT = fn if fn is not None else Identity
+    _QUANT_REC = recurrent
+
+
+def _qrec(t: torch.Tensor) -> torch.Tensor:
+    return (_QUANT_REC or _QUANT)(t)
 
 
 def round_tf32(t: torch.Tensor) -> torch.Tensor:
@@ -131,10 +142,10 @@ def gru_direction(x: torch.Tensor, w_ih, w_hh, b_ih, b_hh, reverse: bool) -> tor
     gi = linear(x, w_ih, b_ih)                       # [B,L,3H]
     h = x.new_zeros(B, H)
     out = x.new_zeros(B, L, H)
-    wq = _QUANT(w_hh)
+    wq = _qrec(w_hh)
     steps = range(L - 1, -1, -1) if reverse else range(L)
     for t in steps:
-        gh = F.linear(_QUANT(h), wq, b_hh)
+        gh = F.linear(_qrec(h), wq, b_hh)
         i_r, i_z, i_n = gi[:, t].chunk(3, dim=1)
         h_r, h_z, h_n = gh.chunk(3, dim=1)
         r = torch.sigmoid(i_r + h_r)
@@ -153,10 +164,10 @@ def lstm_direction(x: torch.Tensor, w_ih, w_hh, b_ih, b_hh, reverse: bool) -> to
     h = x.new_zeros(B, H)
     c = x.new_zeros(B, H)
     out = x.new_zeros(B, L, H)
-    wq = _QUANT(w_hh)
+    wq = _qrec(w_hh)
     steps = range(L - 1, -1, -1) if reverse else range(L)
     for t in steps:
-        g = gi[:, t] + F.linear(_QUANT(h), wq, b_hh)
+        g = gi[:, t] + F.linear(_qrec(h), wq, b_hh)
         gi_, gf_, gg_, go_ = g.chunk(4, dim=1)
         c = torch.sigmoid(gf_) * c + torch.sigmoid(gi_) * torch.tanh(gg_)
         h = torch.sigmoid(go_) * torch.tanh(c)
@@ -178,7 +189,7 @@ def bi_rnn(sd: SD, p: str, x: torch.Tensor, kind: str) -> torch.Tensor:
     """Bidirectional batch_first GRU/LSTM over the full padded length (no packing in
     generate(): common_layers.py:123, forward_tacotron.py:37,224).  out = [fwd | bwd]."""
     names = ['weight_ih_l0', 'weight_hh_l0', 'bias_ih_l0', 'bias_hh_l0']
-    if _FAST_RNN and _QUANT is Identity:
+    if _FAST_RNN and _QUANT is Identity and _QUANT_REC is None:
         flat = [sd[f'{p}.{n}{sfx}'] for sfx in ('', '_reverse') for n in names]
         B = x.shape[0]
         H = flat[1].shape[1]

@@ -1,0 +1,228 @@
+"""GPU parity tests of the individual sm_100a kernels, called through the C ABI.
+
+Each tensor-core case is checked three ways: tcgen05 kernel vs a float64 torch restatement
+of the same (tf32-rounded) operands, and vs the library's own SIMT cross-check kernel.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from forwardtacotron_b200 import engine as eng            # noqa: E402
+from forwardtacotron_b200 import pack as pk               # noqa: E402
+from forwardtacotron_b200 import runtime as rt            # noqa: E402
+from oracle import ft_oracle as O                         # noqa: E402
+from tests.helpers import load_golden, max_abs            # noqa: E402
+
+DEV = torch.device('cuda', 0)
+
+
+def _handle():
+    return rt.Handle.get(DEV)
+
+
+def _fill(prog, name, cols, gen):
+    """Random tf32-rounded activation in the valid rows of a padded-flat buffer."""
+    g = prog.geo
+    buf = prog.buf(name, cols)
+    v = pk.round_tf32(torch.randn(g.batch, g.seq_len, cols, generator=gen))
+    buf.view(g.batch, g.stride, cols)[:, :g.seq_len] = v.to(DEV)
+    return buf, v.double()
+
+
+def _conv_ref(x, w, k):
+    """x [B,L,Cin] float64, w [Cout,Cin,k] -> [B,L,Cout] with padding k//2 trimmed to L."""
+    y = F.conv1d(x.transpose(1, 2), w.double(), padding=k // 2)[:, :, :x.shape[1]]
+    return y.transpose(1, 2)
+
+
+@pytest.mark.parametrize('B,L,cin,cout,k,relu', [
+    (2, 50, 64, 256, 5, True),        # predictor first conv
+    (3, 130, 256, 256, 1, True),      # k=1, crosses an M-tile boundary
+    (2, 70, 80, 256, 4, True),        # even k (asymmetric trim), Cin=80 (K tail zero-filled by TMA)
+    (1, 300, 256, 80, 3, False),      # N=80, no ReLU
+    (2, 40, 388, 256, 5, True),       # multi-speaker predictor width
+])
+def test_conv_bn(B, L, cin, cout, k, relu):
+    gen = torch.Generator().manual_seed(B * 1000 + L + k)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    a, a_ref = _fill(prog, 'a', cin, gen)
+    w = torch.randn(cout, cin, k, generator=gen) / (cin * k) ** 0.5
+    gamma, beta = torch.rand(cout, generator=gen) + 0.5, torch.randn(cout, generator=gen) * 0.1
+    mean, var = torch.randn(cout, generator=gen) * 0.1, torch.rand(cout, generator=gen) + 0.5
+    packed = pk.pack_bn_conv(w.to(DEV), gamma.to(DEV), beta.to(DEV), mean.to(DEV), var.to(DEV), relu)
+    out = prog.buf('out', cout)
+    prog.gemm(a, packed, out, round_out=False)
+    prog.flush()
+    y = _conv_ref(a_ref, pk.round_tf32(w), k)
+    if relu:
+        y = y.clamp_min(0)
+    s = (gamma / torch.sqrt(var + 1e-5)).double()
+    ref = y * s + (beta.double() - mean.double() * s)
+    for impl in (1, 0):
+        out.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        got = prog.view('out').cpu().double()
+        assert max_abs(got, ref) < 2e-4, f'impl={impl}'
+    prog.h.impl = 0
+    # gap rows stay zero
+    g = prog.geo
+    assert float(out.view(g.batch, g.stride, cout)[:, g.seq_len:].abs().max()) == 0.0
+
+
+def test_bank_maxpool_matches_reference_semantics():
+    """conv bank (k=1..6) + MaxPool1d(2,1,1)[:L] fused epilogue vs torch ops (common_layers.py:97-105)."""
+    B, L, cin, ch, K = 2, 200, 64, 64, 6
+    gen = torch.Generator().manual_seed(5)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    a, a_ref = _fill(prog, 'a', cin, gen)
+    bank = prog.buf('bank', K * ch)
+    refs = []
+    for k in range(1, K + 1):
+        w = torch.randn(ch, cin, k, generator=gen) / (cin * k) ** 0.5
+        gamma, beta = torch.rand(ch, generator=gen) + 0.5, torch.randn(ch, generator=gen) * 0.3
+        mean, var = torch.randn(ch, generator=gen) * 0.1, torch.rand(ch, generator=gen) + 0.5
+        packed = pk.pack_bn_conv(w.to(DEV), gamma.to(DEV), beta.to(DEV), mean.to(DEV), var.to(DEV), True)
+        prog.gemm(a, packed, bank, out_col0=(k - 1) * ch, epilogue=rt.EPI_MAXPOOL, round_out=False)
+        y = _conv_ref(a_ref, pk.round_tf32(w), k).clamp_min(0)
+        s = (gamma / torch.sqrt(var + 1e-5)).double()
+        refs.append(y * s + (beta.double() - mean.double() * s))
+    prog.flush()
+    ref = torch.cat(refs, dim=2).transpose(1, 2)                     # [B, K*ch, L]
+    ref = F.max_pool1d(ref, kernel_size=2, stride=1, padding=1)[:, :, :L].transpose(1, 2)
+    for impl in (1, 0):
+        bank.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        assert max_abs(prog.view('bank').cpu().double(), ref) < 2e-4, f'impl={impl}'
+    prog.h.impl = 0
+
+
+def test_highway_and_transposed_linear():
+    B, L, ch = 2, 150, 256
+    gen = torch.Generator().manual_seed(9)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    a, a_ref = _fill(prog, 'a', ch, gen)
+    w1, w2 = torch.randn(ch, ch, generator=gen) / 16, torch.randn(ch, ch, generator=gen) / 16
+    b1, b2 = torch.randn(ch, generator=gen) * 0.1, torch.randn(ch, generator=gen) * 0.1
+    hw = pk.pack_highway(w1.to(DEV), b1.to(DEV), w2.to(DEV), b2.to(DEV))
+    out = prog.buf('hw', ch)
+    prog.gemm(a, hw, out, epilogue=rt.EPI_HIGHWAY, residual=a, round_out=False)
+    wl, bl = torch.randn(80, ch, generator=gen) / 16, torch.randn(80, generator=gen)
+    lin = pk.pack_linear(wl.to(DEV), bl.to(DEV))
+    mel_cl = prog.buf('mel_cl', 80)
+    mel = prog.dense('mel', (B, 80, L))
+    prog.gemm(a, lin, mel_cl, out_t=mel, round_out=True)
+    prog.flush()
+    x1 = a_ref @ pk.round_tf32(w1).double().T + b1.double()
+    x2 = a_ref @ pk.round_tf32(w2).double().T + b2.double()
+    g = torch.sigmoid(x2)
+    ref_hw = g * x1.clamp_min(0) + (1 - g) * a_ref
+    ref_mel = a_ref @ pk.round_tf32(wl).double().T + bl.double()
+    for impl in (1, 0):
+        out.zero_(); mel.zero_(); mel_cl.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        assert max_abs(prog.view('hw').cpu().double(), ref_hw) < 2e-4, f'impl={impl}'
+        assert max_abs(mel.cpu().double(), ref_mel.transpose(1, 2)) < 2e-4, f'impl={impl}'
+        assert max_abs(prog.view('mel_cl').cpu().double(), ref_mel) < 3e-3      # tf32-rounded copy
+    prog.h.impl = 0
+
+
+@pytest.mark.parametrize('cell,H,B,L', [('gru', 64, 3, 37), ('gru', 128, 5, 20), ('gru', 256, 33, 25),
+                                        ('lstm', 512, 2, 30), ('lstm', 512, 40, 12)])
+def test_recurrence(cell, H, B, L):
+    gen = torch.Generator().manual_seed(H + B)
+    In = 96
+    rnn = (torch.nn.GRU if cell == 'gru' else torch.nn.LSTM)(In, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    packed = pk.PackedRnn(rnn.to(DEV))
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    a, a_ref = _fill(prog, 'x', In, gen)
+    xp = prog.buf('xp', packed.ih.n)
+    out = prog.buf('h', 2 * H)
+    prog.gemm(a, packed.ih, xp, round_out=False)
+    prog.rnn([(packed, xp, out, 0)])
+    prog.run()
+    torch.cuda.synchronize()
+    sd = {'r.' + k: v.detach().cpu() for k, v in rnn.state_dict().items()}
+    O.set_operand_rounding(O.round_tf32)
+    try:
+        with torch.no_grad():
+            ref = O.bi_rnn(sd, 'r', a_ref.float(), cell)
+    finally:
+        O.set_operand_rounding(None)
+    got = prog.view('h').cpu()
+    assert max_abs(got, ref) < 2e-3
+    # second run of the same plan gives the same answer (barrier counters are re-armed)
+    out.zero_()
+    prog.run()
+    torch.cuda.synchronize()
+    assert torch.equal(prog.view('h').cpu(), got)
+
+
+@pytest.mark.parametrize('tag', ['all2', 'ties', 'zero_row'])
+def test_length_regulator_bit_exact_golden(tag):
+    g = load_golden(f'lr_{tag}')
+    h = _handle()
+    x = torch.from_numpy(g['x']).to(DEV)
+    B, T, C = x.shape
+    dur = torch.from_numpy(g['dur']).to(DEV).contiguous()
+    cum = torch.empty((B, T), dtype=torch.int32, device=DEV)
+    lens = torch.empty((B,), dtype=torch.int32, device=DEV)
+    meta = torch.empty((4,), dtype=torch.int32, device=DEV)
+    h.lr_scan(dur, B, T, False, cum, lens, meta)
+    M = int(meta.cpu()[0])
+    assert M == g['out'].shape[1]
+    assert np.array_equal(dur.cpu().numpy().view(np.uint32), g['dur_after'].view(np.uint32))
+    out = torch.full((B, M, C), 7.0, device=DEV)
+    idx = torch.empty((B, M), dtype=torch.int32, device=DEV)
+    a = rt.LrGatherArgs()
+    a.x, a.x_stride, a.x_ld, a.c1, a.c2 = x.data_ptr(), T, C, C, 0
+    a.cum, a.lens, a.batch, a.T, a.M = cum.data_ptr(), lens.data_ptr(), B, T, M
+    a.out, a.out_stride, a.out_ld, a.idx, a.round_tf32 = out.data_ptr(), M, C, idx.data_ptr(), 0
+    h.lr_gather(a)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), g['out'].view(np.uint32))
+    _, idx_ref, lens_ref, _ = O.length_regulate_np(g['x'], g['dur'])
+    assert np.array_equal(idx.cpu().numpy(), idx_ref)
+    assert np.array_equal(lens.cpu().numpy(), lens_ref)
+
+
+def test_length_regulator_full_size_properties():
+    """Config-2 size (64 x 200 x 512): bit-exact vs the numpy oracle + fallback flag."""
+    B, T, C = 64, 200, 512
+    gen = torch.Generator().manual_seed(3)
+    x = torch.randn(B, T, C, generator=gen)
+    dur = torch.rand(B, T, generator=gen) * 5 - 0.5
+    h = _handle()
+    xd, dd = x.to(DEV), dur.to(DEV).contiguous()
+    cum = torch.empty((B, T), dtype=torch.int32, device=DEV)
+    lens = torch.empty((B,), dtype=torch.int32, device=DEV)
+    meta = torch.empty((4,), dtype=torch.int32, device=DEV)
+    h.lr_scan(dd, B, T, True, cum, lens, meta)
+    m = meta.cpu()
+    ref, idx_ref, lens_ref, _ = O.length_regulate_np(x.numpy(), dur.numpy())
+    M = int(m[0])
+    assert M == ref.shape[1] and int(m[1]) == 0 and int(m[2]) == int(lens_ref.sum())
+    out = torch.empty((B, M, C), device=DEV)
+    a = rt.LrGatherArgs()
+    a.x, a.x_stride, a.x_ld, a.c1, a.c2 = xd.data_ptr(), T, C, C, 0
+    a.cum, a.lens, a.batch, a.T, a.M = cum.data_ptr(), lens.data_ptr(), B, T, M
+    a.out, a.out_stride, a.out_ld, a.idx, a.round_tf32 = out.data_ptr(), M, C, None, 0
+    h.lr_gather(a)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), ref.view(np.uint32))
+    # fallback: all durations truncate to <= 0  ->  every duration becomes exactly 2
+    d0 = (torch.rand(B, T, generator=gen) * 0.9 - 0.3).to(DEV).contiguous()
+    h.lr_scan(d0, B, T, True, cum, lens, meta)
+    m = meta.cpu()
+    assert int(m[1]) == 1 and int(m[0]) == 2 * T and bool((d0 == 2.0).all())

@@ -1,0 +1,101 @@
+"""End-to-end parity of the accelerated models against (a) goldens produced by the REAL reference
+and (b) the CPU oracle on fresh seeded inputs.  Tolerances are the north_star's: mel / mel_post
+max-abs <= 1e-2 and relative L2 <= 1e-3 (rel = ||got-ref||_2 / ||ref||_2 per tensor); rounded durations
+identical except at documented .5 ties."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from forwardtacotron_b200 import synth                                      # noqa: E402
+from forwardtacotron_b200.configs import default_config                     # noqa: E402
+from forwardtacotron_b200.models import init_tts_model                      # noqa: E402
+from oracle import ft_oracle as O                                           # noqa: E402
+from tests.helpers import load_golden, synthetic_sd, rel_l2, max_abs        # noqa: E402
+
+DEV = torch.device('cuda', 0)
+MEL_ABS, MEL_REL = 1e-2, 1e-3
+
+
+def _model(tag, sd):
+    m = init_tts_model(default_config(tag))
+    m.load_state_dict(sd)
+    return m.to(DEV).eval()
+
+
+def _rounded(d):
+    return (torch.as_tensor(d).clamp_min(0) + 0.5).long()
+
+
+def _check_durations(got, ref):
+    """Identical after rounding, except where the reference value sits within 1e-3 of a .5 tie."""
+    got, ref = torch.as_tensor(got).cpu(), torch.as_tensor(ref).cpu()
+    assert max_abs(got, ref) < 5e-3
+    diff = _rounded(got) != _rounded(ref)
+    frac = (ref.clamp_min(0) + 0.5) % 1.0
+    near_tie = (frac < 1e-3) | (frac > 1 - 1e-3)
+    assert not bool((diff & ~near_tie).any()), 'rounded durations differ away from a .5 tie'
+    return int(diff.sum())
+
+
+@pytest.mark.parametrize('name', ['ft_spread_b3_t40', 'ft_fallback_b2_t24', 'ft_alpha_b2_t30', 'ft_b1_t74'])
+def test_forward_tacotron_generate_vs_reference_golden(name):
+    g = load_golden(name)
+    sd = synthetic_sd('forward_tacotron', int(g['seed']), bool(g['spread']), float(g['dur_bias']))
+    model = _model('forward_tacotron', sd)
+    pm, em = float(g['pitch_mul']), float(g['energy_mul'])
+    out = model.generate(torch.from_numpy(g['x']).to(DEV), alpha=float(g['alpha']),
+                         pitch_function=lambda p: p * pm, energy_function=lambda e: e * em)
+    torch.cuda.synchronize()
+    assert set(out) == {'mel', 'mel_post', 'dur', 'pitch', 'energy'}
+    assert out['pitch'].shape == g['pitch'].shape and out['dur'].shape == g['dur'].shape
+    ties = _check_durations(out['dur'], g['dur'])
+    assert max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3 and max_abs(out['energy'].cpu(), g['energy']) < 5e-3
+    if ties == 0:
+        assert out['mel'].shape == g['mel'].shape
+        for k in ('mel', 'mel_post'):
+            assert max_abs(out[k].cpu(), g[k]) < MEL_ABS, k
+            assert rel_l2(out[k].cpu(), g[k]) < MEL_REL, k
+
+
+def test_generate_mel_teacher_forced_intermediates():
+    """Stage-level check with the reference's own dur/pitch/energy (decouples rounding ties) + taps."""
+    g = load_golden('ft_spread_b3_t40')
+    sd = synthetic_sd('forward_tacotron', int(g['seed']))
+    model = _model('forward_tacotron', sd)
+    x = torch.from_numpy(g['x']).to(DEV)
+    out = model._generate_mel(x, torch.from_numpy(g['dur']).to(DEV).contiguous(),
+                              torch.from_numpy(g['pitch']).to(DEV), torch.from_numpy(g['energy']).to(DEV))
+    torch.cuda.synchronize()
+    st = model.__dict__['_accel']
+    B, T = x.shape
+    tok = st['programs'][('prenet', B, T)]
+    M = g['mel'].shape[2]
+    frame = st['programs'][('frame', B, M)]
+    assert rel_l2(tok.view('prenet.proj1').cpu(), g['tap_prenet_conv_project1'].transpose(0, 2, 1)) < 1e-3
+    assert rel_l2(tok.view('prenet.h').cpu(), g['tap_prenet']) < 1e-3
+    assert rel_l2(frame.view('lr').cpu(), g['tap_lr']) < 1e-3
+    assert rel_l2(frame.view('lstm.h').cpu(), g['tap_lstm']) < 1e-3
+    assert rel_l2(frame.view('postnet.h').cpu(), g['tap_postnet']) < 1e-3
+    for k in ('mel', 'mel_post'):
+        assert max_abs(out[k].cpu(), g[k]) < MEL_ABS and rel_l2(out[k].cpu(), g[k]) < MEL_REL, k
+
+
+def test_forward_tacotron_vs_oracle_batch16():
+    """A mid-size fresh case against the CPU oracle (same weights), incl. a second call (plan reuse)."""
+    sd = synthetic_sd('forward_tacotron', 11)
+    model = _model('forward_tacotron', sd)
+    x = synth.synth_tokens(16, 96, seed=11)
+    O.use_library_rnn(True)
+    try:
+        ref = O.ft_generate(sd, x)
+    finally:
+        O.use_library_rnn(False)
+    for _ in range(2):
+        out = model.generate(x.to(DEV))
+        torch.cuda.synchronize()
+        ties = _check_durations(out['dur'], ref['dur'])
+        if ties == 0:
+            for k in ('mel', 'mel_post'):
+                assert max_abs(out[k].cpu(), ref[k]) < MEL_ABS and rel_l2(out[k].cpu(), ref[k]) < MEL_REL, k
