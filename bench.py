@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""Headline benchmark: mel frames / second of ForwardTacotron.generate() at batch 64 x 200 phonemes
+(BASELINE.json configs[1]) on N B200s, one process per GPU, sentence-sharded (weak scaling: every
+rank synthesises its own 64 x 200 batch; no data-path collective).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Prints ONE JSON line (rank 0).  `value` = valid mel frames of all ranks / max-over-ranks device time
+with token ids already resident in HBM; `e2e` = the same through host buffers (pinned H2D of the token
+ids + D2H of mel_post inside the timed region).  `--impl reference` times the reference's CPU forward
+(the oracle port of it: the Python reference itself cannot travel to the GPU box) on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'mel_frames_per_sec'
+UNIT = 'frames/s'
+B, T = 64, 200
+SEED = 1234
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            p = json.load(f)
+        return {'hbm': p['hbm_gbs'], 'bf16': p['bf16_tflops'], 'bf16_sustained': p.get('bf16_tflops_sustained'),
+                'source': 'measured (MEASURED_PEAKS.json)'}
+    except Exception:
+        return {'hbm': 6650.0, 'bf16': 1590.0, 'bf16_sustained': 1400.0, 'source': 'fallback (B200_PROFILING.md)'}
+
+
+def build_model(durations: str):
+    """Random-init weights of the named architecture (there is no checkpoint to download)."""
+    from forwardtacotron_b200.configs import default_config
+    from forwardtacotron_b200.models import init_tts_model
+    torch.manual_seed(SEED)
+    model = init_tts_model(default_config('forward_tacotron'))
+    if durations == 'spread':           # SURVEY §8d regime B: shift the duration head so durations vary
+        with torch.no_grad():
+            model.dur_pred.lin.weight.mul_(8.0)
+            model.dur_pred.lin.bias.fill_(3.0)
+    return model.eval()
+
+
+def make_tokens(batch, rank=0):
+    g = torch.Generator().manual_seed(SEED + rank)
+    return torch.randint(1, 135, (batch, T), generator=g, dtype=torch.int64)
+
+
+class ClockSampler:
+    QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.QUERY}',
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == 'active'})
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(sm)}
+
+
+def cpu_forward_timing(sd, batch, runs, warm, threads):
+    """Oracle port of the reference's generate() on the host cores (fused library GRU/LSTM = the kernels the
+    reference itself reaches through torch.nn)."""
+    from oracle import ft_oracle as O
+    torch.set_num_threads(threads)
+    x = make_tokens(batch)
+    O.use_library_rnn(True)
+    times, frames = [], 0
+    try:
+        for i in range(warm + runs):
+            t0 = time.perf_counter()
+            out = O.ft_generate(sd, x)
+            dt = time.perf_counter() - t0
+            if i >= warm:
+                times.append(dt)
+            frames = int(out['mel_lens'].sum())
+    finally:
+        O.use_library_rnn(False)
+    return frames, times
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    model = build_model(args.durations)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    total = args.steps + args.warmup
+    batch = B if total * 5.0 <= 240 else (16 if total * 1.3 <= 240 else 4)
+    frames, times = cpu_forward_timing(sd, batch, args.steps, args.warmup, threads)
+    sec = sum(times) / len(times)
+    value = frames / sec
+    sample = f'{batch} of {B} sentences x {T} phonemes per step (same model, same token distribution)'
+    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'ForwardTacotron singlespeaker generate(), {B}x{T} phonemes, alpha=1.0, '
+                                   f'random-init, durations={args.durations}', 'frames_per_step': frames},
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from forwardtacotron_b200 import runtime as rt
+    dev = torch.device('cuda', local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    peaks = load_peaks()
+    model = build_model(args.durations).to(dev)
+    handle = rt.Handle.get(dev)
+    x_pin = make_tokens(B, rank).pin_memory()
+    x_dev = x_pin.to(dev)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        out = model.generate(x_dev)
+    torch.cuda.synchronize(dev)
+    frames = int((out['dur'] + 0.5).long().sum())                        # valid mel frames per step (this rank)
+    M = out['mel'].shape[2]
+    host_out = torch.empty(out['mel_post'].shape, dtype=torch.float32).pin_memory()
+
+    def timed(step_fn):
+        evs = []
+        barrier()
+        for _ in range(args.steps):
+            flush.zero_()                                                # evict L2 between timed iterations
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            step_fn()
+            b.record()
+            evs.append((a, b))
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def step_resident():
+        model.generate(x_dev)
+
+    def step_e2e():
+        xd = x_pin.to(dev, non_blocking=True)
+        o = model.generate(xd)
+        host_out.copy_(o['mel_post'], non_blocking=True)
+
+    with ClockSampler(local_rank) as clocks:
+        l0 = handle.launch_count()
+        ms_value = timed(step_resident)
+        launches = (handle.launch_count() - l0) // args.steps
+        ms_e2e = timed(step_e2e)
+        # per-launch device times of the two programs (buffers still hold the last step's data)
+        st = model.__dict__['_accel']
+        per = {}
+        for key in (('tok', B, T), ('frame', B, M)):
+            prog = st['programs'][key]
+            for rep in range(4):
+                flush.zero_()
+                for i, (info, ms) in enumerate(prog.run_timed()):
+                    if rep:
+                        e = per.setdefault((key[0], i), {'info': info, 'ms': 0.0})
+                        e['ms'] += ms / 3.0
+    clk = clocks.summary()
+
+    frames_t = torch.tensor([frames], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(frames_t)
+    total_frames = float(frames_t.item())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    kernels = []
+    for (side, i), e in per.items():
+        info, ms = e['info'], e['ms']
+        k = {'side': side, 'label': info['label'], 'kind': info['kind'], 'ms': round(ms, 4)}
+        if info['kind'] == 'gemm':
+            k['tflops'] = round(info['flops'] / ms / 1e9, 1)
+        if info['kind'] in ('rnn', 'glue') and info['bytes']:
+            k['gbs'] = round(info['bytes'] / ms / 1e6, 1)
+        if info['kind'] == 'rnn':
+            k['us_per_step'] = round(ms * 1e3 / info['steps'], 3)
+        kernels.append((k, info))
+    kernels.sort(key=lambda t: -t[0]['ms'])
+    top, top_info = kernels[0]
+    if top['kind'] == 'gemm':
+        peak = peaks['bf16'] / 2.0
+        ach = top_info['flops'] / top['ms'] / 1e9
+        roof = {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak,
+                'traffic': None, 'kernel': f"conv_gemm_tc_kernel[{top['label']}]",
+                'peak_note': f"kind::tf32 = half of the {peaks['source']} bf16 burst figure {peaks['bf16']}"}
+    else:
+        ach = top_info['bytes'] / top['ms'] / 1e6
+        roof = {'bound': 'hbm', 'achieved': ach, 'peak': peaks['hbm'], 'unit': 'GB/s', 'frac': ach / peaks['hbm'],
+                'traffic': None, 'kernel': f"rnn_persistent_kernel[{top['label']}]",
+                'peak_note': f"{peaks['source']}; latency-bound recurrence: {top.get('us_per_step')} us/step"}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+        cf, ct = cpu_forward_timing(sd, 16, runs=2, warm=1, threads=threads)
+        cpu = {'value': cf / (sum(ct) / len(ct)), 'unit': UNIT, 'cores': threads, 'kind': 'port',
+               'sample': f'16 of {B} sentences x {T} phonemes, oracle port of generate(), 1 warm-up + 2 timed runs'}
+
+    sec = ms_value / 1e3
+    line = {'metric': METRIC, 'value': total_frames * args.steps / sec, 'unit': UNIT, 'n_gpus': world,
+            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_value / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'tf32',
+            'data': 'synthetic',
+            'config': {'workload': f'ForwardTacotron singlespeaker generate(), {B}x{T} phonemes per GPU, alpha=1.0, '
+                                   f'random-init, durations={args.durations}', 'frames_per_step_per_gpu': frames,
+                       'padded_mel_len': M, 'l2': 'flushed between timed iterations (512 MiB memset)',
+                       'parallelism': f'sentence-sharded replicas x{world}'},
+            'e2e': {'value': total_frames * args.steps / (ms_e2e / 1e3), 'unit': UNIT,
+                    'h2d_bytes_per_step': x_pin.numel() * 8, 'd2h_bytes_per_step': host_out.numel() * 4},
+            'gpu_launches': int(launches), 'clocks': clk, 'roofline': roof,
+            'kernels': [k for k, _ in kernels[:12]]}
+    if cpu is not None:
+        line['cpu_baseline'] = cpu
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--durations', default='fallback', choices=['fallback', 'spread'],
+                    help="'fallback': as-is random init -> every duration 2 (forward_tacotron.py:176-177); "
+                         "'spread': duration head shifted so durations vary (SURVEY §8d regime B)")
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

@@ -33,6 +33,8 @@ class Program:
         self._rnn_plans: List[int] = []
         self._pending: List[rt.GemmProblem] = []
         self._keep: list = []                         # tensors the plans point into
+        self.info: List[dict] = []                    # per step: kind, label, algorithmic flops / bytes
+        self._label = ''
 
     # ---- buffers ---------------------------------------------------------------------------
     def buf(self, name: str, cols: int) -> torch.Tensor:
@@ -74,6 +76,7 @@ class Program:
         p.out_col0 = out_col0
         p.out_t = rt.ptr(out_t)
         p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
+        p._label = self._label
         self._pending.append(p)
         self._keep += [a, w, out, residual, out_t]
 
@@ -84,10 +87,19 @@ class Program:
         # heaviest tiles first (tile cost ~ taps*cin*bn) for the static round-robin scheduler
         probs = sorted(self._pending, key=lambda q: -(q.taps * q.cin * q.bn))
         self._pending = []
+        g = self.geo
+        valid = g.batch * g.seq_len
         for i in range(0, len(probs), 32):
-            plan = self.h.gemm_plan(probs[i:i + 32])
+            grp = probs[i:i + 32]
+            plan = self.h.gemm_plan(grp)
             self._gemm_plans.append(plan)
             self.steps.append(lambda plan=plan: self.h.gemm_run(plan))
+            # algorithmic work: valid rows only (gap rows and the maxpool halo are overhead)
+            flops = sum(2.0 * valid * q.cin * q.taps * q.n for q in grp)
+            nbytes = sum(4.0 * valid * (q.cin + q.n) + 4.0 * q.taps * q.n * q.cin for q in grp)
+            labels = sorted({getattr(q, '_label', '') for q in grp})
+            self.info.append({'kind': 'gemm', 'label': '+'.join(l for l in labels if l) or 'gemm',
+                              'flops': flops, 'bytes': nbytes, 'problems': len(grp)})
 
     def rnn(self, specs):
         """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one cooperative launch."""
@@ -105,14 +117,38 @@ class Program:
         plan = self.h.rnn_plan(probs)
         self._rnn_plans.append(plan)
         self.steps.append(lambda plan=plan: self.h.rnn_run(plan))
+        valid = g.batch * g.seq_len
+        flops = sum(2.0 * 2 * valid * r.hidden * (4 if r.cell else 3) * r.hidden for r, _, _, _ in specs)
+        # x-projection read + h write per step, W_hh once
+        nbytes = sum(4.0 * valid * (2 * (4 if r.cell else 3) * r.hidden + 2 * r.hidden) + 4.0 * r.w_hh.numel()
+                     for r, _, _, _ in specs)
+        self.info.append({'kind': 'rnn', 'label': self._label or 'rnn', 'flops': flops, 'bytes': nbytes,
+                          'steps': g.seq_len, 'problems': len(specs)})
 
-    def call(self, fn: Callable[[], None]):
+    def call(self, fn: Callable[[], None], label: str = 'glue', nbytes: float = 0.0):
         self.flush()
         self.steps.append(fn)
+        self.info.append({'kind': 'glue', 'label': label, 'flops': 0.0, 'bytes': nbytes})
+
+    def label(self, text: str):
+        self._label = text
 
     def run(self):
         for s in self.steps:
             s()
+
+    def run_timed(self):
+        """Like run(), with a CUDA-event pair around every launch on the current stream.
+        Returns [(info, milliseconds)] after a device synchronize (profiling aid for bench.py)."""
+        evs = []
+        for s in self.steps:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            s()
+            b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize(self.device)
+        return [(i, a.elapsed_time(b)) for i, (a, b) in zip(self.info, evs)]
 
     def close(self):
         for p in self._gemm_plans:
@@ -155,18 +191,25 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     xp = prog.buf(f'{tag}.xproj', c.rnn.ih.n)
     levels = []
 
+    def named(name, fn):
+        def run():
+            prog.label(f'{tag}.{name}')
+            fn()
+            prog.label('')
+        return run
+
     def l_bank():   # conv bank k=1..K, each trimmed to L, ReLU->BN, + MaxPool1d(2,1,1)[:L] fused (:97-105)
         for k, w in enumerate(c.bank):
             prog.gemm(x, w, bank, out_col0=k * ch, epilogue=rt.EPI_MAXPOOL)
-    levels.append(l_bank)
-    levels.append(lambda: prog.gemm(bank, c.proj1, p1))                               # :109
-    levels.append(lambda: prog.gemm(p1, c.proj2, p2, residual=x))                     # :111-114
-    levels.append(lambda: prog.gemm(p2, c.pre_highway, hw[0]))                        # :118
-    for i, w in enumerate(c.highways):                                                # :119-120
-        levels.append(lambda i=i, w=w: prog.gemm(hw[i & 1], w, hw[(i + 1) & 1], epilogue=rt.EPI_HIGHWAY,
-                                                 residual=hw[i & 1]))
+    levels.append(named('bank', l_bank))
+    levels.append(named('proj1', lambda: prog.gemm(bank, c.proj1, p1)))                           # :109
+    levels.append(named('proj2', lambda: prog.gemm(p1, c.proj2, p2, residual=x)))                 # :111-114
+    levels.append(named('pre_highway', lambda: prog.gemm(p2, c.pre_highway, hw[0])))              # :118
+    for i, w in enumerate(c.highways):                                                            # :119-120
+        levels.append(named(f'highway{i}', lambda i=i, w=w: prog.gemm(
+            hw[i & 1], w, hw[(i + 1) & 1], epilogue=rt.EPI_HIGHWAY, residual=hw[i & 1])))
     last = hw[len(c.highways) & 1]
-    levels.append(lambda: prog.gemm(last, c.rnn.ih, xp, round_out=False))             # W_ih half of :123
+    levels.append(named('gru_ih', lambda: prog.gemm(last, c.rnn.ih, xp, round_out=False)))        # W_ih half of :123
     return levels, (c.rnn, xp, out, out_col0)
 
 
@@ -184,10 +227,16 @@ def predictor_levels(prog: Program, tag: str, p: PredictorPack, emb: torch.Tenso
     c = [prog.buf(f'{tag}.c0', ch), prog.buf(f'{tag}.c1', ch)]
     xp = prog.buf(f'{tag}.xproj', p.rnn.ih.n)
     h = prog.buf(f'{tag}.h', 2 * p.rnn.hidden)
-    levels = [lambda: prog.gemm(emb, p.convs[0], c[0]),
-              lambda: prog.gemm(c[0], p.convs[1], c[1]),
-              lambda: prog.gemm(c[1], p.convs[2], c[0]),
-              lambda: prog.gemm(c[0], p.rnn.ih, xp, round_out=False)]
+    def named(name, fn):
+        def run():
+            prog.label(f'{tag}.{name}')
+            fn()
+            prog.label('')
+        return run
+    levels = [named('conv0', lambda: prog.gemm(emb, p.convs[0], c[0])),
+              named('conv1', lambda: prog.gemm(c[0], p.convs[1], c[1])),
+              named('conv2', lambda: prog.gemm(c[1], p.convs[2], c[0])),
+              named('gru_ih', lambda: prog.gemm(c[0], p.rnn.ih, xp, round_out=False))]
     return levels, (p.rnn, xp, h, 0), h
 
 

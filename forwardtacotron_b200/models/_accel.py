@@ -88,13 +88,19 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     mel_post = prog.dense('mel_post', (batch, n_mels, M))
     post = prog.buf('postnet.h', 2 * packs['postnet'].rnn.hidden)
 
+    prog.label('lstm_ih')
     prog.gemm(x, lstm.ih, xp, round_out=False)                    # W_ih half of self.lstm (:224)
+    prog.label('lstm')
     prog.rnn([(lstm, xp, hl, 0)])
+    prog.label('lin')
     prog.gemm(hl, packs['lin'], mel_cl, out_t=mel)                # self.lin + transpose (:226-227)
     prog.flush()
+    prog.label('')
     levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post)
     eng.run_levels(prog, [levels])
+    prog.label('postnet.gru')
     prog.rnn([gru])
+    prog.label('post_proj')
     prog.gemm(post, packs['post_proj'], None, out_t=mel_post)     # self.post_proj + transpose (:230-231)
     prog.flush()
     return prog

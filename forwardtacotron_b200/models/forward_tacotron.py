@@ -157,7 +157,9 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             branches.append(levels)
             grus.append(gru)
         eng.run_levels(prog, branches)
+        prog.label('token_side_grus')
         prog.rnn(grus)
+        prog.label('')
         for name, p, hbuf in heads:
             y = prog.dense(f'{name}.y', (batch, T))
             prog.call(lambda p=p, hbuf=hbuf, y=y, name=name: h.rowdot(
