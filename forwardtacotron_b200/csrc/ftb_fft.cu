@@ -13,7 +13,7 @@ __global__ void __launch_bounds__(256)
 add_layernorm_kernel(const float* __restrict__ x, const float* __restrict__ res, int ld, int e,
                      const float* __restrict__ g1, const float* __restrict__ b1, const float* __restrict__ g2,
                      const float* __restrict__ b2, int batch, int seq_len, int seq_stride, float* __restrict__ out,
-                     int round) {
+                     float* __restrict__ out_full, int round) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
   if (row >= static_cast<long long>(batch) * seq_len) return;
@@ -55,7 +55,10 @@ add_layernorm_kernel(const float* __restrict__ x, const float* __restrict__ res,
 #pragma unroll
   for (int i = 0; i < 32; ++i) {
     const int c = lane + i * 32;
-    if (i < per && c < e) out[off + c] = round ? round_tf32(v[i]) : v[i];
+    if (i < per && c < e) {
+      out[off + c] = round ? round_tf32(v[i]) : v[i];
+      if (out_full) out_full[off + c] = v[i];
+    }
   }
 }
 
@@ -63,7 +66,7 @@ add_layernorm_kernel(const float* __restrict__ x, const float* __restrict__ res,
 __global__ void __launch_bounds__(256)
 posenc_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, const float* __restrict__ x_in,
               const float* __restrict__ pe, const float* __restrict__ scale_ptr, int e, int batch, int seq_len,
-              int seq_stride, float* __restrict__ out, int round) {
+              int seq_stride, float* __restrict__ out, float* __restrict__ out_full, int round) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
   if (row >= static_cast<long long>(batch) * seq_len) return;
@@ -75,6 +78,7 @@ posenc_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, 
   for (int c = lane; c < e; c += 32) {
     const float v = src[c] + sc * per[c];
     out[off + c] = round ? round_tf32(v) : v;
+    if (out_full) out_full[off + c] = v;
   }
 }
 
@@ -173,24 +177,24 @@ using namespace ftb;
 
 extern "C" int ftb_add_layernorm(ftb_handle h, const float* x, const float* res, int ld, int e, const float* gamma,
                                  const float* beta, const float* gamma2, const float* beta2, int batch, int seq_len,
-                                 int seq_stride, float* out, int round_tf32, void* stream) {
+                                 int seq_stride, float* out, float* out_full, int round_tf32, void* stream) {
   if (!h || !x || !gamma || !beta || !out || e < 1 || e > 1024 || e > ld || batch < 1 || seq_len < 1)
     return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * seq_len;
   add_layernorm_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, res, ld, e, gamma, beta, gamma2, beta2, batch, seq_len, seq_stride, out, round_tf32);
+      x, res, ld, e, gamma, beta, gamma2, beta2, batch, seq_len, seq_stride, out, out_full, round_tf32);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }
 
 extern "C" int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, const float* x_in, const float* pe,
                           const float* scale_ptr, int e, int batch, int seq_len, int seq_stride, float* out,
-                          int round_tf32, void* stream) {
+                          float* out_full, int round_tf32, void* stream) {
   if (!h || !pe || !scale_ptr || !out || e < 1 || batch < 1 || seq_len < 1) return FTB_E_ARG;
   if (tok ? !table : !x_in) return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * seq_len;
   posenc_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      tok, table, x_in, pe, scale_ptr, e, batch, seq_len, seq_stride, out, round_tf32);
+      tok, table, x_in, pe, scale_ptr, e, batch, seq_len, seq_stride, out, out_full, round_tf32);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }

@@ -208,9 +208,13 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
               for (int q = 0; q < 4; ++q) {
                 const float a1 = x1[j + q] + __ldg(p->bias0 + u + j + q);
                 const float a2 = x2[j + q] + __ldg(p->bias0 + units + u + j + q);
-                y[q] = epi_finish(p, epi_highway(a1, a2, xs[q]));
+                y[q] = epi_highway(a1, a2, xs[q]);
               }
-              *reinterpret_cast<float4*>(o + j) = make_float4(y[0], y[1], y[2], y[3]);
+              if (p->out_full)
+                *reinterpret_cast<float4*>(p->out_full + r * p->out_ld + p->out_col0 + u + j) =
+                    make_float4(y[0], y[1], y[2], y[3]);
+              *reinterpret_cast<float4*>(o + j) =
+                  make_float4(epi_finish(p, y[0]), epi_finish(p, y[1]), epi_finish(p, y[2]), epi_finish(p, y[3]));
             }
           }
         }
@@ -252,6 +256,12 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
 #pragma unroll
               for (int j = 0; j < CHUNK; ++j)
                 if (nb + j < N) ot[static_cast<long long>(j) * p->seq_len] = v[j];
+            }
+            if (p->out_full) {
+              float* of = p->out_full + r * p->out_ld + p->out_col0 + nb;
+#pragma unroll
+              for (int j = 0; j < CHUNK; ++j)
+                if (nb + j < N) of[j] = v[j];
             }
             if (p->out) {
               float* o = p->out + r * p->out_ld + p->out_col0 + nb;
@@ -323,6 +333,7 @@ __global__ void conv_gemm_simt_kernel(const GemmProblemDev* __restrict__ probs, 
       if (p->residual) v += p->residual[r * p->res_ld + n];
       if (p->out_t) p->out_t[(static_cast<long long>(b) * N + n) * p->seq_len + t] = v;
     }
+    if (p->out_full) p->out_full[r * p->out_ld + p->out_col0 + n] = v;
     if (p->out) p->out[r * p->out_ld + p->out_col0 + n] = epi_finish(p, v);
   }
 }
@@ -386,7 +397,8 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
       return FTB_E_ARG;
     }
     d.a = q.a; d.w = q.w; d.bias0 = q.bias0; d.scale = q.scale; d.shift = q.shift;
-    d.residual = q.residual; d.out = q.out; d.out_t = q.out_t;
+    d.residual = q.residual; d.out = q.out; d.out_t = q.out_t; d.out_full = q.out_full;
+    if (q.out_full && (!q.out || !aligned16(q.out_full))) return FTB_E_ALIGN;
     d.rows = q.rows; d.lda = q.lda; d.cin = q.cin; d.taps = q.taps; d.tap0 = q.tap0;
     d.w_tap_rows = q.w_tap_rows; d.n = q.n; d.bn = q.bn; d.epilogue = q.epilogue; d.flags = q.flags;
     d.res_ld = q.res_ld; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;

@@ -24,6 +24,7 @@ struct alignas(128) GemmProblemDev {
   const float* residual;
   float* out;
   float* out_t;
+  float* out_full;
   long long rows;
   int lda, cin, taps, tap0, w_tap_rows, n, bn, epilogue, flags;
   int res_ld, out_ld, out_col0;
@@ -32,7 +33,7 @@ struct alignas(128) GemmProblemDev {
   int m_tiles, n_tiles;  // tile grid of this problem
   int m_step, m_shift;   // tile i covers rows [i*m_step + m_shift, +128)
   int tile_base;         // first global tile id
-  int pad_[3];
+  int pad_[1];
 };
 
 struct GemmPlan {

@@ -30,7 +30,7 @@ embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, i
 
 __global__ void __launch_bounds__(256)
 rowdot_kernel(const float* __restrict__ x, int x_ld, int k, const float* __restrict__ w,
-              const float* __restrict__ bias, int n_out, float inv_alpha, int batch, int T, int seq_stride,
+              const float* __restrict__ bias, int n_out, float alpha, int batch, int T, int seq_stride,
               float* __restrict__ y) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
@@ -50,7 +50,7 @@ rowdot_kernel(const float* __restrict__ x, int x_ld, int k, const float* __restr
     for (int s = 16; s > 0; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
   }
   if (lane == 0) {
-    for (int o = 0; o < n_out; ++o) y[row * n_out + o] = (acc[o] + bias[o]) * inv_alpha;
+    for (int o = 0; o < n_out; ++o) y[row * n_out + o] = __fdiv_rn(acc[o] + bias[o], alpha);   // `/ alpha`: a true division
   }
 }
 
@@ -85,11 +85,11 @@ extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, i
 }
 
 extern "C" int ftb_rowdot(ftb_handle h, const float* x, int x_ld, int k, const float* w, const float* bias,
-                          int n_out, float inv_alpha, int batch, int T, int seq_stride, float* y, void* stream) {
-  if (!h || !x || !w || !bias || !y || n_out < 1 || n_out > 4 || k < 1 || batch < 1 || T < 1) return FTB_E_ARG;
+                          int n_out, float alpha, int batch, int T, int seq_stride, float* y, void* stream) {
+  if (!h || !x || !w || !bias || !y || n_out < 1 || n_out > 4 || k < 1 || batch < 1 || T < 1 || alpha == 0.0f) return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * T;
   rowdot_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, x_ld, k, w, bias, n_out, inv_alpha, batch, T, seq_stride, y);
+      x, x_ld, k, w, bias, n_out, alpha, batch, T, seq_stride, y);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }

@@ -59,7 +59,8 @@ class Program:
     # ---- GEMM problems: queued, then flushed as one persistent launch ------------------------
     def gemm(self, a: torch.Tensor, w: PackedGemm, out: Optional[torch.Tensor], *, out_col0: int = 0,
              epilogue: int = rt.EPI_AFFINE, round_out: bool = True, residual: Optional[torch.Tensor] = None,
-             out_t: Optional[torch.Tensor] = None, cin: Optional[int] = None):
+             out_t: Optional[torch.Tensor] = None, cin: Optional[int] = None,
+             out_full: Optional[torch.Tensor] = None):
         g = self.geo
         p = rt.GemmProblem()
         p.a, p.rows, p.lda = a.data_ptr(), g.rows, a.shape[1]
@@ -75,10 +76,12 @@ class Program:
         p.out_ld = out.shape[1] if out is not None else 0
         p.out_col0 = out_col0
         p.out_t = rt.ptr(out_t)
+        p.out_full = rt.ptr(out_full)
+        assert out_full is None or (out is not None and out_full.shape == out.shape)
         p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
         p._label = self._label
         self._pending.append(p)
-        self._keep += [a, w, out, residual, out_t]
+        self._keep += [a, w, out, residual, out_t, out_full]
 
     def flush(self):
         """Close the current group: everything queued since the last flush runs as one launch."""
@@ -179,7 +182,8 @@ class CbhgPack:
         self.in_channels, self.channels = in_channels, channels
 
 
-def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torch.Tensor, out_col0: int = 0):
+def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torch.Tensor, out_col0: int = 0,
+                x_full: Optional[torch.Tensor] = None):
     """Returns the list of per-level closures for one CBHG over input buffer x [rows, in_channels];
     level i may be queued only after level i-1 has been flushed.  The last entry runs the BiGRU."""
     K = len(c.bank)
@@ -188,6 +192,9 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     p1 = prog.buf(f'{tag}.proj1', c.proj1.n)
     p2 = prog.buf(f'{tag}.proj2', c.proj2.n)
     hw = [prog.buf(f'{tag}.hw0', ch), prog.buf(f'{tag}.hw1', ch)]
+    # unrounded twins of the highway activations: the residual term (1-g)*x uses full fp32 values, only the
+    # GEMM operand copy is tf32-rounded
+    hwf = [prog.buf(f'{tag}.hw0_full', ch), prog.buf(f'{tag}.hw1_full', ch)]
     xp = prog.buf(f'{tag}.xproj', c.rnn.ih.n)
     levels = []
 
@@ -203,11 +210,13 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
             prog.gemm(x, w, bank, out_col0=k * ch, epilogue=rt.EPI_MAXPOOL)
     levels.append(named('bank', l_bank))
     levels.append(named('proj1', lambda: prog.gemm(bank, c.proj1, p1)))                           # :109
-    levels.append(named('proj2', lambda: prog.gemm(p1, c.proj2, p2, residual=x)))                 # :111-114
-    levels.append(named('pre_highway', lambda: prog.gemm(p2, c.pre_highway, hw[0])))              # :118
+    levels.append(named('proj2', lambda: prog.gemm(p1, c.proj2, p2,                               # :111-114
+                                                   residual=x_full if x_full is not None else x)))
+    levels.append(named('pre_highway', lambda: prog.gemm(p2, c.pre_highway, hw[0], out_full=hwf[0])))   # :118
     for i, w in enumerate(c.highways):                                                            # :119-120
         levels.append(named(f'highway{i}', lambda i=i, w=w: prog.gemm(
-            hw[i & 1], w, hw[(i + 1) & 1], epilogue=rt.EPI_HIGHWAY, residual=hw[i & 1])))
+            hw[i & 1], w, hw[(i + 1) & 1], epilogue=rt.EPI_HIGHWAY, residual=hwf[i & 1],
+            out_full=hwf[(i + 1) & 1])))
     last = hw[len(c.highways) & 1]
     levels.append(named('gru_ih', lambda: prog.gemm(last, c.rnn.ih, xp, round_out=False)))        # W_ih half of :123
     return levels, (c.rnn, xp, out, out_col0)

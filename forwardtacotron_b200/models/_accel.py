@@ -2,7 +2,7 @@
 the frame-side (post length-regulator) program common to ForwardTacotron and
 MultiForwardTacotron, and the host-side result assembly."""
 from collections import OrderedDict
-from typing import Dict, Optional, Tuple
+from typing import Dict, Optional, Tuple  # noqa: F401
 
 import torch
 import torch.nn as nn
@@ -93,10 +93,11 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     prog.label('lstm')
     prog.rnn([(lstm, xp, hl, 0)])
     prog.label('lin')
-    prog.gemm(hl, packs['lin'], mel_cl, out_t=mel)                # self.lin + transpose (:226-227)
+    mel_full = prog.buf('mel_cl_full', n_mels)
+    prog.gemm(hl, packs['lin'], mel_cl, out_t=mel, out_full=mel_full)   # self.lin + transpose (:226-227)
     prog.flush()
     prog.label('')
-    levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post)
+    levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full)
     eng.run_levels(prog, [levels])
     prog.label('postnet.gru')
     prog.rnn([gru])
@@ -117,3 +118,114 @@ def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
     handle.lr_scan(dur, B, T, apply_fallback, cum, lens, meta)
     m = meta.cpu()
     return cum, lens, int(m[0]), int(m[2])
+
+
+def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program, prog: eng.Program,
+                          pre: torch.Tensor, extra: Optional[torch.Tensor], c2: int, dur_hat: torch.Tensor,
+                          pitch_hat: torch.Tensor, energy_hat: torch.Tensor, cum: torch.Tensor, lens: torch.Tensor,
+                          M: int, pitch_strength: float, energy_strength: float,
+                          round_tf32: bool = True) -> Dict[str, torch.Tensor]:
+    """K5/K6 gather (projection adds + optional speaker tail fused into the source read) into the frame
+    program's 'lr' buffer, then the frame-side launches; returns the reference's result dict
+    (forward_tacotron.py:214-233)."""
+    B, T = dur_hat.shape
+    pitch = pitch_hat.reshape(B, T).to(torch.float32).contiguous()
+    energy = energy_hat.reshape(B, T).to(torch.float32).contiguous()
+    C1 = pre.shape[1]
+    g = rt.LrGatherArgs()
+    g.x, g.x_stride, g.x_ld, g.c1 = pre.data_ptr(), tok_prog.geo.stride, C1, C1
+    g.extra, g.c2 = rt.ptr(extra) if c2 else None, c2
+    g.pitch, g.energy = pitch.data_ptr(), energy.data_ptr()
+    (wp, bp), (we, be) = packs['pitch_proj'], packs['energy_proj']
+    g.wp, g.bp, g.ps = wp.data_ptr(), bp.data_ptr(), pitch_strength
+    g.we, g.be, g.es = we.data_ptr(), be.data_ptr(), energy_strength
+    g.cum, g.lens = cum.data_ptr(), lens.data_ptr()
+    g.batch, g.T, g.M = B, T, M
+    lr = prog.bufs['lr']
+    g.out, g.out_stride, g.out_ld = lr.data_ptr(), prog.geo.stride, lr.shape[1]
+    g.idx, g.round_tf32 = None, int(round_tf32)
+    handle.lr_gather(g)
+    prog.run()
+    mel = prog.bufs['mel'].clone()
+    mel_post = prog.bufs['mel_post'].clone() if 'mel_post' in prog.bufs else mel
+    return {'mel': mel, 'mel_post': mel_post, 'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat}
+
+
+# ------------------------------------------------------------------------------------------------
+# FFT-block transformer (FastPitch / MultiFastPitch; common_layers.py:148-223)
+# ------------------------------------------------------------------------------------------------
+
+class FftLayerPack:
+    def __init__(self, layer):
+        a = layer.self_attn
+        self.in_proj = pk.pack_linear(a.in_proj_weight, a.in_proj_bias)
+        self.out_proj = pk.pack_linear(a.out_proj.weight, a.out_proj.bias)
+        self.conv1 = pk.pack_conv(layer.conv1.weight, layer.conv1.bias, relu=True)       # conv -> +bias -> ReLU
+        self.conv2 = pk.pack_conv(layer.conv2.weight, layer.conv2.bias)
+        f = lambda t: t.detach().float().contiguous()
+        self.n1 = (f(layer.norm1.weight), f(layer.norm1.bias))
+        self.n2 = (f(layer.norm2.weight), f(layer.norm2.bias))
+
+
+class TransformerPack:
+    """Packed weights of one ForwardTransformer (common_layers.py:188-223)."""
+
+    def __init__(self, m):
+        self.d_model, self.heads = m.d_model, m.heads
+        self.layers = [FftLayerPack(l) for l in m.layers]
+        self.norm = (m.norm.weight.detach().float().contiguous(), m.norm.bias.detach().float().contiguous())
+        self.pe = m.pos_encoder.pe.detach().float()[:, 0, :].contiguous()           # [max_len, E]
+        self.scale = m.pos_encoder.scale.detach().float().contiguous()
+        self.max_len = self.pe.shape[0]
+
+
+def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torch.Tensor, out: torch.Tensor,
+                       key_tok: Optional[torch.Tensor], round_final: bool = True,
+                       x_full: Optional[torch.Tensor] = None):
+    """Per-level closures of one ForwardTransformer over x [rows, E] (positional encoding already applied);
+    the last level writes LayerNorm_final(LayerNorm2(...)) into `out`.  Post-norm FFT block
+    (common_layers.py:170-185): x = LN1(x + MHA(x)); x = LN2(x + conv2(relu(conv1(x))))."""
+    h, g = prog.h, prog.geo
+    E = tp.d_model
+    F = tp.layers[0].conv1.n
+    qkv = prog.buf(f'{tag}.qkv', 3 * E)
+    att = prog.buf(f'{tag}.att', E)
+    y = prog.buf(f'{tag}.blk_y', E)
+    x1 = prog.buf(f'{tag}.x1', E)
+    x1f = prog.buf(f'{tag}.x1_full', E)          # unrounded twins: residual adds use full fp32 values
+    c1 = prog.buf(f'{tag}.c1', F)
+    xs = [x, prog.buf(f'{tag}.x2', E)]
+    xsf = [x_full if x_full is not None else x, prog.buf(f'{tag}.x2_full', E)]
+    levels = []
+
+    def named(name, fn):
+        def run():
+            prog.label(f'{tag}.{name}')
+            fn()
+            prog.label('')
+        return run
+
+    n = len(tp.layers)
+    for i, l in enumerate(tp.layers):
+        src = xs[0] if i == 0 else xs[1]
+        srcf = xsf[0] if i == 0 else xsf[1]
+        dst = out if i == n - 1 else xs[1]
+        dstf = None if i == n - 1 else xsf[1]
+        last = tp.norm if i == n - 1 else (None, None)
+        levels.append(named(f'l{i}.in_proj', lambda l=l, src=src: prog.gemm(src, l.in_proj, qkv, round_out=False)))
+        levels.append(lambda l=l: prog.call(
+            lambda: h.mha(qkv, E, tp.heads, key_tok, g.batch, g.seq_len, g.stride, att),
+            label=f'{tag}.mha', nbytes=4.0 * g.batch * g.seq_len * 4 * E))
+        levels.append(named(f'l{i}.out_proj', lambda l=l, srcf=srcf: prog.gemm(att, l.out_proj, y, residual=srcf,
+                                                                               round_out=False)))
+        levels.append(lambda l=l: prog.call(
+            lambda: h.add_layernorm(y, None, E, E, l.n1[0], l.n1[1], None, None, g.batch, g.seq_len, g.stride, x1,
+                                    out_full=x1f),
+            label=f'{tag}.norm1', nbytes=8.0 * g.batch * g.seq_len * E))
+        levels.append(named(f'l{i}.conv1', lambda l=l: prog.gemm(x1, l.conv1, c1)))
+        levels.append(named(f'l{i}.conv2', lambda l=l: prog.gemm(c1, l.conv2, y, residual=x1f, round_out=False)))
+        levels.append(lambda l=l, dst=dst, dstf=dstf, last=last: prog.call(
+            lambda: h.add_layernorm(y, None, E, E, l.n2[0], l.n2[1], last[0], last[1], g.batch, g.seq_len,
+                                    g.stride, dst, round_tf32=(round_final or dst is not out), out_full=dstf),
+            label=f'{tag}.norm2', nbytes=8.0 * g.batch * g.seq_len * E))
+    return levels

@@ -115,6 +115,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
     def _build_packs(self) -> dict:
         return {
             'embedding': pk.round_tf32(self.embedding.weight),
+            'embedding_full': self.embedding.weight.detach().float().contiguous(),
             'dur': _accel.pack_predictor(self.dur_pred), 'dur_emb': pk.round_tf32(self.dur_pred.embedding.weight),
             'pitch': _accel.pack_predictor(self.pitch_pred),
             'pitch_emb': pk.round_tf32(self.pitch_pred.embedding.weight),
@@ -152,8 +153,11 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         if prenet:
             emb = prog.buf('emb', packs['embedding'].shape[1])
             prog.call(lambda: h.embed(tok, packs['embedding'], emb, emb.shape[1], batch, T, geo.stride))
+            embf = prog.buf('emb_full', emb.shape[1])         # unrounded copy: the CBHG residual (:114)
+            prog.call(lambda: h.embed(tok, packs['embedding_full'], embf, embf.shape[1], batch, T, geo.stride,
+                                      round_tf32=False))
             out = prog.buf('prenet.h', 2 * packs['prenet'].rnn.hidden)
-            levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out)
+            levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out, x_full=embf)
             branches.append(levels)
             grus.append(gru)
         eng.run_levels(prog, branches)
@@ -164,7 +168,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             y = prog.dense(f'{name}.y', (batch, T))
             prog.call(lambda p=p, hbuf=hbuf, y=y, name=name: h.rowdot(
                 hbuf, hbuf.shape[1], hbuf.shape[1], p.lin_w, p.lin_b, 1,
-                (1.0 / prog.alpha) if name == 'dur' else 1.0, batch, T, geo.stride, y))
+                prog.alpha if name == 'dur' else 1.0, batch, T, geo.stride, y))
         prog.alpha = 1.0
         return prog
 
@@ -212,24 +216,8 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         pre = tok_prog.bufs['prenet.h']
         C = pre.shape[1]
         prog = self._program(st, ('frame', B, M), lambda: _accel.build_frame_program(h, packs, B, M, C, self.n_mels))
-        pitch = pitch_hat.reshape(B, T).to(torch.float32).contiguous()
-        energy = energy_hat.reshape(B, T).to(torch.float32).contiguous()
-        g = rt.LrGatherArgs()
-        g.x, g.x_stride, g.x_ld, g.c1 = pre.data_ptr(), tok_prog.geo.stride, C, C
-        g.extra, g.c2 = None, 0
-        g.pitch, g.energy = pitch.data_ptr(), energy.data_ptr()
-        (wp, bp), (we, be) = packs['pitch_proj'], packs['energy_proj']
-        g.wp, g.bp, g.ps = wp.data_ptr(), bp.data_ptr(), float(self.pitch_strength)
-        g.we, g.be, g.es = we.data_ptr(), be.data_ptr(), float(self.energy_strength)
-        g.cum, g.lens = cum.data_ptr(), lens.data_ptr()
-        g.batch, g.T, g.M = B, T, M
-        lr = prog.bufs['lr']
-        g.out, g.out_stride, g.out_ld = lr.data_ptr(), prog.geo.stride, C
-        g.idx, g.round_tf32 = None, 1
-        h.lr_gather(g)                                                        # :214-222
-        prog.run()                                                            # :224-231
-        return {'mel': prog.bufs['mel'].clone(), 'mel_post': prog.bufs['mel_post'].clone(), 'dur': dur_hat,
-                'pitch': pitch_hat, 'energy': energy_hat}
+        return _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, None, 0, dur_hat, pitch_hat, energy_hat,
+                                            cum, lens, M, float(self.pitch_strength), float(self.energy_strength))
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod

@@ -157,6 +157,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
     def _build_packs(self) -> dict:
         packs = {
             'embedding': pk.round_tf32(self.embedding.weight),
+            'embedding_full': self.embedding.weight.detach().float().contiguous(),
             'prenet': _accel.pack_cbhg(self.prenet),
             'lstm': pk.PackedRnn(self.lstm),
             'lin': pk.pack_linear(self.lin.weight, self.lin.bias),
@@ -212,8 +213,11 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         emb = prog.buf('emb', packs['embedding'].shape[1])
         prog.call(lambda: h.embed(tok, packs['embedding'], emb, emb.shape[1], batch, T, geo.stride),
                   label='embed')
+        embf = prog.buf('emb_full', emb.shape[1])             # unrounded copy: the CBHG residual
+        prog.call(lambda: h.embed(tok, packs['embedding_full'], embf, embf.shape[1], batch, T, geo.stride,
+                                  round_tf32=False), label='embed_full')
         out = prog.buf('prenet.h', 2 * packs['prenet'].rnn.hidden)
-        levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out)
+        levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out, x_full=embf)
         branches.append(levels)
         grus.append(gru)
         eng.run_levels(prog, branches)

@@ -24,8 +24,14 @@ def ceil_to(x: int, m: int) -> int:
 
 
 def pick_bn(n: int) -> int:
-    """N-tile width of the tcgen05 kernel: multiple of 16, at most 256."""
-    return min(256, ceil_to(n, 16))
+    """N-tile width of the tcgen05 kernel: a multiple of 16, at most 256, chosen to minimise the padded
+    width ceil(n/bn)*bn (ties -> the widest tile): 384 -> 192 x 2, 80 -> 80, 768 -> 256 x 3."""
+    best = None
+    for bn in range(256, 15, -16):
+        pad = ceil_to(n, bn)
+        if best is None or pad < best[0]:
+            best = (pad, bn)
+    return best[1]
 
 
 class PackedGemm:

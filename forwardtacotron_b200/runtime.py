@@ -27,7 +27,8 @@ class GemmProblem(C.Structure):
                 ('n', C.c_int32), ('bn', C.c_int32), ('epilogue', C.c_int32), ('flags', C.c_int32),
                 ('bias0', _fp), ('scale', _fp), ('shift', _fp), ('residual', _fp), ('res_ld', C.c_int32),
                 ('out', _fp), ('out_ld', C.c_int32), ('out_col0', C.c_int32),
-                ('out_t', _fp), ('batch', C.c_int32), ('seq_len', C.c_int32), ('seq_stride', C.c_int32)]
+                ('out_t', _fp), ('batch', C.c_int32), ('seq_len', C.c_int32), ('seq_stride', C.c_int32),
+                ('out_full', _fp)]
 
 
 class RnnProblem(C.Structure):
@@ -86,9 +87,9 @@ def load_library() -> C.CDLL:
                                C.c_int, C.c_int, C.c_int, _fp, _fp]
     lib.ftb_argmax_lastdim.argtypes = [_fp, _fp, C.c_int64, C.c_int, _fp, _fp]
     lib.ftb_add_layernorm.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp,
-                                      C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
+                                      C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, _fp]
     lib.ftb_posenc.argtypes = [_fp, _fp, _fp, _fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
-                               _fp, C.c_int, _fp]
+                               _fp, _fp, C.c_int, _fp]
     lib.ftb_mha.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
     _lib = lib
     return lib
@@ -177,20 +178,21 @@ class Handle:
         self.check(self.lib.ftb_embed(self.h, ptr(tok), ptr(table), e1, ptr(tok2), ptr(table2), e2, ptr(extra), e3,
                                       batch, T, stride, ptr(out), out_ld, int(round_tf32), self.stream()))
 
-    def rowdot(self, x, x_ld, k, w, bias, n_out, inv_alpha, batch, T, stride, y):
-        self.check(self.lib.ftb_rowdot(self.h, ptr(x), x_ld, k, ptr(w), ptr(bias), n_out, float(inv_alpha),
+    def rowdot(self, x, x_ld, k, w, bias, n_out, alpha, batch, T, stride, y):
+        self.check(self.lib.ftb_rowdot(self.h, ptr(x), x_ld, k, ptr(w), ptr(bias), n_out, float(alpha),
                                        batch, T, stride, ptr(y), self.stream()))
 
     def argmax(self, x, n, c, out):
         self.check(self.lib.ftb_argmax_lastdim(self.h, ptr(x), n, c, ptr(out), self.stream()))
 
-    def add_layernorm(self, x, res, ld, e, g, b, g2, b2, batch, L, stride, out, round_tf32=True):
+    def add_layernorm(self, x, res, ld, e, g, b, g2, b2, batch, L, stride, out, round_tf32=True, out_full=None):
         self.check(self.lib.ftb_add_layernorm(self.h, ptr(x), ptr(res), ld, e, ptr(g), ptr(b), ptr(g2), ptr(b2),
-                                              batch, L, stride, ptr(out), int(round_tf32), self.stream()))
+                                              batch, L, stride, ptr(out), ptr(out_full), int(round_tf32),
+                                              self.stream()))
 
-    def posenc(self, tok, table, x_in, pe, scale, e, batch, L, stride, out, round_tf32=True):
+    def posenc(self, tok, table, x_in, pe, scale, e, batch, L, stride, out, round_tf32=True, out_full=None):
         self.check(self.lib.ftb_posenc(self.h, ptr(tok), ptr(table), ptr(x_in), ptr(pe), ptr(scale), e, batch, L,
-                                       stride, ptr(out), int(round_tf32), self.stream()))
+                                       stride, ptr(out), ptr(out_full), int(round_tf32), self.stream()))
 
     def mha(self, qkv, e, heads, key_tok, batch, L, stride, out, round_tf32=True):
         self.check(self.lib.ftb_mha(self.h, ptr(qkv), e, heads, ptr(key_tok), batch, L, stride, ptr(out),

@@ -94,6 +94,8 @@ typedef struct {
   int32_t out_ld, out_col0;
   float* out_t;          /* optional [batch, n, seq_len] transposed, never rounded; or null  */
   int32_t batch, seq_len, seq_stride;
+  float* out_full;       /* optional [rows, out_ld]: the same values as `out` but never tf32-rounded (the
+                            copy a later layer adds as its residual); requires `out`; or null        */
 } ftb_gemm_problem;
 
 /* A plan = up to FTB_MAX_PROBLEMS independent problems run by ONE persistent launch. */
@@ -180,10 +182,10 @@ int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1,
               const float* extra, int e3,
               int batch, int T, int seq_stride, float* out, int out_ld, int round_tf32, void* stream);
 
-/* Predictor head: y[b,t,o] = (dot(x[b*seq_stride+t, :k], w[o,:]) + bias[o]) * inv_alpha
+/* Predictor head: y[b,t,o] = (dot(x[b*seq_stride+t, :k], w[o,:]) + bias[o]) / alpha
  * (self.lin + `/ alpha`, forward_tacotron.py:38-39).  n_out <= 4.  y is dense [batch, T, n_out]. */
 int ftb_rowdot(ftb_handle h, const float* x, int x_ld, int k, const float* w, const float* bias,
-               int n_out, float inv_alpha, int batch, int T, int seq_stride, float* y, void* stream);
+               int n_out, float alpha, int batch, int T, int seq_stride, float* y, void* stream);
 
 /* argmax over the last axis of [n, c] (c <= 8) -> int64 (multi_forward_tacotron.py:252, per (b,t)). */
 int ftb_argmax_lastdim(ftb_handle h, const float* x, int64_t n, int c, int64_t* out, void* stream);
@@ -192,17 +194,20 @@ int ftb_argmax_lastdim(ftb_handle h, const float* x, int64_t n, int c, int64_t* 
  * K7/K8  FFT-block pieces (FastPitch, common_layers.py:127-223)
  * ------------------------------------------------------------------------------------ */
 /* y = LayerNorm(x (+ res)) * gamma + beta, eps = 1e-5, over the last axis e (<= 1024), only
- * valid rows; optional second LayerNorm chained (the ForwardTransformer's final norm).   */
+ * valid rows; optional second LayerNorm chained (the ForwardTransformer's final norm).
+ * `out` is tf32-rounded when round_tf32 != 0 (it feeds a GEMM); `out_full` (optional) receives
+ * the unrounded values (the residual copy).                                                   */
 int ftb_add_layernorm(ftb_handle h, const float* x, const float* res, int ld, int e,
                       const float* gamma, const float* beta,
                       const float* gamma2, const float* beta2,
-                      int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
+                      int batch, int seq_len, int seq_stride, float* out, float* out_full, int round_tf32,
+                      void* stream);
 
 /* x[b,t,:] = emb[tok[b,t], :] + scale * pe[t, :]   (PositionalEncoding, common_layers.py:143-145);
  * tok == null: in-place x += scale*pe over an existing activation (post-LR postnet input). */
 int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, const float* x_in, const float* pe,
                const float* scale_ptr, int e, int batch, int seq_len, int seq_stride,
-               float* out, int round_tf32, void* stream);
+               float* out, float* out_full, int round_tf32, void* stream);
 
 /* 2..8-head self attention over qkv [rows, 3e] (packed in_proj output), softmax over keys with
  * optional key padding (tok[b,s] == 0 masked, common_layers.py:232-233); out [rows, e]. */

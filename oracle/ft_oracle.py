@@ -347,7 +347,7 @@ def mft_generate(sd: SD, x: torch.Tensor, speaker_emb: torch.Tensor, alpha: floa
     mel_post = linear(post, sd['post_proj.weight']).transpose(1, 2)
     return {'mel': mel, 'mel_post': mel_post, 'dur': torch.from_numpy(dur_clamped),
             'pitch': pitch_hat, 'energy': energy_hat, 'pitch_cond': pitch_cond.unsqueeze(1),
-            'mel_lens': torch.from_numpy(lens)}
+            'pitch_cond_logits': pc_logits, 'mel_lens': torch.from_numpy(lens)}
 
 
 # --------------------------------------------------------------------------
