@@ -13,7 +13,7 @@ SOURCES = ['ftb_api.cu', 'ftb_gemm.cu', 'ftb_rnn.cu', 'ftb_lr.cu', 'ftb_misc.cu'
 HEADERS = ['ftb_internal.h', 'ftb_ptx.cuh', os.path.join('..', '..', 'include', 'ftb200.h')]
 # fast-math is deliberately NOT enabled: the gate math needs accurate expf/tanhf.
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
-              '-Xcompiler', '-fPIC']
+              '-Xcompiler', '-fPIC'] + os.environ.get('FTB_NVCC_EXTRA', '').split()   # e.g. -DFTB_RNN_PROFILE
 
 
 def _nvcc():

@@ -41,7 +41,7 @@ extern "C" int ftb_destroy(ftb_handle h) {
   for (auto& kv : h->gemm_plans) cudaFree(kv.second.dev);
   for (auto& kv : h->rnn_plans) {
     cudaFree(kv.second.dev);
-    cudaFree(kv.second.counters);
+    for (void* x : kv.second.hx) cudaFree(x);
   }
   delete h;
   return 0;
@@ -92,7 +92,7 @@ extern "C" int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream) {
   if (!h) return FTB_E_ARG;
   auto it = h->rnn_plans.find(plan);
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
-  h->launches += static_cast<int64_t>(it->second.launches.size());
+  h->launches += static_cast<int64_t>(it->second.launches.size() + it->second.problems.size());   // + sentinel pre-fills
   return rnn_plan_launch(it->second, static_cast<cudaStream_t>(stream));
 }
 
@@ -101,7 +101,7 @@ extern "C" int ftb_rnn_plan_destroy(ftb_handle h, int plan) {
   auto it = h->rnn_plans.find(plan);
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
   cudaFree(it->second.dev);
-  cudaFree(it->second.counters);
+  for (void* x : it->second.hx) cudaFree(x);
   h->rnn_plans.erase(it);
   return 0;
 }

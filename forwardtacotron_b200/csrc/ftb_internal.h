@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <cstdint>
 #include <map>
 #include <vector>
@@ -52,6 +53,7 @@ struct RnnProblemDev {
   const float* w_hh;
   const float* b_hh;
   float* out;
+  __half* hx;            // fp16 exchange tensor [2][seq_len][batch][hidden], sentinel-armed before each run
   int cell, hidden, batch, seq_len, seq_stride, out_ld, out_col0;
   int gates;             // 3 or 4
   int units_per_cta;     // hidden units owned by one CTA
@@ -68,12 +70,16 @@ struct RnnProblemDev {
 struct RnnLaunch {
   int first = 0, count = 0;           // parts [first, first+count) of RnnPlan::dev
   int ctas = 0;
+  int smem = 0;                       // dynamic shared memory of this launch (max over its parts)
 };
 
 struct RnnPlan {
   RnnProblemDev* dev = nullptr;       // all parts of all launches
-  unsigned int* counters = nullptr;   // one counter per barrier group, zeroed on the stream before each run
+  unsigned int* counters = nullptr;   // unused since the in-band sentinel protocol (kept for ABI of the struct)
   int ngroups = 0;
+  std::vector<ftb_rnn_problem> problems;   // originals
+  std::vector<void*> hx;                   // per problem: fp16 exchange tensor (owned by the plan)
+  std::vector<size_t> hx_bytes;
   std::vector<RnnLaunch> launches;
 };
 

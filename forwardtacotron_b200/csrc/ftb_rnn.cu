@@ -1,21 +1,35 @@
 // K3/K4: persistent bidirectional GRU / LSTM recurrence for sm_100a.
 //
-// One cooperative launch runs every (problem, direction, batch-group, unit-slice) CTA of a
-// plan.  A CTA owns U hidden units (all gates: G*U rows of W_hh) for NB batch columns and
-// keeps its W_hh rows RESIDENT IN REGISTERS as tf32 mma.sync A-fragments for all time steps
-// (LSTM H=512: 64 rows x 512 = 128 KB per CTA, half the register file).  Per step:
-//     h_{t-1} (published through the layer's own output tensor, L2-resident)
-//       -> B-fragments by 128-bit ld.global.cg       [K is permuted so 8 consecutive k feed 4 MMAs]
-//       -> mma.sync.m16n8k8 tf32, fp32 accumulate, K split over KS warps
-//       -> partial sums through padded smem -> gate math in fp32 (c, h stay in registers)
-//       -> h_t stored (tf32-rounded: it is the next step's MMA operand and the next GEMM's A)
-//       -> ONE barrier per step among the `slices` CTAs that share (direction, batch group):
-//          release-add on a global counter, acquire-spin by one thread.
-// The tcgen05 path is deliberately not used here: the per-step GEMM is [G*U x H] x [H x NB]
-// with NB <= 32, latency- not throughput-bound, and the operands that change every step (h)
-// would have to be re-staged into swizzled smem for a UMMA descriptor; register-resident
-// weights + mma.sync keep the critical path to L2-load -> HMMA -> smem reduce.
+// One cooperative launch runs every (problem, direction, batch-group, unit-slice) CTA of a plan.
+// A CTA owns U = 32 hidden units (all gates: G*U rows of W_hh) for NB = 16 batch columns and keeps
+// its W_hh rows RESIDENT IN REGISTERS as fp16 mma.sync A-fragments for all time steps (LSTM H=512:
+// 128 rows x 512 = 128 KB per CTA, half the register file).
+//
+// Operand precision.  The recurrent product uses fp16 operands with fp32 accumulation: fp16 carries
+// the same 11 significant bits as tf32 (|h| <= 1 and |W_hh| ~ 1/sqrt(H) sit well inside its range; below
+// 6e-5 the absolute error is < 3e-8), but a legacy-path HMMA.16816 moves twice the MACs of the tf32
+// HMMA.1688 per issue slot -- measured here: tf32 mma.sync sustains ~290 MAC/clk/SM on B200 and was the
+// bound of the first version of this kernel (profiles/r1b_rnn_phases.txt).  h_t is therefore published
+// twice: as fp32 (exactly the fp16 value, hence tf32-exact) into the layer output the next GEMM reads,
+// and as fp16 into a compact exchange tensor hx[dir][t][b][H] that the other CTAs poll.
+//
+// Per step:
+//     h_{t-1} (fp16, L2-resident) -> staged ONCE per CTA into smem by 128-bit ld.relaxed.gpu loads that
+//         POLL THE DATA ITSELF: hx is pre-filled with 0xFFFF halves (an fp16 NaN no arithmetic here
+//         produces), so "h arrived" == "no sentinel left".  No counter, no __threadfence, no atomic on
+//         the critical path.  The K range is split over KS = 2 warp groups that synchronise with named
+//         barriers, so each half starts its MMAs as soon as its own bytes have landed.
+//       -> B-fragments from smem (one LDS.128 feeds two k-steps: K is permuted inside 32-wide blocks),
+//          mma.sync.m16n8k16 f16 -> fp32 accumulators
+//       -> partial sums through double-buffered padded smem -> ONE __syncthreads per step
+//       -> gate math in fp32 (c, h stay in registers; x-projection rows arrive through a 4-stage cp.async
+//          ring issued three steps ahead, so their DRAM latency is off the critical path)
+//       -> h_t stores (fp32 to `out`, fp16 pairs to hx).
+// tcgen05 is deliberately not used here: the per-step GEMM is [G*U x H] x [H x 16]; a UMMA would need W_hh
+// in shared memory (256 KB fp32-class for this slice) or TMEM (all 512 columns), and h re-staged into a
+// swizzled tile every step; the per-step cost is dominated by the L2 hand-off, not by the MMA issue.
 #include <cstdio>
+#include <cuda_fp16.h>
 
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
@@ -23,40 +37,73 @@
 namespace ftb {
 
 constexpr int RNN_THREADS = 512;
-constexpr int RNN_NB = 32;               // batch columns per CTA
-constexpr int RNN_U = 16;                // hidden units per CTA
+constexpr int RNN_U = 32;                // hidden units per CTA
+constexpr int RNN_NB = RNN_THREADS / RNN_U;   // 16 batch columns per CTA: one (unit, batch) pair per thread
+constexpr int RNN_KS = 2;                // K split (warp groups)
+constexpr int RNN_XS = 4;                // cp.async stages of the x-projection ring
 
-__device__ __forceinline__ void mma_tf32_16x8x8(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+// D(16x8, f32) += A(16x16, f16, row) * B(16x8, f16, col)
+__device__ __forceinline__ void mma_f16_16x8x16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
-      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
-__device__ __forceinline__ float4 ld_cg_f4(const float* p) {
-  float4 v;
-  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+// Coherent (L2) 128-bit load: the polled value IS the payload, so relaxed ordering is enough.
+__device__ __forceinline__ uint4 ld_relaxed_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
+__device__ __forceinline__ void st_relaxed_u32(void* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ bool has_sentinel(uint32_t w) {      // either fp16 half == 0xFFFF
+  return ((w & 0xFFFFu) == 0xFFFFu) || ((w >> 16) == 0xFFFFu);
+}
+__device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
+  const __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// exp/rcp at ~2 ulp: absolute gate error ~3e-7, far below the operand rounding of the h @ W_hh products
+__device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_fast(float x) { return __fdividef(2.0f, 1.0f + __expf(-2.0f * x)) - 1.0f; }
 
-template <int G, int H, int KS>
-__device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned* counters, float* smem_p) {
-  constexpr int U = RNN_U, NB = RNN_NB;
-  constexpr int RC = G * U;              // W_hh rows owned by this CTA
-  constexpr int RS = RC / 16;            // 16-row MMA strips
-  constexpr int WARPS = RS * KS;         // MMA warps (<= 16)
-  constexpr int KW = H / KS;             // k extent per warp (multiple of 32)
-  constexpr int KGROUPS = KW / 32;       // 4 k-steps (32 k) per group: two float4 of h per n-tile
-  constexpr int NT = NB / 8;
-  constexpr int S = RC + 4;              // smem row stride of the partial-sum tile [KS][NB][S]
-  constexpr int PAIRS = U * NB;
-  constexpr int PPT = (PAIRS + RNN_THREADS - 1) / RNN_THREADS;
+template <int G, int H>
+struct RnnTiling {
+  static constexpr int U = RNN_U, NB = RNN_NB, KS = RNN_KS;
+  static constexpr int RC = G * U;              // W_hh rows owned by this CTA (128 / 96)
+  static constexpr int RS = RC / 16;            // 16-row MMA strips (8 / 6)
+  static constexpr int WARPS = RS * KS;         // MMA warps (16 / 12)
+  static constexpr int KW = H / KS;             // k extent per warp group (multiple of 32)
+  static constexpr int KB = KW / 32;            // 32-wide k blocks: one LDS.128 of h feeds 2 k-steps per n-tile
+  static constexpr int NT = NB / 8;             // 2 n-tiles
+  static constexpr int S = RC + 4;              // fp32 row stride of the partial-sum tile [KS][NB][S] (S = 4 mod 16)
+  static constexpr int HS = H + 32;             // fp16 row stride of the staged h tile (HS/2 = 16 mod 32 words)
+  static constexpr int XSTR = G * U;            // per-batch stride of an x-projection stage (floats)
+  static constexpr int GS = RS * 32;            // threads of one K group
+  static constexpr int ITEMS = NB * KW / 8;     // 16-byte items (8 halves) of one K-half of h
+  static constexpr int IPT = (ITEMS + GS - 1) / GS;
+  static constexpr int SMEM_BYTES = NB * HS * 2 + (2 * KS * NB * S + RNN_XS * NB * XSTR) * 4;
   static_assert(RC % 16 == 0 && KW % 32 == 0 && WARPS * 32 <= RNN_THREADS, "bad recurrence tiling");
+  static_assert(U * NB == RNN_THREADS && (NB * G * U / 4) <= RNN_THREADS, "one (unit, batch) pair / x chunk per thread");
+};
+
+template <int G, int H>
+__device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* smem) {
+  using T = RnnTiling<G, H>;
+  constexpr int U = T::U, NB = T::NB, KS = T::KS, WARPS = T::WARPS, KW = T::KW, KB = T::KB;
+  constexpr int NT = T::NT, S = T::S, HS = T::HS, XSTR = T::XSTR, GS = T::GS, ITEMS = T::ITEMS, IPT = T::IPT;
+  __half* h_s = reinterpret_cast<__half*>(smem);                       // [NB][HS] fp16
+  float* p_s = reinterpret_cast<float*>(smem + NB * HS * 2);           // [2][KS][NB][S]
+  float* x_s = p_s + 2 * KS * NB * S;                                  // [XS][NB][XSTR]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slice = local_cta % p.slices;
@@ -66,187 +113,239 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned* counter
   const int b0 = p.b_begin + bg * NB;
   const int nbv = min(NB, p.b_end - b0);            // valid batch columns in this CTA
   const int ntv = (nbv + 7) >> 3;                   // n-tiles that hold any valid column
-  unsigned* counter = counters + p.group_base + dir * p.bgroups + bg;
   const int L = p.seq_len;
   const int GH = G * H;
   const float* whh = p.w_hh + static_cast<size_t>(dir) * GH * H;
   const float* bhh = p.b_hh + dir * GH;
-  float* out_dir = p.out + p.out_col0 + dir * H;    // column base of this direction's h
   const float* xp_dir = p.xproj + dir * GH;
+  // exchange tensor hx[dir][t][b][H] (fp16)
+  __half* hx_dir = p.hx + static_cast<size_t>(dir) * L * p.batch * H;
 
-  // ---- W_hh fragments -> registers (once) -------------------------------------------------
+  // ---- W_hh fragments -> registers (once), rounded to fp16 here --------------------------------
+  // k order inside a 32-wide block: lane group q owns k = 8q..8q+7; k-step s uses 8q+4s..8q+4s+3.
   const int rs = warp / KS, kq = warp % KS;
   const int q = lane & 3, fr = lane >> 2;
-  uint32_t wfrag[KGROUPS * 4][4];
+  uint32_t wfrag[KB * 2][4];
   if (warp < WARPS) {
     const int lr_lo = rs * 16 + fr, lr_hi = lr_lo + 8;
     const float* w_lo = whh + static_cast<size_t>((lr_lo / U) * H + u0 + (lr_lo % U)) * H;
     const float* w_hi = whh + static_cast<size_t>((lr_hi / U) * H + u0 + (lr_hi % U)) * H;
 #pragma unroll
-    for (int kg = 0; kg < KGROUPS; ++kg) {
+    for (int kb = 0; kb < KB; ++kb) {
 #pragma unroll
-      for (int s = 0; s < 4; ++s) {
-        const int k = kq * KW + kg * 32 + 8 * q + 2 * s;   // slot q -> k, slot q+4 -> k+1
-        wfrag[kg * 4 + s][0] = __float_as_uint(w_lo[k]);
-        wfrag[kg * 4 + s][1] = __float_as_uint(w_hi[k]);
-        wfrag[kg * 4 + s][2] = __float_as_uint(w_lo[k + 1]);
-        wfrag[kg * 4 + s][3] = __float_as_uint(w_hi[k + 1]);
+      for (int s = 0; s < 2; ++s) {
+        const int k = kq * KW + kb * 32 + 8 * q + 4 * s;
+        wfrag[kb * 2 + s][0] = pack_half2(w_lo[k], w_lo[k + 1]);
+        wfrag[kb * 2 + s][1] = pack_half2(w_hi[k], w_hi[k + 1]);
+        wfrag[kb * 2 + s][2] = pack_half2(w_lo[k + 2], w_lo[k + 3]);
+        wfrag[kb * 2 + s][3] = pack_half2(w_hi[k + 2], w_hi[k + 3]);
       }
     }
   }
 
-  // ---- per-thread (unit, batch) pairs: state + biases ------------------------------------
-  float c_state[PPT], h_state[PPT], bias[PPT][G];
-  int pu[PPT], pb[PPT];
-  bool pv[PPT];
+  // ---- this thread's (unit, batch) pair: state + biases --------------------------------------
+  const int pu = tid % U, pb = tid / U;             // a warp = the 32 units of one batch column
+  const bool pv = pb < nbv;
+  float c_state = 0.0f, h_state = 0.0f, bias[G];
 #pragma unroll
-  for (int j = 0; j < PPT; ++j) {
-    const int pi = tid + j * RNN_THREADS;
-    pu[j] = pi % U;
-    pb[j] = pi / U;
-    pv[j] = (pi < PAIRS) && (pb[j] < nbv);
-    c_state[j] = 0.0f;
-    h_state[j] = 0.0f;
+  for (int g = 0; g < G; ++g) bias[g] = pv ? bhh[g * H + u0 + pu] : 0.0f;
+  float* out_pair = p.out + p.out_col0 + dir * H + static_cast<size_t>(b0 + pb) * p.seq_stride * p.out_ld + u0 + pu;
+  __half* hx_pair = hx_dir + static_cast<size_t>(b0 + pb) * H + u0 + pu;       // + t * batch * H
+
+  // ---- x-projection ring: 16-byte chunk `tid` of a step = (batch xb, gate xg_, 4 units) --------
+  constexpr int XCH = U / 4;                        // chunks per (batch, gate)
+  const int xb = tid / (G * XCH), xg_ = (tid / XCH) % G, xpart = tid % XCH;
+  const bool xv = (tid < NB * G * XCH) && (xb < nbv);
+  const float* x_src = xp_dir + static_cast<size_t>(b0 + xb) * p.seq_stride * (2 * GH) + xg_ * H + u0 + xpart * 4;
+  float* x_dst = x_s + xb * XSTR + xg_ * U + xpart * 4;
+  auto prefetch_x = [&](int step) {
+    if (xv && step < L) {
+      const int t = dir ? (L - 1 - step) : step;
+      cp_async16(x_dst + (step % RNN_XS) * (NB * XSTR), x_src + static_cast<size_t>(t) * (2 * GH));
+    }
+    cp_async_commit();
+  };
 #pragma unroll
-    for (int g = 0; g < G; ++g) bias[j][g] = pv[j] ? bhh[g * H + u0 + pu[j]] : 0.0f;
-  }
+  for (int s = 0; s < RNN_XS - 1; ++s) prefetch_x(s);
+
+#ifdef FTB_RNN_PROFILE
+  // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
+  unsigned long long prof[6] = {0, 0, 0, 0, 0, 0};
+  unsigned polls = 0;
+#define FTB_TICK(i) { const long long now_ = clock64(); prof[i] += now_ - tick_; tick_ = now_; }
+  long long tick_ = clock64();
+#else
+#define FTB_TICK(i)
+#endif
 
   for (int step = 0; step < L; ++step) {
     const int t = dir ? (L - 1 - step) : step;
     const int tprev = dir ? (t + 1) : (t - 1);
+    float* pw = p_s + (step & 1) * (KS * NB * S);
+    FTB_TICK(0)
 
-    // x-projection for this step: independent of h, issued before the barrier wait
-    float xg[PPT][G];
+    if (step > 0 && warp < WARPS) {
+      // ---- stage this K-half of h_{t-1} (fp16): poll the data until no sentinel is left --------
+      {
+        const int gtid = rs * 32 + lane;
+        const __half* hsrc = hx_dir + (static_cast<size_t>(tprev) * p.batch + b0) * H + kq * KW;
+        uint4 v[IPT];
+        unsigned pending = 0;
 #pragma unroll
-    for (int j = 0; j < PPT; ++j) {
-      if (pv[j]) {
-        const float* xr = xp_dir + (static_cast<size_t>(b0 + pb[j]) * p.seq_stride + t) * (2 * GH) + u0 + pu[j];
-#pragma unroll
-        for (int g = 0; g < G; ++g) xg[j][g] = __ldg(xr + g * H);
-      }
-    }
-
-    if (step > 0) {
-      // ---- wait until every slice of this (dir, batch group) has published h_{t-1}
-      if (tid == 0) {
-        const unsigned target = static_cast<unsigned>(step) * p.slices;
+        for (int j = 0; j < IPT; ++j) {
+          const int i = gtid + j * GS;
+          v[j] = make_uint4(0u, 0u, 0u, 0u);
+          if (i < ITEMS && (i / (KW / 8)) < nbv) pending |= 1u << j;
+        }
         unsigned spins = 0;
-        while (ld_acquire(counter) < target) {
-          if (++spins > (1u << 24)) {
-            printf("ftb: recurrence barrier timed out (block %d step %d)\n", blockIdx.x, step);
+        while (pending) {
+#pragma unroll
+          for (int j = 0; j < IPT; ++j) {
+            if (pending & (1u << j)) {
+              const int i = gtid + j * GS;
+              const int b = i / (KW / 8), c8 = i % (KW / 8);
+              v[j] = ld_relaxed_u4(hsrc + static_cast<size_t>(b) * H + c8 * 8);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < IPT; ++j) {
+            if ((pending & (1u << j)) && !has_sentinel(v[j].x) && !has_sentinel(v[j].y) &&
+                !has_sentinel(v[j].z) && !has_sentinel(v[j].w))
+              pending &= ~(1u << j);
+          }
+#ifdef FTB_RNN_PROFILE
+          ++polls;
+#endif
+          if (pending && ++spins > (1u << 22)) {
+            printf("ftb: recurrence wait for h timed out (block %d step %d)\n", blockIdx.x, step);
             __trap();
           }
         }
-      }
-      __syncthreads();
-
-      // ---- P = W_hh[slice rows] * h_{t-1}^T   (tensor cores, K split over KS warps)
-      if (warp < WARPS) {
-        float acc[NT][4];
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
-#pragma unroll
-        for (int kg = 0; kg < KGROUPS; ++kg) {
-          float4 hv[NT][2];
-#pragma unroll
-          for (int nt = 0; nt < NT; ++nt) {
-            const int bl = nt * 8 + fr;
-            if (nt < ntv && bl < nbv) {
-              const float* hp = out_dir + (static_cast<size_t>(b0 + bl) * p.seq_stride + tprev) * p.out_ld +
-                                kq * KW + kg * 32 + 8 * q;
-              hv[nt][0] = ld_cg_f4(hp);
-              hv[nt][1] = ld_cg_f4(hp + 4);
-            } else {
-              hv[nt][0] = hv[nt][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-          }
-#pragma unroll
-          for (int nt = 0; nt < NT; ++nt) {
-            if (nt < ntv) {
-              const float* h8 = reinterpret_cast<const float*>(&hv[nt][0]);
-#pragma unroll
-              for (int s = 0; s < 4; ++s)
-                mma_tf32_16x8x8(acc[nt], wfrag[kg * 4 + s], __float_as_uint(h8[2 * s]), __float_as_uint(h8[2 * s + 1]));
-            }
+        for (int j = 0; j < IPT; ++j) {
+          const int i = gtid + j * GS;
+          if (i < ITEMS) {
+            const int b = i / (KW / 8), c8 = i % (KW / 8);
+            *reinterpret_cast<uint4*>(h_s + b * HS + kq * KW + c8 * 8) = v[j];
           }
         }
-        float* pw = smem_p + static_cast<size_t>(kq) * NB * S;
+      }
+      FTB_TICK(1)
+      named_bar_sync(1 + kq, GS);
+      FTB_TICK(2)
+
+      // ---- P = W_hh[slice rows, K-half] * h_{t-1}^T   (tensor cores, fp16 x fp16 -> fp32)
+      float acc[NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
+#pragma unroll
+      for (int kb = 0; kb < KB; ++kb) {
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
           if (nt < ntv) {
-            const int col = nt * 8 + 2 * q, row = rs * 16 + fr;
-            pw[col * S + row] = acc[nt][0];
-            pw[(col + 1) * S + row] = acc[nt][1];
-            pw[col * S + row + 8] = acc[nt][2];
-            pw[(col + 1) * S + row + 8] = acc[nt][3];
+            const uint4 hv = *reinterpret_cast<const uint4*>(h_s + (nt * 8 + fr) * HS + kq * KW + kb * 32 + 8 * q);
+            mma_f16_16x8x16(acc[nt], wfrag[kb * 2 + 0], hv.x, hv.y);
+            mma_f16_16x8x16(acc[nt], wfrag[kb * 2 + 1], hv.z, hv.w);
           }
         }
       }
-      __syncthreads();
+      float* pk = pw + static_cast<size_t>(kq) * NB * S;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        if (nt < ntv) {
+          const int col = nt * 8 + 2 * q, row = rs * 16 + fr;
+          pk[col * S + row] = acc[nt][0];
+          pk[(col + 1) * S + row] = acc[nt][1];
+          pk[col * S + row + 8] = acc[nt][2];
+          pk[(col + 1) * S + row + 8] = acc[nt][3];
+        }
+      }
     }
+    FTB_TICK(3)
+    cp_async_wait<RNN_XS - 2>();          // this thread's chunk of step `step` has landed
+    __syncthreads();                      // partial sums + everyone's x chunks visible; ring slot (step-1) free
+    FTB_TICK(4)
+    prefetch_x(step + RNN_XS - 1);
 
     // ---- gate math (fp32), state update, publish h_t
+    float hnew = 0.0f;
+    if (pv) {
+      const float* xs = x_s + (step % RNN_XS) * (NB * XSTR) + pb * XSTR + pu;
+      float hh[G];
 #pragma unroll
-    for (int j = 0; j < PPT; ++j) {
-      if (pv[j]) {
-        float hh[G];
+      for (int g = 0; g < G; ++g) {
+        float s = bias[g];
+        if (step > 0) {
 #pragma unroll
-        for (int g = 0; g < G; ++g) {
-          float s = bias[j][g];
-          if (step > 0) {
-#pragma unroll
-            for (int ks = 0; ks < KS; ++ks) s += smem_p[(static_cast<size_t>(ks) * NB + pb[j]) * S + g * U + pu[j]];
-          }
-          hh[g] = s;
+          for (int ks = 0; ks < KS; ++ks) s += pw[(static_cast<size_t>(ks) * NB + pb) * S + g * U + pu];
         }
-        float hnew;
-        if (G == 4) {
-          const float ig = sigm(xg[j][0] + hh[0]);
-          const float fg = sigm(xg[j][1] + hh[1]);
-          const float gg = tanhf(xg[j][2] + hh[2]);
-          const float og = sigm(xg[j][3] + hh[3]);
-          c_state[j] = fg * c_state[j] + ig * gg;
-          hnew = og * tanhf(c_state[j]);
-        } else {
-          const float r = sigm(xg[j][0] + hh[0]);
-          const float z = sigm(xg[j][1] + hh[1]);
-          const float n = tanhf(xg[j][2] + r * hh[2]);
-          hnew = (1.0f - z) * n + z * h_state[j];
-        }
-        h_state[j] = hnew;
-        out_dir[(static_cast<size_t>(b0 + pb[j]) * p.seq_stride + t) * p.out_ld + u0 + pu[j]] = round_tf32(hnew);
+        hh[g] = s;
       }
+      if (G == 4) {
+        const float ig = sigm(xs[0] + hh[0]);
+        const float fg = sigm(xs[U] + hh[1]);
+        const float gg = tanh_fast(xs[2 * U] + hh[2]);
+        const float og = sigm(xs[3 * U] + hh[3]);
+        c_state = fg * c_state + ig * gg;
+        hnew = og * tanh_fast(c_state);
+      } else {
+        const float r = sigm(xs[0] + hh[0]);
+        const float z = sigm(xs[U] + hh[1]);
+        const float n = tanh_fast(xs[2 * U] + r * hh[2]);
+        hnew = (1.0f - z) * n + z * h_state;
+      }
+      h_state = hnew;
     }
-    __syncthreads();                      // all h_t stores issued; smem_p free for the next step
-    if (tid == 0) {
-      __threadfence();
-      atomicAdd(counter, 1u);
+    // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
+    const __half h16 = __float2half_rn(hnew);
+    const unsigned mine = __half_as_ushort(h16);
+    const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
+    if (pv) {
+      if ((lane & 1) == 0)
+        st_relaxed_u32(hx_pair + static_cast<size_t>(t) * p.batch * H, mine | (other << 16));
+      out_pair[static_cast<size_t>(t) * p.out_ld] = __half2float(h16);
     }
+    FTB_TICK(5)
   }
+  cp_async_wait<0>();
+#ifdef FTB_RNN_PROFILE
+  if (tid == 0 && (local_cta % 37) == 0)
+    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu poll %llu bar %llu mma %llu sync %llu gate %llu | polls/step %.2f\n",
+           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L,
+           static_cast<float>(polls) / L);
+#endif
 }
 
 __global__ void __launch_bounds__(RNN_THREADS, 1)
-rnn_persistent_kernel(const RnnProblemDev* __restrict__ probs, int nprob, unsigned* counters) {
-  extern __shared__ float rnn_smem[];
+rnn_persistent_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
+  extern __shared__ __align__(16) unsigned char rnn_smem[];
   int pi = 0;
   while (pi + 1 < nprob && static_cast<int>(blockIdx.x) >= probs[pi + 1].cta_base) ++pi;
   const RnnProblemDev p = probs[pi];
   const int local = blockIdx.x - p.cta_base;
   if (local >= p.ctas) return;
   if (p.cell == FTB_CELL_LSTM) {
-    if (p.hidden == 512) rnn_cta<4, 512, 4>(p, local, counters, rnn_smem);
-    else if (p.hidden == 256) rnn_cta<4, 256, 4>(p, local, counters, rnn_smem);
-    else if (p.hidden == 128) rnn_cta<4, 128, 4>(p, local, counters, rnn_smem);
-    else rnn_cta<4, 64, 2>(p, local, counters, rnn_smem);
+    if (p.hidden == 512) rnn_cta<4, 512>(p, local, rnn_smem);
+    else if (p.hidden == 256) rnn_cta<4, 256>(p, local, rnn_smem);
+    else if (p.hidden == 128) rnn_cta<4, 128>(p, local, rnn_smem);
+    else rnn_cta<4, 64>(p, local, rnn_smem);
   } else {
-    if (p.hidden == 512) rnn_cta<3, 512, 4>(p, local, counters, rnn_smem);
-    else if (p.hidden == 256) rnn_cta<3, 256, 4>(p, local, counters, rnn_smem);
-    else if (p.hidden == 128) rnn_cta<3, 128, 4>(p, local, counters, rnn_smem);
-    else rnn_cta<3, 64, 2>(p, local, counters, rnn_smem);
+    if (p.hidden == 512) rnn_cta<3, 512>(p, local, rnn_smem);
+    else if (p.hidden == 256) rnn_cta<3, 256>(p, local, rnn_smem);
+    else if (p.hidden == 128) rnn_cta<3, 128>(p, local, rnn_smem);
+    else rnn_cta<3, 64>(p, local, rnn_smem);
   }
 }
 
-constexpr int RNN_SMEM_BYTES = 4 * RNN_NB * (4 * RNN_U + 4) * 4;   // KS=4, G=4 worst case
+static int rnn_smem_bytes(int cell, int hidden) {
+  const bool lstm = cell == FTB_CELL_LSTM;
+  switch (hidden) {
+    case 512: return lstm ? RnnTiling<4, 512>::SMEM_BYTES : RnnTiling<3, 512>::SMEM_BYTES;
+    case 256: return lstm ? RnnTiling<4, 256>::SMEM_BYTES : RnnTiling<3, 256>::SMEM_BYTES;
+    case 128: return lstm ? RnnTiling<4, 128>::SMEM_BYTES : RnnTiling<3, 128>::SMEM_BYTES;
+    default: return lstm ? RnnTiling<4, 64>::SMEM_BYTES : RnnTiling<3, 64>::SMEM_BYTES;
+  }
+}
 
 // ------------------------------------------------------------------------------------------
 int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan) {
@@ -265,6 +364,12 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
     const int slices = q.hidden / RNN_U;
     const int per_bgroup = 2 * slices;                 // CTAs per batch group (both directions)
     if (per_bgroup > num_sms) return FTB_E_RESIDENT;
+    const size_t hx_bytes = static_cast<size_t>(2) * q.seq_len * q.batch * q.hidden * sizeof(__half);
+    void* hx = nullptr;
+    cudaError_t he = cudaMalloc(&hx, hx_bytes);
+    if (he != cudaSuccess) return static_cast<int>(he);
+    plan->hx.push_back(hx);
+    plan->hx_bytes.push_back(hx_bytes);
     int b = 0;
     while (b < q.batch) {
       int room = (num_sms - cur.ctas) / per_bgroup;    // batch groups that still fit in this launch
@@ -277,7 +382,7 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       const int want = (q.batch - b + RNN_NB - 1) / RNN_NB;
       const int take = want < room ? want : room;
       RnnProblemDev d{};
-      d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out;
+      d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = static_cast<__half*>(hx);
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
       d.gates = q.cell == FTB_CELL_LSTM ? 4 : 3;
@@ -287,6 +392,8 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       d.b_end = (b + take * RNN_NB < q.batch) ? b + take * RNN_NB : q.batch;
       d.cta_base = cur.ctas;
       d.ctas = 2 * take * slices;
+      const int sm = rnn_smem_bytes(q.cell, q.hidden);
+      if (sm > cur.smem) cur.smem = sm;
       d.group_base = ngroups;
       ngroups += 2 * take;
       cur.ctas += d.ctas;
@@ -299,10 +406,10 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
   cudaError_t ce = cudaMalloc(&plan->dev, sizeof(RnnProblemDev) * parts.size());
   if (ce != cudaSuccess) return static_cast<int>(ce);
   ce = cudaMemcpy(plan->dev, parts.data(), sizeof(RnnProblemDev) * parts.size(), cudaMemcpyHostToDevice);
-  if (ce == cudaSuccess) ce = cudaMalloc(&plan->counters, sizeof(unsigned) * ngroups);
   if (ce != cudaSuccess) return static_cast<int>(ce);
   plan->ngroups = ngroups;
   plan->launches = launches;
+  plan->problems.assign(problems, problems + nproblems);
   return 0;
 }
 
@@ -310,21 +417,24 @@ int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t ce = cudaFuncSetAttribute(rnn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          RNN_SMEM_BYTES);
+                                          rnn_smem_bytes(FTB_CELL_LSTM, 512));
     if (ce != cudaSuccess) return static_cast<int>(ce);
     attr_set = true;
   }
-  cudaError_t ce = cudaMemsetAsync(plan.counters, 0, sizeof(unsigned) * plan.ngroups, stream);
-  if (ce != cudaSuccess) return static_cast<int>(ce);
+  // arm the in-band "not written yet" marker (0xFFFF halves) in every exchange slot the recurrences publish
+  cudaError_t ce = cudaSuccess;
+  for (size_t i = 0; i < plan.hx.size(); ++i) {
+    ce = cudaMemsetAsync(plan.hx[i], 0xFF, plan.hx_bytes[i], stream);
+    if (ce != cudaSuccess) return static_cast<int>(ce);
+  }
   for (const RnnLaunch& l : plan.launches) {
     const RnnProblemDev* base = plan.dev + l.first;
     int count = l.count;
-    unsigned* counters = plan.counters;
-    void* args[] = {&base, &count, &counters};
+    void* args[] = {&base, &count};
     // cooperative launch: the driver guarantees that all CTAs of the grid are co-resident,
-    // which the per-step spin barrier relies on.
+    // which the data-polling hand-off of h between CTAs relies on.
     ce = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(rnn_persistent_kernel), dim3(l.ctas), dim3(RNN_THREADS),
-                                     args, RNN_SMEM_BYTES, stream);
+                                     args, l.smem, stream);
     if (ce != cudaSuccess) return static_cast<int>(ce);
   }
   return 0;

@@ -99,5 +99,7 @@ class PackedRnn:
         w_ih = torch.cat([p['weight_ih_l0'], p['weight_ih_l0_reverse']], dim=0)
         b_ih = torch.cat([p['bias_ih_l0'], p['bias_ih_l0_reverse']], dim=0)
         self.ih = pack_linear(w_ih, b_ih)
-        self.w_hh = round_tf32(torch.stack([p['weight_hh_l0'], p['weight_hh_l0_reverse']]))
+        # fp32 here: the recurrence kernel rounds W_hh ONCE to fp16 (same 11 significant bits as tf32) when it
+        # builds its register-resident MMA fragments
+        self.w_hh = torch.stack([p['weight_hh_l0'], p['weight_hh_l0_reverse']]).detach().float().contiguous()
         self.b_hh = torch.stack([p['bias_hh_l0'], p['bias_hh_l0_reverse']]).detach().float().contiguous()

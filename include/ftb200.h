@@ -112,8 +112,10 @@ int ftb_gemm_plan_destroy(ftb_handle h, int plan);
  * Replaces: the time loop of nn.GRU (common_layers.py:123; forward_tacotron.py:37) and
  * nn.LSTM (forward_tacotron.py:224), batch_first, bidirectional, h0 = c0 = 0, run over the
  * full padded length (no packing in generate()).  xproj holds W_ih x + b_ih for
- * [forward | reverse] (K2 output); W_hh stays resident in registers for all steps; one
- * group barrier per time step; h_t is published through `out`, which is also the layer output.
+ * [forward | reverse] (K2 output); W_hh stays resident in registers (fp16 MMA fragments, fp32
+ * accumulation) for all steps; h_t is handed between CTAs through a plan-owned fp16 exchange tensor
+ * whose sentinel pre-fill doubles as the per-step synchronisation (no counter barrier), and written
+ * as fp32 to `out`, the layer output.
  *   GRU  (r,z,n): r = s(xr + Whr h + bhr); z = s(xz + Whz h + bhz);
  *                 n = tanh(xn + r*(Whn h + bhn)); h' = (1-z)*n + z*h
  *   LSTM (i,f,g,o): c' = s(f)*c + s(i)*tanh(g); h' = s(o)*tanh(c')
@@ -125,9 +127,9 @@ typedef struct {
   int32_t hidden;        /* H: 64, 128, 256 or 512                                           */
   int32_t batch, seq_len, seq_stride;
   const float* xproj;    /* [batch*seq_stride, 2*g*H], g = 3 (GRU) / 4 (LSTM)                */
-  const float* w_hh;     /* [2][g*H][H] fp32, tf32-rounded (weight_hh_l0, weight_hh_l0_reverse) */
+  const float* w_hh;     /* [2][g*H][H] fp32 (weight_hh_l0, weight_hh_l0_reverse); rounded to fp16 in-kernel */
   const float* b_hh;     /* [2][g*H]                                                         */
-  float* out;            /* [batch*seq_stride, out_ld]; fwd h at out_col0, bwd at out_col0+H; tf32-rounded */
+  float* out;            /* [batch*seq_stride, out_ld]; fwd h at out_col0, bwd at out_col0+H; fp16-exact values */
   int32_t out_ld, out_col0;
 } ftb_rnn_problem;
 
