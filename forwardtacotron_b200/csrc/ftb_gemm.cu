@@ -29,7 +29,8 @@ constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int TMEM_COLS = 512;          // 2 accumulators x 256 fp32 columns
 constexpr int NUM_THREADS = 192;
 constexpr int EPI_THREADS = 128;
-constexpr int CHUNK = 16;               // columns per tcgen05.ld
+constexpr int CHUNK = 32;               // accumulator columns per epilogue chunk (one tcgen05.ld .x32)
+constexpr int STG_LD = 36;              // staging row stride (floats): conflict-free 128-bit row writes AND reads
 
 struct SmemTail {
   uint64_t full[STAGES];
@@ -38,7 +39,9 @@ struct SmemTail {
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
   uint32_t pad;
-  float exch[2][4][CHUNK];              // maxpool: last row of each 32-row group, double buffered
+  alignas(16) float exch[2][4][CHUNK];  // maxpool: last row of each 32-row group, double buffered
+  alignas(16) float params[2][3][256];              // per tile (double buffered): bias0 / scale / shift of its bn accumulator columns
+  alignas(16) float stg[4][32][STG_LD];             // per epilogue warp: 32 rows x 32 columns staging tile (row<->lane transpose)
 };
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + sizeof(SmemTail) + 1024;   // +1024: manual alignment
 
@@ -165,12 +168,39 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
     }
   } else {
     // ================================ epilogue ====================================
+    // Phase A (lane = accumulator row): tcgen05.ld 32 columns -> bias/ReLU/affine (+ max-pool) -> staging tile.
+    // Phase B (lane = 4 consecutive columns of a row): staging tile -> (+ residual) -> 128-byte coalesced
+    // row-segment stores of `out` (tf32-rounded) / `out_full` (unrounded).  `out_t` ([B, n, L]) is written
+    // in phase A, where consecutive lanes are consecutive t.
     const int g = warp & 3;                       // TMEM lane quarter this warp may read
+    const int etid = g * 32 + lane;
+    float (*stg)[STG_LD] = tail->stg[g];
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const TileCoord tc = decode_tile(probs, nprob, tile);
       const GemmProblemDev* p = tc.p;
       const int buf = it & 1;
+      const int N = p->n;
+      const bool highway = (p->epilogue == FTB_EPI_HIGHWAY);
+      const bool pool = (p->epilogue == FTB_EPI_MAXPOOL);
+
+      // ---- per-tile column parameters -> smem (overlaps the tail of this tile's MMAs)
+      float (*prm)[256] = tail->params[buf];
+      for (int c = etid; c < p->bn; c += EPI_THREADS) {
+        float b0 = 0.0f, sc = 1.0f, sh = 0.0f;
+        if (highway) {
+          const int U = p->bn >> 1;
+          const int u = (tc.n0 >> 1) + (c < U ? c : c - U);
+          b0 = __ldg(p->bias0 + (c < U ? u : (N >> 1) + u));
+        } else if (tc.n0 + c < N) {
+          if (p->bias0) b0 = __ldg(p->bias0 + tc.n0 + c);
+          if (p->scale) sc = __ldg(p->scale + tc.n0 + c);
+          if (p->shift) sh = __ldg(p->shift + tc.n0 + c);
+        }
+        prm[0][c] = b0; prm[1][c] = sc; prm[2][c] = sh;
+      }
+      named_bar_sync(1, EPI_THREADS);
+
       mbar_wait(&tail->tmem_full[buf], (it >> 1) & 1u);
       tc_fence_after();
 
@@ -183,100 +213,135 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         t = static_cast<int>(r - static_cast<long long>(b) * p->seq_stride);
         valid = t < p->seq_len;
       }
+      const bool store = valid && !(pool && lrow == 0);        // pooled tiles: row 0 is the halo row
+      const unsigned smask = __ballot_sync(0xffffffffu, store);
+      const long long r_warp = static_cast<long long>(tc.m0) + g * 32;     // first row of this warp
       const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(g * 32) << 16);
-      const int N = p->n;
+      const bool relu = (p->flags & FTB_F_RELU) != 0;
+      const bool rnd = (p->flags & FTB_F_ROUND_TF32) != 0;
+      const int sub = lane >> 3, part = lane & 7;               // phase-B coordinates
 
-      if (p->epilogue == FTB_EPI_HIGHWAY) {
+      if (highway) {
         const int U = p->bn >> 1;
-        const int units = N >> 1;
         const int u0 = tc.n0 >> 1;
-        for (int j0 = 0; j0 < U; j0 += CHUNK) {
-          float x1[CHUNK], x2[CHUNK];
+        for (int j0 = 0; j0 < U; j0 += 16) {
+          float x1[16], x2[16];
           tmem_ld_32x16(taddr + j0, x1);
           tmem_ld_32x16(taddr + U + j0, x2);
           tmem_ld_wait();
-          if (valid) {
-            const int u = u0 + j0;
-            const float* res = p->residual + r * p->res_ld + u;
-            float* o = p->out + r * p->out_ld + p->out_col0 + u;
 #pragma unroll
-            for (int j = 0; j < CHUNK; j += 4) {
-              const float4 xr = *reinterpret_cast<const float4*>(res + j);
-              const float xs[4] = {xr.x, xr.y, xr.z, xr.w};
-              float y[4];
+          for (int j = 0; j < 16; j += 4) {
+            const float4 b1 = *reinterpret_cast<const float4*>(&prm[0][j0 + j]);
+            const float4 b2 = *reinterpret_cast<const float4*>(&prm[0][U + j0 + j]);
+            *reinterpret_cast<float4*>(&stg[lane][j]) =
+                make_float4(x1[j] + b1.x, x1[j + 1] + b1.y, x1[j + 2] + b1.z, x1[j + 3] + b1.w);
+            *reinterpret_cast<float4*>(&stg[lane][16 + j]) =
+                make_float4(x2[j] + b2.x, x2[j + 1] + b2.y, x2[j + 2] + b2.z, x2[j + 3] + b2.w);
+          }
+          __syncwarp();
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const float a1 = x1[j + q] + __ldg(p->bias0 + u + j + q);
-                const float a2 = x2[j + q] + __ldg(p->bias0 + units + u + j + q);
-                y[q] = epi_highway(a1, a2, xs[q]);
-              }
-              if (p->out_full)
-                *reinterpret_cast<float4*>(p->out_full + r * p->out_ld + p->out_col0 + u + j) =
-                    make_float4(y[0], y[1], y[2], y[3]);
-              *reinterpret_cast<float4*>(o + j) =
-                  make_float4(epi_finish(p, y[0]), epi_finish(p, y[1]), epi_finish(p, y[2]), epi_finish(p, y[3]));
+          for (int i8 = 0; i8 < 8; ++i8) {
+            const int row = i8 * 4 + sub;
+            const float4 mine = *reinterpret_cast<const float4*>(&stg[row][4 * part]);
+            float4 a2;                                          // lanes part<4 hold x1; their x2 sits 4 lanes up
+            a2.x = __shfl_down_sync(0xffffffffu, mine.x, 4);
+            a2.y = __shfl_down_sync(0xffffffffu, mine.y, 4);
+            a2.z = __shfl_down_sync(0xffffffffu, mine.z, 4);
+            a2.w = __shfl_down_sync(0xffffffffu, mine.w, 4);
+            if (part < 4 && ((smask >> row) & 1u)) {
+              const long long rr = r_warp + row;
+              const int u = u0 + j0 + 4 * part;
+              const float4 xr = *reinterpret_cast<const float4*>(p->residual + rr * p->res_ld + u);
+              float4 y;
+              y.x = epi_highway(mine.x, a2.x, xr.x); y.y = epi_highway(mine.y, a2.y, xr.y);
+              y.z = epi_highway(mine.z, a2.z, xr.z); y.w = epi_highway(mine.w, a2.w, xr.w);
+              const long long o = rr * p->out_ld + p->out_col0 + u;
+              if (p->out_full) *reinterpret_cast<float4*>(p->out_full + o) = y;
+              if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+              *reinterpret_cast<float4*>(p->out + o) = y;
             }
           }
+          __syncwarp();
         }
       } else {
-        const bool pool = (p->epilogue == FTB_EPI_MAXPOOL);
         int chunk_i = 0;
         for (int c0 = 0; c0 < p->bn; c0 += CHUNK, ++chunk_i) {
           float v[CHUNK];
-          tmem_ld_32x16(taddr + c0, v);
+          if (c0 + CHUNK <= p->bn) {
+            tmem_ld_32x32(taddr + c0, v);
+          } else {                                              // bn is a multiple of 16: last half chunk
+            float lo[16];
+            tmem_ld_32x16(taddr + c0, lo);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { v[j] = lo[j]; v[16 + j] = 0.0f; }
+          }
           tmem_ld_wait();
           const int nb = tc.n0 + c0;
 #pragma unroll
-          for (int j = 0; j < CHUNK; ++j) v[j] = (nb + j < N) ? epi_affine(p, v[j], nb + j) : 0.0f;
-          bool store = valid;
+          for (int j = 0; j < CHUNK; j += 4) {
+            const float4 b0 = *reinterpret_cast<const float4*>(&prm[0][(c0 + j) & 255]);
+            const float4 sc = *reinterpret_cast<const float4*>(&prm[1][(c0 + j) & 255]);
+            const float4 sh = *reinterpret_cast<const float4*>(&prm[2][(c0 + j) & 255]);
+            v[j] += b0.x; v[j + 1] += b0.y; v[j + 2] += b0.z; v[j + 3] += b0.w;
+            if (relu) {
+              v[j] = fmaxf(v[j], 0.0f); v[j + 1] = fmaxf(v[j + 1], 0.0f);
+              v[j + 2] = fmaxf(v[j + 2], 0.0f); v[j + 3] = fmaxf(v[j + 3], 0.0f);
+            }
+            v[j] = v[j] * sc.x + sh.x; v[j + 1] = v[j + 1] * sc.y + sh.y;
+            v[j + 2] = v[j + 2] * sc.z + sh.z; v[j + 3] = v[j + 3] * sc.w + sh.w;
+          }
           if (pool) {
             float (*ex)[CHUNK] = tail->exch[chunk_i & 1];
             if (lane == 31) {
 #pragma unroll
               for (int j = 0; j < CHUNK; ++j) ex[g][j] = v[j];
             }
-            named_bar_sync(1, EPI_THREADS);
+            named_bar_sync(2, EPI_THREADS);
 #pragma unroll
             for (int j = 0; j < CHUNK; ++j) {
               float prev = __shfl_up_sync(0xffffffffu, v[j], 1);
               if (lane == 0) prev = (g > 0) ? ex[g - 1][j] : v[j];
               v[j] = (t == 0) ? v[j] : fmaxf(v[j], prev);
             }
-            store = valid && (lrow >= 1);           // tile row 0 is the halo row of this tile
           }
-          if (store) {
-            if (p->residual) {
-              const float* res = p->residual + r * p->res_ld + nb;
+          const bool res_a = (p->out_t != nullptr) && (p->residual != nullptr);   // rare: residual in phase A
+          if (store && res_a) {
+            const float* res = p->residual + r * p->res_ld + nb;
 #pragma unroll
-              for (int j = 0; j < CHUNK; ++j)
-                if (nb + j < N) v[j] += __ldg(res + j);
-            }
-            if (p->out_t) {
-              float* ot = p->out_t + (static_cast<long long>(b) * N + nb) * p->seq_len + t;
+            for (int j = 0; j < CHUNK; ++j)
+              if (nb + j < N) v[j] += __ldg(res + j);
+          }
+          if (store && p->out_t) {
+            float* ot = p->out_t + (static_cast<long long>(b) * N + nb) * p->seq_len + t;
 #pragma unroll
-              for (int j = 0; j < CHUNK; ++j)
-                if (nb + j < N) ot[static_cast<long long>(j) * p->seq_len] = v[j];
-            }
-            if (p->out_full) {
-              float* of = p->out_full + r * p->out_ld + p->out_col0 + nb;
+            for (int j = 0; j < CHUNK; ++j)
+              if (nb + j < N) ot[static_cast<long long>(j) * p->seq_len] = v[j];
+          }
+          if (p->out) {
 #pragma unroll
-              for (int j = 0; j < CHUNK; ++j)
-                if (nb + j < N) of[j] = v[j];
-            }
-            if (p->out) {
-              float* o = p->out + r * p->out_ld + p->out_col0 + nb;
-              if (nb + CHUNK <= N) {
+            for (int j = 0; j < CHUNK; j += 4)
+              *reinterpret_cast<float4*>(&stg[lane][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            __syncwarp();
+            const int col = nb + 4 * part;
+            if (col < N) {                                      // N and nb are multiples of 4
 #pragma unroll
-                for (int j = 0; j < CHUNK; j += 4)
-                  *reinterpret_cast<float4*>(o + j) =
-                      make_float4(epi_finish(p, v[j]), epi_finish(p, v[j + 1]), epi_finish(p, v[j + 2]),
-                                  epi_finish(p, v[j + 3]));
-              } else {
-#pragma unroll
-                for (int j = 0; j < CHUNK; ++j)
-                  if (nb + j < N) o[j] = epi_finish(p, v[j]);
+              for (int i8 = 0; i8 < 8; ++i8) {
+                const int row = i8 * 4 + sub;
+                if ((smask >> row) & 1u) {
+                  float4 y = *reinterpret_cast<const float4*>(&stg[row][4 * part]);
+                  const long long rr = r_warp + row;
+                  if (p->residual && !res_a) {
+                    const float4 xr = *reinterpret_cast<const float4*>(p->residual + rr * p->res_ld + col);
+                    y.x += xr.x; y.y += xr.y; y.z += xr.z; y.w += xr.w;
+                  }
+                  const long long o = rr * p->out_ld + p->out_col0 + col;
+                  if (p->out_full) *reinterpret_cast<float4*>(p->out_full + o) = y;
+                  if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+                  *reinterpret_cast<float4*>(p->out + o) = y;
+                }
               }
             }
+            __syncwarp();
           }
         }
       }
@@ -387,6 +452,8 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     if ((q.lda % 4) != 0 || (q.cin % 4) != 0 || q.cin > q.lda) return FTB_E_ALIGN;
     if (!aligned16(q.a) || !aligned16(q.w)) return FTB_E_ALIGN;
     if (q.out && (!aligned16(q.out) || (q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0)) return FTB_E_ALIGN;
+    if (q.out && (q.n % 4) != 0) return FTB_E_SHAPE;          // row segments are stored as float4
+    if (q.residual && ((q.res_ld % 4) != 0 || !aligned16(q.residual))) return FTB_E_ALIGN;
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
     if (q.rows != static_cast<long long>(q.batch) * q.seq_stride) return FTB_E_ARG;
     if (q.epilogue == FTB_EPI_HIGHWAY) {
