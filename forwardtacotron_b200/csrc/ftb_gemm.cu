@@ -70,7 +70,7 @@ __device__ __forceinline__ float epi_affine(const GemmProblemDev* p, float acc, 
   return v * s + b;     // contracted to one FMA: y = relu(acc)*s + b, s/b precomputed on the host
 }
 __device__ __forceinline__ float epi_highway(float x1, float x2, float x) {
-  const float g = 1.0f / (1.0f + expf(-x2));
+  const float g = __fdividef(1.0f, 1.0f + __expf(-x2));     // ~2 ulp: far below the tf32 operand rounding
   return g * fmaxf(x1, 0.0f) + (1.0f - g) * x;
 }
 __device__ __forceinline__ float epi_finish(const GemmProblemDev* p, float v) {
@@ -224,7 +224,21 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       if (highway) {
         const int U = p->bn >> 1;
         const int u0 = tc.n0 >> 1;
+        // residual rows of this lane's phase-B items, fetched ONE CHUNK AHEAD (the epilogue has one warp per
+        // SMSP: an exposed DRAM/L2 round trip per row group was 90% of this path's time)
+        float4 xr_cur[8], xr_nxt[8];
+        auto load_res = [&](float4 (&dst)[8], int j0) {
+#pragma unroll
+          for (int i8 = 0; i8 < 8; ++i8) {
+            const int row = i8 * 4 + sub;
+            dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (part < 4 && j0 < U && ((smask >> row) & 1u))
+              dst[i8] = *reinterpret_cast<const float4*>(p->residual + (r_warp + row) * p->res_ld + u0 + j0 + 4 * part);
+          }
+        };
+        load_res(xr_cur, 0);
         for (int j0 = 0; j0 < U; j0 += 16) {
+          load_res(xr_nxt, j0 + 16);
           float x1[16], x2[16];
           tmem_ld_32x16(taddr + j0, x1);
           tmem_ld_32x16(taddr + U + j0, x2);
@@ -251,7 +265,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             if (part < 4 && ((smask >> row) & 1u)) {
               const long long rr = r_warp + row;
               const int u = u0 + j0 + 4 * part;
-              const float4 xr = *reinterpret_cast<const float4*>(p->residual + rr * p->res_ld + u);
+              const float4 xr = xr_cur[i8];
               float4 y;
               y.x = epi_highway(mine.x, a2.x, xr.x); y.y = epi_highway(mine.y, a2.y, xr.y);
               y.z = epi_highway(mine.z, a2.z, xr.z); y.w = epi_highway(mine.w, a2.w, xr.w);
@@ -262,10 +276,26 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             }
           }
           __syncwarp();
+#pragma unroll
+          for (int i8 = 0; i8 < 8; ++i8) xr_cur[i8] = xr_nxt[i8];
         }
       } else {
         int chunk_i = 0;
+        const bool res_b = (p->residual != nullptr) && (p->out_t == nullptr);      // residual added in phase B
+        float4 xr_cur[8], xr_nxt[8];
+        auto load_res = [&](float4 (&dst)[8], int c0) {
+#pragma unroll
+          for (int i8 = 0; i8 < 8; ++i8) {
+            const int row = i8 * 4 + sub;
+            const int col = tc.n0 + c0 + 4 * part;
+            dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (res_b && c0 < p->bn && col < N && ((smask >> row) & 1u))
+              dst[i8] = *reinterpret_cast<const float4*>(p->residual + (r_warp + row) * p->res_ld + col);
+          }
+        };
+        if (res_b) load_res(xr_cur, 0);
         for (int c0 = 0; c0 < p->bn; c0 += CHUNK, ++chunk_i) {
+          if (res_b) load_res(xr_nxt, c0 + CHUNK);
           float v[CHUNK];
           if (c0 + CHUNK <= p->bn) {
             tmem_ld_32x32(taddr + c0, v);
@@ -330,8 +360,8 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
                 if ((smask >> row) & 1u) {
                   float4 y = *reinterpret_cast<const float4*>(&stg[row][4 * part]);
                   const long long rr = r_warp + row;
-                  if (p->residual && !res_a) {
-                    const float4 xr = *reinterpret_cast<const float4*>(p->residual + rr * p->res_ld + col);
+                  if (res_b) {
+                    const float4 xr = xr_cur[i8];
                     y.x += xr.x; y.y += xr.y; y.z += xr.z; y.w += xr.w;
                   }
                   const long long o = rr * p->out_ld + p->out_col0 + col;
@@ -342,6 +372,10 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
               }
             }
             __syncwarp();
+          }
+          if (res_b) {
+#pragma unroll
+            for (int i8 = 0; i8 < 8; ++i8) xr_cur[i8] = xr_nxt[i8];
           }
         }
       }
