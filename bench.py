@@ -141,6 +141,7 @@ def run_reference(args, rank, world):
 
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
+    from forwardtacotron_b200 import parallel as par
     from forwardtacotron_b200 import runtime as rt
     dev = torch.device('cuda', local_rank)
     torch.cuda.set_device(dev)
@@ -188,6 +189,8 @@ def run_ours(args, rank, world, local_rank):
     def step_e2e():
         xd = x_pin.to(dev, non_blocking=True)
         o = model.generate(xd)
+        if world > 1:            # the path's only collective: gather of the variable-length mels over NVLink
+            par.gather_variable_mels(o['mel_post'], par.mel_lengths(o['dur']))
         host_out.copy_(o['mel_post'], non_blocking=True)
 
     with ClockSampler(local_rank) as clocks:
