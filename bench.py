@@ -265,7 +265,8 @@ def run_ours(args, rank, world, local_rank):
             'e2e': {'value': total_frames * args.steps / (ms_e2e / 1e3), 'unit': UNIT,
                     'h2d_bytes_per_step': x_pin.numel() * 8, 'd2h_bytes_per_step': host_out.numel() * 4},
             'gpu_launches': int(launches), 'clocks': clk, 'roofline': roof,
-            'kernels': [k for k, _ in kernels[:12]]}
+            'kernel_ms_sum': round(sum(k['ms'] for k, _ in kernels), 4),
+            'kernels': [k for k, _ in kernels[:14]]}
     if cpu is not None:
         line['cpu_baseline'] = cpu
     print(json.dumps(line), flush=True)

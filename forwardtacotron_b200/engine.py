@@ -6,6 +6,7 @@ kernels) over a fixed set of device buffers in the padded-flat channel-last layo
 ONE persistent GEMM launch (e.g. the three predictors' first convolutions and the 16 bank
 convolutions), so the SMs see a few hundred tiles per launch instead of ~100.
 """
+import os
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -35,6 +36,12 @@ class Program:
         self._keep: list = []                         # tensors the plans point into
         self.info: List[dict] = []                    # per step: kind, label, algorithmic flops / bytes
         self._label = ''
+        # CUDA graph of the launch list: captured on the second run() (the first one runs eagerly so one-time
+        # cudaFuncSetAttribute calls happen outside capture), re-captured when a launch-time scalar changes
+        self.use_graph = os.environ.get('FTB_CUDA_GRAPHS', '1') != '0'
+        self._graph = None
+        self._graph_key = None
+        self._eager_runs = 0
 
     # ---- buffers ---------------------------------------------------------------------------
     def buf(self, name: str, cols: int) -> torch.Tensor:
@@ -136,9 +143,39 @@ class Program:
     def label(self, text: str):
         self._label = text
 
-    def run(self):
+    def run_eager(self):
         for s in self.steps:
             s()
+
+    def run(self):
+        """Launch every step on the current stream: eagerly the first time, afterwards as ONE CUDA-graph
+        replay (a 20-launch program otherwise leaves the SMs idle between its short kernels)."""
+        key = getattr(self, 'alpha', None)                    # scalars baked into kernel arguments
+        if not self.use_graph:
+            return self.run_eager()
+        if self._graph is not None and self._graph_key == key:
+            self.h.replayed_launches += self._launches_per_run     # kernels inside the replayed graph
+            return self._graph.replay()
+        if self._eager_runs < 1:
+            self._eager_runs += 1
+            n0 = self.h.launch_count()
+            self.run_eager()
+            self._launches_per_run = self.h.launch_count() - n0
+            return
+        try:
+            graph = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.graph(graph, stream=side):
+                self.run_eager()
+            torch.cuda.current_stream(self.device).wait_stream(side)
+        except Exception as exc:                              # capture unsupported: stay on eager launches
+            import warnings
+            warnings.warn(f'forwardtacotron_b200: CUDA-graph capture failed ({exc}); using eager launches')
+            self.use_graph = False
+            return self.run_eager()
+        self._graph, self._graph_key = graph, key
+        return graph.replay()          # (the capture pass already counted these launches once in the C counter)
 
     def run_timed(self):
         """Like run(), with a CUDA-event pair around every launch on the current stream.
@@ -158,6 +195,7 @@ class Program:
             self.h.gemm_destroy(p)
         for p in self._rnn_plans:
             self.h.rnn_destroy(p)
+        self._graph = None
         self._gemm_plans, self._rnn_plans, self.steps = [], [], []
 
     def __del__(self):

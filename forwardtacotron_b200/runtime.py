@@ -118,6 +118,7 @@ class Handle:
         h = _fp()
         self.check(self.lib.ftb_create(self.index, C.byref(h)))
         self.h = h
+        self.replayed_launches = 0      # kernels launched through CUDA-graph replays (engine.Program)
         self.impl = int(os.environ.get('FTB_GEMM_IMPL', '0'))    # 1 = SIMT cross-check kernel (tests only)
 
     @classmethod
@@ -136,7 +137,7 @@ class Handle:
         return torch.cuda.current_stream(self.device).cuda_stream
 
     def launch_count(self) -> int:
-        return int(self.lib.ftb_launch_count(self.h))
+        return int(self.lib.ftb_launch_count(self.h)) + self.replayed_launches
 
     # ---- plans -----------------------------------------------------------------------------
     def gemm_plan(self, problems: List[GemmProblem]) -> int:
