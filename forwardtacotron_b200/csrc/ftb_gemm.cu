@@ -85,6 +85,15 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
   SmemTail* tail = reinterpret_cast<SmemTail*>(smem + STAGES * STAGE_BYTES);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+#ifdef FTB_GEMM_PROFILE
+  long long gp[5] = {0, 0, 0, 0, 0}, gp_t0 = 0;
+  const long long gp_start = clock64();
+#define GP_T0 gp_t0 = clock64();
+#define GP_ACC(i) gp[i] += clock64() - gp_t0;
+#else
+#define GP_T0
+#define GP_ACC(i)
+#endif
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -121,14 +130,19 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
           tma_desc_fence_acquire(&p->tm_w);
           last_p = p;
         }
-        for (int tap = 0; tap < p->taps; ++tap) {
-          for (int kb = 0; kb < p->kblocks; ++kb) {
-            mbar_wait(&tail->empty[stage], phase ^ 1u);
+        // problem fields -> registers: the "memory" clobbers of the barrier/TMA asm would otherwise force a
+        // re-load of every p->field from global memory inside the loops
+        const int taps = p->taps, kblocks = p->kblocks, tap0 = p->tap0, w_tap_rows = p->w_tap_rows;
+        const CUtensorMap* tm_a = &p->tm_a;
+        const CUtensorMap* tm_w = &p->tm_w;
+        for (int tap = 0; tap < taps; ++tap) {
+          for (int kb = 0; kb < kblocks; ++kb) {
+            GP_T0 mbar_wait(&tail->empty[stage], phase ^ 1u); GP_ACC(0)
             uint8_t* sa = smem + stage * STAGE_BYTES;
             uint8_t* sb = sa + A_STAGE_BYTES;
             mbar_expect_tx(&tail->full[stage], tx);
-            tma_load_2d(sa, &p->tm_a, &tail->full[stage], kb * BK, tc.m0 + p->tap0 + tap);
-            tma_load_2d(sb, &p->tm_w, &tail->full[stage], kb * BK, tap * p->w_tap_rows + tc.n0);
+            tma_load_2d(sa, tm_a, &tail->full[stage], kb * BK, tc.m0 + tap0 + tap);
+            tma_load_2d(sb, tm_w, &tail->full[stage], kb * BK, tap * w_tap_rows + tc.n0);
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
         }
@@ -144,13 +158,13 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         const TileCoord tc = decode_tile(probs, nprob, tile);
         const GemmProblemDev* p = tc.p;
         const int buf = it & 1;
-        mbar_wait(&tail->tmem_empty[buf], ((it >> 1) & 1u) ^ 1u);
+        GP_T0 mbar_wait(&tail->tmem_empty[buf], ((it >> 1) & 1u) ^ 1u); GP_ACC(1)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         const uint32_t idesc = umma_idesc_tf32(BM, p->bn);
         const int kiters = p->taps * p->kblocks;
         for (int ki = 0; ki < kiters; ++ki) {
-          mbar_wait(&tail->full[stage], phase);
+          GP_T0 mbar_wait(&tail->full[stage], phase); GP_ACC(2)
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa);
@@ -180,49 +194,62 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       const TileCoord tc = decode_tile(probs, nprob, tile);
       const GemmProblemDev* p = tc.p;
       const int buf = it & 1;
-      const int N = p->n;
-      const bool highway = (p->epilogue == FTB_EPI_HIGHWAY);
-      const bool pool = (p->epilogue == FTB_EPI_MAXPOOL);
+      // problem fields -> registers ONCE per tile: this warp stores to global memory, so without the copies the
+      // compiler re-loads p->out / p->residual / ... from global memory (a long-scoreboard stall) in every
+      // iteration of the store loops -- measured as the dominant epilogue stall (profiles/r1e_gemm_roles.txt)
+      const int N = p->n, P_bn = p->bn, P_res_ld = p->res_ld, P_out_ld = p->out_ld, P_out_col0 = p->out_col0;
+      const int P_seq_len = p->seq_len, P_seq_stride = p->seq_stride, P_flags = p->flags, P_epi = p->epilogue;
+      const long long P_rows = p->rows;
+      const float* const P_bias0 = p->bias0;
+      const float* const P_scale = p->scale;
+      const float* const P_shift = p->shift;
+      const float* const P_residual = p->residual;
+      float* const P_out = p->out;
+      float* const P_out_full = p->out_full;
+      float* const P_out_t = p->out_t;
+      const bool highway = (P_epi == FTB_EPI_HIGHWAY);
+      const bool pool = (P_epi == FTB_EPI_MAXPOOL);
 
       // ---- per-tile column parameters -> smem (overlaps the tail of this tile's MMAs)
       float (*prm)[256] = tail->params[buf];
-      for (int c = etid; c < p->bn; c += EPI_THREADS) {
+      for (int c = etid; c < P_bn; c += EPI_THREADS) {
         float b0 = 0.0f, sc = 1.0f, sh = 0.0f;
         if (highway) {
-          const int U = p->bn >> 1;
+          const int U = P_bn >> 1;
           const int u = (tc.n0 >> 1) + (c < U ? c : c - U);
-          b0 = __ldg(p->bias0 + (c < U ? u : (N >> 1) + u));
+          b0 = __ldg(P_bias0 + (c < U ? u : (N >> 1) + u));
         } else if (tc.n0 + c < N) {
-          if (p->bias0) b0 = __ldg(p->bias0 + tc.n0 + c);
-          if (p->scale) sc = __ldg(p->scale + tc.n0 + c);
-          if (p->shift) sh = __ldg(p->shift + tc.n0 + c);
+          if (P_bias0) b0 = __ldg(P_bias0 + tc.n0 + c);
+          if (P_scale) sc = __ldg(P_scale + tc.n0 + c);
+          if (P_shift) sh = __ldg(P_shift + tc.n0 + c);
         }
         prm[0][c] = b0; prm[1][c] = sc; prm[2][c] = sh;
       }
       named_bar_sync(1, EPI_THREADS);
 
-      mbar_wait(&tail->tmem_full[buf], (it >> 1) & 1u);
+      GP_T0 mbar_wait(&tail->tmem_full[buf], (it >> 1) & 1u); GP_ACC(3)
       tc_fence_after();
+      GP_T0
 
       const int lrow = g * 32 + lane;
       const long long r = static_cast<long long>(tc.m0) + lrow;
       int t = 0, b = 0;
-      bool valid = (r >= 0) && (r < p->rows);
+      bool valid = (r >= 0) && (r < P_rows);
       if (valid) {
-        b = static_cast<int>(r / p->seq_stride);
-        t = static_cast<int>(r - static_cast<long long>(b) * p->seq_stride);
-        valid = t < p->seq_len;
+        b = static_cast<int>(r / P_seq_stride);
+        t = static_cast<int>(r - static_cast<long long>(b) * P_seq_stride);
+        valid = t < P_seq_len;
       }
       const bool store = valid && !(pool && lrow == 0);        // pooled tiles: row 0 is the halo row
       const unsigned smask = __ballot_sync(0xffffffffu, store);
       const long long r_warp = static_cast<long long>(tc.m0) + g * 32;     // first row of this warp
       const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(g * 32) << 16);
-      const bool relu = (p->flags & FTB_F_RELU) != 0;
-      const bool rnd = (p->flags & FTB_F_ROUND_TF32) != 0;
+      const bool relu = (P_flags & FTB_F_RELU) != 0;
+      const bool rnd = (P_flags & FTB_F_ROUND_TF32) != 0;
       const int sub = lane >> 3, part = lane & 7;               // phase-B coordinates
 
       if (highway) {
-        const int U = p->bn >> 1;
+        const int U = P_bn >> 1;
         const int u0 = tc.n0 >> 1;
         // residual rows of this lane's phase-B items, fetched ONE CHUNK AHEAD (the epilogue has one warp per
         // SMSP: an exposed DRAM/L2 round trip per row group was 90% of this path's time)
@@ -233,7 +260,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             const int row = i8 * 4 + sub;
             dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (part < 4 && j0 < U && ((smask >> row) & 1u))
-              dst[i8] = *reinterpret_cast<const float4*>(p->residual + (r_warp + row) * p->res_ld + u0 + j0 + 4 * part);
+              dst[i8] = *reinterpret_cast<const float4*>(P_residual + (r_warp + row) * P_res_ld + u0 + j0 + 4 * part);
           }
         };
         load_res(xr_cur, 0);
@@ -269,10 +296,10 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
               float4 y;
               y.x = epi_highway(mine.x, a2.x, xr.x); y.y = epi_highway(mine.y, a2.y, xr.y);
               y.z = epi_highway(mine.z, a2.z, xr.z); y.w = epi_highway(mine.w, a2.w, xr.w);
-              const long long o = rr * p->out_ld + p->out_col0 + u;
-              if (p->out_full) *reinterpret_cast<float4*>(p->out_full + o) = y;
+              const long long o = rr * P_out_ld + P_out_col0 + u;
+              if (P_out_full) *reinterpret_cast<float4*>(P_out_full + o) = y;
               if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-              *reinterpret_cast<float4*>(p->out + o) = y;
+              *reinterpret_cast<float4*>(P_out + o) = y;
             }
           }
           __syncwarp();
@@ -281,7 +308,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         }
       } else {
         int chunk_i = 0;
-        const bool res_b = (p->residual != nullptr) && (p->out_t == nullptr);      // residual added in phase B
+        const bool res_b = (P_residual != nullptr) && (P_out_t == nullptr);      // residual added in phase B
         float4 xr_cur[8], xr_nxt[8];
         auto load_res = [&](float4 (&dst)[8], int c0) {
 #pragma unroll
@@ -289,15 +316,15 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             const int row = i8 * 4 + sub;
             const int col = tc.n0 + c0 + 4 * part;
             dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (res_b && c0 < p->bn && col < N && ((smask >> row) & 1u))
-              dst[i8] = *reinterpret_cast<const float4*>(p->residual + (r_warp + row) * p->res_ld + col);
+            if (res_b && c0 < P_bn && col < N && ((smask >> row) & 1u))
+              dst[i8] = *reinterpret_cast<const float4*>(P_residual + (r_warp + row) * P_res_ld + col);
           }
         };
         if (res_b) load_res(xr_cur, 0);
-        for (int c0 = 0; c0 < p->bn; c0 += CHUNK, ++chunk_i) {
+        for (int c0 = 0; c0 < P_bn; c0 += CHUNK, ++chunk_i) {
           if (res_b) load_res(xr_nxt, c0 + CHUNK);
           float v[CHUNK];
-          if (c0 + CHUNK <= p->bn) {
+          if (c0 + CHUNK <= P_bn) {
             tmem_ld_32x32(taddr + c0, v);
           } else {                                              // bn is a multiple of 16: last half chunk
             float lo[16];
@@ -334,20 +361,20 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
               v[j] = (t == 0) ? v[j] : fmaxf(v[j], prev);
             }
           }
-          const bool res_a = (p->out_t != nullptr) && (p->residual != nullptr);   // rare: residual in phase A
+          const bool res_a = (P_out_t != nullptr) && (P_residual != nullptr);   // rare: residual in phase A
           if (store && res_a) {
-            const float* res = p->residual + r * p->res_ld + nb;
+            const float* res = P_residual + r * P_res_ld + nb;
 #pragma unroll
             for (int j = 0; j < CHUNK; ++j)
               if (nb + j < N) v[j] += __ldg(res + j);
           }
-          if (store && p->out_t) {
-            float* ot = p->out_t + (static_cast<long long>(b) * N + nb) * p->seq_len + t;
+          if (store && P_out_t) {
+            float* ot = P_out_t + (static_cast<long long>(b) * N + nb) * P_seq_len + t;
 #pragma unroll
             for (int j = 0; j < CHUNK; ++j)
-              if (nb + j < N) ot[static_cast<long long>(j) * p->seq_len] = v[j];
+              if (nb + j < N) ot[static_cast<long long>(j) * P_seq_len] = v[j];
           }
-          if (p->out) {
+          if (P_out) {
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 4)
               *reinterpret_cast<float4*>(&stg[lane][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -364,10 +391,10 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
                     const float4 xr = xr_cur[i8];
                     y.x += xr.x; y.y += xr.y; y.z += xr.z; y.w += xr.w;
                   }
-                  const long long o = rr * p->out_ld + p->out_col0 + col;
-                  if (p->out_full) *reinterpret_cast<float4*>(p->out_full + o) = y;
+                  const long long o = rr * P_out_ld + P_out_col0 + col;
+                  if (P_out_full) *reinterpret_cast<float4*>(P_out_full + o) = y;
                   if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-                  *reinterpret_cast<float4*>(p->out + o) = y;
+                  *reinterpret_cast<float4*>(P_out + o) = y;
                 }
               }
             }
@@ -381,9 +408,17 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       }
       tc_fence_before();
       __syncwarp();
+      GP_ACC(4)
       if (lane == 0) mbar_arrive(&tail->tmem_empty[buf]);
     }
   }
+#ifdef FTB_GEMM_PROFILE
+  if (blockIdx.x == 0 && lane == 0 && (warp <= 2)) {
+    const long long tot = clock64() - gp_start;
+    printf("gemm prof warp %d tiles %d total %lld | wait_empty %lld wait_tmem_empty %lld wait_full %lld wait_tmem_full %lld epi_work %lld\n",
+           warp, (total_tiles + gridDim.x - 1) / gridDim.x, tot, gp[0], gp[1], gp[2], gp[3], gp[4]);
+  }
+#endif
 
   tc_fence_before();
   __syncthreads();
