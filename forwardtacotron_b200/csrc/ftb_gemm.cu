@@ -78,6 +78,149 @@ __device__ __forceinline__ float epi_finish(const GemmProblemDev* p, float v) {
 }
 
 // ------------------------------------------------------------------------------------------
+// Affine / max-pool epilogue of one 128 x bn accumulator tile, as seen by ONE epilogue warp (32 rows).
+// Everything that varies per problem is a template flag, so each instantiation carries only the
+// instructions its layer needs: the epilogue runs with one warp per SMSP and is issue-bound (the
+// all-runtime-branches version executed ~1400 SASS instructions per 32-column chunk, see
+// profiles/r1e_gemm_roles.txt).
+struct EpiCtx {
+  const float (*prm)[256];       // [3][256] bias0 / scale / shift of this tile's columns
+  float (*stg)[STG_LD];          // this warp's 32 x 32 staging tile
+  float (*exch)[4][CHUNK];       // [2][4][CHUNK] max-pool row hand-over between the four warps
+  uint32_t taddr;                // TMEM address of this warp's lanes, column 0 of the tile
+  int bn, n0, N, g, lane, t, b, seq_len, res_ld, out_ld;
+  unsigned smask;                // rows of this warp that are stored
+  bool store;                    // this lane's row is stored
+  long long r, r_warp;           // this lane's row / the warp's first row
+  float relu_lo;                 // 0 (ReLU) or -inf
+  const float* residual;
+  float* out; float* out_full; float* out_t;    // out / out_full already offset by out_col0
+};
+
+template <bool POOL, bool RES, bool FULL, bool OUTT, bool RND>
+__device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
+  const int lane = c.lane, sub = lane >> 3, part = lane & 7;
+  // phase-B base pointers: row (r_warp + sub), column n0 + 4*part; +32 columns per chunk, +4 rows per i8
+  const long long orow = (c.r_warp + sub) * c.out_ld + c.n0 + 4 * part;
+  float* optr = c.out ? c.out + orow : nullptr;
+  float* fptr = FULL ? c.out_full + orow : nullptr;
+  const float* rptr = RES ? c.residual + (c.r_warp + sub) * c.res_ld + c.n0 + 4 * part : nullptr;
+  const long long ostep = 4ll * c.out_ld, rstep = 4ll * c.res_ld;
+  float4 xr_cur[RES ? 8 : 1], xr_nxt[RES ? 8 : 1];
+  auto load_res = [&](float4 (&dst)[RES ? 8 : 1], int c0) {
+    if (RES) {
+#pragma unroll
+      for (int i8 = 0; i8 < 8; ++i8) {
+        dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c0 < c.bn && c.n0 + c0 + 4 * part < c.N && ((c.smask >> (i8 * 4 + sub)) & 1u))
+          dst[i8] = *reinterpret_cast<const float4*>(rptr + i8 * rstep + c0);
+      }
+    }
+  };
+  load_res(xr_cur, 0);
+  int chunk_i = 0;
+  for (int c0 = 0; c0 < c.bn; c0 += CHUNK, ++chunk_i) {
+    load_res(xr_nxt, c0 + CHUNK);
+    float v[CHUNK];
+    if (c0 + CHUNK <= c.bn) {
+      tmem_ld_32x32(c.taddr + c0, v);
+    } else {                                              // bn is a multiple of 16: last half chunk
+      float lo[16];
+      tmem_ld_32x16(c.taddr + c0, lo);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) { v[j] = lo[j]; v[16 + j] = 0.0f; }
+    }
+    tmem_ld_wait();
+    const int nb = c.n0 + c0;
+#pragma unroll
+    for (int j = 0; j < CHUNK; j += 4) {
+      const float4 b0 = *reinterpret_cast<const float4*>(&c.prm[0][(c0 + j) & 255]);
+      const float4 sc = *reinterpret_cast<const float4*>(&c.prm[1][(c0 + j) & 255]);
+      const float4 sh = *reinterpret_cast<const float4*>(&c.prm[2][(c0 + j) & 255]);
+      v[j] = fmaxf(v[j] + b0.x, c.relu_lo) * sc.x + sh.x;
+      v[j + 1] = fmaxf(v[j + 1] + b0.y, c.relu_lo) * sc.y + sh.y;
+      v[j + 2] = fmaxf(v[j + 2] + b0.z, c.relu_lo) * sc.z + sh.z;
+      v[j + 3] = fmaxf(v[j + 3] + b0.w, c.relu_lo) * sc.w + sh.w;
+    }
+    if (POOL) {
+      float (*ex)[CHUNK] = c.exch[chunk_i & 1];
+      if (lane == 31) {
+#pragma unroll
+        for (int j = 0; j < CHUNK; j += 4)
+          *reinterpret_cast<float4*>(&ex[c.g][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+      named_bar_sync(2, EPI_THREADS);
+      const bool first_t = (c.t == 0);
+#pragma unroll
+      for (int j = 0; j < CHUNK; ++j) {
+        float prev = __shfl_up_sync(0xffffffffu, v[j], 1);
+        if (lane == 0) prev = (c.g > 0) ? ex[c.g - 1][j] : v[j];
+        v[j] = first_t ? v[j] : fmaxf(v[j], prev);
+      }
+    }
+    if (OUTT) {
+      if (c.store) {
+        if (c.residual) {                                 // rare: residual together with a transposed output
+          const float* res = c.residual + c.r * c.res_ld + nb;
+#pragma unroll
+          for (int j = 0; j < CHUNK; ++j)
+            if (nb + j < c.N) v[j] += __ldg(res + j);
+        }
+        float* ot = c.out_t + (static_cast<long long>(c.b) * c.N + nb) * c.seq_len + c.t;
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j)
+          if (nb + j < c.N) ot[static_cast<long long>(j) * c.seq_len] = v[j];
+      }
+    }
+    if (optr) {
+#pragma unroll
+      for (int j = 0; j < CHUNK; j += 4)
+        *reinterpret_cast<float4*>(&c.stg[lane][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      __syncwarp();
+      if (nb + 4 * part < c.N) {                          // N and nb are multiples of 4
+#pragma unroll
+        for (int i8 = 0; i8 < 8; ++i8) {
+          const int row = i8 * 4 + sub;
+          if ((c.smask >> row) & 1u) {
+            float4 y = *reinterpret_cast<const float4*>(&c.stg[row][4 * part]);
+            if (RES) { y.x += xr_cur[i8].x; y.y += xr_cur[i8].y; y.z += xr_cur[i8].z; y.w += xr_cur[i8].w; }
+            if (FULL) *reinterpret_cast<float4*>(fptr + i8 * ostep + c0) = y;
+            if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+            *reinterpret_cast<float4*>(optr + i8 * ostep + c0) = y;
+          }
+        }
+      }
+      __syncwarp();
+    }
+    if (RES) {
+#pragma unroll
+      for (int i8 = 0; i8 < 8; ++i8) xr_cur[i8] = xr_nxt[i8];
+    }
+  }
+}
+
+template <bool POOL, bool RES, bool FULL, bool OUTT>
+__device__ __forceinline__ void epi_disp_rnd(const EpiCtx& c, bool rnd) {
+  if (rnd) epi_affine_tile<POOL, RES, FULL, OUTT, true>(c);
+  else epi_affine_tile<POOL, RES, FULL, OUTT, false>(c);
+}
+template <bool POOL, bool RES, bool FULL>
+__device__ __forceinline__ void epi_disp_outt(const EpiCtx& c, bool outt, bool rnd) {
+  if (outt) epi_disp_rnd<POOL, false, FULL, true>(c, rnd);      // with out_t the residual (if any) is added in phase A
+  else epi_disp_rnd<POOL, RES, FULL, false>(c, rnd);
+}
+template <bool POOL, bool RES>
+__device__ __forceinline__ void epi_disp_full(const EpiCtx& c, bool full, bool outt, bool rnd) {
+  if (full) epi_disp_outt<POOL, RES, true>(c, outt, rnd);
+  else epi_disp_outt<POOL, RES, false>(c, outt, rnd);
+}
+__device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool res, bool full, bool outt, bool rnd) {
+  if (pool) epi_disp_full<true, false>(c, full, outt, rnd);     // pooled layers (CBHG bank) never carry a residual
+  else if (res) epi_disp_full<false, true>(c, full, outt, rnd);
+  else epi_disp_full<false, false>(c, full, outt, rnd);
+}
+
+// ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
   extern __shared__ uint8_t smem_raw[];
@@ -307,104 +450,16 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
           for (int i8 = 0; i8 < 8; ++i8) xr_cur[i8] = xr_nxt[i8];
         }
       } else {
-        int chunk_i = 0;
-        const bool res_b = (P_residual != nullptr) && (P_out_t == nullptr);      // residual added in phase B
-        float4 xr_cur[8], xr_nxt[8];
-        auto load_res = [&](float4 (&dst)[8], int c0) {
-#pragma unroll
-          for (int i8 = 0; i8 < 8; ++i8) {
-            const int row = i8 * 4 + sub;
-            const int col = tc.n0 + c0 + 4 * part;
-            dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (res_b && c0 < P_bn && col < N && ((smask >> row) & 1u))
-              dst[i8] = *reinterpret_cast<const float4*>(P_residual + (r_warp + row) * P_res_ld + col);
-          }
-        };
-        if (res_b) load_res(xr_cur, 0);
-        for (int c0 = 0; c0 < P_bn; c0 += CHUNK, ++chunk_i) {
-          if (res_b) load_res(xr_nxt, c0 + CHUNK);
-          float v[CHUNK];
-          if (c0 + CHUNK <= P_bn) {
-            tmem_ld_32x32(taddr + c0, v);
-          } else {                                              // bn is a multiple of 16: last half chunk
-            float lo[16];
-            tmem_ld_32x16(taddr + c0, lo);
-#pragma unroll
-            for (int j = 0; j < 16; ++j) { v[j] = lo[j]; v[16 + j] = 0.0f; }
-          }
-          tmem_ld_wait();
-          const int nb = tc.n0 + c0;
-#pragma unroll
-          for (int j = 0; j < CHUNK; j += 4) {
-            const float4 b0 = *reinterpret_cast<const float4*>(&prm[0][(c0 + j) & 255]);
-            const float4 sc = *reinterpret_cast<const float4*>(&prm[1][(c0 + j) & 255]);
-            const float4 sh = *reinterpret_cast<const float4*>(&prm[2][(c0 + j) & 255]);
-            v[j] += b0.x; v[j + 1] += b0.y; v[j + 2] += b0.z; v[j + 3] += b0.w;
-            if (relu) {
-              v[j] = fmaxf(v[j], 0.0f); v[j + 1] = fmaxf(v[j + 1], 0.0f);
-              v[j + 2] = fmaxf(v[j + 2], 0.0f); v[j + 3] = fmaxf(v[j + 3], 0.0f);
-            }
-            v[j] = v[j] * sc.x + sh.x; v[j + 1] = v[j + 1] * sc.y + sh.y;
-            v[j + 2] = v[j + 2] * sc.z + sh.z; v[j + 3] = v[j + 3] * sc.w + sh.w;
-          }
-          if (pool) {
-            float (*ex)[CHUNK] = tail->exch[chunk_i & 1];
-            if (lane == 31) {
-#pragma unroll
-              for (int j = 0; j < CHUNK; ++j) ex[g][j] = v[j];
-            }
-            named_bar_sync(2, EPI_THREADS);
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j) {
-              float prev = __shfl_up_sync(0xffffffffu, v[j], 1);
-              if (lane == 0) prev = (g > 0) ? ex[g - 1][j] : v[j];
-              v[j] = (t == 0) ? v[j] : fmaxf(v[j], prev);
-            }
-          }
-          const bool res_a = (P_out_t != nullptr) && (P_residual != nullptr);   // rare: residual in phase A
-          if (store && res_a) {
-            const float* res = P_residual + r * P_res_ld + nb;
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j)
-              if (nb + j < N) v[j] += __ldg(res + j);
-          }
-          if (store && P_out_t) {
-            float* ot = P_out_t + (static_cast<long long>(b) * N + nb) * P_seq_len + t;
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j)
-              if (nb + j < N) ot[static_cast<long long>(j) * P_seq_len] = v[j];
-          }
-          if (P_out) {
-#pragma unroll
-            for (int j = 0; j < CHUNK; j += 4)
-              *reinterpret_cast<float4*>(&stg[lane][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            __syncwarp();
-            const int col = nb + 4 * part;
-            if (col < N) {                                      // N and nb are multiples of 4
-#pragma unroll
-              for (int i8 = 0; i8 < 8; ++i8) {
-                const int row = i8 * 4 + sub;
-                if ((smask >> row) & 1u) {
-                  float4 y = *reinterpret_cast<const float4*>(&stg[row][4 * part]);
-                  const long long rr = r_warp + row;
-                  if (res_b) {
-                    const float4 xr = xr_cur[i8];
-                    y.x += xr.x; y.y += xr.y; y.z += xr.z; y.w += xr.w;
-                  }
-                  const long long o = rr * P_out_ld + P_out_col0 + col;
-                  if (P_out_full) *reinterpret_cast<float4*>(P_out_full + o) = y;
-                  if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-                  *reinterpret_cast<float4*>(P_out + o) = y;
-                }
-              }
-            }
-            __syncwarp();
-          }
-          if (res_b) {
-#pragma unroll
-            for (int i8 = 0; i8 < 8; ++i8) xr_cur[i8] = xr_nxt[i8];
-          }
-        }
+        EpiCtx c;
+        c.prm = prm; c.stg = stg; c.exch = tail->exch; c.taddr = taddr;
+        c.bn = P_bn; c.n0 = tc.n0; c.N = N; c.g = g; c.lane = lane; c.t = t; c.b = b; c.seq_len = P_seq_len;
+        c.res_ld = P_res_ld; c.out_ld = P_out_ld; c.smask = smask; c.store = store; c.r = r; c.r_warp = r_warp;
+        c.relu_lo = relu ? 0.0f : -INFINITY;
+        c.residual = P_residual;
+        c.out = P_out ? P_out + P_out_col0 : nullptr;
+        c.out_full = P_out_full ? P_out_full + P_out_col0 : nullptr;
+        c.out_t = P_out_t;
+        epi_dispatch(c, pool, P_residual != nullptr && P_out_t == nullptr, P_out_full != nullptr, P_out_t != nullptr, rnd);
       }
       tc_fence_before();
       __syncwarp();
