@@ -392,18 +392,21 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       const int sub = lane >> 3, part = lane & 7;               // phase-B coordinates
 
       if (highway) {
+        // Phase A (lane = row): x1/x2 chunks of 16 units from TMEM, this row's residual (prefetched one chunk
+        // ahead), the gate math on all 32 lanes, result staged.  Phase B: 64-byte row segments, coalesced.
         const int U = P_bn >> 1;
         const int u0 = tc.n0 >> 1;
-        // residual rows of this lane's phase-B items, fetched ONE CHUNK AHEAD (the epilogue has one warp per
-        // SMSP: an exposed DRAM/L2 round trip per row group was 90% of this path's time)
-        float4 xr_cur[8], xr_nxt[8];
-        auto load_res = [&](float4 (&dst)[8], int j0) {
+        const float* rrow = P_residual + r * P_res_ld + u0;                  // this lane's residual row
+        const int brow = lane >> 2, c4 = lane & 3;                           // phase-B coordinates: 8 rows x 4 float4
+        float* optr = P_out + (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4;
+        float* fptr = P_out_full ? P_out_full + (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4 : nullptr;
+        const long long ostep = 8ll * P_out_ld;
+        float4 xr_cur[4], xr_nxt[4];
+        auto load_res = [&](float4 (&dst)[4], int j0) {
 #pragma unroll
-          for (int i8 = 0; i8 < 8; ++i8) {
-            const int row = i8 * 4 + sub;
-            dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (part < 4 && j0 < U && ((smask >> row) & 1u))
-              dst[i8] = *reinterpret_cast<const float4*>(P_residual + (r_warp + row) * P_res_ld + u0 + j0 + 4 * part);
+          for (int q = 0; q < 4; ++q) {
+            dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (store && j0 < U) dst[q] = *reinterpret_cast<const float4*>(rrow + j0 + 4 * q);
           }
         };
         load_res(xr_cur, 0);
@@ -414,40 +417,30 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
           tmem_ld_32x16(taddr + U + j0, x2);
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 16; j += 4) {
-            const float4 b1 = *reinterpret_cast<const float4*>(&prm[0][j0 + j]);
-            const float4 b2 = *reinterpret_cast<const float4*>(&prm[0][U + j0 + j]);
-            *reinterpret_cast<float4*>(&stg[lane][j]) =
-                make_float4(x1[j] + b1.x, x1[j + 1] + b1.y, x1[j + 2] + b1.z, x1[j + 3] + b1.w);
-            *reinterpret_cast<float4*>(&stg[lane][16 + j]) =
-                make_float4(x2[j] + b2.x, x2[j + 1] + b2.y, x2[j + 2] + b2.z, x2[j + 3] + b2.w);
+          for (int q = 0; q < 4; ++q) {
+            const float4 b1 = *reinterpret_cast<const float4*>(&prm[0][j0 + 4 * q]);
+            const float4 b2 = *reinterpret_cast<const float4*>(&prm[0][U + j0 + 4 * q]);
+            float4 y;
+            y.x = epi_highway(x1[4 * q] + b1.x, x2[4 * q] + b2.x, xr_cur[q].x);
+            y.y = epi_highway(x1[4 * q + 1] + b1.y, x2[4 * q + 1] + b2.y, xr_cur[q].y);
+            y.z = epi_highway(x1[4 * q + 2] + b1.z, x2[4 * q + 2] + b2.z, xr_cur[q].z);
+            y.w = epi_highway(x1[4 * q + 3] + b1.w, x2[4 * q + 3] + b2.w, xr_cur[q].w);
+            *reinterpret_cast<float4*>(&stg[lane][4 * q]) = y;
           }
           __syncwarp();
 #pragma unroll
-          for (int i8 = 0; i8 < 8; ++i8) {
-            const int row = i8 * 4 + sub;
-            const float4 mine = *reinterpret_cast<const float4*>(&stg[row][4 * part]);
-            float4 a2;                                          // lanes part<4 hold x1; their x2 sits 4 lanes up
-            a2.x = __shfl_down_sync(0xffffffffu, mine.x, 4);
-            a2.y = __shfl_down_sync(0xffffffffu, mine.y, 4);
-            a2.z = __shfl_down_sync(0xffffffffu, mine.z, 4);
-            a2.w = __shfl_down_sync(0xffffffffu, mine.w, 4);
-            if (part < 4 && ((smask >> row) & 1u)) {
-              const long long rr = r_warp + row;
-              const int u = u0 + j0 + 4 * part;
-              const float4 xr = xr_cur[i8];
-              float4 y;
-              y.x = epi_highway(mine.x, a2.x, xr.x); y.y = epi_highway(mine.y, a2.y, xr.y);
-              y.z = epi_highway(mine.z, a2.z, xr.z); y.w = epi_highway(mine.w, a2.w, xr.w);
-              const long long o = rr * P_out_ld + P_out_col0 + u;
-              if (P_out_full) *reinterpret_cast<float4*>(P_out_full + o) = y;
+          for (int i4 = 0; i4 < 4; ++i4) {
+            const int row = i4 * 8 + brow;
+            if ((smask >> row) & 1u) {
+              float4 y = *reinterpret_cast<const float4*>(&stg[row][4 * c4]);
+              if (fptr) *reinterpret_cast<float4*>(fptr + i4 * ostep + j0) = y;
               if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-              *reinterpret_cast<float4*>(P_out + o) = y;
+              *reinterpret_cast<float4*>(optr + i4 * ostep + j0) = y;
             }
           }
           __syncwarp();
 #pragma unroll
-          for (int i8 = 0; i8 < 8; ++i8) xr_cur[i8] = xr_nxt[i8];
+          for (int q = 0; q < 4; ++q) xr_cur[q] = xr_nxt[q];
         }
       } else {
         EpiCtx c;
