@@ -79,19 +79,19 @@ __device__ __forceinline__ float tanh_fast(float x) { return __fdividef(2.0f, 1.
 template <int G, int H>
 struct RnnTiling {
   static constexpr int U = RNN_U, NB = RNN_NB, KS = RNN_KS;
+  static constexpr int NG = 2, NBG = NB / NG;   // two independent batch groups of 8 columns (one MMA n-tile each)
   static constexpr int RC = G * U;              // W_hh rows owned by this CTA (128 / 96)
   static constexpr int RS = RC / 16;            // 16-row MMA strips (8 / 6)
   static constexpr int WARPS = RS * KS;         // MMA warps (16 / 12)
   static constexpr int KW = H / KS;             // k extent per warp group (multiple of 32)
-  static constexpr int KB = KW / 32;            // 32-wide k blocks: one LDS.128 of h feeds 2 k-steps per n-tile
-  static constexpr int NT = NB / 8;             // 2 n-tiles
-  static constexpr int S = RC + 4;              // fp32 row stride of the partial-sum tile [KS][NB][S] (S = 4 mod 16)
+  static constexpr int KB = KW / 32;            // 32-wide k blocks: one LDS.128 of h feeds 2 k-steps
+  static constexpr int S = RC + 4;              // fp32 row stride of a partial-sum tile [NG][KS][NBG][S] (S = 4 mod 16)
   static constexpr int HS = H + 32;             // fp16 row stride of the staged h tile (HS/2 = 16 mod 32 words)
   static constexpr int XSTR = G * U;            // per-batch stride of an x-projection stage (floats)
   static constexpr int GS = RS * 32;            // threads of one K group
-  static constexpr int ITEMS = NB * KW / 8;     // 16-byte items (8 halves) of one K-half of h
+  static constexpr int ITEMS = NBG * KW / 8;    // 16-byte items (8 halves) of one K-half of one batch group of h
   static constexpr int IPT = (ITEMS + GS - 1) / GS;
-  static constexpr int SMEM_BYTES = NB * HS * 2 + (2 * KS * NB * S + RNN_XS * NB * XSTR) * 4;
+  static constexpr int SMEM_BYTES = NB * HS * 2 + (NG * KS * NBG * S + RNN_XS * NB * XSTR) * 4;
   static_assert(RC % 16 == 0 && KW % 32 == 0 && WARPS * 32 <= RNN_THREADS, "bad recurrence tiling");
   static_assert(U * NB == RNN_THREADS && (NB * G * U / 4) <= RNN_THREADS, "one (unit, batch) pair / x chunk per thread");
 };
@@ -99,11 +99,11 @@ struct RnnTiling {
 template <int G, int H>
 __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* smem) {
   using T = RnnTiling<G, H>;
-  constexpr int U = T::U, NB = T::NB, KS = T::KS, WARPS = T::WARPS, KW = T::KW, KB = T::KB;
-  constexpr int NT = T::NT, S = T::S, HS = T::HS, XSTR = T::XSTR, GS = T::GS, ITEMS = T::ITEMS, IPT = T::IPT;
-  __half* h_s = reinterpret_cast<__half*>(smem);                       // [NB][HS] fp16
-  float* p_s = reinterpret_cast<float*>(smem + NB * HS * 2);           // [2][KS][NB][S]
-  float* x_s = p_s + 2 * KS * NB * S;                                  // [XS][NB][XSTR]
+  constexpr int U = T::U, NB = T::NB, KS = T::KS, WARPS = T::WARPS, KW = T::KW, KB = T::KB, NBG = T::NBG;
+  constexpr int S = T::S, HS = T::HS, XSTR = T::XSTR, GS = T::GS, ITEMS = T::ITEMS, IPT = T::IPT;
+  __half* h_s = reinterpret_cast<__half*>(smem);                       // [NB][HS] fp16 (rows 0-7 group A, 8-15 group B)
+  float* p_s = reinterpret_cast<float*>(smem + NB * HS * 2);           // [NG][KS][NBG][S]
+  float* x_s = p_s + T::NG * KS * NBG * S;                             // [XS][NB][XSTR]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slice = local_cta % p.slices;
@@ -112,7 +112,6 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   const int u0 = slice * U;
   const int b0 = p.b_begin + bg * NB;
   const int nbv = min(NB, p.b_end - b0);            // valid batch columns in this CTA
-  const int ntv = (nbv + 7) >> 3;                   // n-tiles that hold any valid column
   const int L = p.seq_len;
   const int GH = G * H;
   const float* whh = p.w_hh + static_cast<size_t>(dir) * GH * H;
@@ -125,8 +124,9 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   // k order inside a 32-wide block: lane group q owns k = 8q..8q+7; k-step s uses 8q+4s..8q+4s+3.
   const int rs = warp / KS, kq = warp % KS;
   const int q = lane & 3, fr = lane >> 2;
+  const bool mma_warp = warp < WARPS;
   uint32_t wfrag[KB * 2][4];
-  if (warp < WARPS) {
+  if (mma_warp) {
     const int lr_lo = rs * 16 + fr, lr_hi = lr_lo + 8;
     const float* w_lo = whh + static_cast<size_t>((lr_lo / U) * H + u0 + (lr_lo % U)) * H;
     const float* w_hi = whh + static_cast<size_t>((lr_hi / U) * H + u0 + (lr_hi % U)) * H;
@@ -145,6 +145,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
 
   // ---- this thread's (unit, batch) pair: state + biases --------------------------------------
   const int pu = tid % U, pb = tid / U;             // a warp = the 32 units of one batch column
+  const int pg = pb / NBG, pbl = pb % NBG;          // batch group (warps 0-7: A, 8-15: B) and column inside it
   const bool pv = pb < nbv;
   float c_state = 0.0f, h_state = 0.0f, bias[G];
 #pragma unroll
@@ -168,116 +169,78 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
 #pragma unroll
   for (int s = 0; s < RNN_XS - 1; ++s) prefetch_x(s);
 
-#ifdef FTB_RNN_PROFILE
-  // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
-  unsigned long long prof[6] = {0, 0, 0, 0, 0, 0};
-  unsigned polls = 0;
-#define FTB_TICK(i) { const long long now_ = clock64(); prof[i] += now_ - tick_; tick_ = now_; }
-  long long tick_ = clock64();
-#else
-#define FTB_TICK(i)
-#endif
-
-  for (int step = 0; step < L; ++step) {
-    const int t = dir ? (L - 1 - step) : step;
-    const int tprev = dir ? (t + 1) : (t - 1);
-    float* pw = p_s + (step & 1) * (KS * NB * S);
-    FTB_TICK(0)
-
-    if (step > 0 && warp < WARPS) {
-      // ---- stage this K-half of h_{t-1} (fp16): poll the data until no sentinel is left --------
-      {
-        const int gtid = rs * 32 + lane;
-        const __half* hsrc = hx_dir + (static_cast<size_t>(tprev) * p.batch + b0) * H + kq * KW;
-        uint4 v[IPT];
-        unsigned pending = 0;
+  // ---- h staging: this thread's 16-byte items of (group g, its K half), L2 -> smem by cp.async.cg ----
+  const int gtid = rs * 32 + lane;
+  const __half* hsrc0 = hx_dir + static_cast<size_t>(b0) * H + kq * KW;          // + t * batch * H
+  __half* hdst0 = h_s + kq * KW;
+  auto issue_h = [&](int g, int tsrc) {             // fire-and-forget; one commit group
 #pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-          const int i = gtid + j * GS;
-          v[j] = make_uint4(0u, 0u, 0u, 0u);
-          if (i < ITEMS && (i / (KW / 8)) < nbv) pending |= 1u << j;
-        }
-        unsigned spins = 0;
-        while (pending) {
+    for (int j = 0; j < IPT; ++j) {
+      const int i = gtid + j * GS;
+      const int b = g * NBG + i / (KW / 8), c8 = i % (KW / 8);
+      if (i < ITEMS && b < nbv)
+        cp_async16(hdst0 + b * HS + c8 * 8, hsrc0 + (static_cast<size_t>(tsrc) * p.batch + b) * H + c8 * 8);
+    }
+    cp_async_commit();
+  };
+  // after the copies have landed: "h arrived" == "no 0xFFFF half left"; re-fetch the items that still hold the
+  // sentinel (their producer had not published yet when the copy read L2)
+  auto settle_h = [&](int g, int tsrc, unsigned& retries) {
+    unsigned spins = 0;
+    while (true) {
+      bool again = false;
 #pragma unroll
-          for (int j = 0; j < IPT; ++j) {
-            if (pending & (1u << j)) {
-              const int i = gtid + j * GS;
-              const int b = i / (KW / 8), c8 = i % (KW / 8);
-              v[j] = ld_relaxed_u4(hsrc + static_cast<size_t>(b) * H + c8 * 8);
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < IPT; ++j) {
-            if ((pending & (1u << j)) && !has_sentinel(v[j].x) && !has_sentinel(v[j].y) &&
-                !has_sentinel(v[j].z) && !has_sentinel(v[j].w))
-              pending &= ~(1u << j);
-          }
-#ifdef FTB_RNN_PROFILE
-          ++polls;
-#endif
-          if (pending && ++spins > (1u << 22)) {
-            printf("ftb: recurrence wait for h timed out (block %d step %d)\n", blockIdx.x, step);
-            __trap();
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-          const int i = gtid + j * GS;
-          if (i < ITEMS) {
-            const int b = i / (KW / 8), c8 = i % (KW / 8);
-            *reinterpret_cast<uint4*>(h_s + b * HS + kq * KW + c8 * 8) = v[j];
+      for (int j = 0; j < IPT; ++j) {
+        const int i = gtid + j * GS;
+        const int b = g * NBG + i / (KW / 8), c8 = i % (KW / 8);
+        if (i < ITEMS && b < nbv) {
+          const uint4 v = *reinterpret_cast<const uint4*>(hdst0 + b * HS + c8 * 8);
+          if (has_sentinel(v.x) || has_sentinel(v.y) || has_sentinel(v.z) || has_sentinel(v.w)) {
+            cp_async16(hdst0 + b * HS + c8 * 8, hsrc0 + (static_cast<size_t>(tsrc) * p.batch + b) * H + c8 * 8);
+            again = true;
           }
         }
       }
-      FTB_TICK(1)
-      named_bar_sync(1 + kq, GS);
-      FTB_TICK(2)
-
-      // ---- P = W_hh[slice rows, K-half] * h_{t-1}^T   (tensor cores, fp16 x fp16 -> fp32)
-      float acc[NT][4];
-#pragma unroll
-      for (int nt = 0; nt < NT; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
-#pragma unroll
-      for (int kb = 0; kb < KB; ++kb) {
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-          if (nt < ntv) {
-            const uint4 hv = *reinterpret_cast<const uint4*>(h_s + (nt * 8 + fr) * HS + kq * KW + kb * 32 + 8 * q);
-            mma_f16_16x8x16(acc[nt], wfrag[kb * 2 + 0], hv.x, hv.y);
-            mma_f16_16x8x16(acc[nt], wfrag[kb * 2 + 1], hv.z, hv.w);
-          }
-        }
-      }
-      float* pk = pw + static_cast<size_t>(kq) * NB * S;
-#pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        if (nt < ntv) {
-          const int col = nt * 8 + 2 * q, row = rs * 16 + fr;
-          pk[col * S + row] = acc[nt][0];
-          pk[(col + 1) * S + row] = acc[nt][1];
-          pk[col * S + row + 8] = acc[nt][2];
-          pk[(col + 1) * S + row + 8] = acc[nt][3];
-        }
+      if (!again) break;
+      cp_async_commit();
+      cp_async_wait<0>();
+      ++retries;
+      if (++spins > (1u << 20)) {
+        printf("ftb: recurrence wait for h timed out (block %d)\n", blockIdx.x);
+        __trap();
       }
     }
-    FTB_TICK(3)
-    cp_async_wait<RNN_XS - 2>();          // this thread's chunk of step `step` has landed
-    __syncthreads();                      // partial sums + everyone's x chunks visible; ring slot (step-1) free
-    FTB_TICK(4)
-    prefetch_x(step + RNN_XS - 1);
-
-    // ---- gate math (fp32), state update, publish h_t
+  };
+  // P[g] = W_hh[slice rows, K-half] * h_{t-1}[group g]^T   (tensor cores, fp16 x fp16 -> fp32)
+  auto mma_group = [&](int g) {
+    float acc0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, acc1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    const __half* hrow = h_s + (g * NBG + fr) * HS + kq * KW + 8 * q;
+#pragma unroll
+    for (int kb = 0; kb < KB; ++kb) {
+      const uint4 hv = *reinterpret_cast<const uint4*>(hrow + kb * 32);
+      mma_f16_16x8x16(acc0, wfrag[kb * 2 + 0], hv.x, hv.y);
+      mma_f16_16x8x16(acc1, wfrag[kb * 2 + 1], hv.z, hv.w);
+    }
+    float* pk = p_s + static_cast<size_t>(g * KS + kq) * NBG * S;
+    const int col = 2 * q, row = rs * 16 + fr;
+    pk[col * S + row] = acc0[0] + acc1[0];
+    pk[(col + 1) * S + row] = acc0[1] + acc1[1];
+    pk[col * S + row + 8] = acc0[2] + acc1[2];
+    pk[(col + 1) * S + row + 8] = acc0[3] + acc1[3];
+  };
+  // gate math (fp32), state update and publication of h_t for this thread's pair (threads of group g only)
+  auto gate_group = [&](int step, int t) {
     float hnew = 0.0f;
     if (pv) {
       const float* xs = x_s + (step % RNN_XS) * (NB * XSTR) + pb * XSTR + pu;
+      const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
       float hh[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         float s = bias[g];
         if (step > 0) {
 #pragma unroll
-          for (int ks = 0; ks < KS; ++ks) s += pw[(static_cast<size_t>(ks) * NB + pb) * S + g * U + pu];
+          for (int ks = 0; ks < KS; ++ks) s += pw[ks * NBG * S + g * U];
         }
         hh[g] = s;
       }
@@ -285,7 +248,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         const float ig = sigm(xs[0] + hh[0]);
         const float fg = sigm(xs[U] + hh[1]);
         const float gg = tanh_fast(xs[2 * U] + hh[2]);
-        const float og = sigm(xs[3 * U] + hh[3]);
+        const float og = sigm(xs[3 * U] + hh[G - 1]);
         c_state = fg * c_state + ig * gg;
         hnew = og * tanh_fast(c_state);
       } else {
@@ -305,14 +268,63 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         st_relaxed_u32(hx_pair + static_cast<size_t>(t) * p.batch * H, mine | (other << 16));
       out_pair[static_cast<size_t>(t) * p.out_ld] = __half2float(h16);
     }
+  };
+
+#ifdef FTB_RNN_PROFILE
+  // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
+  unsigned long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define FTB_TICK(i) { const long long now_ = clock64(); prof[i] += now_ - tick_; tick_ = now_; }
+  long long tick_ = clock64();
+#else
+#define FTB_TICK(i)
+#endif
+  unsigned retries = 0;
+  const bool has_b = nbv > NBG;                     // group B holds at least one valid column
+
+  // The two batch groups are independent recurrences that share the register-resident weights.  Their
+  // per-step chains (publish -> L2 -> stage -> MMA -> gates -> publish) are interleaved so that the L2
+  // round trip of one group is covered by the tensor-core and gate phases of the other.
+  for (int step = 0; step < L; ++step) {
+    const int t = dir ? (L - 1 - step) : step;
+    const int tprev = dir ? (t + 1) : (t - 1);
+    FTB_TICK(0)
+    // ---------------- group A --------------------------------------------------------------------
+    if (step > 0 && mma_warp) {
+      cp_async_wait<0>();                  // A copies were issued in the previous iteration
+      settle_h(0, tprev, retries);
+      FTB_TICK(1)
+      named_bar_sync(1 + kq, GS);
+      if (has_b) issue_h(1, tprev);        // group B of t-1 was published at the end of the previous iteration
+      mma_group(0);
+    }
+    if (step == 0 || !mma_warp) cp_async_wait<RNN_XS - 2>();   // x chunk of this step (MMA warps: covered above)
+    __syncthreads();                       // A partial sums + everyone's x chunks visible; ring slot (step-1) free
+    FTB_TICK(2)
+    prefetch_x(step + RNN_XS - 1);
+    if (pg == 0) gate_group(step, t);
+    FTB_TICK(3)
+    // ---------------- group B --------------------------------------------------------------------
+    if (mma_warp) {
+      if (step > 0 && has_b) {
+        cp_async_wait<1>();                // B copies done (the x prefetch just committed may still be in flight)
+        settle_h(1, tprev, retries);
+      }
+      FTB_TICK(4)
+      named_bar_sync(3 + kq, GS);          // also orders gate A's publication before the A re-fetch below
+      if (step + 1 < L) issue_h(0, t);     // group A of step t: published by the A-warps of all CTAs just now
+      if (step > 0 && has_b) mma_group(1);
+    }
+    __syncthreads();                       // B partial sums visible
     FTB_TICK(5)
+    if (pg == 1) gate_group(step, t);
+    FTB_TICK(6)
   }
   cp_async_wait<0>();
 #ifdef FTB_RNN_PROFILE
   if (tid == 0 && (local_cta % 37) == 0)
-    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu poll %llu bar %llu mma %llu sync %llu gate %llu | polls/step %.2f\n",
-           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L,
-           static_cast<float>(polls) / L);
+    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu waitA %llu mmaA+sync %llu gateA %llu waitB %llu mmaB+sync %llu gateB %llu | retries/step %.2f\n",
+           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L, prof[6] / L,
+           static_cast<float>(retries) / L);
 #endif
 }
 
