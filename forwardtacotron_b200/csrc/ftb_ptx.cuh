@@ -211,6 +211,11 @@ __device__ __forceinline__ float round_tf32(float x) {
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
+// Producer side of a split barrier: counts this thread in without waiting (the consumers bar.sync on the same id);
+// shared-memory writes made before the arrive are visible to the threads released by the barrier.
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ float sigmoidf_acc(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
 }  // namespace ftb
