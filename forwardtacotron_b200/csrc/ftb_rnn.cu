@@ -73,8 +73,10 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 // exp/rcp at ~2 ulp: absolute gate error ~3e-7, far below the operand rounding of the h @ W_hh products
-__device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float tanh_fast(float x) { return __fdividef(2.0f, 1.0f + __expf(-2.0f * x)) - 1.0f; }
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigm(float x) { return rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float tanh_fast(float x) { return fmaf(2.0f, rcp_ftz(1.0f + ex2_ftz(-2.8853900817779268f * x)), -1.0f); }
 
 template <int G, int H>
 struct RnnTiling {
@@ -159,44 +161,55 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   const bool xv = (tid < NB * G * XCH) && (xb < nbv);
   const float* x_src = xp_dir + static_cast<size_t>(b0 + xb) * p.seq_stride * (2 * GH) + xg_ * H + u0 + xpart * 4;
   float* x_dst = x_s + xb * XSTR + xg_ * U + xpart * 4;
-  auto prefetch_x = [&](int step) {
-    if (xv && step < L) {
-      const int t = dir ? (L - 1 - step) : step;
-      cp_async16(x_dst + (step % RNN_XS) * (NB * XSTR), x_src + static_cast<size_t>(t) * (2 * GH));
-    }
+  // running pointers (strength-reduced: the per-step 64-bit index math sat on the latency chain of the gate phase)
+  const long long x_step = dir ? -static_cast<long long>(2 * GH) : static_cast<long long>(2 * GH);
+  const float* x_pf = x_src + static_cast<size_t>(dir ? L - 1 : 0) * (2 * GH);
+  int pf_step = 0;
+  auto prefetch_x = [&]() {                         // x rows of step `pf_step` -> ring slot pf_step % XS
+    if (xv && pf_step < L) cp_async16(x_dst + (pf_step & (RNN_XS - 1)) * (NB * XSTR), x_pf);
     cp_async_commit();
+    x_pf += x_step;
+    ++pf_step;
   };
 #pragma unroll
-  for (int s = 0; s < RNN_XS - 1; ++s) prefetch_x(s);
+  for (int s = 0; s < RNN_XS - 1; ++s) prefetch_x();
 
   // ---- h staging: this thread's 16-byte items of (group g, its K half), L2 -> smem by cp.async.cg ----
   const int gtid = rs * 32 + lane;
-  const __half* hsrc0 = hx_dir + static_cast<size_t>(b0) * H + kq * KW;          // + t * batch * H
-  __half* hdst0 = h_s + kq * KW;
-  auto issue_h = [&](int g, int tsrc) {             // fire-and-forget; one commit group
+  const long long h_step = dir ? -static_cast<long long>(p.batch) * H : static_cast<long long>(p.batch) * H;
+  const __half* hp[IPT];                            // group-A item j at time row t (advanced every step); B = + NBG rows
+  __half* hd[IPT];
+  unsigned ok_a = 0, ok_b = 0;
 #pragma unroll
-    for (int j = 0; j < IPT; ++j) {
-      const int i = gtid + j * GS;
-      const int b = g * NBG + i / (KW / 8), c8 = i % (KW / 8);
-      if (i < ITEMS && b < nbv)
-        cp_async16(hdst0 + b * HS + c8 * 8, hsrc0 + (static_cast<size_t>(tsrc) * p.batch + b) * H + c8 * 8);
-    }
+  for (int j = 0; j < IPT; ++j) {
+    const int i = gtid + j * GS;
+    const int b = i / (KW / 8), c8 = i % (KW / 8);
+    hp[j] = hx_dir + (static_cast<size_t>(dir ? L - 1 : 0) * p.batch + b0 + b) * H + kq * KW + c8 * 8;
+    hd[j] = h_s + b * HS + kq * KW + c8 * 8;
+    if (mma_warp && i < ITEMS && b < nbv) ok_a |= 1u << j;
+    if (mma_warp && i < ITEMS && b + NBG < nbv) ok_b |= 1u << j;
+  }
+  // issue / settle take the offset (in halves) of the wanted time row relative to hp[]: 0 = row t, -h_step = row t-1
+  auto issue_h = [&](int g, long long toff) {       // fire-and-forget; one commit group
+    const unsigned ok = g ? ok_b : ok_a;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j)
+      if (ok & (1u << j)) cp_async16(hd[j] + g * (NBG * HS), hp[j] + toff + g * (NBG * H));
     cp_async_commit();
   };
   // after the copies have landed: "h arrived" == "no 0xFFFF half left"; re-fetch the items that still hold the
   // sentinel (their producer had not published yet when the copy read L2)
-  auto settle_h = [&](int g, int tsrc, unsigned& retries) {
+  auto settle_h = [&](int g, long long toff, unsigned& retries) {
+    const unsigned ok = g ? ok_b : ok_a;
     unsigned spins = 0;
     while (true) {
       bool again = false;
 #pragma unroll
       for (int j = 0; j < IPT; ++j) {
-        const int i = gtid + j * GS;
-        const int b = g * NBG + i / (KW / 8), c8 = i % (KW / 8);
-        if (i < ITEMS && b < nbv) {
-          const uint4 v = *reinterpret_cast<const uint4*>(hdst0 + b * HS + c8 * 8);
+        if (ok & (1u << j)) {
+          const uint4 v = *reinterpret_cast<const uint4*>(hd[j] + g * (NBG * HS));
           if (has_sentinel(v.x) || has_sentinel(v.y) || has_sentinel(v.z) || has_sentinel(v.w)) {
-            cp_async16(hdst0 + b * HS + c8 * 8, hsrc0 + (static_cast<size_t>(tsrc) * p.batch + b) * H + c8 * 8);
+            cp_async16(hd[j] + g * (NBG * HS), hp[j] + toff + g * (NBG * H));
             again = true;
           }
         }
@@ -228,20 +241,23 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     pk[col * S + row + 8] = acc0[2] + acc1[2];
     pk[(col + 1) * S + row + 8] = acc0[3] + acc1[3];
   };
-  // gate math (fp32), state update and publication of h_t for this thread's pair (threads of group g only)
-  auto gate_group = [&](int step, int t) {
+  // gate math (fp32), state update and publication of h_t for this thread's pair (threads of group g only).
+  // The partial-sum tiles start zeroed, so step 0 (h_{-1} = 0, no MMA) needs no special case.
+  const long long o_step = dir ? -static_cast<long long>(p.out_ld) : static_cast<long long>(p.out_ld);
+  float* out_p = out_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.out_ld;
+  __half* hx_p = hx_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.batch * H;
+  const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
+  const float* xs0 = x_s + pb * XSTR + pu;
+  auto gate_group = [&](int step) {
     float hnew = 0.0f;
     if (pv) {
-      const float* xs = x_s + (step % RNN_XS) * (NB * XSTR) + pb * XSTR + pu;
-      const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
+      const float* xs = xs0 + (step & (RNN_XS - 1)) * (NB * XSTR);
       float hh[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         float s = bias[g];
-        if (step > 0) {
 #pragma unroll
-          for (int ks = 0; ks < KS; ++ks) s += pw[ks * NBG * S + g * U];
-        }
+        for (int ks = 0; ks < KS; ++ks) s += pw[ks * NBG * S + g * U];
         hh[g] = s;
       }
       if (G == 4) {
@@ -264,10 +280,11 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     const unsigned mine = __half_as_ushort(h16);
     const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
     if (pv) {
-      if ((lane & 1) == 0)
-        st_relaxed_u32(hx_pair + static_cast<size_t>(t) * p.batch * H, mine | (other << 16));
-      out_pair[static_cast<size_t>(t) * p.out_ld] = __half2float(h16);
+      if ((lane & 1) == 0) st_relaxed_u32(hx_p, mine | (other << 16));
+      *out_p = __half2float(h16);
     }
+    out_p += o_step;
+    hx_p += h_step;
   };
 
 #ifdef FTB_RNN_PROFILE
@@ -284,39 +301,40 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   // The two batch groups are independent recurrences that share the register-resident weights.  Their
   // per-step chains (publish -> L2 -> stage -> MMA -> gates -> publish) are interleaved so that the L2
   // round trip of one group is covered by the tensor-core and gate phases of the other.
+  for (int i = tid; i < T::NG * KS * NBG * S; i += RNN_THREADS) p_s[i] = 0.0f;
   for (int step = 0; step < L; ++step) {
-    const int t = dir ? (L - 1 - step) : step;
-    const int tprev = dir ? (t + 1) : (t - 1);
     FTB_TICK(0)
     // ---------------- group A --------------------------------------------------------------------
     if (step > 0 && mma_warp) {
       cp_async_wait<0>();                  // A copies were issued in the previous iteration
-      settle_h(0, tprev, retries);
+      settle_h(0, -h_step, retries);
       FTB_TICK(1)
       named_bar_sync(1 + kq, GS);
-      if (has_b) issue_h(1, tprev);        // group B of t-1 was published at the end of the previous iteration
+      if (has_b) issue_h(1, -h_step);      // group B of t-1 was published at the end of the previous iteration
       mma_group(0);
     }
     if (step == 0 || !mma_warp) cp_async_wait<RNN_XS - 2>();   // x chunk of this step (MMA warps: covered above)
     __syncthreads();                       // A partial sums + everyone's x chunks visible; ring slot (step-1) free
     FTB_TICK(2)
-    prefetch_x(step + RNN_XS - 1);
-    if (pg == 0) gate_group(step, t);
+    prefetch_x();
+    if (pg == 0) gate_group(step);
     FTB_TICK(3)
     // ---------------- group B --------------------------------------------------------------------
     if (mma_warp) {
       if (step > 0 && has_b) {
         cp_async_wait<1>();                // B copies done (the x prefetch just committed may still be in flight)
-        settle_h(1, tprev, retries);
+        settle_h(1, -h_step, retries);
       }
       FTB_TICK(4)
       named_bar_sync(3 + kq, GS);          // also orders gate A's publication before the A re-fetch below
-      if (step + 1 < L) issue_h(0, t);     // group A of step t: published by the A-warps of all CTAs just now
+      if (step + 1 < L) issue_h(0, 0);     // group A of step t: published by the A-warps of all CTAs just now
       if (step > 0 && has_b) mma_group(1);
+#pragma unroll
+      for (int j = 0; j < IPT; ++j) hp[j] += h_step;
     }
     __syncthreads();                       // B partial sums visible
     FTB_TICK(5)
-    if (pg == 1) gate_group(step, t);
+    if (pg == 1) gate_group(step);
     FTB_TICK(6)
   }
   cp_async_wait<0>();
