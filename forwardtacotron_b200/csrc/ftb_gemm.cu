@@ -224,7 +224,9 @@ __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool re
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment by pointer arithmetic on the __shared__ array (an integer round trip would demote every
+  // later access through `tail` to generic LD/ST, which the epilogue pays for in latency)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   SmemTail* tail = reinterpret_cast<SmemTail*>(smem + STAGES * STAGE_BYTES);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
