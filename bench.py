@@ -58,42 +58,90 @@ def make_tokens(batch, rank=0):
 
 
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed region (every ~5 ms through NVML in a thread; falls back
+    to an `nvidia-smi -lms` subprocess when the NVML binding is unavailable)."""
     QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    REASON_BITS = {'sw_power_cap': 0x4, 'hw_slowdown': 0x8, 'sw_thermal_slowdown': 0x20, 'hw_thermal_slowdown': 0x40}
 
     def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+        self.index, self.sm, self.max_sm, self.reasons = index, [], None, set()
+        self.proc = self.thread = self.nvml = self.handle = None
+        self.stop = threading.Event()
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            uuid = uuid if uuid.startswith('GPU-') else 'GPU-' + uuid
+            try:
+                h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except TypeError:
+                h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+        return pynvml, h
+
+    def _poll_nvml(self):
+        n, h = self.nvml, self.handle
+        get_reasons = getattr(n, 'nvmlDeviceGetCurrentClocksEventReasons', None) or \
+            getattr(n, 'nvmlDeviceGetCurrentClocksThrottleReasons')
+        while not self.stop.is_set():
+            try:
+                self.sm.append(int(n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)))
+                mask = int(get_reasons(h))
+                self.reasons.update(k for k, bit in self.REASON_BITS.items() if mask & bit)
+            except Exception:
+                pass
+            self.stop.wait(0.005)
+
+    def _poll_smi(self):
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for line in self.proc.stdout:
+            r = [c.strip() for c in line.split(',')]
+            if r and r[0].isdigit():
+                self.sm.append(int(r[0]))
+            if len(r) > 1 and r[1].isdigit():
+                self.max_sm = max(self.max_sm or 0, int(r[1]))
+            if len(r) >= 6:
+                self.reasons.update(n for n, v in zip(names, r[2:6]) if v.lower() == 'active')
 
     def __enter__(self):
         try:
+            self.nvml, self.handle = self._nvml_handle()
+            self.max_sm = int(self.nvml.nvmlDeviceGetMaxClockInfo(self.handle, self.nvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return self
+        except Exception:
+            self.nvml = None
+        try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.QUERY}',
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                          '--format=csv,noheader,nounits', '-lms', '20'],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread = threading.Thread(target=self._poll_smi, daemon=True)
             self.thread.start()
         except Exception:
             self.proc = None
         return self
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(',')])
-
     def __exit__(self, *exc):
+        self.stop.set()
         if self.proc is not None:
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
             except Exception:
                 self.proc.kill()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
 
     def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == 'active'})
-        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'reasons': reasons, 'samples': len(sm)}
+        sm = sorted(self.sm)
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': self.max_sm,
+                'reasons': sorted(self.reasons), 'samples': len(sm),
+                'source': 'nvml' if self.nvml is not None else 'nvidia-smi'}
 
 
 def cpu_forward_timing(sd, batch, runs, warm, threads):
@@ -260,6 +308,19 @@ def run_ours(args, rank, world, local_rank):
                               'bound': 'hbm', 'achieved': ach, 'peak': peaks['hbm'], 'unit': 'GB/s',
                               'frac': ach / peaks['hbm'], 'traffic': None,
                               'peak_note': f"{peaks['source']}; latency-bound when it is a recurrence"})
+    # measured DRAM traffic (ncu dram__bytes_read.sum + dram__bytes_write.sum, all launches of the function in one
+    # generate(), same workload): committed summary of the launch list under profiles/ (scratch/launch_summary.py)
+    try:
+        tr_files = sorted(f for f in os.listdir(os.path.join(ROOT, 'profiles')) if f.endswith('_traffic.json'))
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', tr_files[-1]))) if tr_files else {}
+    except Exception:
+        tr_files, traffic = [], {}
+    for e in by_kernel:
+        t = traffic.get(e['kernel'])
+        if t and args.durations == 'fallback':
+            e['traffic'] = t['dram_bytes_per_step']
+            e['traffic_note'] = f"DRAM bytes per step over its {t['launches_per_step']} launches, profiles/{tr_files[-1]}"
+            e['algorithmic'] = (groups[e['kernel']]['bytes'] if e['bound'] == 'hbm' else None)
     roof = dict(by_kernel[0])
     top = kernels[0][0]
     roof['largest_launch'] = {k: top[k] for k in ('label', 'kind', 'ms') if k in top}

@@ -280,8 +280,11 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         const int taps = p->taps, kblocks = p->kblocks, tap0 = p->tap0, w_tap_rows = p->w_tap_rows;
         const CUtensorMap* tm_a = &p->tm_a;
         const CUtensorMap* tm_w = &p->tm_w;
-        for (int tap = 0; tap < taps; ++tap) {
-          for (int kb = 0; kb < kblocks; ++kb) {
+        // channel block outer, taps inner: the taps of one channel block re-read the same activation rows shifted by
+        // one, so they hit in L2 back to back (taps-outer re-read the whole [128 x C_in] slab from DRAM per tap:
+        // postnet.proj1 moved 533 MB for a 214 MB input, profiles/r1j_launch_summary.txt)
+        for (int kb = 0; kb < kblocks; ++kb) {
+          for (int tap = 0; tap < taps; ++tap) {
             GP_T0 mbar_wait(&tail->empty[stage], phase ^ 1u); GP_ACC(0)
             uint8_t* sa = smem + stage * STAGE_BYTES;
             uint8_t* sb = sa + A_STAGE_BYTES;
