@@ -39,18 +39,25 @@ def gather_variable_mels(mel: torch.Tensor, lens: torch.Tensor, group=None) -> T
     dev = mel.device
     b_local, C, m_local = mel.shape
     meta = torch.tensor([b_local, m_local], dtype=torch.int64, device=dev)
-    metas = [torch.empty_like(meta) for _ in range(world)]
-    dist.all_gather(metas, meta, group=group)
-    counts = [int(m[0]) for m in metas]
-    b_max, m_max = max(counts), max(int(m[1]) for m in metas)
-    block = torch.zeros((b_max, C, m_max), dtype=mel.dtype, device=dev)
-    block[:b_local, :, :m_local] = mel
-    lens_block = torch.zeros((b_max,), dtype=torch.int64, device=dev)
-    lens_block[:b_local] = lens.to(torch.int64)
+    metas = torch.empty((world, 2), dtype=torch.int64, device=dev)
+    _all_gather(metas, meta, group)
+    metas = metas.cpu()                                  # the one host sync: extents of every shard
+    counts = [int(v) for v in metas[:, 0]]
+    b_max, m_max = max(counts), int(metas[:, 1].max())
+    uniform = all(c == b_max for c in counts) and bool((metas[:, 1] == m_max).all())
+    if uniform and mel.is_contiguous():                  # equal shards (the weak-scaling case): no padding copies
+        block, lens_block = mel, lens.to(torch.int64)
+    else:
+        block = torch.zeros((b_max, C, m_max), dtype=mel.dtype, device=dev)
+        block[:b_local, :, :m_local] = mel
+        lens_block = torch.zeros((b_max,), dtype=torch.int64, device=dev)
+        lens_block[:b_local] = lens.to(torch.int64)
     blocks = torch.empty((world, b_max, C, m_max), dtype=mel.dtype, device=dev)
     lens_all = torch.empty((world, b_max), dtype=torch.int64, device=dev)
     _all_gather(blocks, block, group)
     _all_gather(lens_all, lens_block, group)
+    if uniform:
+        return blocks.view(world * b_max, C, m_max), lens_all.view(-1)
     out = torch.cat([blocks[r, :counts[r]] for r in range(world)], dim=0)
     out_lens = torch.cat([lens_all[r, :counts[r]] for r in range(world)], dim=0)
     return out, out_lens

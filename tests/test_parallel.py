@@ -71,6 +71,11 @@ def _worker(rank, world, port, ret):
         ln = torch.full((rank * 2,), 4 + rank, dtype=torch.int64)
         got, gl = par.gather_variable_mels(mel, ln)
         ok = ok and got.shape == (2, 3, 5) and bool((got == 2.0).all()) and gl.tolist() == [5, 5]
+        # equal shards (the weak-scaling case): gathered without padding copies, rank order kept
+        mel = torch.arange(2 * 3 * 4, dtype=torch.float32).reshape(2, 3, 4) + 100.0 * rank
+        got, gl = par.gather_variable_mels(mel, torch.tensor([4, 3 + rank]))
+        want_u = torch.cat([torch.arange(24, dtype=torch.float32).reshape(2, 3, 4) + 100.0 * r for r in range(world)])
+        ok = ok and torch.equal(got, want_u) and gl.tolist() == [4, 3, 4, 4]
         ret[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
