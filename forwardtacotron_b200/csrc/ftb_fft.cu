@@ -2,6 +2,9 @@
 // residual + LayerNorm (optionally chained with the transformer's final norm), and a
 // flash-style fp32 self-attention for 2..8 heads.  The QKV / out_proj / conv GEMMs run on
 // the tcgen05 kernel (ftb_gemm.cu); these kernels are the HBM-bound / SIMT remainder.
+#include <cstdlib>
+#include <cstring>
+
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
 
@@ -171,6 +174,186 @@ mha_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict__ key
   }
 }
 
+
+// ---------------------------------------------------------------- self attention, register-tiled
+// Same exact-fp32 arithmetic (the FastPitch parity margin leaves no room for tf32 scores), but both products are
+// register-tiled SIMT GEMMs instead of one dot product per lane:
+//   grid = (query tiles of 64, heads, batch), 256 threads; thread (ty, tx) = (tid / 16, tid % 16) owns query rows
+//   4ty..4ty+3.  Per key tile of KT keys: S = Q K^T with a 4 x KT/16 micro-tile per thread (float4 operand reads, the
+//   q rows are a quarter-warp broadcast), scores -> smem, online softmax by one warp per 8 rows (P overwrites S, the
+//   rescale factor goes to smem), then O = O*corr + P V with a 4 x D/16 micro-tile per thread.
+template <int D>
+__global__ void __launch_bounds__(256)
+mha_tiled_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict__ key_tok, int seq_len,
+                 int seq_stride, float* __restrict__ out, int round) {
+  constexpr int QT = 64, KT = (D > 64) ? 32 : 64, NJ = KT / 16, NH = D / 64, LDK = D + 4, LDP = KT + 4;
+  extern __shared__ __align__(16) float mha_sm[];
+  float* sq = mha_sm;                  // [QT][LDK]  q * 1/sqrt(D)
+  float* sk = sq + QT * LDK;           // [KT][LDK]
+  float* sv = sk + KT * LDK;           // [KT][D]
+  float* ss = sv + KT * D;             // [QT][LDP]  scores, then probabilities
+  float* scorr = ss + QT * LDP;        // [QT] rescale factor of this key tile, then 1 / row sum
+  int* smask = reinterpret_cast<int*>(scorr + QT);     // [KT]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, ty = tid >> 4, tx = tid & 15;
+  const int q0 = blockIdx.x * QT, head = blockIdx.y, b = blockIdx.z;
+  const long long rowbase = static_cast<long long>(b) * seq_stride;
+  const int ld = 3 * e;
+  const float scale = rsqrtf(static_cast<float>(D));
+  for (int i = tid; i < QT * (D / 4); i += 256) {
+    const int r = i / (D / 4), c4 = i % (D / 4);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (q0 + r < seq_len) {
+      v = *reinterpret_cast<const float4*>(qkv + (rowbase + q0 + r) * ld + head * D + 4 * c4);
+      v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+    }
+    *reinterpret_cast<float4*>(sq + r * LDK + 4 * c4) = v;
+  }
+  float m_run[8], l_run[8];            // softmax state of rows 8*warp + j (uniform over the warp)
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { m_run[j] = -INFINITY; l_run[j] = 0.0f; }
+  float oacc[4][4 * NH];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int c = 0; c < 4 * NH; ++c) oacc[i][c] = 0.0f;
+
+  for (int k0 = 0; k0 < seq_len; k0 += KT) {
+    __syncthreads();                   // previous tile fully consumed (and sq written, first iteration)
+    for (int i = tid; i < KT * (D / 4); i += 256) {
+      const int r = i / (D / 4), c4 = i % (D / 4);
+      float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
+      if (k0 + r < seq_len) {
+        const float* src = qkv + (rowbase + k0 + r) * ld + head * D + 4 * c4;
+        kv = *reinterpret_cast<const float4*>(src + e);
+        vv = *reinterpret_cast<const float4*>(src + 2 * e);
+      }
+      *reinterpret_cast<float4*>(sk + r * LDK + 4 * c4) = kv;
+      *reinterpret_cast<float4*>(sv + r * D + 4 * c4) = vv;
+    }
+    if (tid < KT) {
+      const int t = k0 + tid;
+      int ok = t < seq_len;
+      if (ok && key_tok) ok = key_tok[static_cast<long long>(b) * seq_len + t] != 0;
+      smask[tid] = ok;
+    }
+    __syncthreads();
+    // ---- S = Q K^T
+    {
+      float sacc[4][NJ];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) sacc[i][j] = 0.0f;
+#pragma unroll 4
+      for (int d = 0; d < D; d += 4) {
+        float4 qv[4], kv[NJ];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) qv[i] = *reinterpret_cast<const float4*>(sq + (4 * ty + i) * LDK + d);
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) kv[j] = *reinterpret_cast<const float4*>(sk + (tx + 16 * j) * LDK + d);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < NJ; ++j) {
+            sacc[i][j] = fmaf(qv[i].x, kv[j].x, sacc[i][j]);
+            sacc[i][j] = fmaf(qv[i].y, kv[j].y, sacc[i][j]);
+            sacc[i][j] = fmaf(qv[i].z, kv[j].z, sacc[i][j]);
+            sacc[i][j] = fmaf(qv[i].w, kv[j].w, sacc[i][j]);
+          }
+      }
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const bool ok = smask[tx + 16 * j] != 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ss[(4 * ty + i) * LDP + tx + 16 * j] = ok ? sacc[i][j] : -INFINITY;
+      }
+    }
+    __syncthreads();
+    // ---- online softmax: warp w owns rows 8w .. 8w+7
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float* row = ss + (8 * warp + j) * LDP;
+      float sv_[KT / 32];
+      float tmax = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < KT / 32; ++c) { sv_[c] = row[lane + 32 * c]; tmax = fmaxf(tmax, sv_[c]); }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+      const float mnew = fmaxf(m_run[j], tmax);
+      const float corr = (m_run[j] == -INFINITY) ? 0.0f : expf(m_run[j] - mnew);   // mnew = -inf only if m_run is
+      float psum = 0.0f;
+#pragma unroll
+      for (int c = 0; c < KT / 32; ++c) {
+        const float pexp = (sv_[c] == -INFINITY) ? 0.0f : expf(sv_[c] - mnew);
+        row[lane + 32 * c] = pexp;
+        psum += pexp;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) psum += __shfl_xor_sync(0xffffffffu, psum, o);
+      l_run[j] = l_run[j] * corr + psum;
+      m_run[j] = mnew;
+      if (lane == 0) scorr[8 * warp + j] = corr;
+    }
+    __syncthreads();
+    // ---- O = O * corr + P V
+    {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float cr = scorr[4 * ty + i];
+#pragma unroll
+        for (int c = 0; c < 4 * NH; ++c) oacc[i][c] *= cr;
+      }
+#pragma unroll 2
+      for (int k = 0; k < KT; k += 4) {
+        float4 pv[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) pv[i] = *reinterpret_cast<const float4*>(ss + (4 * ty + i) * LDP + k);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+          for (int h = 0; h < NH; ++h) {
+            const float4 vv = *reinterpret_cast<const float4*>(sv + (k + kk) * D + 4 * tx + 64 * h);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float pk = kk == 0 ? pv[i].x : kk == 1 ? pv[i].y : kk == 2 ? pv[i].z : pv[i].w;
+              oacc[i][4 * h + 0] = fmaf(pk, vv.x, oacc[i][4 * h + 0]);
+              oacc[i][4 * h + 1] = fmaf(pk, vv.y, oacc[i][4 * h + 1]);
+              oacc[i][4 * h + 2] = fmaf(pk, vv.z, oacc[i][4 * h + 2]);
+              oacc[i][4 * h + 3] = fmaf(pk, vv.w, oacc[i][4 * h + 3]);
+            }
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) scorr[8 * warp + j] = 1.0f / l_run[j];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int t = q0 + 4 * ty + i;
+    if (t < seq_len) {
+      const float inv = scorr[4 * ty + i];
+#pragma unroll
+      for (int h = 0; h < NH; ++h) {
+        float4 v = make_float4(oacc[i][4 * h] * inv, oacc[i][4 * h + 1] * inv, oacc[i][4 * h + 2] * inv,
+                               oacc[i][4 * h + 3] * inv);
+        if (round) { v.x = round_tf32(v.x); v.y = round_tf32(v.y); v.z = round_tf32(v.z); v.w = round_tf32(v.w); }
+        *reinterpret_cast<float4*>(out + (rowbase + t) * e + head * D + 4 * tx + 64 * h) = v;
+      }
+    }
+  }
+}
+
+template <int D>
+static constexpr int mha_tiled_smem() {
+  constexpr int QT = 64, KT = (D > 64) ? 32 : 64, LDK = D + 4, LDP = KT + 4;
+  return (QT * LDK + KT * LDK + KT * D + QT * LDP + QT + KT) * 4;
+}
+
 }  // namespace ftb
 
 using namespace ftb;
@@ -203,12 +386,34 @@ extern "C" int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const i
                        int seq_len, int seq_stride, float* out, int round_tf32, void* stream) {
   if (!h || !qkv || !out || heads < 1 || batch < 1 || seq_len < 1 || e % heads) return FTB_E_ARG;
   const int d = e / heads;
-  const int qt = d > 64 ? 16 : 32;
-  dim3 grid((seq_len + qt - 1) / qt, heads, batch);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (d == 64) mha_kernel<64><<<grid, 256, 0, st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
-  else if (d == 128) mha_kernel<128><<<grid, 256, 0, st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
-  else return FTB_E_SHAPE;
+  static const bool legacy = [] { const char* v = getenv("FTB_MHA_IMPL"); return v && strcmp(v, "legacy") == 0; }();
+  if ((e % 4) != 0 || (reinterpret_cast<uintptr_t>(qkv) & 15u) || (reinterpret_cast<uintptr_t>(out) & 15u))
+    return FTB_E_ALIGN;
+  if (legacy) {                                     // first-build kernel, kept for A/B measurements
+    const int qt = d > 64 ? 16 : 32;
+    dim3 grid((seq_len + qt - 1) / qt, heads, batch);
+    if (d == 64) mha_kernel<64><<<grid, 256, 0, st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
+    else if (d == 128) mha_kernel<128><<<grid, 256, 0, st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
+    else return FTB_E_SHAPE;
+  } else {
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t ce = cudaFuncSetAttribute(mha_tiled_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            mha_tiled_smem<64>());
+      if (ce == cudaSuccess)
+        ce = cudaFuncSetAttribute(mha_tiled_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  mha_tiled_smem<128>());
+      if (ce != cudaSuccess) return static_cast<int>(ce);
+      attr_set = true;
+    }
+    dim3 grid((seq_len + 63) / 64, heads, batch);
+    if (d == 64)
+      mha_tiled_kernel<64><<<grid, 256, mha_tiled_smem<64>(), st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
+    else if (d == 128)
+      mha_tiled_kernel<128><<<grid, 256, mha_tiled_smem<128>(), st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
+    else return FTB_E_SHAPE;
+  }
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }
