@@ -46,6 +46,21 @@ _FAST_PITCH = dict(
 )
 
 
+_MULTI_FAST_PITCH = dict(          # configs/multispeaker.yaml:165-216
+    speaker_emb_dims=256,
+    durpred_d_model=128, durpred_n_heads=2, durpred_layers=4, durpred_d_fft=128, durpred_dropout=0.5,
+    pitch_d_model=128, pitch_n_heads=2, pitch_layers=4, pitch_d_fft=128, pitch_dropout=0.5,
+    pitch_strength=1.0,
+    energy_d_model=128, energy_n_heads=2, energy_layers=4, energy_d_fft=128, energy_dropout=0.5,
+    energy_strength=1.0,
+    pitch_cond_d_model=128, pitch_cond_n_heads=2, pitch_cond_layers=4, pitch_cond_d_fft=128,
+    pitch_cond_dropout=0.5, pitch_cond_output_dims=3,
+    d_model=256, conv1_kernel=9, conv2_kernel=1,
+    prenet_layers=4, prenet_heads=2, prenet_fft=1024, prenet_dropout=0.1,
+    postnet_layers=4, postnet_heads=2, postnet_fft=1024, postnet_dropout=0.1,
+)
+
+
 def default_config(tts_model: str = 'forward_tacotron') -> dict:
     """A config dict of the shape `read_config` (utils/files.py:22) returns,
     restricted to the keys the model constructors read."""
@@ -53,6 +68,7 @@ def default_config(tts_model: str = 'forward_tacotron') -> dict:
         'forward_tacotron': _FORWARD_TACOTRON,
         'multi_forward_tacotron': _MULTI_FORWARD_TACOTRON,
         'fast_pitch': _FAST_PITCH,
+        'multi_fast_pitch': _MULTI_FAST_PITCH,
     }
     if tts_model not in table:
         raise ValueError(f'Model type not supported: {tts_model}')

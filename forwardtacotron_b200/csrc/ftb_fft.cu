@@ -186,7 +186,11 @@ template <int D>
 __global__ void __launch_bounds__(256)
 mha_tiled_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict__ key_tok, int seq_len,
                  int seq_stride, float* __restrict__ out, int round) {
-  constexpr int QT = 64, KT = (D > 64) ? 32 : 64, NJ = KT / 16, NH = D / 64, LDK = D + 4, LDP = KT + 4;
+  // D % 4 == 0 (float4 operand reads).  Row stride LDK = odd multiple of 4 floats (mod 32) keeps the 8 key rows a
+  // quarter-warp reads at once on distinct bank groups.  A thread's output columns are the float4 groups tx + 16h.
+  constexpr int QT = 64, KT = (D > 64) ? 32 : 64, NJ = KT / 16, D4 = D / 4, NH = (D4 + 15) / 16;
+  constexpr int LDK = D + ((D % 8 == 0) ? 4 : 8), LDP = KT + 4;
+  static_assert(D % 4 == 0, "head dim must be a multiple of 4");
   extern __shared__ __align__(16) float mha_sm[];
   float* sq = mha_sm;                  // [QT][LDK]  q * 1/sqrt(D)
   float* sk = sq + QT * LDK;           // [KT][LDK]
@@ -312,6 +316,7 @@ mha_tiled_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict
         for (int kk = 0; kk < 4; ++kk) {
 #pragma unroll
           for (int h = 0; h < NH; ++h) {
+            if ((D4 % 16) != 0 && tx + 16 * h >= D4) continue;
             const float4 vv = *reinterpret_cast<const float4*>(sv + (k + kk) * D + 4 * tx + 64 * h);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -339,6 +344,7 @@ mha_tiled_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict
       const float inv = scorr[4 * ty + i];
 #pragma unroll
       for (int h = 0; h < NH; ++h) {
+        if ((D4 % 16) != 0 && tx + 16 * h >= D4) continue;
         float4 v = make_float4(oacc[i][4 * h] * inv, oacc[i][4 * h + 1] * inv, oacc[i][4 * h + 2] * inv,
                                oacc[i][4 * h + 3] * inv);
         if (round) { v.x = round_tf32(v.x); v.y = round_tf32(v.y); v.z = round_tf32(v.z); v.w = round_tf32(v.w); }
@@ -350,7 +356,7 @@ mha_tiled_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict
 
 template <int D>
 static constexpr int mha_tiled_smem() {
-  constexpr int QT = 64, KT = (D > 64) ? 32 : 64, LDK = D + 4, LDP = KT + 4;
+  constexpr int QT = 64, KT = (D > 64) ? 32 : 64, LDK = D + ((D % 8 == 0) ? 4 : 8), LDP = KT + 4;
   return (QT * LDK + KT * LDK + KT * D + QT * LDP + QT + KT) * 4;
 }
 
@@ -397,22 +403,26 @@ extern "C" int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const i
     else if (d == 128) mha_kernel<128><<<grid, 256, 0, st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
     else return FTB_E_SHAPE;
   } else {
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaError_t ce = cudaFuncSetAttribute(mha_tiled_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            mha_tiled_smem<64>());
-      if (ce == cudaSuccess)
-        ce = cudaFuncSetAttribute(mha_tiled_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  mha_tiled_smem<128>());
-      if (ce != cudaSuccess) return static_cast<int>(ce);
-      attr_set = true;
-    }
     dim3 grid((seq_len + 63) / 64, heads, batch);
-    if (d == 64)
-      mha_tiled_kernel<64><<<grid, 256, mha_tiled_smem<64>(), st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
-    else if (d == 128)
-      mha_tiled_kernel<128><<<grid, 256, mha_tiled_smem<128>(), st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);
-    else return FTB_E_SHAPE;
+    cudaError_t ce = cudaSuccess;
+#define FTB_MHA_CASE(DD)                                                                                          \
+    case DD: {                                                                                                    \
+      static bool attr_##DD = false;                                                                              \
+      if (!attr_##DD) {                                                                                           \
+        ce = cudaFuncSetAttribute(mha_tiled_kernel<DD>, cudaFuncAttributeMaxDynamicSharedMemorySize,              \
+                                  mha_tiled_smem<DD>());                                                          \
+        if (ce != cudaSuccess) return static_cast<int>(ce);                                                       \
+        attr_##DD = true;                                                                                         \
+      }                                                                                                           \
+      mha_tiled_kernel<DD><<<grid, 256, mha_tiled_smem<DD>(), st>>>(qkv, e, key_tok, seq_len, seq_stride, out,    \
+                                                                    round_tf32);                                  \
+      break;                                                                                                      \
+    }
+    switch (d) {          // 64 / 128: FastPitch; 192 / 196 / 256: MultiFastPitch (d_model + speaker [+ cond] dims)
+      FTB_MHA_CASE(64) FTB_MHA_CASE(128) FTB_MHA_CASE(192) FTB_MHA_CASE(196) FTB_MHA_CASE(256)
+      default: return FTB_E_SHAPE;
+    }
+#undef FTB_MHA_CASE
   }
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());

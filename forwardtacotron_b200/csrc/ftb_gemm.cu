@@ -112,7 +112,7 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
 #pragma unroll
       for (int i8 = 0; i8 < 8; ++i8) {
         dst[i8] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (c0 < c.bn && c.n0 + c0 + 4 * part < c.N && ((c.smask >> (i8 * 4 + sub)) & 1u))
+        if (c0 + 4 * part < c.bn && c.n0 + c0 + 4 * part < c.N && ((c.smask >> (i8 * 4 + sub)) & 1u))
           dst[i8] = *reinterpret_cast<const float4*>(rptr + i8 * rstep + c0);
       }
     }
@@ -164,12 +164,12 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
           const float* res = c.residual + c.r * c.res_ld + nb;
 #pragma unroll
           for (int j = 0; j < CHUNK; ++j)
-            if (nb + j < c.N) v[j] += __ldg(res + j);
+            if (c0 + j < c.bn && nb + j < c.N) v[j] += __ldg(res + j);
         }
         float* ot = c.out_t + (static_cast<long long>(c.b) * c.N + nb) * c.seq_len + c.t;
 #pragma unroll
         for (int j = 0; j < CHUNK; ++j)
-          if (nb + j < c.N) ot[static_cast<long long>(j) * c.seq_len] = v[j];
+          if (c0 + j < c.bn && nb + j < c.N) ot[static_cast<long long>(j) * c.seq_len] = v[j];
       }
     }
     if (optr) {
@@ -177,7 +177,8 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
       for (int j = 0; j < CHUNK; j += 4)
         *reinterpret_cast<float4*>(&c.stg[lane][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
       __syncwarp();
-      if (nb + 4 * part < c.N) {                          // N and nb are multiples of 4
+      // a half chunk (bn = 16 mod 32) must not spill into the columns of the next n-tile
+      if (c0 + 4 * part < c.bn && nb + 4 * part < c.N) {  // N, nb and bn are multiples of 4
 #pragma unroll
         for (int i8 = 0; i8 < 8; ++i8) {
           const int row = i8 * 4 + sub;

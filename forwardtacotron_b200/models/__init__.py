@@ -14,4 +14,7 @@ def init_tts_model(config: Dict[str, Any]):
     if kind == 'fast_pitch':
         from .fast_pitch import FastPitch
         return FastPitch.from_config(config)
+    if kind == 'multi_fast_pitch':
+        from .multi_fast_pitch import MultiFastPitch
+        return MultiFastPitch.from_config(config)
     raise ValueError(f'Model type not supported: {kind}')

@@ -427,3 +427,50 @@ def fp_generate(sd: SD, x: torch.Tensor, alpha: float = 1.0,
     mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)
     return {'mel': mel, 'mel_post': mel, 'dur': torch.from_numpy(dur_clamped),
             'pitch': pitch_hat, 'energy': energy_hat, 'mel_lens': torch.from_numpy(lens)}
+
+
+# --------------------------------------------------------------------------
+# MultiFastPitch   (models/multi_fast_pitch.py)
+# --------------------------------------------------------------------------
+
+@torch.no_grad()
+def mfp_generate(sd: SD, x: torch.Tensor, speaker_emb: torch.Tensor, alpha: float = 1.0,
+                 pitch_function=Identity, energy_function=Identity,
+                 pitch_strength: float = 1.0, energy_strength: float = 1.0,
+                 heads: int = 2) -> Dict[str, torch.Tensor]:
+    """MultiFastPitch.generate/_generate_mel, multi_fast_pitch.py:233-305.
+
+    Predictor inputs are concatenations [embedding(x), conditional_embedding(pitch_cond), speaker_emb] (:76-87,
+    :43-48) fed to a ForwardTransformer WITHOUT a pad mask (:242-251); the main branch concatenates the speaker
+    embedding BEFORE the prenet (:277-283, key mask x == 0) and the postnet runs unmasked (:295).
+    Documented deviation (same as MultiForwardTacotron): the reference's
+    `argmax(pitch_cond_hat.squeeze(), dim=1).unsqueeze(0)` (:243) is only well-formed for B = 1; here the arg-max is
+    per (b,t) over the class axis.  'pitch_cond' is returned as [B,T] (== the reference's [1,T] at B = 1).
+    """
+    def plain(p, a=1.0):
+        e = _with_speaker(F.embedding(x, sd[p + '.embedding.weight']), speaker_emb)
+        y = forward_transformer(sd, p + '.transformer', e, heads)
+        return linear(y, sd[p + '.lin.weight'], sd[p + '.lin.bias']) / a
+
+    def conditional(p, cond, a=1.0):
+        e = F.embedding(x, sd[p + '.embedding.weight'])
+        c = F.embedding(cond, sd[p + '.conditional_embedding.weight'])
+        y = forward_transformer(sd, p + '.transformer', _with_speaker(torch.cat([e, c], dim=2), speaker_emb), heads)
+        return linear(y, sd[p + '.lin.weight'], sd[p + '.lin.bias']) / a
+
+    pc_logits = plain('pitch_cond_pred', alpha)                              # [B,T,3]  (:242, divided by alpha)
+    pitch_cond = torch.argmax(pc_logits, dim=-1).long()                      # [B,T]
+    dur_hat = apply_fallback(conditional('dur_pred', pitch_cond, alpha).squeeze(2))
+    pitch_hat = pitch_function(conditional('pitch_pred', pitch_cond).transpose(1, 2))
+    energy_hat = energy_function(plain('energy_pred').transpose(1, 2))
+    key_pad = (x == 0)
+    h = _with_speaker(F.embedding(x, sd['embedding.weight']), speaker_emb)
+    h = forward_transformer(sd, 'prenet', h, heads, key_pad)
+    h = h + cond_projection(sd, 'pitch_proj', pitch_hat) * pitch_strength
+    h = h + cond_projection(sd, 'energy_proj', energy_hat) * energy_strength
+    expanded, _, lens, dur_clamped = length_regulate_np(h.numpy(), dur_hat.numpy())
+    h = forward_transformer(sd, 'postnet', torch.from_numpy(expanded), heads, None)
+    mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)
+    return {'mel': mel, 'mel_post': mel, 'dur': torch.from_numpy(dur_clamped), 'pitch': pitch_hat,
+            'energy': energy_hat, 'pitch_cond': pitch_cond, 'pitch_cond_logits': pc_logits,
+            'mel_lens': torch.from_numpy(lens)}

@@ -121,6 +121,36 @@ def mft_case(name, B, T, seed, patched):
          energy=out['energy'], pitch_cond=out['pitch_cond'])
 
 
+class BatchedMultiFP(MultiFastPitch):
+    """The reference with the ONE B=1-only line (multi_fast_pitch.py:243) replaced by a per-(b,t) arg-max;
+    everything else is the reference's code."""
+
+    def generate(self, x, speaker_emb, alpha=1.0, pitch_function=lambda x: x, energy_function=lambda x: x):
+        self.eval()
+        with torch.no_grad():
+            pitch_cond_hat = self.pitch_cond_pred(x, speaker_emb=speaker_emb, alpha=alpha)
+            pitch_cond_hat = torch.argmax(pitch_cond_hat, dim=-1).long()
+            dur_hat = self.dur_pred(x, x_cond=pitch_cond_hat, speaker_emb=speaker_emb, alpha=alpha).squeeze(2)
+            if torch.sum(dur_hat.long()) <= 0:
+                torch.fill_(dur_hat, value=2.)
+            pitch_hat = pitch_function(self.pitch_pred(x, x_cond=pitch_cond_hat, speaker_emb=speaker_emb).transpose(1, 2))
+            energy_hat = energy_function(self.energy_pred(x, speaker_emb=speaker_emb).transpose(1, 2))
+            return self._generate_mel(x=x, dur_hat=dur_hat, pitch_hat=pitch_hat, energy_hat=energy_hat,
+                                      pitch_cond_hat=pitch_cond_hat, speaker_emb=speaker_emb)
+
+
+def mfp_case(name, B, T, seed, patched, with_pad=False, alpha=1.0):
+    model = build(MultiFastPitch, 'multispeaker.yaml', seed)
+    if patched:
+        model.__class__ = BatchedMultiFP
+    x = synth.synth_tokens(B, T, seed, with_pad=with_pad)
+    semb = synth.synth_speaker_emb(B, 256, seed)
+    out = model.generate(x, semb, alpha=alpha)
+    save(name, x=x, speaker_emb=semb, seed=seed, patched=int(patched), alpha=np.float32(alpha),
+         with_pad=int(with_pad), mel=out['mel'], dur=out['dur'], pitch=out['pitch'], energy=out['energy'],
+         pitch_cond=out['pitch_cond'])
+
+
 def fp_case(name, B, T, seed, with_pad, alpha=1.0):
     model = build(FastPitch, 'singlespeaker.yaml', seed)
     x = synth.synth_tokens(B, T, seed, with_pad=with_pad)
@@ -164,6 +194,11 @@ def cbhg_case():
 
 
 if __name__ == '__main__':
+    if sys.argv[1:] == ['mfp']:          # add the MultiFastPitch fixtures without touching the existing ones
+        with torch.no_grad():
+            mfp_case('mfp_b1_t24', 1, 24, seed=8, patched=False)
+            mfp_case('mfp_pad_b3_t28', 3, 28, seed=9, patched=True, with_pad=True, alpha=1.25)
+        sys.exit(0)
     with torch.no_grad():
         dump_keys()
         lr_cases()
@@ -176,5 +211,7 @@ if __name__ == '__main__':
         mft_case('mft_b3_t32', 3, 32, seed=5, patched=True)
         fp_case('fp_b2_t30', 2, 30, seed=6, with_pad=False)
         fp_case('fp_pad_b3_t36', 3, 36, seed=7, with_pad=True, alpha=1.25)
+        mfp_case('mfp_b1_t24', 1, 24, seed=8, patched=False)
+        mfp_case('mfp_pad_b3_t28', 3, 28, seed=9, patched=True, with_pad=True, alpha=1.25)
     with open(os.path.join(OUT, 'PROVENANCE.txt'), 'w') as f:
         f.write(f'generated by oracle/make_golden.py from {REF}\ntorch {torch.__version__}\n')

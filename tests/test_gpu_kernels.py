@@ -44,6 +44,9 @@ def _conv_ref(x, w, k):
     (2, 70, 80, 256, 4, True),        # even k (asymmetric trim), Cin=80 (K tail zero-filled by TMA)
     (1, 300, 256, 80, 3, False),      # N=80, no ReLU
     (2, 40, 388, 256, 5, True),       # multi-speaker predictor width
+    (2, 40, 392, 1176, 1, False),     # MultiFastPitch in_proj: K tail AND N not a multiple of 16
+    (2, 40, 392, 392, 1, False),      # MultiFastPitch out_proj / conv2 width
+    (1, 70, 392, 128, 9, True),       # MultiFastPitch conv1 (k = 9)
 ])
 def test_conv_bn(B, L, cin, cout, k, relu):
     gen = torch.Generator().manual_seed(B * 1000 + L + k)
@@ -226,3 +229,28 @@ def test_length_regulator_full_size_properties():
     h.lr_scan(d0, B, T, True, cum, lens, meta)
     m = meta.cpu()
     assert int(m[1]) == 1 and int(m[0]) == 2 * T and bool((d0 == 2.0).all())
+
+
+@pytest.mark.parametrize('D,heads,B,L,masked', [(64, 2, 3, 70, True), (128, 2, 2, 130, False), (192, 2, 2, 50, True),
+                                                (196, 2, 2, 77, True), (256, 2, 1, 100, False)])
+def test_mha_matches_torch(D, heads, B, L, masked):
+    """K8 through the C ABI vs torch scaled-dot-product attention in float64 (head dims of FastPitch and
+    MultiFastPitch; key-padding mask = token id 0, common_layers.py:232-233)."""
+    gen = torch.Generator().manual_seed(D + L)
+    E = D * heads
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    qkv, ref = _fill(prog, 'qkv', 3 * E, gen)
+    tok = torch.ones(B, L, dtype=torch.int64)
+    if masked:
+        for b in range(B):
+            tok[b, L - 3 - 5 * b:] = 0
+    tok_d = tok.to(DEV)
+    out = prog.buf('att', E)
+    prog.h.mha(qkv, E, heads, tok_d if masked else None, B, L, prog.geo.stride, out, round_tf32=False)
+    torch.cuda.synchronize()
+    q, k, v = [t.view(B, L, heads, D).transpose(1, 2) for t in ref.chunk(3, dim=-1)]
+    s = q @ k.transpose(-1, -2) / D ** 0.5
+    if masked:
+        s = s.masked_fill((tok == 0)[:, None, None, :], float('-inf'))
+    want = (torch.softmax(s, dim=-1) @ v).transpose(1, 2).reshape(B, L, E)
+    assert max_abs(prog.view('att').cpu().double(), want) < 2e-5

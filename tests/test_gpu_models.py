@@ -28,13 +28,13 @@ def _rounded(d):
     return (torch.as_tensor(d).clamp_min(0) + 0.5).long()
 
 
-def _check_durations(got, ref):
-    """Identical after rounding, except where the reference value sits within 1e-3 of a .5 tie."""
+def _check_durations(got, ref, tie=1e-3):
+    """Identical after rounding, except where the reference value sits within `tie` of a .5 tie."""
     got, ref = torch.as_tensor(got).cpu(), torch.as_tensor(ref).cpu()
     assert max_abs(got, ref) < 2e-3 * max(1.0, float(ref.abs().max()))     # raw values: 2e-3 relative to the range
     diff = _rounded(got) != _rounded(ref)
     frac = (ref.clamp_min(0) + 0.5) % 1.0
-    near_tie = (frac < 1e-3) | (frac > 1 - 1e-3)
+    near_tie = (frac < tie) | (frac > 1 - tie)
     assert not bool((diff & ~near_tie).any()), 'rounded durations differ away from a .5 tie'
     return int(diff.sum())
 
@@ -193,3 +193,52 @@ def test_fast_pitch_rejects_sequences_beyond_positional_table():
     model = _model('fast_pitch', synthetic_sd('fast_pitch', 1))
     with pytest.raises(RuntimeError, match='max_len'):
         model.generate(torch.ones(1, 5001, dtype=torch.int64, device=DEV))
+
+
+@pytest.mark.parametrize('name', ['mfp_b1_t24', 'mfp_pad_b3_t28'])
+def test_multi_fast_pitch_vs_reference_golden(name):
+    """SURVEY §8f "next" row.  mfp_b1_t24 comes from the UNMODIFIED reference (batch 1); mfp_pad_b3_t28 from the
+    reference with the one B=1-only arg-max line generalised (oracle/make_golden.py BatchedMultiFP)."""
+    g = load_golden(name)
+    sd = synthetic_sd('multi_fast_pitch', int(g['seed']))
+    model = _model('multi_fast_pitch', sd)
+    out = model.generate(torch.from_numpy(g['x']).to(DEV), torch.from_numpy(g['speaker_emb']).to(DEV),
+                         alpha=float(g['alpha']))
+    torch.cuda.synchronize()
+    assert set(out) == {'mel', 'mel_post', 'dur', 'pitch', 'energy', 'pitch_cond'}
+    assert out['pitch_cond'].shape == g['pitch_cond'].shape and out['pitch_cond'].dtype == torch.int64
+    assert np.array_equal(out['pitch_cond'].cpu().numpy(), g['pitch_cond'])
+    ties = _check_durations(out['dur'], g['dur'])
+    assert max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3 and max_abs(out['energy'].cpu(), g['energy']) < 5e-3
+    if ties == 0:
+        assert out['mel'].shape == g['mel'].shape
+        assert max_abs(out['mel'].cpu(), g['mel']) < MEL_ABS
+        assert rel_l2(out['mel'].cpu(), g['mel']) < MEL_REL
+
+
+def test_multi_fast_pitch_vs_oracle_batch8():
+    """Fresh seeded cases vs the CPU oracle; the categorical pitch condition may flip only at near ties of the
+    oracle's top-2 logits, mel parity is asserted on every case without a flip or a duration tie."""
+    compared = 0
+    for seed in (11, 12, 13):
+        sd = synthetic_sd('multi_fast_pitch', seed)
+        model = _model('multi_fast_pitch', sd)
+        x = synth.synth_tokens(8, 48, seed=seed, with_pad=True)
+        semb = synth.synth_speaker_emb(8, 256, seed=seed)
+        ref = O.mfp_generate(sd, x, semb, alpha=0.9)
+        out = model.generate(x.to(DEV), semb.to(DEV), alpha=0.9)
+        torch.cuda.synchronize()
+        flips = out['pitch_cond'].cpu() != ref['pitch_cond']
+        top2 = ref['pitch_cond_logits'].topk(2, dim=-1).values
+        margin = top2[..., 0] - top2[..., 1]
+        assert not bool((flips & (margin > 1e-2)).any()), 'pitch condition differs away from a near tie'
+        if bool(flips.any()):
+            continue
+        # raw durations of the 4-layer FFT predictors (values up to ~7 frames at alpha 0.9) carry up to 1.3e-3
+        # RELATIVE error at tf32 (scratch/debug_mfp2.py: max-abs 8e-3): a "documented .5 tie" here is a reference
+        # value closer to the rounding boundary than the raw-value tolerance _check_durations itself allows
+        tie = 2e-3 * max(1.0, float(ref['dur'].abs().max()))
+        if _check_durations(out['dur'], ref['dur'], tie=tie) == 0:
+            compared += 1
+            assert max_abs(out['mel'].cpu(), ref['mel']) < MEL_ABS and rel_l2(out['mel'].cpu(), ref['mel']) < MEL_REL
+    assert compared >= 1

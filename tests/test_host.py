@@ -51,7 +51,7 @@ def test_struct_layout_matches_header(tmp_path):
             assert getattr(ct, f).offset == off, (cname, f)
 
 
-@pytest.mark.parametrize('tag', ['forward_tacotron', 'multi_forward_tacotron', 'fast_pitch'])
+@pytest.mark.parametrize('tag', ['forward_tacotron', 'multi_forward_tacotron', 'fast_pitch', 'multi_fast_pitch'])
 def test_state_dict_contract(tag):
     model = init_tts_model(default_config(tag))
     want = key_table(tag)

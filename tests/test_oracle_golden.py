@@ -105,3 +105,17 @@ def test_fast_pitch_generate(name):
     for k in ('mel', 'pitch', 'energy', 'dur'):
         assert max_abs(out[k], g[k]) < 2e-4, k
         assert rel_l2(out[k], g[k]) < 5e-5, k
+
+
+@pytest.mark.parametrize('name', ['mfp_b1_t24', 'mfp_pad_b3_t28'])
+def test_multi_fast_pitch_generate(name):
+    """MultiFastPitch oracle vs the reference (batch 1: unmodified reference; batch 3: the reference with the one
+    batch-1-only arg-max line generalised, oracle/make_golden.py::BatchedMultiFP)."""
+    g = load_golden(name)
+    sd = synthetic_sd('multi_fast_pitch', int(g['seed']))
+    out = O.mfp_generate(sd, torch.from_numpy(g['x']), torch.from_numpy(g['speaker_emb']), alpha=float(g['alpha']))
+    assert out['mel'].shape == g['mel'].shape
+    assert np.array_equal(out['pitch_cond'].numpy(), g['pitch_cond'])
+    for k in ('mel', 'pitch', 'energy', 'dur'):
+        assert max_abs(out[k], g[k]) < 2e-4, k
+        assert rel_l2(out[k], g[k]) < 5e-5, k
