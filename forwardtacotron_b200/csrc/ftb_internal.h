@@ -54,6 +54,8 @@ struct RnnProblemDev {
   const float* b_hh;
   float* out;
   __half* hx;            // fp16 exchange tensor [2][seq_len][batch][hidden], sentinel-armed before each run
+  const int* lens;       // optional [batch] valid lengths (packed-sequence semantics) or null
+  float pad_value;       // value of out[b, t >= lens[b]]
   int cell, hidden, batch, seq_len, seq_stride, out_ld, out_col0;
   int gates;             // 3 or 4
   int units_per_cta;     // hidden units owned by one CTA

@@ -244,12 +244,16 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   // gate math (fp32), state update and publication of h_t for this thread's pair (threads of group g only).
   // The partial-sum tiles start zeroed, so step 0 (h_{-1} = 0, no MMA) needs no special case.
   const long long o_step = dir ? -static_cast<long long>(p.out_ld) : static_cast<long long>(p.out_ld);
+  // packed-sequence semantics (optional): this pair's sentence is live for t < len_b only
+  const int len_b = (p.lens && pv) ? min(p.lens[b0 + pb], L) : L;
+  const float pad_value = p.pad_value;
   float* out_p = out_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.out_ld;
   __half* hx_p = hx_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.batch * H;
   const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
   const float* xs0 = x_s + pb * XSTR + pu;
   auto gate_group = [&](int step) {
     float hnew = 0.0f;
+    bool dead = false;
     if (pv) {
       const float* xs = xs0 + (step & (RNN_XS - 1)) * (NB * XSTR);
       float hh[G];
@@ -273,7 +277,10 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         const float n = tanh_fast(xs[2 * U] + r * hh[2]);
         hnew = (1.0f - z) * n + z * h_state;
       }
+      const bool live = (dir ? (L - 1 - step) : step) < len_b;
+      if (!live) { hnew = 0.0f; c_state = 0.0f; }     // zero state until the backward pass reaches len_b - 1
       h_state = hnew;
+      dead = !live;
     }
     // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
     const __half h16 = __float2half_rn(hnew);
@@ -281,7 +288,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
     if (pv) {
       if ((lane & 1) == 0) st_relaxed_u32(hx_p, mine | (other << 16));
-      *out_p = __half2float(h16);
+      *out_p = dead ? pad_value : __half2float(h16);
     }
     out_p += o_step;
     hx_p += h_step;
@@ -413,6 +420,7 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       const int take = want < room ? want : room;
       RnnProblemDev d{};
       d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = static_cast<__half*>(hx);
+      d.lens = q.lens; d.pad_value = q.pad_value;
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
       d.gates = q.cell == FTB_CELL_LSTM ? 4 : 3;

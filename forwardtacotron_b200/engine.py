@@ -111,8 +111,9 @@ class Program:
             self.info.append({'kind': 'gemm', 'label': '+'.join(l for l in labels if l) or 'gemm',
                               'flops': flops, 'bytes': nbytes, 'problems': len(grp)})
 
-    def rnn(self, specs):
-        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one cooperative launch."""
+    def rnn(self, specs, lens: Optional[torch.Tensor] = None, pad_value: float = 0.0):
+        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one cooperative launch.
+        `lens` (int32 [batch], device): packed-sequence semantics for every problem of the launch."""
         self.flush()
         g = self.geo
         probs = []
@@ -122,8 +123,9 @@ class Program:
             p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
             p.xproj, p.w_hh, p.b_hh = xproj.data_ptr(), r.w_hh.data_ptr(), r.b_hh.data_ptr()
             p.out, p.out_ld, p.out_col0 = out.data_ptr(), out.shape[1], col0
+            p.lens, p.pad_value = (lens.data_ptr() if lens is not None else None), float(pad_value)
             probs.append(p)
-            self._keep += [r, xproj, out]
+            self._keep += [r, xproj, out] + ([lens] if lens is not None else [])
         plan = self.h.rnn_plan(probs)
         self._rnn_plans.append(plan)
         self.steps.append(lambda plan=plan: self.h.rnn_run(plan))

@@ -131,6 +131,11 @@ typedef struct {
   const float* b_hh;     /* [2][g*H]                                                         */
   float* out;            /* [batch*seq_stride, out_ld]; fwd h at out_col0, bwd at out_col0+H; fp16-exact values */
   int32_t out_ld, out_col0;
+  const int32_t* lens;   /* optional [batch] valid lengths: pack_padded_sequence / pad_packed_sequence semantics
+                            (forward_tacotron.py:147-152) -- sentence b runs over t < lens[b] only (the backward
+                            direction starts at lens[b]-1 from a zero state) and out[b, t >= lens[b]] = pad_value;
+                            null = every sentence runs over all seq_len steps (the generate() path)             */
+  float pad_value;
 } ftb_rnn_problem;
 
 #define FTB_MAX_RNN_PROBLEMS 8

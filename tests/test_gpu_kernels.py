@@ -172,6 +172,42 @@ def test_recurrence(cell, H, B, L):
     assert torch.equal(prog.view('h').cpu(), got)
 
 
+@pytest.mark.parametrize('cell,H,B,L', [('gru', 128, 5, 33), ('lstm', 512, 19, 27)])
+def test_recurrence_packed_sequence_semantics(cell, H, B, L):
+    """`lens` != null: pack_padded_sequence -> RNN -> pad_packed_sequence(padding_value) of forward_tacotron.py:147-152
+    (each sentence runs over its own length, the backward direction starts at len-1, the tail holds the pad value),
+    against torch's packed-sequence RNN in fp32."""
+    from torch.nn.utils.rnn import pack_padded_sequence, pad_packed_sequence
+    gen = torch.Generator().manual_seed(H + B + 1)
+    In, pad = 64, -11.5129
+    rnn = (torch.nn.GRU if cell == 'gru' else torch.nn.LSTM)(In, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    lens = torch.randint(1, L + 1, (B,), generator=gen)
+    lens[0] = L                                          # pad_packed_sequence pads to the longest sentence
+    a_cpu = pk.round_tf32(torch.randn(B, L, In, generator=gen))
+    with torch.no_grad():
+        y, _ = rnn(pack_padded_sequence(a_cpu, lens, batch_first=True, enforce_sorted=False))
+        ref, _ = pad_packed_sequence(y, batch_first=True, padding_value=pad)
+    packed = pk.PackedRnn(rnn.to(DEV))
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    a = prog.buf('x', In)
+    a.view(B, prog.geo.stride, In)[:, :L] = a_cpu.to(DEV)
+    xp = prog.buf('xp', packed.ih.n)
+    out = prog.buf('h', 2 * H)
+    lens_d = lens.to(torch.int32).to(DEV)
+    prog.gemm(a, packed.ih, xp, round_out=False)
+    prog.rnn([(packed, xp, out, 0)], lens=lens_d, pad_value=pad)
+    prog.run()
+    torch.cuda.synchronize()
+    got = prog.view('h').cpu()
+    assert got.shape == ref.shape
+    mask = torch.arange(L)[None, :] >= lens[:, None]
+    assert bool((got[mask] == torch.tensor(pad)).all())                      # the tail is exactly the pad value
+    assert max_abs(got[~mask], ref[~mask]) < 3e-3                            # tf32 x-projection + fp16 recurrent operands
+
+
 @pytest.mark.parametrize('tag', ['all2', 'ties', 'zero_row'])
 def test_length_regulator_bit_exact_golden(tag):
     g = load_golden(f'lr_{tag}')

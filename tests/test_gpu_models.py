@@ -242,3 +242,32 @@ def test_multi_fast_pitch_vs_oracle_batch8():
             compared += 1
             assert max_abs(out['mel'].cpu(), ref['mel']) < MEL_ABS and rel_l2(out['mel'].cpu(), ref['mel']) < MEL_REL
     assert compared >= 1
+
+
+def test_batched_caller_matches_oracle_per_bucket():
+    """sentences of different lengths through forwardtacotron_b200.batching; every bucket is
+    checked against the oracle (= the reference) applied to the same zero-padded bucket, un-padded per sentence."""
+    from forwardtacotron_b200 import batching as bt
+    sd = synthetic_sd('forward_tacotron', 2)
+    model = _model('forward_tacotron', sd)
+    g = torch.Generator().manual_seed(3)
+    seqs = [torch.randint(1, 135, (n,), generator=g).tolist() for n in (30, 24, 31, 9, 10, 29)]
+    mels = bt.synthesize_batched(model, seqs, max_batch=4, device=DEV, max_len_ratio=1.3)
+    lens = [len(s) for s in seqs]
+    compared = 0
+    for bucket in bt.bucket_by_length(lens, 4, 1.3):
+        x = bt.pad_tokens([seqs[i] for i in bucket])
+        O.use_library_rnn(True)
+        try:
+            ref = O.ft_generate(sd, x)
+        finally:
+            O.use_library_rnn(False)
+        frames = bt.own_frames(ref['dur'], [lens[i] for i in bucket])
+        for b, i in enumerate(bucket):
+            if mels[i].shape[2] != frames[b]:
+                continue                                   # a duration tie moved a frame: skip this sentence
+            want = ref['mel_post'][b:b + 1, :, :frames[b]]
+            assert mels[i].shape == tuple(want.shape)
+            assert max_abs(mels[i], want) < MEL_ABS and rel_l2(mels[i], want) < MEL_REL
+            compared += 1
+    assert compared >= 4
