@@ -74,9 +74,12 @@ class AcceleratedMixin:
             raise RuntimeError(f'generate(): x must be int64 [batch, tokens], got {x.dtype} {tuple(x.shape)}')
 
 
-def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_channels: int, n_mels: int):
+def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_channels: int, n_mels: int,
+                        packed_pad_value: Optional[float] = None):
     """LR output [B,M,C] -> BiLSTM -> lin -> CBHG postnet -> post_proj
-    (forward_tacotron.py:224-231).  Returns the Program; the LR gather writes prog.buf('lr')."""
+    (forward_tacotron.py:224-231).  Returns the Program; the LR gather writes prog.buf('lr').
+    `packed_pad_value` != None: the BiLSTM runs with pack_padded_sequence semantics over the int32 lengths the
+    caller writes into prog.bufs['mel_len'] (eval-mode forward(batch), forward_tacotron.py:147-152)."""
     geo = eng.Geometry(batch, M)
     prog = eng.Program(handle, geo)
     lstm: pk.PackedRnn = packs['lstm']
@@ -91,11 +94,33 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     prog.label('lstm_ih')
     prog.gemm(x, lstm.ih, xp, round_out=False)                    # W_ih half of self.lstm (:224)
     prog.label('lstm')
-    prog.rnn([(lstm, xp, hl, 0)])
+    if packed_pad_value is None:
+        prog.rnn([(lstm, xp, hl, 0)])
+    else:
+        mel_len = prog.dense('mel_len', (batch,), torch.int32)
+        # the padded rows feed the `lin` GEMM: keep the pad value tf32-exact like every other operand
+        prog.rnn([(lstm, xp, hl, 0)], lens=mel_len, pad_value=float(pk.round_tf32(torch.tensor([packed_pad_value]))[0]))
     prog.label('lin')
     mel_full = prog.buf('mel_cl_full', n_mels)
     prog.gemm(hl, packs['lin'], mel_cl, out_t=mel, out_full=mel_full)   # self.lin + transpose (:226-227)
     prog.flush()
+    if packed_pad_value is not None:
+        # Rows behind a packed sentence hold lin(padding vector): 1024 identical operands, so the tf32 rounding of
+        # the pad value is a SYSTEMATIC error (2.4e-4 relative on values of magnitude ~30) that the postnet's bank
+        # and BiGRU carry into the valid frames.  Overwrite those rows with the exact fp32 vector instead.
+        g = prog.geo
+        v = packs['lin_pad_vec']
+        v_r = pk.round_tf32(v)
+        t_idx = torch.arange(g.stride, device=mel_cl.device, dtype=torch.int32)
+
+        def fix_pad_rows():
+            m = ((t_idx[None, :] >= mel_len[:, None]) & (t_idx[None, :] < M))        # [B, stride]
+            cl = mel_cl.view(batch, g.stride, n_mels)
+            clf = mel_full.view(batch, g.stride, n_mels)
+            torch.where(m[:, :, None], v_r, cl, out=cl)
+            torch.where(m[:, :, None], v, clf, out=clf)
+            torch.where(m[:, None, :M], v[None, :, None], mel, out=mel)
+        prog.call(fix_pad_rows, label='lin.pad_rows')
     prog.label('')
     levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full)
     eng.run_levels(prog, [levels])

@@ -92,6 +92,9 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         target_len = batch['mel'].size(2)
         if self.training:
             self.step += 1
+        if not self.training and x.is_cuda and not torch.is_grad_enabled():
+            return self._forward_eval(batch)               # the GTA-dump / evaluation use (train_forward.py:33-51)
+
         dur_hat = self.dur_pred(x).squeeze(-1)
         pitch_hat = self.pitch_pred(x).transpose(1, 2)
         energy_hat = self.energy_pred(x).transpose(1, 2)
@@ -124,6 +127,9 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             'prenet': _accel.pack_cbhg(self.prenet),
             'lstm': pk.PackedRnn(self.lstm),
             'lin': pk.pack_linear(self.lin.weight, self.lin.bias),
+            # lin(padding vector) in exact fp32: the mel rows behind a packed sentence (eval-mode forward only)
+            'lin_pad_vec': (self.lin.weight.detach().float().sum(dim=1) * float(self.padding_value)
+                            + self.lin.bias.detach().float()).contiguous(),
             'postnet': _accel.pack_cbhg(self.postnet),
             'post_proj': pk.pack_linear(self.post_proj.weight),
             'pitch_proj': (self.pitch_proj.weight.detach().float().reshape(-1, 3).contiguous(),
@@ -191,6 +197,39 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             pitch_hat = pitch_function(prog.bufs['pitch.y'].clone().unsqueeze(1))       # [B,1,T]
             energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
+
+    def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """forward(batch) in eval mode under no_grad on the sm_100a kernels (forward_tacotron.py:118-165):
+        predictors for the returned dur/pitch/energy, teacher-forced durations / pitch / energy for the mel branch,
+        packed-sequence BiLSTM over batch['mel_len'] (tail = padding_value), outputs padded to the target length."""
+        x = batch['x']
+        self._check_tokens(x)
+        st = self._accel_state(x.device)
+        B, T = x.shape
+        tok = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True, True))
+        tok.bufs['tok'].copy_(x)
+        tok.alpha = 1.0
+        tok.run()
+        dur_hat = tok.bufs['dur.y'].clone()
+        pitch_hat = tok.bufs['pitch.y'].clone().unsqueeze(1)
+        energy_hat = tok.bufs['energy.y'].clone().unsqueeze(1)
+        dur = batch['dur'].to(device=x.device, dtype=torch.float32).contiguous().clone()
+        cum, lens, M_lr, _ = _accel.length_regulate(st['handle'], dur, apply_fallback=False)
+        mel_len = batch['mel_len'].to(device=x.device, dtype=torch.int32).contiguous()
+        M = int(mel_len.max())
+        if M < 1 or M > M_lr or int(mel_len.min()) < 1:
+            raise RuntimeError(f'forward(): mel_len must lie in [1, {M_lr}] (the regulated length), as '
+                               'pack_padded_sequence requires (forward_tacotron.py:147)')
+        pre = tok.bufs['prenet.h']
+        prog = self._program(st, ('frame_packed', B, M), lambda: _accel.build_frame_program(
+            st['handle'], st['packs'], B, M, pre.shape[1], self.n_mels, packed_pad_value=float(self.padding_value)))
+        prog.bufs['mel_len'].copy_(mel_len)
+        out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, pre, None, 0, dur,
+                                           batch['pitch'].to(x.device), batch['energy'].to(x.device), cum, lens, M,
+                                           float(self.pitch_strength), float(self.energy_strength))
+        target_len = batch['mel'].size(2)
+        return {'mel': self._pad(out['mel'], target_len), 'mel_post': self._pad(out['mel_post'], target_len),
+                'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat}
 
     def _generate_mel(self, x: torch.Tensor, dur_hat: torch.Tensor, pitch_hat: torch.Tensor,
                       energy_hat: torch.Tensor) -> Dict[str, torch.Tensor]:

@@ -98,3 +98,24 @@ def synth_speaker_emb(batch: int, dims: int = 256, seed: int = 0) -> torch.Tenso
     g = _gen(f'semb/{batch}x{dims}', seed)
     e = torch.randn((batch, dims), generator=g)
     return e / e.norm(dim=1, keepdim=True)
+
+
+def synth_batch(batch: int, length: int, seed: int = 0, n_mels: int = 80, speaker_dims: int = 0) -> dict:
+    """A collated training-style batch (utils/dataset.py:239-263 layout) for `forward(batch)` in eval mode: ragged
+    token lengths (zero padded), integer durations (0 on the padding), mel_len = sum of durations, per-token
+    pitch / energy, and a mel target whose only used property is its length."""
+    g = _gen(f'batch/{batch}x{length}', seed)
+    x = torch.randint(1, 135, (batch, length), generator=g, dtype=torch.int64)
+    dur = torch.randint(0, 5, (batch, length), generator=g).to(torch.float32)
+    for b in range(batch):
+        keep = length - (b * 5) % max(1, length // 2)
+        x[b, keep:] = 0
+        dur[b, keep:] = 0
+        dur[b, 0] = max(float(dur[b, 0]), 1.0)
+    mel_len = dur.sum(dim=1).long()
+    out = {'x': x, 'dur': dur, 'mel_len': mel_len,
+           'pitch': torch.randn((batch, length), generator=g), 'energy': torch.randn((batch, length), generator=g),
+           'mel': torch.zeros((batch, n_mels, int(mel_len.max()) + 3))}
+    if speaker_dims:
+        out['speaker_emb'] = synth_speaker_emb(batch, speaker_dims, seed)
+    return out

@@ -302,6 +302,45 @@ def ft_generate(sd: SD, x: torch.Tensor, alpha: float = 1.0,
                            pitch_strength, energy_strength, taps)
 
 
+@torch.no_grad()
+def packed_bi_rnn(sd: SD, p: str, x: torch.Tensor, lens: torch.Tensor, kind: str, pad_value: float) -> torch.Tensor:
+    """pack_padded_sequence -> bidirectional RNN -> pad_packed_sequence(padding_value) (forward_tacotron.py:147-152):
+    every sentence runs over its own `lens[b]` steps (the backward direction starts at lens[b]-1 from a zero state);
+    the result is padded to max(lens) with `pad_value`."""
+    B, H2 = x.shape[0], 2 * sd[p + '.weight_hh_l0'].shape[1]
+    M = int(lens.max())
+    out = torch.full((B, M, H2), float(pad_value), dtype=torch.float32)
+    for b in range(B):
+        n = int(lens[b])
+        out[b, :n] = bi_rnn(sd, p, x[b:b + 1, :n], kind)[0]
+    return out
+
+
+@torch.no_grad()
+def ft_forward(sd: SD, batch: Dict[str, torch.Tensor], pitch_strength: float = 1.0, energy_strength: float = 1.0,
+               padding_value: float = -11.5129) -> Dict[str, torch.Tensor]:
+    """ForwardTacotron.forward(batch) in eval mode (forward_tacotron.py:118-165): teacher-forced durations / pitch /
+    energy, packed-sequence BiLSTM over `mel_len`, outputs padded to the target mel length with `padding_value`."""
+    x = batch['x']
+    def pred(p):
+        return series_predictor(sd, p, F.embedding(x, sd[p + '.embedding.weight']))
+    dur_hat = pred('dur_pred').squeeze(-1)
+    pitch_hat = pred('pitch_pred').transpose(1, 2)
+    energy_hat = pred('energy_pred').transpose(1, 2)
+    h = cbhg(sd, 'prenet', F.embedding(x, sd['embedding.weight']).transpose(1, 2))
+    h = h + cond_projection(sd, 'pitch_proj', batch['pitch'].unsqueeze(1)) * pitch_strength
+    h = h + cond_projection(sd, 'energy_proj', batch['energy'].unsqueeze(1)) * energy_strength
+    expanded, _, _, _ = length_regulate_np(h.numpy(), batch['dur'].to(torch.float32).numpy().copy())
+    h = packed_bi_rnn(sd, 'lstm', torch.from_numpy(expanded), batch['mel_len'], 'lstm', padding_value)
+    mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)
+    mel_post = linear(cbhg(sd, 'postnet', mel), sd['post_proj.weight']).transpose(1, 2)
+    target = batch['mel'].shape[2]
+    def pad(t):
+        t = t[:, :, :target]
+        return F.pad(t, [0, target - t.shape[2], 0, 0], 'constant', padding_value)
+    return {'mel': pad(mel), 'mel_post': pad(mel_post), 'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat}
+
+
 # --------------------------------------------------------------------------
 # MultiForwardTacotron   (models/multi_forward_tacotron.py)
 # --------------------------------------------------------------------------

@@ -121,6 +121,15 @@ def mft_case(name, B, T, seed, patched):
          energy=out['energy'], pitch_cond=out['pitch_cond'])
 
 
+def ft_forward_case(name, B, T, seed):
+    """ForwardTacotron.forward(batch) in eval mode (the GTA feature dump path, train_forward.py:33-51)."""
+    model = build(ForwardTacotron, 'singlespeaker.yaml', seed)
+    batch = synth.synth_batch(B, T, seed)
+    out = model(batch)
+    save(name, seed=seed, B=B, T=T, mel=out['mel'], mel_post=out['mel_post'], dur=out['dur'], pitch=out['pitch'],
+         energy=out['energy'])
+
+
 class BatchedMultiFP(MultiFastPitch):
     """The reference with the ONE B=1-only line (multi_fast_pitch.py:243) replaced by a per-(b,t) arg-max;
     everything else is the reference's code."""
@@ -194,6 +203,10 @@ def cbhg_case():
 
 
 if __name__ == '__main__':
+    if sys.argv[1:] == ['ftfwd']:        # eval-mode forward(batch) fixtures only
+        with torch.no_grad():
+            ft_forward_case('ft_forward_b4_t26', 4, 26, seed=10)
+        sys.exit(0)
     if sys.argv[1:] == ['mfp']:          # add the MultiFastPitch fixtures without touching the existing ones
         with torch.no_grad():
             mfp_case('mfp_b1_t24', 1, 24, seed=8, patched=False)
@@ -213,5 +226,6 @@ if __name__ == '__main__':
         fp_case('fp_pad_b3_t36', 3, 36, seed=7, with_pad=True, alpha=1.25)
         mfp_case('mfp_b1_t24', 1, 24, seed=8, patched=False)
         mfp_case('mfp_pad_b3_t28', 3, 28, seed=9, patched=True, with_pad=True, alpha=1.25)
+        ft_forward_case('ft_forward_b4_t26', 4, 26, seed=10)
     with open(os.path.join(OUT, 'PROVENANCE.txt'), 'w') as f:
         f.write(f'generated by oracle/make_golden.py from {REF}\ntorch {torch.__version__}\n')

@@ -119,3 +119,19 @@ def test_multi_fast_pitch_generate(name):
     for k in ('mel', 'pitch', 'energy', 'dur'):
         assert max_abs(out[k], g[k]) < 2e-4, k
         assert rel_l2(out[k], g[k]) < 5e-5, k
+
+
+def test_forward_tacotron_eval_forward():
+    """forward(batch) in eval mode (teacher forcing + packed-sequence BiLSTM, forward_tacotron.py:118-165)."""
+    from forwardtacotron_b200 import synth
+    g = load_golden('ft_forward_b4_t26')
+    sd = synthetic_sd('forward_tacotron', int(g['seed']))
+    batch = synth.synth_batch(int(g['B']), int(g['T']), int(g['seed']))
+    O.use_library_rnn(True)
+    try:
+        out = O.ft_forward(sd, batch)
+    finally:
+        O.use_library_rnn(False)
+    for k in ('mel', 'mel_post', 'dur', 'pitch', 'energy'):
+        assert out[k].shape == g[k].shape, k
+        assert max_abs(out[k], g[k]) < 2e-4, k
