@@ -105,63 +105,98 @@ struct GatherArgs {
   ftb_lr_gather_args a;
 };
 
-// One warp per output row (b, m).
+// Source-centric expansion: one warp per TOKEN (b, t).  The token's row (and the speaker tail) is read once, the
+// pitch / energy projection add is evaluated once (reference operation order, no contraction across the adds,
+// forward_tacotron.py:214-220), and the result is stored to the token's frames m in [cum[t-1], cum[t]) -- no binary
+// search, no per-frame re-evaluation.  The per-channel projection coefficients are staged once per (persistent) block
+// in shared memory as [8][C] = wp0, wp1, wp2, bp, we0, we1, we2, be.  Blocks past the token range zero-fill the tail
+// rows m >= lens[b] of one sentence each (pad_sequence(padding_value=0.), common_layers.py:23).
+constexpr int LR_MAX_GROUPS = 8;          // float4 channel groups per lane: C <= 1024
+
 __global__ void __launch_bounds__(256)
-lr_gather_kernel(const GatherArgs g) {
+lr_gather_kernel(const GatherArgs g, int token_blocks) {
+  extern __shared__ __align__(16) float coef[];
   const ftb_lr_gather_args& a = g.a;
-  const int lane = threadIdx.x & 31;
-  const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
-  if (row >= static_cast<long long>(a.batch) * a.M) return;
-  const int b = static_cast<int>(row / a.M);
-  const int m = static_cast<int>(row - static_cast<long long>(b) * a.M);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int C = a.c1 + a.c2;
-  float* o = a.out + (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
-  const int len = a.lens[b];
-  if (m >= len) {                                   // pad_sequence(padding_value=0.)
-    for (int c = lane * 4; c < C; c += 128) *reinterpret_cast<float4*>(o + c) = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (a.idx && lane == 0) a.idx[row] = -1;
+  if (static_cast<int>(blockIdx.x) >= token_blocks) {
+    // ---- zero tail of sentence b
+    const int b = blockIdx.x - token_blocks;
+    const int len = min(a.lens[b], a.M);
+    for (int m = len + warp; m < a.M; m += 8) {
+      float* o = a.out + (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
+      for (int c = lane * 4; c < C; c += 128) *reinterpret_cast<float4*>(o + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (a.idx && lane == 0) a.idx[static_cast<long long>(b) * a.M + m] = -1;
+    }
     return;
   }
-  // searchsorted(cum, m, right): first t with cum[t] > m
-  const int32_t* cum = a.cum + static_cast<long long>(b) * a.T;
-  int lo = 0, hi = a.T - 1;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (__ldg(cum + mid) > m) hi = mid; else lo = mid + 1;
-  }
-  const int t = lo;
-  if (a.idx && lane == 0) a.idx[row] = t;
-
-  const float* xs = a.x + (static_cast<long long>(b) * a.x_stride + t) * a.x_ld;
-  float pm = 0.f, p0 = 0.f, pp = 0.f, em = 0.f, e0 = 0.f, ep = 0.f;
   const bool proj = (a.pitch != nullptr);
   if (proj) {
-    const float* pr = a.pitch + static_cast<long long>(b) * a.T;
-    const float* er = a.energy + static_cast<long long>(b) * a.T;
-    p0 = pr[t]; e0 = er[t];
-    if (t > 0) { pm = pr[t - 1]; em = er[t - 1]; }
-    if (t + 1 < a.T) { pp = pr[t + 1]; ep = er[t + 1]; }
+    for (int i = threadIdx.x; i < C; i += 256) {
+      coef[0 * C + i] = a.wp[i * 3 + 0]; coef[1 * C + i] = a.wp[i * 3 + 1]; coef[2 * C + i] = a.wp[i * 3 + 2];
+      coef[3 * C + i] = a.bp[i];
+      coef[4 * C + i] = a.we[i * 3 + 0]; coef[5 * C + i] = a.we[i * 3 + 1]; coef[6 * C + i] = a.we[i * 3 + 2];
+      coef[7 * C + i] = a.be[i];
+    }
+    __syncthreads();
   }
-  for (int c = lane * 4; c < C; c += 128) {
-    float4 v;
-    if (c < a.c1) v = *reinterpret_cast<const float4*>(xs + c);
-    else v = *reinterpret_cast<const float4*>(a.extra + static_cast<long long>(b) * a.c2 + (c - a.c1));
+  const long long ntok = static_cast<long long>(a.batch) * a.T;
+  for (long long tokid = blockIdx.x * 8ll + warp; tokid < ntok; tokid += static_cast<long long>(token_blocks) * 8) {
+    const int b = static_cast<int>(tokid / a.T);
+    const int t = static_cast<int>(tokid - static_cast<long long>(b) * a.T);
+    const int32_t* cum = a.cum + static_cast<long long>(b) * a.T;
+    const int m0 = t > 0 ? cum[t - 1] : 0;
+    const int m1 = min(cum[t], a.M);
+    if (m1 <= m0) continue;                            // duration 0 (or beyond M): the token has no frame
+    const float* xs = a.x + (static_cast<long long>(b) * a.x_stride + t) * a.x_ld;
+    float pm = 0.f, p0 = 0.f, pp = 0.f, em = 0.f, e0 = 0.f, ep = 0.f;
     if (proj) {
-      float* vv = reinterpret_cast<float*>(&v);
+      const float* pr = a.pitch + static_cast<long long>(b) * a.T;
+      const float* er = a.energy + static_cast<long long>(b) * a.T;
+      p0 = pr[t]; e0 = er[t];
+      if (t > 0) { pm = pr[t - 1]; em = er[t - 1]; }
+      if (t + 1 < a.T) { pp = pr[t + 1]; ep = er[t + 1]; }
+    }
+    float4 v[LR_MAX_GROUPS];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float* wp = a.wp + (c + j) * 3;
-        const float* we = a.we + (c + j) * 3;
-        // Conv1d(1->C, k=3, pad=1) + bias, scaled add (forward_tacotron.py:214-220)
-        const float pc = __fadd_rn(__fmaf_rn(wp[2], pp, __fmaf_rn(wp[1], p0, __fmul_rn(wp[0], pm))), a.bp[c + j]);
-        const float ec = __fadd_rn(__fmaf_rn(we[2], ep, __fmaf_rn(we[1], e0, __fmul_rn(we[0], em))), a.be[c + j]);
-        vv[j] = __fadd_rn(__fadd_rn(vv[j], __fmul_rn(pc, a.ps)), __fmul_rn(ec, a.es));
+    for (int q = 0; q < LR_MAX_GROUPS; ++q) {
+      const int c = lane * 4 + q * 128;
+      if (c < C) {
+        if (c < a.c1) v[q] = *reinterpret_cast<const float4*>(xs + c);
+        else v[q] = *reinterpret_cast<const float4*>(a.extra + static_cast<long long>(b) * a.c2 + (c - a.c1));
+        if (proj) {
+          const float4 w0 = *reinterpret_cast<const float4*>(coef + 0 * C + c);
+          const float4 w1 = *reinterpret_cast<const float4*>(coef + 1 * C + c);
+          const float4 w2 = *reinterpret_cast<const float4*>(coef + 2 * C + c);
+          const float4 wb = *reinterpret_cast<const float4*>(coef + 3 * C + c);
+          const float4 u0 = *reinterpret_cast<const float4*>(coef + 4 * C + c);
+          const float4 u1 = *reinterpret_cast<const float4*>(coef + 5 * C + c);
+          const float4 u2 = *reinterpret_cast<const float4*>(coef + 6 * C + c);
+          const float4 ub = *reinterpret_cast<const float4*>(coef + 7 * C + c);
+          // Conv1d(1->C, k=3, pad=1) + bias, scaled add (forward_tacotron.py:214-220)
+#define FTB_LR_PROJ(X)                                                                                               \
+          {                                                                                                          \
+            const float pc = __fadd_rn(__fmaf_rn(w2.X, pp, __fmaf_rn(w1.X, p0, __fmul_rn(w0.X, pm))), wb.X);         \
+            const float ec = __fadd_rn(__fmaf_rn(u2.X, ep, __fmaf_rn(u1.X, e0, __fmul_rn(u0.X, em))), ub.X);         \
+            v[q].X = __fadd_rn(__fadd_rn(v[q].X, __fmul_rn(pc, a.ps)), __fmul_rn(ec, a.es));                         \
+          }
+          FTB_LR_PROJ(x) FTB_LR_PROJ(y) FTB_LR_PROJ(z) FTB_LR_PROJ(w)
+#undef FTB_LR_PROJ
+        }
+        if (a.round_tf32) {
+          v[q].x = round_tf32(v[q].x); v[q].y = round_tf32(v[q].y); v[q].z = round_tf32(v[q].z); v[q].w = round_tf32(v[q].w);
+        }
       }
     }
-    if (a.round_tf32) {
-      v.x = round_tf32(v.x); v.y = round_tf32(v.y); v.z = round_tf32(v.z); v.w = round_tf32(v.w);
+    for (int m = m0; m < m1; ++m) {
+      float* o = a.out + (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
+#pragma unroll
+      for (int q = 0; q < LR_MAX_GROUPS; ++q) {
+        const int c = lane * 4 + q * 128;
+        if (c < C) *reinterpret_cast<float4*>(o + c) = v[q];
+      }
+      if (a.idx && lane == 0) a.idx[static_cast<long long>(b) * a.M + m] = t;
     }
-    *reinterpret_cast<float4*>(o + c) = v;
   }
 }
 
@@ -193,9 +228,15 @@ extern "C" int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void*
   if (a.c2 > 0 && (!a.extra || (reinterpret_cast<uintptr_t>(a.extra) & 15u))) return FTB_E_ARG;
   if (a.pitch && (!a.energy || !a.wp || !a.bp || !a.we || !a.be)) return FTB_E_ARG;
   if (a.M == 0) return 0;
+  if (a.c1 + a.c2 > 128 * LR_MAX_GROUPS) return FTB_E_SHAPE;
   GatherArgs g{a};
-  const long long rows = static_cast<long long>(a.batch) * a.M;
-  lr_gather_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(g);
+  const long long ntok = static_cast<long long>(a.batch) * a.T;
+  long long tb = (ntok + 7) / 8;
+  const long long cap = 4ll * h->num_sms;            // persistent: the coefficient table is staged once per block
+  if (tb > cap) tb = cap;
+  const int token_blocks = static_cast<int>(tb);
+  const size_t smem = a.pitch ? static_cast<size_t>(8) * (a.c1 + a.c2) * sizeof(float) : 0;
+  lr_gather_kernel<<<token_blocks + a.batch, 256, smem, static_cast<cudaStream_t>(stream)>>>(g, token_blocks);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }

@@ -119,6 +119,7 @@ class Handle:
         self.check(self.lib.ftb_create(self.index, C.byref(h)))
         self.h = h
         self.replayed_launches = 0      # kernels launched through CUDA-graph replays (engine.Program)
+        self.timing = None              # bench.py: a list -> (name, start event, end event) of the K5/K6 launches
         self.impl = int(os.environ.get('FTB_GEMM_IMPL', '0'))    # 1 = SIMT cross-check kernel (tests only)
 
     @classmethod
@@ -165,12 +166,21 @@ class Handle:
         self.check(self.lib.ftb_rnn_plan_destroy(self.h, plan))
 
     # ---- stateless kernels -------------------------------------------------------------------
+    def _timed(self, name, fn):
+        if self.timing is None:
+            return fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        self.timing.append((name, a, b))
+
     def lr_scan(self, dur, batch, T, apply_fallback, cum, lens, meta):
-        self.check(self.lib.ftb_lr_scan(self.h, ptr(dur), batch, T, int(apply_fallback), ptr(cum), ptr(lens),
-                                        ptr(meta), self.stream()))
+        self._timed('lr_scan', lambda: self.check(self.lib.ftb_lr_scan(
+            self.h, ptr(dur), batch, T, int(apply_fallback), ptr(cum), ptr(lens), ptr(meta), self.stream())))
 
     def lr_gather(self, args: LrGatherArgs):
-        self.check(self.lib.ftb_lr_gather(self.h, C.byref(args), self.stream()))
+        self._timed('lr_gather', lambda: self.check(self.lib.ftb_lr_gather(self.h, C.byref(args), self.stream())))
 
     def embed(self, tok, table, out, out_ld, batch, T, stride, tok2=None, table2=None, extra=None, round_tf32=True):
         e1 = table.shape[1]
