@@ -91,6 +91,8 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         target_len = batch['mel'].size(2)
         if self.training:
             self.step += 1
+        if not self.training and x.is_cuda and not torch.is_grad_enabled():
+            return self._forward_eval(batch)               # the GTA-dump / evaluation use (train_forward.py:33-51)
         tok_mask = make_token_len_mask(x.transpose(0, 1))
         dur_hat = self.dur_pred(x, src_pad_mask=tok_mask).squeeze(-1)
         pitch_hat = self.pitch_pred(x, src_pad_mask=tok_mask).transpose(1, 2)
@@ -130,7 +132,8 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError(f'sequence length {n} exceeds PositionalEncoding.max_len={tp.max_len} '
                                '(same limit as the reference, common_layers.py:129)')
 
-    def _token_program(self, st: dict, batch: int, T: int, predictors: bool) -> eng.Program:
+    def _token_program(self, st: dict, batch: int, T: int, predictors: bool,
+                       mask_predictors: bool = False) -> eng.Program:
         packs, h = st['packs'], st['handle']
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
@@ -150,7 +153,8 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
 
         if predictors:
             for name in ('dur', 'pitch', 'energy'):
-                out = add_transformer(name, packs[name], packs[name + '_emb'], None)   # no mask (:174-180)
+                # generate(): no mask (:174-180); forward(batch): the token pad mask (:132-135)
+                out = add_transformer(name, packs[name], packs[name + '_emb'], tok if mask_predictors else None)
                 heads.append((name, out))
         add_transformer('prenet', packs['prenet'], packs['embedding'], tok)            # key mask x == 0 (:200)
         eng.run_levels(prog, branches)
@@ -163,8 +167,9 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         prog.alpha = 1.0
         return prog
 
-    def _frame_program(self, st: dict, batch: int, M: int) -> eng.Program:
-        """LR output -> postnet transformer (no mask) -> lin -> [B, n_mels, M]  (fast_pitch.py:213-218)."""
+    def _frame_program(self, st: dict, batch: int, M: int, masked: bool = False) -> eng.Program:
+        """LR output -> postnet transformer -> lin -> [B, n_mels, M]  (fast_pitch.py:213-218).  generate(): no mask;
+        `masked`: keys where the caller-filled prog.bufs['frame_tok'] is 0 are masked (forward(batch), :151-155)."""
         packs, h = st['packs'], st['handle']
         tp = packs['postnet']
         self._check_len(tp, M)
@@ -178,7 +183,8 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         mel = prog.dense('mel', (batch, self.n_mels, M))
         prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, M, geo.stride, x0, out_full=x0f),
                   label='postnet.posenc')
-        eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, None, x_full=x0f)])
+        frame_tok = prog.dense('frame_tok', (batch, M), torch.int64) if masked else None
+        eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, frame_tok, x_full=x0f)])
         prog.label('lin')
         prog.gemm(out, packs['lin'], None, out_t=mel)
         prog.flush()
@@ -204,6 +210,34 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
             pitch_hat = pitch_function(prog.bufs['pitch.y'].clone().unsqueeze(1))
             energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
+
+    def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """forward(batch) in eval mode under no_grad on the sm_100a kernels (fast_pitch.py:122-165): predictors and
+        prenet with the token pad mask, teacher-forced durations / pitch / energy, postnet with the frame mask
+        m >= mel_len[b], outputs cut / padded to the target length."""
+        x = batch['x']
+        self._check_tokens(x)
+        st = self._accel_state(x.device)
+        B, T = x.shape
+        tok = self._program(st, ('tok_masked', B, T), lambda: self._token_program(st, B, T, True, mask_predictors=True))
+        tok.bufs['tok'].copy_(x)
+        tok.alpha = 1.0
+        tok.run()
+        dur_hat = tok.bufs['dur.y'].clone()
+        pitch_hat = tok.bufs['pitch.y'].clone().unsqueeze(1)
+        energy_hat = tok.bufs['energy.y'].clone().unsqueeze(1)
+        dur = batch['dur'].to(device=x.device, dtype=torch.float32).contiguous().clone()
+        cum, lens, M, _ = _accel.length_regulate(st['handle'], dur, apply_fallback=False)
+        if M <= 0:
+            raise RuntimeError('forward(): all durations are zero -- nothing to synthesise')
+        prog = self._program(st, ('frame_masked', B, M), lambda: self._frame_program(st, B, M, masked=True))
+        mel_len = batch['mel_len'].to(x.device)
+        prog.bufs['frame_tok'].copy_((torch.arange(M, device=x.device)[None, :] < mel_len[:, None]).to(torch.int64))
+        out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, tok.bufs['prenet.out'], None, 0, dur,
+                                           batch['pitch'].to(x.device), batch['energy'].to(x.device), cum, lens, M,
+                                           float(self.pitch_strength), float(self.energy_strength), round_tf32=False)
+        mel = self.pad(out['mel'], batch['mel'].size(2))
+        return {'mel': mel, 'mel_post': mel.clone(), 'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat}
 
     def _generate_mel(self, x: torch.Tensor, dur_hat: torch.Tensor, pitch_hat: torch.Tensor,
                       energy_hat: torch.Tensor) -> Dict[str, torch.Tensor]:

@@ -468,6 +468,34 @@ def fp_generate(sd: SD, x: torch.Tensor, alpha: float = 1.0,
             'pitch': pitch_hat, 'energy': energy_hat, 'mel_lens': torch.from_numpy(lens)}
 
 
+@torch.no_grad()
+def fp_forward(sd: SD, batch: Dict[str, torch.Tensor], pitch_strength: float = 1.0, energy_strength: float = 1.0,
+               heads: int = 2, padding_value: float = -11.5129) -> Dict[str, torch.Tensor]:
+    """FastPitch.forward(batch) in eval mode (fast_pitch.py:122-165): predictors AND prenet with the token pad mask
+    (x == 0), teacher-forced durations / pitch / energy, postnet with the frame mask m >= mel_len[b], outputs cut /
+    padded to the target mel length with `padding_value`."""
+    x = batch['x']
+    key_pad = (x == 0)
+
+    def pred(p):
+        y = forward_transformer(sd, p + '.transformer', F.embedding(x, sd[p + '.embedding.weight']), heads, key_pad)
+        return linear(y, sd[p + '.lin.weight'], sd[p + '.lin.bias'])
+    dur_hat = pred('dur_pred').squeeze(-1)
+    pitch_hat = pred('pitch_pred').transpose(1, 2)
+    energy_hat = pred('energy_pred').transpose(1, 2)
+    h = forward_transformer(sd, 'prenet', F.embedding(x, sd['embedding.weight']), heads, key_pad)
+    h = h + cond_projection(sd, 'pitch_proj', batch['pitch'].unsqueeze(1)) * pitch_strength
+    h = h + cond_projection(sd, 'energy_proj', batch['energy'].unsqueeze(1)) * energy_strength
+    expanded, _, _, _ = length_regulate_np(h.numpy(), batch['dur'].to(torch.float32).numpy().copy())
+    M = expanded.shape[1]
+    frame_pad = torch.arange(M)[None, :] >= batch['mel_len'][:, None]
+    h = forward_transformer(sd, 'postnet', torch.from_numpy(expanded), heads, frame_pad)
+    mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)
+    target = batch['mel'].shape[2]
+    mel = F.pad(mel[:, :, :target], [0, max(0, target - mel.shape[2]), 0, 0], 'constant', padding_value)
+    return {'mel': mel, 'mel_post': mel, 'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat}
+
+
 # --------------------------------------------------------------------------
 # MultiFastPitch   (models/multi_fast_pitch.py)
 # --------------------------------------------------------------------------

@@ -130,6 +130,14 @@ def ft_forward_case(name, B, T, seed):
          energy=out['energy'])
 
 
+def fp_forward_case(name, B, T, seed):
+    """FastPitch.forward(batch) in eval mode (token / frame pad masks, fast_pitch.py:122-165)."""
+    model = build(FastPitch, 'singlespeaker.yaml', seed)
+    batch = synth.synth_batch(B, T, seed)
+    out = model(batch)
+    save(name, seed=seed, B=B, T=T, mel=out['mel'], dur=out['dur'], pitch=out['pitch'], energy=out['energy'])
+
+
 class BatchedMultiFP(MultiFastPitch):
     """The reference with the ONE B=1-only line (multi_fast_pitch.py:243) replaced by a per-(b,t) arg-max;
     everything else is the reference's code."""
@@ -207,6 +215,10 @@ if __name__ == '__main__':
         with torch.no_grad():
             ft_forward_case('ft_forward_b4_t26', 4, 26, seed=10)
         sys.exit(0)
+    if sys.argv[1:] == ['fpfwd']:
+        with torch.no_grad():
+            fp_forward_case('fp_forward_b4_t26', 4, 26, seed=11)
+        sys.exit(0)
     if sys.argv[1:] == ['mfp']:          # add the MultiFastPitch fixtures without touching the existing ones
         with torch.no_grad():
             mfp_case('mfp_b1_t24', 1, 24, seed=8, patched=False)
@@ -227,5 +239,6 @@ if __name__ == '__main__':
         mfp_case('mfp_b1_t24', 1, 24, seed=8, patched=False)
         mfp_case('mfp_pad_b3_t28', 3, 28, seed=9, patched=True, with_pad=True, alpha=1.25)
         ft_forward_case('ft_forward_b4_t26', 4, 26, seed=10)
+        fp_forward_case('fp_forward_b4_t26', 4, 26, seed=11)
     with open(os.path.join(OUT, 'PROVENANCE.txt'), 'w') as f:
         f.write(f'generated by oracle/make_golden.py from {REF}\ntorch {torch.__version__}\n')

@@ -354,3 +354,24 @@ def test_long_sequence_properties():
     assert out1['mel_post'].shape == (2, 80, int(lens.max())) and bool(torch.isfinite(out1['mel_post']).all())
     assert torch.equal(out1['mel_post'], out2['mel_post']) and torch.equal(out1['dur'], out2['dur'])
     assert int(lens.min()) > 2048                      # spread durations at alpha 0.8: more than one frame per phoneme
+
+
+def test_fast_pitch_eval_forward_vs_reference_golden():
+    """forward(batch) in eval mode under no_grad on the kernels: token pad mask on predictors + prenet, frame mask on
+    the postnet (fast_pitch.py:122-165)."""
+    g = load_golden('fp_forward_b4_t26')
+    sd = synthetic_sd('fast_pitch', int(g['seed']))
+    model = _model('fast_pitch', sd)
+    batch = {k: v.to(DEV) for k, v in synth.synth_batch(int(g['B']), int(g['T']), int(g['seed'])).items()}
+    with torch.no_grad():
+        out = model(batch)
+    torch.cuda.synchronize()
+    assert any(k[0] == 'frame_masked' for k in model.__dict__['_accel']['programs'])
+    assert out['mel'].shape == g['mel'].shape
+    ml = batch['mel_len'].cpu()
+    valid = (torch.arange(g['mel'].shape[2])[None, :] < ml[:, None])[:, None, :].expand(g['mel'].shape)
+    got, want = out['mel'].cpu(), torch.from_numpy(g['mel'])
+    assert max_abs(got[valid], want[valid]) < MEL_ABS and rel_l2(got[valid], want[valid]) < MEL_REL
+    assert rel_l2(got, want) < MEL_REL
+    for k in ('dur', 'pitch', 'energy'):
+        assert max_abs(out[k].cpu()[:, ...], g[k]) < 1e-2, k

@@ -135,3 +135,14 @@ def test_forward_tacotron_eval_forward():
     for k in ('mel', 'mel_post', 'dur', 'pitch', 'energy'):
         assert out[k].shape == g[k].shape, k
         assert max_abs(out[k], g[k]) < 2e-4, k
+
+
+def test_fast_pitch_eval_forward():
+    """FastPitch.forward(batch) in eval mode (token mask on predictors + prenet, frame mask on the postnet)."""
+    from forwardtacotron_b200 import synth
+    g = load_golden('fp_forward_b4_t26')
+    sd = synthetic_sd('fast_pitch', int(g['seed']))
+    out = O.fp_forward(sd, synth.synth_batch(int(g['B']), int(g['T']), int(g['seed'])))
+    for k in ('mel', 'dur', 'pitch', 'energy'):
+        assert out[k].shape == g[k].shape, k
+        assert max_abs(out[k], g[k]) < 2e-4, k
