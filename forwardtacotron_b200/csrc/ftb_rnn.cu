@@ -13,21 +13,27 @@
 // twice: as fp32 (exactly the fp16 value, hence tf32-exact) into the layer output the next GEMM reads,
 // and as fp16 into a compact exchange tensor hx[dir][t][b][H] that the other CTAs poll.
 //
-// Per step:
-//     h_{t-1} (fp16, L2-resident) -> staged ONCE per CTA into smem by 128-bit ld.relaxed.gpu loads that
-//         POLL THE DATA ITSELF: hx is pre-filled with 0xFFFF halves (an fp16 NaN no arithmetic here
-//         produces), so "h arrived" == "no sentinel left".  No counter, no __threadfence, no atomic on
-//         the critical path.  The K range is split over KS = 2 warp groups that synchronise with named
-//         barriers, so each half starts its MMAs as soon as its own bytes have landed.
+// Per step (v4: two interleaved batch groups per CTA, A = columns 0-7, B = columns 8-15):
+//     h_{t-1} (fp16, L2-resident) -> staged ONCE per CTA and group into smem by cp.async.cg (16 B per thread,
+//         bypassing L1).  hx is pre-filled with 0xFFFF halves (an fp16 NaN no arithmetic here produces), so
+//         "h arrived" == "no sentinel left": after cp.async.wait_group each thread checks the 16 bytes it
+//         staged and re-fetches (ld.relaxed.gpu) only those that still hold the sentinel.  No counter, no
+//         __threadfence, no atomic on the critical path.  The K range is split over KS = 2 warp groups that
+//         synchronise with named barriers, so each half starts its MMAs as soon as its own bytes have landed.
 //       -> B-fragments from smem (one LDS.128 feeds two k-steps: K is permuted inside 32-wide blocks),
-//          mma.sync.m16n8k16 f16 -> fp32 accumulators
-//       -> partial sums through double-buffered padded smem -> ONE __syncthreads per step
-//       -> gate math in fp32 (c, h stay in registers; x-projection rows arrive through a 4-stage cp.async
-//          ring issued three steps ahead, so their DRAM latency is off the critical path)
+//          mma.sync.m16n8k16 f16 -> fp32 accumulators; ALL MMA warps work on the group whose h has landed
+//          while the other group's h is still in flight (the L2 hand-off of A hides behind the MMAs of B).
+//       -> partial sums through padded smem -> __syncthreads -> gate math in fp32 by the group's 8 warps
+//          (c, h stay in registers; x-projection rows arrive through a 4-stage cp.async ring issued three
+//          steps ahead, so their DRAM latency is off the critical path)
 //       -> h_t stores (fp32 to `out`, fp16 pairs to hx).
-// tcgen05 is deliberately not used here: the per-step GEMM is [G*U x H] x [H x 16]; a UMMA would need W_hh
-// in shared memory (256 KB fp32-class for this slice) or TMEM (all 512 columns), and h re-staged into a
-// swizzled tile every step; the per-step cost is dominated by the L2 hand-off, not by the MMA issue.
+// Packed-sequence semantics (optional `lens`): a column whose sentence has ended keeps h = c = 0 and writes
+// `pad_value` to `out` -- what pack_padded_sequence / pad_packed_sequence give the reference's eval-mode forward.
+//
+// tcgen05 is deliberately not used here: the per-step GEMM is [G*U x H] x [H x 16]; a UMMA needs W_hh in shared
+// memory (256 KB fp32-class for this slice) or TMEM and h re-staged into a swizzled tile every step.  A TS-mode
+// (A from TMEM) variant was built and measured: ~90 cycles per M128 N16 K16 instruction, 3000 cycles of MMA per
+// step against ~950 here (profiles/r1g_rnn_tcgen05_experiment.txt; source kept in scratch/experiments/).
 #include <cstdio>
 #include <cuda_fp16.h>
 
