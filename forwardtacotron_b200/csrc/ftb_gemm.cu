@@ -2,13 +2,16 @@
 //
 //   warp 0      : TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
 //   warp 1      : MMA issuer     (one elected lane, tcgen05.mma kind::tf32, fp32 accum in TMEM)
-//   warps 2..5  : epilogue       (tcgen05.ld -> fused ReLU/BN-affine/maxpool/highway -> global)
+//   warps 2..9  : epilogue       (tcgen05.ld -> fused ReLU/BN-affine/maxpool/highway -> global), two sets of four
+//                 warps: set 0 drains TMEM accumulator 0 (even tiles of this CTA), set 1 accumulator 1 (odd tiles)
 //
 // A convolution with k taps is k shifted GEMMs over the same channel-last activation
 // matrix: tap j loads the A tile at row (m0 + tap0 + j).  Sentence edges need no masks
 // because the padded-flat layout keeps >= 8 zero rows between sentences and TMA zero-fills
 // rows outside the tensor (include/ftb200.h).  Two 256-column TMEM accumulators let the
-// epilogue of tile i overlap the MMAs of tile i+1.
+// epilogue of tile i overlap the MMAs of tile i+1 AND the epilogue of tile i-1: an epilogue warp is a
+// latency chain (one warp per SM sub-partition ran at ~0.2 IPC, profiles/r1m_gemm_epilogue.txt), so two
+// warps per sub-partition on different tiles nearly double the drain rate of the small-K layers.
 //
 // Precision: operands are fp32 in memory, pre-rounded to tf32 (cvt.rna) by their
 // producers, so the tensor core's mantissa truncation is exact; accumulation is fp32.
@@ -27,10 +30,11 @@ constexpr int A_STAGE_BYTES = BM * BK * 4;        // 16 KB
 constexpr int B_STAGE_BYTES = 256 * BK * 4;       // 32 KB (bn <= 256)
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int TMEM_COLS = 512;          // 2 accumulators x 256 fp32 columns
-constexpr int NUM_THREADS = 192;
-constexpr int EPI_THREADS = 128;
+constexpr int NUM_THREADS = 320;
+constexpr int EPI_THREADS = 128;         // per epilogue set
 constexpr int CHUNK = 32;               // accumulator columns per epilogue chunk (one tcgen05.ld .x32)
 constexpr int STG_LD = 36;              // staging row stride (floats): conflict-free 128-bit row writes AND reads
+constexpr int STG_ROWS = 16;            // the 32 rows of a chunk pass through the staging tile in two halves
 
 struct SmemTail {
   uint64_t full[STAGES];
@@ -39,9 +43,9 @@ struct SmemTail {
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
   uint32_t pad;
-  alignas(16) float exch[2][4][CHUNK];  // maxpool: last row of each 32-row group, double buffered
-  alignas(16) float params[2][3][256];              // per tile (double buffered): bias0 / scale / shift of its bn accumulator columns
-  alignas(16) float stg[4][32][STG_LD];             // per epilogue warp: 32 rows x 32 columns staging tile (row<->lane transpose)
+  alignas(16) float exch[2][2][4][CHUNK];           // per set: maxpool last row of each 32-row group, double buffered
+  alignas(16) float params[2][3][256];              // per set: bias0 / scale / shift of the current tile's bn accumulator columns
+  alignas(16) float stg[8][STG_ROWS][STG_LD];       // per epilogue warp: 16 rows x 32 columns staging tile (row<->lane transpose)
 };
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + sizeof(SmemTail) + 1024;   // +1024: manual alignment
 
@@ -49,6 +53,11 @@ struct TileCoord {
   const GemmProblemDev* p;
   int m0, n0;
 };
+
+// Static schedule: CTA c runs tile i*G + c in even waves i and tile i*G + (G-1-c) in odd waves ("snake"), so with the
+// problems sorted heaviest-first (host side) no CTA collects the heaviest tile of every wave.  A CTA's tile of wave i is
+// out of range only in the last, partial wave, so every role of the CTA stops at the same i.
+__device__ __forceinline__ int sched_tile(int i, int c, int G) { return i * G + ((i & 1) ? (G - 1 - c) : c); }
 
 __device__ __forceinline__ TileCoord decode_tile(const GemmProblemDev* probs, int nprob, int tile) {
   int pi = 0;
@@ -85,8 +94,9 @@ __device__ __forceinline__ float epi_finish(const GemmProblemDev* p, float v) {
 // profiles/r1e_gemm_roles.txt).
 struct EpiCtx {
   const float (*prm)[256];       // [3][256] bias0 / scale / shift of this tile's columns
-  float (*stg)[STG_LD];          // this warp's 32 x 32 staging tile
-  float (*exch)[4][CHUNK];       // [2][4][CHUNK] max-pool row hand-over between the four warps
+  float (*stg)[STG_LD];          // this warp's 16 x 32 staging tile
+  float (*exch)[4][CHUNK];       // [2][4][CHUNK] max-pool row hand-over between the four warps of this set
+  uint32_t pool_bar;             // named barrier of this set for the hand-over
   uint32_t taddr;                // TMEM address of this warp's lanes, column 0 of the tile
   int bn, n0, N, g, lane, t, b, seq_len, res_ld, out_ld;
   unsigned smask;                // rows of this warp that are stored
@@ -149,7 +159,7 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
         for (int j = 0; j < CHUNK; j += 4)
           *reinterpret_cast<float4*>(&ex[c.g][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
       }
-      named_bar_sync(2, EPI_THREADS);
+      named_bar_sync(c.pool_bar, EPI_THREADS);
       const bool first_t = (c.t == 0);
 #pragma unroll
       for (int j = 0; j < CHUNK; ++j) {
@@ -173,25 +183,32 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
       }
     }
     if (optr) {
-#pragma unroll
-      for (int j = 0; j < CHUNK; j += 4)
-        *reinterpret_cast<float4*>(&c.stg[lane][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-      __syncwarp();
       // a half chunk (bn = 16 mod 32) must not spill into the columns of the next n-tile
-      if (c0 + 4 * part < c.bn && nb + 4 * part < c.N) {  // N, nb and bn are multiples of 4
+      const bool cols_ok = c0 + 4 * part < c.bn && nb + 4 * part < c.N;      // N, nb and bn are multiples of 4
 #pragma unroll
-        for (int i8 = 0; i8 < 8; ++i8) {
-          const int row = i8 * 4 + sub;
-          if ((c.smask >> row) & 1u) {
-            float4 y = *reinterpret_cast<const float4*>(&c.stg[row][4 * part]);
-            if (RES) { y.x += xr_cur[i8].x; y.y += xr_cur[i8].y; y.z += xr_cur[i8].z; y.w += xr_cur[i8].w; }
-            if (FULL) *reinterpret_cast<float4*>(fptr + i8 * ostep + c0) = y;
-            if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-            *reinterpret_cast<float4*>(optr + i8 * ostep + c0) = y;
+      for (int h = 0; h < 2; ++h) {
+        if ((lane >> 4) == h) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; j += 4)
+            *reinterpret_cast<float4*>(&c.stg[lane & 15][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+        __syncwarp();
+        if (cols_ok) {
+#pragma unroll
+          for (int i4 = 0; i4 < 4; ++i4) {
+            const int i8 = h * 4 + i4;
+            const int row = i8 * 4 + sub;
+            if ((c.smask >> row) & 1u) {
+              float4 y = *reinterpret_cast<const float4*>(&c.stg[row & 15][4 * part]);
+              if (RES) { y.x += xr_cur[i8].x; y.y += xr_cur[i8].y; y.z += xr_cur[i8].z; y.w += xr_cur[i8].w; }
+              if (FULL) *reinterpret_cast<float4*>(fptr + i8 * ostep + c0) = y;
+              if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+              *reinterpret_cast<float4*>(optr + i8 * ostep + c0) = y;
+            }
           }
         }
+        __syncwarp();
       }
-      __syncwarp();
     }
     if (RES) {
 #pragma unroll
@@ -248,7 +265,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tail->tmem_full[b], 1);
-      mbar_init(&tail->tmem_empty[b], 4);       // one arrive per epilogue warp
+      mbar_init(&tail->tmem_empty[b], 4);       // one arrive per epilogue warp of the set that drains buffer b
     }
     fence_mbar_init();
   }
@@ -267,7 +284,9 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       int stage = 0;
       uint32_t phase = 0;
       const GemmProblemDev* last_p = nullptr;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int it = 0;; ++it) {
+        const int tile = sched_tile(it, blockIdx.x, gridDim.x);
+        if (tile >= total_tiles) break;
         const TileCoord tc = decode_tile(probs, nprob, tile);
         const GemmProblemDev* p = tc.p;
         const uint32_t tx = A_STAGE_BYTES + static_cast<uint32_t>(p->bn) * BK * 4;
@@ -302,8 +321,9 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      for (int it = 0;; ++it) {
+        const int tile = sched_tile(it, blockIdx.x, gridDim.x);
+        if (tile >= total_tiles) break;
         const TileCoord tc = decode_tile(probs, nprob, tile);
         const GemmProblemDev* p = tc.p;
         const int buf = it & 1;
@@ -336,13 +356,16 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
     // row-segment stores of `out` (tf32-rounded) / `out_full` (unrounded).  `out_t` ([B, n, L]) is written
     // in phase A, where consecutive lanes are consecutive t.
     const int g = warp & 3;                       // TMEM lane quarter this warp may read
+    const int set = (warp - 2) >> 2;              // 0: warps 2..5 (even tiles), 1: warps 6..9 (odd tiles)
     const int etid = g * 32 + lane;
-    float (*stg)[STG_LD] = tail->stg[g];
-    int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+    const uint32_t bar_prm = 1 + 2 * set, bar_pool = 2 + 2 * set;      // named barriers of this set
+    float (*stg)[STG_LD] = tail->stg[set * 4 + g];
+    for (int it = set;; it += 2) {
+      const int tile = sched_tile(it, blockIdx.x, gridDim.x);
+      if (tile >= total_tiles) break;
       const TileCoord tc = decode_tile(probs, nprob, tile);
       const GemmProblemDev* p = tc.p;
-      const int buf = it & 1;
+      const int buf = set;                        // == it & 1
       // problem fields -> registers ONCE per tile: this warp stores to global memory, so without the copies the
       // compiler re-loads p->out / p->residual / ... from global memory (a long-scoreboard stall) in every
       // iteration of the store loops -- measured as the dominant epilogue stall (profiles/r1e_gemm_roles.txt)
@@ -360,7 +383,8 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       const bool pool = (P_epi == FTB_EPI_MAXPOOL);
 
       // ---- per-tile column parameters -> smem (overlaps the tail of this tile's MMAs)
-      float (*prm)[256] = tail->params[buf];
+      float (*prm)[256] = tail->params[set];
+      named_bar_sync(bar_prm, EPI_THREADS);       // every warp of the set is done with the previous tile's parameters
       for (int c = etid; c < P_bn; c += EPI_THREADS) {
         float b0 = 0.0f, sc = 1.0f, sh = 0.0f;
         if (highway) {
@@ -374,7 +398,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         }
         prm[0][c] = b0; prm[1][c] = sc; prm[2][c] = sh;
       }
-      named_bar_sync(1, EPI_THREADS);
+      named_bar_sync(bar_prm, EPI_THREADS);
 
       GP_T0 mbar_wait(&tail->tmem_full[buf], (it >> 1) & 1u); GP_ACC(3)
       tc_fence_after();
@@ -407,6 +431,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         float* optr = P_out + (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4;
         float* fptr = P_out_full ? P_out_full + (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4 : nullptr;
         const long long ostep = 8ll * P_out_ld;
+        float* hstg = &stg[0][0];       // [32 rows][16 floats], float4 slots XOR-swizzled by (row >> 1) & 3: conflict-free
         float4 xr_cur[4], xr_nxt[4];
         auto load_res = [&](float4 (&dst)[4], int j0) {
 #pragma unroll
@@ -431,14 +456,14 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             y.y = epi_highway(x1[4 * q + 1] + b1.y, x2[4 * q + 1] + b2.y, xr_cur[q].y);
             y.z = epi_highway(x1[4 * q + 2] + b1.z, x2[4 * q + 2] + b2.z, xr_cur[q].z);
             y.w = epi_highway(x1[4 * q + 3] + b1.w, x2[4 * q + 3] + b2.w, xr_cur[q].w);
-            *reinterpret_cast<float4*>(&stg[lane][4 * q]) = y;
+            *reinterpret_cast<float4*>(hstg + lane * 16 + 4 * (q ^ ((lane >> 1) & 3))) = y;
           }
           __syncwarp();
 #pragma unroll
           for (int i4 = 0; i4 < 4; ++i4) {
             const int row = i4 * 8 + brow;
             if ((smask >> row) & 1u) {
-              float4 y = *reinterpret_cast<const float4*>(&stg[row][4 * c4]);
+              float4 y = *reinterpret_cast<const float4*>(hstg + row * 16 + 4 * (c4 ^ ((row >> 1) & 3)));
               if (fptr) *reinterpret_cast<float4*>(fptr + i4 * ostep + j0) = y;
               if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
               *reinterpret_cast<float4*>(optr + i4 * ostep + j0) = y;
@@ -450,7 +475,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         }
       } else {
         EpiCtx c;
-        c.prm = prm; c.stg = stg; c.exch = tail->exch; c.taddr = taddr;
+        c.prm = prm; c.stg = stg; c.exch = tail->exch[set]; c.pool_bar = bar_pool; c.taddr = taddr;
         c.bn = P_bn; c.n0 = tc.n0; c.N = N; c.g = g; c.lane = lane; c.t = t; c.b = b; c.seq_len = P_seq_len;
         c.res_ld = P_res_ld; c.out_ld = P_out_ld; c.smask = smask; c.store = store; c.r = r; c.r_warp = r_warp;
         c.relu_lo = relu ? 0.0f : -INFINITY;
@@ -467,7 +492,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
     }
   }
 #ifdef FTB_GEMM_PROFILE
-  if (blockIdx.x == 0 && lane == 0 && (warp <= 2)) {
+  if (blockIdx.x == 0 && lane == 0 && (warp <= 2 || warp == 6)) {
     const long long tot = clock64() - gp_start;
     printf("gemm prof warp %d tiles %d total %lld | wait_empty %lld wait_tmem_empty %lld wait_full %lld wait_tmem_full %lld epi_work %lld\n",
            warp, (total_tiles + gridDim.x - 1) / gridDim.x, tot, gp[0], gp[1], gp[2], gp[3], gp[4]);

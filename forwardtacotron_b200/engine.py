@@ -15,6 +15,23 @@ from . import runtime as rt
 from .pack import PackedGemm, PackedRnn
 
 
+def _tile_cost(q) -> float:
+    """Cycles one 128 x bn tile keeps a CTA busy (ftb_gemm.cu): the MMAs (4 per 32-channel block and tap, bn/2 cycles
+    each for kind::tf32) against the epilogue of its bn/32 chunks (two warp sets drain alternate tiles), plus the
+    per-tile fixed cost."""
+    mma = q.taps * ((q.cin + 31) // 32) * 2.0 * q.bn
+    epi = (q.bn / 32.0) * 1800.0 / 2.0
+    return max(mma, epi) + 1500.0
+
+
+def _order_tiles(pending):
+    """Problems of one launch, heaviest tile first: the kernel's static snake schedule (wave i forwards, wave i+1
+    backwards over the CTAs) then hands every CTA a similar mix.  Halving the tile width of a problem whose tile count
+    quantises badly (204 tiles on 148 CTAs) was measured and rejected: a 128-wide tile re-reads A from shared memory
+    twice as often and runs at ~64 % of the 256-wide MMA rate (profiles/r1m_gemm_epilogue.txt)."""
+    return sorted(pending, key=lambda q: -_tile_cost(q))
+
+
 class Geometry:
     """Row geometry of a [batch, seq_len, C] activation in the padded-flat layout."""
 
@@ -94,10 +111,9 @@ class Program:
         """Close the current group: everything queued since the last flush runs as one launch."""
         if not self._pending:
             return
-        # heaviest tiles first (tile cost ~ taps*cin*bn) for the static round-robin scheduler
-        probs = sorted(self._pending, key=lambda q: -(q.taps * q.cin * q.bn))
-        self._pending = []
         g = self.geo
+        probs = _order_tiles(self._pending)
+        self._pending = []
         valid = g.batch * g.seq_len
         for i in range(0, len(probs), 32):
             grp = probs[i:i + 32]

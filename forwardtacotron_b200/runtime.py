@@ -118,6 +118,7 @@ class Handle:
         h = _fp()
         self.check(self.lib.ftb_create(self.index, C.byref(h)))
         self.h = h
+        self.num_sms = torch.cuda.get_device_properties(self.index).multi_processor_count
         self.replayed_launches = 0      # kernels launched through CUDA-graph replays (engine.Program)
         self.timing = None              # bench.py: a list -> (name, start event, end event) of the K5/K6 launches
         self.impl = int(os.environ.get('FTB_GEMM_IMPL', '0'))    # 1 = SIMT cross-check kernel (tests only)
