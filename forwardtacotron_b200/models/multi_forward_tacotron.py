@@ -133,6 +133,8 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         target_len = batch['mel'].size(2)
         if self.training:
             self.step += 1
+        if not self.training and x.is_cuda and not torch.is_grad_enabled():
+            return self._forward_eval(batch)               # the GTA-dump / evaluation use (train_forward.py:33-51)
         pitch_cond_hat = self.pitch_cond_pred(x, semb).squeeze(-1)
         dur_hat = self.dur_pred(x, batch['pitch_cond'], semb).squeeze(-1)
         pitch_hat = self.pitch_pred(x, batch['pitch_cond'], semb).transpose(1, 2)
@@ -161,6 +163,9 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             'prenet': _accel.pack_cbhg(self.prenet),
             'lstm': pk.PackedRnn(self.lstm),
             'lin': pk.pack_linear(self.lin.weight, self.lin.bias),
+            # lin(padding vector) in exact fp32: the mel rows behind a packed sentence (eval-mode forward only)
+            'lin_pad_vec': (self.lin.weight.detach().float().sum(dim=1) * float(self.padding_value)
+                            + self.lin.bias.detach().float()).contiguous(),
             'postnet': _accel.pack_cbhg(self.postnet),
             'post_proj': pk.pack_linear(self.post_proj.weight),
             'pitch_proj': (self.pitch_proj.weight.detach().float().reshape(-1, 3).contiguous(),
@@ -176,10 +181,12 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                 packs[name + '_cemb'] = pk.round_tf32(mod.pitch_cond_embedding.weight)
         return packs
 
-    def _token_program(self, st: dict, batch: int, T: int, predictors: bool) -> eng.Program:
+    def _token_program(self, st: dict, batch: int, T: int, predictors: bool, teacher_cond: bool = False) -> eng.Program:
         """Phoneme-side program.  Phase 1: pitch_cond_pred, energy_pred and the CBHG prenet (level
         interleaved) + their GRUs; arg-max of the pitch condition (:251-252).  Phase 2: dur_pred and
-        pitch_pred, which consume the pitch condition (:253,256)."""
+        pitch_pred, which consume the pitch condition (:253,256).  `teacher_cond` (eval-mode forward, :199-200):
+        the condition is the caller's batch['pitch_cond'] -- the 'pitch_cond' buffer is filled before run() and the
+        arg-max is left out."""
         packs, h = st['packs'], st['handle']
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
@@ -242,7 +249,8 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                 if name == 'pitch_cond':
                     logits = y
             n_cls = logits.shape[2]
-            prog.call(lambda: h.argmax(logits, batch * T, n_cls, pcond), label='pitch_cond.argmax')
+            if not teacher_cond:
+                prog.call(lambda: h.argmax(logits, batch * T, n_cls, pcond), label='pitch_cond.argmax')
             branches2, grus2 = [], []
             for name in ('dur', 'pitch'):
                 levels, gru = add_predictor(name, True)
@@ -286,6 +294,44 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             pitch_hat = pitch_function(prog.bufs['pitch.y'].reshape(B, 1, T).clone())
             energy_hat = energy_function(prog.bufs['energy.y'].reshape(B, 1, T).clone())
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, pitch_cond_hat, scan)
+
+    def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """forward(batch) in eval mode under no_grad on the sm_100a kernels (multi_forward_tacotron.py:186-241):
+        predictors for the returned dur / pitch / energy / pitch_cond (dur and pitch conditioned on the TARGET pitch
+        condition, :199-200), teacher-forced mel branch with the packed-sequence BiLSTM over batch['mel_len']."""
+        x, semb = batch['x'], batch['speaker_emb']
+        self._check_tokens(x)
+        self._check_speaker(x, semb, self.speaker_emb_dims)
+        st = self._accel_state(x.device)
+        B, T = x.shape
+        tok = self._program(st, ('tok_teacher', B, T), lambda: self._token_program(st, B, T, True, teacher_cond=True))
+        tok.bufs['tok'].copy_(x)
+        tok.bufs['semb'].copy_(semb.to(torch.float32))
+        tok.bufs['pitch_cond'].copy_(batch['pitch_cond'])
+        tok.alpha = 1.0
+        tok.run()
+        dur_hat = tok.bufs['dur.y'].reshape(B, T).clone()
+        pitch_hat = tok.bufs['pitch.y'].reshape(B, 1, T).clone()
+        energy_hat = tok.bufs['energy.y'].reshape(B, 1, T).clone()
+        pitch_cond_hat = tok.bufs['pitch_cond.y'].clone()                      # [B,T,3] logits
+        dur = batch['dur'].to(device=x.device, dtype=torch.float32).contiguous().clone()
+        cum, lens, M_lr, _ = _accel.length_regulate(st['handle'], dur, apply_fallback=False)
+        mel_len = batch['mel_len'].to(device=x.device, dtype=torch.int32).contiguous()
+        M = int(mel_len.max())
+        if M < 1 or M > M_lr or int(mel_len.min()) < 1:
+            raise RuntimeError(f'forward(): mel_len must lie in [1, {M_lr}] (the regulated length), as '
+                               'pack_padded_sequence requires (multi_forward_tacotron.py:222)')
+        pre = tok.bufs['prenet.h']
+        C1, C2 = pre.shape[1], self.speaker_emb_dims
+        prog = self._program(st, ('frame_packed', B, M), lambda: _accel.build_frame_program(
+            st['handle'], st['packs'], B, M, C1 + C2, self.n_mels, packed_pad_value=float(self.padding_value)))
+        prog.bufs['mel_len'].copy_(mel_len)
+        out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, pre, tok.bufs['semb'], C2, dur,
+                                           batch['pitch'].to(x.device), batch['energy'].to(x.device), cum, lens, M,
+                                           float(self.pitch_strength), float(self.energy_strength))
+        target_len = batch['mel'].size(2)
+        return {'mel': self._pad(out['mel'], target_len), 'mel_post': self._pad(out['mel_post'], target_len),
+                'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat, 'pitch_cond': pitch_cond_hat}
 
     def _generate_mel(self, x: torch.Tensor, semb: torch.Tensor, dur_hat: torch.Tensor, pitch_hat: torch.Tensor,
                       pitch_cond_hat: torch.Tensor, energy_hat: torch.Tensor) -> Dict[str, torch.Tensor]:

@@ -118,4 +118,8 @@ def synth_batch(batch: int, length: int, seed: int = 0, n_mels: int = 80, speake
            'mel': torch.zeros((batch, n_mels, int(mel_len.max()) + 3))}
     if speaker_dims:
         out['speaker_emb'] = synth_speaker_emb(batch, speaker_dims, seed)
+        # utils/dataset.py:141-142: 1 = unvoiced (zero pitch), 2 = voiced, 0 = padding
+        cond = torch.randint(1, 3, (batch, length), generator=g, dtype=torch.int64)
+        cond[x == 0] = 0
+        out['pitch_cond'] = cond
     return out

@@ -389,6 +389,42 @@ def mft_generate(sd: SD, x: torch.Tensor, speaker_emb: torch.Tensor, alpha: floa
             'pitch_cond_logits': pc_logits, 'mel_lens': torch.from_numpy(lens)}
 
 
+@torch.no_grad()
+def mft_forward(sd: SD, batch: Dict[str, torch.Tensor], pitch_strength: float = 1.0, energy_strength: float = 1.0,
+                padding_value: float = -11.5129) -> Dict[str, torch.Tensor]:
+    """MultiForwardTacotron.forward(batch) in eval mode (multi_forward_tacotron.py:186-241): the dur / pitch predictors
+    are conditioned on the TARGET pitch condition batch['pitch_cond'] (:199-200), the mel branch is teacher forced and
+    runs the BiLSTM with packed-sequence semantics over `mel_len`."""
+    x, semb, cond = batch['x'], batch['speaker_emb'], batch['pitch_cond']
+
+    def plain(p):
+        return series_predictor(sd, p, _with_speaker(F.embedding(x, sd[p + '.embedding.weight']), semb))
+
+    def conditional(p):
+        e = F.embedding(x, sd[p + '.embedding.weight'])
+        c = F.embedding(cond, sd[p + '.pitch_cond_embedding.weight'])
+        return series_predictor(sd, p, _with_speaker(torch.cat([e, c], dim=2), semb))
+
+    pitch_cond_hat = plain('pitch_cond_pred').squeeze(-1)                    # [B,T,3]
+    dur_hat = conditional('dur_pred').squeeze(-1)
+    pitch_hat = conditional('pitch_pred').transpose(1, 2)
+    energy_hat = plain('energy_pred').transpose(1, 2)
+    h = _with_speaker(cbhg(sd, 'prenet', F.embedding(x, sd['embedding.weight']).transpose(1, 2)), semb)
+    h = h + cond_projection(sd, 'pitch_proj', batch['pitch'].unsqueeze(1)) * pitch_strength
+    h = h + cond_projection(sd, 'energy_proj', batch['energy'].unsqueeze(1)) * energy_strength
+    expanded, _, _, _ = length_regulate_np(h.numpy(), batch['dur'].to(torch.float32).numpy().copy())
+    h = packed_bi_rnn(sd, 'lstm', torch.from_numpy(expanded), batch['mel_len'], 'lstm', padding_value)
+    mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)
+    mel_post = linear(cbhg(sd, 'postnet', mel), sd['post_proj.weight']).transpose(1, 2)
+    target = batch['mel'].shape[2]
+
+    def pad(t):
+        t = t[:, :, :target]
+        return F.pad(t, [0, target - t.shape[2], 0, 0], 'constant', padding_value)
+    return {'mel': pad(mel), 'mel_post': pad(mel_post), 'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat,
+            'pitch_cond': pitch_cond_hat}
+
+
 # --------------------------------------------------------------------------
 # FastPitch   (models/fast_pitch.py, FFT blocks in common_layers.py:127-223)
 # --------------------------------------------------------------------------

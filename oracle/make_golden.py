@@ -130,6 +130,15 @@ def ft_forward_case(name, B, T, seed):
          energy=out['energy'])
 
 
+def mft_forward_case(name, B, T, seed):
+    """MultiForwardTacotron.forward(batch) in eval mode (multi_forward_tacotron.py:186-241)."""
+    model = build(MultiForwardTacotron, 'multispeaker.yaml', seed)
+    batch = synth.synth_batch(B, T, seed, speaker_dims=256)
+    out = model(batch)
+    save(name, seed=seed, B=B, T=T, mel=out['mel'], mel_post=out['mel_post'], dur=out['dur'], pitch=out['pitch'],
+         energy=out['energy'], pitch_cond=out['pitch_cond'])
+
+
 def fp_forward_case(name, B, T, seed):
     """FastPitch.forward(batch) in eval mode (token / frame pad masks, fast_pitch.py:122-165)."""
     model = build(FastPitch, 'singlespeaker.yaml', seed)
@@ -214,6 +223,10 @@ if __name__ == '__main__':
     if sys.argv[1:] == ['ftfwd']:        # eval-mode forward(batch) fixtures only
         with torch.no_grad():
             ft_forward_case('ft_forward_b4_t26', 4, 26, seed=10)
+        sys.exit(0)
+    if sys.argv[1:] == ['mftfwd']:
+        with torch.no_grad():
+            mft_forward_case('mft_forward_b4_t26', 4, 26, seed=12)
         sys.exit(0)
     if sys.argv[1:] == ['fpfwd']:
         with torch.no_grad():

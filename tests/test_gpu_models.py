@@ -274,13 +274,17 @@ def test_batched_caller_matches_oracle_per_bucket():
     assert compared >= 4
 
 
-def test_forward_tacotron_eval_forward_vs_reference_golden():
+@pytest.mark.parametrize('kind,golden,speaker_dims', [('forward_tacotron', 'ft_forward_b4_t26', 0),
+                                                      ('multi_forward_tacotron', 'mft_forward_b4_t26', 256)])
+def test_forward_tacotron_eval_forward_vs_reference_golden(kind, golden, speaker_dims):
     """forward(batch) in eval mode under no_grad (the GTA feature dump, train_forward.py:33-51)
-    runs on the kernels: teacher-forced durations, packed-sequence BiLSTM (tail = padding value), padded outputs."""
-    g = load_golden('ft_forward_b4_t26')
-    sd = synthetic_sd('forward_tacotron', int(g['seed']))
-    model = _model('forward_tacotron', sd)
-    batch = {k: v.to(DEV) for k, v in synth.synth_batch(int(g['B']), int(g['T']), int(g['seed'])).items()}
+    runs on the kernels: teacher-forced durations, packed-sequence BiLSTM (tail = padding value), padded outputs;
+    MultiForwardTacotron additionally conditions dur / pitch on the target pitch condition."""
+    g = load_golden(golden)
+    sd = synthetic_sd(kind, int(g['seed']))
+    model = _model(kind, sd)
+    batch = {k: v.to(DEV) for k, v in synth.synth_batch(int(g['B']), int(g['T']), int(g['seed']),
+                                                        speaker_dims=speaker_dims).items()}
     with torch.no_grad():
         out = model(batch)
     torch.cuda.synchronize()
@@ -303,6 +307,9 @@ def test_forward_tacotron_eval_forward_vs_reference_golden():
         assert rel_l2(got[valid], want[valid]) < (MEL_REL if k == 'mel' else 3e-3), k
     assert max_abs(out['dur'].cpu(), g['dur']) < 5e-3 and max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3
     assert max_abs(out['energy'].cpu(), g['energy']) < 5e-3
+    if speaker_dims:
+        assert out['pitch_cond'].shape == g['pitch_cond'].shape
+        assert max_abs(out['pitch_cond'].cpu(), g['pitch_cond']) < 5e-3
     # the target-length tail is exactly the padding value, like the reference's _pad (:236-239)
     assert bool((out['mel_post'][:, :, int(batch['mel_len'].max()):] == model.padding_value).all())
 

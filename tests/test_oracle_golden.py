@@ -137,6 +137,22 @@ def test_forward_tacotron_eval_forward():
         assert max_abs(out[k], g[k]) < 2e-4, k
 
 
+def test_multi_forward_tacotron_eval_forward():
+    """MultiForwardTacotron.forward(batch) in eval mode: predictors conditioned on the target pitch condition."""
+    from forwardtacotron_b200 import synth
+    g = load_golden('mft_forward_b4_t26')
+    sd = synthetic_sd('multi_forward_tacotron', int(g['seed']))
+    batch = synth.synth_batch(int(g['B']), int(g['T']), int(g['seed']), speaker_dims=256)
+    O.use_library_rnn(True)
+    try:
+        out = O.mft_forward(sd, batch)
+    finally:
+        O.use_library_rnn(False)
+    for k in ('mel', 'mel_post', 'dur', 'pitch', 'energy', 'pitch_cond'):
+        assert out[k].shape == g[k].shape, k
+        assert max_abs(out[k], g[k]) < 2e-4, k
+
+
 def test_fast_pitch_eval_forward():
     """FastPitch.forward(batch) in eval mode (token mask on predictors + prenet, frame mask on the postnet)."""
     from forwardtacotron_b200 import synth
