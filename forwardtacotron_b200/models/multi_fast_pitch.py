@@ -131,6 +131,8 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         target_len = batch['mel'].size(2)
         if self.training:
             self.step += 1
+        if not self.training and x.is_cuda and not torch.is_grad_enabled():
+            return self._forward_eval(batch)               # the GTA-dump / evaluation use (train_forward.py:33-51)
         tok_mask = make_token_len_mask(x.transpose(0, 1))
         dur_hat = self.dur_pred(x, x_cond=pitch_cond, speaker_emb=semb, src_pad_mask=tok_mask).squeeze(-1)
         pitch_hat = self.pitch_pred(x, x_cond=pitch_cond, speaker_emb=semb, src_pad_mask=tok_mask).transpose(1, 2)
@@ -175,9 +177,12 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError(f'sequence length {n} exceeds PositionalEncoding.max_len={tp.max_len} '
                                '(same limit as the reference, common_layers.py:129)')
 
-    def _token_program(self, st: dict, batch: int, T: int, predictors: bool) -> eng.Program:
+    def _token_program(self, st: dict, batch: int, T: int, predictors: bool, mask_predictors: bool = False,
+                       teacher_cond: bool = False) -> eng.Program:
         """Phase 1: pitch_cond_pred, energy_pred and the prenet transformer (level interleaved), arg-max of the pitch
-        condition (:242-243).  Phase 2: dur_pred and pitch_pred, which consume it (:244,248)."""
+        condition (:242-243).  Phase 2: dur_pred and pitch_pred, which consume it (:244,248).  Eval-mode forward(batch)
+        (:205-210): `mask_predictors` gives every predictor the token pad mask, `teacher_cond` takes the condition from
+        the caller-filled 'pitch_cond' buffer instead of the arg-max."""
         packs, h = st['packs'], st['handle']
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
@@ -212,7 +217,8 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         branches, outs = [], {}
         if predictors:
             for name in ('pitch_cond', 'energy'):
-                outs[name], lv = add_transformer(name, packs[name], packs[name + '_emb'], None, None)
+                outs[name], lv = add_transformer(name, packs[name], packs[name + '_emb'], None,
+                                                 tok if mask_predictors else None)
                 branches.append(lv)
         _, lv = add_transformer('prenet', packs['prenet'], packs['embedding'], None, tok)   # key mask x == 0 (:275)
         branches.append(lv)
@@ -220,10 +226,12 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         if predictors:
             logits = add_head('pitch_cond', outs['pitch_cond'])
             add_head('energy', outs['energy'])
-            prog.call(lambda: h.argmax(logits, batch * T, logits.shape[2], pcond), label='pitch_cond.argmax')
+            if not teacher_cond:
+                prog.call(lambda: h.argmax(logits, batch * T, logits.shape[2], pcond), label='pitch_cond.argmax')
             branches2 = []
             for name in ('dur', 'pitch'):
-                outs[name], lv = add_transformer(name, packs[name], packs[name + '_emb'], packs[name + '_cemb'], None)
+                outs[name], lv = add_transformer(name, packs[name], packs[name + '_emb'], packs[name + '_cemb'],
+                                                 tok if mask_predictors else None)
                 branches2.append(lv)
             eng.run_levels(prog, branches2)
             add_head('dur', outs['dur'])
@@ -231,8 +239,9 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         prog.alpha = 1.0
         return prog
 
-    def _frame_program(self, st: dict, batch: int, M: int) -> eng.Program:
-        """LR output -> postnet transformer (no mask) -> lin -> [B, n_mels, M]  (:293-298)."""
+    def _frame_program(self, st: dict, batch: int, M: int, masked: bool = False) -> eng.Program:
+        """LR output -> postnet transformer -> lin -> [B, n_mels, M]  (:293-298).  generate(): no mask; `masked`: keys
+        where the caller-filled prog.bufs['frame_tok'] is 0 are masked (forward(batch), :230-234)."""
         packs, h = st['packs'], st['handle']
         tp = packs['postnet']
         self._check_len(tp, M)
@@ -246,7 +255,8 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         mel = prog.dense('mel', (batch, self.n_mels, M))
         prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, M, geo.stride, x0, out_full=x0f),
                   label='postnet.posenc')
-        eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, None, x_full=x0f)])
+        frame_tok = prog.dense('frame_tok', (batch, M), torch.int64) if masked else None
+        eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, frame_tok, x_full=x0f)])
         prog.label('lin')
         prog.gemm(out, packs['lin'], None, out_t=mel)
         prog.flush()
@@ -282,6 +292,40 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
             pitch_hat = pitch_function(prog.bufs['pitch.y'].reshape(B, 1, T).clone())
             energy_hat = energy_function(prog.bufs['energy.y'].reshape(B, 1, T).clone())
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, pitch_cond_hat, scan)
+
+    def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """forward(batch) in eval mode under no_grad on the sm_100a kernels (multi_fast_pitch.py:192-245): predictors
+        and prenet with the token pad mask, dur / pitch conditioned on the target pitch condition, teacher-forced
+        durations / pitch / energy, postnet with the frame mask m >= mel_len[b], outputs cut / padded to the target."""
+        x, semb = batch['x'], batch['speaker_emb']
+        self._check_tokens(x)
+        self._check_speaker(x, semb, self.speaker_emb_dims)
+        st = self._accel_state(x.device)
+        B, T = x.shape
+        tok = self._program(st, ('tok_masked', B, T),
+                            lambda: self._token_program(st, B, T, True, mask_predictors=True, teacher_cond=True))
+        tok.bufs['tok'].copy_(x)
+        tok.bufs['semb'].copy_(semb.to(torch.float32))
+        tok.bufs['pitch_cond'].copy_(batch['pitch_cond'])
+        tok.alpha = 1.0
+        tok.run()
+        dur_hat = tok.bufs['dur.y'].reshape(B, T).clone()
+        pitch_hat = tok.bufs['pitch.y'].reshape(B, 1, T).clone()
+        energy_hat = tok.bufs['energy.y'].reshape(B, 1, T).clone()
+        pitch_cond_hat = tok.bufs['pitch_cond.y'].clone()                      # [B,T,3] logits
+        dur = batch['dur'].to(device=x.device, dtype=torch.float32).contiguous().clone()
+        cum, lens, M, _ = _accel.length_regulate(st['handle'], dur, apply_fallback=False)
+        if M <= 0:
+            raise RuntimeError('forward(): all durations are zero -- nothing to synthesise')
+        prog = self._program(st, ('frame_masked', B, M), lambda: self._frame_program(st, B, M, masked=True))
+        mel_len = batch['mel_len'].to(x.device)
+        prog.bufs['frame_tok'].copy_((torch.arange(M, device=x.device)[None, :] < mel_len[:, None]).to(torch.int64))
+        out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, tok.bufs['prenet.out'], None, 0, dur,
+                                           batch['pitch'].to(x.device), batch['energy'].to(x.device), cum, lens, M,
+                                           float(self.pitch_strength), float(self.energy_strength), round_tf32=False)
+        mel = self.pad(out['mel'], batch['mel'].size(2))
+        return {'mel': mel, 'mel_post': mel.clone(), 'pitch_cond': pitch_cond_hat, 'dur': dur_hat,
+                'pitch': pitch_hat, 'energy': energy_hat}
 
     def _generate_mel(self, x: torch.Tensor, speaker_emb: torch.Tensor, dur_hat: torch.Tensor,
                       pitch_hat: torch.Tensor, pitch_cond_hat: torch.Tensor,

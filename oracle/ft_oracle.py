@@ -577,3 +577,41 @@ def mfp_generate(sd: SD, x: torch.Tensor, speaker_emb: torch.Tensor, alpha: floa
     return {'mel': mel, 'mel_post': mel, 'dur': torch.from_numpy(dur_clamped), 'pitch': pitch_hat,
             'energy': energy_hat, 'pitch_cond': pitch_cond, 'pitch_cond_logits': pc_logits,
             'mel_lens': torch.from_numpy(lens)}
+
+
+@torch.no_grad()
+def mfp_forward(sd: SD, batch: Dict[str, torch.Tensor], pitch_strength: float = 1.0, energy_strength: float = 1.0,
+                heads: int = 2, padding_value: float = -11.5129) -> Dict[str, torch.Tensor]:
+    """MultiFastPitch.forward(batch) in eval mode (multi_fast_pitch.py:192-245): every predictor AND the prenet run
+    with the token pad mask (x == 0, :205-218), dur / pitch are conditioned on the TARGET pitch condition, the mel
+    branch is teacher forced and the postnet runs with the frame mask m >= mel_len[b] (:230-234)."""
+    x, semb, cond = batch['x'], batch['speaker_emb'], batch['pitch_cond']
+    key_pad = (x == 0)
+
+    def plain(p):
+        e = _with_speaker(F.embedding(x, sd[p + '.embedding.weight']), semb)
+        y = forward_transformer(sd, p + '.transformer', e, heads, key_pad)
+        return linear(y, sd[p + '.lin.weight'], sd[p + '.lin.bias'])
+
+    def conditional(p):
+        e = F.embedding(x, sd[p + '.embedding.weight'])
+        c = F.embedding(cond, sd[p + '.conditional_embedding.weight'])
+        y = forward_transformer(sd, p + '.transformer', _with_speaker(torch.cat([e, c], dim=2), semb), heads, key_pad)
+        return linear(y, sd[p + '.lin.weight'], sd[p + '.lin.bias'])
+
+    dur_hat = conditional('dur_pred').squeeze(-1)
+    pitch_hat = conditional('pitch_pred').transpose(1, 2)
+    pitch_cond_hat = plain('pitch_cond_pred')                                # [B,T,3]
+    energy_hat = plain('energy_pred').transpose(1, 2)
+    h = forward_transformer(sd, 'prenet', _with_speaker(F.embedding(x, sd['embedding.weight']), semb), heads, key_pad)
+    h = h + cond_projection(sd, 'pitch_proj', batch['pitch'].unsqueeze(1)) * pitch_strength
+    h = h + cond_projection(sd, 'energy_proj', batch['energy'].unsqueeze(1)) * energy_strength
+    expanded, _, _, _ = length_regulate_np(h.numpy(), batch['dur'].to(torch.float32).numpy().copy())
+    M = expanded.shape[1]
+    frame_pad = torch.arange(M)[None, :] >= batch['mel_len'][:, None]
+    h = forward_transformer(sd, 'postnet', torch.from_numpy(expanded), heads, frame_pad)
+    mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)
+    target = batch['mel'].shape[2]
+    mel = F.pad(mel[:, :, :target], [0, max(0, target - mel.shape[2]), 0, 0], 'constant', padding_value)
+    return {'mel': mel, 'mel_post': mel, 'dur': dur_hat, 'pitch': pitch_hat, 'energy': energy_hat,
+            'pitch_cond': pitch_cond_hat}

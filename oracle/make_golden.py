@@ -147,6 +147,15 @@ def fp_forward_case(name, B, T, seed):
     save(name, seed=seed, B=B, T=T, mel=out['mel'], dur=out['dur'], pitch=out['pitch'], energy=out['energy'])
 
 
+def mfp_forward_case(name, B, T, seed):
+    """MultiFastPitch.forward(batch) in eval mode (multi_fast_pitch.py:192-245)."""
+    model = build(MultiFastPitch, 'multispeaker.yaml', seed)
+    batch = synth.synth_batch(B, T, seed, speaker_dims=256)
+    out = model(batch)
+    save(name, seed=seed, B=B, T=T, mel=out['mel'], dur=out['dur'], pitch=out['pitch'], energy=out['energy'],
+         pitch_cond=out['pitch_cond'])
+
+
 class BatchedMultiFP(MultiFastPitch):
     """The reference with the ONE B=1-only line (multi_fast_pitch.py:243) replaced by a per-(b,t) arg-max;
     everything else is the reference's code."""
@@ -227,6 +236,10 @@ if __name__ == '__main__':
     if sys.argv[1:] == ['mftfwd']:
         with torch.no_grad():
             mft_forward_case('mft_forward_b4_t26', 4, 26, seed=12)
+        sys.exit(0)
+    if sys.argv[1:] == ['mfpfwd']:
+        with torch.no_grad():
+            mfp_forward_case('mfp_forward_b4_t26', 4, 26, seed=13)
         sys.exit(0)
     if sys.argv[1:] == ['fpfwd']:
         with torch.no_grad():

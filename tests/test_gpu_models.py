@@ -363,13 +363,16 @@ def test_long_sequence_properties():
     assert int(lens.min()) > 2048                      # spread durations at alpha 0.8: more than one frame per phoneme
 
 
-def test_fast_pitch_eval_forward_vs_reference_golden():
+@pytest.mark.parametrize('kind,golden,speaker_dims', [('fast_pitch', 'fp_forward_b4_t26', 0),
+                                                      ('multi_fast_pitch', 'mfp_forward_b4_t26', 256)])
+def test_fast_pitch_eval_forward_vs_reference_golden(kind, golden, speaker_dims):
     """forward(batch) in eval mode under no_grad on the kernels: token pad mask on predictors + prenet, frame mask on
-    the postnet (fast_pitch.py:122-165)."""
-    g = load_golden('fp_forward_b4_t26')
-    sd = synthetic_sd('fast_pitch', int(g['seed']))
-    model = _model('fast_pitch', sd)
-    batch = {k: v.to(DEV) for k, v in synth.synth_batch(int(g['B']), int(g['T']), int(g['seed'])).items()}
+    the postnet (fast_pitch.py:122-165; multi_fast_pitch.py:192-245 with the target pitch condition)."""
+    g = load_golden(golden)
+    sd = synthetic_sd(kind, int(g['seed']))
+    model = _model(kind, sd)
+    batch = {k: v.to(DEV) for k, v in synth.synth_batch(int(g['B']), int(g['T']), int(g['seed']),
+                                                        speaker_dims=speaker_dims).items()}
     with torch.no_grad():
         out = model(batch)
     torch.cuda.synchronize()
@@ -380,5 +383,6 @@ def test_fast_pitch_eval_forward_vs_reference_golden():
     got, want = out['mel'].cpu(), torch.from_numpy(g['mel'])
     assert max_abs(got[valid], want[valid]) < MEL_ABS and rel_l2(got[valid], want[valid]) < MEL_REL
     assert rel_l2(got, want) < MEL_REL
-    for k in ('dur', 'pitch', 'energy'):
+    for k in ('dur', 'pitch', 'energy') + (('pitch_cond',) if speaker_dims else ()):
+        assert out[k].shape == g[k].shape, k
         assert max_abs(out[k].cpu()[:, ...], g[k]) < 1e-2, k

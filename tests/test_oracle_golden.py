@@ -162,3 +162,14 @@ def test_fast_pitch_eval_forward():
     for k in ('mel', 'dur', 'pitch', 'energy'):
         assert out[k].shape == g[k].shape, k
         assert max_abs(out[k], g[k]) < 2e-4, k
+
+
+def test_multi_fast_pitch_eval_forward():
+    """MultiFastPitch.forward(batch) in eval mode: token mask everywhere, target pitch condition, frame mask."""
+    from forwardtacotron_b200 import synth
+    g = load_golden('mfp_forward_b4_t26')
+    sd = synthetic_sd('multi_fast_pitch', int(g['seed']))
+    out = O.mfp_forward(sd, synth.synth_batch(int(g['B']), int(g['T']), int(g['seed']), speaker_dims=256))
+    for k in ('mel', 'dur', 'pitch', 'energy', 'pitch_cond'):
+        assert out[k].shape == g[k].shape, k
+        assert max_abs(out[k], g[k]) < 2e-4, k
