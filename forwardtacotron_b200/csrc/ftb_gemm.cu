@@ -15,7 +15,11 @@
 //
 // Precision: operands are fp32 in memory, pre-rounded to tf32 (cvt.rna) by their
 // producers, so the tensor core's mantissa truncation is exact; accumulation is fp32.
+// FTB_F_A_F16 problems keep both operands in fp16 instead (same 11-bit significand; kind::f16 runs at twice the
+// tf32 rate on half the bytes): a 128-byte swizzle row then holds 64 channels and one MMA consumes K = 16.
+// FTB_F_OUT_F16 problems store their result as fp16 for such a consumer.
 #include <cstdio>
+#include <cuda_fp16.h>
 
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
@@ -105,9 +109,10 @@ struct EpiCtx {
   float relu_lo;                 // 0 (ReLU) or -inf
   const float* residual;
   float* out; float* out_full; float* out_t;    // out / out_full already offset by out_col0
+  __half* out16;                                // FTB_F_OUT_F16: the fp16 output (offset by out_col0), `out` is null
 };
 
-template <bool POOL, bool RES, bool FULL, bool OUTT, bool RND>
+template <bool POOL, bool RES, bool FULL, bool OUTT, bool RND, bool OUT16 = false>
 __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
   const int lane = c.lane, sub = lane >> 3, part = lane & 7;
   // phase-B base pointers: row (r_warp + sub), column n0 + 4*part; +32 columns per chunk, +4 rows per i8
@@ -116,6 +121,9 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
   float* fptr = FULL ? c.out_full + orow : nullptr;
   const float* rptr = RES ? c.residual + (c.r_warp + sub) * c.res_ld + c.n0 + 4 * part : nullptr;
   const long long ostep = 4ll * c.out_ld, rstep = 4ll * c.res_ld;
+  // fp16 output: lane = (row r8 of 8, 8 consecutive columns c8): 16-byte stores, 64-byte row segments
+  const int r8 = lane >> 2, c8 = lane & 3;
+  __half* o16 = OUT16 ? c.out16 + (c.r_warp + r8) * c.out_ld + c.n0 + 8 * c8 : nullptr;
   float4 xr_cur[RES ? 8 : 1], xr_nxt[RES ? 8 : 1];
   auto load_res = [&](float4 (&dst)[RES ? 8 : 1], int c0) {
     if (RES) {
@@ -182,7 +190,36 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
           if (c0 + j < c.bn && nb + j < c.N) ot[static_cast<long long>(j) * c.seq_len] = v[j];
       }
     }
-    if (optr) {
+    if (OUT16) {
+      const bool cols_ok = c0 + 8 * c8 < c.bn && nb + 8 * c8 < c.N;          // N, nb and bn are multiples of 8
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if ((lane >> 4) == h) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; j += 4)
+            *reinterpret_cast<float4*>(&c.stg[lane & 15][j]) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+        __syncwarp();
+        if (cols_ok) {
+#pragma unroll
+          for (int i2 = 0; i2 < 2; ++i2) {
+            const int row = h * 16 + i2 * 8 + r8;
+            if ((c.smask >> row) & 1u) {
+              const float4 y0 = *reinterpret_cast<const float4*>(&c.stg[row & 15][8 * c8]);
+              const float4 y1 = *reinterpret_cast<const float4*>(&c.stg[row & 15][8 * c8 + 4]);
+              uint4 pk;
+              __half2 t;
+              t = __floats2half2_rn(y0.x, y0.y); pk.x = *reinterpret_cast<const uint32_t*>(&t);
+              t = __floats2half2_rn(y0.z, y0.w); pk.y = *reinterpret_cast<const uint32_t*>(&t);
+              t = __floats2half2_rn(y1.x, y1.y); pk.z = *reinterpret_cast<const uint32_t*>(&t);
+              t = __floats2half2_rn(y1.z, y1.w); pk.w = *reinterpret_cast<const uint32_t*>(&t);
+              *reinterpret_cast<uint4*>(o16 + static_cast<long long>(h * 16 + i2 * 8) * c.out_ld + c0) = pk;
+            }
+          }
+        }
+        __syncwarp();
+      }
+    } else if (optr) {
       // a half chunk (bn = 16 mod 32) must not spill into the columns of the next n-tile
       const bool cols_ok = c0 + 4 * part < c.bn && nb + 4 * part < c.N;      // N, nb and bn are multiples of 4
 #pragma unroll
@@ -233,6 +270,11 @@ __device__ __forceinline__ void epi_disp_full(const EpiCtx& c, bool full, bool o
   else epi_disp_outt<POOL, RES, false>(c, outt, rnd);
 }
 __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool res, bool full, bool outt, bool rnd) {
+  if (c.out16) {                                                  // fp16 output: plain / pooled, nothing else
+    if (pool) epi_affine_tile<true, false, false, false, false, true>(c);
+    else epi_affine_tile<false, false, false, false, false, true>(c);
+    return;
+  }
   if (pool) epi_disp_full<true, false>(c, full, outt, rnd);     // pooled layers (CBHG bank) never carry a residual
   else if (res) epi_disp_full<false, true>(c, full, outt, rnd);
   else epi_disp_full<false, false>(c, full, outt, rnd);
@@ -298,6 +340,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         // problem fields -> registers: the "memory" clobbers of the barrier/TMA asm would otherwise force a
         // re-load of every p->field from global memory inside the loops
         const int taps = p->taps, kblocks = p->kblocks, tap0 = p->tap0, w_tap_rows = p->w_tap_rows;
+        const int kelems = p->kelems;
         const CUtensorMap* tm_a = &p->tm_a;
         const CUtensorMap* tm_w = &p->tm_w;
         // channel block outer, taps inner: the taps of one channel block re-read the same activation rows shifted by
@@ -309,8 +352,8 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             uint8_t* sa = smem + stage * STAGE_BYTES;
             uint8_t* sb = sa + A_STAGE_BYTES;
             mbar_expect_tx(&tail->full[stage], tx);
-            tma_load_2d(sa, tm_a, &tail->full[stage], kb * BK, tc.m0 + tap0 + tap);
-            tma_load_2d(sb, tm_w, &tail->full[stage], kb * BK, tap * w_tap_rows + tc.n0);
+            tma_load_2d(sa, tm_a, &tail->full[stage], kb * kelems, tc.m0 + tap0 + tap);
+            tma_load_2d(sb, tm_w, &tail->full[stage], kb * kelems, tap * w_tap_rows + tc.n0);
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           }
         }
@@ -330,7 +373,8 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         GP_T0 mbar_wait(&tail->tmem_empty[buf], ((it >> 1) & 1u) ^ 1u); GP_ACC(1)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
-        const uint32_t idesc = umma_idesc_tf32(BM, p->bn);
+        const bool f16 = (p->flags & FTB_F_A_F16) != 0;
+        const uint32_t idesc = f16 ? umma_idesc_f16(BM, p->bn) : umma_idesc_tf32(BM, p->bn);
         const int kiters = p->taps * p->kblocks;
         for (int ki = 0; ki < kiters; ++ki) {
           GP_T0 mbar_wait(&tail->full[stage], phase); GP_ACC(2)
@@ -338,10 +382,13 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
           const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa);
           const uint64_t db = umma_desc_sw128(sa + A_STAGE_BYTES);
+          // +32 bytes per MMA (8 tf32 / 16 fp16 channels) inside the 128-byte swizzle row: +2 in (addr >> 4) units
+          if (f16) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            // +32 bytes per UMMA_K step inside the 128-byte swizzle row: +2 in (addr >> 4) units
-            umma_tf32(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / UMMA_K; ++k) umma_f16_ss(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
+          } else {
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
           }
           umma_commit(&tail->empty[stage]);     // frees the smem slot when these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -419,7 +466,6 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(g * 32) << 16);
       const bool relu = (P_flags & FTB_F_RELU) != 0;
       const bool rnd = (P_flags & FTB_F_ROUND_TF32) != 0;
-      const int sub = lane >> 3, part = lane & 7;               // phase-B coordinates
 
       if (highway) {
         // Phase A (lane = row): x1/x2 chunks of 16 units from TMEM, this row's residual (prefetched one chunk
@@ -480,7 +526,9 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         c.res_ld = P_res_ld; c.out_ld = P_out_ld; c.smask = smask; c.store = store; c.r = r; c.r_warp = r_warp;
         c.relu_lo = relu ? 0.0f : -INFINITY;
         c.residual = P_residual;
-        c.out = P_out ? P_out + P_out_col0 : nullptr;
+        const bool out16 = (P_flags & FTB_F_OUT_F16) != 0;
+        c.out = (P_out && !out16) ? P_out + P_out_col0 : nullptr;
+        c.out16 = out16 ? reinterpret_cast<__half*>(P_out) + P_out_col0 : nullptr;
         c.out_full = P_out_full ? P_out_full + P_out_col0 : nullptr;
         c.out_t = P_out_t;
         epi_dispatch(c, pool, P_residual != nullptr && P_out_t == nullptr, P_out_full != nullptr, P_out_t != nullptr, rnd);
@@ -515,6 +563,12 @@ __device__ __forceinline__ float simt_acc(const GemmProblemDev* p, long long r, 
   for (int tap = 0; tap < p->taps; ++tap) {
     const long long ra = r + p->tap0 + tap;
     if (ra < 0 || ra >= p->rows) continue;
+    if (p->flags & FTB_F_A_F16) {
+      const __half* a = reinterpret_cast<const __half*>(p->a) + ra * p->lda;
+      const __half* w = reinterpret_cast<const __half*>(p->w) + (static_cast<long long>(tap) * p->w_tap_rows + wrow) * p->cin;
+      for (int c = 0; c < p->cin; ++c) acc = fmaf(__half2float(a[c]), __half2float(w[c]), acc);
+      continue;
+    }
     const float* a = p->a + ra * p->lda;
     const float* w = p->w + (static_cast<long long>(tap) * p->w_tap_rows + wrow) * p->cin;
     for (int c = 0; c < p->cin; ++c) acc = fmaf(a[c], w[c], acc);
@@ -547,7 +601,9 @@ __global__ void conv_gemm_simt_kernel(const GemmProblemDev* __restrict__ probs, 
       if (p->out_t) p->out_t[(static_cast<long long>(b) * N + n) * p->seq_len + t] = v;
     }
     if (p->out_full) p->out_full[r * p->out_ld + p->out_col0 + n] = v;
-    if (p->out) p->out[r * p->out_ld + p->out_col0 + n] = epi_finish(p, v);
+    if (p->out && (p->flags & FTB_F_OUT_F16))
+      reinterpret_cast<__half*>(p->out)[r * p->out_ld + p->out_col0 + n] = __float2half_rn(v);
+    else if (p->out) p->out[r * p->out_ld + p->out_col0 + n] = epi_finish(p, v);
   }
 }
 
@@ -569,15 +625,16 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D fp32 row-major [rows, cols] (leading dimension ld floats), box {32, box_rows}, 128B swizzle.
-static int make_map(CUtensorMap* m, const float* base, long long rows, int cols, int ld, int box_rows) {
+// 2-D row-major [rows, cols] fp32 or fp16 (leading dimension ld elements), box {128 bytes, box_rows}, 128B swizzle.
+static int make_map(CUtensorMap* m, const void* base, long long rows, int cols, int ld, int box_rows, bool f16) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return FTB_E_DRIVER;
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
-  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 4};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), static_cast<cuuint32_t>(box_rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * (f16 ? 2 : 4)};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(f16 ? 2 * BK : BK), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult res = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+  CUresult res = enc(m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                     const_cast<void*>(base), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return res == CUDA_SUCCESS ? 0 : FTB_E_SHAPE;
@@ -597,10 +654,13 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     if (q.rows < 1 || q.cin < 1 || q.taps < 1 || q.n < 1) return FTB_E_ARG;
     if (q.bn < 16 || q.bn > 256 || (q.bn % 16) != 0) return FTB_E_SHAPE;
     if (q.w_tap_rows < q.n || (q.w_tap_rows % q.bn) != 0) return FTB_E_SHAPE;
-    if ((q.lda % 4) != 0 || (q.cin % 4) != 0 || q.cin > q.lda) return FTB_E_ALIGN;
+    const bool a16 = (q.flags & FTB_F_A_F16) != 0, o16 = (q.flags & FTB_F_OUT_F16) != 0;
+    const int amul = a16 ? 8 : 4, omul = o16 ? 8 : 4;        // elements per 16 bytes
+    if ((q.lda % amul) != 0 || (q.cin % amul) != 0 || q.cin > q.lda) return FTB_E_ALIGN;
     if (!aligned16(q.a) || !aligned16(q.w)) return FTB_E_ALIGN;
-    if (q.out && (!aligned16(q.out) || (q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0)) return FTB_E_ALIGN;
-    if (q.out && (q.n % 4) != 0) return FTB_E_SHAPE;          // row segments are stored as float4
+    if (q.out && (!aligned16(q.out) || (q.out_ld % omul) != 0 || (q.out_col0 % omul) != 0)) return FTB_E_ALIGN;
+    if (q.out && (q.n % omul) != 0) return FTB_E_SHAPE;       // row segments are stored as 16-byte vectors
+    if (o16 && (!q.out || q.residual || q.out_t || q.out_full || q.epilogue == FTB_EPI_HIGHWAY)) return FTB_E_ARG;
     if (q.residual && ((q.res_ld % 4) != 0 || !aligned16(q.residual))) return FTB_E_ALIGN;
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
     if (q.rows != static_cast<long long>(q.batch) * q.seq_stride) return FTB_E_ARG;
@@ -611,14 +671,15 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     } else if (q.epilogue != FTB_EPI_AFFINE && q.epilogue != FTB_EPI_MAXPOOL) {
       return FTB_E_ARG;
     }
-    d.a = q.a; d.w = q.w; d.bias0 = q.bias0; d.scale = q.scale; d.shift = q.shift;
-    d.residual = q.residual; d.out = q.out; d.out_t = q.out_t; d.out_full = q.out_full;
+    d.a = static_cast<const float*>(q.a); d.w = static_cast<const float*>(q.w); d.bias0 = q.bias0; d.scale = q.scale; d.shift = q.shift;
+    d.residual = q.residual; d.out = static_cast<float*>(q.out); d.out_t = q.out_t; d.out_full = q.out_full;
     if (q.out_full && (!q.out || !aligned16(q.out_full))) return FTB_E_ALIGN;
     d.rows = q.rows; d.lda = q.lda; d.cin = q.cin; d.taps = q.taps; d.tap0 = q.tap0;
     d.w_tap_rows = q.w_tap_rows; d.n = q.n; d.bn = q.bn; d.epilogue = q.epilogue; d.flags = q.flags;
     d.res_ld = q.res_ld; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
     d.batch = q.batch; d.seq_len = q.seq_len; d.seq_stride = q.seq_stride;
-    d.kblocks = (q.cin + BK - 1) / BK;
+    d.kelems = a16 ? 2 * BK : BK;
+    d.kblocks = (q.cin + d.kelems - 1) / d.kelems;
     d.n_tiles = (q.n + q.bn - 1) / q.bn;
     if (q.epilogue == FTB_EPI_MAXPOOL) {
       d.m_step = BM - 1; d.m_shift = -1;
@@ -628,9 +689,9 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     d.m_tiles = static_cast<int>((q.rows + d.m_step - 1) / d.m_step);
     d.tile_base = tile_base;
     tile_base += d.m_tiles * d.n_tiles;
-    int rc = make_map(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM);
+    int rc = make_map(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
     if (rc) return rc;
-    rc = make_map(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, q.bn);
+    rc = make_map(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, q.bn, a16);
     if (rc) return rc;
     const long long e = q.rows * q.n;
     if (e > simt_elems) simt_elems = e;

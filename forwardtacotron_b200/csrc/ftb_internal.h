@@ -17,7 +17,7 @@ namespace ftb {
 struct alignas(128) GemmProblemDev {
   CUtensorMap tm_a;      // A [rows, cin] fp32, box {32, 128}, SWIZZLE_128B
   CUtensorMap tm_w;      // W [taps*w_tap_rows, cin] fp32, box {32, bn}, SWIZZLE_128B
-  const float* a;
+  const float* a;        // fp16 data when FTB_F_A_F16 (only the SIMT cross-check kernel dereferences a / w)
   const float* w;
   const float* bias0;
   const float* scale;
@@ -30,11 +30,11 @@ struct alignas(128) GemmProblemDev {
   int lda, cin, taps, tap0, w_tap_rows, n, bn, epilogue, flags;
   int res_ld, out_ld, out_col0;
   int batch, seq_len, seq_stride;
-  int kblocks;           // ceil(cin / 32)
+  int kblocks;           // ceil(cin / kelems)
   int m_tiles, n_tiles;  // tile grid of this problem
   int m_step, m_shift;   // tile i covers rows [i*m_step + m_shift, +128)
   int tile_base;         // first global tile id
-  int pad_[1];
+  int kelems;            // operand elements per 128-byte k-block: 32 (tf32) or 64 (fp16, FTB_F_A_F16)
 };
 
 struct GemmPlan {

@@ -15,11 +15,15 @@ from . import runtime as rt
 from .pack import PackedGemm, PackedRnn
 
 
+_F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
+
+
 def _tile_cost(q) -> float:
     """Cycles one 128 x bn tile keeps a CTA busy (ftb_gemm.cu): the MMAs (4 per 32-channel block and tap, bn/2 cycles
     each for kind::tf32) against the epilogue of its bn/32 chunks (two warp sets drain alternate tiles), plus the
     per-tile fixed cost."""
-    mma = q.taps * ((q.cin + 31) // 32) * 2.0 * q.bn
+    kelems = 64 if (q.flags & rt.F_A_F16) else 32           # channels per 128-byte k-block
+    mma = q.taps * ((q.cin + kelems - 1) // kelems) * 2.0 * q.bn
     epi = (q.bn / 32.0) * 1800.0 / 2.0
     return max(mma, epi) + 1500.0
 
@@ -61,12 +65,13 @@ class Program:
         self._eager_runs = 0
 
     # ---- buffers ---------------------------------------------------------------------------
-    def buf(self, name: str, cols: int) -> torch.Tensor:
-        """Zero-initialised [rows, cols] activation; gap rows are never written so they stay zero."""
+    def buf(self, name: str, cols: int, dtype=torch.float32) -> torch.Tensor:
+        """Zero-initialised [rows, cols] activation; gap rows are never written so they stay zero.  fp16 buffers are
+        GEMM-to-GEMM operands (FTB_F_OUT_F16 producer, FTB_F_A_F16 consumer)."""
         if name not in self.bufs:
-            self.bufs[name] = torch.zeros((self.geo.rows, cols), dtype=torch.float32, device=self.device)
+            self.bufs[name] = torch.zeros((self.geo.rows, cols), dtype=dtype, device=self.device)
         b = self.bufs[name]
-        assert b.shape[1] == cols, (name, b.shape, cols)
+        assert b.shape[1] == cols and b.dtype == dtype, (name, b.shape, cols, b.dtype)
         return b
 
     def dense(self, name: str, shape, dtype=torch.float32) -> torch.Tensor:
@@ -90,9 +95,14 @@ class Program:
         p.a, p.rows, p.lda = a.data_ptr(), g.rows, a.shape[1]
         p.cin = cin if cin is not None else w.cin
         assert p.cin == w.cin and p.cin <= a.shape[1], (p.cin, w.cin, a.shape)
-        p.w, p.taps, p.tap0, p.w_tap_rows = w.w.data_ptr(), w.taps, w.tap0, w.n_pad
+        a16 = a.dtype == torch.float16
+        o16 = out is not None and out.dtype == torch.float16
+        wt = w.w16 if a16 else w.w
+        p.w, p.taps, p.tap0, p.w_tap_rows = wt.data_ptr(), w.taps, w.tap0, w.n_pad
         p.n, p.bn, p.epilogue = w.n, w.bn, epilogue
-        p.flags = (rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out else 0)
+        p.flags = ((rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out and not o16 else 0) |
+                   (rt.F_A_F16 if a16 else 0) | (rt.F_OUT_F16 if o16 else 0))
+        assert not o16 or (residual is None and out_t is None and out_full is None), 'fp16 output: plain epilogue only'
         p.bias0, p.scale, p.shift = rt.ptr(w.bias0), rt.ptr(w.scale), rt.ptr(w.shift)
         p.residual = rt.ptr(residual)
         p.res_ld = residual.shape[1] if residual is not None else 0
@@ -105,7 +115,7 @@ class Program:
         p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
         p._label = self._label
         self._pending.append(p)
-        self._keep += [a, w, out, residual, out_t, out_full]
+        self._keep += [a, w, wt, out, residual, out_t, out_full]
 
     def flush(self):
         """Close the current group: everything queued since the last flush runs as one launch."""
@@ -244,8 +254,11 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     level i may be queued only after level i-1 has been flushed.  The last entry runs the BiGRU."""
     K = len(c.bank)
     ch = c.channels
-    bank = prog.buf(f'{tag}.bank', K * ch)
-    p1 = prog.buf(f'{tag}.proj1', c.proj1.n)
+    # bank -> proj1 -> proj2 are GEMM-to-GEMM hand-offs with K = 3 * K*ch and 3 * proj1.n: fp16 operands (the same
+    # 11-bit significand the tf32 path keeps) halve their traffic and double the MMA rate
+    f16 = _F16_OPERANDS and (K * ch) % 8 == 0 and c.proj1.n % 8 == 0
+    bank = prog.buf(f'{tag}.bank', K * ch, torch.float16 if f16 else torch.float32)
+    p1 = prog.buf(f'{tag}.proj1', c.proj1.n, torch.float16 if f16 else torch.float32)
     p2 = prog.buf(f'{tag}.proj2', c.proj2.n)
     hw = [prog.buf(f'{tag}.hw0', ch), prog.buf(f'{tag}.hw1', ch)]
     # unrounded twins of the highway activations: the residual term (1-g)*x uses full fp32 values, only the

@@ -44,6 +44,16 @@ class PackedGemm:
         self.n_pad = w.shape[1]
         self.cin = w.shape[2]
         self.bias0, self.scale, self.shift, self.relu = bias0, scale, shift, relu
+        self._w16 = None
+
+    @property
+    def w16(self) -> torch.Tensor:
+        """The same packed weight in fp16 (FTB_F_A_F16 problems): tf32-rounded values have an 11-bit significand, so
+        the conversion is exact inside fp16's exponent range (|w| < 6e-5 loses relative, not absolute, precision)."""
+        if self._w16 is None:
+            assert self.cin % 8 == 0, 'fp16 operands need cin % 8 == 0 (16-byte TMA rows)'
+            self._w16 = self.w.to(torch.float16).contiguous()
+        return self._w16
 
 
 def _f(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:

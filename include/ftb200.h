@@ -71,14 +71,19 @@ int64_t ftb_launch_count(ftb_handle h);
  *   Only rows with (r % seq_stride) < seq_len are stored; null bias0/scale/shift mean 0/1/0.
  * ------------------------------------------------------------------------------------ */
 enum { FTB_EPI_AFFINE = 0, FTB_EPI_MAXPOOL = 1, FTB_EPI_HIGHWAY = 2 };
-enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2 };
+/* FTB_F_A_F16  : `a` and `w` hold IEEE fp16 (same 11-bit significand as tf32; lda / cin counted in fp16 elements,
+ *                multiples of 8); the MMAs are kind::f16 with fp32 accumulation -- twice the tensor rate and half
+ *                the operand traffic of tf32.  Used where the producer of `a` is another K1/K2 problem.
+ * FTB_F_OUT_F16: `out` is fp16 [rows, out_ld] (out_ld, out_col0, n multiples of 8), rounded to nearest; only with
+ *                AFFINE / MAXPOOL, without residual / out_t / out_full; ROUND_TF32 is ignored.                  */
+enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2, FTB_F_A_F16 = 4, FTB_F_OUT_F16 = 8 };
 
 typedef struct {
-  const float* a;        /* [rows, lda] activations (tf32-rounded by their producer)         */
+  const void* a;         /* [rows, lda] activations: fp32 tf32-rounded by their producer, or fp16 (A_F16) */
   int64_t rows;          /* batch * seq_stride                                               */
   int32_t lda;           /* floats, multiple of 4                                            */
   int32_t cin;           /* reduction extent per tap (<= lda)                                */
-  const float* w;        /* packed [taps][w_tap_rows][cin] fp32, tf32-rounded                 */
+  const void* w;         /* packed [taps][w_tap_rows][cin] fp32 tf32-rounded, or fp16 (A_F16)   */
   int32_t taps, tap0;    /* tap j reads row r + tap0 + j   (tap0 = -(k/2))                   */
   int32_t w_tap_rows;    /* rows per tap in w (n rounded up to a multiple of bn)             */
   int32_t n;             /* output channels (HIGHWAY: 2*units)                               */
@@ -90,7 +95,7 @@ typedef struct {
   const float* shift;    /* [n] or null                                                      */
   const float* residual; /* [rows, res_ld] or null                                           */
   int32_t res_ld;
-  float* out;            /* [rows, out_ld], written at columns out_col0 + n; may be null      */
+  void* out;             /* [rows, out_ld] fp32 (fp16 with OUT_F16), written at columns out_col0 + n; may be null */
   int32_t out_ld, out_col0;
   float* out_t;          /* optional [batch, n, seq_len] transposed, never rounded; or null  */
   int32_t batch, seq_len, seq_stride;

@@ -77,6 +77,50 @@ def test_conv_bn(B, L, cin, cout, k, relu):
     assert float(out.view(g.batch, g.stride, cout)[:, g.seq_len:].abs().max()) == 0.0
 
 
+@pytest.mark.parametrize('B,L,cin,cout,k,relu,pool,in16,out16', [
+    (2, 130, 256, 256, 3, True, False, True, False),     # fp16 operands, fp32 result (CBHG proj2)
+    (2, 130, 2048, 256, 3, True, False, True, True),      # fp16 operands and result (CBHG proj1, K = 3 x 2048)
+    (3, 70, 80, 256, 4, True, True, False, True),         # tf32 operands, pooled fp16 result (postnet bank conv)
+    (2, 200, 256, 128, 16, True, True, True, True),       # fp16 both sides, pooled, N = 128 < one chunk group
+    (1, 50, 72, 48, 5, False, False, True, True),         # K tail (72 of 128 per k-block), half chunk (bn = 48)
+])
+def test_conv_fp16_operands(B, L, cin, cout, k, relu, pool, in16, out16):
+    """FTB_F_A_F16 / FTB_F_OUT_F16: fp16 GEMM-to-GEMM hand-off buffers (kind::f16 MMAs, fp16 row-segment stores)."""
+    gen = torch.Generator().manual_seed(B * 100 + L + k)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    v = torch.randn(B, L, cin, generator=gen).to(torch.float16 if in16 else torch.float32)
+    if not in16:
+        v = pk.round_tf32(v)
+    a = prog.buf('a', cin, torch.float16 if in16 else torch.float32)
+    a.view(g.batch, g.stride, cin)[:, :L] = v.to(DEV)
+    w = torch.randn(cout, cin, k, generator=gen) / (cin * k) ** 0.5
+    gamma, beta = torch.rand(cout, generator=gen) + 0.5, torch.randn(cout, generator=gen) * 0.1
+    mean, var = torch.randn(cout, generator=gen) * 0.1, torch.rand(cout, generator=gen) + 0.5
+    packed = pk.pack_bn_conv(w.to(DEV), gamma.to(DEV), beta.to(DEV), mean.to(DEV), var.to(DEV), relu)
+    out = prog.buf('out', cout + 8, torch.float16 if out16 else torch.float32)     # written at column 8
+    prog.gemm(a, packed, out, out_col0=8, epilogue=rt.EPI_MAXPOOL if pool else rt.EPI_AFFINE, round_out=False)
+    prog.flush()
+    w_used = (packed.w16 if in16 else packed.w).cpu().double()[:, :cout, :].permute(1, 2, 0)     # [cout, cin, k]
+    y = _conv_ref(v.double(), w_used, k)
+    if relu:
+        y = y.clamp_min(0)
+    sc = (gamma / torch.sqrt(var + 1e-5)).double()
+    ref = y * sc + (beta.double() - mean.double() * sc)
+    if pool:
+        ref = F.max_pool1d(ref.transpose(1, 2), kernel_size=2, stride=1, padding=1)[:, :, :L].transpose(1, 2)
+    tol = 2e-4 + (float(ref.abs().max()) * 2.0 ** -11 if out16 else 0.0)
+    for impl in (1, 0):
+        out.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        got = out.view(g.batch, g.stride, cout + 8)[:, :L, 8:].cpu().double()
+        assert max_abs(got, ref) < tol, f'impl={impl}'
+        assert float(out[:, :8].abs().max()) == 0.0 and float(out.view(g.batch, g.stride, -1)[:, L:].abs().max()) == 0.0
+    prog.h.impl = 0
+
+
 def test_bank_maxpool_matches_reference_semantics():
     """conv bank (k=1..6) + MaxPool1d(2,1,1)[:L] fused epilogue vs torch ops (common_layers.py:97-105)."""
     B, L, cin, ch, K = 2, 200, 64, 64, 6
