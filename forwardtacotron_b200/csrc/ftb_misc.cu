@@ -1,30 +1,39 @@
 // Small glue kernels: embedding gather into the padded-flat layout, predictor head
 // (row dot products), arg-max over a tiny class axis.  All are bandwidth/latency trivial
 // next to the GEMMs and recurrences; one warp per row, coalesced accesses.
+#include <cuda_fp16.h>
+
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
 
 namespace ftb {
 
+// mode: 0 = fp32 as stored, 1 = fp32 rounded to tf32, 2 = fp16 (out is a __half array, out_ld in halves): the operand
+// copy of a buffer a FTB_F_A_F16 GEMM problem reads.
+__device__ __forceinline__ void embed_store(float* out, long long i, float v, int mode) {
+  if (mode == 2) reinterpret_cast<__half*>(out)[i] = __float2half_rn(v);
+  else out[i] = mode ? round_tf32(v) : v;
+}
+
 __global__ void __launch_bounds__(256)
 embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
              const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
              const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
-             float* __restrict__ out, int out_ld, int round) {
+             float* __restrict__ out, int out_ld, int mode) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
   if (row >= static_cast<long long>(batch) * T) return;
   const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
-  float* o = out + (static_cast<long long>(b) * seq_stride + t) * out_ld;
+  const long long o = (static_cast<long long>(b) * seq_stride + t) * out_ld;
   const float* s1 = table + tok[row] * e1;
-  for (int c = lane; c < e1; c += 32) o[c] = round ? round_tf32(s1[c]) : s1[c];
+  for (int c = lane; c < e1; c += 32) embed_store(out, o + c, s1[c], mode);
   if (e2 > 0) {
     const float* s2 = table2 + tok2[row] * e2;
-    for (int c = lane; c < e2; c += 32) o[e1 + c] = round ? round_tf32(s2[c]) : s2[c];
+    for (int c = lane; c < e2; c += 32) embed_store(out, o + e1 + c, s2[c], mode);
   }
   if (e3 > 0) {
     const float* s3 = extra + static_cast<long long>(b) * e3;
-    for (int c = lane; c < e3; c += 32) o[e1 + e2 + c] = round ? round_tf32(s3[c]) : s3[c];
+    for (int c = lane; c < e3; c += 32) embed_store(out, o + e1 + e2 + c, s3[c], mode);
   }
 }
 
@@ -76,7 +85,7 @@ extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, i
   if (!h || !tok || !table || !out || e1 < 1 || batch < 1 || T < 1) return FTB_E_ARG;
   if (e2 > 0 && (!tok2 || !table2)) return FTB_E_ARG;
   if (e3 > 0 && !extra) return FTB_E_ARG;
-  if (e1 + e2 + e3 > out_ld || seq_stride < T) return FTB_E_ARG;
+  if (e1 + e2 + e3 > out_ld || seq_stride < T || round_tf32 < 0 || round_tf32 > 2) return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * T;
   embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, round_tf32);

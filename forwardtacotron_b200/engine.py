@@ -15,7 +15,7 @@ from . import runtime as rt
 from .pack import PackedGemm, PackedRnn
 
 
-_F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
+F16_OPERANDS = _F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -302,7 +302,9 @@ class PredictorPack:
 
 def predictor_levels(prog: Program, tag: str, p: PredictorPack, emb: torch.Tensor):
     ch = p.convs[0].n
-    c = [prog.buf(f'{tag}.c0', ch), prog.buf(f'{tag}.c1', ch)]
+    # conv0 -> conv1 -> conv2 -> gru_ih are GEMM-to-GEMM hand-offs: fp16 operand buffers (see cbhg_levels)
+    cdt = torch.float16 if (_F16_OPERANDS and ch % 8 == 0) else torch.float32
+    c = [prog.buf(f'{tag}.c0', ch, cdt), prog.buf(f'{tag}.c1', ch, cdt)]
     xp = prog.buf(f'{tag}.xproj', p.rnn.ih.n)
     h = prog.buf(f'{tag}.h', 2 * p.rnn.hidden)
     def named(name, fn):

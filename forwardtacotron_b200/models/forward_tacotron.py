@@ -157,7 +157,9 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                 grus.append(gru)
                 heads.append((name, p, hbuf))
         if prenet:
-            emb = prog.buf('emb', packs['embedding'].shape[1])
+            # the bank's operand copy of the embedding: fp16 (kind::f16 MMAs); the residual uses emb_full below
+            E = packs['embedding'].shape[1]
+            emb = prog.buf('emb', E, torch.float16 if (eng.F16_OPERANDS and E % 8 == 0) else torch.float32)
             prog.call(lambda: h.embed(tok, packs['embedding'], emb, emb.shape[1], batch, T, geo.stride))
             embf = prog.buf('emb_full', emb.shape[1])         # unrounded copy: the CBHG residual (:114)
             prog.call(lambda: h.embed(tok, packs['embedding_full'], embf, embf.shape[1], batch, T, geo.stride,

@@ -187,8 +187,9 @@ class Handle:
         e1 = table.shape[1]
         e2 = table2.shape[1] if table2 is not None else 0
         e3 = extra.shape[1] if extra is not None else 0
+        mode = 2 if out.dtype == torch.float16 else int(round_tf32)       # fp16 operand copy / tf32-rounded / as stored
         self.check(self.lib.ftb_embed(self.h, ptr(tok), ptr(table), e1, ptr(tok2), ptr(table2), e2, ptr(extra), e3,
-                                      batch, T, stride, ptr(out), out_ld, int(round_tf32), self.stream()))
+                                      batch, T, stride, ptr(out), out_ld, mode, self.stream()))
 
     def rowdot(self, x, x_ld, k, w, bias, n_out, alpha, batch, T, stride, y):
         self.check(self.lib.ftb_rowdot(self.h, ptr(x), x_ld, k, ptr(w), ptr(bias), n_out, float(alpha),

@@ -188,7 +188,9 @@ int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void* stream);
  * ------------------------------------------------------------------------------------ */
 /* nn.Embedding (forward_tacotron.py:31,210) (+ concatenated conditioning embedding and speaker
  * vector, multi_forward_tacotron.py:40-42,82-86) into the padded-flat layout:
- * out[b*seq_stride+t, :] = table[tok[b,t], :e1] ++ table2[tok2[b,t], :e2] ++ extra[b, :e3]. */
+ * out[b*seq_stride+t, :] = table[tok[b,t], :e1] ++ table2[tok2[b,t], :e2] ++ extra[b, :e3].
+ * round_tf32: 0 = fp32 as stored, 1 = fp32 rounded to tf32, 2 = `out` is an fp16 array (out_ld in fp16 elements):
+ * the operand copy a FTB_F_A_F16 problem reads. */
 int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1,
               const int64_t* tok2, const float* table2, int e2,
               const float* extra, int e3,
