@@ -1,6 +1,8 @@
 // K5/K6: duration rounding + warp-scan cumsum, and the LengthRegulator gather with the
 // pitch/energy projection add fused into the source read.  HBM-bound integer/copy work:
 // 128-bit accesses, one warp per output row, no tensor cores.
+#include <cuda_fp16.h>
+
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
 
@@ -124,8 +126,14 @@ lr_gather_kernel(const GatherArgs g, int token_blocks) {
     const int b = blockIdx.x - token_blocks;
     const int len = min(a.lens[b], a.M);
     for (int m = len + warp; m < a.M; m += 8) {
-      float* o = a.out + (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
-      for (int c = lane * 4; c < C; c += 128) *reinterpret_cast<float4*>(o + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+      const long long o0 = (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
+      if (a.round_tf32 == 2) {
+        __half* o = reinterpret_cast<__half*>(a.out) + o0;
+        for (int c = lane * 4; c < C; c += 128) *reinterpret_cast<uint2*>(o + c) = make_uint2(0u, 0u);
+      } else {
+        float* o = a.out + o0;
+        for (int c = lane * 4; c < C; c += 128) *reinterpret_cast<float4*>(o + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       if (a.idx && lane == 0) a.idx[static_cast<long long>(b) * a.M + m] = -1;
     }
     return;
@@ -183,17 +191,31 @@ lr_gather_kernel(const GatherArgs g, int token_blocks) {
           FTB_LR_PROJ(x) FTB_LR_PROJ(y) FTB_LR_PROJ(z) FTB_LR_PROJ(w)
 #undef FTB_LR_PROJ
         }
-        if (a.round_tf32) {
+        if (a.round_tf32 == 1) {
           v[q].x = round_tf32(v[q].x); v[q].y = round_tf32(v[q].y); v[q].z = round_tf32(v[q].z); v[q].w = round_tf32(v[q].w);
         }
       }
     }
     for (int m = m0; m < m1; ++m) {
-      float* o = a.out + (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
+      const long long o0 = (static_cast<long long>(b) * a.out_stride + m) * a.out_ld;
+      if (a.round_tf32 == 2) {                       // fp16 operand copy for a FTB_F_A_F16 consumer (out_ld in halves)
+        __half* o = reinterpret_cast<__half*>(a.out) + o0;
 #pragma unroll
-      for (int q = 0; q < LR_MAX_GROUPS; ++q) {
-        const int c = lane * 4 + q * 128;
-        if (c < C) *reinterpret_cast<float4*>(o + c) = v[q];
+        for (int q = 0; q < LR_MAX_GROUPS; ++q) {
+          const int c = lane * 4 + q * 128;
+          if (c < C) {
+            const __half2 lo = __floats2half2_rn(v[q].x, v[q].y), hi = __floats2half2_rn(v[q].z, v[q].w);
+            *reinterpret_cast<uint2*>(o + c) = make_uint2(*reinterpret_cast<const uint32_t*>(&lo),
+                                                          *reinterpret_cast<const uint32_t*>(&hi));
+          }
+        }
+      } else {
+        float* o = a.out + o0;
+#pragma unroll
+        for (int q = 0; q < LR_MAX_GROUPS; ++q) {
+          const int c = lane * 4 + q * 128;
+          if (c < C) *reinterpret_cast<float4*>(o + c) = v[q];
+        }
       }
       if (a.idx && lane == 0) a.idx[static_cast<long long>(b) * a.M + m] = t;
     }

@@ -132,10 +132,12 @@ class Program:
             self.steps.append(lambda plan=plan: self.h.gemm_run(plan))
             # algorithmic work: valid rows only (gap rows and the maxpool halo are overhead)
             flops = sum(2.0 * valid * q.cin * q.taps * q.n for q in grp)
-            nbytes = sum(4.0 * valid * (q.cin + q.n) + 4.0 * q.taps * q.n * q.cin for q in grp)
+            flops_f16 = sum(2.0 * valid * q.cin * q.taps * q.n for q in grp if q.flags & rt.F_A_F16)
+            nbytes = sum((2.0 if q.flags & rt.F_A_F16 else 4.0) * (valid * q.cin + q.taps * q.n * q.cin) +
+                         (2.0 if q.flags & rt.F_OUT_F16 else 4.0) * valid * q.n for q in grp)
             labels = sorted({getattr(q, '_label', '') for q in grp})
             self.info.append({'kind': 'gemm', 'label': '+'.join(l for l in labels if l) or 'gemm',
-                              'flops': flops, 'bytes': nbytes, 'problems': len(grp)})
+                              'flops': flops, 'flops_f16': flops_f16, 'bytes': nbytes, 'problems': len(grp)})
 
     def rnn(self, specs, lens: Optional[torch.Tensor] = None, pad_value: float = 0.0):
         """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one cooperative launch.

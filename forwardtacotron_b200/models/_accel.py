@@ -83,7 +83,8 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     geo = eng.Geometry(batch, M)
     prog = eng.Program(handle, geo)
     lstm: pk.PackedRnn = packs['lstm']
-    x = prog.buf('lr', in_channels)
+    # the regulated sequence feeds only the W_ih GEMM: fp16 operand copy (K5 writes it directly)
+    x = prog.buf('lr', in_channels, torch.float16 if (eng.F16_OPERANDS and in_channels % 8 == 0) else torch.float32)
     xp = prog.buf('lstm.xproj', lstm.ih.n)
     hl = prog.buf('lstm.h', 2 * lstm.hidden)
     mel_cl = prog.buf('mel_cl', n_mels)
@@ -168,7 +169,7 @@ def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program,
     g.batch, g.T, g.M = B, T, M
     lr = prog.bufs['lr']
     g.out, g.out_stride, g.out_ld = lr.data_ptr(), prog.geo.stride, lr.shape[1]
-    g.idx, g.round_tf32 = None, int(round_tf32)
+    g.idx, g.round_tf32 = None, (2 if lr.dtype == torch.float16 else int(round_tf32))
     handle.lr_gather(g)
     prog.run()
     mel = prog.bufs['mel'].clone()

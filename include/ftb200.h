@@ -179,7 +179,7 @@ typedef struct {
   int32_t batch, T, M;
   float* out; int32_t out_stride /*rows per sentence*/, out_ld;
   int32_t* idx;                                   /* [batch, M] or null                      */
-  int32_t round_tf32;
+  int32_t round_tf32;                             /* 0 as computed, 1 tf32-rounded, 2 = `out` is fp16 (out_ld in halves) */
 } ftb_lr_gather_args;
 int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void* stream);
 

@@ -278,6 +278,13 @@ def test_length_regulator_bit_exact_golden(tag):
     _, idx_ref, lens_ref, _ = O.length_regulate_np(g['x'], g['dur'])
     assert np.array_equal(idx.cpu().numpy(), idx_ref)
     assert np.array_equal(lens.cpu().numpy(), lens_ref)
+    # mode 2: the fp16 operand copy (what the W_ih GEMM of the BiLSTM reads) is the same gather, rounded to nearest
+    if C % 8 == 0:
+        out16 = torch.full((B, M, C), 7.0, device=DEV, dtype=torch.float16)
+        a.out, a.round_tf32, a.idx = out16.data_ptr(), 2, None
+        h.lr_gather(a)
+        torch.cuda.synchronize()
+        assert torch.equal(out16.cpu(), torch.from_numpy(g['out']).to(torch.float16))
 
 
 def test_length_regulator_full_size_properties():
