@@ -39,10 +39,7 @@ extern "C" int ftb_create(int device, ftb_handle* out) {
 extern "C" int ftb_destroy(ftb_handle h) {
   if (!h) return FTB_E_ARG;
   for (auto& kv : h->gemm_plans) cudaFree(kv.second.dev);
-  for (auto& kv : h->rnn_plans) {
-    cudaFree(kv.second.dev);
-    for (void* x : kv.second.hx) cudaFree(x);
-  }
+  for (auto& kv : h->rnn_plans) rnn_plan_free(kv.second);
   delete h;
   return 0;
 }
@@ -92,7 +89,7 @@ extern "C" int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream) {
   if (!h) return FTB_E_ARG;
   auto it = h->rnn_plans.find(plan);
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
-  h->launches += static_cast<int64_t>(it->second.launches.size() + it->second.problems.size());   // + sentinel pre-fills
+  h->launches += static_cast<int64_t>(it->second.launches.size() + it->second.hx.size());   // + sentinel pre-fills (L2 hand-off)
   return rnn_plan_launch(it->second, static_cast<cudaStream_t>(stream));
 }
 
@@ -100,8 +97,7 @@ extern "C" int ftb_rnn_plan_destroy(ftb_handle h, int plan) {
   if (!h) return FTB_E_ARG;
   auto it = h->rnn_plans.find(plan);
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
-  cudaFree(it->second.dev);
-  for (void* x : it->second.hx) cudaFree(x);
+  rnn_plan_free(it->second);
   h->rnn_plans.erase(it);
   return 0;
 }

@@ -67,18 +67,26 @@ struct RnnProblemDev {
   int group_base;        // first barrier-counter index (one per (dir, bgroup))
   int b_begin, b_end;    // batch columns covered by this part (a problem too large for one
                          // co-resident grid is split into parts that run in successive launches)
+  int problem;           // index of the originating ftb_rnn_problem
 };
 
 struct RnnLaunch {
   int first = 0, count = 0;           // parts [first, first+count) of RnnPlan::dev
   int ctas = 0;
   int smem = 0;                       // dynamic shared memory of this launch (max over its parts)
+  int cluster = 0;                    // cluster size of this launch (0: cooperative launch, L2 hand-off)
+  int lane = 0;                       // 0: the caller's stream; k > 0: side stream k-1 of the plan (concurrent lanes)
 };
 
 struct RnnPlan {
   RnnProblemDev* dev = nullptr;       // all parts of all launches
   unsigned int* counters = nullptr;   // unused since the in-band sentinel protocol (kept for ABI of the struct)
   int ngroups = 0;
+  int cluster = 0;                    // 1: thread-block-cluster hand-off (per-launch cluster size); 0: L2 hand-off
+  int lanes = 1;                      // concurrent launch sequences (one per cluster size)
+  std::vector<cudaStream_t> side;     // lanes - 1 side streams + their join events, forked from the caller's stream
+  std::vector<cudaEvent_t> joined;
+  cudaEvent_t forked = nullptr;
   std::vector<ftb_rnn_problem> problems;   // originals
   std::vector<void*> hx;                   // per problem: fp16 exchange tensor (owned by the plan)
   std::vector<size_t> hx_bytes;
@@ -87,6 +95,7 @@ struct RnnPlan {
 
 int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan);
 int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream);
+void rnn_plan_free(RnnPlan& plan);
 
 }  // namespace ftb
 

@@ -35,6 +35,8 @@
 // (A from TMEM) variant was built and measured: ~90 cycles per M128 N16 K16 instruction, 3000 cycles of MMA per
 // step against ~950 here (profiles/r1g_rnn_tcgen05_experiment.txt; source kept in scratch/experiments/).
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <cuda_fp16.h>
 
 #include "ftb_internal.h"
@@ -84,10 +86,35 @@ __device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz
 __device__ __forceinline__ float sigm(float x) { return rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
 __device__ __forceinline__ float tanh_fast(float x) { return fmaf(2.0f, rcp_ftz(1.0f + ex2_ftz(-2.8853900817779268f * x)), -1.0f); }
 
-template <int G, int H>
+// ---- thread-block-cluster hand-off (distributed shared memory) ---------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// 16-byte asynchronous store into a peer CTA's shared memory; completes 16 tx-bytes on the peer's mbarrier
+__device__ __forceinline__ void st_async_v4(uint32_t raddr, const uint4& v, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(raddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+template <int G, int H, bool CL = false>
 struct RnnTiling {
   static constexpr int U = RNN_U, NB = RNN_NB, KS = RNN_KS;
-  static constexpr int NG = 2, NBG = NB / NG;   // two independent batch groups of 8 columns (one MMA n-tile each)
+  // L2 hand-off: two independent batch groups of 8 columns (one MMA n-tile each), interleaved to hide the L2 round trip.
+  // Cluster hand-off: ONE group of 16 columns (two n-tiles that share every A fragment): the hand-off is short enough
+  // that halving the number of phases per step wins over hiding it.
+  static constexpr int NG = CL ? 1 : 2, NBG = NB / NG;
   static constexpr int RC = G * U;              // W_hh rows owned by this CTA (128 / 96)
   static constexpr int RS = RC / 16;            // 16-row MMA strips (8 / 6)
   static constexpr int WARPS = RS * KS;         // MMA warps (16 / 12)
@@ -100,18 +127,31 @@ struct RnnTiling {
   static constexpr int ITEMS = NBG * KW / 8;    // 16-byte items (8 halves) of one K-half of one batch group of h
   static constexpr int IPT = (ITEMS + GS - 1) / GS;
   static constexpr int SMEM_BYTES = NB * HS * 2 + (NG * KS * NBG * S + RNN_XS * NB * XSTR) * 4;
+  // cluster hand-off: h tiles [2 step parities][SL slices][NB columns][32 units] fp16 + 2 mbarriers
+  static constexpr int SL = H / U;              // unit slices = CTAs of one (direction, batch group) unit
+  static constexpr int HCL_BYTES = 2 * NG * SL * NBG * U * 2;
+  static constexpr int TXB = SL * NBG * U * 2;  // bytes one (group, step) hand-off delivers to every CTA of the unit
+  static constexpr int ND = (SL + 7) / 8;       // peers one lane stores to
+  static constexpr int SMEM_BYTES_CL = HCL_BYTES + (NG * KS * NBG * S + RNN_XS * NB * XSTR) * 4 + 2 * NG * 8;
   static_assert(RC % 16 == 0 && KW % 32 == 0 && WARPS * 32 <= RNN_THREADS, "bad recurrence tiling");
   static_assert(U * NB == RNN_THREADS && (NB * G * U / 4) <= RNN_THREADS, "one (unit, batch) pair / x chunk per thread");
 };
 
-template <int G, int H>
+// CL = false: h handed between CTAs through L2 (in-band sentinel polling; cooperative launch).
+// CL = true : the SL CTAs of one (direction, batch group) unit sit in one thread-block cluster and push h_t
+//             straight into each other's shared memory (st.async + mbarrier complete_tx); see the header.
+template <int G, int H, bool CL>
 __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* smem) {
-  using T = RnnTiling<G, H>;
+  using T = RnnTiling<G, H, CL>;
   constexpr int U = T::U, NB = T::NB, KS = T::KS, WARPS = T::WARPS, KW = T::KW, KB = T::KB, NBG = T::NBG;
   constexpr int S = T::S, HS = T::HS, XSTR = T::XSTR, GS = T::GS, ITEMS = T::ITEMS, IPT = T::IPT;
-  __half* h_s = reinterpret_cast<__half*>(smem);                       // [NB][HS] fp16 (rows 0-7 group A, 8-15 group B)
-  float* p_s = reinterpret_cast<float*>(smem + NB * HS * 2);           // [NG][KS][NBG][S]
+  constexpr int NG = T::NG, SL = T::SL, ND = T::ND;
+  constexpr int TILE = NBG * U;                                        // halves of one slice of one group's h tile
+  __half* h_s = reinterpret_cast<__half*>(smem);                       // L2: [NB][HS] fp16 (rows 0-7 group A, 8-15 group B)
+                                                                       // CL: [2][NG][SL][NBG][U] fp16
+  float* p_s = reinterpret_cast<float*>(smem + (CL ? T::HCL_BYTES : NB * HS * 2));   // [NG][KS][NBG][S]
   float* x_s = p_s + T::NG * KS * NBG * S;                             // [XS][NB][XSTR]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(x_s + RNN_XS * NB * XSTR);            // CL: [2][NG] "h tile full"
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slice = local_cta % p.slices;
@@ -231,7 +271,36 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     }
   };
   // P[g] = W_hh[slice rows, K-half] * h_{t-1}[group g]^T   (tensor cores, fp16 x fp16 -> fp32)
-  auto mma_group = [&](int g) {
+  auto mma_group = [&](int g, int par) {
+    if (CL) {
+      // both n-tiles (columns 0-7 / 8-15) per A fragment; slice kb of the K range is a [NB][U] tile, so the two
+      // LDS.128 of a warp cover 2 x 512 contiguous bytes
+      float acc[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+      const __half* hrow = h_s + (par * SL + kq * KB) * TILE + fr * U + 8 * q;
+#pragma unroll
+      for (int kb = 0; kb < KB; ++kb) {
+        const uint4 h0 = *reinterpret_cast<const uint4*>(hrow + kb * TILE);
+        const uint4 h1 = *reinterpret_cast<const uint4*>(hrow + kb * TILE + 8 * U);
+        mma_f16_16x8x16(acc[0], wfrag[kb * 2 + 0], h0.x, h0.y);
+        mma_f16_16x8x16(acc[2], wfrag[kb * 2 + 0], h1.x, h1.y);
+        mma_f16_16x8x16(acc[1], wfrag[kb * 2 + 1], h0.z, h0.w);
+        mma_f16_16x8x16(acc[3], wfrag[kb * 2 + 1], h1.z, h1.w);
+      }
+      float* pk = p_s + static_cast<size_t>(kq) * NB * S;
+      const int col = 2 * q, row = rs * 16 + fr;
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        pk[(8 * nt + col) * S + row] = acc[2 * nt][0] + acc[2 * nt + 1][0];
+        pk[(8 * nt + col + 1) * S + row] = acc[2 * nt][1] + acc[2 * nt + 1][1];
+        pk[(8 * nt + col) * S + row + 8] = acc[2 * nt][2] + acc[2 * nt + 1][2];
+        pk[(8 * nt + col + 1) * S + row + 8] = acc[2 * nt][3] + acc[2 * nt + 1][3];
+      }
+      return;
+    }
     float acc0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, acc1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     const __half* hrow = h_s + (g * NBG + fr) * HS + kq * KW + 8 * q;
 #pragma unroll
@@ -247,6 +316,22 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     pk[col * S + row + 8] = acc0[2] + acc1[2];
     pk[(col + 1) * S + row + 8] = acc0[3] + acc1[3];
   };
+  // cluster hand-off: this lane's peers (CTAs of the same unit = cluster ranks [rank - slice, rank - slice + SL))
+  uint32_t rdata[ND], rbar[ND], rvalid = 0;
+  if (CL) {
+    const uint32_t ubase = cluster_ctarank() - slice;
+#pragma unroll
+    for (int d = 0; d < ND; ++d) {
+      const int peer = (lane & 7) + 8 * d;
+      rdata[d] = rbar[d] = 0;
+      if (peer < SL) {
+        rvalid |= 1u << d;
+        // tile [par][pg][slice][pbl][unit octet lane/8]
+        rdata[d] = mapa_shared(smem_u32(h_s), ubase + peer) + ((pg * SL + slice) * TILE + pbl * U + (lane >> 3) * 8) * 2;
+        rbar[d] = mapa_shared(smem_u32(bars), ubase + peer) + pg * 8;
+      }
+    }
+  }
   // gate math (fp32), state update and publication of h_t for this thread's pair (threads of group g only).
   // The partial-sum tiles start zeroed, so step 0 (h_{-1} = 0, no MMA) needs no special case.
   const long long o_step = dir ? -static_cast<long long>(p.out_ld) : static_cast<long long>(p.out_ld);
@@ -288,16 +373,34 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       h_state = hnew;
       dead = !live;
     }
-    // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
     const __half h16 = __float2half_rn(hnew);
     const unsigned mine = __half_as_ushort(h16);
-    const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
-    if (pv) {
-      if ((lane & 1) == 0) st_relaxed_u32(hx_p, mine | (other << 16));
-      *out_p = dead ? pad_value : __half2float(h16);
+    if (CL) {
+      // publish: all-gather the 8 units of this lane's octet (3 xor rounds) -> one 16-byte chunk of column pbl;
+      // lane l pushes chunk l/8 into the tile of peer l%8 (and l%8 + 8) of the unit
+      const unsigned o1 = __shfl_xor_sync(0xffffffffu, mine, 1);
+      const unsigned w = (lane & 1) ? (o1 | (mine << 16)) : (mine | (o1 << 16));
+      const unsigned o2 = __shfl_xor_sync(0xffffffffu, w, 2);
+      const unsigned d0 = (lane & 2) ? o2 : w, d1 = (lane & 2) ? w : o2;
+      const unsigned e0 = __shfl_xor_sync(0xffffffffu, d0, 4), e1 = __shfl_xor_sync(0xffffffffu, d1, 4);
+      const uint4 v = (lane & 4) ? make_uint4(e0, e1, d0, d1) : make_uint4(d0, d1, e0, e1);
+      if (step + 1 < L) {
+        const uint32_t poff = (step & 1) * (NG * SL * TILE * 2), boff = (step & 1) * (NG * 8);
+#pragma unroll
+        for (int d = 0; d < ND; ++d)
+          if (rvalid & (1u << d)) st_async_v4(rdata[d] + poff, v, rbar[d] + boff);
+      }
+      if (pv) *out_p = dead ? pad_value : __half2float(h16);
+    } else {
+      // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
+      const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
+      if (pv) {
+        if ((lane & 1) == 0) st_relaxed_u32(hx_p, mine | (other << 16));
+        *out_p = dead ? pad_value : __half2float(h16);
+      }
+      hx_p += h_step;
     }
     out_p += o_step;
-    hx_p += h_step;
   };
 
 #ifdef FTB_RNN_PROFILE
@@ -315,8 +418,39 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   // per-step chains (publish -> L2 -> stage -> MMA -> gates -> publish) are interleaved so that the L2
   // round trip of one group is covered by the tensor-core and gate phases of the other.
   for (int i = tid; i < T::NG * KS * NBG * S; i += RNN_THREADS) p_s[i] = 0.0f;
+  if (CL) {
+    // "h tile full" barriers: one local arrival (the expect_tx that arms a phase) + TXB bytes from the unit's CTAs.
+    // Tile / barrier [par] carries h_t for t = par (mod 2).  A phase is re-armed by the thread that
+    // saw it complete, before this CTA's next publication (CTA barriers in between) and hence before any peer can
+    // send the step after next; the two tiles of a group alternate, so a peer one step ahead never overwrites a
+    // tile that is still being read.
+    if (tid == 0) {
+#pragma unroll
+      for (int i = 0; i < 2; ++i) mbar_init(&bars[i], 1);
+      fence_mbar_init();
+#pragma unroll
+      for (int i = 0; i < 2; ++i) mbar_expect_tx(&bars[i], T::TXB);
+    }
+    cluster_sync_all();                    // every peer's barriers exist before the first remote store
+  }
   for (int step = 0; step < L; ++step) {
     FTB_TICK(0)
+    if (CL) {
+      const int par = (step - 1) & 1;
+      if (step > 0 && mma_warp) {
+        mbar_wait(&bars[par], ((step - 1) >> 1) & 1);    // h_{t-1} of all 16 columns has landed in this CTA's tile
+        if (tid == 0 && step + 1 < L) mbar_expect_tx(&bars[par], T::TXB);
+        FTB_TICK(1)
+        mma_group(0, par);
+      }
+      cp_async_wait<RNN_XS - 2>();         // own x chunk of this step
+      __syncthreads();                     // partial sums + everyone's x chunks visible; ring slot (step-1) free
+      FTB_TICK(2)
+      prefetch_x();
+      gate_group(step);                    // every thread owns one (unit, column) pair
+      FTB_TICK(3)
+      continue;
+    }
     // ---------------- group A --------------------------------------------------------------------
     if (step > 0 && mma_warp) {
       cp_async_wait<0>();                  // A copies were issued in the previous iteration
@@ -324,7 +458,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       FTB_TICK(1)
       named_bar_sync(1 + kq, GS);
       if (has_b) issue_h(1, -h_step);      // group B of t-1 was published at the end of the previous iteration
-      mma_group(0);
+      mma_group(0, 0);
     }
     if (step == 0 || !mma_warp) cp_async_wait<RNN_XS - 2>();   // x chunk of this step (MMA warps: covered above)
     __syncthreads();                       // A partial sums + everyone's x chunks visible; ring slot (step-1) free
@@ -341,7 +475,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       FTB_TICK(4)
       named_bar_sync(3 + kq, GS);          // also orders gate A's publication before the A re-fetch below
       if (step + 1 < L) issue_h(0, 0);     // group A of step t: published by the A-warps of all CTAs just now
-      if (step > 0 && has_b) mma_group(1);
+      if (step > 0 && has_b) mma_group(1, 0);
 #pragma unroll
       for (int j = 0; j < IPT; ++j) hp[j] += h_step;
     }
@@ -359,6 +493,22 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
 #endif
 }
 
+template <bool CL>
+__device__ __forceinline__ void rnn_dispatch(const RnnProblemDev& p, int local, unsigned char* smem) {
+  if (p.cell == FTB_CELL_LSTM) {
+    if (p.hidden == 512) rnn_cta<4, 512, CL>(p, local, smem);
+    else if (p.hidden == 256) rnn_cta<4, 256, CL>(p, local, smem);
+    else if (p.hidden == 128) rnn_cta<4, 128, CL>(p, local, smem);
+    else rnn_cta<4, 64, CL>(p, local, smem);
+  } else {
+    if (p.hidden == 512) rnn_cta<3, 512, CL>(p, local, smem);
+    else if (p.hidden == 256) rnn_cta<3, 256, CL>(p, local, smem);
+    else if (p.hidden == 128) rnn_cta<3, 128, CL>(p, local, smem);
+    else rnn_cta<3, 64, CL>(p, local, smem);
+  }
+}
+
+// L2 hand-off; cooperative launch (every CTA of the grid must be co-resident: CTAs poll each other's data)
 __global__ void __launch_bounds__(RNN_THREADS, 1)
 rnn_persistent_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
   extern __shared__ __align__(16) unsigned char rnn_smem[];
@@ -367,65 +517,90 @@ rnn_persistent_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
   const RnnProblemDev p = probs[pi];
   const int local = blockIdx.x - p.cta_base;
   if (local >= p.ctas) return;
-  if (p.cell == FTB_CELL_LSTM) {
-    if (p.hidden == 512) rnn_cta<4, 512>(p, local, rnn_smem);
-    else if (p.hidden == 256) rnn_cta<4, 256>(p, local, rnn_smem);
-    else if (p.hidden == 128) rnn_cta<4, 128>(p, local, rnn_smem);
-    else rnn_cta<4, 64>(p, local, rnn_smem);
-  } else {
-    if (p.hidden == 512) rnn_cta<3, 512>(p, local, rnn_smem);
-    else if (p.hidden == 256) rnn_cta<3, 256>(p, local, rnn_smem);
-    else if (p.hidden == 128) rnn_cta<3, 128>(p, local, rnn_smem);
-    else rnn_cta<3, 64>(p, local, rnn_smem);
-  }
+  rnn_dispatch<false>(p, local, rnn_smem);
 }
 
-static int rnn_smem_bytes(int cell, int hidden) {
+// Cluster hand-off; launched with a cluster dimension that is a multiple of every part's slice count, every part
+// starting on a cluster boundary.  Units (= SL consecutive CTAs) never straddle clusters and depend on nothing outside
+// their cluster, so no grid-wide co-residency is needed.  Padding CTAs only take part in the two cluster barriers.
+__global__ void __launch_bounds__(RNN_THREADS, 1)
+rnn_cluster_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
+  extern __shared__ __align__(16) unsigned char rnn_smem[];
+  int pi = 0;
+  while (pi + 1 < nprob && static_cast<int>(blockIdx.x) >= probs[pi + 1].cta_base) ++pi;
+  const RnnProblemDev p = probs[pi];
+  const int local = blockIdx.x - p.cta_base;
+  if (local < p.ctas) rnn_dispatch<true>(p, local, rnn_smem);
+  else cluster_sync_all();                 // pairs with the barrier after the mbarrier set-up of the working CTAs
+  cluster_sync_all();                      // no CTA leaves while a peer may still store into its shared memory
+}
+
+static int rnn_smem_bytes(int cell, int hidden, bool cluster) {
   const bool lstm = cell == FTB_CELL_LSTM;
+#define FTB_RNN_SMEM(GG, HH) (cluster ? RnnTiling<GG, HH, true>::SMEM_BYTES_CL : RnnTiling<GG, HH, false>::SMEM_BYTES)
   switch (hidden) {
-    case 512: return lstm ? RnnTiling<4, 512>::SMEM_BYTES : RnnTiling<3, 512>::SMEM_BYTES;
-    case 256: return lstm ? RnnTiling<4, 256>::SMEM_BYTES : RnnTiling<3, 256>::SMEM_BYTES;
-    case 128: return lstm ? RnnTiling<4, 128>::SMEM_BYTES : RnnTiling<3, 128>::SMEM_BYTES;
-    default: return lstm ? RnnTiling<4, 64>::SMEM_BYTES : RnnTiling<3, 64>::SMEM_BYTES;
+    case 512: return lstm ? FTB_RNN_SMEM(4, 512) : FTB_RNN_SMEM(3, 512);
+    case 256: return lstm ? FTB_RNN_SMEM(4, 256) : FTB_RNN_SMEM(3, 256);
+    case 128: return lstm ? FTB_RNN_SMEM(4, 128) : FTB_RNN_SMEM(3, 128);
+    default: return lstm ? FTB_RNN_SMEM(4, 64) : FTB_RNN_SMEM(3, 64);
   }
+#undef FTB_RNN_SMEM
 }
 
 // ------------------------------------------------------------------------------------------
-int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan) {
-  if (!problems || nproblems < 1 || nproblems > FTB_MAX_RNN_PROBLEMS) return FTB_E_ARG;
-  std::vector<RnnProblemDev> parts;
-  std::vector<RnnLaunch> launches;
+// Max co-resident clusters of `cs` CTAs of the cluster kernel (0 = this cluster size cannot be launched here).
+static int rnn_cluster_capacity(int cs, int smem) {
+  if (cudaFuncSetAttribute(rnn_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           rnn_smem_bytes(FTB_CELL_LSTM, 512, true)) != cudaSuccess) { cudaGetLastError(); return 0; }
+  if (cs > 8 && cudaFuncSetAttribute(rnn_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cs * 16);
+  cfg.blockDim = dim3(RNN_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, rnn_cluster_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+// Lays the (problem, direction, batch group, slice) CTAs out over launches of at most `capacity` CTAs; every part starts
+// on a multiple of `align` CTAs (cluster size; 1 for the L2 hand-off).
+static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& which, int capacity, int align, bool cluster,
+                     int lane, std::vector<RnnProblemDev>* parts, std::vector<RnnLaunch>* launches) {
   RnnLaunch cur;
+  cur.first = static_cast<int>(parts->size());
+  cur.cluster = cluster ? align : 0;
+  cur.lane = lane;
   int ngroups = 0;
-  for (int i = 0; i < nproblems; ++i) {
+  auto up = [align](int v) { return (v + align - 1) / align * align; };
+  for (int i : which) {
     const ftb_rnn_problem& q = problems[i];
-    if (!q.xproj || !q.w_hh || !q.b_hh || !q.out) return FTB_E_ARG;
-    if (q.cell != FTB_CELL_GRU && q.cell != FTB_CELL_LSTM) return FTB_E_ARG;
-    if (q.hidden != 64 && q.hidden != 128 && q.hidden != 256 && q.hidden != 512) return FTB_E_SHAPE;
-    if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
-    if ((q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0 || (reinterpret_cast<uintptr_t>(q.out) & 15u)) return FTB_E_ALIGN;
     const int slices = q.hidden / RNN_U;
     const int per_bgroup = 2 * slices;                 // CTAs per batch group (both directions)
-    if (per_bgroup > num_sms) return FTB_E_RESIDENT;
-    const size_t hx_bytes = static_cast<size_t>(2) * q.seq_len * q.batch * q.hidden * sizeof(__half);
-    void* hx = nullptr;
-    cudaError_t he = cudaMalloc(&hx, hx_bytes);
-    if (he != cudaSuccess) return static_cast<int>(he);
-    plan->hx.push_back(hx);
-    plan->hx_bytes.push_back(hx_bytes);
+    if (per_bgroup > capacity) return FTB_E_RESIDENT;
     int b = 0;
     while (b < q.batch) {
-      int room = (num_sms - cur.ctas) / per_bgroup;    // batch groups that still fit in this launch
-      if (room == 0) {
-        launches.push_back(cur);
+      int room = (capacity - up(cur.ctas)) / per_bgroup;    // batch groups that still fit in this launch
+      if (room <= 0) {
+        cur.ctas = up(cur.ctas);
+        launches->push_back(cur);
         cur = RnnLaunch();
-        cur.first = static_cast<int>(parts.size());
-        room = num_sms / per_bgroup;
+        cur.first = static_cast<int>(parts->size());
+        cur.cluster = cluster ? align : 0;
+        cur.lane = lane;
+        room = capacity / per_bgroup;
       }
       const int want = (q.batch - b + RNN_NB - 1) / RNN_NB;
       const int take = want < room ? want : room;
       RnnProblemDev d{};
-      d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = static_cast<__half*>(hx);
+      d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = nullptr;
       d.lens = q.lens; d.pad_value = q.pad_value;
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
@@ -434,19 +609,107 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       d.bgroups = take;
       d.b_begin = b;
       d.b_end = (b + take * RNN_NB < q.batch) ? b + take * RNN_NB : q.batch;
-      d.cta_base = cur.ctas;
+      d.cta_base = up(cur.ctas);
       d.ctas = 2 * take * slices;
-      const int sm = rnn_smem_bytes(q.cell, q.hidden);
+      const int sm = rnn_smem_bytes(q.cell, q.hidden, cluster);
       if (sm > cur.smem) cur.smem = sm;
       d.group_base = ngroups;
+      d.problem = i;
       ngroups += 2 * take;
-      cur.ctas += d.ctas;
+      cur.ctas = d.cta_base + d.ctas;
       cur.count += 1;
-      parts.push_back(d);
+      parts->push_back(d);
       b = d.b_end;
     }
   }
-  if (cur.count) launches.push_back(cur);
+  if (cur.count) {
+    cur.ctas = up(cur.ctas);
+    launches->push_back(cur);
+  }
+  return ngroups;
+}
+
+int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan) {
+  if (!problems || nproblems < 1 || nproblems > FTB_MAX_RNN_PROBLEMS) return FTB_E_ARG;
+  int max_slices = 0;
+  for (int i = 0; i < nproblems; ++i) {
+    const ftb_rnn_problem& q = problems[i];
+    if (!q.xproj || !q.w_hh || !q.b_hh || !q.out) return FTB_E_ARG;
+    if (q.cell != FTB_CELL_GRU && q.cell != FTB_CELL_LSTM) return FTB_E_ARG;
+    if (q.hidden != 64 && q.hidden != 128 && q.hidden != 256 && q.hidden != 512) return FTB_E_SHAPE;
+    if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
+    if ((q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0 || (reinterpret_cast<uintptr_t>(q.out) & 15u)) return FTB_E_ALIGN;
+    if (q.hidden / RNN_U > max_slices) max_slices = q.hidden / RNN_U;
+  }
+  // L2 hand-off layout (always possible on a device that holds one batch group)
+  std::vector<RnnProblemDev> parts;
+  std::vector<RnnLaunch> launches;
+  std::vector<int> all(nproblems);
+  for (int i = 0; i < nproblems; ++i) all[i] = i;
+  int ngroups = rnn_place(problems, all, num_sms, 1, false, 0, &parts, &launches);
+  if (ngroups < 0) return ngroups;
+  // Cluster hand-off (FTB_RNN_HANDOFF=l2 disables it).  Problems are grouped by slice count = cluster size; every group
+  // is its own launch sequence ("lane") and the lanes run concurrently (side streams forked from / joined to the
+  // caller's stream), because a launch has ONE cluster size and large clusters pack badly into the GPCs (B200: 15
+  // resident clusters of 8 CTAs, 7 of 16).  Taken when no lane needs more launches than the L2 layout.
+  plan->cluster = 0;
+  const char* mode = getenv("FTB_RNN_HANDOFF");
+  if (!(mode && strcmp(mode, "l2") == 0)) {
+    std::vector<RnnProblemDev> cparts;
+    std::vector<RnnLaunch> claunches;
+    int cg = 0, lanes = 0;
+    size_t depth = 0;
+    bool ok = true;
+    for (int cs = 16; cs >= 2 && ok; cs >>= 1) {
+      std::vector<int> which;
+      int smem = 0;
+      for (int i = 0; i < nproblems; ++i) {
+        if (problems[i].hidden / RNN_U != cs) continue;
+        which.push_back(i);
+        const int sm = rnn_smem_bytes(problems[i].cell, problems[i].hidden, true);
+        if (sm > smem) smem = sm;
+      }
+      if (which.empty()) continue;
+      const int cap = rnn_cluster_capacity(cs, smem) * cs;
+      const size_t before = claunches.size();
+      const int g = cap >= 2 * cs ? rnn_place(problems, which, cap, cs, true, lanes, &cparts, &claunches) : -1;
+      if (getenv("FTB_RNN_DEBUG"))
+        fprintf(stderr, "ftb: rnn plan: %zu problem(s) with cluster size %d: resident capacity %d CTAs -> %zu launch(es); "
+                        "L2 layout %zu launch(es)\n", which.size(), cs, cap, claunches.size() - before, launches.size());
+      if (g < 0) { ok = false; break; }
+      cg += g;
+      if (claunches.size() - before > depth) depth = claunches.size() - before;
+      ++lanes;
+    }
+    if (ok && lanes > 0 && (depth <= launches.size() || (mode && strcmp(mode, "cluster") == 0))) {
+      parts.swap(cparts);
+      launches.swap(claunches);
+      ngroups = cg;
+      plan->cluster = 1;
+      plan->lanes = lanes;
+      for (int i = 1; i < lanes; ++i) {
+        cudaStream_t st = nullptr;
+        cudaEvent_t ev = nullptr;
+        if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return FTB_E_ARG;
+        if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return FTB_E_ARG;
+        plan->side.push_back(st);
+        plan->joined.push_back(ev);
+      }
+      if (lanes > 1 && cudaEventCreateWithFlags(&plan->forked, cudaEventDisableTiming) != cudaSuccess) return FTB_E_ARG;
+    }
+  }
+  if (!plan->cluster) {
+    for (int i = 0; i < nproblems; ++i) {
+      const ftb_rnn_problem& q = problems[i];
+      const size_t hx_bytes = static_cast<size_t>(2) * q.seq_len * q.batch * q.hidden * sizeof(__half);
+      void* hx = nullptr;
+      cudaError_t he = cudaMalloc(&hx, hx_bytes);
+      if (he != cudaSuccess) return static_cast<int>(he);
+      plan->hx.push_back(hx);
+      plan->hx_bytes.push_back(hx_bytes);
+    }
+    for (RnnProblemDev& d : parts) d.hx = static_cast<__half*>(plan->hx[d.problem]);
+  }
   cudaError_t ce = cudaMalloc(&plan->dev, sizeof(RnnProblemDev) * parts.size());
   if (ce != cudaSuccess) return static_cast<int>(ce);
   ce = cudaMemcpy(plan->dev, parts.data(), sizeof(RnnProblemDev) * parts.size(), cudaMemcpyHostToDevice);
@@ -457,16 +720,59 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
   return 0;
 }
 
+void rnn_plan_free(RnnPlan& plan) {
+  cudaFree(plan.dev);
+  for (void* x : plan.hx) cudaFree(x);
+  for (cudaStream_t st : plan.side) cudaStreamDestroy(st);
+  for (cudaEvent_t ev : plan.joined) cudaEventDestroy(ev);
+  if (plan.forked) cudaEventDestroy(plan.forked);
+  plan = RnnPlan();
+}
+
 int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream) {
+  cudaError_t ce = cudaSuccess;
+  if (plan.cluster) {
+    // attributes were set by rnn_cluster_capacity() when the plan was built
+    if (plan.lanes > 1) {
+      ce = cudaEventRecord(plan.forked, stream);
+      if (ce != cudaSuccess) return static_cast<int>(ce);
+      for (cudaStream_t st : plan.side) {
+        ce = cudaStreamWaitEvent(st, plan.forked, 0);
+        if (ce != cudaSuccess) return static_cast<int>(ce);
+      }
+    }
+    for (const RnnLaunch& l : plan.launches) {
+      const RnnProblemDev* base = plan.dev + l.first;
+      int count = l.count;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(l.ctas);
+      cfg.blockDim = dim3(RNN_THREADS);
+      cfg.dynamicSmemBytes = l.smem;
+      cfg.stream = l.lane ? plan.side[l.lane - 1] : stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = l.cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      ce = cudaLaunchKernelEx(&cfg, rnn_cluster_kernel, base, count);
+      if (ce != cudaSuccess) return static_cast<int>(ce);
+    }
+    for (size_t i = 0; i < plan.side.size(); ++i) {
+      ce = cudaEventRecord(plan.joined[i], plan.side[i]);
+      if (ce != cudaSuccess) return static_cast<int>(ce);
+      ce = cudaStreamWaitEvent(stream, plan.joined[i], 0);
+      if (ce != cudaSuccess) return static_cast<int>(ce);
+    }
+    return 0;
+  }
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t ce = cudaFuncSetAttribute(rnn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          rnn_smem_bytes(FTB_CELL_LSTM, 512));
+    ce = cudaFuncSetAttribute(rnn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              rnn_smem_bytes(FTB_CELL_LSTM, 512, false));
     if (ce != cudaSuccess) return static_cast<int>(ce);
     attr_set = true;
   }
   // arm the in-band "not written yet" marker (0xFFFF halves) in every exchange slot the recurrences publish
-  cudaError_t ce = cudaSuccess;
   for (size_t i = 0; i < plan.hx.size(); ++i) {
     ce = cudaMemsetAsync(plan.hx[i], 0xFF, plan.hx_bytes[i], stream);
     if (ce != cudaSuccess) return static_cast<int>(ce);
