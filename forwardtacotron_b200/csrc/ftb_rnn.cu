@@ -342,7 +342,16 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   __half* hx_p = hx_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.batch * H;
   const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
   const float* xs0 = x_s + pb * XSTR + pu;
+#ifdef FTB_RNN_PROFILE
+  // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
+  unsigned long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define FTB_TICK(i) { const long long now_ = clock64(); prof[i] += now_ - tick_; tick_ = now_; }
+  long long tick_ = clock64();
+#else
+#define FTB_TICK(i)
+#endif
   auto gate_group = [&](int step) {
+    if (CL) { FTB_TICK(7) }
     float hnew = 0.0f;
     bool dead = false;
     if (pv) {
@@ -375,6 +384,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     }
     const __half h16 = __float2half_rn(hnew);
     const unsigned mine = __half_as_ushort(h16);
+    if (CL) { FTB_TICK(4) }
     if (CL) {
       // publish: all-gather the 8 units of this lane's octet (3 xor rounds) -> one 16-byte chunk of column pbl;
       // lane l pushes chunk l/8 into the tile of peer l%8 (and l%8 + 8) of the unit
@@ -384,6 +394,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       const unsigned d0 = (lane & 2) ? o2 : w, d1 = (lane & 2) ? w : o2;
       const unsigned e0 = __shfl_xor_sync(0xffffffffu, d0, 4), e1 = __shfl_xor_sync(0xffffffffu, d1, 4);
       const uint4 v = (lane & 4) ? make_uint4(e0, e1, d0, d1) : make_uint4(d0, d1, e0, e1);
+      FTB_TICK(5)
       if (step + 1 < L) {
         const uint32_t poff = (step & 1) * (NG * SL * TILE * 2), boff = (step & 1) * (NG * 8);
 #pragma unroll
@@ -391,6 +402,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
           if (rvalid & (1u << d)) st_async_v4(rdata[d] + poff, v, rbar[d] + boff);
       }
       if (pv) *out_p = dead ? pad_value : __half2float(h16);
+      FTB_TICK(6)
     } else {
       // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
       const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
@@ -403,14 +415,6 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     out_p += o_step;
   };
 
-#ifdef FTB_RNN_PROFILE
-  // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
-  unsigned long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#define FTB_TICK(i) { const long long now_ = clock64(); prof[i] += now_ - tick_; tick_ = now_; }
-  long long tick_ = clock64();
-#else
-#define FTB_TICK(i)
-#endif
   unsigned retries = 0;
   const bool has_b = nbv > NBG;                     // group B holds at least one valid column
 
@@ -446,8 +450,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       cp_async_wait<RNN_XS - 2>();         // own x chunk of this step
       __syncthreads();                     // partial sums + everyone's x chunks visible; ring slot (step-1) free
       FTB_TICK(2)
-      prefetch_x();
       gate_group(step);                    // every thread owns one (unit, column) pair
+      prefetch_x();                        // after the publication: off the step-to-step critical path
       FTB_TICK(3)
       continue;
     }
@@ -463,8 +467,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     if (step == 0 || !mma_warp) cp_async_wait<RNN_XS - 2>();   // x chunk of this step (MMA warps: covered above)
     __syncthreads();                       // A partial sums + everyone's x chunks visible; ring slot (step-1) free
     FTB_TICK(2)
-    prefetch_x();
     if (pg == 0) gate_group(step);
+    prefetch_x();                          // after group A's publication: off its step-to-step critical path
     FTB_TICK(3)
     // ---------------- group B --------------------------------------------------------------------
     if (mma_warp) {
@@ -487,8 +491,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   cp_async_wait<0>();
 #ifdef FTB_RNN_PROFILE
   if (tid == 0 && (local_cta % 37) == 0)
-    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu waitA %llu mmaA+sync %llu gateA %llu waitB %llu mmaB+sync %llu gateB %llu | retries/step %.2f\n",
-           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L, prof[6] / L,
+    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu waitA %llu mmaA+sync %llu gateA %llu waitB %llu mmaB+sync %llu gateB %llu p7 %llu | retries/step %.2f\n",
+           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L, prof[6] / L, prof[7] / L,
            static_cast<float>(retries) / L);
 #endif
 }
