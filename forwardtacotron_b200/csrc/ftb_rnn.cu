@@ -457,7 +457,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     }
     // ---------------- group A --------------------------------------------------------------------
     if (step > 0 && mma_warp) {
-      cp_async_wait<0>();                  // A copies were issued in the previous iteration
+      cp_async_wait<1>();                  // A copies were issued in the previous iteration (the x prefetch committed
+                                           // after them may still be in flight: it is needed three steps from now)
       settle_h(0, -h_step, retries);
       FTB_TICK(1)
       named_bar_sync(1 + kq, GS);
@@ -468,12 +469,11 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     __syncthreads();                       // A partial sums + everyone's x chunks visible; ring slot (step-1) free
     FTB_TICK(2)
     if (pg == 0) gate_group(step);
-    prefetch_x();                          // after group A's publication: off its step-to-step critical path
     FTB_TICK(3)
     // ---------------- group B --------------------------------------------------------------------
     if (mma_warp) {
       if (step > 0 && has_b) {
-        cp_async_wait<1>();                // B copies done (the x prefetch just committed may still be in flight)
+        cp_async_wait<0>();                // B copies done (and the x prefetch of the previous step, long since)
         settle_h(1, -h_step, retries);
       }
       FTB_TICK(4)
@@ -483,6 +483,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
 #pragma unroll
       for (int j = 0; j < IPT; ++j) hp[j] += h_step;
     }
+    prefetch_x();                          // newest cp.async group: never waited for before the step after next
     __syncthreads();                       // B partial sums visible
     FTB_TICK(5)
     if (pg == 1) gate_group(step);
