@@ -293,6 +293,8 @@ def run_ours(args, rank, world, local_rank):
             k['gbs'] = round(info['bytes'] / ms / 1e6, 1)
         if info['kind'] == 'rnn':
             k['us_per_step'] = round(ms * 1e3 / info['steps'], 3)
+            k['handoff'] = info.get('handoff')
+            k['kernel_launches'] = info.get('kernel_launches')
         kernels.append((k, info))
     C = model.lstm.input_size
     lr_bytes = {'lr_gather': 4.0 * B * T * C + 4.0 * B * T + 4.0 * B * M * C, 'lr_scan': 2 * 4.0 * B * T}
@@ -306,11 +308,13 @@ def run_ours(args, rank, world, local_rank):
     #                            tensor peak of its operand mix: kind::f16 layers against the measured bf16 burst figure,
     #                            kind::tf32 layers against half of it (each launch is timed alone); `peak` is the
     #                            FLOP-weighted harmonic mean, i.e. flops / (time at peak of every layer);
-    #   rnn_persistent_kernel -> HBM bound: x-projection reads + layer-output writes / summed launch time (the kernel is a
-    #                            latency chain; its fraction of the HBM peak is reported for completeness).
+    #   rnn_cluster_kernel / rnn_persistent_kernel (cluster / L2 hand-off of h) -> HBM bound: x-projection
+    #                            reads + layer-output writes / summed launch time (the kernels are latency chains;
+    #                            their fraction of the HBM peak is reported for completeness).
     groups = {}
     for k, info in kernels:
-        fn = {'gemm': 'conv_gemm_tc_kernel', 'rnn': 'rnn_persistent_kernel'}.get(k['kind'], k['kind'])
+        fn = {'gemm': 'conv_gemm_tc_kernel',
+              'rnn': 'rnn_cluster_kernel' if info.get('handoff') == 'cluster' else 'rnn_persistent_kernel'}.get(k['kind'], k['kind'])
         if k.get('side') == 'lr':
             fn = k['label'] + '_kernel'
         g = groups.setdefault(fn, {'ms': 0.0, 'flops': 0.0, 'flops_f16': 0.0, 'bytes': 0.0, 'launches': 0})
@@ -318,7 +322,7 @@ def run_ours(args, rank, world, local_rank):
         g['ms'] += k['ms']
         g['flops'] += info.get('flops') or 0.0
         g['bytes'] += info.get('bytes') or 0.0
-        g['launches'] += 1
+        g['launches'] += info.get('kernel_launches') or 1
     by_kernel = []
     for fn, g in sorted(groups.items(), key=lambda kv: -kv[1]['ms']):
         if fn == 'conv_gemm_tc_kernel':

@@ -93,6 +93,16 @@ extern "C" int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream) {
   return rnn_plan_launch(it->second, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int ftb_rnn_plan_info(ftb_handle h, int plan, int* handoff, int* kernel_launches, int* lanes) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->rnn_plans.find(plan);
+  if (it == h->rnn_plans.end()) return FTB_E_PLAN;
+  if (handoff) *handoff = it->second.cluster ? 1 : 0;
+  if (kernel_launches) *kernel_launches = static_cast<int>(it->second.launches.size());
+  if (lanes) *lanes = it->second.lanes;
+  return 0;
+}
+
 extern "C" int ftb_rnn_plan_destroy(ftb_handle h, int plan) {
   if (!h) return FTB_E_ARG;
   auto it = h->rnn_plans.find(plan);

@@ -1,9 +1,28 @@
 // K3/K4: persistent bidirectional GRU / LSTM recurrence for sm_100a.
 //
-// One cooperative launch runs every (problem, direction, batch-group, unit-slice) CTA of a plan.
-// A CTA owns U = 32 hidden units (all gates: G*U rows of W_hh) for NB = 16 batch columns and keeps
-// its W_hh rows RESIDENT IN REGISTERS as fp16 mma.sync A-fragments for all time steps (LSTM H=512:
-// 128 rows x 512 = 128 KB per CTA, half the register file).
+// One launch runs every (problem, direction, batch-group, unit-slice) CTA of a plan.  A CTA owns U = 32 hidden
+// units (all gates: G*U rows of W_hh) for NB = 16 batch columns and keeps its W_hh rows RESIDENT IN REGISTERS as
+// fp16 mma.sync A-fragments for all time steps (LSTM H=512: 128 rows x 512 = 128 KB per CTA, half the register
+// file).  The H/32 CTAs of one (direction, batch group) -- a "unit" -- exchange h_t every step; units are
+// independent of each other.  Two hand-off protocols, chosen per plan (rnn_plan_build):
+//
+// (1) CLUSTER hand-off (rnn_cluster_kernel; the GRUs, and the LSTM when <= 7 units are needed).  The CTAs of a unit
+//     sit in one thread-block cluster (size = H/32 = 2..16).  After the gate math every thread owns h_t of one
+//     (unit, column) pair; three xor-shuffle rounds gather 8 units into a 16-byte chunk and each lane pushes its
+//     chunk straight into the staged h tile of a peer CTA's SHARED MEMORY with
+//         st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32
+//     The consumer waits on a local mbarrier whose phase completes when all H*32 bytes of the step have landed
+//     (one local arrive.expect_tx arms the phase).  Tiles and barriers are double-buffered by step parity; a peer
+//     can never be two steps ahead because its step t+1 needs this CTA's h_t.  No global-memory exchange tensor,
+//     no sentinel pre-fill, no cooperative launch (units never straddle clusters).  The hand-off costs ~450 cycles
+//     (L2 path: ~1800), so the CTA runs ONE group of 16 columns (two n-tiles per A fragment, one CTA barrier per
+//     step) instead of interleaving two groups.  Problems are grouped by cluster size into concurrent launch
+//     "lanes" (side streams), because a launch has one cluster size and large clusters pack badly into the GPCs:
+//     this B200 keeps 15 clusters of 8 and 7 clusters of 16 CTAs resident (7 GPCs x 20 SMs + 1 x 8).  The batch-64
+//     LSTM needs 8 units of 16 CTAs and therefore stays on protocol (2).
+//
+// (2) L2 hand-off (rnn_persistent_kernel, cooperative launch; v4: two interleaved batch groups per CTA, A = columns
+//     0-7, B = columns 8-15).
 //
 // Operand precision.  The recurrent product uses fp16 operands with fp32 accumulation: fp16 carries
 // the same 11 significant bits as tf32 (|h| <= 1 and |W_hh| ~ 1/sqrt(H) sit well inside its range; below
@@ -11,21 +30,21 @@
 // HMMA.1688 per issue slot -- measured here: tf32 mma.sync sustains ~290 MAC/clk/SM on B200 and was the
 // bound of the first version of this kernel (profiles/r1b_rnn_phases.txt).  h_t is therefore published
 // twice: as fp32 (exactly the fp16 value, hence tf32-exact) into the layer output the next GEMM reads,
-// and as fp16 into a compact exchange tensor hx[dir][t][b][H] that the other CTAs poll.
+// and as fp16 to the other CTAs of the unit (peer shared memory, or the exchange tensor hx[dir][t][b][H]).
 //
-// Per step (v4: two interleaved batch groups per CTA, A = columns 0-7, B = columns 8-15):
-//     h_{t-1} (fp16, L2-resident) -> staged ONCE per CTA and group into smem by cp.async.cg (16 B per thread,
-//         bypassing L1).  hx is pre-filled with 0xFFFF halves (an fp16 NaN no arithmetic here produces), so
-//         "h arrived" == "no sentinel left": after cp.async.wait_group each thread checks the 16 bytes it
-//         staged and re-fetches (ld.relaxed.gpu) only those that still hold the sentinel.  No counter, no
-//         __threadfence, no atomic on the critical path.  The K range is split over KS = 2 warp groups that
-//         synchronise with named barriers, so each half starts its MMAs as soon as its own bytes have landed.
+// Per step of protocol (2):
+//     h_{t-1} (fp16, L2-resident) -> loaded ONCE per CTA and group with ld.relaxed.gpu (16 B per thread, issued one
+//         phase ahead, staged into smem when it is needed).  hx is pre-filled with 0xFFFF halves (an fp16 NaN no
+//         arithmetic here produces), so "h arrived" == "no sentinel left": each thread checks the 16 bytes it
+//         loaded and re-fetches only those that still hold the sentinel.  No counter, no __threadfence, no atomic
+//         on the critical path.  The K range is split over KS = 2 warp groups that synchronise with named
+//         barriers, so each half starts its MMAs as soon as its own bytes have landed.
 //       -> B-fragments from smem (one LDS.128 feeds two k-steps: K is permuted inside 32-wide blocks),
 //          mma.sync.m16n8k16 f16 -> fp32 accumulators; ALL MMA warps work on the group whose h has landed
 //          while the other group's h is still in flight (the L2 hand-off of A hides behind the MMAs of B).
 //       -> partial sums through padded smem -> __syncthreads -> gate math in fp32 by the group's 8 warps
 //          (c, h stay in registers; x-projection rows arrive through a 4-stage cp.async ring issued three
-//          steps ahead, so their DRAM latency is off the critical path)
+//          steps ahead -- always the newest cp.async group, so nothing on the chain ever waits for it)
 //       -> h_t stores (fp32 to `out`, fp16 pairs to hx).
 // Packed-sequence semantics (optional `lens`): a column whose sentence has ended keeps h = c = 0 and writes
 // `pad_value` to `out` -- what pack_padded_sequence / pad_packed_sequence give the reference's eval-mode forward.
@@ -235,38 +254,34 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     if (mma_warp && i < ITEMS && b < nbv) ok_a |= 1u << j;
     if (mma_warp && i < ITEMS && b + NBG < nbv) ok_b |= 1u << j;
   }
-  // issue / settle take the offset (in halves) of the wanted time row relative to hp[]: 0 = row t, -h_step = row t-1
-  auto issue_h = [&](int g, long long toff) {       // fire-and-forget; one commit group
+  // issue / settle take the offset (in halves) of the wanted time row relative to hp[]: 0 = row t, -h_step = row t-1.
+  // The items travel through REGISTERS (ld.relaxed.gpu at issue time, st.shared at settle time): an LDGSTS per thread
+  // cost ~600 cycles of issue time per group on the step-to-step chain (profiles/r1o_rnn_phases.txt); an LDG issues in
+  // a few cycles and its latency is covered by the other group's phases.  Only one group is in flight at a time.
+  uint4 hv[IPT];
+  auto issue_h = [&](int g, long long toff) {
     const unsigned ok = g ? ok_b : ok_a;
 #pragma unroll
     for (int j = 0; j < IPT; ++j)
-      if (ok & (1u << j)) cp_async16(hd[j] + g * (NBG * HS), hp[j] + toff + g * (NBG * H));
-    cp_async_commit();
+      if (ok & (1u << j)) hv[j] = ld_relaxed_u4(hp[j] + toff + g * (NBG * H));
   };
-  // after the copies have landed: "h arrived" == "no 0xFFFF half left"; re-fetch the items that still hold the
-  // sentinel (their producer had not published yet when the copy read L2)
+  // "h arrived" == "no 0xFFFF half left"; re-fetch the items that still hold the sentinel (their producer had not
+  // published yet when the load read L2), then place them in the staged tile
   auto settle_h = [&](int g, long long toff, unsigned& retries) {
     const unsigned ok = g ? ok_b : ok_a;
-    unsigned spins = 0;
-    while (true) {
-      bool again = false;
 #pragma unroll
-      for (int j = 0; j < IPT; ++j) {
-        if (ok & (1u << j)) {
-          const uint4 v = *reinterpret_cast<const uint4*>(hd[j] + g * (NBG * HS));
-          if (has_sentinel(v.x) || has_sentinel(v.y) || has_sentinel(v.z) || has_sentinel(v.w)) {
-            cp_async16(hd[j] + g * (NBG * HS), hp[j] + toff + g * (NBG * H));
-            again = true;
+    for (int j = 0; j < IPT; ++j) {
+      if (ok & (1u << j)) {
+        unsigned spins = 0;
+        while (has_sentinel(hv[j].x) || has_sentinel(hv[j].y) || has_sentinel(hv[j].z) || has_sentinel(hv[j].w)) {
+          hv[j] = ld_relaxed_u4(hp[j] + toff + g * (NBG * H));
+          ++retries;
+          if (++spins > (1u << 22)) {
+            printf("ftb: recurrence wait for h timed out (block %d)\n", blockIdx.x);
+            __trap();
           }
         }
-      }
-      if (!again) break;
-      cp_async_commit();
-      cp_async_wait<0>();
-      ++retries;
-      if (++spins > (1u << 20)) {
-        printf("ftb: recurrence wait for h timed out (block %d)\n", blockIdx.x);
-        __trap();
+        *reinterpret_cast<uint4*>(hd[j] + g * (NBG * HS)) = hv[j];
       }
     }
   };
@@ -301,20 +316,30 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       }
       return;
     }
-    float acc0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, acc1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    // NCH independent accumulator chains
+    constexpr int NCH = 2;                 // 4 chains spill at the 128-register cap: LSTM 0.86 -> 0.97 ms (measured)
+    float acc[NCH][4];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
     const __half* hrow = h_s + (g * NBG + fr) * HS + kq * KW + 8 * q;
 #pragma unroll
     for (int kb = 0; kb < KB; ++kb) {
-      const uint4 hv = *reinterpret_cast<const uint4*>(hrow + kb * 32);
-      mma_f16_16x8x16(acc0, wfrag[kb * 2 + 0], hv.x, hv.y);
-      mma_f16_16x8x16(acc1, wfrag[kb * 2 + 1], hv.z, hv.w);
+      const uint4 hq = *reinterpret_cast<const uint4*>(hrow + kb * 32);
+      mma_f16_16x8x16(acc[(2 * kb) % NCH], wfrag[kb * 2 + 0], hq.x, hq.y);
+      mma_f16_16x8x16(acc[(2 * kb + 1) % NCH], wfrag[kb * 2 + 1], hq.z, hq.w);
+    }
+    if (NCH == 4) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { acc[0][j] += acc[2][j]; acc[1][j] += acc[3][j]; }
     }
     float* pk = p_s + static_cast<size_t>(g * KS + kq) * NBG * S;
     const int col = 2 * q, row = rs * 16 + fr;
-    pk[col * S + row] = acc0[0] + acc1[0];
-    pk[(col + 1) * S + row] = acc0[1] + acc1[1];
-    pk[col * S + row + 8] = acc0[2] + acc1[2];
-    pk[(col + 1) * S + row + 8] = acc0[3] + acc1[3];
+    pk[col * S + row] = acc[0][0] + acc[1][0];
+    pk[(col + 1) * S + row] = acc[0][1] + acc[1][1];
+    pk[col * S + row + 8] = acc[0][2] + acc[1][2];
+    pk[(col + 1) * S + row + 8] = acc[0][3] + acc[1][3];
   };
   // cluster hand-off: this lane's peers (CTAs of the same unit = cluster ranks [rank - slice, rank - slice + SL))
   uint32_t rdata[ND], rbar[ND], rvalid = 0;
@@ -344,7 +369,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   const float* xs0 = x_s + pb * XSTR + pu;
 #ifdef FTB_RNN_PROFILE
   // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
-  unsigned long long prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  unsigned long long prof[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 #define FTB_TICK(i) { const long long now_ = clock64(); prof[i] += now_ - tick_; tick_ = now_; }
   long long tick_ = clock64();
 #else
@@ -457,25 +482,23 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     }
     // ---------------- group A --------------------------------------------------------------------
     if (step > 0 && mma_warp) {
-      cp_async_wait<1>();                  // A copies were issued in the previous iteration (the x prefetch committed
-                                           // after them may still be in flight: it is needed three steps from now)
-      settle_h(0, -h_step, retries);
+      settle_h(0, -h_step, retries);       // A loads were issued in the previous iteration
       FTB_TICK(1)
       named_bar_sync(1 + kq, GS);
+      FTB_TICK(8)
       if (has_b) issue_h(1, -h_step);      // group B of t-1 was published at the end of the previous iteration
+      FTB_TICK(9)
       mma_group(0, 0);
+      FTB_TICK(10)
     }
-    if (step == 0 || !mma_warp) cp_async_wait<RNN_XS - 2>();   // x chunk of this step (MMA warps: covered above)
+    cp_async_wait<RNN_XS - 2>();           // own x chunk of this step (issued three steps ago)
     __syncthreads();                       // A partial sums + everyone's x chunks visible; ring slot (step-1) free
     FTB_TICK(2)
     if (pg == 0) gate_group(step);
     FTB_TICK(3)
     // ---------------- group B --------------------------------------------------------------------
     if (mma_warp) {
-      if (step > 0 && has_b) {
-        cp_async_wait<0>();                // B copies done (and the x prefetch of the previous step, long since)
-        settle_h(1, -h_step, retries);
-      }
+      if (step > 0 && has_b) settle_h(1, -h_step, retries);
       FTB_TICK(4)
       named_bar_sync(3 + kq, GS);          // also orders gate A's publication before the A re-fetch below
       if (step + 1 < L) issue_h(0, 0);     // group A of step t: published by the A-warps of all CTAs just now
@@ -492,8 +515,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   cp_async_wait<0>();
 #ifdef FTB_RNN_PROFILE
   if (tid == 0 && (local_cta % 37) == 0)
-    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu waitA %llu mmaA+sync %llu gateA %llu waitB %llu mmaB+sync %llu gateB %llu p7 %llu | retries/step %.2f\n",
-           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L, prof[6] / L, prof[7] / L,
+    printf("rnn prof G=%d H=%d cta %d L %d: cycles/step top %llu waitA %llu mmaA+sync %llu gateA %llu waitB %llu mmaB+sync %llu gateB %llu p7 %llu barA %llu issueB %llu mmaA %llu | retries/step %.2f\n",
+           G, H, local_cta, L, prof[0] / L, prof[1] / L, prof[2] / L, prof[3] / L, prof[4] / L, prof[5] / L, prof[6] / L, prof[7] / L, prof[8] / L, prof[9] / L, prof[10] / L,
            static_cast<float>(retries) / L);
 #endif
 }

@@ -140,7 +140,7 @@ class Program:
                               'flops': flops, 'flops_f16': flops_f16, 'bytes': nbytes, 'problems': len(grp)})
 
     def rnn(self, specs, lens: Optional[torch.Tensor] = None, pad_value: float = 0.0):
-        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one cooperative launch.
+        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one plan (cluster or cooperative launches).
         `lens` (int32 [batch], device): packed-sequence semantics for every problem of the launch."""
         self.flush()
         g = self.geo
@@ -163,7 +163,7 @@ class Program:
         nbytes = sum(4.0 * valid * (2 * (4 if r.cell else 3) * r.hidden + 2 * r.hidden) + 4.0 * r.w_hh.numel()
                      for r, _, _, _ in specs)
         self.info.append({'kind': 'rnn', 'label': self._label or 'rnn', 'flops': flops, 'bytes': nbytes,
-                          'steps': g.seq_len, 'problems': len(specs)})
+                          'steps': g.seq_len, 'problems': len(specs), **self.h.rnn_info(plan)})
 
     def call(self, fn: Callable[[], None], label: str = 'glue', nbytes: float = 0.0):
         self.flush()

@@ -52,7 +52,7 @@ class LrGatherArgs(C.Structure):
 # every symbol include/ftb200.h declares (tests check that the .so exports all of them)
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
            'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy',
-           'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy',
+           'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
            'ftb_lr_scan', 'ftb_lr_gather', 'ftb_embed', 'ftb_rowdot', 'ftb_argmax_lastdim',
            'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha']
 
@@ -79,6 +79,7 @@ def load_library() -> C.CDLL:
     lib.ftb_rnn_plan_create.argtypes = [_fp, C.POINTER(RnnProblem), C.c_int, C.POINTER(C.c_int)]
     lib.ftb_rnn_plan_run.argtypes = [_fp, C.c_int, _fp]
     lib.ftb_rnn_plan_destroy.argtypes = [_fp, C.c_int]
+    lib.ftb_rnn_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_lr_scan.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_lr_gather.argtypes = [_fp, C.POINTER(LrGatherArgs), _fp]
     lib.ftb_embed.argtypes = [_fp, _fp, _fp, C.c_int, _fp, _fp, C.c_int, _fp, C.c_int,
@@ -162,6 +163,12 @@ class Handle:
 
     def rnn_run(self, plan: int):
         self.check(self.lib.ftb_rnn_plan_run(self.h, plan, self.stream()))
+
+    def rnn_info(self, plan: int) -> dict:
+        """Layout the library chose for the plan on this device (include/ftb200.h: ftb_rnn_plan_info)."""
+        handoff, launches, lanes = C.c_int(), C.c_int(), C.c_int()
+        self.check(self.lib.ftb_rnn_plan_info(self.h, plan, C.byref(handoff), C.byref(launches), C.byref(lanes)))
+        return {'handoff': 'cluster' if handoff.value else 'l2', 'kernel_launches': launches.value, 'lanes': lanes.value}
 
     def rnn_destroy(self, plan: int):
         self.check(self.lib.ftb_rnn_plan_destroy(self.h, plan))

@@ -118,9 +118,12 @@ int ftb_gemm_plan_destroy(ftb_handle h, int plan);
  * nn.LSTM (forward_tacotron.py:224), batch_first, bidirectional, h0 = c0 = 0, run over the
  * full padded length (no packing in generate()).  xproj holds W_ih x + b_ih for
  * [forward | reverse] (K2 output); W_hh stays resident in registers (fp16 MMA fragments, fp32
- * accumulation) for all steps; h_t is handed between CTAs through a plan-owned fp16 exchange tensor
- * whose sentinel pre-fill doubles as the per-step synchronisation (no counter barrier), and written
- * as fp32 to `out`, the layer output.
+ * accumulation) for all steps; h_t is handed between the CTAs of one (direction, 16-sentence group)
+ * either through peer shared memory inside a thread-block cluster (st.async + mbarrier; the GRUs and
+ * small-batch LSTMs) or through a plan-owned fp16 exchange tensor in L2 whose sentinel pre-fill doubles
+ * as the per-step synchronisation (no counter barrier); the plan picks the protocol from the cluster
+ * occupancy of the device (FTB_RNN_HANDOFF=l2|cluster overrides).  h_t is written as fp32 to `out`, the
+ * layer output.  A plan may launch on plan-owned side streams that are forked from and joined to `stream`.
  *   GRU  (r,z,n): r = s(xr + Whr h + bhr); z = s(xz + Whz h + bhz);
  *                 n = tanh(xn + r*(Whn h + bhn)); h' = (1-z)*n + z*h
  *   LSTM (i,f,g,o): c' = s(f)*c + s(i)*tanh(g); h' = s(o)*tanh(c')
@@ -147,6 +150,9 @@ typedef struct {
 int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems, int nproblems, int* plan_out);
 int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream);
 int ftb_rnn_plan_destroy(ftb_handle h, int plan);
+/* How the plan was laid out on this device: *handoff = 1 thread-block-cluster hand-off, 0 L2 hand-off;
+ * *kernel_launches = kernel launches per run; *lanes = concurrent launch sequences (1 = all on `stream`). */
+int ftb_rnn_plan_info(ftb_handle h, int plan, int* handoff, int* kernel_launches, int* lanes);
 
 /* ------------------------------------------------------------------------------------
  * K5/K6  duration rounding + LengthRegulator gather (+ fused pitch/energy projection add)

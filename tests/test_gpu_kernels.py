@@ -216,6 +216,37 @@ def test_recurrence(cell, H, B, L):
     assert torch.equal(prog.view('h').cpu(), got)
 
 
+@pytest.mark.parametrize('cell,H,B,L', [('gru', 64, 17, 21), ('gru', 256, 20, 19), ('lstm', 512, 33, 9)])
+def test_recurrence_handoff_protocols_agree(cell, H, B, L, monkeypatch):
+    """The two hand-off protocols of K3/K4 (peer shared memory inside a thread-block cluster / fp16 exchange tensor in
+    L2 with in-band sentinels) run the same arithmetic in the same order: their outputs are bit-identical, and the plan
+    reports which one it took (cluster sizes 2, 8 and the non-portable 16 are all exercised here)."""
+    gen = torch.Generator().manual_seed(7 * H + B)
+    In = 64
+    rnn = (torch.nn.GRU if cell == 'gru' else torch.nn.LSTM)(In, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    packed = pk.PackedRnn(rnn.to(DEV))
+    got = {}
+    for mode in ('cluster', 'l2'):
+        monkeypatch.setenv('FTB_RNN_HANDOFF', mode)
+        prog = eng.Program(_handle(), eng.Geometry(B, L))
+        g2 = torch.Generator().manual_seed(B)
+        a, _ = _fill(prog, 'x', In, g2)
+        xp = prog.buf('xp', packed.ih.n)
+        out = prog.buf('h', 2 * H)
+        prog.gemm(a, packed.ih, xp, round_out=False)
+        prog.rnn([(packed, xp, out, 0)])
+        assert prog.info[-1]['handoff'] == mode
+        for _ in range(2):                                   # second run: barriers / sentinels re-armed
+            prog.run()
+        torch.cuda.synchronize()
+        got[mode] = prog.view('h').cpu().clone()
+        assert bool(torch.isfinite(got[mode]).all())
+    assert torch.equal(got['cluster'], got['l2'])
+
+
 @pytest.mark.parametrize('cell,H,B,L', [('gru', 128, 5, 33), ('lstm', 512, 19, 27)])
 def test_recurrence_packed_sequence_semantics(cell, H, B, L):
     """`lens` != null: pack_padded_sequence -> RNN -> pad_packed_sequence(padding_value) of forward_tacotron.py:147-152
