@@ -265,6 +265,17 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     for (int j = 0; j < IPT; ++j)
       if (ok & (1u << j)) hv[j] = ld_relaxed_u4(hp[j] + toff + g * (NBG * H));
   };
+  // Opportunistic second poll one phase after the issue: an item that came back with the sentinel (its producer was
+  // slower than this CTA) is re-requested now, so the blocking re-fetch in settle_h -- which stalls the whole K group at
+  // its named barrier for a full L2 round trip -- becomes the exception.
+  auto refresh_h = [&](int g, long long toff) {
+    const unsigned ok = g ? ok_b : ok_a;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j)
+      if ((ok & (1u << j)) &&
+          (has_sentinel(hv[j].x) || has_sentinel(hv[j].y) || has_sentinel(hv[j].z) || has_sentinel(hv[j].w)))
+        hv[j] = ld_relaxed_u4(hp[j] + toff + g * (NBG * H));
+  };
   // "h arrived" == "no 0xFFFF half left"; re-fetch the items that still hold the sentinel (their producer had not
   // published yet when the load read L2), then place them in the staged tile
   auto settle_h = [&](int g, long long toff, unsigned& retries) {
@@ -489,6 +500,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       if (has_b) issue_h(1, -h_step);      // group B of t-1 was published at the end of the previous iteration
       FTB_TICK(9)
       mma_group(0, 0);
+      if (has_b) refresh_h(1, -h_step);
       FTB_TICK(10)
     }
     cp_async_wait<RNN_XS - 2>();           // own x chunk of this step (issued three steps ago)
@@ -503,6 +515,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       named_bar_sync(3 + kq, GS);          // also orders gate A's publication before the A re-fetch below
       if (step + 1 < L) issue_h(0, 0);     // group A of step t: published by the A-warps of all CTAs just now
       if (step > 0 && has_b) mma_group(1, 0);
+      if (step + 1 < L) refresh_h(0, 0);
 #pragma unroll
       for (int j = 0; j < IPT; ++j) hp[j] += h_step;
     }
