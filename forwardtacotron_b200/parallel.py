@@ -25,12 +25,30 @@ def mel_lengths(dur: torch.Tensor) -> torch.Tensor:
     return (dur.clamp_min(0) + 0.5).long().sum(dim=1)
 
 
+_HOST_GROUPS = {}
+
+
+def _host_group(group):
+    """A gloo twin of the default (NCCL) process group for host-side metadata, created on first use by a collective
+    call of all ranks; None when `group` is a sub-group or the twin cannot be created (then the metadata travels
+    through NCCL and costs a device sync)."""
+    if group is not None and group is not dist.group.WORLD:
+        return None
+    if 'world' not in _HOST_GROUPS:
+        try:
+            _HOST_GROUPS['world'] = dist.new_group(backend='gloo')
+        except Exception:
+            _HOST_GROUPS['world'] = None
+    return _HOST_GROUPS['world']
+
+
 def gather_variable_mels(mel: torch.Tensor, lens: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
     """All-gather `[b_local, C, M_local]` mels whose batch and frame extents differ per rank.
 
-    Two collectives: one all_gather of (b_local, M_local) per rank, one all_gather of the zero-padded
-    `[b_max, C, M_max]` blocks (plus the lengths).  Returns (`[B_total, C, M_max]`, `[B_total]` int64) with the
-    sentences in rank order, i.e. the order of the un-sharded batch under `shard_slice`.
+    The extents (b_local, M_local) of every shard are host-known shapes: they are exchanged over a host-side (gloo)
+    group, so the GPU stream is never drained -- the NCCL all_gather of the zero-padded `[b_max, C, M_max]` blocks (plus
+    the lengths) is enqueued behind the still-running frame program of `generate()`.  Returns (`[B_total, C, M_max]`,
+    `[B_total]` int64) with the sentences in rank order, i.e. the order of the un-sharded batch under `shard_slice`.
     Frames beyond a shard's own M_local are zero (the shard never computed them).
     """
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
@@ -38,10 +56,16 @@ def gather_variable_mels(mel: torch.Tensor, lens: torch.Tensor, group=None) -> T
     world = dist.get_world_size(group)
     dev = mel.device
     b_local, C, m_local = mel.shape
-    meta = torch.tensor([b_local, m_local], dtype=torch.int64, device=dev)
-    metas = torch.empty((world, 2), dtype=torch.int64, device=dev)
-    _all_gather(metas, meta, group)
-    metas = metas.cpu()                                  # the one host sync: extents of every shard
+    host = _host_group(group) if mel.is_cuda else group
+    if host is not None or not mel.is_cuda:
+        meta = torch.tensor([b_local, m_local], dtype=torch.int64)
+        metas = torch.empty((world, 2), dtype=torch.int64)
+        _all_gather(metas, meta, host)
+    else:
+        meta = torch.tensor([b_local, m_local], dtype=torch.int64, device=dev)
+        metas = torch.empty((world, 2), dtype=torch.int64, device=dev)
+        _all_gather(metas, meta, group)
+        metas = metas.cpu()                              # sub-group without a host twin: one device sync
     counts = [int(v) for v in metas[:, 0]]
     b_max, m_max = max(counts), int(metas[:, 1].max())
     uniform = all(c == b_max for c in counts) and bool((metas[:, 1] == m_max).all())
