@@ -4,6 +4,19 @@
 
 using namespace ftb;
 
+namespace {
+// Plans allocate, set function attributes and launch on the handle's device: make it current for the call and put
+// the caller's device back afterwards (a process that drives several GPUs keeps one handle per device).
+struct DeviceScope {
+  int prev = -1;
+  bool switched = false;
+  explicit DeviceScope(int device) {
+    if (cudaGetDevice(&prev) == cudaSuccess && prev != device) switched = cudaSetDevice(device) == cudaSuccess;
+  }
+  ~DeviceScope() { if (switched) cudaSetDevice(prev); }
+};
+}  // namespace
+
 extern "C" int ftb_version(void) { return FTB_VERSION; }
 
 extern "C" const char* ftb_error_string(int code) {
@@ -48,6 +61,7 @@ extern "C" int64_t ftb_launch_count(ftb_handle h) { return h ? h->launches : -1;
 
 extern "C" int ftb_gemm_plan_create(ftb_handle h, const ftb_gemm_problem* problems, int nproblems, int* plan_out) {
   if (!h || !plan_out) return FTB_E_ARG;
+  DeviceScope scope(h->device);
   GemmPlan plan;
   const int rc = gemm_plan_build(problems, nproblems, &plan);
   if (rc) return rc;
@@ -59,6 +73,7 @@ extern "C" int ftb_gemm_plan_create(ftb_handle h, const ftb_gemm_problem* proble
 
 extern "C" int ftb_gemm_plan_run(ftb_handle h, int plan, int impl, void* stream) {
   if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
   auto it = h->gemm_plans.find(plan);
   if (it == h->gemm_plans.end()) return FTB_E_PLAN;
   h->launches += 1;
@@ -67,6 +82,7 @@ extern "C" int ftb_gemm_plan_run(ftb_handle h, int plan, int impl, void* stream)
 
 extern "C" int ftb_gemm_plan_destroy(ftb_handle h, int plan) {
   if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
   auto it = h->gemm_plans.find(plan);
   if (it == h->gemm_plans.end()) return FTB_E_PLAN;
   cudaFree(it->second.dev);
@@ -76,6 +92,7 @@ extern "C" int ftb_gemm_plan_destroy(ftb_handle h, int plan) {
 
 extern "C" int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems, int nproblems, int* plan_out) {
   if (!h || !plan_out) return FTB_E_ARG;
+  DeviceScope scope(h->device);
   RnnPlan plan;
   const int rc = rnn_plan_build(problems, nproblems, h->num_sms, &plan);
   if (rc) return rc;
@@ -87,6 +104,7 @@ extern "C" int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems
 
 extern "C" int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream) {
   if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
   auto it = h->rnn_plans.find(plan);
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
   h->launches += static_cast<int64_t>(it->second.launches.size() + it->second.hx.size());   // + sentinel pre-fills (L2 hand-off)
@@ -105,6 +123,7 @@ extern "C" int ftb_rnn_plan_info(ftb_handle h, int plan, int* handoff, int* kern
 
 extern "C" int ftb_rnn_plan_destroy(ftb_handle h, int plan) {
   if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
   auto it = h->rnn_plans.find(plan);
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
   rnn_plan_free(it->second);

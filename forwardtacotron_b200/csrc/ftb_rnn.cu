@@ -740,6 +740,9 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
     }
   }
   if (!plan->cluster) {
+    cudaError_t ae = cudaFuncSetAttribute(rnn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          rnn_smem_bytes(FTB_CELL_LSTM, 512, false));
+    if (ae != cudaSuccess) return static_cast<int>(ae);
     for (int i = 0; i < nproblems; ++i) {
       const ftb_rnn_problem& q = problems[i];
       const size_t hx_bytes = static_cast<size_t>(2) * q.seq_len * q.batch * q.hidden * sizeof(__half);
@@ -806,13 +809,7 @@ int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream) {
     }
     return 0;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    ce = cudaFuncSetAttribute(rnn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              rnn_smem_bytes(FTB_CELL_LSTM, 512, false));
-    if (ce != cudaSuccess) return static_cast<int>(ce);
-    attr_set = true;
-  }
+  // (the shared-memory attribute of rnn_persistent_kernel was set for this device when the plan was built)
   // arm the in-band "not written yet" marker (0xFFFF halves) in every exchange slot the recurrences publish
   for (size_t i = 0; i < plan.hx.size(); ++i) {
     ce = cudaMemsetAsync(plan.hx[i], 0xFF, plan.hx_bytes[i], stream);

@@ -200,6 +200,17 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
 
+    def generate_jit(self, x: torch.Tensor, alpha: float = 1.0, beta: float = 1.0) -> Dict[str, torch.Tensor]:
+        """The callback-free twin of generate() the reference exports to TorchScript (forward_tacotron.py:186-200):
+        durations / alpha, pitch * beta, no pitch / energy callbacks and -- unlike generate() -- no eval() side effect.
+        It runs on the same sm_100a kernels; the module itself is not scriptable (the kernels are reached through
+        ctypes), so the method is offered under the reference's name for callers of an exported model."""
+        if self.training:
+            raise RuntimeError('generate_jit(): the module is in training mode; the reference exports and calls the '
+                               'scripted module in eval mode (README "Export Model with TorchScript") -- call .eval() first')
+        beta = float(beta)
+        return self.generate(x, alpha=float(alpha), pitch_function=lambda p: p * beta)
+
     def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         """forward(batch) in eval mode under no_grad on the sm_100a kernels (forward_tacotron.py:118-165):
         predictors for the returned dur/pitch/energy, teacher-forced durations / pitch / energy for the mel branch,

@@ -334,6 +334,25 @@ def test_forward_tacotron_tiny_and_odd_shapes(B, T):
             assert max_abs(out[k].cpu(), ref[k]) < MEL_ABS and rel_l2(out[k].cpu(), ref[k]) < MEL_REL, k
 
 
+def test_forward_tacotron_generate_jit_twin():
+    """generate_jit(x, alpha, beta) (forward_tacotron.py:186-200) = generate() with the pitch scaled by beta and no
+    callbacks; bit-identical to the equivalent generate() call, and it refuses a module left in training mode."""
+    model = init_tts_model(default_config('forward_tacotron'))
+    model.load_state_dict(synth.synth_state_dict(model.state_dict(), seed=5))
+    model = model.to(DEV).eval()
+    x = synth.synth_tokens(3, 29, seed=5).to(DEV)
+    a = model.generate_jit(x, alpha=1.25, beta=1.5)
+    b = model.generate(x, alpha=1.25, pitch_function=lambda p: p * 1.5)
+    assert set(a) == {'mel', 'mel_post', 'dur', 'pitch', 'energy'}
+    for k in a:
+        assert torch.equal(a[k], b[k]), k
+    base = model.generate(x, alpha=1.25)
+    assert torch.equal(a['pitch'], base['pitch'] * 1.5) and torch.equal(a['dur'], base['dur'])
+    model.train()
+    with pytest.raises(RuntimeError):
+        model.generate_jit(x)
+
+
 def test_forward_tacotron_all_zero_durations_raise():
     """dur_hat <= 0 everywhere with the integer fallback NOT triggered cannot happen in generate() (the fallback fills
     2.0, forward_tacotron.py:176-177); the teacher-forced entry with all-zero durations has nothing to synthesise."""
