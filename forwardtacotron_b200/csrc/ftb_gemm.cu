@@ -82,9 +82,15 @@ __device__ __forceinline__ float epi_affine(const GemmProblemDev* p, float acc, 
   const float b = p->shift ? __ldg(p->shift + n) : 0.0f;
   return v * s + b;     // contracted to one FMA: y = relu(acc)*s + b, s/b precomputed on the host
 }
+// y = g*relu(x1) + (1-g)*x with g = sigmoid(x2) (common_layers.py:36-39), as x + g*(relu(x1) - x): 7 instructions per
+// output (FMUL, MUFU.EX2, FADD, MUFU.RCP, FMNMX, FADD, FFMA).  The highway epilogue is issue-bound (~430 SASS
+// instructions per 16-unit chunk before this form, profiles/r1r_highway_ncu.txt); __expf / __fdividef carried range
+// fix-ups that the bare ex2 / rcp (~2 ulp, far below the tf32 operand rounding) do not need: |x2| < 88 here.
 __device__ __forceinline__ float epi_highway(float x1, float x2, float x) {
-  const float g = __fdividef(1.0f, 1.0f + __expf(-x2));     // ~2 ulp: far below the tf32 operand rounding
-  return g * fmaxf(x1, 0.0f) + (1.0f - g) * x;
+  float e, g;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x2));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(g) : "f"(1.0f + e));
+  return fmaf(g, fmaxf(x1, 0.0f) - x, x);
 }
 __device__ __forceinline__ float epi_finish(const GemmProblemDev* p, float v) {
   return (p->flags & FTB_F_ROUND_TF32) ? round_tf32(v) : v;
