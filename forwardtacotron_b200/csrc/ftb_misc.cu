@@ -15,11 +15,10 @@ __device__ __forceinline__ void embed_store(float* out, long long i, float v, in
   else out[i] = mode ? round_tf32(v) : v;
 }
 
-__global__ void __launch_bounds__(256)
-embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
-             const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
-             const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
-             float* __restrict__ out, int out_ld, int mode) {
+__device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
+                                           const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
+                                           const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
+                                           float* __restrict__ out, int out_ld, int mode) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
   if (row >= static_cast<long long>(batch) * T) return;
@@ -38,9 +37,24 @@ embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, i
 }
 
 __global__ void __launch_bounds__(256)
-rowdot_kernel(const float* __restrict__ x, int x_ld, int k, const float* __restrict__ w,
-              const float* __restrict__ bias, int n_out, float alpha, int batch, int T, int seq_stride,
-              float* __restrict__ y) {
+embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
+             const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
+             const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
+             float* __restrict__ out, int out_ld, int mode) {
+  embed_rows(tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, mode);
+}
+
+struct EmbedBatch { ftb_embed_item item[FTB_MAX_GLUE_ITEMS]; };
+__global__ void __launch_bounds__(256)
+embed_batch_kernel(const __grid_constant__ EmbedBatch args, int batch, int T, int seq_stride) {
+  const ftb_embed_item& it = args.item[blockIdx.y];
+  embed_rows(it.tok, it.table, it.e1, it.tok2, it.table2, it.e2, it.extra, it.e3, batch, T, seq_stride, it.out, it.out_ld,
+             it.round_tf32);
+}
+
+__device__ __forceinline__ void rowdot_rows(const float* __restrict__ x, int x_ld, int k, const float* __restrict__ w,
+                                            const float* __restrict__ bias, int n_out, float alpha, int batch, int T,
+                                            int seq_stride, float* __restrict__ y) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
   if (row >= static_cast<long long>(batch) * T) return;
@@ -61,6 +75,20 @@ rowdot_kernel(const float* __restrict__ x, int x_ld, int k, const float* __restr
   if (lane == 0) {
     for (int o = 0; o < n_out; ++o) y[row * n_out + o] = __fdiv_rn(acc[o] + bias[o], alpha);   // `/ alpha`: a true division
   }
+}
+
+__global__ void __launch_bounds__(256)
+rowdot_kernel(const float* __restrict__ x, int x_ld, int k, const float* __restrict__ w,
+              const float* __restrict__ bias, int n_out, float alpha, int batch, int T, int seq_stride,
+              float* __restrict__ y) {
+  rowdot_rows(x, x_ld, k, w, bias, n_out, alpha, batch, T, seq_stride, y);
+}
+
+struct RowdotBatch { ftb_rowdot_item item[FTB_MAX_GLUE_ITEMS]; };
+__global__ void __launch_bounds__(256)
+rowdot_batch_kernel(const __grid_constant__ RowdotBatch args, int batch, int T, int seq_stride) {
+  const ftb_rowdot_item& it = args.item[blockIdx.y];
+  rowdot_rows(it.x, it.x_ld, it.k, it.w, it.bias, it.n_out, it.alpha, batch, T, seq_stride, it.y);
 }
 
 __global__ void argmax_kernel(const float* __restrict__ x, long long n, int c, int64_t* __restrict__ out) {
@@ -89,6 +117,41 @@ extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, i
   const long long rows = static_cast<long long>(batch) * T;
   embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, round_tf32);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int nitems, int batch, int T, int seq_stride,
+                               void* stream) {
+  if (!h || !items || nitems < 1 || nitems > FTB_MAX_GLUE_ITEMS || batch < 1 || T < 1 || seq_stride < T) return FTB_E_ARG;
+  EmbedBatch args{};
+  for (int i = 0; i < nitems; ++i) {
+    const ftb_embed_item& q = items[i];
+    if (!q.tok || !q.table || !q.out || q.e1 < 1) return FTB_E_ARG;
+    if (q.e2 > 0 && (!q.tok2 || !q.table2)) return FTB_E_ARG;
+    if (q.e3 > 0 && !q.extra) return FTB_E_ARG;
+    if (q.e1 + q.e2 + q.e3 > q.out_ld || q.round_tf32 < 0 || q.round_tf32 > 2) return FTB_E_ARG;
+    args.item[i] = q;
+  }
+  const long long rows = static_cast<long long>(batch) * T;
+  embed_batch_kernel<<<dim3(static_cast<unsigned>((rows + 7) / 8), nitems), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      args, batch, T, seq_stride);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int ftb_rowdot_batch(ftb_handle h, const ftb_rowdot_item* items, int nitems, int batch, int T, int seq_stride,
+                                void* stream) {
+  if (!h || !items || nitems < 1 || nitems > FTB_MAX_GLUE_ITEMS || batch < 1 || T < 1 || seq_stride < T) return FTB_E_ARG;
+  RowdotBatch args{};
+  for (int i = 0; i < nitems; ++i) {
+    const ftb_rowdot_item& q = items[i];
+    if (!q.x || !q.w || !q.bias || !q.y || q.n_out < 1 || q.n_out > 4 || q.k < 1 || q.alpha == 0.0f) return FTB_E_ARG;
+    args.item[i] = q;
+  }
+  const long long rows = static_cast<long long>(batch) * T;
+  rowdot_batch_kernel<<<dim3(static_cast<unsigned>((rows + 7) / 8), nitems), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      args, batch, T, seq_stride);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }

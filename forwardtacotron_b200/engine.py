@@ -54,6 +54,7 @@ class Program:
         self._gemm_plans: List[int] = []
         self._rnn_plans: List[int] = []
         self._pending: List[rt.GemmProblem] = []
+        self._glue: list = []                         # queued embeddings / predictor heads: one batched launch per kind
         self._keep: list = []                         # tensors the plans point into
         self.info: List[dict] = []                    # per step: kind, label, algorithmic flops / bytes
         self._label = ''
@@ -117,8 +118,40 @@ class Program:
         self._pending.append(p)
         self._keep += [a, w, wt, out, residual, out_t, out_full]
 
+    # ---- embeddings / predictor heads: queued, flushed as ONE batched launch per kind ---------
+    def embed(self, tok, table, out, tok2=None, table2=None, extra=None, round_tf32=True):
+        """nn.Embedding (+ second table / per-sentence vector concat) into a padded-flat buffer; consecutive calls share
+        one launch (ftb_embed_batch)."""
+        if self._glue and self._glue[0][0] != 'embed':
+            self._flush_glue()
+        self._glue.append(('embed', (tok, table, out, tok2, table2, extra, round_tf32)))
+        self._keep += [tok, table, out, tok2, table2, extra]
+
+    def rowdot(self, x, w, bias, n_out, alpha, y):
+        """Predictor head (lin + / alpha); `alpha` may be a callable evaluated at launch time.  Consecutive calls
+        share one launch (ftb_rowdot_batch)."""
+        if self._glue and self._glue[0][0] != 'rowdot':
+            self._flush_glue()
+        self._glue.append(('rowdot', (x, w, bias, n_out, alpha, y)))
+        self._keep += [x, w, bias, y]
+
+    def _flush_glue(self):
+        g = self.geo
+        while self._glue:
+            kind = self._glue[0][0]
+            items = [it for _, it in self._glue[:rt.MAX_GLUE_ITEMS]]
+            self._glue = self._glue[rt.MAX_GLUE_ITEMS:]
+            if kind == 'embed':
+                self.steps.append(lambda items=items: self.h.embed_batch(items, g.batch, g.seq_len, g.stride))
+            else:
+                self.steps.append(lambda items=items: self.h.rowdot_batch(
+                    [(x, w, b, n, (a() if callable(a) else a), y) for x, w, b, n, a, y in items],
+                    g.batch, g.seq_len, g.stride))
+            self.info.append({'kind': 'glue', 'label': f'{kind} x{len(items)}', 'flops': 0.0, 'bytes': 0.0})
+
     def flush(self):
         """Close the current group: everything queued since the last flush runs as one launch."""
+        self._flush_glue()
         if not self._pending:
             return
         g = self.geo
@@ -174,6 +207,7 @@ class Program:
         self._label = text
 
     def run_eager(self):
+        self.flush()
         for s in self.steps:
             s()
 
@@ -211,6 +245,7 @@ class Program:
         """Like run(), with a CUDA-event pair around every launch on the current stream.
         Returns [(info, milliseconds)] after a device synchronize (profiling aid for bench.py)."""
         evs = []
+        self.flush()
         for s in self.steps:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()

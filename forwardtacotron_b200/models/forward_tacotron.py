@@ -150,8 +150,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             for name in ('dur', 'pitch', 'energy'):
                 p = packs[name]
                 emb = prog.buf(f'{name}.emb', packs[name + '_emb'].shape[1])
-                prog.call(lambda emb=emb, name=name: h.embed(tok, packs[name + '_emb'], emb, emb.shape[1],
-                                                             batch, T, geo.stride))
+                prog.embed(tok, packs[name + '_emb'], emb)          # queued: all embeddings share one launch
                 levels, gru, hbuf = eng.predictor_levels(prog, name, p, emb)
                 branches.append(levels)
                 grus.append(gru)
@@ -160,10 +159,9 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             # the bank's operand copy of the embedding: fp16 (kind::f16 MMAs); the residual uses emb_full below
             E = packs['embedding'].shape[1]
             emb = prog.buf('emb', E, torch.float16 if (eng.F16_OPERANDS and E % 8 == 0) else torch.float32)
-            prog.call(lambda: h.embed(tok, packs['embedding'], emb, emb.shape[1], batch, T, geo.stride))
+            prog.embed(tok, packs['embedding'], emb)
             embf = prog.buf('emb_full', emb.shape[1])         # unrounded copy: the CBHG residual (:114)
-            prog.call(lambda: h.embed(tok, packs['embedding_full'], embf, embf.shape[1], batch, T, geo.stride,
-                                      round_tf32=False))
+            prog.embed(tok, packs['embedding_full'], embf, round_tf32=False)
             out = prog.buf('prenet.h', 2 * packs['prenet'].rnn.hidden)
             levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out, x_full=embf)
             branches.append(levels)
@@ -174,9 +172,8 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         prog.label('')
         for name, p, hbuf in heads:
             y = prog.dense(f'{name}.y', (batch, T))
-            prog.call(lambda p=p, hbuf=hbuf, y=y, name=name: h.rowdot(
-                hbuf, hbuf.shape[1], hbuf.shape[1], p.lin_w, p.lin_b, 1,
-                prog.alpha if name == 'dur' else 1.0, batch, T, geo.stride, y))
+            prog.rowdot(hbuf, p.lin_w, p.lin_b, 1, (lambda: prog.alpha) if name == 'dur' else 1.0, y)
+        prog.flush()                                                # the three heads: one launch
         prog.alpha = 1.0
         return prog
 

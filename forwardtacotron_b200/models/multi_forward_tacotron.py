@@ -203,10 +203,8 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             width = e1 + e2 + S
             ld = pk.ceil_to(width, 4)
             emb = prog.buf(f'{name}.emb', ld)
-            prog.call(lambda: h.embed(tok, packs[name + '_emb'], emb, ld, batch, T, geo.stride,
-                                      tok2=pcond if conditional else None,
-                                      table2=packs[name + '_cemb'] if conditional else None, extra=semb),
-                      label=f'{name}.embed')
+            prog.embed(tok, packs[name + '_emb'], emb, tok2=pcond if conditional else None,
+                       table2=packs[name + '_cemb'] if conditional else None, extra=semb)
             levels, gru, hbuf = eng.predictor_levels(prog, name, p, emb)
             heads.append((name, p, hbuf))
             return levels, gru
@@ -220,11 +218,9 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         # the bank's operand copy of the embedding: fp16 (kind::f16 MMAs); the residual uses emb_full below
         E = packs['embedding'].shape[1]
         emb = prog.buf('emb', E, torch.float16 if (eng.F16_OPERANDS and E % 8 == 0) else torch.float32)
-        prog.call(lambda: h.embed(tok, packs['embedding'], emb, emb.shape[1], batch, T, geo.stride),
-                  label='embed')
+        prog.embed(tok, packs['embedding'], emb)
         embf = prog.buf('emb_full', emb.shape[1])             # unrounded copy: the CBHG residual
-        prog.call(lambda: h.embed(tok, packs['embedding_full'], embf, embf.shape[1], batch, T, geo.stride,
-                                  round_tf32=False), label='embed_full')
+        prog.embed(tok, packs['embedding_full'], embf, round_tf32=False)
         out = prog.buf('prenet.h', 2 * packs['prenet'].rnn.hidden)
         levels, gru = eng.cbhg_levels(prog, 'prenet', packs['prenet'], emb, out, x_full=embf)
         branches.append(levels)

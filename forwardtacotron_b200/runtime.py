@@ -37,6 +37,21 @@ class RnnProblem(C.Structure):
                 ('out_ld', C.c_int32), ('out_col0', C.c_int32), ('lens', _fp), ('pad_value', C.c_float)]
 
 
+class EmbedItem(C.Structure):
+    _fields_ = [('tok', _fp), ('table', _fp), ('e1', C.c_int32),
+                ('tok2', _fp), ('table2', _fp), ('e2', C.c_int32),
+                ('extra', _fp), ('e3', C.c_int32),
+                ('out', _fp), ('out_ld', C.c_int32), ('round_tf32', C.c_int32)]
+
+
+class RowdotItem(C.Structure):
+    _fields_ = [('x', _fp), ('x_ld', C.c_int32), ('k', C.c_int32), ('w', _fp), ('bias', _fp),
+                ('n_out', C.c_int32), ('alpha', C.c_float), ('y', _fp)]
+
+
+MAX_GLUE_ITEMS = 8
+
+
 class LrGatherArgs(C.Structure):
     _fields_ = [('x', _fp), ('x_stride', C.c_int32), ('x_ld', C.c_int32), ('c1', C.c_int32),
                 ('extra', _fp), ('c2', C.c_int32),
@@ -53,7 +68,8 @@ class LrGatherArgs(C.Structure):
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
            'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy',
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
-           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_embed', 'ftb_rowdot', 'ftb_argmax_lastdim',
+           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
+           'ftb_argmax_lastdim',
            'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha']
 
 _lib = None
@@ -79,6 +95,8 @@ def load_library() -> C.CDLL:
     lib.ftb_rnn_plan_create.argtypes = [_fp, C.POINTER(RnnProblem), C.c_int, C.POINTER(C.c_int)]
     lib.ftb_rnn_plan_run.argtypes = [_fp, C.c_int, _fp]
     lib.ftb_rnn_plan_destroy.argtypes = [_fp, C.c_int]
+    lib.ftb_embed_batch.argtypes = [_fp, C.POINTER(EmbedItem), C.c_int, C.c_int, C.c_int, C.c_int, _fp]
+    lib.ftb_rowdot_batch.argtypes = [_fp, C.POINTER(RowdotItem), C.c_int, C.c_int, C.c_int, C.c_int, _fp]
     lib.ftb_rnn_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_lr_scan.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_lr_gather.argtypes = [_fp, C.POINTER(LrGatherArgs), _fp]
@@ -197,6 +215,25 @@ class Handle:
         mode = 2 if out.dtype == torch.float16 else int(round_tf32)       # fp16 operand copy / tf32-rounded / as stored
         self.check(self.lib.ftb_embed(self.h, ptr(tok), ptr(table), e1, ptr(tok2), ptr(table2), e2, ptr(extra), e3,
                                       batch, T, stride, ptr(out), out_ld, mode, self.stream()))
+
+    def embed_batch(self, items, batch, T, stride):
+        """items: [(tok, table, out, tok2, table2, extra, round_tf32)] -> ONE launch (include/ftb200.h: ftb_embed_batch)."""
+        arr = (EmbedItem * len(items))()
+        for a, (tok, table, out, tok2, table2, extra, round_tf32) in zip(arr, items):
+            a.tok, a.table, a.e1 = ptr(tok), ptr(table), table.shape[1]
+            a.tok2, a.table2, a.e2 = ptr(tok2), ptr(table2), (table2.shape[1] if table2 is not None else 0)
+            a.extra, a.e3 = ptr(extra), (extra.shape[1] if extra is not None else 0)
+            a.out, a.out_ld = ptr(out), out.shape[1]
+            a.round_tf32 = 2 if out.dtype == torch.float16 else int(round_tf32)
+        self.check(self.lib.ftb_embed_batch(self.h, arr, len(items), batch, T, stride, self.stream()))
+
+    def rowdot_batch(self, items, batch, T, stride):
+        """items: [(x, w, bias, n_out, alpha, y)] -> ONE launch (include/ftb200.h: ftb_rowdot_batch)."""
+        arr = (RowdotItem * len(items))()
+        for a, (x, w, bias, n_out, alpha, y) in zip(arr, items):
+            a.x, a.x_ld, a.k = ptr(x), x.shape[1], x.shape[1]
+            a.w, a.bias, a.n_out, a.alpha, a.y = ptr(w), ptr(bias), n_out, float(alpha), ptr(y)
+        self.check(self.lib.ftb_rowdot_batch(self.h, arr, len(items), batch, T, stride, self.stream()))
 
     def rowdot(self, x, x_ld, k, w, bias, n_out, alpha, batch, T, stride, y):
         self.check(self.lib.ftb_rowdot(self.h, ptr(x), x_ld, k, ptr(w), ptr(bias), n_out, float(alpha),

@@ -207,6 +207,28 @@ int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1,
 int ftb_rowdot(ftb_handle h, const float* x, int x_ld, int k, const float* w, const float* bias,
                int n_out, float alpha, int batch, int T, int seq_stride, float* y, void* stream);
 
+/* Batched forms: up to FTB_MAX_GLUE_ITEMS independent embeddings / predictor heads over the same [batch, T] token grid
+ * in ONE launch (grid.y = item).  The token-side program of generate() issues five embeddings (three predictors, the
+ * prenet operand copy and its unrounded twin: forward_tacotron.py:31,210) and three heads (:38-39) back to back; each is
+ * a few microseconds of work, so separate launches are pure launch latency. */
+#define FTB_MAX_GLUE_ITEMS 8
+typedef struct {
+  const int64_t* tok; const float* table; int32_t e1;
+  const int64_t* tok2; const float* table2; int32_t e2;
+  const float* extra; int32_t e3;
+  float* out; int32_t out_ld;
+  int32_t round_tf32;      /* as ftb_embed */
+} ftb_embed_item;
+int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int nitems, int batch, int T, int seq_stride, void* stream);
+
+typedef struct {
+  const float* x; int32_t x_ld, k;
+  const float* w; const float* bias;
+  int32_t n_out; float alpha;
+  float* y;
+} ftb_rowdot_item;
+int ftb_rowdot_batch(ftb_handle h, const ftb_rowdot_item* items, int nitems, int batch, int T, int seq_stride, void* stream);
+
 /* argmax over the last axis of [n, c] (c <= 8) -> int64 (multi_forward_tacotron.py:252, per (b,t)). */
 int ftb_argmax_lastdim(ftb_handle h, const float* x, int64_t n, int c, int64_t* out, void* stream);
 

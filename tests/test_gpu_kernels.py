@@ -372,3 +372,63 @@ def test_mha_matches_torch(D, heads, B, L, masked):
         s = s.masked_fill((tok == 0)[:, None, None, :], float('-inf'))
     want = (torch.softmax(s, dim=-1) @ v).transpose(1, 2).reshape(B, L, E)
     assert max_abs(prog.view('att').cpu().double(), want) < 2e-5
+
+
+def test_embed_and_heads_batched_match_single_and_torch():
+    """ftb_embed_batch / ftb_rowdot_batch == the single-item entry points == torch (forward_tacotron.py:31,38-39)."""
+    h = _handle()
+    gen = torch.Generator().manual_seed(5)
+    B, T = 3, 37
+    geo = eng.Geometry(B, T)
+    rows = B * geo.stride
+    tok = torch.randint(0, 40, (B, T), generator=gen).to(DEV)
+    tok2 = torch.randint(0, 3, (B, T), generator=gen).to(DEV)
+    tabs = [torch.randn(40, e, generator=gen).to(DEV) for e in (64, 256, 32)]
+    tab2 = torch.randn(3, 16, generator=gen).to(DEV)
+    extra = torch.randn(B, 20, generator=gen).to(DEV)
+    specs = [(tabs[0], None, None, None, True), (tabs[1], None, None, None, False),
+             (tabs[2], tok2, tab2, extra, True), (tabs[1], None, None, None, 'f16')]
+    singles, batched, items = [], [], []
+    for table, t2, tb2, ex, mode in specs:
+        width = table.shape[1] + (tb2.shape[1] if tb2 is not None else 0) + (ex.shape[1] if ex is not None else 0)
+        dt = torch.float16 if mode == 'f16' else torch.float32
+        a = torch.zeros(rows, width, device=DEV, dtype=dt)
+        b = torch.zeros_like(a)
+        h.embed(tok, table, a, width, B, T, geo.stride, tok2=t2, table2=tb2, extra=ex, round_tf32=bool(mode))
+        items.append((tok, table, b, t2, tb2, ex, bool(mode)))
+        singles.append(a)
+        batched.append(b)
+    h.embed_batch(items, B, T, geo.stride)
+    torch.cuda.synchronize()
+    for (table, t2, tb2, ex, mode), a, b in zip(specs, singles, batched):
+        assert torch.equal(a, b)
+        want = [table[tok]]
+        if tb2 is not None:
+            want.append(tb2[t2])
+        if ex is not None:
+            want.append(ex[:, None, :].expand(B, T, -1))
+        want = torch.cat(want, dim=-1)
+        got = b.view(B, geo.stride, -1)[:, :T]
+        if mode == 'f16':
+            assert torch.equal(got, want.half())
+        elif mode:
+            assert max_abs(got.cpu(), want.cpu()) <= 2 ** -11 * float(want.abs().max())
+        else:
+            assert torch.equal(got, want)
+    # heads
+    xs = [torch.randn(rows, k, generator=gen).to(DEV) for k in (128, 128, 64)]
+    ws = [torch.randn(n, k, generator=gen).to(DEV) for n, k in ((1, 128), (1, 128), (4, 64))]
+    bs = [torch.randn(w.shape[0], generator=gen).to(DEV) for w in ws]
+    alphas = [1.3, 1.0, 1.0]
+    ya = [torch.zeros(B, T, w.shape[0], device=DEV) for w in ws]
+    yb = [torch.zeros_like(y) for y in ya]
+    for x, w, b, al, y in zip(xs, ws, bs, alphas, ya):
+        h.rowdot(x, x.shape[1], x.shape[1], w, b, w.shape[0], al, B, T, geo.stride, y)
+    h.rowdot_batch([(x, w, b, w.shape[0], al, y) for x, w, b, al, y in zip(xs, ws, bs, alphas, yb)], B, T, geo.stride)
+    torch.cuda.synchronize()
+    for x, w, b, al, y1, y2 in zip(xs, ws, bs, alphas, ya, yb):
+        assert torch.equal(y1, y2)
+        want = (x.view(B, geo.stride, -1)[:, :T].double() @ w.double().t() + b.double()) / al
+        assert max_abs(y2.double().cpu(), want.cpu()) < 1e-4
+    with pytest.raises(RuntimeError):
+        h.embed_batch(items * 3, B, T, geo.stride)                 # > FTB_MAX_GLUE_ITEMS
