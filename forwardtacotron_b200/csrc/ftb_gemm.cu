@@ -123,13 +123,16 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
   const int lane = c.lane, sub = lane >> 3, part = lane & 7;
   // phase-B base pointers: row (r_warp + sub), column n0 + 4*part; +32 columns per chunk, +4 rows per i8
   const long long orow = (c.r_warp + sub) * c.out_ld + c.n0 + 4 * part;
+  // fp16 output next to a residual / unrounded twin / transposed output: phase-B layout, 8-byte stores of 4 halves
+  constexpr bool O16_FAST = OUT16 && !RES && !FULL && !OUTT;
   float* optr = c.out ? c.out + orow : nullptr;
+  __half* hptr = (OUT16 && !O16_FAST) ? c.out16 + orow : nullptr;
   float* fptr = FULL ? c.out_full + orow : nullptr;
   const float* rptr = RES ? c.residual + (c.r_warp + sub) * c.res_ld + c.n0 + 4 * part : nullptr;
   const long long ostep = 4ll * c.out_ld, rstep = 4ll * c.res_ld;
   // fp16 output: lane = (row r8 of 8, 8 consecutive columns c8): 16-byte stores, 64-byte row segments
   const int r8 = lane >> 2, c8 = lane & 3;
-  __half* o16 = OUT16 ? c.out16 + (c.r_warp + r8) * c.out_ld + c.n0 + 8 * c8 : nullptr;
+  __half* o16 = O16_FAST ? c.out16 + (c.r_warp + r8) * c.out_ld + c.n0 + 8 * c8 : nullptr;
   float4 xr_cur[RES ? 8 : 1], xr_nxt[RES ? 8 : 1];
   auto load_res = [&](float4 (&dst)[RES ? 8 : 1], int c0) {
     if (RES) {
@@ -196,7 +199,7 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
           if (c0 + j < c.bn && nb + j < c.N) ot[static_cast<long long>(j) * c.seq_len] = v[j];
       }
     }
-    if (OUT16) {
+    if (O16_FAST) {
       const bool cols_ok = c0 + 8 * c8 < c.bn && nb + 8 * c8 < c.N;          // N, nb and bn are multiples of 8
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
@@ -225,7 +228,7 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
         }
         __syncwarp();
       }
-    } else if (optr) {
+    } else if (optr || hptr) {
       // a half chunk (bn = 16 mod 32) must not spill into the columns of the next n-tile
       const bool cols_ok = c0 + 4 * part < c.bn && nb + 4 * part < c.N;      // N, nb and bn are multiples of 4
 #pragma unroll
@@ -245,8 +248,15 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
               float4 y = *reinterpret_cast<const float4*>(&c.stg[row & 15][4 * part]);
               if (RES) { y.x += xr_cur[i8].x; y.y += xr_cur[i8].y; y.z += xr_cur[i8].z; y.w += xr_cur[i8].w; }
               if (FULL) *reinterpret_cast<float4*>(fptr + i8 * ostep + c0) = y;
-              if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-              *reinterpret_cast<float4*>(optr + i8 * ostep + c0) = y;
+              if (OUT16) {
+                const __half2 lo = __floats2half2_rn(y.x, y.y), hi = __floats2half2_rn(y.z, y.w);
+                uint2 pk;
+                pk.x = *reinterpret_cast<const uint32_t*>(&lo); pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0) = pk;
+              } else {
+                if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+                *reinterpret_cast<float4*>(optr + i8 * ostep + c0) = y;
+              }
             }
           }
         }
@@ -276,9 +286,18 @@ __device__ __forceinline__ void epi_disp_full(const EpiCtx& c, bool full, bool o
   else epi_disp_outt<POOL, RES, false>(c, outt, rnd);
 }
 __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool res, bool full, bool outt, bool rnd) {
-  if (c.out16) {                                                  // fp16 output: plain / pooled, nothing else
-    if (pool) epi_affine_tile<true, false, false, false, false, true>(c);
-    else epi_affine_tile<false, false, false, false, false, true>(c);
+  if (c.out16) {                                                  // fp16 operand copy as `out`
+    if (pool) epi_affine_tile<true, false, false, false, false, true>(c);        // CBHG bank: never residual / twin
+    else if (outt) {
+      if (full) epi_affine_tile<false, false, true, true, false, true>(c);
+      else epi_affine_tile<false, false, false, true, false, true>(c);
+    } else if (res) {
+      if (full) epi_affine_tile<false, true, true, false, false, true>(c);
+      else epi_affine_tile<false, true, false, false, false, true>(c);
+    } else {
+      if (full) epi_affine_tile<false, false, true, false, false, true>(c);
+      else epi_affine_tile<false, false, false, false, false, true>(c);
+    }
     return;
   }
   if (pool) epi_disp_full<true, false>(c, full, outt, rnd);     // pooled layers (CBHG bank) never carry a residual
@@ -480,7 +499,10 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         const int u0 = tc.n0 >> 1;
         const float* rrow = P_residual + r * P_res_ld + u0;                  // this lane's residual row
         const int brow = lane >> 2, c4 = lane & 3;                           // phase-B coordinates: 8 rows x 4 float4
-        float* optr = P_out + (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4;
+        const bool h16 = (P_flags & FTB_F_OUT_F16) != 0;                     // `out` is the fp16 operand copy
+        const long long ooff = (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4;
+        float* optr = P_out + ooff;
+        __half* hptr = reinterpret_cast<__half*>(P_out) + ooff;
         float* fptr = P_out_full ? P_out_full + (r_warp + brow) * P_out_ld + P_out_col0 + u0 + 4 * c4 : nullptr;
         const long long ostep = 8ll * P_out_ld;
         float* hstg = &stg[0][0];       // [32 rows][16 floats], float4 slots XOR-swizzled by (row >> 1) & 3: conflict-free
@@ -517,8 +539,15 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             if ((smask >> row) & 1u) {
               float4 y = *reinterpret_cast<const float4*>(hstg + row * 16 + 4 * (c4 ^ ((row >> 1) & 3)));
               if (fptr) *reinterpret_cast<float4*>(fptr + i4 * ostep + j0) = y;
-              if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
-              *reinterpret_cast<float4*>(optr + i4 * ostep + j0) = y;
+              if (h16) {
+                const __half2 lo = __floats2half2_rn(y.x, y.y), hi = __floats2half2_rn(y.z, y.w);
+                uint2 pk;
+                pk.x = *reinterpret_cast<const uint32_t*>(&lo); pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                *reinterpret_cast<uint2*>(hptr + i4 * ostep + j0) = pk;
+              } else {
+                if (rnd) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+                *reinterpret_cast<float4*>(optr + i4 * ostep + j0) = y;
+              }
             }
           }
           __syncwarp();
@@ -666,7 +695,7 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     if (!aligned16(q.a) || !aligned16(q.w)) return FTB_E_ALIGN;
     if (q.out && (!aligned16(q.out) || (q.out_ld % omul) != 0 || (q.out_col0 % omul) != 0)) return FTB_E_ALIGN;
     if (q.out && (q.n % omul) != 0) return FTB_E_SHAPE;       // row segments are stored as 16-byte vectors
-    if (o16 && (!q.out || q.residual || q.out_t || q.out_full || q.epilogue == FTB_EPI_HIGHWAY)) return FTB_E_ARG;
+    if (o16 && (!q.out || (q.epilogue == FTB_EPI_MAXPOOL && (q.residual || q.out_t || q.out_full)))) return FTB_E_ARG;
     if (q.residual && ((q.res_ld % 4) != 0 || !aligned16(q.residual))) return FTB_E_ALIGN;
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
     if (q.rows != static_cast<long long>(q.batch) * q.seq_stride) return FTB_E_ARG;

@@ -226,7 +226,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   float c_state = 0.0f, h_state = 0.0f, bias[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) bias[g] = pv ? bhh[g * H + u0 + pu] : 0.0f;
-  float* out_pair = p.out + p.out_col0 + dir * H + static_cast<size_t>(b0 + pb) * p.seq_stride * p.out_ld + u0 + pu;
+  // element offset into `out`; the layer output is stored as fp32 or (out_f16) as the fp16 value itself
+  const size_t out_pair = p.out_col0 + dir * H + static_cast<size_t>(b0 + pb) * p.seq_stride * p.out_ld + u0 + pu;
   __half* hx_pair = hx_dir + static_cast<size_t>(b0 + pb) * H + u0 + pu;       // + t * batch * H
 
   // ---- x-projection ring: 16-byte chunk `tid` of a step = (batch xb, gate xg_, 4 units) --------
@@ -379,11 +380,17 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   }
   // gate math (fp32), state update and publication of h_t for this thread's pair (threads of group g only).
   // The partial-sum tiles start zeroed, so step 0 (h_{-1} = 0, no MMA) needs no special case.
-  const long long o_step = dir ? -static_cast<long long>(p.out_ld) : static_cast<long long>(p.out_ld);
+  const bool o16 = p.out_f16 != 0;
+  const int osz = o16 ? 2 : 4;
+  const long long o_step = (dir ? -static_cast<long long>(p.out_ld) : static_cast<long long>(p.out_ld)) * osz;
   // packed-sequence semantics (optional): this pair's sentence is live for t < len_b only
   const int len_b = (p.lens && pv) ? min(p.lens[b0 + pb], L) : L;
   const float pad_value = p.pad_value;
-  float* out_p = out_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.out_ld;
+  char* out_p = reinterpret_cast<char*>(p.out) + (out_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.out_ld) * osz;
+  auto store_out = [&](bool dead, __half h16) {
+    if (o16) *reinterpret_cast<__half*>(out_p) = dead ? __float2half_rn(pad_value) : h16;
+    else *reinterpret_cast<float*>(out_p) = dead ? pad_value : __half2float(h16);
+  };
   __half* hx_p = hx_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.batch * H;
   const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
   const float* xs0 = x_s + pb * XSTR + pu;
@@ -446,14 +453,14 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         for (int d = 0; d < ND; ++d)
           if (rvalid & (1u << d)) st_async_v4(rdata[d] + poff, v, rbar[d] + boff);
       }
-      if (pv) *out_p = dead ? pad_value : __half2float(h16);
+      if (pv) store_out(dead, h16);
       FTB_TICK(6)
     } else {
       // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
       const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
       if (pv) {
         if ((lane & 1) == 0) st_relaxed_u32(hx_p, mine | (other << 16));
-        *out_p = dead ? pad_value : __half2float(h16);
+        store_out(dead, h16);
       }
       hx_p += h_step;
     }
@@ -651,7 +658,7 @@ static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& wh
       const int take = want < room ? want : room;
       RnnProblemDev d{};
       d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = nullptr;
-      d.lens = q.lens; d.pad_value = q.pad_value;
+      d.lens = q.lens; d.pad_value = q.pad_value; d.out_f16 = q.out_f16;
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
       d.gates = q.cell == FTB_CELL_LSTM ? 4 : 3;

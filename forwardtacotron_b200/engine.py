@@ -103,8 +103,10 @@ class Program:
         p.n, p.bn, p.epilogue = w.n, w.bn, epilogue
         p.flags = ((rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out and not o16 else 0) |
                    (rt.F_A_F16 if a16 else 0) | (rt.F_OUT_F16 if o16 else 0))
-        assert not o16 or (residual is None and out_t is None and out_full is None), 'fp16 output: plain epilogue only'
+        assert not o16 or epilogue != rt.EPI_MAXPOOL or (residual is None and out_t is None and out_full is None)
         p.bias0, p.scale, p.shift = rt.ptr(w.bias0), rt.ptr(w.scale), rt.ptr(w.shift)
+        assert residual is None or residual.dtype == torch.float32, 'the residual term reads the fp32 twin'
+        assert out_full is None or out_full.dtype == torch.float32
         p.residual = rt.ptr(residual)
         p.res_ld = residual.shape[1] if residual is not None else 0
         p.out = rt.ptr(out)
@@ -185,6 +187,7 @@ class Program:
             p.xproj, p.w_hh, p.b_hh = xproj.data_ptr(), r.w_hh.data_ptr(), r.b_hh.data_ptr()
             p.out, p.out_ld, p.out_col0 = out.data_ptr(), out.shape[1], col0
             p.lens, p.pad_value = (lens.data_ptr() if lens is not None else None), float(pad_value)
+            p.out_f16 = int(out.dtype == torch.float16)       # h_t is fp16-exact: an fp16 layer output loses nothing
             probs.append(p)
             self._keep += [r, xproj, out] + ([lens] if lens is not None else [])
         plan = self.h.rnn_plan(probs)
@@ -296,8 +299,12 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     f16 = _F16_OPERANDS and (K * ch) % 8 == 0 and c.proj1.n % 8 == 0
     bank = prog.buf(f'{tag}.bank', K * ch, torch.float16 if f16 else torch.float32)
     p1 = prog.buf(f'{tag}.proj1', c.proj1.n, torch.float16 if f16 else torch.float32)
-    p2 = prog.buf(f'{tag}.proj2', c.proj2.n)
-    hw = [prog.buf(f'{tag}.hw0', ch), prog.buf(f'{tag}.hw1', ch)]
+    # proj2 -> pre_highway -> highways -> gru_ih: small-K layers paced by operand delivery from L2
+    # (profiles/r1r_highway_ncu.txt): fp16 operand copies halve it; the residual terms keep their fp32 twins
+    f16s = _F16_OPERANDS and c.proj2.n % 8 == 0 and ch % 8 == 0
+    sdt = torch.float16 if f16s else torch.float32
+    p2 = prog.buf(f'{tag}.proj2', c.proj2.n, sdt)
+    hw = [prog.buf(f'{tag}.hw0', ch, sdt), prog.buf(f'{tag}.hw1', ch, sdt)]
     # unrounded twins of the highway activations: the residual term (1-g)*x uses full fp32 values, only the
     # GEMM operand copy is tf32-rounded
     hwf = [prog.buf(f'{tag}.hw0_full', ch), prog.buf(f'{tag}.hw1_full', ch)]

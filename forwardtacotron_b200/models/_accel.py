@@ -86,11 +86,15 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     # the regulated sequence feeds only the W_ih GEMM: fp16 operand copy (K5 writes it directly)
     x = prog.buf('lr', in_channels, torch.float16 if (eng.F16_OPERANDS and in_channels % 8 == 0) else torch.float32)
     xp = prog.buf('lstm.xproj', lstm.ih.n)
-    hl = prog.buf('lstm.h', 2 * lstm.hidden)
-    mel_cl = prog.buf('mel_cl', n_mels)
+    # the recurrences hand h_t on in fp16, so their layer outputs are fp16-exact: `lin` and `post_proj` (their only
+    # readers) take them as fp16 operands
+    odt = torch.float16 if eng.F16_OPERANDS else torch.float32
+    hl = prog.buf('lstm.h', 2 * lstm.hidden, odt)
+    # channels-last mel: only the postnet bank's operand (the residual uses mel_cl_full): fp16 copy
+    mel_cl = prog.buf('mel_cl', n_mels, torch.float16 if (eng.F16_OPERANDS and n_mels % 8 == 0) else torch.float32)
     mel = prog.dense('mel', (batch, n_mels, M))
     mel_post = prog.dense('mel_post', (batch, n_mels, M))
-    post = prog.buf('postnet.h', 2 * packs['postnet'].rnn.hidden)
+    post = prog.buf('postnet.h', 2 * packs['postnet'].rnn.hidden, odt)
 
     prog.label('lstm_ih')
     prog.gemm(x, lstm.ih, xp, round_out=False)                    # W_ih half of self.lstm (:224)
@@ -118,7 +122,7 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
             m = ((t_idx[None, :] >= mel_len[:, None]) & (t_idx[None, :] < M))        # [B, stride]
             cl = mel_cl.view(batch, g.stride, n_mels)
             clf = mel_full.view(batch, g.stride, n_mels)
-            torch.where(m[:, :, None], v_r, cl, out=cl)
+            torch.where(m[:, :, None], v_r.to(cl.dtype), cl, out=cl)
             torch.where(m[:, :, None], v, clf, out=clf)
             torch.where(m[:, None, :M], v[None, :, None], mel, out=mel)
         prog.call(fix_pad_rows, label='lin.pad_rows')

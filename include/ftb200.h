@@ -74,8 +74,9 @@ enum { FTB_EPI_AFFINE = 0, FTB_EPI_MAXPOOL = 1, FTB_EPI_HIGHWAY = 2 };
 /* FTB_F_A_F16  : `a` and `w` hold IEEE fp16 (same 11-bit significand as tf32; lda / cin counted in fp16 elements,
  *                multiples of 8); the MMAs are kind::f16 with fp32 accumulation -- twice the tensor rate and half
  *                the operand traffic of tf32.  Used where the producer of `a` is another K1/K2 problem.
- * FTB_F_OUT_F16: `out` is fp16 [rows, out_ld] (out_ld, out_col0, n multiples of 8), rounded to nearest; only with
- *                AFFINE / MAXPOOL, without residual / out_t / out_full; ROUND_TF32 is ignored.                  */
+ * FTB_F_OUT_F16: `out` is fp16 [rows, out_ld] (out_ld, out_col0, n multiples of 8), rounded to nearest: the operand
+ *                copy for a following FTB_F_A_F16 problem.  Any epilogue; residual / out_t / out_full (always fp32)
+ *                may accompany it except with MAXPOOL; ROUND_TF32 is ignored.                                   */
 enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2, FTB_F_A_F16 = 4, FTB_F_OUT_F16 = 8 };
 
 typedef struct {
@@ -144,6 +145,8 @@ typedef struct {
                             direction starts at lens[b]-1 from a zero state) and out[b, t >= lens[b]] = pad_value;
                             null = every sentence runs over all seq_len steps (the generate() path)             */
   float pad_value;
+  int32_t out_f16;       /* != 0: `out` is fp16 [batch*seq_stride, out_ld] (h_t is fp16-exact, so this loses nothing):
+                            the operand copy for a following FTB_F_A_F16 GEMM (lin / post_proj)                 */
 } ftb_rnn_problem;
 
 #define FTB_MAX_RNN_PROBLEMS 8

@@ -182,6 +182,63 @@ def test_highway_and_transposed_linear():
     prog.h.impl = 0
 
 
+def test_fp16_operand_copy_next_to_twin_residual_transposed():
+    """FTB_F_OUT_F16 with out_full / residual / highway / out_t: the small-K chain proj2 -> pre_highway -> highways
+    -> gru_ih and `lin` hand fp16 operand copies on while their fp32 twins feed the residual terms."""
+    B, L, ch = 2, 150, 128
+    gen = torch.Generator().manual_seed(19)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    v = torch.randn(B, L, ch, generator=gen)
+    a16 = prog.buf('a16', ch, torch.float16)
+    a32 = prog.buf('a32', ch)
+    a16.view(B, g.stride, ch)[:, :L] = v.to(DEV).half()
+    a32.view(B, g.stride, ch)[:, :L] = v.to(DEV)
+    a_ref = v.half().double()
+    w1, w2 = torch.randn(ch, ch, generator=gen) / 11, torch.randn(ch, ch, generator=gen) / 11
+    b1, b2 = torch.randn(ch, generator=gen) * 0.1, torch.randn(ch, generator=gen) * 0.1
+    hw = pk.pack_highway(w1.to(DEV), b1.to(DEV), w2.to(DEV), b2.to(DEV))
+    hw_o, hw_f = prog.buf('hw', ch, torch.float16), prog.buf('hw_full', ch)
+    prog.gemm(a16, hw, hw_o, epilogue=rt.EPI_HIGHWAY, residual=a32, out_full=hw_f)
+    wl, bl = torch.randn(80, ch, generator=gen) / 11, torch.randn(80, generator=gen)
+    lin = pk.pack_linear(wl.to(DEV), bl.to(DEV))
+    mel_cl, mel_f = prog.buf('mel_cl', 80, torch.float16), prog.buf('mel_cl_full', 80)
+    mel = prog.dense('mel', (B, 80, L))
+    prog.gemm(a16, lin, mel_cl, out_t=mel, out_full=mel_f)
+    wp = torch.randn(ch, ch, generator=gen) / 11
+    proj = pk.pack_linear(wp.to(DEV), None)
+    p_res = prog.buf('p_res', ch, torch.float16)                 # residual only
+    p_twin, p_twin_f = prog.buf('p_twin', ch, torch.float16), prog.buf('p_twin_full', ch)
+    prog.gemm(a16, proj, p_res, residual=a32)
+    prog.gemm(a16, proj, p_twin, out_full=p_twin_f)
+    prog.flush()
+    r16 = lambda w: w.half().double()        # noqa: E731  (the packed fp16 weight copy of a tf32-rounded weight)
+    x1 = a_ref @ r16(pk.round_tf32(w1)).T + b1.double()
+    x2 = a_ref @ r16(pk.round_tf32(w2)).T + b2.double()
+    gate = torch.sigmoid(x2)
+    ref_hw = gate * x1.clamp_min(0) + (1 - gate) * v.double()
+    ref_mel = a_ref @ r16(pk.round_tf32(wl)).T + bl.double()
+    ref_p = a_ref @ r16(pk.round_tf32(wp)).T
+    for impl in (1, 0):
+        for b in (hw_o, hw_f, mel_cl, mel_f, mel, p_res, p_twin, p_twin_f):
+            b.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        view = lambda n: prog.view(n).cpu().double()             # noqa: E731
+        assert max_abs(view('hw_full'), ref_hw) < 2e-4, impl
+        assert torch.equal(prog.view('hw'), prog.view('hw_full').half()), impl
+        assert max_abs(view('mel_cl_full'), ref_mel) < 2e-4, impl
+        assert max_abs(mel.cpu().double(), ref_mel.transpose(1, 2)) < 2e-4, impl
+        assert torch.equal(prog.view('mel_cl'), prog.view('mel_cl_full').half()), impl
+        assert max_abs(view('p_twin_full'), ref_p) < 2e-4, impl
+        assert torch.equal(prog.view('p_twin'), prog.view('p_twin_full').half()), impl
+        assert max_abs(view('p_res'), ref_p + v.double()) < 2e-4 + 2.0 ** -11 * float((ref_p + v.double()).abs().max()), impl
+        for n in ('hw', 'mel_cl', 'p_res', 'p_twin'):             # pad rows untouched
+            assert float(prog.bufs[n].view(B, g.stride, -1)[:, L:].float().abs().max()) == 0.0
+    prog.h.impl = 0
+
+
 @pytest.mark.parametrize('cell,H,B,L', [('gru', 64, 3, 37), ('gru', 128, 5, 20), ('gru', 256, 33, 25),
                                         ('lstm', 512, 2, 30), ('lstm', 512, 40, 12)])
 def test_recurrence(cell, H, B, L):
@@ -236,14 +293,18 @@ def test_recurrence_handoff_protocols_agree(cell, H, B, L, monkeypatch):
         a, _ = _fill(prog, 'x', In, g2)
         xp = prog.buf('xp', packed.ih.n)
         out = prog.buf('h', 2 * H)
+        out16 = prog.buf('h16', 2 * H, torch.float16)        # out_f16: the same values stored as fp16 (h_t is fp16-exact)
         prog.gemm(a, packed.ih, xp, round_out=False)
         prog.rnn([(packed, xp, out, 0)])
         assert prog.info[-1]['handoff'] == mode
+        prog.rnn([(packed, xp, out16, 0)])
         for _ in range(2):                                   # second run: barriers / sentinels re-armed
             prog.run()
         torch.cuda.synchronize()
         got[mode] = prog.view('h').cpu().clone()
         assert bool(torch.isfinite(got[mode]).all())
+        assert torch.equal(prog.view('h16').float().cpu(), got[mode])
+        assert float(out16.view(B, prog.geo.stride, -1)[:, L:].float().abs().max()) == 0.0
     assert torch.equal(got['cluster'], got['l2'])
 
 
@@ -278,7 +339,13 @@ def test_recurrence_packed_sequence_semantics(cell, H, B, L):
     torch.cuda.synchronize()
     got = prog.view('h').cpu()
     assert got.shape == ref.shape
+    out16 = prog.buf('h16', 2 * H, torch.float16)
+    prog.rnn([(packed, xp, out16, 0)], lens=lens_d, pad_value=pad)
+    prog.run()
+    torch.cuda.synchronize()
     mask = torch.arange(L)[None, :] >= lens[:, None]
+    got16 = prog.view('h16').float().cpu()
+    assert torch.equal(got16[~mask], got[~mask]) and bool((got16[mask] == torch.tensor(pad).half().float()).all())
     assert bool((got[mask] == torch.tensor(pad)).all())                      # the tail is exactly the pad value
     assert max_abs(got[~mask], ref[~mask]) < 3e-3                            # tf32 x-projection + fp16 recurrent operands
 
