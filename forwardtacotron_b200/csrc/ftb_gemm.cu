@@ -113,6 +113,7 @@ struct EpiCtx {
   bool store;                    // this lane's row is stored
   long long r, r_warp;           // this lane's row / the warp's first row
   float relu_lo;                 // 0 (ReLU) or -inf
+  bool plain;                    // bias only: no ReLU, no scale / shift (linear layers, the W_ih projections)
   const float* residual;
   float* out; float* out_full; float* out_t;    // out / out_full already offset by out_col0
   __half* out16;                                // FTB_F_OUT_F16: the fp16 output (offset by out_col0), `out` is null
@@ -159,15 +160,23 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
     }
     tmem_ld_wait();
     const int nb = c.n0 + c0;
+    if (c.plain) {                                        // warp-uniform: a third of the parameter loads and math
 #pragma unroll
-    for (int j = 0; j < CHUNK; j += 4) {
-      const float4 b0 = *reinterpret_cast<const float4*>(&c.prm[0][(c0 + j) & 255]);
-      const float4 sc = *reinterpret_cast<const float4*>(&c.prm[1][(c0 + j) & 255]);
-      const float4 sh = *reinterpret_cast<const float4*>(&c.prm[2][(c0 + j) & 255]);
-      v[j] = fmaxf(v[j] + b0.x, c.relu_lo) * sc.x + sh.x;
-      v[j + 1] = fmaxf(v[j + 1] + b0.y, c.relu_lo) * sc.y + sh.y;
-      v[j + 2] = fmaxf(v[j + 2] + b0.z, c.relu_lo) * sc.z + sh.z;
-      v[j + 3] = fmaxf(v[j + 3] + b0.w, c.relu_lo) * sc.w + sh.w;
+      for (int j = 0; j < CHUNK; j += 4) {
+        const float4 b0 = *reinterpret_cast<const float4*>(&c.prm[0][(c0 + j) & 255]);
+        v[j] += b0.x; v[j + 1] += b0.y; v[j + 2] += b0.z; v[j + 3] += b0.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < CHUNK; j += 4) {
+        const float4 b0 = *reinterpret_cast<const float4*>(&c.prm[0][(c0 + j) & 255]);
+        const float4 sc = *reinterpret_cast<const float4*>(&c.prm[1][(c0 + j) & 255]);
+        const float4 sh = *reinterpret_cast<const float4*>(&c.prm[2][(c0 + j) & 255]);
+        v[j] = fmaxf(v[j] + b0.x, c.relu_lo) * sc.x + sh.x;
+        v[j + 1] = fmaxf(v[j + 1] + b0.y, c.relu_lo) * sc.y + sh.y;
+        v[j + 2] = fmaxf(v[j + 2] + b0.z, c.relu_lo) * sc.z + sh.z;
+        v[j + 3] = fmaxf(v[j + 3] + b0.w, c.relu_lo) * sc.w + sh.w;
+      }
     }
     if (POOL) {
       float (*ex)[CHUNK] = c.exch[chunk_i & 1];
@@ -210,12 +219,18 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
         }
         __syncwarp();
         if (cols_ok) {
+          // all staging reads first, then the predicated stores: one shared-memory latency per half, not one per row
+          float4 ya[2], yb[2];
+#pragma unroll
+          for (int i2 = 0; i2 < 2; ++i2) {
+            ya[i2] = *reinterpret_cast<const float4*>(&c.stg[i2 * 8 + r8][8 * c8]);
+            yb[i2] = *reinterpret_cast<const float4*>(&c.stg[i2 * 8 + r8][8 * c8 + 4]);
+          }
 #pragma unroll
           for (int i2 = 0; i2 < 2; ++i2) {
             const int row = h * 16 + i2 * 8 + r8;
             if ((c.smask >> row) & 1u) {
-              const float4 y0 = *reinterpret_cast<const float4*>(&c.stg[row & 15][8 * c8]);
-              const float4 y1 = *reinterpret_cast<const float4*>(&c.stg[row & 15][8 * c8 + 4]);
+              const float4 y0 = ya[i2], y1 = yb[i2];
               uint4 pk;
               __half2 t;
               t = __floats2half2_rn(y0.x, y0.y); pk.x = *reinterpret_cast<const uint32_t*>(&t);
@@ -240,12 +255,15 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
         }
         __syncwarp();
         if (cols_ok) {
+          float4 ys[4];
+#pragma unroll
+          for (int i4 = 0; i4 < 4; ++i4) ys[i4] = *reinterpret_cast<const float4*>(&c.stg[i4 * 4 + sub][4 * part]);
 #pragma unroll
           for (int i4 = 0; i4 < 4; ++i4) {
             const int i8 = h * 4 + i4;
             const int row = i8 * 4 + sub;
             if ((c.smask >> row) & 1u) {
-              float4 y = *reinterpret_cast<const float4*>(&c.stg[row & 15][4 * part]);
+              float4 y = ys[i4];
               if (RES) { y.x += xr_cur[i8].x; y.y += xr_cur[i8].y; y.z += xr_cur[i8].z; y.w += xr_cur[i8].w; }
               if (FULL) *reinterpret_cast<float4*>(fptr + i8 * ostep + c0) = y;
               if (OUT16) {
@@ -325,6 +343,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
 #define GP_ACC(i)
 #endif
 
+  pdl_launch_dependents();
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&tail->full[s], 1);
@@ -344,6 +363,8 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
+  // everything above (barriers, TMEM) overlapped the tail of the previous kernel; its outputs are read from here on
+  pdl_wait();
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -533,11 +554,17 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             *reinterpret_cast<float4*>(hstg + lane * 16 + 4 * (q ^ ((lane >> 1) & 3))) = y;
           }
           __syncwarp();
+          float4 ys[4];
+#pragma unroll
+          for (int i4 = 0; i4 < 4; ++i4) {
+            const int row = i4 * 8 + brow;
+            ys[i4] = *reinterpret_cast<const float4*>(hstg + row * 16 + 4 * (c4 ^ ((row >> 1) & 3)));
+          }
 #pragma unroll
           for (int i4 = 0; i4 < 4; ++i4) {
             const int row = i4 * 8 + brow;
             if ((smask >> row) & 1u) {
-              float4 y = *reinterpret_cast<const float4*>(hstg + row * 16 + 4 * (c4 ^ ((row >> 1) & 3)));
+              float4 y = ys[i4];
               if (fptr) *reinterpret_cast<float4*>(fptr + i4 * ostep + j0) = y;
               if (h16) {
                 const __half2 lo = __floats2half2_rn(y.x, y.y), hi = __floats2half2_rn(y.z, y.w);
@@ -560,6 +587,7 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         c.bn = P_bn; c.n0 = tc.n0; c.N = N; c.g = g; c.lane = lane; c.t = t; c.b = b; c.seq_len = P_seq_len;
         c.res_ld = P_res_ld; c.out_ld = P_out_ld; c.smask = smask; c.store = store; c.r = r; c.r_warp = r_warp;
         c.relu_lo = relu ? 0.0f : -INFINITY;
+        c.plain = !relu && P_scale == nullptr && P_shift == nullptr;
         c.residual = P_residual;
         const bool out16 = (P_flags & FTB_F_OUT_F16) != 0;
         c.out = (P_out && !out16) ? P_out + P_out_col0 : nullptr;
@@ -756,8 +784,18 @@ int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t s
     attr_set = true;
   }
   const int grid = plan.total_tiles < num_sms ? plan.total_tiles : num_sms;
-  conv_gemm_tc_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(plan.dev, plan.nprob, plan.total_tiles);
-  return static_cast<int>(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel, static_cast<const GemmProblemDev*>(plan.dev),
+                                             plan.nprob, plan.total_tiles));
 }
 
 }  // namespace ftb

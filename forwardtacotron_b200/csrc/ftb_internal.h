@@ -4,12 +4,19 @@
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <cstdint>
+#include <cstdlib>
 #include <map>
 #include <vector>
 
 #include "../../include/ftb200.h"
 
 namespace ftb {
+
+// FTB_PDL=0 turns programmatic dependent launches off (every kernel then waits for its predecessor to drain).
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("FTB_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
 
 // ------------------------------------------------------------------ conv-GEMM (ftb_gemm.cu)
 // Device-resident problem record.  CUtensorMap needs 64-byte alignment; the struct is

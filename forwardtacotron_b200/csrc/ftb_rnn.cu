@@ -246,6 +246,8 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     x_pf += x_step;
     ++pf_step;
   };
+  // W_hh and the biases above are weights; the x-projection is the previous kernel's output
+  pdl_wait();
 #pragma unroll
   for (int s = 0; s < RNN_XS - 1; ++s) prefetch_x();
 
@@ -583,6 +585,7 @@ rnn_persistent_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
 __global__ void __launch_bounds__(RNN_THREADS, 1)
 rnn_cluster_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
   extern __shared__ __align__(16) unsigned char rnn_smem[];
+  pdl_launch_dependents();
   int pi = 0;
   while (pi + 1 < nprob && static_cast<int>(blockIdx.x) >= probs[pi + 1].cta_base) ++pi;
   const RnnProblemDev p = probs[pi];
@@ -809,11 +812,13 @@ int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream) {
       cfg.blockDim = dim3(RNN_THREADS);
       cfg.dynamicSmemBytes = l.smem;
       cfg.stream = l.lane ? plan.side[l.lane - 1] : stream;
-      cudaLaunchAttribute attr[1];
+      cudaLaunchAttribute attr[2];
       attr[0].id = cudaLaunchAttributeClusterDimension;
       attr[0].val.clusterDim.x = l.cluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[1].val.programmaticStreamSerializationAllowed = 1;
       cfg.attrs = attr;
-      cfg.numAttrs = 1;
+      cfg.numAttrs = (l.lane == 0 && pdl_enabled()) ? 2 : 1;    // side lanes follow an event wait, not a kernel
       ce = cudaLaunchKernelEx(&cfg, rnn_cluster_kernel, base, count);
       if (ce != cudaSuccess) return static_cast<int>(ce);
     }
