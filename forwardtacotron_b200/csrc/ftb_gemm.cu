@@ -24,6 +24,7 @@
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
 
+
 namespace ftb {
 
 constexpr int BM = 128;                 // tile rows  (UMMA M)
@@ -33,6 +34,10 @@ constexpr int STAGES = 4;
 constexpr int A_STAGE_BYTES = BM * BK * 4;        // 16 KB
 constexpr int B_STAGE_BYTES = 256 * BK * 4;       // 32 KB (bn <= 256)
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+// CTA-pair mode: a CTA stages only half of the W tile, so the same 192 KB ring holds six 32 KB stages
+constexpr int PAIR_STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES / 2;
+constexpr int PAIR_STAGES = (STAGES * STAGE_BYTES) / PAIR_STAGE_BYTES;
+constexpr double GEMM_PAIR_MIN_KITERS = 8.0;      // mean k-blocks per tile from which a launch runs as CTA pairs
 constexpr int TMEM_COLS = 512;          // 2 accumulators x 256 fp32 columns
 constexpr int NUM_THREADS = 320;
 constexpr int EPI_THREADS = 128;         // per epilogue set
@@ -41,8 +46,8 @@ constexpr int STG_LD = 36;              // staging row stride (floats): conflict
 constexpr int STG_ROWS = 16;            // the 32 rows of a chunk pass through the staging tile in two halves
 
 struct SmemTail {
-  uint64_t full[STAGES];
-  uint64_t empty[STAGES];
+  uint64_t full[PAIR_STAGES];
+  uint64_t empty[PAIR_STAGES];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
@@ -63,13 +68,15 @@ struct TileCoord {
 // out of range only in the last, partial wave, so every role of the CTA stops at the same i.
 __device__ __forceinline__ int sched_tile(int i, int c, int G) { return i * G + ((i & 1) ? (G - 1 - c) : c); }
 
-__device__ __forceinline__ TileCoord decode_tile(const GemmProblemDev* probs, int nprob, int tile) {
+// pair_rank < 0: one tile per CTA.  Otherwise (CTA-pair plans) `tile` counts PAIRS of consecutive m-tiles of one n-tile
+// and the CTA of rank r takes the r-th of the two (the second may lie behind the last row: it then stores nothing).
+__device__ __forceinline__ TileCoord decode_tile(const GemmProblemDev* probs, int nprob, int tile, int pair_rank) {
   int pi = 0;
   while (pi + 1 < nprob && tile >= probs[pi + 1].tile_base) ++pi;
   const GemmProblemDev* p = probs + pi;
   const int local = tile - p->tile_base;
   const int nt = local % p->n_tiles;
-  const int mt = local / p->n_tiles;
+  const int mt = pair_rank < 0 ? local / p->n_tiles : 2 * (local / p->n_tiles) + pair_rank;
   return {p, mt * p->m_step + p->m_shift, nt * p->bn};
 }
 
@@ -324,8 +331,8 @@ __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool re
 }
 
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(NUM_THREADS, 1)
-conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
+template <bool PAIR>
+__device__ __forceinline__ void conv_gemm_tc_body(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment by pointer arithmetic on the __shared__ array (an integer round trip would demote every
   // later access through `tail` to generic LD/ST, which the epilogue pays for in latency)
@@ -343,24 +350,35 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
 #define GP_ACC(i)
 #endif
 
+  // CTA-pair mode: the two CTAs of a cluster share one schedule slot and run M = 256 MMAs (cta_group::2) issued by the
+  // even CTA; each loads its own A tile and HALF of the W tile, which is what lifts the 64 B/clk per-SM operand ingest
+  // bound of the 128 x 256 single-CTA tile (profiles/r1t_gemm_ingest.txt).
+  constexpr int NSTAGE = PAIR ? PAIR_STAGES : STAGES;
+  constexpr int SBYTES = PAIR ? PAIR_STAGE_BYTES : STAGE_BYTES;
+  const int rank = PAIR ? static_cast<int>(cta_rank_in_cluster()) : 0;
+  const bool leader = rank == 0;
+  const int pair_rank = PAIR ? rank : -1;
+  const int sched_c = PAIR ? (blockIdx.x >> 1) : blockIdx.x;
+  const int sched_g = PAIR ? (gridDim.x >> 1) : gridDim.x;
   pdl_launch_dependents();
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < NSTAGE; ++s) {
       mbar_init(&tail->full[s], 1);
       mbar_init(&tail->empty[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tail->tmem_full[b], 1);
-      mbar_init(&tail->tmem_empty[b], 4);       // one arrive per epilogue warp of the set that drains buffer b
+      mbar_init(&tail->tmem_empty[b], PAIR ? 8 : 4);   // one arrive per epilogue warp (of both CTAs) draining buffer b
     }
     fence_mbar_init();
   }
   if (warp == 1) {                              // whole warp: .sync.aligned
-    tmem_alloc(&tail->tmem_base, TMEM_COLS);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_pair(&tail->tmem_base, TMEM_COLS); tmem_relinquish_pair(); }
+    else { tmem_alloc(&tail->tmem_base, TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_barrier();      // the peer's barriers exist before any remote arrive / multicast commit
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tail->tmem_base;
   // everything above (barriers, TMEM) overlapped the tail of the previous kernel; its outputs are read from here on
@@ -373,11 +391,14 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       uint32_t phase = 0;
       const GemmProblemDev* last_p = nullptr;
       for (int it = 0;; ++it) {
-        const int tile = sched_tile(it, blockIdx.x, gridDim.x);
+        const int tile = sched_tile(it, sched_c, sched_g);
         if (tile >= total_tiles) break;
-        const TileCoord tc = decode_tile(probs, nprob, tile);
+        const TileCoord tc = decode_tile(probs, nprob, tile, pair_rank);
         const GemmProblemDev* p = tc.p;
-        const uint32_t tx = A_STAGE_BYTES + static_cast<uint32_t>(p->bn) * BK * 4;
+        // pair: the leader's barrier collects both CTAs' A tiles and W halves
+        const uint32_t tx = PAIR ? 2u * (A_STAGE_BYTES + static_cast<uint32_t>(p->bn / 2) * BK * 4)
+                                 : A_STAGE_BYTES + static_cast<uint32_t>(p->bn) * BK * 4;
+        const int w_row0 = tc.n0 + (PAIR ? rank * (p->bn / 2) : 0);
         if (p != last_p) {
           tma_desc_fence_acquire(&p->tm_a);
           tma_desc_fence_acquire(&p->tm_w);
@@ -395,40 +416,59 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int tap = 0; tap < taps; ++tap) {
             GP_T0 mbar_wait(&tail->empty[stage], phase ^ 1u); GP_ACC(0)
-            uint8_t* sa = smem + stage * STAGE_BYTES;
+            uint8_t* sa = smem + stage * SBYTES;
             uint8_t* sb = sa + A_STAGE_BYTES;
-            mbar_expect_tx(&tail->full[stage], tx);
-            tma_load_2d(sa, tm_a, &tail->full[stage], kb * kelems, tc.m0 + tap0 + tap);
-            tma_load_2d(sb, tm_w, &tail->full[stage], kb * kelems, tap * w_tap_rows + tc.n0);
-            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            if (PAIR) {
+              if (leader) mbar_expect_tx(&tail->full[stage], tx);
+              tma_load_2d_pair(sa, tm_a, &tail->full[stage], kb * kelems, tc.m0 + tap0 + tap);
+              tma_load_2d_pair(sb, tm_w, &tail->full[stage], kb * kelems, tap * w_tap_rows + w_row0);
+            } else {
+              mbar_expect_tx(&tail->full[stage], tx);
+              tma_load_2d(sa, tm_a, &tail->full[stage], kb * kelems, tc.m0 + tap0 + tap);
+              tma_load_2d(sb, tm_w, &tail->full[stage], kb * kelems, tap * w_tap_rows + tc.n0);
+            }
+            if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0) {
+    if (lane == 0 && leader) {
       int stage = 0;
       uint32_t phase = 0;
       for (int it = 0;; ++it) {
-        const int tile = sched_tile(it, blockIdx.x, gridDim.x);
+        const int tile = sched_tile(it, sched_c, sched_g);
         if (tile >= total_tiles) break;
-        const TileCoord tc = decode_tile(probs, nprob, tile);
+        const TileCoord tc = decode_tile(probs, nprob, tile, pair_rank);
         const GemmProblemDev* p = tc.p;
         const int buf = it & 1;
         GP_T0 mbar_wait(&tail->tmem_empty[buf], ((it >> 1) & 1u) ^ 1u); GP_ACC(1)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         const bool f16 = (p->flags & FTB_F_A_F16) != 0;
-        const uint32_t idesc = f16 ? umma_idesc_f16(BM, p->bn) : umma_idesc_tf32(BM, p->bn);
+        const uint32_t mma_m = PAIR ? 2 * BM : BM;
+        const uint32_t idesc = f16 ? umma_idesc_f16(mma_m, p->bn) : umma_idesc_tf32(mma_m, p->bn);
         const int kiters = p->taps * p->kblocks;
         for (int ki = 0; ki < kiters; ++ki) {
           GP_T0 mbar_wait(&tail->full[stage], phase); GP_ACC(2)
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sa = smem_u32(smem + stage * SBYTES);
           const uint64_t da = umma_desc_sw128(sa);
           const uint64_t db = umma_desc_sw128(sa + A_STAGE_BYTES);
           // +32 bytes per MMA (8 tf32 / 16 fp16 channels) inside the 128-byte swizzle row: +2 in (addr >> 4) units
+          if (PAIR) {
+            if (f16) {
+#pragma unroll
+              for (int k = 0; k < BK / UMMA_K; ++k)
+                umma_f16_ss_pair(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
+            } else {
+#pragma unroll
+              for (int k = 0; k < BK / UMMA_K; ++k)
+                umma_tf32_pair(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
+            }
+            umma_commit_pair(&tail->empty[stage]);      // frees the slot in BOTH CTAs
+          } else {
           if (f16) {
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) umma_f16_ss(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
@@ -437,9 +477,11 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
             for (int k = 0; k < BK / UMMA_K; ++k) umma_tf32(d_tmem, da + 2u * k, db + 2u * k, idesc, (ki | k) != 0 ? 1u : 0u);
           }
           umma_commit(&tail->empty[stage]);     // frees the smem slot when these MMAs retire
-          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          }
+          if (++stage == NSTAGE) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(&tail->tmem_full[buf]);     // accumulator complete -> epilogue
+        if (PAIR) umma_commit_pair(&tail->tmem_full[buf]);      // both CTAs' epilogues
+        else umma_commit(&tail->tmem_full[buf]);     // accumulator complete -> epilogue
       }
     }
   } else {
@@ -454,9 +496,9 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
     const uint32_t bar_prm = 1 + 2 * set, bar_pool = 2 + 2 * set;      // named barriers of this set
     float (*stg)[STG_LD] = tail->stg[set * 4 + g];
     for (int it = set;; it += 2) {
-      const int tile = sched_tile(it, blockIdx.x, gridDim.x);
+      const int tile = sched_tile(it, sched_c, sched_g);
       if (tile >= total_tiles) break;
-      const TileCoord tc = decode_tile(probs, nprob, tile);
+      const TileCoord tc = decode_tile(probs, nprob, tile, pair_rank);
       const GemmProblemDev* p = tc.p;
       const int buf = set;                        // == it & 1
       // problem fields -> registers ONCE per tile: this warp stores to global memory, so without the copies the
@@ -599,7 +641,10 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
       tc_fence_before();
       __syncwarp();
       GP_ACC(4)
-      if (lane == 0) mbar_arrive(&tail->tmem_empty[buf]);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_leader(&tail->tmem_empty[buf]);
+        else mbar_arrive(&tail->tmem_empty[buf]);
+      }
     }
   }
 #ifdef FTB_GEMM_PROFILE
@@ -611,11 +656,23 @@ conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int tot
 #endif
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_barrier();      // neither CTA frees tensor memory (or leaves) while the pair's MMAs may still use it
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
+  conv_gemm_tc_body<false>(probs, nprob, total_tiles);
+}
+// CTA-pair form: launched with a cluster dimension of 2; `total_tiles` counts tile PAIRS.
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_gemm_tc_pair_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
+  conv_gemm_tc_body<true>(probs, nprob, total_tiles);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -708,6 +765,26 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* plan) {
   if (!problems || nproblems < 1 || nproblems > FTB_MAX_PROBLEMS) return FTB_E_ARG;
   std::vector<GemmProblemDev> host(nproblems);
+  // CTA pairs (cta_group::2 MMAs; each CTA stages half of the W tile, so the ring holds six stages instead of four).
+  // Measured (profiles/r1t_gemm_pair.txt): the deeper ring pays on launches whose tiles run many k-blocks (banks,
+  // proj1: -12..15 %) and the cluster launch + cross-CTA barriers cost 2-3 us on launches of one short tile per CTA.
+  // Default: by the work-weighted mean k-block count per tile; FTB_GEMM_PAIR=0/1 forces it.
+  const char* pair_env = getenv("FTB_GEMM_PAIR");
+  bool pair;
+  if (pair_env && (pair_env[0] == '0' || pair_env[0] == '1')) {
+    pair = pair_env[0] == '1';
+  } else {
+    double tiles = 0.0, kiters = 0.0;
+    for (int i = 0; i < nproblems; ++i) {
+      const ftb_gemm_problem& q = problems[i];
+      if (q.bn < 16 || q.rows < 1 || q.cin < 1) continue;         // rejected below
+      const int kel = (q.flags & FTB_F_A_F16) ? 2 * BK : BK;
+      const double t = static_cast<double>((q.rows + BM - 1) / BM) * ((q.n + q.bn - 1) / q.bn);
+      tiles += t;
+      kiters += t * q.taps * ((q.cin + kel - 1) / kel);
+    }
+    pair = tiles > 0.0 && kiters / tiles >= GEMM_PAIR_MIN_KITERS;
+  }
   int tile_base = 0;
   long long simt_elems = 0;
   for (int i = 0; i < nproblems; ++i) {
@@ -751,10 +828,10 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     }
     d.m_tiles = static_cast<int>((q.rows + d.m_step - 1) / d.m_step);
     d.tile_base = tile_base;
-    tile_base += d.m_tiles * d.n_tiles;
+    tile_base += (pair ? (d.m_tiles + 1) / 2 : d.m_tiles) * d.n_tiles;
     int rc = make_map(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
     if (rc) return rc;
-    rc = make_map(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, q.bn, a16);
+    rc = make_map(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, pair ? q.bn / 2 : q.bn, a16);
     if (rc) return rc;
     const long long e = q.rows * q.n;
     if (e > simt_elems) simt_elems = e;
@@ -765,6 +842,7 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
   ce = cudaMemcpy(dev, host.data(), sizeof(GemmProblemDev) * nproblems, cudaMemcpyHostToDevice);
   if (ce != cudaSuccess) { cudaFree(dev); return static_cast<int>(ce); }
   plan->dev = dev; plan->nprob = nproblems; plan->total_tiles = tile_base; plan->simt_elems = simt_elems;
+  plan->pair = pair;
   return 0;
 }
 
@@ -781,21 +859,35 @@ int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t s
   if (!attr_set) {
     cudaError_t ce = cudaFuncSetAttribute(conv_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (ce != cudaSuccess) return static_cast<int>(ce);
+    ce = cudaFuncSetAttribute(conv_gemm_tc_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (ce != cudaSuccess) return static_cast<int>(ce);
     attr_set = true;
   }
-  const int grid = plan.total_tiles < num_sms ? plan.total_tiles : num_sms;
+  const int slots = plan.pair ? num_sms / 2 : num_sms;          // schedule slots: CTAs or CTA pairs
+  const int used = plan.total_tiles < slots ? plan.total_tiles : slots;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
+  cfg.gridDim = dim3(plan.pair ? 2 * used : used);
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (plan.pair) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel, static_cast<const GemmProblemDev*>(plan.dev),
-                                             plan.nprob, plan.total_tiles));
+  cfg.numAttrs = na;
+  const GemmProblemDev* dev = plan.dev;
+  if (plan.pair)
+    return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_pair_kernel, dev, plan.nprob, plan.total_tiles));
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel, dev, plan.nprob, plan.total_tiles));
 }
 
 }  // namespace ftb

@@ -49,6 +49,7 @@ struct GemmPlan {
   int nprob = 0;
   int total_tiles = 0;
   long long simt_elems = 0;   // max rows*n over problems (SIMT cross-check grid)
+  bool pair = false;          // CTA-pair plan: total_tiles / tile_base count tile pairs, tm_w boxes hold bn/2 rows
 };
 
 int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* plan);

@@ -182,6 +182,56 @@ def test_highway_and_transposed_linear():
     prog.h.impl = 0
 
 
+def test_gemm_cta_pair_mode_agrees(monkeypatch):
+    """FTB_GEMM_PAIR=1 (cta_group::2: M = 256 MMAs issued by the even CTA of a 2-CTA cluster, each CTA staging half of
+    the W tile, six-stage ring) against the single-CTA kernel on one launch mixing a pooled fp16 bank convolution, a
+    k=3 projection with residual, a highway layer and a transposed linear layer; odd m-tile counts included."""
+    B, L, ch = 3, 171, 128                      # 3 * stride rows -> an odd number of m-tiles for the pooled problem
+    got = {}
+    for mode in ('0', '1'):
+        monkeypatch.setenv('FTB_GEMM_PAIR', mode)
+        gen = torch.Generator().manual_seed(23)
+        prog = eng.Program(_handle(), eng.Geometry(B, L))
+        g = prog.geo
+        v = torch.randn(B, L, ch, generator=gen)
+        a16, a32 = prog.buf('a16', ch, torch.float16), prog.buf('a32', ch)
+        a16.view(B, g.stride, ch)[:, :L] = v.to(DEV).half()
+        a32.view(B, g.stride, ch)[:, :L] = v.to(DEV)
+        w = torch.randn(256, ch, 5, generator=gen) / (ch * 5) ** 0.5
+        gamma, beta = torch.rand(256, generator=gen) + 0.5, torch.randn(256, generator=gen) * 0.1
+        mean, var = torch.randn(256, generator=gen) * 0.1, torch.rand(256, generator=gen) + 0.5
+        bank = pk.pack_bn_conv(w.to(DEV), gamma.to(DEV), beta.to(DEV), mean.to(DEV), var.to(DEV), True)
+        o_bank = prog.buf('bank', 256, torch.float16)
+        prog.gemm(a16, bank, o_bank, epilogue=rt.EPI_MAXPOOL)
+        w3 = torch.randn(ch, ch, 3, generator=gen) / (ch * 3) ** 0.5
+        proj = pk.pack_bn_conv(w3.to(DEV), gamma[:ch].to(DEV), beta[:ch].to(DEV), mean[:ch].to(DEV), var[:ch].to(DEV), False)
+        o_proj = prog.buf('proj', ch)
+        prog.gemm(a16, proj, o_proj, residual=a32)
+        w1, w2 = torch.randn(ch, ch, generator=gen) / 11, torch.randn(ch, ch, generator=gen) / 11
+        hw = pk.pack_highway(w1.to(DEV), torch.zeros(ch, device=DEV), w2.to(DEV), torch.ones(ch, device=DEV))
+        o_hw, o_hwf = prog.buf('hw', ch, torch.float16), prog.buf('hw_full', ch)
+        prog.gemm(a16, hw, o_hw, epilogue=rt.EPI_HIGHWAY, residual=a32, out_full=o_hwf)
+        lin = pk.pack_linear((torch.randn(80, ch, generator=gen) / 11).to(DEV), torch.randn(80, generator=gen).to(DEV))
+        mel = prog.dense('mel', (B, 80, L))
+        prog.gemm(a32, lin, None, out_t=mel)
+        prog.flush()
+        prog.run()
+        torch.cuda.synchronize()
+        got[mode] = [t.float().cpu().clone() for t in (o_bank, o_proj, o_hw, o_hwf, mel)]
+        prog.h.impl = 1                                      # SIMT cross-check of the same plan
+        ref = []
+        for t in (o_bank, o_proj, o_hw, o_hwf, mel):
+            t.zero_()
+        prog.run()
+        torch.cuda.synchronize()
+        prog.h.impl = 0
+        for a, t in zip(got[mode], (o_bank, o_proj, o_hw, o_hwf, mel)):
+            assert max_abs(a, t.float().cpu()) < 2e-3, mode
+    for a, b in zip(got['0'], got['1']):
+        assert max_abs(a, b) < 1e-5
+        assert float(a.abs().max()) > 0.1
+
+
 def test_fp16_operand_copy_next_to_twin_residual_transposed():
     """FTB_F_OUT_F16 with out_full / residual / highway / out_t: the small-K chain proj2 -> pre_highway -> highways
     -> gru_ih and `lin` hand fp16 operand copies on while their fp32 twins feed the residual terms."""
