@@ -289,6 +289,7 @@ def run_ours(args, rank, world, local_rank):
         if info['kind'] == 'gemm':
             k['tflops'] = round(info['flops'] / ms / 1e9, 1)
             k['f16_share'] = round((info.get('flops_f16') or 0.0) / max(info['flops'], 1.0), 3)
+            k['cta_pairs'] = bool(info.get('cta_pairs'))
         if info['kind'] in ('rnn', 'glue') and info['bytes']:
             k['gbs'] = round(info['bytes'] / ms / 1e6, 1)
         if info['kind'] == 'rnn':
@@ -333,6 +334,9 @@ def run_ours(args, rank, world, local_rank):
                               'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak,
                               'traffic': None,
                               'f16_flop_share': round(f16 / max(g['flops'], 1.0), 3),
+                              'pair_launches_per_step': sum(1 for kk, _ in kernels if kk.get('cta_pairs')),
+                              'kernel_note': 'conv_gemm_tc_kernel and its 2-CTA form conv_gemm_tc_pair_kernel '
+                                             '(same body, tcgen05.mma.cta_group::2; picked per launch)',
                               'peak_note': f"FLOP-weighted: kind::f16 layers at the {peaks['source']} bf16 burst figure "
                                            f"{peaks['bf16']}, kind::tf32 layers at half of it"})
         elif g['bytes']:

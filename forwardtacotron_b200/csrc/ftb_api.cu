@@ -80,6 +80,15 @@ extern "C" int ftb_gemm_plan_run(ftb_handle h, int plan, int impl, void* stream)
   return gemm_plan_launch(it->second, impl, h->num_sms, static_cast<cudaStream_t>(stream));
 }
 
+extern "C" int ftb_gemm_plan_info(ftb_handle h, int plan, int* cta_pairs, int* tiles) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->gemm_plans.find(plan);
+  if (it == h->gemm_plans.end()) return FTB_E_PLAN;
+  if (cta_pairs) *cta_pairs = it->second.pair ? 1 : 0;
+  if (tiles) *tiles = it->second.total_tiles;
+  return 0;
+}
+
 extern "C" int ftb_gemm_plan_destroy(ftb_handle h, int plan) {
   if (!h) return FTB_E_ARG;
   DeviceScope scope(h->device);

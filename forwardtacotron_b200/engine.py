@@ -172,7 +172,8 @@ class Program:
                          (2.0 if q.flags & rt.F_OUT_F16 else 4.0) * valid * q.n for q in grp)
             labels = sorted({getattr(q, '_label', '') for q in grp})
             self.info.append({'kind': 'gemm', 'label': '+'.join(l for l in labels if l) or 'gemm',
-                              'flops': flops, 'flops_f16': flops_f16, 'bytes': nbytes, 'problems': len(grp)})
+                              'flops': flops, 'flops_f16': flops_f16, 'bytes': nbytes, 'problems': len(grp),
+                              **self.h.gemm_info(plan)})
 
     def rnn(self, specs, lens: Optional[torch.Tensor] = None, pad_value: float = 0.0):
         """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one plan (cluster or cooperative launches).

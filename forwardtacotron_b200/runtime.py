@@ -67,7 +67,7 @@ class LrGatherArgs(C.Structure):
 
 # every symbol include/ftb200.h declares (tests check that the .so exports all of them)
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
-           'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy',
+           'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy', 'ftb_gemm_plan_info',
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
            'ftb_lr_scan', 'ftb_lr_gather', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
@@ -93,6 +93,7 @@ def load_library() -> C.CDLL:
     lib.ftb_gemm_plan_create.argtypes = [_fp, C.POINTER(GemmProblem), C.c_int, C.POINTER(C.c_int)]
     lib.ftb_gemm_plan_run.argtypes = [_fp, C.c_int, C.c_int, _fp]
     lib.ftb_gemm_plan_destroy.argtypes = [_fp, C.c_int]
+    lib.ftb_gemm_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_rnn_plan_create.argtypes = [_fp, C.POINTER(RnnProblem), C.c_int, C.POINTER(C.c_int)]
     lib.ftb_rnn_plan_run.argtypes = [_fp, C.c_int, _fp]
     lib.ftb_rnn_plan_destroy.argtypes = [_fp, C.c_int]
@@ -182,6 +183,12 @@ class Handle:
 
     def rnn_run(self, plan: int):
         self.check(self.lib.ftb_rnn_plan_run(self.h, plan, self.stream()))
+
+    def gemm_info(self, plan: int) -> dict:
+        """What the library chose for the plan (include/ftb200.h: ftb_gemm_plan_info)."""
+        pair, tiles = C.c_int(0), C.c_int(0)
+        self.check(self.lib.ftb_gemm_plan_info(self.h, plan, C.byref(pair), C.byref(tiles)))
+        return {'cta_pairs': bool(pair.value), 'slots': tiles.value}
 
     def rnn_info(self, plan: int) -> dict:
         """Layout the library chose for the plan on this device (include/ftb200.h: ftb_rnn_plan_info)."""

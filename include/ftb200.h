@@ -111,6 +111,11 @@ int ftb_gemm_plan_create(ftb_handle h, const ftb_gemm_problem* problems, int npr
  * (test-only: same problems, no tensor cores, used by tests to bisect descriptor bugs).   */
 int ftb_gemm_plan_run(ftb_handle h, int plan, int impl, void* stream);
 int ftb_gemm_plan_destroy(ftb_handle h, int plan);
+/* What the library chose for the plan: *cta_pairs = 1 when the launch runs as 2-CTA clusters (conv_gemm_tc_pair_kernel:
+ * tcgen05.mma.cta_group::2, M = 256, half of the W tile staged per CTA, six-stage ring; picked for launches whose tiles
+ * run >= 8 k-blocks on average, FTB_GEMM_PAIR=0/1 forces), *tiles = schedule slots (tiles, or tile pairs).  Either
+ * pointer may be null. */
+int ftb_gemm_plan_info(ftb_handle h, int plan, int* cta_pairs, int* tiles);
 
 /* ------------------------------------------------------------------------------------
  * K3/K4  persistent bidirectional GRU / LSTM recurrence

@@ -17,7 +17,8 @@ for r in rows:
         e[r['Metric Name'].split('.')[0]] = v * scale
 ls = list(launch.values())
 # one generate() = the launches from one embed_kernel to the next
-starts = [i for i, e in enumerate(ls) if e['name'] == 'embed_kernel' and (i == 0 or ls[i - 1]['name'] != 'embed_kernel')]
+is_embed = lambda e: e['name'].startswith('embed')          # embed_kernel / embed_batch_kernel open a generate()
+starts = [i for i, e in enumerate(ls) if is_embed(e) and (i == 0 or not is_embed(ls[i - 1]))]
 seg = ls[starts[1]:starts[2]] if len(starts) > 2 else ls[starts[0]:]
 tot = sum(e['us'] for e in seg)
 print(f'# one generate(): {len(seg)} launches, sum of cold-cache serialised kernel times {tot:.1f} us')
@@ -31,5 +32,13 @@ for k, a in sorted(agg.items(), key=lambda kv: -kv[1]['us']):
 print('# per launch:')
 for i, e in enumerate(seg):
     print(f"{i:3d} {e['name']:26s} grid {e['grid']:>14s} {e['us']:8.1f} us  rd {e.get('dram__bytes_read', 0) / 1e6:8.1f} MB  wr {e.get('dram__bytes_write', 0) / 1e6:8.1f} MB")
-json.dump({k: {'launches_per_step': a['n'], 'dram_bytes_per_step': a['rd'] + a['wr'], 'us_serialised': a['us']}
-           for k, a in agg.items()}, open(f'profiles/{tag}_traffic.json', 'w'), indent=1)
+out = {k: {'launches_per_step': a['n'], 'dram_bytes_per_step': a['rd'] + a['wr'], 'us_serialised': a['us']}
+       for k, a in agg.items()}
+# the CTA-pair form of the conv GEMM is the same kernel body: bench.py reports the family under conv_gemm_tc_kernel
+if 'conv_gemm_tc_pair_kernel' in out:
+    pr = out.pop('conv_gemm_tc_pair_kernel')
+    base = out.setdefault('conv_gemm_tc_kernel', {'launches_per_step': 0, 'dram_bytes_per_step': 0.0, 'us_serialised': 0.0})
+    for k in ('launches_per_step', 'dram_bytes_per_step', 'us_serialised'):
+        base[k] += pr[k]
+    base['pair_launches_per_step'] = pr['launches_per_step']
+json.dump(out, open(f'profiles/{tag}_traffic.json', 'w'), indent=1)

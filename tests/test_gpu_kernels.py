@@ -226,7 +226,8 @@ def test_gemm_cta_pair_mode_agrees(monkeypatch):
         torch.cuda.synchronize()
         prog.h.impl = 0
         for a, t in zip(got[mode], (o_bank, o_proj, o_hw, o_hwf, mel)):
-            assert max_abs(a, t.float().cpu()) < 2e-3, mode
+            # fp16 outputs: the two kernels may round a value to neighbouring halves (one ulp = 2^-10 relative)
+            assert max_abs(a, t.float().cpu()) < 5e-4 + 2.0 ** -10 * float(a.abs().max()), mode
     for a, b in zip(got['0'], got['1']):
         assert max_abs(a, b) < 1e-5
         assert float(a.abs().max()) > 0.1
