@@ -17,7 +17,17 @@
 // producers, so the tensor core's mantissa truncation is exact; accumulation is fp32.
 // FTB_F_A_F16 problems keep both operands in fp16 instead (same 11-bit significand; kind::f16 runs at twice the
 // tf32 rate on half the bytes): a 128-byte swizzle row then holds 64 channels and one MMA consumes K = 16.
-// FTB_F_OUT_F16 problems store their result as fp16 for such a consumer.
+// FTB_F_OUT_F16 problems store their result as fp16 for such a consumer (next to any fp32 twin / transposed output).
+//
+// Two forms of the same body (template <bool PAIR>):
+//   conv_gemm_tc_kernel       one CTA per tile, tcgen05.mma.cta_group::1 (M = 128), 4-stage ring of 48 KB
+//   conv_gemm_tc_pair_kernel  the two CTAs of a 2-CTA cluster take two consecutive m-tiles of one n-tile: each stages its
+//                             own A tile and HALF of the W tile, the even CTA issues tcgen05.mma.cta_group::2 (M = 256)
+//                             for both, tcgen05.commit multicasts the "slot free" / "accumulator ready" arrives to both
+//                             CTAs; 6-stage ring of 32 KB.  Picked per launch (gemm_plan_build) for tiles of >= 8
+//                             k-blocks; the large-K layers are bound by how fast stages land, and a stage that carries
+//                             the same MMA work in 2/3 of the bytes makes the ring 1.5x deeper (profiles/r1t_gemm_pair.txt).
+// Both start under programmatic dependent launch: barrier set-up and the TMEM allocation run before griddepcontrol.wait.
 #include <cstdio>
 #include <cuda_fp16.h>
 

@@ -20,11 +20,28 @@ __device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, cons
                                            const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
                                            float* __restrict__ out, int out_ld, int mode) {
   const int lane = threadIdx.x & 31;
-  const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
-  if (row >= static_cast<long long>(batch) * T) return;
-  const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);          // batch * T < 2^31 (checked by the callers)
+  if (row >= batch * T) return;
+  const int b = row / T, t = row - b * T;
   const long long o = (static_cast<long long>(b) * seq_stride + t) * out_ld;
   const float* s1 = table + tok[row] * e1;
+  if (e2 == 0 && e3 == 0 && (e1 & 3) == 0 && (out_ld & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0) {
+    // the common case (one table, width a multiple of 4): 16-byte reads, 16- / 8-byte stores
+    for (int c = lane * 4; c < e1; c += 128) {
+      const float4 v = *reinterpret_cast<const float4*>(s1 + c);
+      if (mode == 2) {
+        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(out) + o + c) =
+            make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+      } else {
+        float4 y = v;
+        if (mode) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
+        *reinterpret_cast<float4*>(out + o + c) = y;
+      }
+    }
+    return;
+  }
   for (int c = lane; c < e1; c += 32) embed_store(out, o + c, s1[c], mode);
   if (e2 > 0) {
     const float* s2 = table2 + tok2[row] * e2;
@@ -56,9 +73,9 @@ __device__ __forceinline__ void rowdot_rows(const float* __restrict__ x, int x_l
                                             const float* __restrict__ bias, int n_out, float alpha, int batch, int T,
                                             int seq_stride, float* __restrict__ y) {
   const int lane = threadIdx.x & 31;
-  const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
-  if (row >= static_cast<long long>(batch) * T) return;
-  const int b = static_cast<int>(row / T), t = static_cast<int>(row % T);
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);          // batch * T < 2^31 (checked by the callers)
+  if (row >= batch * T) return;
+  const int b = row / T, t = row - b * T;
   const float* xr = x + (static_cast<long long>(b) * seq_stride + t) * x_ld;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
   for (int c = lane; c < k; c += 32) {
@@ -73,7 +90,8 @@ __device__ __forceinline__ void rowdot_rows(const float* __restrict__ x, int x_l
     for (int s = 16; s > 0; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
   }
   if (lane == 0) {
-    for (int o = 0; o < n_out; ++o) y[row * n_out + o] = __fdiv_rn(acc[o] + bias[o], alpha);   // `/ alpha`: a true division
+    for (int o = 0; o < n_out; ++o)
+      y[static_cast<long long>(row) * n_out + o] = __fdiv_rn(acc[o] + bias[o], alpha);   // `/ alpha`: a true division
   }
 }
 
@@ -115,6 +133,7 @@ extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, i
   if (e3 > 0 && !extra) return FTB_E_ARG;
   if (e1 + e2 + e3 > out_ld || seq_stride < T || round_tf32 < 0 || round_tf32 > 2) return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * T;
+  if (rows > 0x7fffffffll) return FTB_E_ARG;
   embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, round_tf32);
   h->launches += 1;
@@ -134,6 +153,7 @@ extern "C" int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int ni
     args.item[i] = q;
   }
   const long long rows = static_cast<long long>(batch) * T;
+  if (rows > 0x7fffffffll) return FTB_E_ARG;
   embed_batch_kernel<<<dim3(static_cast<unsigned>((rows + 7) / 8), nitems), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       args, batch, T, seq_stride);
   h->launches += 1;
@@ -150,6 +170,7 @@ extern "C" int ftb_rowdot_batch(ftb_handle h, const ftb_rowdot_item* items, int 
     args.item[i] = q;
   }
   const long long rows = static_cast<long long>(batch) * T;
+  if (rows > 0x7fffffffll) return FTB_E_ARG;
   rowdot_batch_kernel<<<dim3(static_cast<unsigned>((rows + 7) / 8), nitems), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       args, batch, T, seq_stride);
   h->launches += 1;
@@ -160,6 +181,7 @@ extern "C" int ftb_rowdot(ftb_handle h, const float* x, int x_ld, int k, const f
                           int n_out, float alpha, int batch, int T, int seq_stride, float* y, void* stream) {
   if (!h || !x || !w || !bias || !y || n_out < 1 || n_out > 4 || k < 1 || batch < 1 || T < 1 || alpha == 0.0f) return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * T;
+  if (rows > 0x7fffffffll) return FTB_E_ARG;
   rowdot_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       x, x_ld, k, w, bias, n_out, alpha, batch, T, seq_stride, y);
   h->launches += 1;
