@@ -78,7 +78,21 @@ __device__ __forceinline__ void rowdot_rows(const float* __restrict__ x, int x_l
   const int b = row / T, t = row - b * T;
   const float* xr = x + (static_cast<long long>(b) * seq_stride + t) * x_ld;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int c = lane; c < k; c += 32) {
+  int c_done = 0;
+  if ((k & 3) == 0 && (x_ld & 3) == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) & 15u) == 0) {
+    for (int c = lane * 4; c < k; c += 128) {          // 16-byte reads of the row and of every weight vector
+      const float4 xv = *reinterpret_cast<const float4*>(xr + c);
+#pragma unroll
+      for (int o = 0; o < 4; ++o) {
+        if (o < n_out) {
+          const float4 wv = __ldg(reinterpret_cast<const float4*>(w + o * k + c));
+          acc[o] = fmaf(xv.w, wv.w, fmaf(xv.z, wv.z, fmaf(xv.y, wv.y, fmaf(xv.x, wv.x, acc[o]))));
+        }
+      }
+    }
+    c_done = k;
+  }
+  for (int c = c_done + lane; c < k; c += 32) {
     const float xv = xr[c];
 #pragma unroll
     for (int o = 0; o < 4; ++o)
