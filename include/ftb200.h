@@ -128,8 +128,8 @@ int ftb_gemm_plan_info(ftb_handle h, int plan, int* cta_pairs, int* tiles);
  * either through peer shared memory inside a thread-block cluster (st.async + mbarrier; the GRUs and
  * small-batch LSTMs) or through a plan-owned fp16 exchange tensor in L2 whose sentinel pre-fill doubles
  * as the per-step synchronisation (no counter barrier); the plan picks the protocol from the cluster
- * occupancy of the device (FTB_RNN_HANDOFF=l2|cluster overrides).  h_t is written as fp32 to `out`, the
- * layer output.  A plan may launch on plan-owned side streams that are forked from and joined to `stream`.
+ * occupancy of the device (FTB_RNN_HANDOFF=l2|cluster overrides).  h_t is written to `out`, the layer
+ * output, as fp32 or (out_f16) as the fp16 value it already is.  A plan may launch on plan-owned side streams that are forked from and joined to `stream`.
  *   GRU  (r,z,n): r = s(xr + Whr h + bhr); z = s(xz + Whz h + bhz);
  *                 n = tanh(xn + r*(Whn h + bhn)); h' = (1-z)*n + z*h
  *   LSTM (i,f,g,o): c' = s(f)*c + s(i)*tanh(g); h' = s(o)*tanh(c')
