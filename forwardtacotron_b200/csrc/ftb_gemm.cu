@@ -865,13 +865,17 @@ int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t s
     conv_gemm_simt_kernel<<<grid, 256, 0, stream>>>(plan.dev, plan.nprob);
     return static_cast<int>(cudaGetLastError());
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t ce = cudaFuncSetAttribute(conv_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+  // function attributes are per device: set them once for every device a plan is launched on
+  static bool attr_set[64] = {};
+  int dev_id = 0;
+  cudaError_t ce = cudaGetDevice(&dev_id);
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  if (dev_id < 0 || dev_id >= 64 || !attr_set[dev_id]) {
+    ce = cudaFuncSetAttribute(conv_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (ce != cudaSuccess) return static_cast<int>(ce);
     ce = cudaFuncSetAttribute(conv_gemm_tc_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (ce != cudaSuccess) return static_cast<int>(ce);
-    attr_set = true;
+    if (dev_id >= 0 && dev_id < 64) attr_set[dev_id] = true;
   }
   const int slots = plan.pair ? num_sms / 2 : num_sms;          // schedule slots: CTAs or CTA pairs
   const int used = plan.total_tiles < slots ? plan.total_tiles : slots;
