@@ -192,7 +192,9 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   const int GH = G * H;
   const float* whh = p.w_hh + static_cast<size_t>(dir) * GH * H;
   const float* bhh = p.b_hh + dir * GH;
-  const float* xp_dir = p.xproj + dir * GH;
+  // x-projection element type: fp32, or (x_f16) the fp16 copy a FTB_F_OUT_F16 GEMM wrote
+  const bool x16 = p.x_f16 != 0;
+  const int xesz = x16 ? 2 : 4;
   // exchange tensor hx[dir][t][b][H] (fp16)
   __half* hx_dir = p.hx + static_cast<size_t>(dir) * L * p.batch * H;
 
@@ -231,17 +233,20 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   __half* hx_pair = hx_dir + static_cast<size_t>(b0 + pb) * H + u0 + pu;       // + t * batch * H
 
   // ---- x-projection ring: 16-byte chunk `tid` of a step = (batch xb, gate xg_, 4 units) --------
-  constexpr int XCH = U / 4;                        // chunks per (batch, gate)
+  const int xce = 16 / xesz;                        // elements per 16-byte chunk
+  const int XCH = U / xce;                          // chunks per (batch, gate)
   const int xb = tid / (G * XCH), xg_ = (tid / XCH) % G, xpart = tid % XCH;
   const bool xv = (tid < NB * G * XCH) && (xb < nbv);
-  const float* x_src = xp_dir + static_cast<size_t>(b0 + xb) * p.seq_stride * (2 * GH) + xg_ * H + u0 + xpart * 4;
-  float* x_dst = x_s + xb * XSTR + xg_ * U + xpart * 4;
+  const char* x_src = reinterpret_cast<const char*>(p.xproj) +
+                      (static_cast<size_t>(b0 + xb) * p.seq_stride * (2 * GH) + dir * GH + xg_ * H + u0 + xpart * xce) * xesz;
+  char* x_dst = reinterpret_cast<char*>(x_s) + (xb * XSTR + xg_ * U + xpart * xce) * xesz;
+  const int x_stage = NB * XSTR * xesz;             // bytes per ring stage
   // running pointers (strength-reduced: the per-step 64-bit index math sat on the latency chain of the gate phase)
-  const long long x_step = dir ? -static_cast<long long>(2 * GH) : static_cast<long long>(2 * GH);
-  const float* x_pf = x_src + static_cast<size_t>(dir ? L - 1 : 0) * (2 * GH);
+  const long long x_step = (dir ? -static_cast<long long>(2 * GH) : static_cast<long long>(2 * GH)) * xesz;
+  const char* x_pf = x_src + static_cast<size_t>(dir ? L - 1 : 0) * (2 * GH) * xesz;
   int pf_step = 0;
   auto prefetch_x = [&]() {                         // x rows of step `pf_step` -> ring slot pf_step % XS
-    if (xv && pf_step < L) cp_async16(x_dst + (pf_step & (RNN_XS - 1)) * (NB * XSTR), x_pf);
+    if (xv && pf_step < L) cp_async16(x_dst + (pf_step & (RNN_XS - 1)) * x_stage, x_pf);
     cp_async_commit();
     x_pf += x_step;
     ++pf_step;
@@ -395,7 +400,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   };
   __half* hx_p = hx_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.batch * H;
   const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
-  const float* xs0 = x_s + pb * XSTR + pu;
+  const char* xs0 = reinterpret_cast<const char*>(x_s) + (pb * XSTR + pu) * xesz;
 #ifdef FTB_RNN_PROFILE
   // per-phase cycle accounting of warp 0 / lane 0 (diagnostic build only: -DFTB_RNN_PROFILE)
   unsigned long long prof[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -409,7 +414,12 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
     float hnew = 0.0f;
     bool dead = false;
     if (pv) {
-      const float* xs = xs0 + (step & (RNN_XS - 1)) * (NB * XSTR);
+      const char* xsb = xs0 + (step & (RNN_XS - 1)) * x_stage;
+      float xs[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+        xs[g] = x16 ? __half2float(*reinterpret_cast<const __half*>(xsb + g * U * 2))
+                    : *reinterpret_cast<const float*>(xsb + g * U * 4);
       float hh[G];
 #pragma unroll
       for (int g = 0; g < G; ++g) {
@@ -420,15 +430,15 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       }
       if (G == 4) {
         const float ig = sigm(xs[0] + hh[0]);
-        const float fg = sigm(xs[U] + hh[1]);
-        const float gg = tanh_fast(xs[2 * U] + hh[2]);
-        const float og = sigm(xs[3 * U] + hh[G - 1]);
+        const float fg = sigm(xs[1] + hh[1]);
+        const float gg = tanh_fast(xs[2] + hh[2]);
+        const float og = sigm(xs[G - 1] + hh[G - 1]);
         c_state = fg * c_state + ig * gg;
         hnew = og * tanh_fast(c_state);
       } else {
         const float r = sigm(xs[0] + hh[0]);
-        const float z = sigm(xs[U] + hh[1]);
-        const float n = tanh_fast(xs[2 * U] + r * hh[2]);
+        const float z = sigm(xs[1] + hh[1]);
+        const float n = tanh_fast(xs[2] + r * hh[2]);
         hnew = (1.0f - z) * n + z * h_state;
       }
       const bool live = (dir ? (L - 1 - step) : step) < len_b;
@@ -661,7 +671,7 @@ static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& wh
       const int take = want < room ? want : room;
       RnnProblemDev d{};
       d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = nullptr;
-      d.lens = q.lens; d.pad_value = q.pad_value; d.out_f16 = q.out_f16;
+      d.lens = q.lens; d.pad_value = q.pad_value; d.out_f16 = q.out_f16; d.x_f16 = q.x_f16;
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
       d.gates = q.cell == FTB_CELL_LSTM ? 4 : 3;

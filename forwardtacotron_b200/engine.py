@@ -15,6 +15,11 @@ from . import runtime as rt
 from .pack import PackedGemm, PackedRnn
 
 
+# fp16 x-projections for the frame-side recurrences (BiLSTM, postnet BiGRU): halves the fp32 `W_ih x` traffic of the two
+# epilogue-bound projection GEMMs for one more rounding to 11 bits.  Measured on the goldens: mel rel-L2 7.01e-4 ->
+# 7.13e-4 (ForwardTacotron worst case), 7.06e-4 -> 7.27e-4 (MultiForwardTacotron), tolerance 1e-3; generate() 2.65 ->
+# 2.58 ms.  The token-side recurrences (predictors, prenet) keep fp32 x-projections.  FTB_X16=0 disables it.
+X16 = os.environ.get('FTB_X16', '1') != '0'
 F16_OPERANDS = _F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
 
 
@@ -189,6 +194,7 @@ class Program:
             p.out, p.out_ld, p.out_col0 = out.data_ptr(), out.shape[1], col0
             p.lens, p.pad_value = (lens.data_ptr() if lens is not None else None), float(pad_value)
             p.out_f16 = int(out.dtype == torch.float16)       # h_t is fp16-exact: an fp16 layer output loses nothing
+            p.x_f16 = int(xproj.dtype == torch.float16)
             probs.append(p)
             self._keep += [r, xproj, out] + ([lens] if lens is not None else [])
         plan = self.h.rnn_plan(probs)
@@ -290,7 +296,7 @@ class CbhgPack:
 
 
 def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torch.Tensor, out_col0: int = 0,
-                x_full: Optional[torch.Tensor] = None):
+                x_full: Optional[torch.Tensor] = None, xproj_f16: bool = False):
     """Returns the list of per-level closures for one CBHG over input buffer x [rows, in_channels];
     level i may be queued only after level i-1 has been flushed.  The last entry runs the BiGRU."""
     K = len(c.bank)
@@ -309,7 +315,7 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     # unrounded twins of the highway activations: the residual term (1-g)*x uses full fp32 values, only the
     # GEMM operand copy is tf32-rounded
     hwf = [prog.buf(f'{tag}.hw0_full', ch), prog.buf(f'{tag}.hw1_full', ch)]
-    xp = prog.buf(f'{tag}.xproj', c.rnn.ih.n)
+    xp = prog.buf(f'{tag}.xproj', c.rnn.ih.n, torch.float16 if (xproj_f16 and c.rnn.ih.n % 8 == 0) else torch.float32)
     levels = []
 
     def named(name, fn):

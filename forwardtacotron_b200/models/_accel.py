@@ -85,7 +85,8 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     lstm: pk.PackedRnn = packs['lstm']
     # the regulated sequence feeds only the W_ih GEMM: fp16 operand copy (K5 writes it directly)
     x = prog.buf('lr', in_channels, torch.float16 if (eng.F16_OPERANDS and in_channels % 8 == 0) else torch.float32)
-    xp = prog.buf('lstm.xproj', lstm.ih.n)
+    x16 = eng.X16 and eng.F16_OPERANDS and lstm.ih.n % 8 == 0
+    xp = prog.buf('lstm.xproj', lstm.ih.n, torch.float16 if x16 else torch.float32)
     # the recurrences hand h_t on in fp16, so their layer outputs are fp16-exact: `lin` and `post_proj` (their only
     # readers) take them as fp16 operands
     odt = torch.float16 if eng.F16_OPERANDS else torch.float32
@@ -127,7 +128,7 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
             torch.where(m[:, None, :M], v[None, :, None], mel, out=mel)
         prog.call(fix_pad_rows, label='lin.pad_rows')
     prog.label('')
-    levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full)
+    levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full, xproj_f16=x16)
     eng.run_levels(prog, [levels])
     prog.label('postnet.gru')
     prog.rnn([gru])

@@ -35,7 +35,7 @@ class RnnProblem(C.Structure):
     _fields_ = [('cell', C.c_int32), ('hidden', C.c_int32), ('batch', C.c_int32), ('seq_len', C.c_int32),
                 ('seq_stride', C.c_int32), ('xproj', _fp), ('w_hh', _fp), ('b_hh', _fp), ('out', _fp),
                 ('out_ld', C.c_int32), ('out_col0', C.c_int32), ('lens', _fp), ('pad_value', C.c_float),
-                ('out_f16', C.c_int32)]
+                ('out_f16', C.c_int32), ('x_f16', C.c_int32)]
 
 
 class EmbedItem(C.Structure):

@@ -152,6 +152,8 @@ typedef struct {
   float pad_value;
   int32_t out_f16;       /* != 0: `out` is fp16 [batch*seq_stride, out_ld] (h_t is fp16-exact, so this loses nothing):
                             the operand copy for a following FTB_F_A_F16 GEMM (lin / post_proj)                 */
+  int32_t x_f16;         /* != 0: `xproj` is fp16 [batch*seq_stride, 2*g*H] (a FTB_F_OUT_F16 GEMM wrote it): half the
+                            x-projection traffic for one more rounding to 11 bits              */
 } ftb_rnn_problem;
 
 #define FTB_MAX_RNN_PROBLEMS 8

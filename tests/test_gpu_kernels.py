@@ -336,7 +336,7 @@ def test_recurrence_handoff_protocols_agree(cell, H, B, L, monkeypatch):
         for p in rnn.parameters():
             p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
     packed = pk.PackedRnn(rnn.to(DEV))
-    got = {}
+    got, gotx = {}, {}
     for mode in ('cluster', 'l2'):
         monkeypatch.setenv('FTB_RNN_HANDOFF', mode)
         prog = eng.Program(_handle(), eng.Geometry(B, L))
@@ -349,6 +349,10 @@ def test_recurrence_handoff_protocols_agree(cell, H, B, L, monkeypatch):
         prog.rnn([(packed, xp, out, 0)])
         assert prog.info[-1]['handoff'] == mode
         prog.rnn([(packed, xp, out16, 0)])
+        xp16 = prog.buf('xp16', packed.ih.n, torch.float16)  # x_f16: the x-projection as an fp16 GEMM output
+        outx = prog.buf('hx16', 2 * H)
+        prog.gemm(a, packed.ih, xp16, round_out=False)
+        prog.rnn([(packed, xp16, outx, 0)])
         for _ in range(2):                                   # second run: barriers / sentinels re-armed
             prog.run()
         torch.cuda.synchronize()
@@ -356,7 +360,11 @@ def test_recurrence_handoff_protocols_agree(cell, H, B, L, monkeypatch):
         assert bool(torch.isfinite(got[mode]).all())
         assert torch.equal(prog.view('h16').float().cpu(), got[mode])
         assert float(out16.view(B, prog.geo.stride, -1)[:, L:].float().abs().max()) == 0.0
+        gotx[mode] = prog.view('hx16').cpu().clone()
+        assert max_abs(gotx[mode], got[mode]) < 5e-3         # one more rounding of the gate pre-activations to 11 bits
+        assert max_abs(gotx[mode], got[mode]) > 0.0
     assert torch.equal(got['cluster'], got['l2'])
+    assert torch.equal(gotx['cluster'], gotx['l2'])
 
 
 @pytest.mark.parametrize('cell,H,B,L', [('gru', 128, 5, 33), ('lstm', 512, 19, 27)])

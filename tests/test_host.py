@@ -32,7 +32,7 @@ def test_struct_layout_matches_header(tmp_path):
     import subprocess
     src = tmp_path / 'probe.c'
     fields = {'ftb_gemm_problem': (rt.GemmProblem, ['w', 'bias0', 'out', 'out_t', 'seq_stride']),
-              'ftb_rnn_problem': (rt.RnnProblem, ['xproj', 'out', 'out_col0', 'pad_value', 'out_f16']),
+              'ftb_rnn_problem': (rt.RnnProblem, ['xproj', 'out', 'out_col0', 'pad_value', 'out_f16', 'x_f16']),
               'ftb_lr_gather_args': (rt.LrGatherArgs, ['extra', 'wp', 'ps', 'we', 'cum', 'out', 'idx', 'round_tf32']),
               'ftb_embed_item': (rt.EmbedItem, ['table', 'e1', 'tok2', 'e2', 'extra', 'e3', 'out', 'out_ld', 'round_tf32']),
               'ftb_rowdot_item': (rt.RowdotItem, ['x_ld', 'k', 'w', 'bias', 'n_out', 'alpha', 'y'])}
