@@ -28,6 +28,7 @@ extern "C" const char* ftb_error_string(int code) {
     case FTB_E_PLAN: return "unknown plan id";
     case FTB_E_DRIVER: return "cuTensorMapEncodeTiled unavailable (no CUDA driver)";
     case FTB_E_RESIDENT: return "persistent recurrence grid does not fit on the device";
+    case FTB_E_LIMIT: return "size exceeds the fixed capacity of the no-allocation entry point (FTB_LR_STATIC_MAX_*)";
     default: break;
   }
   if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));

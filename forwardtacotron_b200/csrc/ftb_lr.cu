@@ -3,6 +3,8 @@
 // 128-bit accesses, one warp per output row, no tensor cores.
 #include <cuda_fp16.h>
 
+#include <mutex>
+
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
 
@@ -261,4 +263,105 @@ extern "C" int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void*
   lr_gather_kernel<<<token_blocks + a.batch, 256, smem, static_cast<cudaStream_t>(stream)>>>(g, token_blocks);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------------
+// ftb_lr_regulate_static: scan + gather with NO allocation anywhere on the call path.
+//
+// The scan's intermediates (cum [batch*T], lens [batch], meta [4]) normally live in caller-allocated
+// scratch tensors (ftb_lr_scan / ftb_lr_gather).  Here they live in ONE file-scope device array that
+// every GPU loading the library holds until exit (FTB_LR_STATIC_BYTES, see include/ftb200.h).  All
+// calls on a device share it: it keeps the previous call's contents (meta is re-zeroed per call, cum and
+// lens are fully overwritten for the [batch, T] in use), and two calls that overlap on the GPU race.
+//
+// `g_lr_static` in HOST code is only a host-side stand-in for the symbol, never a device address: the
+// device address is taken once per device with cudaGetSymbolAddress, with that device current.
+// ------------------------------------------------------------------------------------------------
+namespace ftb {
+
+constexpr int LR_STATIC_WORDS = FTB_LR_STATIC_MAX_TOKENS + FTB_LR_STATIC_MAX_BATCH + 64;
+static_assert(sizeof(int32_t) * LR_STATIC_WORDS == FTB_LR_STATIC_BYTES, "ftb200.h states the footprint");
+static __device__ __align__(256) int32_t g_lr_static[LR_STATIC_WORDS];
+
+constexpr int LR_STATIC_MAX_DEVICES = 64;
+static int32_t* g_lr_static_addr[LR_STATIC_MAX_DEVICES];      // device address of g_lr_static per device (host table)
+static std::mutex g_lr_static_mu;
+
+// Device address of the scratch on `device`, which must be the current device.
+static int lr_static_scratch(int device, int32_t** out) {
+  if (device < 0 || device >= LR_STATIC_MAX_DEVICES) return FTB_E_ARG;
+  std::lock_guard<std::mutex> lock(g_lr_static_mu);
+  if (!g_lr_static_addr[device]) {
+    int32_t* p = nullptr;
+    const cudaError_t ce = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_lr_static);
+    if (ce != cudaSuccess) return static_cast<int>(ce);
+    if (!p) return FTB_E_ARG;
+    g_lr_static_addr[device] = p;
+  }
+  *out = g_lr_static_addr[device];
+  return 0;
+}
+
+struct CurrentDevice {                  // make the handle's device current for the call, restore afterwards
+  int prev = -1;
+  bool switched = false;
+  cudaError_t err = cudaSuccess;
+  explicit CurrentDevice(int device) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != device) { err = cudaSetDevice(device); switched = (err == cudaSuccess); }
+  }
+  ~CurrentDevice() { if (switched) cudaSetDevice(prev); }
+};
+
+}  // namespace ftb
+
+extern "C" int ftb_lr_regulate_static(ftb_handle h, const float* x, int x_stride, int x_ld, int c, float* dur,
+                                      int batch, int T, int apply_fallback, int M, float* out, int out_stride,
+                                      int out_ld, int32_t* idx, int32_t* lens_out, int32_t* meta_out, void* stream) {
+  if (!h || !x || !dur || !out || batch < 1 || T < 1 || M < 0 || c < 1) return FTB_E_ARG;
+  if (batch > FTB_LR_STATIC_MAX_BATCH || static_cast<long long>(batch) * T > FTB_LR_STATIC_MAX_TOKENS)
+    return FTB_E_LIMIT;
+  if ((c % 4) || (x_ld % 4) || (out_ld % 4)) return FTB_E_ALIGN;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15u) return FTB_E_ALIGN;
+  if (c > 128 * LR_MAX_GROUPS || c > x_ld || c > out_ld || M > out_stride || T > x_stride) return FTB_E_SHAPE;
+  CurrentDevice scope(h->device);
+  if (scope.err != cudaSuccess) return static_cast<int>(scope.err);
+  int32_t* scratch = nullptr;
+  const int rc = lr_static_scratch(h->device, &scratch);
+  if (rc) return rc;
+  int32_t* cum = scratch;                                                  // [batch*T]
+  int32_t* lens = scratch + FTB_LR_STATIC_MAX_TOKENS;                       // [batch]
+  int32_t* meta = scratch + FTB_LR_STATIC_MAX_TOKENS + FTB_LR_STATIC_MAX_BATCH;   // [4], must start at zero
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t ce = cudaMemsetAsync(meta, 0, 4 * sizeof(int32_t), st);
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  lr_scan_kernel<<<batch, SCAN_THREADS, 0, st>>>(dur, batch, T, apply_fallback, cum, lens, meta);
+  const long long n = static_cast<long long>(batch) * T;
+  int blocks = static_cast<int>((n + 255) / 256);
+  if (blocks > 1184) blocks = 1184;
+  lr_finalize_kernel<<<blocks, 256, 0, st>>>(dur, n, meta);
+  h->launches += 2;
+  if (M > 0) {
+    GatherArgs g{};
+    g.a.x = x; g.a.x_stride = x_stride; g.a.x_ld = x_ld; g.a.c1 = c;
+    g.a.cum = cum; g.a.lens = lens; g.a.batch = batch; g.a.T = T; g.a.M = M;
+    g.a.out = out; g.a.out_stride = out_stride; g.a.out_ld = out_ld; g.a.idx = idx; g.a.round_tf32 = 0;
+    long long tb = (n + 7) / 8;
+    const long long cap = 4ll * h->num_sms;
+    if (tb > cap) tb = cap;
+    const int token_blocks = static_cast<int>(tb);
+    lr_gather_kernel<<<token_blocks + batch, 256, 0, st>>>(g, token_blocks);
+    h->launches += 1;
+  }
+  ce = cudaGetLastError();
+  if (ce != cudaSuccess) return static_cast<int>(ce);
+  if (lens_out) {
+    ce = cudaMemcpyAsync(lens_out, lens, sizeof(int32_t) * batch, cudaMemcpyDeviceToDevice, st);
+    if (ce != cudaSuccess) return static_cast<int>(ce);
+  }
+  if (meta_out) {
+    ce = cudaMemcpyAsync(meta_out, meta, sizeof(int32_t) * 4, cudaMemcpyDeviceToDevice, st);
+    if (ce != cudaSuccess) return static_cast<int>(ce);
+  }
+  return 0;
 }

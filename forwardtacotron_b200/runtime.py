@@ -69,7 +69,7 @@ class LrGatherArgs(C.Structure):
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
            'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy', 'ftb_gemm_plan_info',
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
-           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
+           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
            'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha']
 
@@ -102,6 +102,8 @@ def load_library() -> C.CDLL:
     lib.ftb_rnn_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_lr_scan.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_lr_gather.argtypes = [_fp, C.POINTER(LrGatherArgs), _fp]
+    lib.ftb_lr_regulate_static.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_embed.argtypes = [_fp, _fp, _fp, C.c_int, _fp, _fp, C.c_int, _fp, C.c_int,
                               C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, _fp]
     lib.ftb_rowdot.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_float,
@@ -215,6 +217,14 @@ class Handle:
 
     def lr_gather(self, args: LrGatherArgs):
         self._timed('lr_gather', lambda: self.check(self.lib.ftb_lr_gather(self.h, C.byref(args), self.stream())))
+
+    def lr_regulate_static(self, x, x_stride, c, dur, batch, T, apply_fallback, M, out, out_stride,
+                           idx=None, lens_out=None, meta_out=None):
+        """Scan + gather with the intermediates in the library's static device scratch: no allocation on the call
+        path (include/ftb200.h: ftb_lr_regulate_static).  x [.., x_ld] / out [.., out_ld] are 2-D row views."""
+        self.check(self.lib.ftb_lr_regulate_static(
+            self.h, ptr(x), x_stride, x.shape[-1], c, ptr(dur), batch, T, int(apply_fallback), M,
+            ptr(out), out_stride, out.shape[-1], ptr(idx), ptr(lens_out), ptr(meta_out), self.stream()))
 
     def embed(self, tok, table, out, out_ld, batch, T, stride, tok2=None, table2=None, extra=None, round_tf32=True):
         e1 = table.shape[1]

@@ -38,6 +38,7 @@ extern "C" {
 #define FTB_E_PLAN     (-4)   /* unknown plan id                                         */
 #define FTB_E_DRIVER   (-5)   /* cuTensorMapEncodeTiled unavailable (no driver)          */
 #define FTB_E_RESIDENT (-6)   /* persistent recurrence grid does not fit on the device   */
+#define FTB_E_LIMIT    (-7)   /* size beyond the fixed capacity of a no-allocation entry  */
 
 typedef struct ftb_context* ftb_handle;
 
@@ -198,6 +199,31 @@ typedef struct {
   int32_t round_tf32;                             /* 0 as computed, 1 tf32-rounded, 2 = `out` is fp16 (out_ld in halves) */
 } ftb_lr_gather_args;
 int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void* stream);
+
+/* No-allocation LengthRegulator: ftb_lr_scan + ftb_lr_gather (fp32 output, no projection / speaker tail) as ONE call
+ * whose intermediates (cum, lens, meta) live in a file-scope `static __device__` array of the library instead of
+ * caller-allocated scratch tensors.
+ *
+ * This entry point has NO counterpart in the reference: it was added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  It calls no cudaMalloc / cudaFree / allocating library routine; the caller passes inputs and outputs only.
+ *   - capacity: batch <= FTB_LR_STATIC_MAX_BATCH and batch*T <= FTB_LR_STATIC_MAX_TOKENS, else FTB_E_LIMIT;
+ *     every GPU that loads the library holds FTB_LR_STATIC_BYTES of device memory for the array until exit;
+ *   - the array is shared by all calls on a device and keeps the last call's contents (meta is re-zeroed per call,
+ *     cum / lens are overwritten for the [batch, T] in use): calls that OVERLAP on the GPU (different streams without
+ *     ordering) race -- serialise them;
+ *   - the first call on a device resolves the array's device address (cudaGetSymbolAddress); make it outside capture.
+ * Semantics = ftb_lr_scan(dur in place, fallback) followed by ftb_lr_gather(round_tf32 = 0): out[b*out_stride + m, :c]
+ * = x[b*x_stride + idx, :c] for m < min(lens[b], M), rows m in [lens[b], M) = 0.0; M is the caller's frame capacity
+ * per sentence (frames beyond it are dropped).  idx [batch, M], lens_out [batch], meta_out [4] are optional outputs
+ * (meta as in ftb_lr_scan: max len, fallback flag, total frames).                                                 */
+#define FTB_LR_STATIC_MAX_TOKENS 65536
+#define FTB_LR_STATIC_MAX_BATCH  1024
+#define FTB_LR_STATIC_BYTES      (4 * (FTB_LR_STATIC_MAX_TOKENS + FTB_LR_STATIC_MAX_BATCH + 64))   /* 266 496 */
+int ftb_lr_regulate_static(ftb_handle h, const float* x, int x_stride /*rows per sentence*/, int x_ld, int c,
+                           float* dur, int batch, int T, int apply_fallback, int M,
+                           float* out, int out_stride /*rows per sentence*/, int out_ld,
+                           int32_t* idx, int32_t* lens_out, int32_t* meta_out, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Small glue kernels
