@@ -8,7 +8,28 @@
 #include "ftb_internal.h"
 #include "ftb_ptx.cuh"
 
+#include <cuda_fp16.h>
+
 namespace ftb {
+
+// round mode 3 of K7/K8: `out` is an fp16 array of THREE column blocks of width e (row stride 3e halves), [hi | lo | hi]
+// with hi = fp16(v), lo = fp16(v - hi): the split-precision GEMM operand (include/ftb200.h, FTB_F_OUT_SPLIT).
+__device__ __forceinline__ void store_split1(float* out, long long row_off3, int e, int c, float v) {
+  __half* o = reinterpret_cast<__half*>(out) + row_off3 + c;
+  const __half hi = __float2half_rn(v);
+  o[0] = hi; o[e] = __float2half_rn(v - __half2float(hi)); o[2 * e] = hi;
+}
+__device__ __forceinline__ void store_split4(float* out, long long row_off3, int e, int c, float4 v) {
+  __half* o = reinterpret_cast<__half*>(out) + row_off3 + c;
+  const __half2 h0 = __floats2half2_rn(v.x, v.y), h1 = __floats2half2_rn(v.z, v.w);
+  const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+  const __half2 l0 = __floats2half2_rn(v.x - f0.x, v.y - f0.y), l1 = __floats2half2_rn(v.z - f1.x, v.w - f1.y);
+  const uint2 ph = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+  const uint2 pl = make_uint2(*reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1));
+  *reinterpret_cast<uint2*>(o) = ph;
+  *reinterpret_cast<uint2*>(o + e) = pl;
+  *reinterpret_cast<uint2*>(o + 2 * e) = ph;
+}
 
 // ---------------------------------------------------------------- residual + LayerNorm
 // One warp per row; e <= 1024 -> up to 32 values per lane held in registers.
@@ -59,7 +80,8 @@ add_layernorm_kernel(const float* __restrict__ x, const float* __restrict__ res,
   for (int i = 0; i < 32; ++i) {
     const int c = lane + i * 32;
     if (i < per && c < e) {
-      out[off + c] = round ? round_tf32(v[i]) : v[i];
+      if (round == 3) store_split1(out, (static_cast<long long>(b) * seq_stride + t) * 3 * e, e, c, v[i]);
+      else out[off + c] = round ? round_tf32(v[i]) : v[i];
       if (out_full) out_full[off + c] = v[i];
     }
   }
@@ -80,7 +102,8 @@ posenc_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, 
   const float* per = pe + static_cast<long long>(t) * e;
   for (int c = lane; c < e; c += 32) {
     const float v = src[c] + sc * per[c];
-    out[off + c] = round ? round_tf32(v) : v;
+    if (round == 3) store_split1(out, off * 3, e, c, v);
+    else out[off + c] = round ? round_tf32(v) : v;
     if (out_full) out_full[off + c] = v;
   }
 }
@@ -347,6 +370,7 @@ mha_tiled_kernel(const float* __restrict__ qkv, int e, const int64_t* __restrict
         if ((D4 % 16) != 0 && tx + 16 * h >= D4) continue;
         float4 v = make_float4(oacc[i][4 * h] * inv, oacc[i][4 * h + 1] * inv, oacc[i][4 * h + 2] * inv,
                                oacc[i][4 * h + 3] * inv);
+        if (round == 3) { store_split4(out, (rowbase + t) * 3 * e, e, head * D + 4 * tx + 64 * h, v); continue; }
         if (round) { v.x = round_tf32(v.x); v.y = round_tf32(v.y); v.z = round_tf32(v.z); v.w = round_tf32(v.w); }
         *reinterpret_cast<float4*>(out + (rowbase + t) * e + head * D + 4 * tx + 64 * h) = v;
       }
@@ -369,6 +393,7 @@ extern "C" int ftb_add_layernorm(ftb_handle h, const float* x, const float* res,
                                  int seq_stride, float* out, float* out_full, int round_tf32, void* stream) {
   if (!h || !x || !gamma || !beta || !out || e < 1 || e > 1024 || e > ld || batch < 1 || seq_len < 1)
     return FTB_E_ARG;
+  if (round_tf32 == 3 && (e % 8)) return FTB_E_SHAPE;
   const long long rows = static_cast<long long>(batch) * seq_len;
   add_layernorm_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       x, res, ld, e, gamma, beta, gamma2, beta2, batch, seq_len, seq_stride, out, out_full, round_tf32);
@@ -381,6 +406,7 @@ extern "C" int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, 
                           float* out_full, int round_tf32, void* stream) {
   if (!h || !pe || !scale_ptr || !out || e < 1 || batch < 1 || seq_len < 1) return FTB_E_ARG;
   if (tok ? !table : !x_in) return FTB_E_ARG;
+  if (round_tf32 == 3 && (e % 8)) return FTB_E_SHAPE;
   const long long rows = static_cast<long long>(batch) * seq_len;
   posenc_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       tok, table, x_in, pe, scale_ptr, e, batch, seq_len, seq_stride, out, out_full, round_tf32);
@@ -392,11 +418,12 @@ extern "C" int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const i
                        int seq_len, int seq_stride, float* out, int round_tf32, void* stream) {
   if (!h || !qkv || !out || heads < 1 || batch < 1 || seq_len < 1 || e % heads) return FTB_E_ARG;
   const int d = e / heads;
+  if (round_tf32 == 3 && (e % 8)) return FTB_E_SHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   static const bool legacy = [] { const char* v = getenv("FTB_MHA_IMPL"); return v && strcmp(v, "legacy") == 0; }();
   if ((e % 4) != 0 || (reinterpret_cast<uintptr_t>(qkv) & 15u) || (reinterpret_cast<uintptr_t>(out) & 15u))
     return FTB_E_ALIGN;
-  if (legacy) {                                     // first-build kernel, kept for A/B measurements
+  if (legacy && round_tf32 != 3) {                  // first-build kernel, kept for A/B measurements
     const int qt = d > 64 ? 16 : 32;
     dim3 grid((seq_len + qt - 1) / qt, heads, batch);
     if (d == 64) mha_kernel<64><<<grid, 256, 0, st>>>(qkv, e, key_tok, seq_len, seq_stride, out, round_tf32);

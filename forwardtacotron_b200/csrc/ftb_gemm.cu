@@ -134,15 +134,16 @@ struct EpiCtx {
   const float* residual;
   float* out; float* out_full; float* out_t;    // out / out_full already offset by out_col0
   __half* out16;                                // FTB_F_OUT_F16: the fp16 output (offset by out_col0), `out` is null
+  bool split;                                   // FTB_F_OUT_SPLIT: out16 receives [hi | lo | hi] column blocks of width N
 };
 
-template <bool POOL, bool RES, bool FULL, bool OUTT, bool RND, bool OUT16 = false>
+template <bool POOL, bool RES, bool FULL, bool OUTT, bool RND, bool OUT16 = false, bool SPLIT = false>
 __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
   const int lane = c.lane, sub = lane >> 3, part = lane & 7;
   // phase-B base pointers: row (r_warp + sub), column n0 + 4*part; +32 columns per chunk, +4 rows per i8
   const long long orow = (c.r_warp + sub) * c.out_ld + c.n0 + 4 * part;
   // fp16 output next to a residual / unrounded twin / transposed output: phase-B layout, 8-byte stores of 4 halves
-  constexpr bool O16_FAST = OUT16 && !RES && !FULL && !OUTT;
+  constexpr bool O16_FAST = OUT16 && !RES && !FULL && !OUTT && !SPLIT;
   float* optr = c.out ? c.out + orow : nullptr;
   __half* hptr = (OUT16 && !O16_FAST) ? c.out16 + orow : nullptr;
   float* fptr = FULL ? c.out_full + orow : nullptr;
@@ -288,6 +289,16 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
                 uint2 pk;
                 pk.x = *reinterpret_cast<const uint32_t*>(&lo); pk.y = *reinterpret_cast<const uint32_t*>(&hi);
                 *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0) = pk;
+                if (SPLIT) {
+                  // FTB_F_OUT_SPLIT: [hi | lo | hi] column blocks of width N -- the K-concatenated operand of a
+                  // split-precision consumer (weights packed as [W_hi | W_hi | W_lo]): hi*W_hi + lo*W_hi + hi*W_lo
+                  const float2 f0 = __half22float2(lo), f1 = __half22float2(hi);
+                  const __half2 r0 = __floats2half2_rn(y.x - f0.x, y.y - f0.y), r1 = __floats2half2_rn(y.z - f1.x, y.w - f1.y);
+                  uint2 pr;
+                  pr.x = *reinterpret_cast<const uint32_t*>(&r0); pr.y = *reinterpret_cast<const uint32_t*>(&r1);
+                  *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0 + c.N) = pr;
+                  *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0 + 2 * c.N) = pk;
+                }
               } else {
                 if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
                 *reinterpret_cast<float4*>(optr + i8 * ostep + c0) = y;
@@ -322,6 +333,7 @@ __device__ __forceinline__ void epi_disp_full(const EpiCtx& c, bool full, bool o
 }
 __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool res, bool full, bool outt, bool rnd) {
   if (c.out16) {                                                  // fp16 operand copy as `out`
+    if (c.split) { epi_affine_tile<false, false, false, false, false, true, true>(c); return; }
     if (pool) epi_affine_tile<true, false, false, false, false, true>(c);        // CBHG bank: never residual / twin
     else if (outt) {
       if (full) epi_affine_tile<false, false, true, true, false, true>(c);
@@ -646,6 +658,7 @@ __device__ __forceinline__ void conv_gemm_tc_body(const GemmProblemDev* __restri
         c.out16 = out16 ? reinterpret_cast<__half*>(P_out) + P_out_col0 : nullptr;
         c.out_full = P_out_full ? P_out_full + P_out_col0 : nullptr;
         c.out_t = P_out_t;
+        c.split = (P_flags & FTB_F_OUT_SPLIT) != 0;
         epi_dispatch(c, pool, P_residual != nullptr && P_out_t == nullptr, P_out_full != nullptr, P_out_t != nullptr, rnd);
       }
       tc_fence_before();
@@ -731,7 +744,11 @@ __global__ void conv_gemm_simt_kernel(const GemmProblemDev* __restrict__ probs, 
       if (p->out_t) p->out_t[(static_cast<long long>(b) * N + n) * p->seq_len + t] = v;
     }
     if (p->out_full) p->out_full[r * p->out_ld + p->out_col0 + n] = v;
-    if (p->out && (p->flags & FTB_F_OUT_F16))
+    if (p->out && (p->flags & FTB_F_OUT_SPLIT)) {
+      __half* o = reinterpret_cast<__half*>(p->out) + r * p->out_ld + p->out_col0 + n;
+      const __half hi = __float2half_rn(v);
+      o[0] = hi; o[p->n] = __float2half_rn(v - __half2float(hi)); o[2 * p->n] = hi;
+    } else if (p->out && (p->flags & FTB_F_OUT_F16))
       reinterpret_cast<__half*>(p->out)[r * p->out_ld + p->out_col0 + n] = __float2half_rn(v);
     else if (p->out) p->out[r * p->out_ld + p->out_col0 + n] = epi_finish(p, v);
   }
@@ -811,6 +828,10 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     if (q.out && (!aligned16(q.out) || (q.out_ld % omul) != 0 || (q.out_col0 % omul) != 0)) return FTB_E_ALIGN;
     if (q.out && (q.n % omul) != 0) return FTB_E_SHAPE;       // row segments are stored as 16-byte vectors
     if (o16 && (!q.out || (q.epilogue == FTB_EPI_MAXPOOL && (q.residual || q.out_t || q.out_full)))) return FTB_E_ARG;
+    if (q.flags & FTB_F_OUT_SPLIT) {
+      if (!o16 || q.epilogue != FTB_EPI_AFFINE || q.residual || q.out_t || q.out_full) return FTB_E_ARG;
+      if (q.out_ld < q.out_col0 + 3 * q.n || (q.n % 8) != 0) return FTB_E_SHAPE;
+    }
     if (q.residual && ((q.res_ld % 4) != 0 || !aligned16(q.residual))) return FTB_E_ALIGN;
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
     if (q.rows != static_cast<long long>(q.batch) * q.seq_stride) return FTB_E_ARG;

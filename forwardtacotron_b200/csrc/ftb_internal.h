@@ -66,6 +66,7 @@ struct RnnProblemDev {
   float pad_value;       // value of out[b, t >= lens[b]]
   int out_f16;           // `out` holds fp16 (the operand copy of a following FTB_F_A_F16 problem)
   int x_f16;             // `xproj` holds fp16 (written by a FTB_F_OUT_F16 problem)
+  int precise;           // split-precision recurrent product + exact gates (cluster hand-off; ftb_rnn_problem.precise)
   int cell, hidden, batch, seq_len, seq_stride, out_ld, out_col0;
   int gates;             // 3 or 4
   int units_per_cta;     // hidden units owned by one CTA

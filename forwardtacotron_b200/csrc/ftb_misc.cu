@@ -9,10 +9,20 @@
 namespace ftb {
 
 // mode: 0 = fp32 as stored, 1 = fp32 rounded to tf32, 2 = fp16 (out is a __half array, out_ld in halves): the operand
-// copy of a buffer a FTB_F_A_F16 GEMM problem reads.
-__device__ __forceinline__ void embed_store(float* out, long long i, float v, int mode) {
-  if (mode == 2) reinterpret_cast<__half*>(out)[i] = __float2half_rn(v);
-  else out[i] = mode ? round_tf32(v) : v;
+// copy of a buffer a FTB_F_A_F16 GEMM problem reads; 3 = split fp16 (out_ld = 3*seg halves): hi = fp16(v) at column c,
+// lo = fp16(v - hi) at seg + c, hi again at 2*seg + c -- the operand of a split-precision (FTB_F_OUT_SPLIT) consumer.
+__device__ __forceinline__ void embed_store(float* out, long long i, float v, int mode, int seg) {
+  if (mode == 3) {
+    __half* o = reinterpret_cast<__half*>(out);
+    const __half hi = __float2half_rn(v);
+    o[i] = hi;
+    o[i + seg] = __float2half_rn(v - __half2float(hi));
+    o[i + 2 * seg] = hi;
+  } else if (mode == 2) {
+    reinterpret_cast<__half*>(out)[i] = __float2half_rn(v);
+  } else {
+    out[i] = mode ? round_tf32(v) : v;
+  }
 }
 
 __device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
@@ -25,7 +35,8 @@ __device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, cons
   const int b = row / T, t = row - b * T;
   const long long o = (static_cast<long long>(b) * seq_stride + t) * out_ld;
   const float* s1 = table + tok[row] * e1;
-  if (e2 == 0 && e3 == 0 && (e1 & 3) == 0 && (out_ld & 3) == 0 &&
+  const int seg = out_ld / 3;
+  if (mode != 3 && e2 == 0 && e3 == 0 && (e1 & 3) == 0 && (out_ld & 3) == 0 &&
       ((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0) {
     // the common case (one table, width a multiple of 4): 16-byte reads, 16- / 8-byte stores
     for (int c = lane * 4; c < e1; c += 128) {
@@ -42,14 +53,14 @@ __device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, cons
     }
     return;
   }
-  for (int c = lane; c < e1; c += 32) embed_store(out, o + c, s1[c], mode);
+  for (int c = lane; c < e1; c += 32) embed_store(out, o + c, s1[c], mode, seg);
   if (e2 > 0) {
     const float* s2 = table2 + tok2[row] * e2;
-    for (int c = lane; c < e2; c += 32) embed_store(out, o + e1 + c, s2[c], mode);
+    for (int c = lane; c < e2; c += 32) embed_store(out, o + e1 + c, s2[c], mode, seg);
   }
   if (e3 > 0) {
     const float* s3 = extra + static_cast<long long>(b) * e3;
-    for (int c = lane; c < e3; c += 32) embed_store(out, o + e1 + e2 + c, s3[c], mode);
+    for (int c = lane; c < e3; c += 32) embed_store(out, o + e1 + e2 + c, s3[c], mode, seg);
   }
 }
 
@@ -145,7 +156,8 @@ extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, i
   if (!h || !tok || !table || !out || e1 < 1 || batch < 1 || T < 1) return FTB_E_ARG;
   if (e2 > 0 && (!tok2 || !table2)) return FTB_E_ARG;
   if (e3 > 0 && !extra) return FTB_E_ARG;
-  if (e1 + e2 + e3 > out_ld || seq_stride < T || round_tf32 < 0 || round_tf32 > 2) return FTB_E_ARG;
+  if (seq_stride < T || round_tf32 < 0 || round_tf32 > 3) return FTB_E_ARG;
+  if (e1 + e2 + e3 > (round_tf32 == 3 ? out_ld / 3 : out_ld) || (round_tf32 == 3 && out_ld % 3)) return FTB_E_ARG;
   const long long rows = static_cast<long long>(batch) * T;
   if (rows > 0x7fffffffll) return FTB_E_ARG;
   embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
@@ -163,7 +175,8 @@ extern "C" int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int ni
     if (!q.tok || !q.table || !q.out || q.e1 < 1) return FTB_E_ARG;
     if (q.e2 > 0 && (!q.tok2 || !q.table2)) return FTB_E_ARG;
     if (q.e3 > 0 && !q.extra) return FTB_E_ARG;
-    if (q.e1 + q.e2 + q.e3 > q.out_ld || q.round_tf32 < 0 || q.round_tf32 > 2) return FTB_E_ARG;
+    if (q.round_tf32 < 0 || q.round_tf32 > 3) return FTB_E_ARG;
+    if (q.e1 + q.e2 + q.e3 > (q.round_tf32 == 3 ? q.out_ld / 3 : q.out_ld) || (q.round_tf32 == 3 && q.out_ld % 3)) return FTB_E_ARG;
     args.item[i] = q;
   }
   const long long rows = static_cast<long long>(batch) * T;

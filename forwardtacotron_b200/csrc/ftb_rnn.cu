@@ -102,6 +102,9 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // exp/rcp at ~2 ulp: absolute gate error ~3e-7, far below the operand rounding of the h @ W_hh products
 __device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// ex2 / rcp forms (~2 ulp): the gates of the PRECISE recurrences (duration predictors) and of -DFTB_RNN_EXACT_GATES builds
+__device__ __forceinline__ float sigm_x(float x) { return rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float tanh_x(float x) { return fmaf(2.0f, rcp_ftz(1.0f + ex2_ftz(-2.8853900817779268f * x)), -1.0f); }
 #ifndef FTB_RNN_EXACT_GATES
 // One MUFU.TANH per gate (tanh.approx.f32, max relative error 2^-11 -- the precision h_t is rounded to anyway when it
 // is handed to the next step as an fp16 MMA operand) instead of ex2 + rcp: a shorter dependent chain in the gate phase.
@@ -136,7 +139,13 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
-template <int G, int H, bool CL = false>
+// PR (precise; cluster hand-off only): split-fp16 recurrent product.  h_t = hi + lo/2048 with hi = fp16(h_t),
+// lo = fp16(2048 (h_t - hi)), W_hh likewise; the step computes W_hi hi + (W_lo hi + W_hi lo)/2048 in two fp32 accumulator
+// sets (three MMAs per k-step instead of one): ~2^-20 relative operand precision instead of 2^-11.  h_t is handed over as
+// two tiles (hi, lo), stored to `out` as the unrounded fp32 value, and the gates use the ex2/rcp forms.  For the DURATION
+// predictors, whose output is rounded to integers (forward_tacotron.py:174-177, common_layers.py:18-21).
+constexpr float RNN_LO_SCALE = 2048.0f;
+template <int G, int H, bool CL = false, bool PR = false>
 struct RnnTiling {
   static constexpr int U = RNN_U, NB = RNN_NB, KS = RNN_KS;
   // L2 hand-off: two independent batch groups of 8 columns (one MMA n-tile each), interleaved to hide the L2 round trip.
@@ -157,20 +166,22 @@ struct RnnTiling {
   static constexpr int SMEM_BYTES = NB * HS * 2 + (NG * KS * NBG * S + RNN_XS * NB * XSTR) * 4;
   // cluster hand-off: h tiles [2 step parities][SL slices][NB columns][32 units] fp16 + 2 mbarriers
   static constexpr int SL = H / U;              // unit slices = CTAs of one (direction, batch group) unit
-  static constexpr int HCL_BYTES = 2 * NG * SL * NBG * U * 2;
-  static constexpr int TXB = SL * NBG * U * 2;  // bytes one (group, step) hand-off delivers to every CTA of the unit
+  static constexpr int HCL_TILE_BYTES = 2 * NG * SL * NBG * U * 2;     // one set of tiles (hi); PR adds the lo set behind it
+  static constexpr int HCL_BYTES = (PR ? 2 : 1) * HCL_TILE_BYTES;
+  static constexpr int TXB = (PR ? 2 : 1) * SL * NBG * U * 2;  // bytes one (group, step) hand-off delivers to every CTA of the unit
   static constexpr int ND = (SL + 7) / 8;       // peers one lane stores to
   static constexpr int SMEM_BYTES_CL = HCL_BYTES + (NG * KS * NBG * S + RNN_XS * NB * XSTR) * 4 + 2 * NG * 8;
   static_assert(RC % 16 == 0 && KW % 32 == 0 && WARPS * 32 <= RNN_THREADS, "bad recurrence tiling");
+  static_assert(!PR || CL, "the precise recurrence exists on the cluster hand-off only");
   static_assert(U * NB == RNN_THREADS && (NB * G * U / 4) <= RNN_THREADS, "one (unit, batch) pair / x chunk per thread");
 };
 
 // CL = false: h handed between CTAs through L2 (in-band sentinel polling; cooperative launch).
 // CL = true : the SL CTAs of one (direction, batch group) unit sit in one thread-block cluster and push h_t
 //             straight into each other's shared memory (st.async + mbarrier complete_tx); see the header.
-template <int G, int H, bool CL>
+template <int G, int H, bool CL, bool PR = false>
 __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* smem) {
-  using T = RnnTiling<G, H, CL>;
+  using T = RnnTiling<G, H, CL, PR>;
   constexpr int U = T::U, NB = T::NB, KS = T::KS, WARPS = T::WARPS, KW = T::KW, KB = T::KB, NBG = T::NBG;
   constexpr int S = T::S, HS = T::HS, XSTR = T::XSTR, GS = T::GS, ITEMS = T::ITEMS, IPT = T::IPT;
   constexpr int NG = T::NG, SL = T::SL, ND = T::ND;
@@ -204,6 +215,10 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   const int q = lane & 3, fr = lane >> 2;
   const bool mma_warp = warp < WARPS;
   uint32_t wfrag[KB * 2][4];
+  uint32_t wfrag_lo[PR ? KB * 2 : 1][4];              // PR: fp16(2048 (w - fp16(w)))
+  auto pack_lo2 = [](float a, float b) {
+    return pack_half2((a - __half2float(__float2half_rn(a))) * RNN_LO_SCALE, (b - __half2float(__float2half_rn(b))) * RNN_LO_SCALE);
+  };
   if (mma_warp) {
     const int lr_lo = rs * 16 + fr, lr_hi = lr_lo + 8;
     const float* w_lo = whh + static_cast<size_t>((lr_lo / U) * H + u0 + (lr_lo % U)) * H;
@@ -217,6 +232,12 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         wfrag[kb * 2 + s][1] = pack_half2(w_hi[k], w_hi[k + 1]);
         wfrag[kb * 2 + s][2] = pack_half2(w_lo[k + 2], w_lo[k + 3]);
         wfrag[kb * 2 + s][3] = pack_half2(w_hi[k + 2], w_hi[k + 3]);
+        if (PR) {
+          wfrag_lo[kb * 2 + s][0] = pack_lo2(w_lo[k], w_lo[k + 1]);
+          wfrag_lo[kb * 2 + s][1] = pack_lo2(w_hi[k], w_hi[k + 1]);
+          wfrag_lo[kb * 2 + s][2] = pack_lo2(w_lo[k + 2], w_lo[k + 3]);
+          wfrag_lo[kb * 2 + s][3] = pack_lo2(w_hi[k + 2], w_hi[k + 3]);
+        }
       }
     }
   }
@@ -323,6 +344,13 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+      float acs[PR ? 4 : 1][4];              // PR: the two cross terms, scaled by 2048
+      if (PR) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acs[PR ? i : 0][j] = 0.0f;
+      }
       const __half* hrow = h_s + (par * SL + kq * KB) * TILE + fr * U + 8 * q;
 #pragma unroll
       for (int kb = 0; kb < KB; ++kb) {
@@ -332,6 +360,24 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         mma_f16_16x8x16(acc[2], wfrag[kb * 2 + 0], h1.x, h1.y);
         mma_f16_16x8x16(acc[1], wfrag[kb * 2 + 1], h0.z, h0.w);
         mma_f16_16x8x16(acc[3], wfrag[kb * 2 + 1], h1.z, h1.w);
+        if (PR) {
+          const uint4 l0 = *reinterpret_cast<const uint4*>(hrow + kb * TILE + T::HCL_TILE_BYTES / 2);
+          const uint4 l1 = *reinterpret_cast<const uint4*>(hrow + kb * TILE + 8 * U + T::HCL_TILE_BYTES / 2);
+          mma_f16_16x8x16(acs[0], wfrag_lo[PR ? kb * 2 + 0 : 0], h0.x, h0.y);      // W_lo * h_hi
+          mma_f16_16x8x16(acs[PR ? 2 : 0], wfrag_lo[PR ? kb * 2 + 0 : 0], h1.x, h1.y);
+          mma_f16_16x8x16(acs[PR ? 1 : 0], wfrag_lo[PR ? kb * 2 + 1 : 0], h0.z, h0.w);
+          mma_f16_16x8x16(acs[PR ? 3 : 0], wfrag_lo[PR ? kb * 2 + 1 : 0], h1.z, h1.w);
+          mma_f16_16x8x16(acs[0], wfrag[kb * 2 + 0], l0.x, l0.y);                  // W_hi * h_lo
+          mma_f16_16x8x16(acs[PR ? 2 : 0], wfrag[kb * 2 + 0], l1.x, l1.y);
+          mma_f16_16x8x16(acs[PR ? 1 : 0], wfrag[kb * 2 + 1], l0.z, l0.w);
+          mma_f16_16x8x16(acs[PR ? 3 : 0], wfrag[kb * 2 + 1], l1.z, l1.w);
+        }
+      }
+      if (PR) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(acs[PR ? i : 0][j], 1.0f / RNN_LO_SCALE, acc[i][j]);
       }
       float* pk = p_s + static_cast<size_t>(kq) * NB * S;
       const int col = 2 * q, row = rs * 16 + fr;
@@ -394,9 +440,9 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   const int len_b = (p.lens && pv) ? min(p.lens[b0 + pb], L) : L;
   const float pad_value = p.pad_value;
   char* out_p = reinterpret_cast<char*>(p.out) + (out_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.out_ld) * osz;
-  auto store_out = [&](bool dead, __half h16) {
+  auto store_out = [&](bool dead, __half h16, float hfull) {
     if (o16) *reinterpret_cast<__half*>(out_p) = dead ? __float2half_rn(pad_value) : h16;
-    else *reinterpret_cast<float*>(out_p) = dead ? pad_value : __half2float(h16);
+    else *reinterpret_cast<float*>(out_p) = dead ? pad_value : (PR ? hfull : __half2float(h16));
   };
   __half* hx_p = hx_pair + static_cast<size_t>(dir ? L - 1 : 0) * p.batch * H;
   const float* pw = p_s + static_cast<size_t>(pg * KS) * NBG * S + pbl * S + pu;
@@ -429,16 +475,16 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
         hh[g] = s;
       }
       if (G == 4) {
-        const float ig = sigm(xs[0] + hh[0]);
-        const float fg = sigm(xs[1] + hh[1]);
-        const float gg = tanh_fast(xs[2] + hh[2]);
-        const float og = sigm(xs[G - 1] + hh[G - 1]);
+        const float ig = PR ? sigm_x(xs[0] + hh[0]) : sigm(xs[0] + hh[0]);
+        const float fg = PR ? sigm_x(xs[1] + hh[1]) : sigm(xs[1] + hh[1]);
+        const float gg = PR ? tanh_x(xs[2] + hh[2]) : tanh_fast(xs[2] + hh[2]);
+        const float og = PR ? sigm_x(xs[G - 1] + hh[G - 1]) : sigm(xs[G - 1] + hh[G - 1]);
         c_state = fg * c_state + ig * gg;
-        hnew = og * tanh_fast(c_state);
+        hnew = og * (PR ? tanh_x(c_state) : tanh_fast(c_state));
       } else {
-        const float r = sigm(xs[0] + hh[0]);
-        const float z = sigm(xs[1] + hh[1]);
-        const float n = tanh_fast(xs[2] + r * hh[2]);
+        const float r = PR ? sigm_x(xs[0] + hh[0]) : sigm(xs[0] + hh[0]);
+        const float z = PR ? sigm_x(xs[1] + hh[1]) : sigm(xs[1] + hh[1]);
+        const float n = PR ? tanh_x(xs[2] + r * hh[2]) : tanh_fast(xs[2] + r * hh[2]);
         hnew = (1.0f - z) * n + z * h_state;
       }
       const bool live = (dir ? (L - 1 - step) : step) < len_b;
@@ -458,21 +504,34 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
       const unsigned d0 = (lane & 2) ? o2 : w, d1 = (lane & 2) ? w : o2;
       const unsigned e0 = __shfl_xor_sync(0xffffffffu, d0, 4), e1 = __shfl_xor_sync(0xffffffffu, d1, 4);
       const uint4 v = (lane & 4) ? make_uint4(e0, e1, d0, d1) : make_uint4(d0, d1, e0, e1);
+      uint4 vl = make_uint4(0u, 0u, 0u, 0u);
+      if (PR) {                              // the same gather for the lo halves fp16(2048 (h - hi))
+        const unsigned ml = __half_as_ushort(__float2half_rn((hnew - __half2float(h16)) * RNN_LO_SCALE));
+        const unsigned p1 = __shfl_xor_sync(0xffffffffu, ml, 1);
+        const unsigned wl = (lane & 1) ? (p1 | (ml << 16)) : (ml | (p1 << 16));
+        const unsigned p2 = __shfl_xor_sync(0xffffffffu, wl, 2);
+        const unsigned f0 = (lane & 2) ? p2 : wl, f1 = (lane & 2) ? wl : p2;
+        const unsigned g0 = __shfl_xor_sync(0xffffffffu, f0, 4), g1 = __shfl_xor_sync(0xffffffffu, f1, 4);
+        vl = (lane & 4) ? make_uint4(g0, g1, f0, f1) : make_uint4(f0, f1, g0, g1);
+      }
       FTB_TICK(5)
       if (step + 1 < L) {
         const uint32_t poff = (step & 1) * (NG * SL * TILE * 2), boff = (step & 1) * (NG * 8);
 #pragma unroll
         for (int d = 0; d < ND; ++d)
-          if (rvalid & (1u << d)) st_async_v4(rdata[d] + poff, v, rbar[d] + boff);
+          if (rvalid & (1u << d)) {
+            st_async_v4(rdata[d] + poff, v, rbar[d] + boff);
+            if (PR) st_async_v4(rdata[d] + poff + T::HCL_TILE_BYTES, vl, rbar[d] + boff);
+          }
       }
-      if (pv) store_out(dead, h16);
+      if (pv) store_out(dead, h16, hnew);
       FTB_TICK(6)
     } else {
       // publish: fp16 pair (even lane stores its own + the odd neighbour's half) and the fp32 layer output
       const unsigned other = __shfl_down_sync(0xffffffffu, mine, 1);
       if (pv) {
         if ((lane & 1) == 0) st_relaxed_u32(hx_p, mine | (other << 16));
-        store_out(dead, h16);
+        store_out(dead, h16, hnew);
       }
       hx_p += h_step;
     }
@@ -564,6 +623,13 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
 
 template <bool CL>
 __device__ __forceinline__ void rnn_dispatch(const RnnProblemDev& p, int local, unsigned char* smem) {
+  if constexpr (CL) {
+    if (p.precise) {                       // GRU only (rnn_plan_build): the duration predictors
+      if (p.hidden == 128) rnn_cta<3, 128, true, true>(p, local, smem);
+      else rnn_cta<3, 64, true, true>(p, local, smem);
+      return;
+    }
+  }
   if (p.cell == FTB_CELL_LSTM) {
     if (p.hidden == 512) rnn_cta<4, 512, CL>(p, local, smem);
     else if (p.hidden == 256) rnn_cta<4, 256, CL>(p, local, smem);
@@ -605,8 +671,14 @@ rnn_cluster_kernel(const RnnProblemDev* __restrict__ probs, int nprob) {
   cluster_sync_all();                      // no CTA leaves while a peer may still store into its shared memory
 }
 
-static int rnn_smem_bytes(int cell, int hidden, bool cluster) {
+static int rnn_smem_bytes(int cell, int hidden, bool cluster, bool precise = false) {
   const bool lstm = cell == FTB_CELL_LSTM;
+  if (precise) {
+    switch (hidden) {
+      case 128: return RnnTiling<3, 128, true, true>::SMEM_BYTES_CL;
+      default: return RnnTiling<3, 64, true, true>::SMEM_BYTES_CL;
+    }
+  }
 #define FTB_RNN_SMEM(GG, HH) (cluster ? RnnTiling<GG, HH, true>::SMEM_BYTES_CL : RnnTiling<GG, HH, false>::SMEM_BYTES)
   switch (hidden) {
     case 512: return lstm ? FTB_RNN_SMEM(4, 512) : FTB_RNN_SMEM(3, 512);
@@ -672,6 +744,7 @@ static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& wh
       RnnProblemDev d{};
       d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = nullptr;
       d.lens = q.lens; d.pad_value = q.pad_value; d.out_f16 = q.out_f16; d.x_f16 = q.x_f16;
+      d.precise = (cluster && q.precise) ? 1 : 0;
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
       d.gates = q.cell == FTB_CELL_LSTM ? 4 : 3;
@@ -681,7 +754,7 @@ static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& wh
       d.b_end = (b + take * RNN_NB < q.batch) ? b + take * RNN_NB : q.batch;
       d.cta_base = up(cur.ctas);
       d.ctas = 2 * take * slices;
-      const int sm = rnn_smem_bytes(q.cell, q.hidden, cluster);
+      const int sm = rnn_smem_bytes(q.cell, q.hidden, cluster, cluster && q.precise);
       if (sm > cur.smem) cur.smem = sm;
       d.group_base = ngroups;
       d.problem = i;
@@ -702,6 +775,7 @@ static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& wh
 int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan) {
   if (!problems || nproblems < 1 || nproblems > FTB_MAX_RNN_PROBLEMS) return FTB_E_ARG;
   int max_slices = 0;
+  bool any_precise = false;
   for (int i = 0; i < nproblems; ++i) {
     const ftb_rnn_problem& q = problems[i];
     if (!q.xproj || !q.w_hh || !q.b_hh || !q.out) return FTB_E_ARG;
@@ -710,6 +784,11 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
     if ((q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0 || (reinterpret_cast<uintptr_t>(q.out) & 15u)) return FTB_E_ALIGN;
     if (q.hidden / RNN_U > max_slices) max_slices = q.hidden / RNN_U;
+    if (q.precise) {
+      // split-precision recurrence: GRU, H <= 128, fp32 x-projection and output, cluster hand-off only
+      if (q.cell != FTB_CELL_GRU || q.hidden > 128 || q.x_f16 || q.out_f16) return FTB_E_SHAPE;
+      any_precise = true;
+    }
   }
   // L2 hand-off layout (always possible on a device that holds one batch group)
   std::vector<RnnProblemDev> parts;
@@ -736,7 +815,7 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       for (int i = 0; i < nproblems; ++i) {
         if (problems[i].hidden / RNN_U != cs) continue;
         which.push_back(i);
-        const int sm = rnn_smem_bytes(problems[i].cell, problems[i].hidden, true);
+        const int sm = rnn_smem_bytes(problems[i].cell, problems[i].hidden, true, problems[i].precise != 0);
         if (sm > smem) smem = sm;
       }
       if (which.empty()) continue;
@@ -751,7 +830,7 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       if (claunches.size() - before > depth) depth = claunches.size() - before;
       ++lanes;
     }
-    if (ok && lanes > 0 && (depth <= launches.size() || (mode && strcmp(mode, "cluster") == 0))) {
+    if (ok && lanes > 0 && (depth <= launches.size() || any_precise || (mode && strcmp(mode, "cluster") == 0))) {
       parts.swap(cparts);
       launches.swap(claunches);
       ngroups = cg;
@@ -768,6 +847,7 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       if (lanes > 1 && cudaEventCreateWithFlags(&plan->forked, cudaEventDisableTiming) != cudaSuccess) return FTB_E_ARG;
     }
   }
+  if (!plan->cluster && any_precise) return FTB_E_RESIDENT;      // no silent loss of precision on the L2 path
   if (!plan->cluster) {
     cudaError_t ae = cudaFuncSetAttribute(rnn_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           rnn_smem_bytes(FTB_CELL_LSTM, 512, false));

@@ -12,7 +12,11 @@ from typing import Callable, Dict, List, Optional
 import torch
 
 from . import runtime as rt
-from .pack import PackedGemm, PackedRnn
+from .pack import PackedGemm, PackedRnn, ceil_to
+
+
+def pk_ceil8(n: int) -> int:
+    return ceil_to(n, 8)
 
 
 # fp16 x-projections for the frame-side recurrences (BiLSTM, postnet BiGRU): halves the fp32 `W_ih x` traffic of the two
@@ -21,6 +25,10 @@ from .pack import PackedGemm, PackedRnn
 # 2.58 ms.  The token-side recurrences (predictors, prenet) keep fp32 x-projections.  FTB_X16=0 disables it.
 X16 = os.environ.get('FTB_X16', '1') != '0'
 F16_OPERANDS = _F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
+# Split-precision duration predictor (conv stack + W_ih as [hi | lo | hi] fp16 operands, recurrence with hi/lo h and
+# W_hh, exact gates): raw duration error ~1e-5 instead of ~3e-3, so the rounded durations (common_layers.py:21) match
+# the reference's except within ~1e-4 of a .5 tie.  FTB_PRECISE_DUR=0 restores the single-fp16 path (diagnostic).
+PRECISE_DUR = os.environ.get('FTB_PRECISE_DUR', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -95,19 +103,27 @@ class Program:
     def gemm(self, a: torch.Tensor, w: PackedGemm, out: Optional[torch.Tensor], *, out_col0: int = 0,
              epilogue: int = rt.EPI_AFFINE, round_out: bool = True, residual: Optional[torch.Tensor] = None,
              out_t: Optional[torch.Tensor] = None, cin: Optional[int] = None,
-             out_full: Optional[torch.Tensor] = None):
+             out_full: Optional[torch.Tensor] = None, split_in: bool = False, split_out: bool = False):
+        """split_in: `a` is a [hi | lo | hi] fp16 operand (3 * ceil8(cin) columns) and the weight its w16s form;
+        split_out: `out` (fp16, 3*n columns) receives the result in that layout (FTB_F_OUT_SPLIT)."""
         g = self.geo
         p = rt.GemmProblem()
         p.a, p.rows, p.lda = a.data_ptr(), g.rows, a.shape[1]
-        p.cin = cin if cin is not None else w.cin
-        assert p.cin == w.cin and p.cin <= a.shape[1], (p.cin, w.cin, a.shape)
         a16 = a.dtype == torch.float16
         o16 = out is not None and out.dtype == torch.float16
-        wt = w.w16 if a16 else w.w
+        if split_in:
+            assert a16 and a.shape[1] == 3 * pk_ceil8(w.cin), (a.shape, w.cin)
+            wt = w.w16s
+            p.cin = a.shape[1]
+        else:
+            p.cin = cin if cin is not None else w.cin
+            assert p.cin == w.cin and p.cin <= a.shape[1], (p.cin, w.cin, a.shape)
+            wt = w.w16 if a16 else w.w
+        assert not split_out or (o16 and out.shape[1] == 3 * w.n and out_col0 == 0)
         p.w, p.taps, p.tap0, p.w_tap_rows = wt.data_ptr(), w.taps, w.tap0, w.n_pad
         p.n, p.bn, p.epilogue = w.n, w.bn, epilogue
         p.flags = ((rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out and not o16 else 0) |
-                   (rt.F_A_F16 if a16 else 0) | (rt.F_OUT_F16 if o16 else 0))
+                   (rt.F_A_F16 if a16 else 0) | (rt.F_OUT_F16 if o16 else 0) | (rt.F_OUT_SPLIT if split_out else 0))
         assert not o16 or epilogue != rt.EPI_MAXPOOL or (residual is None and out_t is None and out_full is None)
         p.bias0, p.scale, p.shift = rt.ptr(w.bias0), rt.ptr(w.scale), rt.ptr(w.shift)
         assert residual is None or residual.dtype == torch.float32, 'the residual term reads the fp32 twin'
@@ -122,6 +138,7 @@ class Program:
         assert out_full is None or (out is not None and out_full.shape == out.shape)
         p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
         p._label = self._label
+        p._alg_cin = w.cin                     # algorithmic reduction extent (a split operand carries 3x the columns)
         self._pending.append(p)
         self._keep += [a, w, wt, out, residual, out_t, out_full]
 
@@ -171,8 +188,8 @@ class Program:
             self._gemm_plans.append(plan)
             self.steps.append(lambda plan=plan: self.h.gemm_run(plan))
             # algorithmic work: valid rows only (gap rows and the maxpool halo are overhead)
-            flops = sum(2.0 * valid * q.cin * q.taps * q.n for q in grp)
-            flops_f16 = sum(2.0 * valid * q.cin * q.taps * q.n for q in grp if q.flags & rt.F_A_F16)
+            flops = sum(2.0 * valid * q._alg_cin * q.taps * q.n for q in grp)
+            flops_f16 = sum(2.0 * valid * q._alg_cin * q.taps * q.n for q in grp if q.flags & rt.F_A_F16)
             nbytes = sum((2.0 if q.flags & rt.F_A_F16 else 4.0) * (valid * q.cin + q.taps * q.n * q.cin) +
                          (2.0 if q.flags & rt.F_OUT_F16 else 4.0) * valid * q.n for q in grp)
             labels = sorted({getattr(q, '_label', '') for q in grp})
@@ -195,6 +212,7 @@ class Program:
             p.lens, p.pad_value = (lens.data_ptr() if lens is not None else None), float(pad_value)
             p.out_f16 = int(out.dtype == torch.float16)       # h_t is fp16-exact: an fp16 layer output loses nothing
             p.x_f16 = int(xproj.dtype == torch.float16)
+            p.precise = int(getattr(r, 'precise', False))
             probs.append(p)
             self._keep += [r, xproj, out] + ([lens] if lens is not None else [])
         plan = self.h.rnn_plan(probs)
@@ -345,14 +363,25 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
 class PredictorPack:
     """Packed weights of one SeriesPredictor (forward_tacotron.py:14-39 and the multi variants)."""
 
-    def __init__(self, convs: List[PackedGemm], rnn: PackedRnn, lin_w: torch.Tensor, lin_b: torch.Tensor):
-        self.convs, self.rnn = convs, rnn
+    def __init__(self, convs: List[PackedGemm], rnn: PackedRnn, lin_w: torch.Tensor, lin_b: torch.Tensor,
+                 precise: bool = False):
+        self.convs, self.rnn, self.precise = convs, rnn, precise
         self.lin_w = lin_w.detach().float().contiguous()
         self.lin_b = lin_b.detach().float().contiguous()
 
 
+def predictor_emb_buffer(prog: Program, tag: str, p: PredictorPack, width: int) -> torch.Tensor:
+    """Input buffer of a predictor's first convolution: fp32 (tf32-rounded by the embedding kernel), or for a precise
+    predictor the [hi | lo | hi] fp16 operand (embed mode 3)."""
+    if p.precise:
+        return prog.buf(f'{tag}.emb', 3 * pk_ceil8(width), torch.float16)
+    return prog.buf(f'{tag}.emb', width)
+
+
 def predictor_levels(prog: Program, tag: str, p: PredictorPack, emb: torch.Tensor):
     ch = p.convs[0].n
+    if p.precise:
+        return _precise_predictor_levels(prog, tag, p, emb)
     # conv0 -> conv1 -> conv2 -> gru_ih are GEMM-to-GEMM hand-offs: fp16 operand buffers (see cbhg_levels)
     cdt = torch.float16 if (_F16_OPERANDS and ch % 8 == 0) else torch.float32
     c = [prog.buf(f'{tag}.c0', ch, cdt), prog.buf(f'{tag}.c1', ch, cdt)]
@@ -368,6 +397,29 @@ def predictor_levels(prog: Program, tag: str, p: PredictorPack, emb: torch.Tenso
               named('conv1', lambda: prog.gemm(c[0], p.convs[1], c[1])),
               named('conv2', lambda: prog.gemm(c[1], p.convs[2], c[0])),
               named('gru_ih', lambda: prog.gemm(c[0], p.rnn.ih, xp, round_out=False))]
+    return levels, (p.rnn, xp, h, 0), h
+
+
+def _precise_predictor_levels(prog: Program, tag: str, p: PredictorPack, emb: torch.Tensor):
+    """The split-precision predictor: every activation travels as [hi | lo | hi] fp16 column blocks, every weight as
+    [W_hi | W_hi | W_lo] (PackedGemm.w16s); the W_ih projection is written as unrounded fp32 and the recurrence runs with
+    ftb_rnn_problem.precise.  3x the MMA work of the single-fp16 path on ~2.6 % of the model's FLOPs."""
+    ch = p.convs[0].n
+    assert ch % 8 == 0
+    c = [prog.buf(f'{tag}.c0', 3 * ch, torch.float16), prog.buf(f'{tag}.c1', 3 * ch, torch.float16)]
+    xp = prog.buf(f'{tag}.xproj', p.rnn.ih.n)
+    h = prog.buf(f'{tag}.h', 2 * p.rnn.hidden)
+
+    def named(name, fn):
+        def run():
+            prog.label(f'{tag}.{name}')
+            fn()
+            prog.label('')
+        return run
+    levels = [named('conv0', lambda: prog.gemm(emb, p.convs[0], c[0], split_in=True, split_out=True)),
+              named('conv1', lambda: prog.gemm(c[0], p.convs[1], c[1], split_in=True, split_out=True)),
+              named('conv2', lambda: prog.gemm(c[1], p.convs[2], c[0], split_in=True, split_out=True)),
+              named('gru_ih', lambda: prog.gemm(c[0], p.rnn.ih, xp, round_out=False, split_in=True))]
     return levels, (p.rnn, xp, h, 0), h
 
 

@@ -12,9 +12,10 @@ from .. import pack as pk
 from .. import runtime as rt
 
 
-def pack_bn_conv(m) -> pk.PackedGemm:
+def pack_bn_conv(m, split: bool = False) -> pk.PackedGemm:
     bn = m.bnorm
-    return pk.pack_bn_conv(m.conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, m.relu is True)
+    return pk.pack_bn_conv(m.conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var, m.relu is True,
+                           split=split)
 
 
 def pack_cbhg(m) -> eng.CbhgPack:
@@ -25,8 +26,12 @@ def pack_cbhg(m) -> eng.CbhgPack:
                         m.conv1d_bank[0].conv.in_channels, m.conv1d_bank[0].conv.out_channels)
 
 
-def pack_predictor(m) -> eng.PredictorPack:
-    return eng.PredictorPack([pack_bn_conv(c) for c in m.convs], pk.PackedRnn(m.rnn), m.lin.weight, m.lin.bias)
+def pack_predictor(m, precise: bool = False) -> eng.PredictorPack:
+    """precise: the split-precision form of the whole predictor (conv stack, W_ih projection, recurrence) -- the
+    DURATION predictor, whose output is rounded to integers (forward_tacotron.py:174-177, common_layers.py:18-21)."""
+    precise = precise and eng.PRECISE_DUR and m.rnn.hidden_size <= 128 and isinstance(m.rnn, torch.nn.GRU)
+    return eng.PredictorPack([pack_bn_conv(c, split=precise) for c in m.convs], pk.PackedRnn(m.rnn, precise=precise),
+                             m.lin.weight, m.lin.bias, precise=precise)
 
 
 class AcceleratedMixin:
@@ -187,12 +192,12 @@ def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program,
 # ------------------------------------------------------------------------------------------------
 
 class FftLayerPack:
-    def __init__(self, layer):
+    def __init__(self, layer, split: bool = False):
         a = layer.self_attn
-        self.in_proj = pk.pack_linear(a.in_proj_weight, a.in_proj_bias)
-        self.out_proj = pk.pack_linear(a.out_proj.weight, a.out_proj.bias)
-        self.conv1 = pk.pack_conv(layer.conv1.weight, layer.conv1.bias, relu=True)       # conv -> +bias -> ReLU
-        self.conv2 = pk.pack_conv(layer.conv2.weight, layer.conv2.bias)
+        self.in_proj = pk.pack_linear(a.in_proj_weight, a.in_proj_bias, split=split)
+        self.out_proj = pk.pack_linear(a.out_proj.weight, a.out_proj.bias, split=split)
+        self.conv1 = pk.pack_conv(layer.conv1.weight, layer.conv1.bias, relu=True, split=split)   # conv -> +bias -> ReLU
+        self.conv2 = pk.pack_conv(layer.conv2.weight, layer.conv2.bias, split=split)
         f = lambda t: t.detach().float().contiguous()
         self.n1 = (f(layer.norm1.weight), f(layer.norm1.bias))
         self.n2 = (f(layer.norm2.weight), f(layer.norm2.bias))
@@ -201,9 +206,13 @@ class FftLayerPack:
 class TransformerPack:
     """Packed weights of one ForwardTransformer (common_layers.py:188-223)."""
 
-    def __init__(self, m):
+    def __init__(self, m, precise: bool = False):
+        """precise: the split-precision form (every GEMM operand as fp16 [hi | lo | hi] column blocks, weights as
+        [W_hi | W_hi | W_lo]) -- the duration predictor, whose output is rounded to integers (fast_pitch.py:174-177)."""
         self.d_model, self.heads = m.d_model, m.heads
-        self.layers = [FftLayerPack(l) for l in m.layers]
+        self.precise = bool(precise and eng.PRECISE_DUR and m.d_model % 8 == 0
+                            and m.layers[0].conv1.weight.shape[0] % 8 == 0)
+        self.layers = [FftLayerPack(l, split=self.precise) for l in m.layers]
         self.norm = (m.norm.weight.detach().float().contiguous(), m.norm.bias.detach().float().contiguous())
         self.pe = m.pos_encoder.pe.detach().float()[:, 0, :].contiguous()           # [max_len, E]
         self.scale = m.pos_encoder.scale.detach().float().contiguous()
@@ -219,13 +228,17 @@ def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torc
     h, g = prog.h, prog.geo
     E = tp.d_model
     F = tp.layers[0].conv1.n
+    PR = tp.precise                              # GEMM operands are [hi | lo | hi] fp16 buffers of 3x the width
+    opw, opdt = (3, torch.float16) if PR else (1, torch.float32)
+    rmode = 3 if PR else True
+    assert not PR or (x.dtype == torch.float16 and x.shape[1] == 3 * E and x_full is not None)
     qkv = prog.buf(f'{tag}.qkv', 3 * E)
-    att = prog.buf(f'{tag}.att', E)
+    att = prog.buf(f'{tag}.att', opw * E, opdt)
     y = prog.buf(f'{tag}.blk_y', E)
-    x1 = prog.buf(f'{tag}.x1', E)
+    x1 = prog.buf(f'{tag}.x1', opw * E, opdt)
     x1f = prog.buf(f'{tag}.x1_full', E)          # unrounded twins: residual adds use full fp32 values
-    c1 = prog.buf(f'{tag}.c1', F)
-    xs = [x, prog.buf(f'{tag}.x2', E)]
+    c1 = prog.buf(f'{tag}.c1', opw * F, opdt)
+    xs = [x, prog.buf(f'{tag}.x2', opw * E, opdt)]
     xsf = [x_full if x_full is not None else x, prog.buf(f'{tag}.x2_full', E)]
     levels = []
 
@@ -243,20 +256,24 @@ def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torc
         dst = out if i == n - 1 else xs[1]
         dstf = None if i == n - 1 else xsf[1]
         last = tp.norm if i == n - 1 else (None, None)
-        levels.append(named(f'l{i}.in_proj', lambda l=l, src=src: prog.gemm(src, l.in_proj, qkv, round_out=False)))
+        levels.append(named(f'l{i}.in_proj', lambda l=l, src=src: prog.gemm(src, l.in_proj, qkv, round_out=False,
+                                                                            split_in=PR)))
         levels.append(lambda l=l: prog.call(
-            lambda: h.mha(qkv, E, tp.heads, key_tok, g.batch, g.seq_len, g.stride, att),
+            lambda: h.mha(qkv, E, tp.heads, key_tok, g.batch, g.seq_len, g.stride, att, round_tf32=rmode),
             label=f'{tag}.mha', nbytes=4.0 * g.batch * g.seq_len * 4 * E))
         levels.append(named(f'l{i}.out_proj', lambda l=l, srcf=srcf: prog.gemm(att, l.out_proj, y, residual=srcf,
-                                                                               round_out=False)))
+                                                                               round_out=False, split_in=PR)))
         levels.append(lambda l=l: prog.call(
             lambda: h.add_layernorm(y, None, E, E, l.n1[0], l.n1[1], None, None, g.batch, g.seq_len, g.stride, x1,
-                                    out_full=x1f),
+                                    round_tf32=rmode, out_full=x1f),
             label=f'{tag}.norm1', nbytes=8.0 * g.batch * g.seq_len * E))
-        levels.append(named(f'l{i}.conv1', lambda l=l: prog.gemm(x1, l.conv1, c1)))
-        levels.append(named(f'l{i}.conv2', lambda l=l: prog.gemm(c1, l.conv2, y, residual=x1f, round_out=False)))
+        levels.append(named(f'l{i}.conv1', lambda l=l: prog.gemm(x1, l.conv1, c1, split_in=PR, split_out=PR)))
+        levels.append(named(f'l{i}.conv2', lambda l=l: prog.gemm(c1, l.conv2, y, residual=x1f, round_out=False,
+                                                                 split_in=PR)))
+        # the last layer's output (`out`) is fp32: tf32-rounded when it feeds a GEMM, as computed for a predictor head
         levels.append(lambda l=l, dst=dst, dstf=dstf, last=last: prog.call(
             lambda: h.add_layernorm(y, None, E, E, l.n2[0], l.n2[1], last[0], last[1], g.batch, g.seq_len,
-                                    g.stride, dst, round_tf32=(round_final or dst is not out), out_full=dstf),
+                                    g.stride, dst, round_tf32=((rmode if dst is not out else round_final)),
+                                    out_full=dstf),
             label=f'{tag}.norm2', nbytes=8.0 * g.batch * g.seq_len * E))
     return levels

@@ -122,7 +122,7 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
             'energy_proj': (f(self.energy_proj.weight).reshape(-1, 3).contiguous(), f(self.energy_proj.bias)),
         }
         for name, mod in (('dur', self.dur_pred), ('pitch', self.pitch_pred), ('energy', self.energy_pred)):
-            packs[name] = _accel.TransformerPack(mod.transformer)
+            packs[name] = _accel.TransformerPack(mod.transformer, precise=(name == 'dur'))
             packs[name + '_emb'] = f(mod.embedding.weight)
             packs[name + '_lin'] = (f(mod.lin.weight), f(mod.lin.bias))
         return packs
@@ -143,10 +143,11 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         def add_transformer(tag, tp, table, key_tok):
             self._check_len(tp, T)
             E = tp.d_model
-            x0 = prog.buf(f'{tag}.x', E)
+            x0 = prog.buf(f'{tag}.x', 3 * E, torch.float16) if tp.precise else prog.buf(f'{tag}.x', E)
             x0f = prog.buf(f'{tag}.x_full', E)
             out = prog.buf(f'{tag}.out', E)
-            prog.call(lambda: h.posenc(tok, table, None, tp.pe, tp.scale, E, batch, T, geo.stride, x0, out_full=x0f),
+            prog.call(lambda: h.posenc(tok, table, None, tp.pe, tp.scale, E, batch, T, geo.stride, x0,
+                                       round_tf32=3 if tp.precise else True, out_full=x0f),
                       label=f'{tag}.embed+posenc')                      # embedding + x + scale*pe (:143-145)
             branches.append(_accel.transformer_levels(prog, tag, tp, x0, out, key_tok, round_final=False, x_full=x0f))
             return out

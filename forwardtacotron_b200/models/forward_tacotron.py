@@ -119,7 +119,8 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         return {
             'embedding': pk.round_tf32(self.embedding.weight),
             'embedding_full': self.embedding.weight.detach().float().contiguous(),
-            'dur': _accel.pack_predictor(self.dur_pred), 'dur_emb': pk.round_tf32(self.dur_pred.embedding.weight),
+            'dur': _accel.pack_predictor(self.dur_pred, precise=True),
+            'dur_emb': self.dur_pred.embedding.weight.detach().float().contiguous(),
             'pitch': _accel.pack_predictor(self.pitch_pred),
             'pitch_emb': pk.round_tf32(self.pitch_pred.embedding.weight),
             'energy': _accel.pack_predictor(self.energy_pred),
@@ -149,8 +150,8 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         if predictors:
             for name in ('dur', 'pitch', 'energy'):
                 p = packs[name]
-                emb = prog.buf(f'{name}.emb', packs[name + '_emb'].shape[1])
-                prog.embed(tok, packs[name + '_emb'], emb)          # queued: all embeddings share one launch
+                emb = eng.predictor_emb_buffer(prog, name, p, packs[name + '_emb'].shape[1])
+                prog.embed(tok, packs[name + '_emb'], emb, round_tf32=3 if p.precise else True)   # queued: one launch
                 levels, gru, hbuf = eng.predictor_levels(prog, name, p, emb)
                 branches.append(levels)
                 grus.append(gru)

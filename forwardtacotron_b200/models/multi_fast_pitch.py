@@ -165,7 +165,8 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         }
         for name, mod in (('dur', self.dur_pred), ('pitch', self.pitch_pred), ('energy', self.energy_pred),
                           ('pitch_cond', self.pitch_cond_pred)):
-            packs[name] = _accel.TransformerPack(mod.transformer)
+            # durations and the pitch-condition arg-max are rounded to integers: split-precision predictors
+            packs[name] = _accel.TransformerPack(mod.transformer, precise=name in ('dur', 'pitch_cond'))
             packs[name + '_emb'] = f(mod.embedding.weight)
             if hasattr(mod, 'conditional_embedding'):
                 packs[name + '_cemb'] = f(mod.conditional_embedding.weight)
@@ -195,13 +196,14 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
             self._check_len(tp, T)
             E = tp.d_model
             cat = prog.buf(f'{tag}.cat', E)
-            x0 = prog.buf(f'{tag}.x', E)
+            x0 = prog.buf(f'{tag}.x', 3 * E, torch.float16) if tp.precise else prog.buf(f'{tag}.x', E)
             x0f = prog.buf(f'{tag}.x_full', E)
             out = prog.buf(f'{tag}.out', E)
             prog.call(lambda: h.embed(tok, table, cat, E, batch, T, geo.stride,
                                       tok2=pcond if ctable is not None else None, table2=ctable, extra=semb,
                                       round_tf32=False), label=f'{tag}.embed')
-            prog.call(lambda: h.posenc(None, None, cat, tp.pe, tp.scale, E, batch, T, geo.stride, x0, out_full=x0f),
+            prog.call(lambda: h.posenc(None, None, cat, tp.pe, tp.scale, E, batch, T, geo.stride, x0,
+                                       round_tf32=3 if tp.precise else True, out_full=x0f),
                       label=f'{tag}.posenc')
             return out, _accel.transformer_levels(prog, tag, tp, x0, out, key_tok, round_final=False, x_full=x0f)
 

@@ -175,10 +175,12 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         }
         for name, mod in (('dur', self.dur_pred), ('pitch', self.pitch_pred), ('energy', self.energy_pred),
                           ('pitch_cond', self.pitch_cond_pred)):
-            packs[name] = _accel.pack_predictor(mod)
-            packs[name + '_emb'] = pk.round_tf32(mod.embedding.weight)
+            # the two predictors whose output is rounded to integers (durations :253-255 / LengthRegulator, and the
+            # arg-max of the pitch condition :251-252) run the split-precision path; their embedding kernel rounds
+            packs[name] = _accel.pack_predictor(mod, precise=name in ('dur', 'pitch_cond'))
+            packs[name + '_emb'] = mod.embedding.weight.detach().float().contiguous()
             if hasattr(mod, 'pitch_cond_embedding'):
-                packs[name + '_cemb'] = pk.round_tf32(mod.pitch_cond_embedding.weight)
+                packs[name + '_cemb'] = mod.pitch_cond_embedding.weight.detach().float().contiguous()
         return packs
 
     def _token_program(self, st: dict, batch: int, T: int, predictors: bool, teacher_cond: bool = False) -> eng.Program:
@@ -201,10 +203,10 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             e1 = packs[name + '_emb'].shape[1]
             e2 = packs[name + '_cemb'].shape[1] if conditional else 0
             width = e1 + e2 + S
-            ld = pk.ceil_to(width, 4)
-            emb = prog.buf(f'{name}.emb', ld)
+            emb = eng.predictor_emb_buffer(prog, name, p, pk.ceil_to(width, 4))
             prog.embed(tok, packs[name + '_emb'], emb, tok2=pcond if conditional else None,
-                       table2=packs[name + '_cemb'] if conditional else None, extra=semb)
+                       table2=packs[name + '_cemb'] if conditional else None, extra=semb,
+                       round_tf32=3 if p.precise else True)
             levels, gru, hbuf = eng.predictor_levels(prog, name, p, emb)
             heads.append((name, p, hbuf))
             return levels, gru

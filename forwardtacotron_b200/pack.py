@@ -45,6 +45,8 @@ class PackedGemm:
         self.cin = w.shape[2]
         self.bias0, self.scale, self.shift, self.relu = bias0, scale, shift, relu
         self._w16 = None
+        self.w_src = None            # unrounded fp32 copy of `w`; kept only by packs built with split=True
+        self._w16s = None
 
     @property
     def w16(self) -> torch.Tensor:
@@ -56,33 +58,54 @@ class PackedGemm:
         return self._w16
 
 
+    @property
+    def w16s(self) -> torch.Tensor:
+        """Split-precision weight for a [hi | lo | hi] operand (FTB_F_OUT_SPLIT producers, embed mode 3): per tap
+        [n_pad][3*seg] = [W_hi | W_hi | W_lo] with seg = cin rounded up to 8, W_hi = fp16(W), W_lo = fp16(W - W_hi), so
+        one kind::f16 GEMM over K = 3*seg accumulates a_hi*W_hi + a_lo*W_hi + a_hi*W_lo."""
+        if self._w16s is None:
+            assert self.w_src is not None, 'pack with split=True'
+            seg = ceil_to(self.cin, 8)
+            hi = self.w_src.to(torch.float16)
+            lo = (self.w_src - hi.float()).to(torch.float16)
+            w = self.w_src.new_zeros((self.taps, self.n_pad, 3 * seg), dtype=torch.float16)
+            w[:, :, :self.cin] = hi
+            w[:, :, seg:seg + self.cin] = hi
+            w[:, :, 2 * seg:2 * seg + self.cin] = lo
+            self._w16s = w.contiguous()
+        return self._w16s
+
+
 def _f(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     return None if t is None else t.detach().to(torch.float32).contiguous()
 
 
 def pack_conv(weight: torch.Tensor, bias: Optional[torch.Tensor] = None, bn: Optional[int] = None,
-              scale=None, shift=None, relu=False) -> PackedGemm:
+              scale=None, shift=None, relu=False, split=False) -> PackedGemm:
     """Conv1d weight [Cout, Cin, k] (padding k//2, common_layers.py:50) -> taps x [Cout_pad, Cin]."""
     cout, cin, k = weight.shape
     bn = bn or pick_bn(cout)
     n_pad = ceil_to(cout, bn)
     w = weight.new_zeros((k, n_pad, cin), dtype=torch.float32)
     w[:, :cout, :] = weight.detach().permute(2, 0, 1)
-    return PackedGemm(round_tf32(w), k, -(k // 2), cout, bn, _f(bias), _f(scale), _f(shift), relu)
+    g = PackedGemm(round_tf32(w), k, -(k // 2), cout, bn, _f(bias), _f(scale), _f(shift), relu)
+    if split:
+        g.w_src = w
+    return g
 
 
-def pack_bn_conv(conv_w, gamma, beta, mean, var, relu: bool, bn: Optional[int] = None) -> PackedGemm:
+def pack_bn_conv(conv_w, gamma, beta, mean, var, relu: bool, bn: Optional[int] = None, split=False) -> PackedGemm:
     """BatchNormConv (conv -> ReLU? -> BN eval, common_layers.py:54-57): BN becomes the per-channel
     affine y = v*s + b applied AFTER the ReLU in the epilogue (it cannot be folded into the weights
     when relu=True)."""
     s = gamma.detach().float() / torch.sqrt(var.detach().float() + BN_EPS)
     b = beta.detach().float() - mean.detach().float() * s
-    return pack_conv(conv_w, None, bn, s, b, relu)
+    return pack_conv(conv_w, None, bn, s, b, relu, split)
 
 
 def pack_linear(weight: torch.Tensor, bias: Optional[torch.Tensor] = None, bn: Optional[int] = None,
-                relu=False) -> PackedGemm:
-    return pack_conv(weight.detach().unsqueeze(2), bias, bn, None, None, relu)
+                relu=False, split=False) -> PackedGemm:
+    return pack_conv(weight.detach().unsqueeze(2), bias, bn, None, None, relu, split)
 
 
 def pack_highway(w1, b1, w2, b2, bn: int = 256) -> PackedGemm:
@@ -102,13 +125,16 @@ def pack_highway(w1, b1, w2, b2, bn: int = 256) -> PackedGemm:
 class PackedRnn:
     """Bidirectional GRU/LSTM: input projection as one GEMM over both directions, W_hh resident."""
 
-    def __init__(self, rnn: torch.nn.RNNBase):
+    def __init__(self, rnn: torch.nn.RNNBase, precise: bool = False):
+        """precise: the split-precision form (duration predictors): W_ih packed for a [hi | lo | hi] operand, the
+        recurrence run with ftb_rnn_problem.precise."""
+        self.precise = precise
         p = dict(rnn.named_parameters())
         self.cell = 1 if isinstance(rnn, torch.nn.LSTM) else 0
         self.hidden = rnn.hidden_size
         w_ih = torch.cat([p['weight_ih_l0'], p['weight_ih_l0_reverse']], dim=0)
         b_ih = torch.cat([p['bias_ih_l0'], p['bias_ih_l0_reverse']], dim=0)
-        self.ih = pack_linear(w_ih, b_ih)
+        self.ih = pack_linear(w_ih, b_ih, split=precise)
         # fp32 here: the recurrence kernel rounds W_hh ONCE to fp16 (same 11 significant bits as tf32) when it
         # builds its register-resident MMA fragments
         self.w_hh = torch.stack([p['weight_hh_l0'], p['weight_hh_l0_reverse']]).detach().float().contiguous()

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libftb200.so')
 
 EPI_AFFINE, EPI_MAXPOOL, EPI_HIGHWAY = 0, 1, 2
-F_RELU, F_ROUND, F_A_F16, F_OUT_F16 = 1, 2, 4, 8
+F_RELU, F_ROUND, F_A_F16, F_OUT_F16, F_OUT_SPLIT = 1, 2, 4, 8, 16
 CELL_GRU, CELL_LSTM = 0, 1
 SEQ_GAP = 8          # zero rows between sentences in the padded-flat layout (>= largest conv reach)
 
@@ -35,7 +35,7 @@ class RnnProblem(C.Structure):
     _fields_ = [('cell', C.c_int32), ('hidden', C.c_int32), ('batch', C.c_int32), ('seq_len', C.c_int32),
                 ('seq_stride', C.c_int32), ('xproj', _fp), ('w_hh', _fp), ('b_hh', _fp), ('out', _fp),
                 ('out_ld', C.c_int32), ('out_col0', C.c_int32), ('lens', _fp), ('pad_value', C.c_float),
-                ('out_f16', C.c_int32), ('x_f16', C.c_int32)]
+                ('out_f16', C.c_int32), ('x_f16', C.c_int32), ('precise', C.c_int32)]
 
 
 class EmbedItem(C.Structure):
@@ -230,7 +230,8 @@ class Handle:
         e1 = table.shape[1]
         e2 = table2.shape[1] if table2 is not None else 0
         e3 = extra.shape[1] if extra is not None else 0
-        mode = 2 if out.dtype == torch.float16 else int(round_tf32)       # fp16 operand copy / tf32-rounded / as stored
+        # split fp16 [hi | lo | hi] / fp16 operand copy / tf32-rounded / as stored
+        mode = 3 if int(round_tf32) == 3 else (2 if out.dtype == torch.float16 else int(round_tf32))
         self.check(self.lib.ftb_embed(self.h, ptr(tok), ptr(table), e1, ptr(tok2), ptr(table2), e2, ptr(extra), e3,
                                       batch, T, stride, ptr(out), out_ld, mode, self.stream()))
 
@@ -242,7 +243,7 @@ class Handle:
             a.tok2, a.table2, a.e2 = ptr(tok2), ptr(table2), (table2.shape[1] if table2 is not None else 0)
             a.extra, a.e3 = ptr(extra), (extra.shape[1] if extra is not None else 0)
             a.out, a.out_ld = ptr(out), out.shape[1]
-            a.round_tf32 = 2 if out.dtype == torch.float16 else int(round_tf32)
+            a.round_tf32 = 3 if int(round_tf32) == 3 else (2 if out.dtype == torch.float16 else int(round_tf32))
         self.check(self.lib.ftb_embed_batch(self.h, arr, len(items), batch, T, stride, self.stream()))
 
     def rowdot_batch(self, items, batch, T, stride):

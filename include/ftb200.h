@@ -77,8 +77,15 @@ enum { FTB_EPI_AFFINE = 0, FTB_EPI_MAXPOOL = 1, FTB_EPI_HIGHWAY = 2 };
  *                the operand traffic of tf32.  Used where the producer of `a` is another K1/K2 problem.
  * FTB_F_OUT_F16: `out` is fp16 [rows, out_ld] (out_ld, out_col0, n multiples of 8), rounded to nearest: the operand
  *                copy for a following FTB_F_A_F16 problem.  Any epilogue; residual / out_t / out_full (always fp32)
- *                may accompany it except with MAXPOOL; ROUND_TF32 is ignored.                                   */
-enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2, FTB_F_A_F16 = 4, FTB_F_OUT_F16 = 8 };
+ *                may accompany it except with MAXPOOL; ROUND_TF32 is ignored.
+ * FTB_F_OUT_SPLIT: (with FTB_F_OUT_F16, AFFINE epilogue, no residual / out_t / out_full) `out` receives every value v as
+ *                THREE fp16 column blocks of width n: hi = fp16(v) at out_col0 + c, lo = fp16(v - hi) at out_col0 + n + c,
+ *                hi again at out_col0 + 2n + c (out_ld >= out_col0 + 3n).  A consumer whose weights are packed as
+ *                [W_hi | W_hi | W_lo] along K (cin = 3n, FTB_F_A_F16) then accumulates hi*W_hi + lo*W_hi + hi*W_lo: the
+ *                product at ~2^-20 relative operand precision instead of 2^-11, on the same kind::f16 MMAs.  Used for
+ *                the DURATION predictor, whose output is rounded to integers (forward_tacotron.py:174-177,
+ *                common_layers.py:18-21): an operand error of 2^-11 moves durations across the .5 boundary.           */
+enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2, FTB_F_A_F16 = 4, FTB_F_OUT_F16 = 8, FTB_F_OUT_SPLIT = 16 };
 
 typedef struct {
   const void* a;         /* [rows, lda] activations: fp32 tf32-rounded by their producer, or fp16 (A_F16) */
@@ -155,6 +162,11 @@ typedef struct {
                             the operand copy for a following FTB_F_A_F16 GEMM (lin / post_proj)                 */
   int32_t x_f16;         /* != 0: `xproj` is fp16 [batch*seq_stride, 2*g*H] (a FTB_F_OUT_F16 GEMM wrote it): half the
                             x-projection traffic for one more rounding to 11 bits              */
+  int32_t precise;       /* != 0 (GRU, H <= 128, fp32 xproj / out): split-precision recurrence -- h_t and W_hh enter the
+                            MMAs as fp16 hi + lo pairs (three products per k-step, ~2^-20 relative operand precision
+                            instead of 2^-11), the gates use ex2/rcp instead of tanh.approx, `out` receives the
+                            unrounded fp32 h_t.  For the duration predictors, whose output is rounded to integers
+                            (forward_tacotron.py:174-177); needs the cluster hand-off (else FTB_E_RESIDENT)      */
 } ftb_rnn_problem;
 
 #define FTB_MAX_RNN_PROBLEMS 8
@@ -232,7 +244,8 @@ int ftb_lr_regulate_static(ftb_handle h, const float* x, int x_stride /*rows per
  * vector, multi_forward_tacotron.py:40-42,82-86) into the padded-flat layout:
  * out[b*seq_stride+t, :] = table[tok[b,t], :e1] ++ table2[tok2[b,t], :e2] ++ extra[b, :e3].
  * round_tf32: 0 = fp32 as stored, 1 = fp32 rounded to tf32, 2 = `out` is an fp16 array (out_ld in fp16 elements):
- * the operand copy a FTB_F_A_F16 problem reads. */
+ * the operand copy a FTB_F_A_F16 problem reads; 3 = `out` is an fp16 array of THREE column blocks of width out_ld/3,
+ * [hi | lo | hi] with hi = fp16(v), lo = fp16(v - hi): the split-precision operand layout of FTB_F_OUT_SPLIT. */
 int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1,
               const int64_t* tok2, const float* table2, int e2,
               const float* extra, int e3,
@@ -274,7 +287,9 @@ int ftb_argmax_lastdim(ftb_handle h, const float* x, int64_t n, int c, int64_t* 
 /* y = LayerNorm(x (+ res)) * gamma + beta, eps = 1e-5, over the last axis e (<= 1024), only
  * valid rows; optional second LayerNorm chained (the ForwardTransformer's final norm).
  * `out` is tf32-rounded when round_tf32 != 0 (it feeds a GEMM); `out_full` (optional) receives
- * the unrounded values (the residual copy).                                                   */
+ * the unrounded values (the residual copy).  round_tf32 == 3 (here, in ftb_posenc and in ftb_mha; e % 8 == 0): `out`
+ * is an fp16 array [rows, 3e] = [hi | lo | hi] with hi = fp16(v), lo = fp16(v - hi), the split-precision GEMM operand
+ * (FTB_F_OUT_SPLIT) of the duration predictor's FFT blocks (fast_pitch.py:14-41).                                   */
 int ftb_add_layernorm(ftb_handle h, const float* x, const float* res, int ld, int e,
                       const float* gamma, const float* beta,
                       const float* gamma2, const float* beta2,

@@ -558,3 +558,109 @@ def test_embed_and_heads_batched_match_single_and_torch():
         assert max_abs(y2.double().cpu(), want.cpu()) < 1e-4
     with pytest.raises(RuntimeError):
         h.embed_batch(items * 3, B, T, geo.stride)                 # > FTB_MAX_GLUE_ITEMS
+
+
+# --------------------------------------------------------------------------------------------------
+# Split-precision path of the duration predictor (FTB_F_OUT_SPLIT, embed mode 3, ftb_rnn_problem.precise)
+# --------------------------------------------------------------------------------------------------
+
+def _split3(v):
+    """[..., C] fp32 -> [..., 3*C8] fp16 [hi | lo | hi] (C8 = C rounded up to 8), the layout embed mode 3 / OUT_SPLIT write."""
+    C = v.shape[-1]
+    seg = pk.ceil_to(C, 8)
+    hi = v.to(torch.float16)
+    lo = (v - hi.float()).to(torch.float16)
+    out = torch.zeros(v.shape[:-1] + (3 * seg,), dtype=torch.float16)
+    out[..., :C], out[..., seg:seg + C], out[..., 2 * seg:2 * seg + C] = hi, lo, hi
+    return out
+
+
+@pytest.mark.parametrize('B,L,cin,cout,k', [(2, 50, 64, 256, 5), (3, 130, 256, 256, 5), (2, 40, 388, 256, 5),
+                                            (2, 70, 256, 384, 1)])
+def test_conv_split_precision(B, L, cin, cout, k):
+    """[hi | lo | hi] operand x [W_hi | W_hi | W_lo] weight on kind::f16 MMAs: the conv at ~2^-20 relative operand
+    precision on operands that are NOT pre-rounded (the single-fp16 product of the same operands is off by ~1e-3), result written back in the split layout."""
+    gen = torch.Generator().manual_seed(B * 1000 + L + k + cin)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    v = torch.randn(B, L, cin, generator=gen)                       # NOT pre-rounded: the point of the split path
+    seg = pk.ceil_to(cin, 8)
+    a = prog.buf('a', 3 * seg, torch.float16)
+    a.view(g.batch, g.stride, 3 * seg)[:, :L] = _split3(v).to(DEV)
+    w = torch.randn(cout, cin, k, generator=gen) / (cin * k) ** 0.5
+    gamma, beta = torch.rand(cout, generator=gen) + 0.5, torch.randn(cout, generator=gen) * 0.1
+    mean, var = torch.randn(cout, generator=gen) * 0.1, torch.rand(cout, generator=gen) + 0.5
+    packed = pk.pack_bn_conv(w.to(DEV), gamma.to(DEV), beta.to(DEV), mean.to(DEV), var.to(DEV), True, split=True)
+    out = prog.buf('out', 3 * cout, torch.float16)
+    out32 = prog.buf('out32', cout)
+    prog.gemm(a, packed, out, split_in=True, split_out=True)
+    prog.gemm(a, packed, out32, split_in=True, round_out=False)
+    prog.flush()
+    y = _conv_ref(v.double(), w, k).clamp_min(0)
+    s = (gamma / torch.sqrt(var + 1e-5)).double()
+    ref = y * s + (beta.double() - mean.double() * s)
+    for impl in (1, 0):
+        out.zero_(); out32.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        got32 = prog.view('out32').cpu().double()
+        o = prog.view('out').cpu()
+        hi, lo, hi2 = o[..., :cout], o[..., cout:2 * cout], o[..., 2 * cout:]
+        assert max_abs(got32, ref) < 1e-4, f'impl={impl}'        # fp32 accumulation over K = 3 * cin * k
+        assert torch.equal(hi, hi2)
+        assert max_abs(hi.double() + lo.double(), ref) < 1e-4, f'impl={impl}'
+        assert torch.equal(hi, got32.float().to(torch.float16))     # hi is the rounded value, lo the remainder
+    prog.h.impl = 0
+    assert float(out.view(g.batch, g.stride, -1)[:, L:].float().abs().max()) == 0.0
+
+
+def test_embed_split_mode():
+    B, T, E, S = 3, 17, 12, 20
+    gen = torch.Generator().manual_seed(5)
+    table, table2 = torch.randn(30, E, generator=gen), torch.randn(4, 4, generator=gen)
+    extra = torch.randn(B, S, generator=gen)
+    tok, tok2 = torch.randint(0, 30, (B, T), generator=gen), torch.randint(0, 4, (B, T), generator=gen)
+    prog = eng.Program(_handle(), eng.Geometry(B, T))
+    seg = pk.ceil_to(E + 4 + S, 8)
+    out = prog.buf('e', 3 * seg, torch.float16)
+    prog.embed(tok.to(DEV), table.to(DEV), out, tok2=tok2.to(DEV), table2=table2.to(DEV), extra=extra.to(DEV),
+               round_tf32=3)
+    prog.run()
+    torch.cuda.synchronize()
+    v = torch.cat([table[tok], table2[tok2], extra[:, None, :].expand(-1, T, -1)], dim=2)
+    assert torch.equal(prog.view('e').cpu(), _split3(v))
+
+
+@pytest.mark.parametrize('H,B,L', [(64, 20, 60), (128, 9, 41), (64, 64, 200)])
+def test_recurrence_precise(H, B, L):
+    """ftb_rnn_problem.precise: split-fp16 recurrent product + ex2/rcp gates + unrounded fp32 h_t, fed by the split
+    W_ih projection -- against the fp32 oracle GRU in float64-free plain fp32 (no operand rounding at all)."""
+    gen = torch.Generator().manual_seed(H + B)
+    In = 256
+    rnn = torch.nn.GRU(In, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    packed = pk.PackedRnn(rnn.to(DEV), precise=True)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    v = torch.randn(B, L, In, generator=gen)
+    a = prog.buf('x', 3 * In, torch.float16)
+    a.view(g.batch, g.stride, 3 * In)[:, :L] = _split3(v).to(DEV)
+    xp = prog.buf('xp', packed.ih.n)
+    out = prog.buf('h', 2 * H)
+    prog.gemm(a, packed.ih, xp, round_out=False, split_in=True)
+    prog.rnn([(packed, xp, out, 0)])
+    assert prog.info[-1]['handoff'] == 'cluster'
+    prog.run()
+    torch.cuda.synchronize()
+    sd = {'r.' + k: v_.detach().cpu().double() for k, v_ in rnn.state_dict().items()}
+    with torch.no_grad():
+        ref = O.bi_rnn(sd, 'r', v.double(), 'gru')
+    got = prog.view('h').cpu()
+    assert max_abs(got, ref) < 2e-5, max_abs(got, ref)             # the single-fp16 recurrence sits at ~1e-3
+    out.zero_()
+    prog.run()
+    torch.cuda.synchronize()
+    assert torch.equal(prog.view('h').cpu(), got)
