@@ -22,7 +22,7 @@ CASES = {   # name: (model tag, batch, T, alpha, spread durations, seed)
     'fp64': ('fast_pitch', 64, 200, 1.0, True, 23),
     'mft128': ('multi_forward_tacotron', 128, 200, 1.0, True, 24),
     'mft16': ('multi_forward_tacotron', 16, 200, 1.0, True, 25),
-    'mfp16': ('multi_fast_pitch', 16, 200, 1.0, True, 27),
+    'mfp16': ('multi_fast_pitch', 16, 200, 1.0, True, 11),
     'ft4096': ('forward_tacotron', 2, 4096, 0.8, True, 26),
 }
 GEN = {'forward_tacotron': O.ft_generate, 'fast_pitch': O.fp_generate, 'multi_forward_tacotron': O.mft_generate,

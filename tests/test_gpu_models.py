@@ -29,15 +29,48 @@ def _rounded(d):
     return (torch.as_tensor(d).clamp_min(0) + 0.5).long()
 
 
-def _check_durations(got, ref, tie=1e-3):
-    """Identical after rounding, except where the reference value sits within `tie` of a .5 tie."""
+DUR_WINDOW = 2e-4      # the documented .5-tie window, in frames: raw durations agree to better than
+                       # this (measured <= 8.1e-5 at BASELINE sizes, profiles/r2_err_report.txt), so a rounded duration
+                       # can differ only where the reference value lies within it of a rounding boundary
+
+
+# MultiFastPitch's duration predictor is four FFT blocks of width 392 (K = 3 * 3528 per conv1 MMA chain): the tensor
+# core's fp32 accumulator truncates instead of rounding, a bias that grows with K (scratch/debug_mfp_dur.py: 1e-4 per
+# unit-scale activation after four layers although every operand is split to ~2^-20), so its raw durations agree to
+# 2.4e-4 and its window is wider.
+DUR_WINDOW_MFP = 5e-4
+
+
+def _check_durations(got, ref, window=DUR_WINDOW):
+    """Raw durations within `window`; rounded durations identical except where the reference value sits within
+    `window` of a .5 tie.  Returns the number of such flips (0 in every case measured so far)."""
     got, ref = torch.as_tensor(got).cpu(), torch.as_tensor(ref).cpu()
-    assert max_abs(got, ref) < 2e-3 * max(1.0, float(ref.abs().max()))     # raw values: 2e-3 relative to the range
+    assert max_abs(got, ref) < window, max_abs(got, ref)
     diff = _rounded(got) != _rounded(ref)
     frac = (ref.clamp_min(0) + 0.5) % 1.0
-    near_tie = (frac < tie) | (frac > 1 - tie)
+    near_tie = (frac < window) | (frac > 1 - window)
     assert not bool((diff & ~near_tie).any()), 'rounded durations differ away from a .5 tie'
     return int(diff.sum())
+
+
+def _mel_checked(model, args, out, ref, flips, keys=('mel', 'mel_post')):
+    """mel / mel_post parity, UNCONDITIONALLY: generate()'s own output when every rounded duration matches; when a
+    duration flipped inside the tie window (the frame count then differs) the teacher-forced entry fed with the
+    reference's dur / pitch / energy, so the mel check never silently disappears."""
+    if flips:
+        dev = lambda k: torch.as_tensor(ref[k]).to(DEV)                    # noqa: E731
+        dur = dev('dur').to(torch.float32).contiguous().clone()
+        if 'pitch_cond' in ref:
+            out = model._generate_mel(*args, dur, dev('pitch'), dev('pitch_cond'), dev('energy'))
+        else:
+            out = model._generate_mel(*args, dur, dev('pitch'), dev('energy'))
+        torch.cuda.synchronize()
+    for k in keys:
+        r = torch.as_tensor(ref[k])
+        assert out[k].shape == r.shape, (k, out[k].shape, r.shape)
+        assert max_abs(out[k].cpu(), r) < MEL_ABS, k
+        assert rel_l2(out[k].cpu(), r) < MEL_REL, k
+    return out
 
 
 @pytest.mark.parametrize('name', ['ft_spread_b3_t40', 'ft_fallback_b2_t24', 'ft_alpha_b2_t30', 'ft_b1_t74'])
@@ -46,18 +79,15 @@ def test_forward_tacotron_generate_vs_reference_golden(name):
     sd = synthetic_sd('forward_tacotron', int(g['seed']), bool(g['spread']), float(g['dur_bias']))
     model = _model('forward_tacotron', sd)
     pm, em = float(g['pitch_mul']), float(g['energy_mul'])
-    out = model.generate(torch.from_numpy(g['x']).to(DEV), alpha=float(g['alpha']),
+    x = torch.from_numpy(g['x']).to(DEV)
+    out = model.generate(x, alpha=float(g['alpha']),
                          pitch_function=lambda p: p * pm, energy_function=lambda e: e * em)
     torch.cuda.synchronize()
     assert set(out) == {'mel', 'mel_post', 'dur', 'pitch', 'energy'}
     assert out['pitch'].shape == g['pitch'].shape and out['dur'].shape == g['dur'].shape
     ties = _check_durations(out['dur'], g['dur'])
     assert max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3 and max_abs(out['energy'].cpu(), g['energy']) < 5e-3
-    if ties == 0:
-        assert out['mel'].shape == g['mel'].shape
-        for k in ('mel', 'mel_post'):
-            assert max_abs(out[k].cpu(), g[k]) < MEL_ABS, k
-            assert rel_l2(out[k].cpu(), g[k]) < MEL_REL, k
+    _mel_checked(model, (x,), out, g, ties)
 
 
 def test_generate_mel_teacher_forced_intermediates():
@@ -96,10 +126,7 @@ def test_forward_tacotron_vs_oracle_batch16():
     for _ in range(2):
         out = model.generate(x.to(DEV))
         torch.cuda.synchronize()
-        ties = _check_durations(out['dur'], ref['dur'])
-        if ties == 0:
-            for k in ('mel', 'mel_post'):
-                assert max_abs(out[k].cpu(), ref[k]) < MEL_ABS and rel_l2(out[k].cpu(), ref[k]) < MEL_REL, k
+        _mel_checked(model, (x.to(DEV),), out, ref, _check_durations(out['dur'], ref['dur']))
 
 
 # --------------------------------------------------------------------------------------------------
@@ -113,24 +140,21 @@ def test_multi_forward_tacotron_vs_reference_golden(name):
     g = load_golden(name)
     sd = synthetic_sd('multi_forward_tacotron', int(g['seed']))
     model = _model('multi_forward_tacotron', sd)
-    out = model.generate(torch.from_numpy(g['x']).to(DEV), torch.from_numpy(g['speaker_emb']).to(DEV))
+    args = (torch.from_numpy(g['x']).to(DEV), torch.from_numpy(g['speaker_emb']).to(DEV))
+    out = model.generate(*args)
     torch.cuda.synchronize()
     assert set(out) == {'mel', 'mel_post', 'dur', 'pitch', 'energy', 'pitch_cond'}
     assert out['pitch_cond'].shape == g['pitch_cond'].shape and out['pitch_cond'].dtype == torch.int64
     assert np.array_equal(out['pitch_cond'].cpu().numpy(), g['pitch_cond'])
     ties = _check_durations(out['dur'], g['dur'])
     assert max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3 and max_abs(out['energy'].cpu(), g['energy']) < 5e-3
-    if ties == 0:
-        assert out['mel'].shape == g['mel'].shape
-        for k in ('mel', 'mel_post'):
-            assert max_abs(out[k].cpu(), g[k]) < MEL_ABS, k
-            assert rel_l2(out[k].cpu(), g[k]) < MEL_REL, k
+    _mel_checked(model, args, out, g, ties)
 
 
 def test_multi_forward_tacotron_vs_oracle_batch8():
-    """Fresh seeded cases vs the CPU oracle.  The categorical pitch condition may flip only where the
-    oracle's top-2 logits are within 1e-2 (a tf32-vs-fp32 near tie); mel parity is asserted on every
-    case without a flip or a duration tie, and at least one such case must exist."""
+    """Fresh seeded cases vs the CPU oracle.  The categorical pitch condition (split-precision predictor) may flip
+    only where the oracle's top-2 logits are within 1e-3; such a case is counted and skipped (its durations are then
+    conditioned differently), mel parity is asserted on every other case, and all three must not be skipped."""
     compared = 0
     for seed in (5, 6, 7):
         sd = synthetic_sd('multi_forward_tacotron', seed)
@@ -147,14 +171,12 @@ def test_multi_forward_tacotron_vs_oracle_batch8():
         flips = out['pitch_cond'].cpu() != ref['pitch_cond']
         top2 = ref['pitch_cond_logits'].topk(2, dim=-1).values
         margin = (top2[..., 0] - top2[..., 1]).unsqueeze(1)
-        assert not bool((flips & (margin > 1e-2)).any()), 'pitch condition differs away from a near tie'
+        assert not bool((flips & (margin > 1e-3)).any()), 'pitch condition differs away from a near tie'
         if bool(flips.any()):
             continue
-        if _check_durations(out['dur'], ref['dur']) == 0:
-            compared += 1
-            for k in ('mel', 'mel_post'):
-                assert max_abs(out[k].cpu(), ref[k]) < MEL_ABS and rel_l2(out[k].cpu(), ref[k]) < MEL_REL, k
-    assert compared >= 1
+        compared += 1
+        _mel_checked(model, (x.to(DEV), semb.to(DEV)), out, ref, _check_durations(out['dur'], ref['dur']))
+    assert compared >= 2
 
 
 @pytest.mark.parametrize('name', ['fp_b2_t30', 'fp_pad_b3_t36'])
@@ -172,11 +194,8 @@ def test_fast_pitch_vs_reference_golden(name):
     assert rel_l2(tok.view('prenet.out').cpu(), g['tap_prenet']) < 1e-3
     ties = _check_durations(out['dur'], g['dur'])
     assert max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3 and max_abs(out['energy'].cpu(), g['energy']) < 5e-3
-    if ties == 0:
-        assert out['mel'].shape == g['mel'].shape
-        assert out['mel_post'].data_ptr() == out['mel'].data_ptr()            # the same tensor (:220)
-        assert max_abs(out['mel'].cpu(), g['mel']) < MEL_ABS
-        assert rel_l2(out['mel'].cpu(), g['mel']) < MEL_REL
+    assert out['mel_post'].data_ptr() == out['mel'].data_ptr()                # the same tensor (:220)
+    _mel_checked(model, (x,), out, g, ties, keys=('mel',))
 
 
 def test_fast_pitch_vs_oracle_batch8():
@@ -186,8 +205,7 @@ def test_fast_pitch_vs_oracle_batch8():
     ref = O.fp_generate(sd, x)
     out = model.generate(x.to(DEV))
     torch.cuda.synchronize()
-    if _check_durations(out['dur'], ref['dur']) == 0:
-        assert max_abs(out['mel'].cpu(), ref['mel']) < MEL_ABS and rel_l2(out['mel'].cpu(), ref['mel']) < MEL_REL
+    _mel_checked(model, (x.to(DEV),), out, ref, _check_durations(out['dur'], ref['dur']), keys=('mel',))
 
 
 def test_fast_pitch_rejects_sequences_beyond_positional_table():
@@ -203,23 +221,20 @@ def test_multi_fast_pitch_vs_reference_golden(name):
     g = load_golden(name)
     sd = synthetic_sd('multi_fast_pitch', int(g['seed']))
     model = _model('multi_fast_pitch', sd)
-    out = model.generate(torch.from_numpy(g['x']).to(DEV), torch.from_numpy(g['speaker_emb']).to(DEV),
-                         alpha=float(g['alpha']))
+    args = (torch.from_numpy(g['x']).to(DEV), torch.from_numpy(g['speaker_emb']).to(DEV))
+    out = model.generate(*args, alpha=float(g['alpha']))
     torch.cuda.synchronize()
     assert set(out) == {'mel', 'mel_post', 'dur', 'pitch', 'energy', 'pitch_cond'}
     assert out['pitch_cond'].shape == g['pitch_cond'].shape and out['pitch_cond'].dtype == torch.int64
     assert np.array_equal(out['pitch_cond'].cpu().numpy(), g['pitch_cond'])
-    ties = _check_durations(out['dur'], g['dur'])
+    ties = _check_durations(out['dur'], g['dur'], DUR_WINDOW_MFP)
     assert max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3 and max_abs(out['energy'].cpu(), g['energy']) < 5e-3
-    if ties == 0:
-        assert out['mel'].shape == g['mel'].shape
-        assert max_abs(out['mel'].cpu(), g['mel']) < MEL_ABS
-        assert rel_l2(out['mel'].cpu(), g['mel']) < MEL_REL
+    _mel_checked(model, args, out, g, ties, keys=('mel',))
 
 
 def test_multi_fast_pitch_vs_oracle_batch8():
-    """Fresh seeded cases vs the CPU oracle; the categorical pitch condition may flip only at near ties of the
-    oracle's top-2 logits, mel parity is asserted on every case without a flip or a duration tie."""
+    """Fresh seeded cases vs the CPU oracle; the categorical pitch condition (split-precision predictor) may flip only
+    where the oracle's top-2 logits are within 1e-3; mel parity is asserted on every case without such a flip."""
     compared = 0
     for seed in (11, 12, 13):
         sd = synthetic_sd('multi_fast_pitch', seed)
@@ -232,17 +247,13 @@ def test_multi_fast_pitch_vs_oracle_batch8():
         flips = out['pitch_cond'].cpu() != ref['pitch_cond']
         top2 = ref['pitch_cond_logits'].topk(2, dim=-1).values
         margin = top2[..., 0] - top2[..., 1]
-        assert not bool((flips & (margin > 1e-2)).any()), 'pitch condition differs away from a near tie'
+        assert not bool((flips & (margin > 1e-3)).any()), 'pitch condition differs away from a near tie'
         if bool(flips.any()):
             continue
-        # raw durations of the 4-layer FFT predictors (values up to ~7 frames at alpha 0.9) carry up to 1.3e-3
-        # RELATIVE error at tf32 (scratch/debug_mfp2.py: max-abs 8e-3): a "documented .5 tie" here is a reference
-        # value closer to the rounding boundary than the raw-value tolerance _check_durations itself allows
-        tie = 2e-3 * max(1.0, float(ref['dur'].abs().max()))
-        if _check_durations(out['dur'], ref['dur'], tie=tie) == 0:
-            compared += 1
-            assert max_abs(out['mel'].cpu(), ref['mel']) < MEL_ABS and rel_l2(out['mel'].cpu(), ref['mel']) < MEL_REL
-    assert compared >= 1
+        compared += 1
+        _mel_checked(model, (x.to(DEV), semb.to(DEV)), out, ref,
+                     _check_durations(out['dur'], ref['dur'], DUR_WINDOW_MFP), keys=('mel',))
+    assert compared >= 2
 
 
 def test_batched_caller_matches_oracle_per_bucket():
@@ -328,10 +339,7 @@ def test_forward_tacotron_tiny_and_odd_shapes(B, T):
         O.use_library_rnn(False)
     out = model.generate(x.to(DEV))
     torch.cuda.synchronize()
-    if _check_durations(out['dur'], ref['dur']) == 0:
-        assert out['mel'].shape == ref['mel'].shape
-        for k in ('mel', 'mel_post'):
-            assert max_abs(out[k].cpu(), ref[k]) < MEL_ABS and rel_l2(out[k].cpu(), ref[k]) < MEL_REL, k
+    _mel_checked(model, (x.to(DEV),), out, ref, _check_durations(out['dur'], ref['dur']))
 
 
 def test_forward_tacotron_generate_jit_twin():
