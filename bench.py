@@ -25,8 +25,29 @@ sys.path.insert(0, ROOT)
 
 METRIC = 'mel_frames_per_sec'
 UNIT = 'frames/s'
-B, T = 64, 200
 SEED = 1234
+# BASELINE.json configs.  'weak': every rank runs `batch` sentences (the driver's scaling run);
+# 'strong': `batch` is the GLOBAL batch, sentence-sharded over the ranks (configs 4 and 5 are defined that way).
+WORKLOADS = {
+    'config2': dict(model='forward_tacotron', batch=64, T=200, alpha=1.0, scaling='weak', durations='fallback',
+                    name='ForwardTacotron singlespeaker generate()'),
+    'config3': dict(model='fast_pitch', batch=64, T=200, alpha=1.0, scaling='weak', durations='spread',
+                    name='FastPitch (FFT-block variant) generate()'),
+    'config4': dict(model='multi_forward_tacotron', batch=128, T=200, alpha=1.0, scaling='strong', durations='fallback',
+                    name='MultiForwardTacotron generate() with 256-d speaker embedding'),
+    'config5': dict(model='forward_tacotron', batch=32, T=4096, alpha=0.8, scaling='strong', durations='fallback',
+                    name='ForwardTacotron long-article generate()'),
+}
+
+
+def workload_config(wl, durations, world):
+    """The `config` object both arms print (same dict -> the driver's same_config check passes)."""
+    w = WORKLOADS[wl]
+    per = f"{w['batch']}x{w['T']} phonemes per GPU" if w['scaling'] == 'weak' else \
+        f"{w['batch']}x{w['T']} phonemes sentence-sharded over the GPUs"
+    return {'workload': f"{w['name']}, {per}, alpha={w['alpha']}, random-init, durations={durations}",
+            'baseline_config': wl, 'model': w['model'], 'batch': w['batch'], 'tokens': w['T'], 'alpha': w['alpha'],
+            'durations': durations, 'scaling': w['scaling']}
 
 
 def load_peaks():
@@ -39,12 +60,12 @@ def load_peaks():
         return {'hbm': 6650.0, 'bf16': 1590.0, 'bf16_sustained': 1400.0, 'source': 'fallback (B200_PROFILING.md)'}
 
 
-def build_model(durations: str):
+def build_model(durations: str, tag: str = 'forward_tacotron'):
     """Random-init weights of the named architecture (there is no checkpoint to download)."""
     from forwardtacotron_b200.configs import default_config
     from forwardtacotron_b200.models import init_tts_model
     torch.manual_seed(SEED)
-    model = init_tts_model(default_config('forward_tacotron'))
+    model = init_tts_model(default_config(tag))
     if durations == 'spread':           # SURVEY §8d regime B: shift the duration head so durations vary
         with torch.no_grad():
             model.dur_pred.lin.weight.mul_(8.0)
@@ -52,9 +73,15 @@ def build_model(durations: str):
     return model.eval()
 
 
-def make_tokens(batch, rank=0):
-    g = torch.Generator().manual_seed(SEED + rank)
+def make_tokens(batch, T, rank=0, step=0):
+    g = torch.Generator().manual_seed(SEED + rank + 7919 * step)
     return torch.randint(1, 135, (batch, T), generator=g, dtype=torch.int64)
+
+
+def make_speaker(batch, rank=0):
+    g = torch.Generator().manual_seed(SEED + 31 + rank)
+    e = torch.randn(batch, 256, generator=g)
+    return e / e.norm(dim=1, keepdim=True)            # resemblyzer embeddings are unit-norm
 
 
 class ClockSampler:
@@ -144,18 +171,28 @@ class ClockSampler:
                 'source': 'nvml' if self.nvml is not None else 'nvidia-smi'}
 
 
-def cpu_forward_timing(sd, batch, runs, warm, threads):
+def cpu_forward_timing(sd, batch, runs, warm, threads, wl='config2', device='cpu'):
     """Oracle port of the reference's generate() on the host cores (fused library GRU/LSTM = the kernels the
-    reference itself reaches through torch.nn)."""
+    reference itself reaches through torch.nn); device='cuda': the same eager PyTorch program on the GPU (cuDNN / cuBLAS
+    eager, what `tts_model.to(device)` of gen_forward.py:66-67 gives a user of the reference on this box)."""
     from oracle import ft_oracle as O
     torch.set_num_threads(threads)
-    x = make_tokens(batch)
+    w = WORKLOADS[wl]
+    gen = {'forward_tacotron': O.ft_generate, 'fast_pitch': O.fp_generate,
+           'multi_forward_tacotron': O.mft_generate}[w['model']]
+    x = make_tokens(batch, w['T']).to(device)
+    args = (x, make_speaker(batch).to(device)) if w['model'].startswith('multi') else (x,)
+    sd = {k: v.to(device) for k, v in sd.items()}
     O.use_library_rnn(True)
     times, frames = [], 0
     try:
         for i in range(warm + runs):
+            if device != 'cpu':
+                torch.cuda.synchronize()
             t0 = time.perf_counter()
-            out = O.ft_generate(sd, x)
+            out = gen(sd, *args, alpha=w['alpha'])
+            if device != 'cpu':
+                torch.cuda.synchronize()
             dt = time.perf_counter() - t0
             if i >= warm:
                 times.append(dt)
@@ -165,25 +202,44 @@ def cpu_forward_timing(sd, batch, runs, warm, threads):
     return frames, times
 
 
+def reference_sample(wl, total_runs):
+    """Sentences per CPU step: the workload's whole per-GPU batch when `total_runs` of it fit in ~4 minutes of host time
+    (config 2: ~1 s per 64x200 step), else a bounded sample of it."""
+    w = WORKLOADS[wl]
+    est = 1.0 * w['batch'] * w['T'] / (64 * 200)             # ~1 s per 12 800 tokens on 16-32 host cores
+    batch = w['batch']
+    while batch > 1 and total_runs * est * batch / w['batch'] > 240:
+        batch //= 2
+    return batch
+
+
 def run_reference(args, rank, world):
+    """`--impl reference` / `--impl eager-gpu`: rank 0 alone runs; the other ranks exit 0 without work."""
     if rank != 0:
         return
+    wl = args.workload
+    w = WORKLOADS[wl]
+    durations = args.durations or w['durations']
     threads = os.cpu_count() or 1
-    model = build_model(args.durations)
+    model = build_model(durations, w['model'])
     sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
-    total = args.steps + args.warmup
-    batch = B if total * 5.0 <= 240 else (16 if total * 1.3 <= 240 else 4)
-    frames, times = cpu_forward_timing(sd, batch, args.steps, args.warmup, threads)
+    gpu = args.impl == 'eager-gpu'
+    batch = w['batch'] if gpu else reference_sample(wl, args.steps + args.warmup)
+    frames, times = cpu_forward_timing(sd, batch, args.steps, args.warmup, threads, wl, 'cuda' if gpu else 'cpu')
     sec = sum(times) / len(times)
     value = frames / sec
-    sample = f'{batch} of {B} sentences x {T} phonemes per step (same model, same token distribution)'
-    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+    sample = f"{batch} of {w['batch']} sentences x {w['T']} phonemes per step (same model, same token distribution)"
+    line = {'impl': args.impl, 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': f'ForwardTacotron singlespeaker generate(), {B}x{T} phonemes, alpha=1.0, '
-                                   f'random-init, durations={args.durations}', 'frames_per_step': frames},
+            'scaling': w['scaling'], 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': workload_config(wl, durations, world), 'frames_per_step': frames,
             'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': threads, 'kind': 'port', 'sample': sample},
             'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    if gpu:
+        del line['cpu_baseline']
+        line['note'] = ('informative leg: the oracle port of generate() as eager PyTorch on ONE B200 (cuDNN GRU/LSTM, '
+                        'cuBLAS/cuDNN convolutions, torch defaults: fp32 matmuls, cuDNN convolutions may use TF32) -- what a user of the reference gets from '
+                        'tts_model.to(device) (gen_forward.py:66-67); wall-clock around generate() + synchronize')
     print(json.dumps(line), flush=True)
 
 
@@ -196,11 +252,27 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     peaks = load_peaks()
-    model = build_model(args.durations).to(dev)
+    wl = args.workload
+    w = WORKLOADS[wl]
+    durations = args.durations or w['durations']
+    T, alpha = w['T'], w['alpha']
+    multi = w['model'].startswith('multi')
+    model = build_model(durations, w['model']).to(dev)
     handle = rt.Handle.get(dev)
-    x_pin = make_tokens(B, rank).pin_memory()
+    if w['scaling'] == 'weak':                       # every rank its own batch
+        B = w['batch']
+        x_pin = make_tokens(B, T, rank).pin_memory()
+        semb = make_speaker(B, rank).to(dev) if multi else None
+    else:                                            # one global batch, sentence-sharded (parallel.shard_slice)
+        sl = par.shard_slice(w['batch'], rank, world)
+        B = sl.stop - sl.start
+        x_pin = make_tokens(w['batch'], T)[sl].contiguous().pin_memory()
+        semb = make_speaker(w['batch'])[sl].contiguous().to(dev) if multi else None
     x_dev = x_pin.to(dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    def generate(x):
+        return model.generate(x, semb, alpha=alpha) if multi else model.generate(x, alpha=alpha)
 
     def barrier():
         if world > 1:
@@ -208,11 +280,12 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize(dev)
 
     for _ in range(max(args.warmup, 3)):
-        out = model.generate(x_dev)
+        out = generate(x_dev)
     torch.cuda.synchronize(dev)
     frames = int((out['dur'] + 0.5).long().sum())                        # valid mel frames per step (this rank)
     M = out['mel'].shape[2]
     host_out = torch.empty(out['mel_post'].shape, dtype=torch.float32).pin_memory()
+    b_cap = w['batch'] if w['scaling'] == 'weak' else -(-w['batch'] // world)
 
     def timed(step_fn):
         evs = []
@@ -232,13 +305,15 @@ def run_ours(args, rank, world, local_rank):
         return float(t.item())
 
     def step_resident():
-        model.generate(x_dev)
+        generate(x_dev)
 
     def step_e2e():
         xd = x_pin.to(dev, non_blocking=True)
-        o = model.generate(xd)
-        if world > 1:            # the path's only collective: gather of the variable-length mels over NVLink
-            par.gather_variable_mels(o['mel_post'], par.mel_lengths(o['dur']))
+        o = generate(xd)
+        if world > 1:
+            # the path's only exchange: the variable-length mels travel to ONE consumer (rank 0) over NVLink, point to
+            # point, sized by a device-side metadata all_gather; no rank but the consumer ever syncs with its host
+            par.gather_variable_mels(o['mel_post'], par.mel_lengths(o['dur']), dst=0, b_cap=b_cap)
         host_out.copy_(o['mel_post'], non_blocking=True)
 
     with ClockSampler(local_rank) as clocks:
@@ -252,7 +327,7 @@ def run_ours(args, rank, world, local_rank):
         st = model.__dict__['_accel']
         per = {}
         for key in (('tok', B, T), ('frame', B, M)):
-            prog = st['programs'][key]
+            prog = model.program_for(*key)
             for rep in range(4):
                 flush.zero_()
                 for i, (info, ms) in enumerate(prog.run_timed()):
@@ -265,7 +340,7 @@ def run_ours(args, rank, world, local_rank):
         for rep in range(4):
             flush.zero_()
             handle.timing = []
-            model.generate(x_dev)
+            generate(x_dev)
             torch.cuda.synchronize(dev)
             if rep:
                 for name, a, b in handle.timing:
@@ -297,8 +372,12 @@ def run_ours(args, rank, world, local_rank):
             k['handoff'] = info.get('handoff')
             k['kernel_launches'] = info.get('kernel_launches')
         kernels.append((k, info))
-    C = model.lstm.input_size
-    lr_bytes = {'lr_gather': 4.0 * B * T * C + 4.0 * B * T + 4.0 * B * M * C, 'lr_scan': 2 * 4.0 * B * T}
+    lr_buf = model.program_for('frame', B, M).bufs['lr']
+    C = lr_buf.shape[1]
+    # bytes the gather really moves: fp32 source rows + durations + the regulated rows in the dtype the product path
+    # writes (fp16 operand copy for the BiLSTM's W_ih GEMM: 2 bytes per element, not SURVEY 8d's fp32 figure)
+    lr_bytes = {'lr_gather': 4.0 * B * T * C + 4.0 * B * T + float(lr_buf.element_size()) * B * M * C,
+                'lr_scan': 2 * 4.0 * B * T}
     for name, ms in lr_ms.items():
         k = {'side': 'lr', 'label': name, 'kind': 'glue', 'ms': round(ms, 4),
              'gbs': round(lr_bytes[name] / ms / 1e6, 1), 'note': 'event-timed around the C-ABI call (includes launch gaps)'}
@@ -354,7 +433,7 @@ def run_ours(args, rank, world, local_rank):
         tr_files, traffic = [], {}
     for e in by_kernel:
         t = traffic.get(e['kernel'])
-        if t and args.durations == 'fallback':
+        if t and wl == 'config2' and durations == 'fallback':
             e['traffic'] = t['dram_bytes_per_step']
             e['traffic_note'] = f"DRAM bytes per step over its {t['launches_per_step']} launches, profiles/{tr_files[-1]}"
             e['algorithmic'] = (groups[e['kernel']]['bytes'] if e['bound'] == 'hbm' else None)
@@ -366,19 +445,21 @@ def run_ours(args, rank, world, local_rank):
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         sd = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
-        cf, ct = cpu_forward_timing(sd, 16, runs=2, warm=1, threads=threads)
+        nb = reference_sample(wl, 3)
+        cf, ct = cpu_forward_timing(sd, nb, runs=2, warm=1, threads=threads, wl=wl)
         cpu = {'value': cf / (sum(ct) / len(ct)), 'unit': UNIT, 'cores': threads, 'kind': 'port',
-               'sample': f'16 of {B} sentences x {T} phonemes, oracle port of generate(), 1 warm-up + 2 timed runs'}
+               'sample': f"{nb} of {w['batch']} sentences x {T} phonemes per step (the --impl reference sample), "
+                         'oracle port of generate(), 1 warm-up + 2 timed runs'}
 
     sec = ms_value / 1e3
     line = {'metric': METRIC, 'value': total_frames * args.steps / sec, 'unit': UNIT, 'n_gpus': world,
             'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_value / args.steps,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'tf32+f16',
+            'higher_is_better': True, 'scaling': w['scaling'], 'vs_baseline': None, 'dtype': 'tf32+f16',
             'data': 'synthetic',
-            'config': {'workload': f'ForwardTacotron singlespeaker generate(), {B}x{T} phonemes per GPU, alpha=1.0, '
-                                   f'random-init, durations={args.durations}', 'frames_per_step_per_gpu': frames,
-                       'padded_mel_len': M, 'l2': 'flushed between timed iterations (512 MiB memset)',
-                       'parallelism': f'sentence-sharded replicas x{world}'},
+            'config': workload_config(wl, durations, world),
+            'run': {'frames_per_step_rank0': frames, 'sentences_rank0': B, 'padded_mel_len_rank0': M,
+                    'l2': 'flushed between timed iterations (512 MiB memset)',
+                    'parallelism': f'sentence-sharded x{world}, weights replicated'},
             'e2e': {'value': total_frames * args.steps / (ms_e2e / 1e3), 'unit': UNIT,
                     'h2d_bytes_per_step': x_pin.numel() * 8, 'd2h_bytes_per_step': host_out.numel() * 4},
             'gpu_launches': int(launches), 'clocks': clk, 'roofline': roof, 'roofline_by_kernel': by_kernel,
@@ -396,8 +477,11 @@ def main():
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
-    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--durations', default='fallback', choices=['fallback', 'spread'],
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference', 'eager-gpu'])
+    ap.add_argument('--workload', default='config2', choices=sorted(WORKLOADS),
+                    help='BASELINE.json config: config2 (default, the headline), config3 FastPitch, config4 MultiFT 128 '
+                         'sharded, config5 32x4096 sharded')
+    ap.add_argument('--durations', default=None, choices=['fallback', 'spread'],
                     help="'fallback': as-is random init -> every duration 2 (forward_tacotron.py:176-177); "
                          "'spread': duration head shifted so durations vary (SURVEY §8d regime B)")
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -405,7 +489,7 @@ def main():
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
-    if args.impl == 'reference':
+    if args.impl in ('reference', 'eager-gpu'):
         run_reference(args, rank, world)
     else:
         run_ours(args, rank, world, local_rank)

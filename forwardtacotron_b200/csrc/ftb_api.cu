@@ -52,7 +52,7 @@ extern "C" int ftb_create(int device, ftb_handle* out) {
 
 extern "C" int ftb_destroy(ftb_handle h) {
   if (!h) return FTB_E_ARG;
-  for (auto& kv : h->gemm_plans) cudaFree(kv.second.dev);
+  for (auto& kv : h->gemm_plans) gemm_plan_free(kv.second);
   for (auto& kv : h->rnn_plans) rnn_plan_free(kv.second);
   delete h;
   return 0;
@@ -95,9 +95,17 @@ extern "C" int ftb_gemm_plan_destroy(ftb_handle h, int plan) {
   DeviceScope scope(h->device);
   auto it = h->gemm_plans.find(plan);
   if (it == h->gemm_plans.end()) return FTB_E_PLAN;
-  cudaFree(it->second.dev);
+  gemm_plan_free(it->second);
   h->gemm_plans.erase(it);
   return 0;
+}
+
+extern "C" int ftb_gemm_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream) {
+  if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
+  auto it = h->gemm_plans.find(plan);
+  if (it == h->gemm_plans.end()) return FTB_E_PLAN;
+  return gemm_plan_set_geometry(it->second, seq_len, seq_stride, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems, int nproblems, int* plan_out) {
@@ -105,7 +113,7 @@ extern "C" int ftb_rnn_plan_create(ftb_handle h, const ftb_rnn_problem* problems
   DeviceScope scope(h->device);
   RnnPlan plan;
   const int rc = rnn_plan_build(problems, nproblems, h->num_sms, &plan);
-  if (rc) return rc;
+  if (rc) { rnn_plan_free(plan); return rc; }      // releases whatever the build had created before it failed
   const int id = h->next_plan++;
   h->rnn_plans[id] = plan;
   *plan_out = id;
@@ -119,6 +127,14 @@ extern "C" int ftb_rnn_plan_run(ftb_handle h, int plan, void* stream) {
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
   h->launches += static_cast<int64_t>(it->second.launches.size() + it->second.hx.size());   // + sentinel pre-fills (L2 hand-off)
   return rnn_plan_launch(it->second, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ftb_rnn_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream) {
+  if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
+  auto it = h->rnn_plans.find(plan);
+  if (it == h->rnn_plans.end()) return FTB_E_PLAN;
+  return rnn_plan_set_geometry(it->second, seq_len, seq_stride, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int ftb_rnn_plan_info(ftb_handle h, int plan, int* handoff, int* kernel_launches, int* lanes) {

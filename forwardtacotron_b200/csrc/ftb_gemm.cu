@@ -354,8 +354,12 @@ __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool re
 
 // ------------------------------------------------------------------------------------------
 template <bool PAIR>
-__device__ __forceinline__ void conv_gemm_tc_body(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
+__device__ __forceinline__ void conv_gemm_tc_body(const GemmProblemDev* __restrict__ probs, int nprob) {
   extern __shared__ uint8_t smem_raw[];
+  // schedule slots at the plan's CURRENT geometry: plan metadata the host uploads (ftb_gemm_plan_set_geometry), not an
+  // output of the preceding kernel, and not a kernel argument -- a captured CUDA graph replays with whatever sequence
+  // length the records hold
+  const int total_tiles = probs[0].plan_tiles;
   // 1024-byte alignment by pointer arithmetic on the __shared__ array (an integer round trip would demote every
   // later access through `tail` to generic LD/ST, which the epilogue pays for in latency)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -689,13 +693,13 @@ __device__ __forceinline__ void conv_gemm_tc_body(const GemmProblemDev* __restri
 }
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
-  conv_gemm_tc_body<false>(probs, nprob, total_tiles);
+conv_gemm_tc_kernel(const GemmProblemDev* __restrict__ probs, int nprob) {
+  conv_gemm_tc_body<false>(probs, nprob);
 }
 // CTA-pair form: launched with a cluster dimension of 2; `total_tiles` counts tile PAIRS.
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-conv_gemm_tc_pair_kernel(const GemmProblemDev* __restrict__ probs, int nprob, int total_tiles) {
-  conv_gemm_tc_body<true>(probs, nprob, total_tiles);
+conv_gemm_tc_pair_kernel(const GemmProblemDev* __restrict__ probs, int nprob) {
+  conv_gemm_tc_body<true>(probs, nprob);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -858,6 +862,7 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
       d.m_step = BM; d.m_shift = 0;
     }
     d.m_tiles = static_cast<int>((q.rows + d.m_step - 1) / d.m_step);
+    d.cap_rows = q.rows;
     d.tile_base = tile_base;
     tile_base += (pair ? (d.m_tiles + 1) / 2 : d.m_tiles) * d.n_tiles;
     int rc = make_map(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
@@ -867,6 +872,7 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     const long long e = q.rows * q.n;
     if (e > simt_elems) simt_elems = e;
   }
+  for (GemmProblemDev& d : host) d.plan_tiles = tile_base;
   GemmProblemDev* dev = nullptr;
   cudaError_t ce = cudaMalloc(&dev, sizeof(GemmProblemDev) * nproblems);
   if (ce != cudaSuccess) return static_cast<int>(ce);
@@ -874,7 +880,39 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
   if (ce != cudaSuccess) { cudaFree(dev); return static_cast<int>(ce); }
   plan->dev = dev; plan->nprob = nproblems; plan->total_tiles = tile_base; plan->simt_elems = simt_elems;
   plan->pair = pair;
+  plan->cap_tiles = tile_base;
+  plan->host = new std::vector<GemmProblemDev>(std::move(host));
   return 0;
+}
+
+void gemm_plan_free(GemmPlan& plan) {
+  cudaFree(plan.dev);
+  delete plan.host;
+  plan = GemmPlan();
+}
+
+// Launch-time geometry: the same buffers (allocated for cap_rows) hold `batch` sentences of `seq_len` rows at stride
+// `seq_stride` -- rows, tile grid and schedule are recomputed and the records re-uploaded in stream order, so a program
+// built once per capacity bucket serves every sequence length inside it (generate() sees a new length on almost every
+// call with real text).  The caller keeps the rows t in [seq_len, seq_stride) of every sentence zero.
+int gemm_plan_set_geometry(GemmPlan& plan, int seq_len, int seq_stride, cudaStream_t stream) {
+  if (!plan.host || seq_len < 1 || seq_stride < seq_len) return FTB_E_ARG;
+  std::vector<GemmProblemDev>& host = *plan.host;
+  int tile_base = 0;
+  for (GemmProblemDev& d : host) {
+    const long long rows = static_cast<long long>(d.batch) * seq_stride;
+    if (rows > d.cap_rows) return FTB_E_LIMIT;
+    d.rows = rows; d.seq_len = seq_len; d.seq_stride = seq_stride;
+    d.m_tiles = static_cast<int>((rows + d.m_step - 1) / d.m_step);
+    d.tile_base = tile_base;
+    tile_base += (plan.pair ? (d.m_tiles + 1) / 2 : d.m_tiles) * d.n_tiles;
+  }
+  if (tile_base > plan.cap_tiles) return FTB_E_LIMIT;
+  for (GemmProblemDev& d : host) d.plan_tiles = tile_base;
+  plan.total_tiles = tile_base;
+  // pageable source: the runtime stages the bytes before the call returns, so `host` may change again afterwards
+  return static_cast<int>(cudaMemcpyAsync(plan.dev, host.data(), sizeof(GemmProblemDev) * host.size(),
+                                          cudaMemcpyHostToDevice, stream));
 }
 
 int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t stream) {
@@ -899,7 +937,9 @@ int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t s
     if (dev_id >= 0 && dev_id < 64) attr_set[dev_id] = true;
   }
   const int slots = plan.pair ? num_sms / 2 : num_sms;          // schedule slots: CTAs or CTA pairs
-  const int used = plan.total_tiles < slots ? plan.total_tiles : slots;
+  // sized by the capacity geometry: the grid is baked into captured graphs, the tile count is not (a CTA without a
+  // tile at the current geometry sets up, finds its first schedule slot past plan_tiles and leaves)
+  const int used = plan.cap_tiles < slots ? plan.cap_tiles : slots;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(plan.pair ? 2 * used : used);
   cfg.blockDim = dim3(NUM_THREADS);
@@ -921,8 +961,8 @@ int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t s
   cfg.numAttrs = na;
   const GemmProblemDev* dev = plan.dev;
   if (plan.pair)
-    return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_pair_kernel, dev, plan.nprob, plan.total_tiles));
-  return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel, dev, plan.nprob, plan.total_tiles));
+    return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_pair_kernel, dev, plan.nprob));
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel, dev, plan.nprob));
 }
 
 }  // namespace ftb

@@ -42,6 +42,8 @@ struct alignas(128) GemmProblemDev {
   int m_step, m_shift;   // tile i covers rows [i*m_step + m_shift, +128)
   int tile_base;         // first global tile id
   int kelems;            // operand elements per 128-byte k-block: 32 (tf32) or 64 (fp16, FTB_F_A_F16)
+  int plan_tiles;        // schedule slots of the whole plan at the CURRENT geometry (the kernels read record 0)
+  long long cap_rows;    // rows the buffers / tensor maps were built for (ftb_gemm_plan_set_geometry may not exceed it)
 };
 
 struct GemmPlan {
@@ -50,10 +52,14 @@ struct GemmPlan {
   int total_tiles = 0;
   long long simt_elems = 0;   // max rows*n over problems (SIMT cross-check grid)
   bool pair = false;          // CTA-pair plan: total_tiles / tile_base count tile pairs, tm_w boxes hold bn/2 rows
+  int cap_tiles = 0;          // total_tiles at the geometry the plan was built with (sizes the grid; >= total_tiles)
+  std::vector<GemmProblemDev>* host = nullptr;   // host copy of the records (re-uploaded by gemm_plan_set_geometry)
 };
 
 int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* plan);
 int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t stream);
+int gemm_plan_set_geometry(GemmPlan& plan, int seq_len, int seq_stride, cudaStream_t stream);
+void gemm_plan_free(GemmPlan& plan);
 
 // ------------------------------------------------------------------ recurrences (ftb_rnn.cu)
 struct RnnProblemDev {
@@ -102,10 +108,13 @@ struct RnnPlan {
   std::vector<void*> hx;                   // per problem: fp16 exchange tensor (owned by the plan)
   std::vector<size_t> hx_bytes;
   std::vector<RnnLaunch> launches;
+  std::vector<RnnProblemDev> host_parts;   // host copy of `dev` (re-uploaded by rnn_plan_set_geometry)
+  int cap_len = 0, cap_stride = 0;         // geometry the plan (exchange tensors included) was built for
 };
 
 int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, RnnPlan* plan);
 int rnn_plan_launch(RnnPlan& plan, cudaStream_t stream);
+int rnn_plan_set_geometry(RnnPlan& plan, int seq_len, int seq_stride, cudaStream_t stream);
 void rnn_plan_free(RnnPlan& plan);
 
 }  // namespace ftb

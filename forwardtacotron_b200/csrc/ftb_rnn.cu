@@ -839,12 +839,17 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
       for (int i = 1; i < lanes; ++i) {
         cudaStream_t st = nullptr;
         cudaEvent_t ev = nullptr;
-        if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return FTB_E_ARG;
-        if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return FTB_E_ARG;
+        cudaError_t se = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+        if (se != cudaSuccess) return static_cast<int>(se);
         plan->side.push_back(st);
+        se = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        if (se != cudaSuccess) return static_cast<int>(se);
         plan->joined.push_back(ev);
       }
-      if (lanes > 1 && cudaEventCreateWithFlags(&plan->forked, cudaEventDisableTiming) != cudaSuccess) return FTB_E_ARG;
+      if (lanes > 1) {
+        const cudaError_t fe = cudaEventCreateWithFlags(&plan->forked, cudaEventDisableTiming);
+        if (fe != cudaSuccess) return static_cast<int>(fe);
+      }
     }
   }
   if (!plan->cluster && any_precise) return FTB_E_RESIDENT;      // no silent loss of precision on the L2 path
@@ -870,7 +875,24 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
   plan->ngroups = ngroups;
   plan->launches = launches;
   plan->problems.assign(problems, problems + nproblems);
+  plan->host_parts = parts;
+  plan->cap_len = problems[0].seq_len;
+  plan->cap_stride = problems[0].seq_stride;
+  for (int i = 1; i < nproblems; ++i) {
+    if (problems[i].seq_len < plan->cap_len) plan->cap_len = problems[i].seq_len;
+    if (problems[i].seq_stride < plan->cap_stride) plan->cap_stride = problems[i].seq_stride;
+  }
   return 0;
+}
+
+// Launch-time geometry (see gemm_plan_set_geometry): every problem of the plan runs `seq_len` steps over rows at
+// stride `seq_stride`; buffers and the L2 exchange tensors keep the capacity they were built with.
+int rnn_plan_set_geometry(RnnPlan& plan, int seq_len, int seq_stride, cudaStream_t stream) {
+  if (seq_len < 1 || seq_stride < seq_len) return FTB_E_ARG;
+  if (seq_len > plan.cap_len || seq_stride > plan.cap_stride) return FTB_E_LIMIT;
+  for (RnnProblemDev& d : plan.host_parts) { d.seq_len = seq_len; d.seq_stride = seq_stride; }
+  return static_cast<int>(cudaMemcpyAsync(plan.dev, plan.host_parts.data(), sizeof(RnnProblemDev) * plan.host_parts.size(),
+                                          cudaMemcpyHostToDevice, stream));
 }
 
 void rnn_plan_free(RnnPlan& plan) {

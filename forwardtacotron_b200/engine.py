@@ -49,20 +49,55 @@ def _order_tiles(pending):
     return sorted(pending, key=lambda q: -_tile_cost(q))
 
 
+def capacity_bucket(n: int) -> int:
+    """Sequence-length capacity a program is built for: the next multiple of 64 (256 beyond 1024).  Only buffer sizes
+    follow the bucket; rows, tiles and steps follow the actual length (Program.set_seq_len), so no work is padded."""
+    step = 64 if n <= 1024 else 256
+    return (n + step - 1) // step * step
+
+
 class Geometry:
-    """Row geometry of a [batch, seq_len, C] activation in the padded-flat layout."""
+    """Row geometry of a [batch, seq_len, C] activation in the padded-flat layout.  Buffers are allocated for
+    `cap` >= seq_len rows per sentence (+ the gap); seq_len / stride / rows are the CURRENT layout inside them."""
 
     def __init__(self, batch: int, seq_len: int):
-        self.batch, self.seq_len = batch, seq_len
+        self.batch, self.cap = batch, seq_len
+        self.cap_rows = batch * rt.seq_stride(seq_len)
+        self.set_len(seq_len)
+
+    def set_len(self, seq_len: int):
+        assert 1 <= seq_len <= self.cap, (seq_len, self.cap)
+        self.seq_len = seq_len
         self.stride = rt.seq_stride(seq_len)
-        self.rows = batch * self.stride
+        self.rows = self.batch * self.stride
+
+
+class _Bufs(dict):
+    """name -> tensor.  Padded-flat activations are stored at capacity; dense tensors with a sequence axis (shape
+    marker -1 in Program.dense) are handed out as the view of the CURRENT length over the head of their storage."""
+
+    def __init__(self, prog):
+        super().__init__()
+        self.prog, self.dyn = prog, {}
+
+    def __getitem__(self, k):
+        t = dict.__getitem__(self, k)
+        shape = self.dyn.get(k)
+        if shape is None:
+            return t
+        cur = tuple(self.prog.geo.seq_len if d == -1 else d for d in shape)
+        n = 1
+        for d in cur:
+            n *= d
+        return t.view(-1)[:n].view(cur)
 
 
 class Program:
     def __init__(self, handle: rt.Handle, geo: Geometry):
         self.h, self.geo = handle, geo
         self.device = handle.device
-        self.bufs: Dict[str, torch.Tensor] = {}
+        self.bufs: Dict[str, torch.Tensor] = _Bufs(self)
+        self._flat: List[str] = []                    # names of the padded-flat activation buffers
         self.steps: List[Callable[[], None]] = []
         self._gemm_plans: List[int] = []
         self._rnn_plans: List[int] = []
@@ -74,8 +109,8 @@ class Program:
         # CUDA graph of the launch list: captured on the second run() (the first one runs eagerly so one-time
         # cudaFuncSetAttribute calls happen outside capture), re-captured when a launch-time scalar changes
         self.use_graph = os.environ.get('FTB_CUDA_GRAPHS', '1') != '0'
-        self._graph = None
-        self._graph_key = None
+        self._graphs: Dict[tuple, object] = {}        # (launch-time scalars, seq_len) -> captured graph
+        self._baked_len = False                       # a glue kernel takes seq_len as a kernel ARGUMENT
         self._eager_runs = 0
 
     # ---- buffers ---------------------------------------------------------------------------
@@ -83,21 +118,52 @@ class Program:
         """Zero-initialised [rows, cols] activation; gap rows are never written so they stay zero.  fp16 buffers are
         GEMM-to-GEMM operands (FTB_F_OUT_F16 producer, FTB_F_A_F16 consumer)."""
         if name not in self.bufs:
-            self.bufs[name] = torch.zeros((self.geo.rows, cols), dtype=dtype, device=self.device)
+            self.bufs[name] = torch.zeros((self.geo.cap_rows, cols), dtype=dtype, device=self.device)
+            self._flat.append(name)
         b = self.bufs[name]
         assert b.shape[1] == cols and b.dtype == dtype, (name, b.shape, cols, b.dtype)
         return b
 
     def dense(self, name: str, shape, dtype=torch.float32) -> torch.Tensor:
+        """Dense tensor; a -1 in `shape` marks the sequence axis: storage is sized for the capacity and
+        self.bufs[name] is always the contiguous view of the current length over its head."""
         if name not in self.bufs:
-            self.bufs[name] = torch.zeros(shape, dtype=dtype, device=self.device)
+            full = tuple(self.geo.cap if d == -1 else d for d in shape)
+            dict.__setitem__(self.bufs, name, torch.zeros(full, dtype=dtype, device=self.device))
+            if -1 in shape:
+                self.bufs.dyn[name] = tuple(shape)
         return self.bufs[name]
 
     def view(self, name: str) -> torch.Tensor:
-        """[batch, seq_len, C] view of a padded-flat buffer (valid rows only)."""
+        """[batch, seq_len, C] view of a padded-flat buffer (valid rows only) at the current geometry."""
         b = self.bufs[name]
         g = self.geo
-        return b.view(g.batch, g.stride, b.shape[1])[:, :g.seq_len]
+        return b[:g.rows].view(g.batch, g.stride, b.shape[1])[:, :g.seq_len]
+
+    def set_seq_len(self, seq_len: int):
+        """Re-point the whole program at sentences of `seq_len` <= capacity rows (ftb_*_plan_set_geometry): plans keep
+        their buffers, tensor maps and captured graphs; rows that become gap rows under the new stride are zeroed, the
+        invariant every convolution tap relies on (include/ftb200.h)."""
+        self.flush()
+        g = self.geo
+        if seq_len == g.seq_len:
+            return
+        g.set_len(seq_len)
+        for name in self._flat:
+            b = dict.__getitem__(self.bufs, name)
+            b[:g.rows].view(g.batch, g.stride, b.shape[1])[:, seq_len:].zero_()
+        for plan in self._gemm_plans:
+            self.h.gemm_set_geometry(plan, seq_len, g.stride)
+        for plan in self._rnn_plans:
+            self.h.rnn_set_geometry(plan, seq_len, g.stride)
+        valid = g.batch * seq_len
+        for i in self.info:
+            if 'flops_row' in i:
+                i['flops'], i['bytes'] = i['flops_row'] * valid, i['bytes_row'] * valid + i['bytes_fixed']
+                if 'flops_f16_row' in i:
+                    i['flops_f16'] = i['flops_f16_row'] * valid
+                if 'steps' in i:
+                    i['steps'] = seq_len
 
     # ---- GEMM problems: queued, then flushed as one persistent launch ------------------------
     def gemm(self, a: torch.Tensor, w: PackedGemm, out: Optional[torch.Tensor], *, out_col0: int = 0,
@@ -161,6 +227,8 @@ class Program:
 
     def _flush_glue(self):
         g = self.geo
+        if self._glue:
+            self._baked_len = True
         while self._glue:
             kind = self._glue[0][0]
             items = [it for _, it in self._glue[:rt.MAX_GLUE_ITEMS]]
@@ -193,8 +261,11 @@ class Program:
             nbytes = sum((2.0 if q.flags & rt.F_A_F16 else 4.0) * (valid * q.cin + q.taps * q.n * q.cin) +
                          (2.0 if q.flags & rt.F_OUT_F16 else 4.0) * valid * q.n for q in grp)
             labels = sorted({getattr(q, '_label', '') for q in grp})
+            wbytes = sum((2.0 if q.flags & rt.F_A_F16 else 4.0) * q.taps * q.n * q.cin for q in grp)
             self.info.append({'kind': 'gemm', 'label': '+'.join(l for l in labels if l) or 'gemm',
                               'flops': flops, 'flops_f16': flops_f16, 'bytes': nbytes, 'problems': len(grp),
+                              'flops_row': flops / valid, 'flops_f16_row': flops_f16 / valid,
+                              'bytes_row': (nbytes - wbytes) / valid, 'bytes_fixed': wbytes,
                               **self.h.gemm_info(plan)})
 
     def rnn(self, specs, lens: Optional[torch.Tensor] = None, pad_value: float = 0.0):
@@ -223,11 +294,14 @@ class Program:
         # x-projection read + h write per step, W_hh once
         nbytes = sum(4.0 * valid * (2 * (4 if r.cell else 3) * r.hidden + 2 * r.hidden) + 4.0 * r.w_hh.numel()
                      for r, _, _, _ in specs)
+        wbytes = sum(4.0 * r.w_hh.numel() for r, _, _, _ in specs)
         self.info.append({'kind': 'rnn', 'label': self._label or 'rnn', 'flops': flops, 'bytes': nbytes,
+                          'flops_row': flops / valid, 'bytes_row': (nbytes - wbytes) / valid, 'bytes_fixed': wbytes,
                           'steps': g.seq_len, 'problems': len(specs), **self.h.rnn_info(plan)})
 
     def call(self, fn: Callable[[], None], label: str = 'glue', nbytes: float = 0.0):
         self.flush()
+        self._baked_len = True
         self.steps.append(fn)
         self.info.append({'kind': 'glue', 'label': label, 'flops': 0.0, 'bytes': nbytes})
 
@@ -242,12 +316,15 @@ class Program:
     def run(self):
         """Launch every step on the current stream: eagerly the first time, afterwards as ONE CUDA-graph
         replay (a 20-launch program otherwise leaves the SMs idle between its short kernels)."""
-        key = getattr(self, 'alpha', None)                    # scalars baked into kernel arguments
+        # baked into kernel arguments of a captured graph: launch-time scalars, and (glue kernels only -- the GEMM and
+        # recurrence kernels read their geometry from the device records) the sequence length
+        key = (getattr(self, 'alpha', None), self.geo.seq_len if self._baked_len else None)
         if not self.use_graph:
             return self.run_eager()
-        if self._graph is not None and self._graph_key == key:
+        graph = self._graphs.get(key)
+        if graph is not None:
             self.h.replayed_launches += self._launches_per_run     # kernels inside the replayed graph
-            return self._graph.replay()
+            return graph.replay()
         if self._eager_runs < 1:
             self._eager_runs += 1
             n0 = self.h.launch_count()
@@ -266,7 +343,9 @@ class Program:
             warnings.warn(f'forwardtacotron_b200: CUDA-graph capture failed ({exc}); using eager launches')
             self.use_graph = False
             return self.run_eager()
-        self._graph, self._graph_key = graph, key
+        while len(self._graphs) >= 8:                         # a few distinct lengths / scalars stay captured
+            self._graphs.pop(next(iter(self._graphs)))
+        self._graphs[key] = graph
         return graph.replay()          # (the capture pass already counted these launches once in the C counter)
 
     def run_timed(self):
@@ -288,7 +367,7 @@ class Program:
             self.h.gemm_destroy(p)
         for p in self._rnn_plans:
             self.h.rnn_destroy(p)
-        self._graph = None
+        self._graphs = {}
         self._gemm_plans, self._rnn_plans, self.steps = [], [], []
 
     def __del__(self):

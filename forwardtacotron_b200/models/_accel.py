@@ -59,16 +59,29 @@ class AcceleratedMixin:
         return st
 
     def _program(self, st: dict, key, builder):
+        """key = (kind, batch, seq_len).  Programs are cached per CAPACITY bucket of the sequence length
+        (engine.capacity_bucket) and re-pointed at the actual length (Program.set_seq_len: a few small uploads and
+        strided memsets): the regulated length M is data dependent and new on almost every call with real text
+        (common_layers.py:23), and a program owns ~20 buffers, tensor maps and a captured graph."""
+        kind, batch, seq_len = key
+        ckey = (kind, batch, eng.capacity_bucket(seq_len))
         progs = st['programs']
-        if key in progs:
-            progs.move_to_end(key)
-            return progs[key]
-        prog = builder()
-        progs[key] = prog
-        while len(progs) > self.MAX_PROGRAMS * 2:
-            _, old = progs.popitem(last=False)
-            old.close()
+        if ckey in progs:
+            progs.move_to_end(ckey)
+            prog = progs[ckey]
+        else:
+            prog = builder(ckey[2])
+            progs[ckey] = prog
+            while len(progs) > self.MAX_PROGRAMS * 2:
+                _, old = progs.popitem(last=False)
+                old.close()
+        prog.set_seq_len(seq_len)
         return prog
+
+    def program_for(self, kind: str, batch: int, seq_len: int):
+        """The cached program that served (kind, batch, seq_len), or None (tests, bench.py)."""
+        st = self.__dict__.get('_accel')
+        return None if st is None else st['programs'].get((kind, batch, eng.capacity_bucket(seq_len)))
 
     @staticmethod
     def _check_tokens(x: torch.Tensor):
@@ -98,8 +111,8 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     hl = prog.buf('lstm.h', 2 * lstm.hidden, odt)
     # channels-last mel: only the postnet bank's operand (the residual uses mel_cl_full): fp16 copy
     mel_cl = prog.buf('mel_cl', n_mels, torch.float16 if (eng.F16_OPERANDS and n_mels % 8 == 0) else torch.float32)
-    mel = prog.dense('mel', (batch, n_mels, M))
-    mel_post = prog.dense('mel_post', (batch, n_mels, M))
+    mel = prog.dense('mel', (batch, n_mels, -1))
+    mel_post = prog.dense('mel_post', (batch, n_mels, -1))
     post = prog.buf('postnet.h', 2 * packs['postnet'].rnn.hidden, odt)
 
     prog.label('lstm_ih')
@@ -122,15 +135,18 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
         g = prog.geo
         v = packs['lin_pad_vec']
         v_r = pk.round_tf32(v)
-        t_idx = torch.arange(g.stride, device=mel_cl.device, dtype=torch.int32)
+        t_all = torch.arange(g.stride, device=mel_cl.device, dtype=torch.int32)
 
         def fix_pad_rows():
-            m = ((t_idx[None, :] >= mel_len[:, None]) & (t_idx[None, :] < M))        # [B, stride]
-            cl = mel_cl.view(batch, g.stride, n_mels)
-            clf = mel_full.view(batch, g.stride, n_mels)
+            L = g.seq_len                                                            # current geometry of the program
+            t_idx = t_all[:g.stride]
+            m = ((t_idx[None, :] >= mel_len[:, None]) & (t_idx[None, :] < L))        # [B, stride]
+            cl = mel_cl[:g.rows].view(batch, g.stride, n_mels)
+            clf = mel_full[:g.rows].view(batch, g.stride, n_mels)
             torch.where(m[:, :, None], v_r.to(cl.dtype), cl, out=cl)
             torch.where(m[:, :, None], v, clf, out=clf)
-            torch.where(m[:, None, :M], v[None, :, None], mel, out=mel)
+            mel_now = prog.bufs['mel']
+            torch.where(m[:, None, :L], v[None, :, None], mel_now, out=mel_now)
         prog.call(fix_pad_rows, label='lin.pad_rows')
     prog.label('')
     levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full, xproj_f16=x16)

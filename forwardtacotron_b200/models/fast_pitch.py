@@ -127,6 +127,10 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
             packs[name + '_lin'] = (f(mod.lin.weight), f(mod.lin.bias))
         return packs
 
+    def _program(self, st: dict, key, builder):
+        self._check_len(st['packs']['prenet'], key[2])       # the ACTUAL length; programs are built per capacity bucket
+        return super()._program(st, key, builder)
+
     def _check_len(self, tp: '_accel.TransformerPack', n: int):
         if n > tp.max_len:
             raise RuntimeError(f'sequence length {n} exceeds PositionalEncoding.max_len={tp.max_len} '
@@ -137,16 +141,15 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         packs, h = st['packs'], st['handle']
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
-        tok = prog.dense('tok', (batch, T), torch.int64)
+        tok = prog.dense('tok', (batch, -1), torch.int64)
         branches, heads = [], []
 
         def add_transformer(tag, tp, table, key_tok):
-            self._check_len(tp, T)
             E = tp.d_model
             x0 = prog.buf(f'{tag}.x', 3 * E, torch.float16) if tp.precise else prog.buf(f'{tag}.x', E)
             x0f = prog.buf(f'{tag}.x_full', E)
             out = prog.buf(f'{tag}.out', E)
-            prog.call(lambda: h.posenc(tok, table, None, tp.pe, tp.scale, E, batch, T, geo.stride, x0,
+            prog.call(lambda: h.posenc(tok, table, None, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0,
                                        round_tf32=3 if tp.precise else True, out_full=x0f),
                       label=f'{tag}.embed+posenc')                      # embedding + x + scale*pe (:143-145)
             branches.append(_accel.transformer_levels(prog, tag, tp, x0, out, key_tok, round_final=False, x_full=x0f))
@@ -161,10 +164,10 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         eng.run_levels(prog, branches)
         for name, out in heads:
             w, b = packs[name + '_lin']
-            y = prog.dense(f'{name}.y', (batch, T))
+            y = prog.dense(f'{name}.y', (batch, -1))
             prog.call(lambda out=out, w=w, b=b, y=y, name=name: h.rowdot(
                 out, out.shape[1], out.shape[1], w, b, 1, prog.alpha if name == 'dur' else 1.0,
-                batch, T, geo.stride, y), label=f'{name}.lin')
+                batch, geo.seq_len, geo.stride, y), label=f'{name}.lin')
         prog.alpha = 1.0
         return prog
 
@@ -173,7 +176,6 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         `masked`: keys where the caller-filled prog.bufs['frame_tok'] is 0 are masked (forward(batch), :151-155)."""
         packs, h = st['packs'], st['handle']
         tp = packs['postnet']
-        self._check_len(tp, M)
         geo = eng.Geometry(batch, M)
         prog = eng.Program(h, geo)
         E = tp.d_model
@@ -181,10 +183,10 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         x0 = prog.buf('postnet.x', E)
         x0f = prog.buf('postnet.x_full', E)
         out = prog.buf('postnet.out', E)
-        mel = prog.dense('mel', (batch, self.n_mels, M))
-        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, M, geo.stride, x0, out_full=x0f),
+        mel = prog.dense('mel', (batch, self.n_mels, -1))
+        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0, out_full=x0f),
                   label='postnet.posenc')
-        frame_tok = prog.dense('frame_tok', (batch, M), torch.int64) if masked else None
+        frame_tok = prog.dense('frame_tok', (batch, -1), torch.int64) if masked else None
         eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, frame_tok, x_full=x0f)])
         prog.label('lin')
         prog.gemm(out, packs['lin'], None, out_t=mel)
@@ -202,7 +204,7 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True))
+            prog = self._program(st, ('tok', B, T), lambda T: self._token_program(st, B, T, True))
             prog.bufs['tok'].copy_(x)
             prog.alpha = float(alpha)
             prog.run()
@@ -220,7 +222,7 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         self._check_tokens(x)
         st = self._accel_state(x.device)
         B, T = x.shape
-        tok = self._program(st, ('tok_masked', B, T), lambda: self._token_program(st, B, T, True, mask_predictors=True))
+        tok = self._program(st, ('tok_masked', B, T), lambda T: self._token_program(st, B, T, True, mask_predictors=True))
         tok.bufs['tok'].copy_(x)
         tok.alpha = 1.0
         tok.run()
@@ -231,7 +233,7 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         cum, lens, M, _ = _accel.length_regulate(st['handle'], dur, apply_fallback=False)
         if M <= 0:
             raise RuntimeError('forward(): all durations are zero -- nothing to synthesise')
-        prog = self._program(st, ('frame_masked', B, M), lambda: self._frame_program(st, B, M, masked=True))
+        prog = self._program(st, ('frame_masked', B, M), lambda M: self._frame_program(st, B, M, masked=True))
         mel_len = batch['mel_len'].to(x.device)
         prog.bufs['frame_tok'].copy_((torch.arange(M, device=x.device)[None, :] < mel_len[:, None]).to(torch.int64))
         out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, tok.bufs['prenet.out'], None, 0, dur,
@@ -247,7 +249,7 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('prenet', B, T), lambda: self._token_program(st, B, T, False))
+            prog = self._program(st, ('prenet', B, T), lambda T: self._token_program(st, B, T, False))
             prog.bufs['tok'].copy_(x)
             prog.run()
             if not (dur_hat.is_cuda and dur_hat.dtype == torch.float32 and dur_hat.is_contiguous()):
@@ -262,7 +264,7 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         if M <= 0:
             raise RuntimeError('generate(): all rounded durations are zero -- nothing to synthesise')
         pre = tok_prog.bufs['prenet.out']
-        prog = self._program(st, ('frame', B, M), lambda: self._frame_program(st, B, M))
+        prog = self._program(st, ('frame', B, M), lambda M: self._frame_program(st, B, M))
         return _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, None, 0, dur_hat, pitch_hat, energy_hat,
                                             cum, lens, M, float(self.pitch_strength), float(self.energy_strength),
                                             round_tf32=False)

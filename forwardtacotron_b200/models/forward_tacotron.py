@@ -145,7 +145,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         packs, h = st['packs'], st['handle']
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
-        tok = prog.dense('tok', (batch, T), torch.int64)
+        tok = prog.dense('tok', (batch, -1), torch.int64)
         branches, grus, heads = [], [], []
         if predictors:
             for name in ('dur', 'pitch', 'energy'):
@@ -172,7 +172,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         prog.rnn(grus)
         prog.label('')
         for name, p, hbuf in heads:
-            y = prog.dense(f'{name}.y', (batch, T))
+            y = prog.dense(f'{name}.y', (batch, -1))
             prog.rowdot(hbuf, p.lin_w, p.lin_b, 1, (lambda: prog.alpha) if name == 'dur' else 1.0, y)
         prog.flush()                                                # the three heads: one launch
         prog.alpha = 1.0
@@ -188,7 +188,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True, True))
+            prog = self._program(st, ('tok', B, T), lambda T: self._token_program(st, B, T, True, True))
             prog.bufs['tok'].copy_(x)
             prog.alpha = float(alpha)
             prog.run()
@@ -217,7 +217,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         self._check_tokens(x)
         st = self._accel_state(x.device)
         B, T = x.shape
-        tok = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True, True))
+        tok = self._program(st, ('tok', B, T), lambda T: self._token_program(st, B, T, True, True))
         tok.bufs['tok'].copy_(x)
         tok.alpha = 1.0
         tok.run()
@@ -232,7 +232,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError(f'forward(): mel_len must lie in [1, {M_lr}] (the regulated length), as '
                                'pack_padded_sequence requires (forward_tacotron.py:147)')
         pre = tok.bufs['prenet.h']
-        prog = self._program(st, ('frame_packed', B, M), lambda: _accel.build_frame_program(
+        prog = self._program(st, ('frame_packed', B, M), lambda M: _accel.build_frame_program(
             st['handle'], st['packs'], B, M, pre.shape[1], self.n_mels, packed_pad_value=float(self.padding_value)))
         prog.bufs['mel_len'].copy_(mel_len)
         out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, pre, None, 0, dur,
@@ -249,7 +249,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('prenet', B, T), lambda: self._token_program(st, B, T, False, True))
+            prog = self._program(st, ('prenet', B, T), lambda T: self._token_program(st, B, T, False, True))
             prog.bufs['tok'].copy_(x)
             prog.run()
             if not (dur_hat.is_cuda and dur_hat.dtype == torch.float32 and dur_hat.is_contiguous()):
@@ -265,7 +265,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError('generate(): all rounded durations are zero -- nothing to synthesise')
         pre = tok_prog.bufs['prenet.h']
         C = pre.shape[1]
-        prog = self._program(st, ('frame', B, M), lambda: _accel.build_frame_program(h, packs, B, M, C, self.n_mels))
+        prog = self._program(st, ('frame', B, M), lambda M: _accel.build_frame_program(h, packs, B, M, C, self.n_mels))
         return _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, None, 0, dur_hat, pitch_hat, energy_hat,
                                             cum, lens, M, float(self.pitch_strength), float(self.energy_strength))
 

@@ -173,6 +173,10 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
             packs[name + '_lin'] = (f(mod.lin.weight), f(mod.lin.bias))
         return packs
 
+    def _program(self, st: dict, key, builder):
+        self._check_len(st['packs']['prenet'], key[2])       # the ACTUAL length; programs are built per capacity bucket
+        return super()._program(st, key, builder)
+
     def _check_len(self, tp: '_accel.TransformerPack', n: int):
         if n > tp.max_len:
             raise RuntimeError(f'sequence length {n} exceeds PositionalEncoding.max_len={tp.max_len} '
@@ -187,22 +191,21 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         packs, h = st['packs'], st['handle']
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
-        tok = prog.dense('tok', (batch, T), torch.int64)
+        tok = prog.dense('tok', (batch, -1), torch.int64)
         semb = prog.dense('semb', (batch, self.speaker_emb_dims))
-        pcond = prog.dense('pitch_cond', (batch, T), torch.int64)
+        pcond = prog.dense('pitch_cond', (batch, -1), torch.int64)
 
         def add_transformer(tag, tp, table, ctable, key_tok):
             """concat [table[tok], ctable[pcond], semb] -> + scale*pe -> transformer levels."""
-            self._check_len(tp, T)
             E = tp.d_model
             cat = prog.buf(f'{tag}.cat', E)
             x0 = prog.buf(f'{tag}.x', 3 * E, torch.float16) if tp.precise else prog.buf(f'{tag}.x', E)
             x0f = prog.buf(f'{tag}.x_full', E)
             out = prog.buf(f'{tag}.out', E)
-            prog.call(lambda: h.embed(tok, table, cat, E, batch, T, geo.stride,
+            prog.call(lambda: h.embed(tok, table, cat, E, batch, geo.seq_len, geo.stride,
                                       tok2=pcond if ctable is not None else None, table2=ctable, extra=semb,
                                       round_tf32=False), label=f'{tag}.embed')
-            prog.call(lambda: h.posenc(None, None, cat, tp.pe, tp.scale, E, batch, T, geo.stride, x0,
+            prog.call(lambda: h.posenc(None, None, cat, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0,
                                        round_tf32=3 if tp.precise else True, out_full=x0f),
                       label=f'{tag}.posenc')
             return out, _accel.transformer_levels(prog, tag, tp, x0, out, key_tok, round_final=False, x_full=x0f)
@@ -210,9 +213,9 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         def add_head(name, out):
             w, b = packs[name + '_lin']
             n_out = w.shape[0]
-            y = prog.dense(f'{name}.y', (batch, T, n_out))
+            y = prog.dense(f'{name}.y', (batch, -1, n_out))
             alpha_of = (lambda: prog.alpha) if name in ('dur', 'pitch_cond') else (lambda: 1.0)
-            prog.call(lambda: h.rowdot(out, out.shape[1], out.shape[1], w, b, n_out, alpha_of(), batch, T,
+            prog.call(lambda: h.rowdot(out, out.shape[1], out.shape[1], w, b, n_out, alpha_of(), batch, geo.seq_len,
                                        geo.stride, y), label=f'{name}.lin')
             return y
 
@@ -229,7 +232,7 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
             logits = add_head('pitch_cond', outs['pitch_cond'])
             add_head('energy', outs['energy'])
             if not teacher_cond:
-                prog.call(lambda: h.argmax(logits, batch * T, logits.shape[2], pcond), label='pitch_cond.argmax')
+                prog.call(lambda: h.argmax(logits, batch * geo.seq_len, logits.shape[2], pcond), label='pitch_cond.argmax')
             branches2 = []
             for name in ('dur', 'pitch'):
                 outs[name], lv = add_transformer(name, packs[name], packs[name + '_emb'], packs[name + '_cemb'],
@@ -246,7 +249,6 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         where the caller-filled prog.bufs['frame_tok'] is 0 are masked (forward(batch), :230-234)."""
         packs, h = st['packs'], st['handle']
         tp = packs['postnet']
-        self._check_len(tp, M)
         geo = eng.Geometry(batch, M)
         prog = eng.Program(h, geo)
         E = tp.d_model
@@ -254,10 +256,10 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         x0 = prog.buf('postnet.x', E)
         x0f = prog.buf('postnet.x_full', E)
         out = prog.buf('postnet.out', E)
-        mel = prog.dense('mel', (batch, self.n_mels, M))
-        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, M, geo.stride, x0, out_full=x0f),
+        mel = prog.dense('mel', (batch, self.n_mels, -1))
+        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0, out_full=x0f),
                   label='postnet.posenc')
-        frame_tok = prog.dense('frame_tok', (batch, M), torch.int64) if masked else None
+        frame_tok = prog.dense('frame_tok', (batch, -1), torch.int64) if masked else None
         eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, frame_tok, x_full=x0f)])
         prog.label('lin')
         prog.gemm(out, packs['lin'], None, out_t=mel)
@@ -283,7 +285,7 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True))
+            prog = self._program(st, ('tok', B, T), lambda T: self._token_program(st, B, T, True))
             prog.bufs['tok'].copy_(x)
             prog.bufs['semb'].copy_(speaker_emb.to(torch.float32))
             prog.alpha = float(alpha)
@@ -305,7 +307,7 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         st = self._accel_state(x.device)
         B, T = x.shape
         tok = self._program(st, ('tok_masked', B, T),
-                            lambda: self._token_program(st, B, T, True, mask_predictors=True, teacher_cond=True))
+                            lambda T: self._token_program(st, B, T, True, mask_predictors=True, teacher_cond=True))
         tok.bufs['tok'].copy_(x)
         tok.bufs['semb'].copy_(semb.to(torch.float32))
         tok.bufs['pitch_cond'].copy_(batch['pitch_cond'])
@@ -319,7 +321,7 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         cum, lens, M, _ = _accel.length_regulate(st['handle'], dur, apply_fallback=False)
         if M <= 0:
             raise RuntimeError('forward(): all durations are zero -- nothing to synthesise')
-        prog = self._program(st, ('frame_masked', B, M), lambda: self._frame_program(st, B, M, masked=True))
+        prog = self._program(st, ('frame_masked', B, M), lambda M: self._frame_program(st, B, M, masked=True))
         mel_len = batch['mel_len'].to(x.device)
         prog.bufs['frame_tok'].copy_((torch.arange(M, device=x.device)[None, :] < mel_len[:, None]).to(torch.int64))
         out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, tok.bufs['prenet.out'], None, 0, dur,
@@ -338,7 +340,7 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('prenet', B, T), lambda: self._token_program(st, B, T, False))
+            prog = self._program(st, ('prenet', B, T), lambda T: self._token_program(st, B, T, False))
             prog.bufs['tok'].copy_(x)
             prog.bufs['semb'].copy_(speaker_emb.to(torch.float32))
             prog.run()
@@ -354,7 +356,7 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         if M <= 0:
             raise RuntimeError('generate(): all rounded durations are zero -- nothing to synthesise')
         pre = tok_prog.bufs['prenet.out']
-        prog = self._program(st, ('frame', B, M), lambda: self._frame_program(st, B, M))
+        prog = self._program(st, ('frame', B, M), lambda M: self._frame_program(st, B, M))
         out = _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, None, 0, dur_hat, pitch_hat, energy_hat,
                                            cum, lens, M, float(self.pitch_strength), float(self.energy_strength),
                                            round_tf32=False)

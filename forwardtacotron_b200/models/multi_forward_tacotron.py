@@ -193,9 +193,9 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         geo = eng.Geometry(batch, T)
         prog = eng.Program(h, geo)
         S = self.speaker_emb_dims
-        tok = prog.dense('tok', (batch, T), torch.int64)
+        tok = prog.dense('tok', (batch, -1), torch.int64)
         semb = prog.dense('semb', (batch, S))
-        pcond = prog.dense('pitch_cond', (batch, T), torch.int64)
+        pcond = prog.dense('pitch_cond', (batch, -1), torch.int64)
         heads = []
 
         def add_predictor(name, conditional):
@@ -234,9 +234,9 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
 
         def add_head(name, p, hbuf):
             n_out = p.lin_w.shape[0]
-            y = prog.dense(f'{name}.y', (batch, T, n_out))
+            y = prog.dense(f'{name}.y', (batch, -1, n_out))
             prog.call(lambda: h.rowdot(hbuf, hbuf.shape[1], hbuf.shape[1], p.lin_w, p.lin_b, n_out,
-                                       prog.alpha if name == 'dur' else 1.0, batch, T, geo.stride, y),
+                                       prog.alpha if name == 'dur' else 1.0, batch, geo.seq_len, geo.stride, y),
                       label=f'{name}.lin')
             return y
 
@@ -250,7 +250,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                     logits = y
             n_cls = logits.shape[2]
             if not teacher_cond:
-                prog.call(lambda: h.argmax(logits, batch * T, n_cls, pcond), label='pitch_cond.argmax')
+                prog.call(lambda: h.argmax(logits, batch * geo.seq_len, n_cls, pcond), label='pitch_cond.argmax')
             branches2, grus2 = [], []
             for name in ('dur', 'pitch'):
                 levels, gru = add_predictor(name, True)
@@ -283,7 +283,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('tok', B, T), lambda: self._token_program(st, B, T, True))
+            prog = self._program(st, ('tok', B, T), lambda T: self._token_program(st, B, T, True))
             prog.bufs['tok'].copy_(x)
             prog.bufs['semb'].copy_(speaker_emb.to(torch.float32))
             prog.alpha = float(alpha)
@@ -304,7 +304,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         self._check_speaker(x, semb, self.speaker_emb_dims)
         st = self._accel_state(x.device)
         B, T = x.shape
-        tok = self._program(st, ('tok_teacher', B, T), lambda: self._token_program(st, B, T, True, teacher_cond=True))
+        tok = self._program(st, ('tok_teacher', B, T), lambda T: self._token_program(st, B, T, True, teacher_cond=True))
         tok.bufs['tok'].copy_(x)
         tok.bufs['semb'].copy_(semb.to(torch.float32))
         tok.bufs['pitch_cond'].copy_(batch['pitch_cond'])
@@ -323,7 +323,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                                'pack_padded_sequence requires (multi_forward_tacotron.py:222)')
         pre = tok.bufs['prenet.h']
         C1, C2 = pre.shape[1], self.speaker_emb_dims
-        prog = self._program(st, ('frame_packed', B, M), lambda: _accel.build_frame_program(
+        prog = self._program(st, ('frame_packed', B, M), lambda M: _accel.build_frame_program(
             st['handle'], st['packs'], B, M, C1 + C2, self.n_mels, packed_pad_value=float(self.padding_value)))
         prog.bufs['mel_len'].copy_(mel_len)
         out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, pre, tok.bufs['semb'], C2, dur,
@@ -341,7 +341,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         with torch.no_grad():
             st = self._accel_state(x.device)
             B, T = x.shape
-            prog = self._program(st, ('prenet', B, T), lambda: self._token_program(st, B, T, False))
+            prog = self._program(st, ('prenet', B, T), lambda T: self._token_program(st, B, T, False))
             prog.bufs['tok'].copy_(x)
             prog.bufs['semb'].copy_(semb.to(torch.float32))
             prog.run()
@@ -359,7 +359,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
         pre = tok_prog.bufs['prenet.h']
         C1, C2 = pre.shape[1], self.speaker_emb_dims
         prog = self._program(st, ('frame', B, M),
-                             lambda: _accel.build_frame_program(h, packs, B, M, C1 + C2, self.n_mels))
+                             lambda M: _accel.build_frame_program(h, packs, B, M, C1 + C2, self.n_mels))
         out = _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, tok_prog.bufs['semb'], C2, dur_hat,
                                            pitch_hat, energy_hat, cum, lens, M,
                                            float(self.pitch_strength), float(self.energy_strength))

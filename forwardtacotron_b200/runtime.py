@@ -68,6 +68,7 @@ class LrGatherArgs(C.Structure):
 # every symbol include/ftb200.h declares (tests check that the .so exports all of them)
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
            'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy', 'ftb_gemm_plan_info',
+           'ftb_gemm_plan_set_geometry', 'ftb_rnn_plan_set_geometry',
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
            'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
@@ -94,6 +95,8 @@ def load_library() -> C.CDLL:
     lib.ftb_gemm_plan_run.argtypes = [_fp, C.c_int, C.c_int, _fp]
     lib.ftb_gemm_plan_destroy.argtypes = [_fp, C.c_int]
     lib.ftb_gemm_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.ftb_gemm_plan_set_geometry.argtypes = [_fp, C.c_int, C.c_int, C.c_int, _fp]
+    lib.ftb_rnn_plan_set_geometry.argtypes = [_fp, C.c_int, C.c_int, C.c_int, _fp]
     lib.ftb_rnn_plan_create.argtypes = [_fp, C.POINTER(RnnProblem), C.c_int, C.POINTER(C.c_int)]
     lib.ftb_rnn_plan_run.argtypes = [_fp, C.c_int, _fp]
     lib.ftb_rnn_plan_destroy.argtypes = [_fp, C.c_int]
@@ -173,6 +176,12 @@ class Handle:
 
     def gemm_run(self, plan: int, impl: Optional[int] = None):
         self.check(self.lib.ftb_gemm_plan_run(self.h, plan, self.impl if impl is None else impl, self.stream()))
+
+    def gemm_set_geometry(self, plan: int, seq_len: int, stride: int):
+        self.check(self.lib.ftb_gemm_plan_set_geometry(self.h, plan, seq_len, stride, self.stream()))
+
+    def rnn_set_geometry(self, plan: int, seq_len: int, stride: int):
+        self.check(self.lib.ftb_rnn_plan_set_geometry(self.h, plan, seq_len, stride, self.stream()))
 
     def gemm_destroy(self, plan: int):
         self.check(self.lib.ftb_gemm_plan_destroy(self.h, plan))

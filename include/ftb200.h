@@ -124,6 +124,14 @@ int ftb_gemm_plan_destroy(ftb_handle h, int plan);
  * run >= 8 k-blocks on average, FTB_GEMM_PAIR=0/1 forces), *tiles = schedule slots (tiles, or tile pairs).  Either
  * pointer may be null. */
 int ftb_gemm_plan_info(ftb_handle h, int plan, int* cta_pairs, int* tiles);
+/* Launch-time geometry.  A plan is built for a CAPACITY (the rows / seq_len / seq_stride of its problems); afterwards every
+ * problem can be re-pointed, in stream order, at `batch` sentences of `seq_len` <= capacity rows at stride `seq_stride`
+ * (batch * seq_stride <= the built rows, else FTB_E_LIMIT) inside the same buffers: rows, tile grid and schedule are
+ * recomputed and the device records re-uploaded; tensor maps, buffers and captured CUDA graphs stay valid (the kernels
+ * read the geometry from the records, not from their arguments).  The caller keeps rows t in [seq_len, seq_stride) of
+ * every sentence zero.  generate() of the reference sees a new regulated length M on almost every call
+ * (common_layers.py:23 pads to the batch maximum); this is what lets one plan serve a whole bucket of lengths.  */
+int ftb_gemm_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * K3/K4  persistent bidirectional GRU / LSTM recurrence
@@ -176,6 +184,9 @@ int ftb_rnn_plan_destroy(ftb_handle h, int plan);
 /* How the plan was laid out on this device: *handoff = 1 thread-block-cluster hand-off, 0 L2 hand-off;
  * *kernel_launches = kernel launches per run; *lanes = concurrent launch sequences (1 = all on `stream`). */
 int ftb_rnn_plan_info(ftb_handle h, int plan, int* handoff, int* kernel_launches, int* lanes);
+/* Launch-time geometry of a recurrence plan (see ftb_gemm_plan_set_geometry): seq_len <= the built seq_len and
+ * seq_stride <= the built seq_stride, else FTB_E_LIMIT; the L2 exchange tensors keep their built size. */
+int ftb_rnn_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * K5/K6  duration rounding + LengthRegulator gather (+ fused pitch/energy projection add)

@@ -269,20 +269,31 @@ def ft_generate_mel(sd: SD, x: torch.Tensor, dur_hat, pitch_hat, energy_hat,
         taps['prenet'] = h
     h = h + cond_projection(sd, 'pitch_proj', pitch_hat) * pitch_strength      # :214-216
     h = h + cond_projection(sd, 'energy_proj', energy_hat) * energy_strength   # :218-220
-    dur_np = dur_hat.numpy()
-    expanded, idx, lens, dur_clamped = length_regulate_np(h.numpy(), dur_np)   # :222
-    h = torch.from_numpy(expanded)
+    if h.is_cuda:
+        # bench.py --impl eager-gpu only: the reference's own torch formulation of the LengthRegulator
+        # (common_layers.py:17-24: clamp, (dur + 0.5).long(), repeat_interleave per sentence, pad_sequence)
+        d = dur_hat.clone()
+        d[d < 0] = 0
+        rep = (d + 0.5).long()
+        h = torch.nn.utils.rnn.pad_sequence([torch.repeat_interleave(h[i], rep[i], dim=0) for i in range(h.shape[0])],
+                                            batch_first=True)
+        lens_t, dur_t = rep.sum(dim=1), d
+    else:
+        expanded, idx, lens, dur_clamped = length_regulate_np(h.numpy(), dur_hat.numpy())   # :222
+        h = torch.from_numpy(expanded)
+        lens_t, dur_t = torch.from_numpy(lens), torch.from_numpy(dur_clamped)
+        if taps is not None:
+            taps['idx'] = torch.from_numpy(idx)
     if taps is not None:
         taps['lr'] = h
-        taps['idx'] = torch.from_numpy(idx)
     h = bi_rnn(sd, 'lstm', h, 'lstm')                                          # :224
     if taps is not None:
         taps['lstm'] = h
     mel = linear(h, sd['lin.weight'], sd['lin.bias']).transpose(1, 2)          # :226-227
     post = cbhg(sd, 'postnet', mel)                                            # :229
     mel_post = linear(post, sd['post_proj.weight']).transpose(1, 2)            # :230-231
-    return {'mel': mel, 'mel_post': mel_post, 'dur': torch.from_numpy(dur_clamped),
-            'pitch': pitch_hat, 'energy': energy_hat, 'mel_lens': torch.from_numpy(lens)}
+    return {'mel': mel, 'mel_post': mel_post, 'dur': dur_t,
+            'pitch': pitch_hat, 'energy': energy_hat, 'mel_lens': lens_t}
 
 
 @torch.no_grad()

@@ -20,7 +20,7 @@ torch.cuda.synchronize()
 print('dur err', float((out['dur'].cpu() - ref['dur']).abs().max()), 'mean', float((out['dur'].cpu() - ref['dur']).mean()))
 st = model.__dict__['_accel']
 B, T = x.shape
-prog = st['programs'][('tok', B, T)]
+prog = model.program_for('tok', B, T)
 prog.use_graph = False
 sd64 = {k: (v.double() if v.is_floating_point() else v) for k, v in sd.items()}
 p = 'dur_pred.transformer'

@@ -34,7 +34,7 @@ for name in ['fp_b2_t30', 'fp_pad_b3_t36']:
     m = model('fast_pitch', sd)
     x = torch.from_numpy(g['x']).to(DEV)
     o = m.generate(x, alpha=float(g['alpha']))
-    tok = m.__dict__['_accel']['programs'][('tok', x.shape[0], x.shape[1])]
+    tok = m.program_for('tok', x.shape[0], x.shape[1])
     line = (f"{name}: dur {max_abs(o['dur'].cpu(), g['dur']):.2e} pitch {max_abs(o['pitch'].cpu(), g['pitch']):.2e} "
             f"durT rel {rel_l2(tok.view('dur.out').cpu(), g['tap_dur_transformer']):.2e} "
             f"prenet rel {rel_l2(tok.view('prenet.out').cpu(), g['tap_prenet']):.2e}")

@@ -1,0 +1,115 @@
+"""torchrun worker of tests/test_gpu_sharded.py: parallel.generate_sharded over NCCL against the PER-SHARD oracle.
+
+    python -m torch.distributed.run --nproc-per-node N tests/sharded_worker.py <case>
+
+The reference's results depend on batch composition (pad_sequence to the batch max, batch-global fallback: SURVEY.md §8e),
+so the oracle of a G-GPU run is the reference applied to each shard separately.  Every rank runs the CPU oracle on ITS
+shard and checks its own generate() output against it (durations inside the documented window, mel through the
+teacher-forced entry at 1e-2 / 1e-3); the consumer rank additionally checks that the gathered tensor holds every rank's
+block bit-exactly, in rank order, zero-padded to the global frame maximum."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from forwardtacotron_b200 import parallel as par, synth                 # noqa: E402
+from forwardtacotron_b200.configs import default_config                # noqa: E402
+from forwardtacotron_b200.models import init_tts_model                 # noqa: E402
+from oracle import ft_oracle as O                                      # noqa: E402
+from tests.helpers import synthetic_sd, rel_l2, max_abs                # noqa: E402
+
+CASES = {   # name: (model, global batch, T, alpha, seed)
+    'config4_multift_128x200': ('multi_forward_tacotron', 128, 200, 1.0, 24),
+    'config5_ft_32x4096': ('forward_tacotron', 32, 4096, 0.8, 26),
+    'small_ragged': ('forward_tacotron', 2 * 4 + 1, 40, 1.0, 3),
+}
+DUR_WINDOW, MEL_ABS, MEL_REL = 2e-4, 1e-2, 1e-3
+
+
+def main(case):
+    tag, B, T, alpha, seed = CASES[case]
+    rank, world, lr = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
+    dev = torch.device('cuda', lr)
+    torch.cuda.set_device(dev)
+    dist.init_process_group('nccl', device_id=dev)
+    torch.set_num_threads(max(1, (os.cpu_count() or 8) // world))
+    sd = synthetic_sd(tag, seed)
+    model = init_tts_model(default_config(tag))
+    model.load_state_dict(sd)
+    model = model.to(dev).eval()
+    multi = tag.startswith('multi')
+    x = synth.synth_tokens(B, T, seed=seed)
+    semb = synth.synth_speaker_emb(B, 256, seed=seed) if multi else None
+    sl = par.shard_slice(B, rank, world)
+    ok, msg = True, []
+
+    # the sharded run: gathered to rank 0 only, then to every rank
+    xd = x.to(dev)
+    sd_dev = semb.to(dev) if multi else None
+    one = par.generate_sharded(model, xd, sd_dev, dst=0, alpha=alpha)
+    everywhere = par.generate_sharded(model, xd, sd_dev, alpha=alpha)
+    own = model.generate(*((xd[sl], sd_dev[sl]) if multi else (xd[sl],)), alpha=alpha)
+    torch.cuda.synchronize()
+    lens = par.mel_lengths(own['dur'])
+    M = own['mel_post'].shape[2]
+    for name, res in (('dst=0', one), ('all', everywhere)):
+        if res['mel_post'] is None:
+            ok &= rank != 0 and name == 'dst=0'
+            continue
+        ok &= bool(torch.equal(res['mel_lens'][sl], lens))
+        ok &= bool(torch.equal(res['mel_post'][sl, :, :M], own['mel_post']))
+        ok &= bool(torch.equal(res['mel'][sl, :, :M], own['mel']))
+        ok &= bool((res['mel_post'][sl, :, M:] == 0).all())
+        ok &= res['mel_post'].shape[0] == B
+    if rank == 0:       # the consumer holds every rank's block: compare against what each rank computed itself
+        blocks = [None] * world
+    m_all = torch.zeros((world,), dtype=torch.int64, device=dev)
+    m_all[rank] = M
+    dist.all_reduce(m_all)
+    ok &= one['mel_post'] is None or one['mel_post'].shape[2] == int(m_all.max())
+    # checksum of every rank's own block against the gathered copy on rank 0
+    cs = torch.zeros((world,), dtype=torch.float64, device=dev)
+    cs[rank] = own['mel_post'].double().sum()
+    dist.all_reduce(cs)
+    if rank == 0:
+        for r in range(world):
+            s = par.shard_slice(B, r, world)
+            got = one['mel_post'][s].double().sum()
+            ok &= bool(torch.isclose(got, cs[r], rtol=1e-12, atol=1e-9))
+
+    # this rank's shard against the oracle applied to the same shard
+    O.use_library_rnn(True)
+    try:
+        gen = O.mft_generate if multi else O.ft_generate
+        ref = gen(sd, *((x[sl], semb[sl]) if multi else (x[sl],)), alpha=alpha)
+    finally:
+        O.use_library_rnn(False)
+    d_err = max_abs(own['dur'].cpu(), ref['dur'])
+    flips = int(((own['dur'].cpu().clamp_min(0) + 0.5).long() != (ref['dur'].clamp_min(0) + 0.5).long()).sum())
+    ok &= d_err < DUR_WINDOW and flips == 0
+    tf_args = (xd[sl], sd_dev[sl]) if multi else (xd[sl],)
+    dur = ref['dur'].to(dev).contiguous().clone()
+    if multi:
+        got = model._generate_mel(*tf_args, dur, ref['pitch'].to(dev), ref['pitch_cond'].to(dev), ref['energy'].to(dev))
+    else:
+        got = model._generate_mel(*tf_args, dur, ref['pitch'].to(dev), ref['energy'].to(dev))
+    torch.cuda.synchronize()
+    for k in ('mel', 'mel_post'):
+        a, r = max_abs(got[k].cpu(), ref[k]), rel_l2(got[k].cpu(), ref[k])
+        ok &= got[k].shape == ref[k].shape and a < MEL_ABS and r < MEL_REL
+        msg.append(f'{k} abs {a:.2e} rel {r:.2e}')
+        if flips == 0:
+            ok &= max_abs(own[k].cpu(), ref[k]) < MEL_ABS and rel_l2(own[k].cpu(), ref[k]) < MEL_REL
+    print(f'[{case}] rank {rank}/{world}: shard {sl.start}:{sl.stop} M {M} dur err {d_err:.2e} flips {flips} '
+          + ' '.join(msg) + (' OK' if ok else ' MISMATCH'), flush=True)
+    t = torch.tensor([int(ok)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t) else 1)
+
+
+if __name__ == '__main__':
+    main(sys.argv[1])

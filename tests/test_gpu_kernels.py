@@ -664,3 +664,58 @@ def test_recurrence_precise(H, B, L):
     prog.run()
     torch.cuda.synchronize()
     assert torch.equal(prog.view('h').cpu(), got)
+
+
+def test_program_set_seq_len_reuses_plans():
+    """Launch-time geometry (ftb_*_plan_set_geometry): ONE program built for a capacity of 64 rows per sentence runs a
+    k = 5 convolution + BiGRU at 50, 23, 64 and 50 rows again -- each time equal to a program built for exactly that
+    length (bit-exact: same kernels, same tiles modulo the row count), with graphs replayed after the first run."""
+    B, cin, cout, H = 5, 64, 96, 64
+    gen = torch.Generator().manual_seed(77)
+    w = torch.randn(cout, cin, 5, generator=gen) / (cin * 5) ** 0.5
+    packed = pk.pack_conv(w.to(DEV), torch.randn(cout, generator=gen).to(DEV), relu=True)
+    rnn = torch.nn.GRU(cout, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    prnn = pk.PackedRnn(rnn.to(DEV))
+
+    def build(L):
+        prog = eng.Program(_handle(), eng.Geometry(B, L))
+        a = prog.buf('a', cin)
+        y = prog.buf('y', cout)
+        xp = prog.buf('xp', prnn.ih.n)
+        h = prog.buf('h', 2 * H)
+        mel = prog.dense('mel', (B, cout, -1))
+        prog.gemm(a, packed, y, out_t=mel)
+        prog.flush()
+        prog.gemm(y, prnn.ih, xp, round_out=False)
+        prog.rnn([(prnn, xp, h, 0)])
+        return prog
+
+    def fill(prog, v):
+        g = prog.geo
+        a = prog.bufs['a']
+        a[:g.rows].view(g.batch, g.stride, cin)[:, :g.seq_len] = v.to(DEV)
+
+    big = build(64)
+    for L in (50, 23, 64, 50):
+        v = pk.round_tf32(torch.randn(B, L, cin, generator=gen))
+        big.set_seq_len(L)
+        fill(big, v)
+        for _ in range(2):                       # eager, then graph capture / replay
+            big.run()
+        exact = build(L)
+        fill(exact, v)
+        exact.run()
+        torch.cuda.synchronize()
+        for name in ('y', 'h'):
+            assert torch.equal(big.view(name), exact.view(name)), (L, name)
+        assert big.bufs['mel'].shape == (B, cout, L) and torch.equal(big.bufs['mel'], exact.bufs['mel'])
+        g = big.geo
+        for name in ('a', 'y', 'xp', 'h'):       # the gap rows of the current layout are zero
+            b = big.bufs[name]
+            assert float(b[:g.rows].view(B, g.stride, -1)[:, L:].float().abs().max()) == 0.0, (L, name)
+        exact.close()
+    with pytest.raises(AssertionError):
+        big.set_seq_len(65)

@@ -101,9 +101,9 @@ def test_generate_mel_teacher_forced_intermediates():
     torch.cuda.synchronize()
     st = model.__dict__['_accel']
     B, T = x.shape
-    tok = st['programs'][('prenet', B, T)]
+    tok = model.program_for('prenet', B, T)
     M = g['mel'].shape[2]
-    frame = st['programs'][('frame', B, M)]
+    frame = model.program_for('frame', B, M)
     assert rel_l2(tok.view('prenet.proj1').cpu(), g['tap_prenet_conv_project1'].transpose(0, 2, 1)) < 1e-3
     assert rel_l2(tok.view('prenet.h').cpu(), g['tap_prenet']) < 1e-3
     assert rel_l2(frame.view('lr').cpu(), g['tap_lr']) < 1e-3
@@ -189,7 +189,7 @@ def test_fast_pitch_vs_reference_golden(name):
     torch.cuda.synchronize()
     assert set(out) == {'mel', 'mel_post', 'dur', 'pitch', 'energy'}
     st = model.__dict__['_accel']
-    tok = st['programs'][('tok', x.shape[0], x.shape[1])]
+    tok = model.program_for('tok', x.shape[0], x.shape[1])
     assert rel_l2(tok.view('dur.out').cpu(), g['tap_dur_transformer']) < 1e-3
     assert rel_l2(tok.view('prenet.out').cpu(), g['tap_prenet']) < 1e-3
     ties = _check_durations(out['dur'], g['dur'])
@@ -299,7 +299,7 @@ def test_forward_tacotron_eval_forward_vs_reference_golden(kind, golden, speaker
     with torch.no_grad():
         out = model(batch)
     torch.cuda.synchronize()
-    assert ('frame_packed', int(g['B']), int(batch['mel_len'].max())) in model.__dict__['_accel']['programs']
+    assert model.program_for('frame_packed', int(g['B']), int(batch['mel_len'].max())) is not None
     # frames t < mel_len[b] are the sentence (what the GTA dump keeps, train_forward.py:45): absolute + relative
     # tolerance.  Frames between mel_len[b] and max(mel_len) hold lin(padding vector) run through the postnet -- values
     # of magnitude ~30 in the reference too -- so only the relative tolerance is meaningful there.
@@ -413,3 +413,25 @@ def test_fast_pitch_eval_forward_vs_reference_golden(kind, golden, speaker_dims)
     for k in ('dur', 'pitch', 'energy') + (('pitch_cond',) if speaker_dims else ()):
         assert out[k].shape == g[k].shape, k
         assert max_abs(out[k].cpu()[:, ...], g[k]) < 1e-2, k
+
+
+def test_generate_reuses_programs_across_lengths():
+    """the regulated length M is new on almost every call with real text.  Programs are cached per capacity
+    bucket and re-pointed at the actual length: sentences of 40, 33 and 40 tokens (one bucket) and their different M all
+    go through ONE token program and the frame programs of at most two buckets, each call equal to the oracle."""
+    sd = synthetic_sd('forward_tacotron', 4)
+    model = _model('forward_tacotron', sd)
+    progs = None
+    for T, seed in ((40, 1), (33, 2), (40, 3), (17, 4), (33, 2)):
+        x = synth.synth_tokens(3, T, seed=seed)
+        O.use_library_rnn(True)
+        try:
+            ref = O.ft_generate(sd, x)
+        finally:
+            O.use_library_rnn(False)
+        out = model.generate(x.to(DEV))
+        torch.cuda.synchronize()
+        _mel_checked(model, (x.to(DEV),), out, ref, _check_durations(out['dur'], ref['dur']))
+        progs = model.__dict__['_accel']['programs']
+    assert sum(1 for k in progs if k[0] == 'tok') == 1
+    assert sum(1 for k in progs if k[0] == 'frame') <= 3

@@ -76,6 +76,24 @@ def _worker(rank, world, port, ret):
         got, gl = par.gather_variable_mels(mel, torch.tensor([4, 3 + rank]))
         want_u = torch.cat([torch.arange(24, dtype=torch.float32).reshape(2, 3, 4) + 100.0 * r for r in range(world)])
         ok = ok and torch.equal(got, want_u) and gl.tolist() == [4, 3, 4, 4]
+        # gather to ONE consumer (dst = 0): the same result there, nothing (and no host sync) anywhere else
+        one = par.generate_sharded(_StubModel(), x, alpha=1.0, dst=0)
+        if rank == 0:
+            ok = ok and torch.equal(one['mel_post'], want) and torch.equal(one['mel_lens'], lens) and \
+                torch.equal(one['mel'], out['mel'])
+        else:
+            ok = ok and one['mel_post'] is None and one['mel_lens'] is None and one['mel'] is None
+        post_only = par.generate_sharded(_StubModel(), x, alpha=1.0, dst=1, gather_mel=False)
+        ok = ok and post_only['mel'] is None and ((post_only['mel_post'] is None) == (rank != 1))
+        if rank == 1:
+            ok = ok and torch.equal(post_only['mel_post'], want)
+        # equal frame extents: the consumer receives every block straight into its slice of the result
+        mel = torch.arange(2 * 3 * 4, dtype=torch.float32).reshape(2, 3, 4) + 100.0 * rank
+        got, gl = par.gather_variable_mels(mel, torch.tensor([4, 3 + rank]), dst=0)
+        if rank == 0:
+            ok = ok and torch.equal(got, want_u) and gl.tolist() == [4, 3, 4, 4]
+        else:
+            ok = ok and got is None and gl is None
         ret[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
