@@ -290,14 +290,14 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
                 pk.x = *reinterpret_cast<const uint32_t*>(&lo); pk.y = *reinterpret_cast<const uint32_t*>(&hi);
                 *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0) = pk;
                 if (SPLIT) {
-                  // FTB_F_OUT_SPLIT: [hi | lo | hi] column blocks of width N -- the K-concatenated operand of a
+                  // FTB_F_OUT_SPLIT: [hi | lo | hi] column blocks of width out_ld / 3 -- the K-concatenated operand of a
                   // split-precision consumer (weights packed as [W_hi | W_hi | W_lo]): hi*W_hi + lo*W_hi + hi*W_lo
                   const float2 f0 = __half22float2(lo), f1 = __half22float2(hi);
                   const __half2 r0 = __floats2half2_rn(y.x - f0.x, y.y - f0.y), r1 = __floats2half2_rn(y.z - f1.x, y.w - f1.y);
                   uint2 pr;
                   pr.x = *reinterpret_cast<const uint32_t*>(&r0); pr.y = *reinterpret_cast<const uint32_t*>(&r1);
-                  *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0 + c.N) = pr;
-                  *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0 + 2 * c.N) = pk;
+                  *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0 + c.out_ld / 3) = pr;
+                  *reinterpret_cast<uint2*>(hptr + i8 * ostep + c0 + 2 * (c.out_ld / 3)) = pk;
                 }
               } else {
                 if (RND) { y.x = round_tf32(y.x); y.y = round_tf32(y.y); y.z = round_tf32(y.z); y.w = round_tf32(y.w); }
@@ -333,7 +333,11 @@ __device__ __forceinline__ void epi_disp_full(const EpiCtx& c, bool full, bool o
 }
 __device__ __forceinline__ void epi_dispatch(const EpiCtx& c, bool pool, bool res, bool full, bool outt, bool rnd) {
   if (c.out16) {                                                  // fp16 operand copy as `out`
-    if (c.split) { epi_affine_tile<false, false, false, false, false, true, true>(c); return; }
+    if (c.split) {
+      if (pool) epi_affine_tile<true, false, false, false, false, true, true>(c);
+      else epi_affine_tile<false, false, false, false, false, true, true>(c);
+      return;
+    }
     if (pool) epi_affine_tile<true, false, false, false, false, true>(c);        // CBHG bank: never residual / twin
     else if (outt) {
       if (full) epi_affine_tile<false, false, true, true, false, true>(c);
@@ -751,7 +755,8 @@ __global__ void conv_gemm_simt_kernel(const GemmProblemDev* __restrict__ probs, 
     if (p->out && (p->flags & FTB_F_OUT_SPLIT)) {
       __half* o = reinterpret_cast<__half*>(p->out) + r * p->out_ld + p->out_col0 + n;
       const __half hi = __float2half_rn(v);
-      o[0] = hi; o[p->n] = __float2half_rn(v - __half2float(hi)); o[2 * p->n] = hi;
+      const int seg = p->out_ld / 3;
+      o[0] = hi; o[seg] = __float2half_rn(v - __half2float(hi)); o[2 * seg] = hi;
     } else if (p->out && (p->flags & FTB_F_OUT_F16))
       reinterpret_cast<__half*>(p->out)[r * p->out_ld + p->out_col0 + n] = __float2half_rn(v);
     else if (p->out) p->out[r * p->out_ld + p->out_col0 + n] = epi_finish(p, v);
@@ -833,8 +838,8 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     if (q.out && (q.n % omul) != 0) return FTB_E_SHAPE;       // row segments are stored as 16-byte vectors
     if (o16 && (!q.out || (q.epilogue == FTB_EPI_MAXPOOL && (q.residual || q.out_t || q.out_full)))) return FTB_E_ARG;
     if (q.flags & FTB_F_OUT_SPLIT) {
-      if (!o16 || q.epilogue != FTB_EPI_AFFINE || q.residual || q.out_t || q.out_full) return FTB_E_ARG;
-      if (q.out_ld < q.out_col0 + 3 * q.n || (q.n % 8) != 0) return FTB_E_SHAPE;
+      if (!o16 || q.epilogue == FTB_EPI_HIGHWAY || q.residual || q.out_t || q.out_full) return FTB_E_ARG;
+      if ((q.out_ld % 24) != 0 || q.out_col0 + q.n > q.out_ld / 3 || (q.n % 8) != 0) return FTB_E_SHAPE;
     }
     if (q.residual && ((q.res_ld % 4) != 0 || !aligned16(q.residual))) return FTB_E_ALIGN;
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;

@@ -185,7 +185,7 @@ class Program:
             p.cin = cin if cin is not None else w.cin
             assert p.cin == w.cin and p.cin <= a.shape[1], (p.cin, w.cin, a.shape)
             wt = w.w16 if a16 else w.w
-        assert not split_out or (o16 and out.shape[1] == 3 * w.n and out_col0 == 0)
+        assert not split_out or (o16 and out.shape[1] % 24 == 0 and out_col0 + w.n <= out.shape[1] // 3)
         p.w, p.taps, p.tap0, p.w_tap_rows = wt.data_ptr(), w.taps, w.tap0, w.n_pad
         p.n, p.bn, p.epilogue = w.n, w.bn, epilogue
         p.flags = ((rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out and not o16 else 0) |
@@ -393,7 +393,8 @@ class CbhgPack:
 
 
 def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torch.Tensor, out_col0: int = 0,
-                x_full: Optional[torch.Tensor] = None, xproj_f16: bool = False):
+                x_full: Optional[torch.Tensor] = None, xproj_f16: bool = False,
+                x_split: Optional[torch.Tensor] = None):
     """Returns the list of per-level closures for one CBHG over input buffer x [rows, in_channels];
     level i may be queued only after level i-1 has been flushed.  The last entry runs the BiGRU."""
     K = len(c.bank)
@@ -401,8 +402,15 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     # bank -> proj1 -> proj2 are GEMM-to-GEMM hand-offs with K = 3 * K*ch and 3 * proj1.n: fp16 operands (the same
     # 11-bit significand the tf32 path keeps) halve their traffic and double the MMA rate
     f16 = _F16_OPERANDS and (K * ch) % 8 == 0 and c.proj1.n % 8 == 0
-    bank = prog.buf(f'{tag}.bank', K * ch, torch.float16 if f16 else torch.float32)
-    p1 = prog.buf(f'{tag}.proj1', c.proj1.n, torch.float16 if f16 else torch.float32)
+    # x_split (the packed-sequence frame program): the whole conv chain bank -> proj1 -> proj2 runs split-precision,
+    # because the |value| ~ 30 padding rows next to a packed sentence reach its valid frames through every conv tap
+    chain_split = x_split is not None and c.proj1.w_src is not None and c.proj2.w_src is not None
+    if chain_split:
+        bank = prog.buf(f'{tag}.bank', 3 * K * ch, torch.float16)
+        p1 = prog.buf(f'{tag}.proj1', 3 * c.proj1.n, torch.float16)
+    else:
+        bank = prog.buf(f'{tag}.bank', K * ch, torch.float16 if f16 else torch.float32)
+        p1 = prog.buf(f'{tag}.proj1', c.proj1.n, torch.float16 if f16 else torch.float32)
     # proj2 -> pre_highway -> highways -> gru_ih: small-K layers paced by operand delivery from L2
     # (profiles/r1r_highway_ncu.txt): fp16 operand copies halve it; the residual terms keep their fp32 twins
     f16s = _F16_OPERANDS and c.proj2.n % 8 == 0 and ch % 8 == 0
@@ -424,10 +432,15 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
 
     def l_bank():   # conv bank k=1..K, each trimmed to L, ReLU->BN, + MaxPool1d(2,1,1)[:L] fused (:97-105)
         for k, w in enumerate(c.bank):
-            prog.gemm(x, w, bank, out_col0=k * ch, epilogue=rt.EPI_MAXPOOL)
+            if x_split is not None:          # [hi | lo | hi] copy of x (split-precision operand, PackedGemm.w16s)
+                prog.gemm(x_split, w, bank, out_col0=k * ch, epilogue=rt.EPI_MAXPOOL, split_in=True,
+                          split_out=chain_split)
+            else:
+                prog.gemm(x, w, bank, out_col0=k * ch, epilogue=rt.EPI_MAXPOOL)
     levels.append(named('bank', l_bank))
-    levels.append(named('proj1', lambda: prog.gemm(bank, c.proj1, p1)))                           # :109
-    levels.append(named('proj2', lambda: prog.gemm(p1, c.proj2, p2,                               # :111-114
+    levels.append(named('proj1', lambda: prog.gemm(bank, c.proj1, p1, split_in=chain_split,       # :109
+                                                   split_out=chain_split)))
+    levels.append(named('proj2', lambda: prog.gemm(p1, c.proj2, p2, split_in=chain_split,         # :111-114
                                                    residual=x_full if x_full is not None else x)))
     levels.append(named('pre_highway', lambda: prog.gemm(p2, c.pre_highway, hw[0], out_full=hwf[0])))   # :118
     for i, w in enumerate(c.highways):                                                            # :119-120

@@ -18,10 +18,12 @@ def pack_bn_conv(m, split: bool = False) -> pk.PackedGemm:
                            split=split)
 
 
-def pack_cbhg(m) -> eng.CbhgPack:
-    bank = [pack_bn_conv(c) for c in m.conv1d_bank]
+def pack_cbhg(m, split_bank: bool = False) -> eng.CbhgPack:
+    """split_bank: the bank / proj1 / proj2 weights also keep their unrounded copy, so the conv chain can run on
+    [hi | lo | hi] split operands (the packed-sequence frame program, whose input carries |value| ~ 30 padding rows)."""
+    bank = [pack_bn_conv(c, split=split_bank) for c in m.conv1d_bank]
     hws = [pk.pack_highway(h.W1.weight, h.W1.bias, h.W2.weight, h.W2.bias) for h in m.highways]
-    return eng.CbhgPack(bank, pack_bn_conv(m.conv_project1), pack_bn_conv(m.conv_project2),
+    return eng.CbhgPack(bank, pack_bn_conv(m.conv_project1, split=split_bank), pack_bn_conv(m.conv_project2, split=split_bank),
                         pk.pack_linear(m.pre_highway.weight), hws, pk.PackedRnn(m.rnn),
                         m.conv1d_bank[0].conv.in_channels, m.conv1d_bank[0].conv.out_channels)
 
@@ -147,9 +149,24 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
             torch.where(m[:, :, None], v, clf, out=clf)
             mel_now = prog.bufs['mel']
             torch.where(m[:, None, :L], v[None, :, None], mel_now, out=mel_now)
+            if mel_split is not None:
+                # The padding rows (|value| ~ 30) sit next to every packed sentence: a single fp16 / tf32 rounding of
+                # operands of that size is a 7e-3 absolute error that the bank taps and the backward GRU carry into the
+                # valid frames.  The postnet bank therefore reads the mel as a split operand [hi | lo | hi].
+                hi = clf.to(torch.float16)
+                sp = mel_split[:g.rows].view(batch, g.stride, 3 * seg)
+                sp[:, :, :n_mels] = hi
+                sp[:, :, seg:seg + n_mels] = (clf - hi.float()).to(torch.float16)
+                sp[:, :, 2 * seg:2 * seg + n_mels] = hi
+                sp[:, L:] = 0
+        seg = pk.ceil_to(n_mels, 8)
+        mel_split = prog.buf('mel_split', 3 * seg, torch.float16) if packs['postnet'].bank[0].w_src is not None else None
         prog.call(fix_pad_rows, label='lin.pad_rows')
+    else:
+        mel_split = None
     prog.label('')
-    levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full, xproj_f16=x16)
+    levels, gru = eng.cbhg_levels(prog, 'postnet', packs['postnet'], mel_cl, post, x_full=mel_full, xproj_f16=x16,
+                                  x_split=mel_split)
     eng.run_levels(prog, [levels])
     prog.label('postnet.gru')
     prog.rnn([gru])

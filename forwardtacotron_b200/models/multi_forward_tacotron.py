@@ -166,7 +166,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             # lin(padding vector) in exact fp32: the mel rows behind a packed sentence (eval-mode forward only)
             'lin_pad_vec': (self.lin.weight.detach().float().sum(dim=1) * float(self.padding_value)
                             + self.lin.bias.detach().float()).contiguous(),
-            'postnet': _accel.pack_cbhg(self.postnet),
+            'postnet': _accel.pack_cbhg(self.postnet, split_bank=True),
             'post_proj': pk.pack_linear(self.post_proj.weight),
             'pitch_proj': (self.pitch_proj.weight.detach().float().reshape(-1, 3).contiguous(),
                            self.pitch_proj.bias.detach().float().contiguous()),

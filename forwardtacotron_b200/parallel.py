@@ -25,78 +25,106 @@ def mel_lengths(dur: torch.Tensor) -> torch.Tensor:
     return (dur.clamp_min(0) + 0.5).long().sum(dim=1)
 
 
-def _meta_exchange(b_local: int, m_local: int, lens: torch.Tensor, b_cap: int, group) -> torch.Tensor:
-    """[world, 2 + b_cap] int32 on the data device: (b_local, M_local, lens...) of every rank, exchanged by ONE small
-    collective of the data-path backend itself (NCCL on the GPUs) -- enqueued on the stream behind the still-running
-    frame program, no host-side (gloo / TCP) round trip.  Only the ranks that must size a receive buffer read it."""
+_HOST_GROUPS = {}
+
+
+def _host_group(group):
+    """A gloo twin of the default (NCCL) process group for host-known shapes, created on first use by a collective call
+    of all ranks; None when `group` is a sub-group or the twin cannot be created (the shapes then travel through NCCL
+    and the consumer pays one device sync)."""
+    if group is not None and group is not dist.group.WORLD:
+        return None
+    if 'world' not in _HOST_GROUPS:
+        try:
+            _HOST_GROUPS['world'] = dist.new_group(backend='gloo')
+        except Exception:
+            _HOST_GROUPS['world'] = None
+    return _HOST_GROUPS['world']
+
+
+def _shapes(b_local: int, m_local: int, dev, on_cuda: bool, group):
+    """(b_local, M_local) of every rank as host integers.  Both are HOST-known on every rank the moment generate()
+    returns (tensor shapes; generate() itself read M from the device while the frame program was being enqueued), so
+    they are exchanged host to host (gloo) while the GPUs are still busy: no device sync, nothing on the GPU timeline.
+    The per-sentence lengths live on the device and travel with the payload instead."""
     world = dist.get_world_size(group)
-    dev = lens.device
-    meta = torch.zeros((2 + b_cap,), dtype=torch.int32, device=dev)
-    meta[0], meta[1] = b_local, m_local
-    meta[2:2 + b_local] = lens.to(torch.int32)
-    metas = torch.empty((world, 2 + b_cap), dtype=torch.int32, device=dev)
-    _all_gather(metas, meta, group)
-    return metas
+    host = _host_group(group) if on_cuda else group
+    if host is not None:
+        meta = torch.tensor([b_local, m_local], dtype=torch.int64)
+        metas = torch.empty((world, 2), dtype=torch.int64)
+        _all_gather(metas, meta, host)
+    else:                                                # sub-group without a host twin: one device sync
+        meta = torch.tensor([b_local, m_local], dtype=torch.int64, device=dev)
+        metas = torch.empty((world, 2), dtype=torch.int64, device=dev)
+        _all_gather(metas, meta, group)
+        metas = metas.cpu()
+    return [int(v) for v in metas[:, 0]], [int(v) for v in metas[:, 1]]
 
 
 def gather_variable_mels(mel: torch.Tensor, lens: torch.Tensor, group=None, dst: Optional[int] = None,
                          b_cap: Optional[int] = None) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """Gather `[b_local, C, M_local]` mels whose batch and frame extents differ per rank.
 
-    dst = r   : gather to rank r only (the consumer): every other rank SENDS its own contiguous block, exactly its own
-                size, point to point (NVLink through NCCL send/recv) and returns (None, None) without ever draining
-                its stream; rank r reads the tiny metadata tensor once (its only host sync, after which every peer is
-                done generating anyway), sizes `[B_total, C, M_max]` and receives each block straight into its slice
-                when the frame extents agree (no staging copy).
+    dst = r   : gather to rank r only (the consumer): every other rank SENDS its own contiguous block and its lengths,
+                exactly their own size, point to point (NVLink through NCCL send/recv) and returns (None, None); rank r
+                sizes `[B_total, C, M_max]` from the host-exchanged shapes and receives each block straight into its
+                slice when the frame extents agree (no staging copy).  Root ingest = the payload once, not world x.
     dst = None: every rank receives everything (all_gather of zero-padded blocks), for callers that need it everywhere.
-    `b_cap` is an upper bound of b_local over the ranks (default: exchanged first -- costs one more tiny collective and
-    a sync; `generate_sharded` knows it from the shard split).  Returns (`[B_total, C, M_max]`, `[B_total]` int64) with
-    the sentences in rank order; frames beyond a shard's own M_local are zero.
+    No rank drains its stream: the receives / collectives are enqueued behind the still-running frame program.
+    Returns (`[B_total, C, M_max]`, `[B_total]` int64) with the sentences in rank order; frames beyond a shard's own
+    M_local are zero.  (`b_cap` is accepted for compatibility and unused.)
     """
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return mel, lens.to(torch.int64)
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dev = mel.device
     b_local, C, m_local = mel.shape
-    if b_cap is None:
-        t = torch.tensor([b_local], dtype=torch.int32, device=dev)
-        _all_reduce_max(t, group)
-        b_cap = int(t.item())
-    metas = _meta_exchange(b_local, m_local, lens, b_cap, group)
+    counts, ms = _shapes(b_local, m_local, dev, mel.is_cuda, group)
+    m_max, total = max(ms), sum(counts)
+    lens = lens.to(torch.int64)
     if dst is not None and rank != dst:
-        if b_local > 0 and m_local > 0:
-            _p2p([dist.P2POp(dist.isend, mel.contiguous(), _global_rank(dst, group), group)])
+        if b_local > 0:
+            ops = [dist.P2POp(dist.isend, lens.contiguous(), _global_rank(dst, group), group)]
+            if m_local > 0:
+                ops.append(dist.P2POp(dist.isend, mel.contiguous(), _global_rank(dst, group), group))
+            _p2p(ops)
         return None, None
-    metas = metas.cpu()                                   # the consumer's one host sync
-    counts = [int(v) for v in metas[:, 0]]
-    ms = [int(v) for v in metas[:, 1]]
-    m_max = max(ms)
-    lens_all = torch.cat([metas[r, 2:2 + counts[r]] for r in range(world)]).to(torch.int64).to(dev)
     if dst is None:
         b_max = max(counts)
         uniform = all(c == b_max for c in counts) and all(m == m_max for m in ms)
         if uniform and mel.is_contiguous():               # equal shards (the weak-scaling case): no padding copies
-            block = mel
+            block, lens_block = mel, lens
         else:
             block = torch.zeros((b_max, C, m_max), dtype=mel.dtype, device=dev)
             block[:b_local, :, :m_local] = mel
+            lens_block = torch.zeros((b_max,), dtype=torch.int64, device=dev)
+            lens_block[:b_local] = lens
         blocks = torch.empty((world, b_max, C, m_max), dtype=mel.dtype, device=dev)
+        lens_blocks = torch.empty((world, b_max), dtype=torch.int64, device=dev)
         _all_gather(blocks, block, group)
+        _all_gather(lens_blocks, lens_block, group)
         if uniform:
-            return blocks.view(world * b_max, C, m_max), lens_all
-        return torch.cat([blocks[r, :counts[r]] for r in range(world)], dim=0), lens_all
-    total = sum(counts)
+            return blocks.view(world * b_max, C, m_max), lens_blocks.view(-1)
+        return (torch.cat([blocks[r, :counts[r]] for r in range(world)], dim=0),
+                torch.cat([lens_blocks[r, :counts[r]] for r in range(world)], dim=0))
     exact = all(m == m_max or c == 0 for m, c in zip(ms, counts))
     out = (torch.empty if exact else torch.zeros)((total, C, m_max), dtype=mel.dtype, device=dev)
+    lens_all = torch.empty((total,), dtype=torch.int64, device=dev)
     ops, staged, b0 = [], [], 0
     for r in range(world):
         sl = slice(b0, b0 + counts[r])
         b0 += counts[r]
-        if counts[r] == 0 or ms[r] == 0:
+        if counts[r] == 0:
             continue
         if r == rank:
-            out[sl, :, :m_local] = mel
-        elif ms[r] == m_max:
+            lens_all[sl] = lens
+            if m_local > 0:
+                out[sl, :, :m_local] = mel
+            continue
+        ops.append(dist.P2POp(dist.irecv, lens_all[sl], _global_rank(r, group), group))
+        if ms[r] == 0:
+            continue
+        if ms[r] == m_max:
             ops.append(dist.P2POp(dist.irecv, out[sl], _global_rank(r, group), group))       # contiguous slice: in place
         else:
             buf = torch.empty((counts[r], C, ms[r]), dtype=mel.dtype, device=dev)
@@ -130,10 +158,6 @@ def _all_gather(dst: torch.Tensor, src: torch.Tensor, group) -> None:
     dist.all_gather(parts, src, group=group)
     for r, p in enumerate(parts):
         dst[r].copy_(p)
-
-
-def _all_reduce_max(t: torch.Tensor, group) -> None:
-    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
 
 
 def generate_sharded(model, x: torch.Tensor, speaker_emb: Optional[torch.Tensor] = None, group=None,

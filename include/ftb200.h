@@ -78,10 +78,11 @@ enum { FTB_EPI_AFFINE = 0, FTB_EPI_MAXPOOL = 1, FTB_EPI_HIGHWAY = 2 };
  * FTB_F_OUT_F16: `out` is fp16 [rows, out_ld] (out_ld, out_col0, n multiples of 8), rounded to nearest: the operand
  *                copy for a following FTB_F_A_F16 problem.  Any epilogue; residual / out_t / out_full (always fp32)
  *                may accompany it except with MAXPOOL; ROUND_TF32 is ignored.
- * FTB_F_OUT_SPLIT: (with FTB_F_OUT_F16, AFFINE epilogue, no residual / out_t / out_full) `out` receives every value v as
- *                THREE fp16 column blocks of width n: hi = fp16(v) at out_col0 + c, lo = fp16(v - hi) at out_col0 + n + c,
- *                hi again at out_col0 + 2n + c (out_ld >= out_col0 + 3n).  A consumer whose weights are packed as
- *                [W_hi | W_hi | W_lo] along K (cin = 3n, FTB_F_A_F16) then accumulates hi*W_hi + lo*W_hi + hi*W_lo: the
+ * FTB_F_OUT_SPLIT: (with FTB_F_OUT_F16, AFFINE or MAXPOOL epilogue, no residual / out_t / out_full) `out` receives every
+ *                value v as THREE fp16 column blocks of width seg = out_ld / 3: hi = fp16(v) at out_col0 + c, lo =
+ *                fp16(v - hi) at seg + out_col0 + c, hi again at 2 seg + out_col0 + c (out_col0 + n <= seg, so several
+ *                problems -- the CBHG bank -- fill one split buffer).  A consumer whose weights are packed as
+ *                [W_hi | W_hi | W_lo] along K (cin = 3 seg, FTB_F_A_F16) then accumulates hi*W_hi + lo*W_hi + hi*W_lo: the
  *                product at ~2^-20 relative operand precision instead of 2^-11, on the same kind::f16 MMAs.  Used for
  *                the DURATION predictor, whose output is rounded to integers (forward_tacotron.py:174-177,
  *                common_layers.py:18-21): an operand error of 2^-11 moves durations across the .5 boundary.           */

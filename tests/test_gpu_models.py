@@ -311,11 +311,12 @@ def test_forward_tacotron_eval_forward_vs_reference_golden(kind, golden, speaker
         got, want = out[k].cpu(), torch.from_numpy(g[k])
         assert max_abs(got[valid], want[valid]) < MEL_ABS, k
         # 'mel' and the un-padded (longest) sentence meet the 1e-3 bar.  'mel_post' of a PADDED sentence is bounded at
-        # 3e-3: its postnet sees the lin(padding vector) rows (|value| ~ 30, exact here) next to the sentence, and the
-        # tf32 rounding of operands of that magnitude (abs error ~7e-3 per element instead of ~2e-4) reaches the
-        # neighbouring valid frames through the conv bank taps and the backward GRU.
+        # 2e-3 (measured 1.33e-3; round 1: 3e-3 / 2.5e-3): its postnet sees the lin(padding vector) rows (|value| ~ 30)
+        # next to the sentence.  The conv chain bank -> proj1 -> proj2 now runs split-precision on those rows
+        # (engine.cbhg_levels chain_split), what is left enters through the single-fp16 highway / W_ih operands of the
+        # padding rows and the backward GRU that starts inside them.
         assert rel_l2(got[longest], want[longest]) < MEL_REL, k
-        assert rel_l2(got[valid], want[valid]) < (MEL_REL if k == 'mel' else 3e-3), k
+        assert rel_l2(got[valid], want[valid]) < (MEL_REL if k == 'mel' else 2e-3), k
     assert max_abs(out['dur'].cpu(), g['dur']) < 5e-3 and max_abs(out['pitch'].cpu(), g['pitch']) < 5e-3
     assert max_abs(out['energy'].cpu(), g['energy']) < 5e-3
     if speaker_dims:
