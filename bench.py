@@ -249,6 +249,7 @@ def run_ours(args, rank, world, local_rank):
     from forwardtacotron_b200 import runtime as rt
     dev = torch.device('cuda', local_rank)
     torch.cuda.set_device(dev)
+    numa = par.bind_host_to_device(dev) if world > 1 else None
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     peaks = load_peaks()
@@ -307,14 +308,43 @@ def run_ours(args, rank, world, local_rank):
     def step_resident():
         generate(x_dev)
 
+    exchange = par.LengthExchange(dev) if world > 1 else None
+    d2h_stream = torch.cuda.Stream(dev) if world > 1 else None
+    counts = [B] * world if w['scaling'] == 'weak' else \
+        [(lambda s: s.stop - s.start)(par.shard_slice(w['batch'], r, world)) for r in range(world)]
+
+    trace = [] if os.environ.get('FTB_E2E_TRACE') else None
+
+    def mark():
+        if trace is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            trace.append((e, time.perf_counter()))
+
     def step_e2e():
+        mark()
         xd = x_pin.to(dev, non_blocking=True)
-        o = generate(xd)
         if world > 1:
-            # the path's only exchange: the variable-length mels travel to ONE consumer (rank 0) over NVLink, point to
-            # point, sized by a device-side metadata all_gather; no rank but the consumer ever syncs with its host
-            par.gather_variable_mels(o['mel_post'], par.mel_lengths(o['dur']), dst=0, b_cap=b_cap)
-        host_out.copy_(o['mel_post'], non_blocking=True)
+            # the path's only exchange: the regulated lengths cross in one 16-byte NCCL all_gather enqueued from inside
+            # generate(), then the variable-length mels travel to ONE consumer (rank 0) over NVLink, point to point;
+            # nothing is exchanged on the host and no rank drains its stream
+            with exchange:
+                o = generate(xd)
+            mark()
+            # this rank's own D2H (PCIe copy engine) runs beside the NVLink gather: side stream, joined below
+            main = torch.cuda.current_stream(dev)
+            d2h_stream.wait_stream(main)
+            with torch.cuda.stream(d2h_stream):
+                host_out.copy_(o['mel_post'], non_blocking=True)
+            o['mel_post'].record_stream(d2h_stream)
+            par.gather_variable_mels(o['mel_post'], par.mel_lengths(o['dur']), dst=0,
+                                     shapes=(counts, exchange.lengths()))
+            mark()
+            main.wait_stream(d2h_stream)            # the timed region ends when BOTH the gather and the D2H are done
+        else:
+            o = generate(xd)
+            host_out.copy_(o['mel_post'], non_blocking=True)
+        mark()
 
     with ClockSampler(local_rank) as clocks:
         l0 = handle.launch_count()
@@ -323,6 +353,14 @@ def run_ours(args, rank, world, local_rank):
         for _ in range(2):                 # untimed: first-use setup of the gather collectives / pinned copy path
             step_e2e()
         ms_e2e = timed(step_e2e)
+        if trace:                       # FTB_E2E_TRACE=1: where an e2e step goes (device and host clocks), per rank
+            torch.cuda.synchronize(dev)
+            n = 4 if world > 1 else 2
+            rows = [trace[i:i + n] for i in range(len(trace) - n * args.steps, len(trace), n)]
+            dev_ms = [sum(r[j][0].elapsed_time(r[j + 1][0]) for r in rows) / len(rows) for j in range(n - 1)]
+            host_ms = [sum((r[j + 1][1] - r[j][1]) * 1e3 for r in rows) / len(rows) for j in range(n - 1)]
+            sys.stderr.write(f'e2e trace rank {rank}: device ms per phase {[round(v, 3) for v in dev_ms]} host ms '
+                             f'{[round(v, 3) for v in host_ms]} (phases: h2d+generate, gather, d2h)\n')
         # per-launch device times of the two programs (buffers still hold the last step's data)
         st = model.__dict__['_accel']
         per = {}
@@ -459,7 +497,8 @@ def run_ours(args, rank, world, local_rank):
             'config': workload_config(wl, durations, world),
             'run': {'frames_per_step_rank0': frames, 'sentences_rank0': B, 'padded_mel_len_rank0': M,
                     'l2': 'flushed between timed iterations (512 MiB memset)',
-                    'parallelism': f'sentence-sharded x{world}, weights replicated'},
+                    'parallelism': f'sentence-sharded x{world}, weights replicated',
+                    'host_cpus_rank0': numa},
             'e2e': {'value': total_frames * args.steps / (ms_e2e / 1e3), 'unit': UNIT,
                     'h2d_bytes_per_step': x_pin.numel() * 8, 'd2h_bytes_per_step': host_out.numel() * 4},
             'gpu_launches': int(launches), 'clocks': clk, 'roofline': roof, 'roofline_by_kernel': by_kernel,

@@ -176,17 +176,33 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     return prog
 
 
+# Set by forwardtacotron_b200.parallel around a sharded generate(): called with (meta, lens) -- both device tensors --
+# right after K5's scan has been enqueued and BEFORE this rank's host blocks on the scan result, so a collective it
+# enqueues (the exchange of the regulated lengths between the ranks) runs on the GPU while the host is waiting anyway.
+scan_hook = None
+_PINNED_META = {}
+
+
 def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
     """Runs K5's scan on `dur` (clamped / fallback-filled IN PLACE like the reference) and reads the
-    three integers the host needs (max length, fallback flag, total frames): the one D2H sync."""
+    three integers the host needs (max length, fallback flag, total frames): the one D2H sync of generate(), through a
+    pinned buffer and an event (the host waits for the 16-byte copy, not for a stream drain)."""
     B, T = dur.shape
     dev = dur.device
     cum = torch.empty((B, T), dtype=torch.int32, device=dev)
     lens = torch.empty((B,), dtype=torch.int32, device=dev)
     meta = torch.empty((4,), dtype=torch.int32, device=dev)
     handle.lr_scan(dur, B, T, apply_fallback, cum, lens, meta)
-    m = meta.cpu()
-    return cum, lens, int(m[0]), int(m[2])
+    pin = _PINNED_META.get(dev)
+    if pin is None:
+        pin = _PINNED_META[dev] = (torch.empty((4,), dtype=torch.int32).pin_memory(), torch.cuda.Event())
+    host, ev = pin
+    host.copy_(meta, non_blocking=True)
+    ev.record(torch.cuda.current_stream(dev))
+    if scan_hook is not None:
+        scan_hook(meta, lens)
+    ev.synchronize()
+    return cum, lens, int(host[0]), int(host[2])
 
 
 def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program, prog: eng.Program,

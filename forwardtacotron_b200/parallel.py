@@ -12,6 +12,30 @@ import torch
 import torch.distributed as dist
 
 
+def bind_host_to_device(device: torch.device) -> Optional[str]:
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off (sysfs `local_cpulist` of the PCI device), so the
+    pinned staging buffers of the H2D / D2H copies are first-touched on that node.  One process per GPU under torchrun is
+    not NUMA-bound by default; with 8 ranks copying their mels to the host at once the far-node traffic shows.  Returns
+    the cpu list it bound to, or None when sysfs does not say (then nothing changes)."""
+    import os
+    try:
+        p = torch.cuda.get_device_properties(device)
+        path = f'/sys/bus/pci/devices/{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0/local_cpulist'
+        with open(path) as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(','):
+            lo, _, hi = part.partition('-')
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return spec
+    except Exception:
+        return None
+
+
 def shard_slice(n: int, rank: int, world: int) -> slice:
     """Contiguous, balanced slice of `n` sentences for `rank` (the first n % world ranks get one more)."""
     base, extra = divmod(n, world)
@@ -42,6 +66,59 @@ def _host_group(group):
     return _HOST_GROUPS['world']
 
 
+class LengthExchange:
+    """Device-side exchange of the regulated lengths M_local between the ranks of a sharded generate().
+
+    `with LengthExchange(model_device, group) as ex: out = model.generate(...)`: while active, the accelerated models
+    call `ex._hook(meta, lens)` right after the LengthRegulator scan has been enqueued (models/_accel.scan_hook), where
+    this class enqueues ONE 16-byte NCCL all_gather of `meta` and an asynchronous copy of the result into pinned host
+    memory.  The collective runs on the GPU at a point where this rank's host is waiting for the scan result anyway;
+    `ex.lengths()` afterwards only waits for that copy's event -- no host-side (gloo / TCP) round trip and no stream
+    drain between generate() and the gather of the mels."""
+
+    def __init__(self, device: torch.device, group=None):
+        self.device, self.group = device, group
+        self.world = dist.get_world_size(group)
+        self._dev = torch.zeros((self.world, 4), dtype=torch.int32, device=device)
+        self._host = torch.zeros((self.world, 4), dtype=torch.int32).pin_memory()
+        self._event = torch.cuda.Event()
+        self._scanned = torch.cuda.Event()
+        self._side = torch.cuda.Stream(device)
+        self._fired = False
+
+    def _hook(self, meta: torch.Tensor, lens: torch.Tensor) -> None:
+        if self._fired:                       # one exchange per generate() (the first scan)
+            return
+        self._fired = True
+        # On a SIDE stream that waits for the scan only: the collective is a rendezvous of all ranks, and the compute
+        # stream (frame program next) must not wait for the slowest rank's token program.
+        main = torch.cuda.current_stream(self.device)
+        self._scanned.record(main)
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(self._scanned)
+            dist.all_gather_into_tensor(self._dev, meta, group=self.group)
+            self._host.copy_(self._dev, non_blocking=True)
+            self._event.record(self._side)
+        meta.record_stream(self._side)
+
+    def __enter__(self):
+        from .models import _accel
+        self._fired = False
+        _accel.scan_hook = self._hook
+        return self
+
+    def __exit__(self, *exc):
+        from .models import _accel
+        _accel.scan_hook = None
+        if not self._fired and exc[0] is None:      # a rank with an empty shard still takes part in the collective
+            self._hook(torch.zeros((4,), dtype=torch.int32, device=self.device), None)
+
+    def lengths(self):
+        """M_local of every rank (host integers)."""
+        self._event.synchronize()
+        return [int(v) for v in self._host[:, 0]]
+
+
 def _shapes(b_local: int, m_local: int, dev, on_cuda: bool, group):
     """(b_local, M_local) of every rank as host integers.  Both are HOST-known on every rank the moment generate()
     returns (tensor shapes; generate() itself read M from the device while the frame program was being enqueued), so
@@ -62,7 +139,7 @@ def _shapes(b_local: int, m_local: int, dev, on_cuda: bool, group):
 
 
 def gather_variable_mels(mel: torch.Tensor, lens: torch.Tensor, group=None, dst: Optional[int] = None,
-                         b_cap: Optional[int] = None) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+                         b_cap: Optional[int] = None, shapes=None) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """Gather `[b_local, C, M_local]` mels whose batch and frame extents differ per rank.
 
     dst = r   : gather to rank r only (the consumer): every other rank SENDS its own contiguous block and its lengths,
@@ -72,14 +149,15 @@ def gather_variable_mels(mel: torch.Tensor, lens: torch.Tensor, group=None, dst:
     dst = None: every rank receives everything (all_gather of zero-padded blocks), for callers that need it everywhere.
     No rank drains its stream: the receives / collectives are enqueued behind the still-running frame program.
     Returns (`[B_total, C, M_max]`, `[B_total]` int64) with the sentences in rank order; frames beyond a shard's own
-    M_local are zero.  (`b_cap` is accepted for compatibility and unused.)
+    M_local are zero.  `shapes` = ([b_local of every rank], [M_local of every rank]) when the caller already has them
+    (generate_sharded: shard split + LengthExchange) -- then nothing is exchanged on the host.  (`b_cap`: unused.)
     """
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return mel, lens.to(torch.int64)
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dev = mel.device
     b_local, C, m_local = mel.shape
-    counts, ms = _shapes(b_local, m_local, dev, mel.is_cuda, group)
+    counts, ms = shapes if shapes is not None else _shapes(b_local, m_local, dev, mel.is_cuda, group)
     m_max, total = max(ms), sum(counts)
     lens = lens.to(torch.int64)
     if dst is not None and rank != dst:
@@ -174,20 +252,30 @@ def generate_sharded(model, x: torch.Tensor, speaker_emb: Optional[torch.Tensor]
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     sl = shard_slice(x.shape[0], rank, world)
     args = (x[sl],) if speaker_emb is None else (x[sl], speaker_emb[sl])
-    if sl.stop > sl.start:
-        out = model.generate(*args, **generate_kwargs)
-        lens = mel_lengths(out['dur'])
-        mel, mel_post = out['mel'], out['mel_post']
-    else:                                  # more ranks than sentences: contribute an empty block
-        n_mels = getattr(model, 'n_mels', 80)
-        mel = mel_post = torch.zeros((0, n_mels, 0), device=x.device)
-        lens = torch.zeros((0,), dtype=torch.int64, device=x.device)
+    # accelerated models on the GPUs: the regulated lengths are exchanged on the device from inside generate()
+    ex = LengthExchange(x.device, group) if (world > 1 and x.is_cuda and hasattr(model, 'program_for')) else None
+
+    def run():
+        if sl.stop > sl.start:
+            o = model.generate(*args, **generate_kwargs)
+            return mel_lengths(o['dur']), o['mel'], o['mel_post']
+        n_mels = getattr(model, 'n_mels', 80)          # more ranks than sentences: contribute an empty block
+        empty = torch.zeros((0, n_mels, 0), device=x.device)
+        return torch.zeros((0,), dtype=torch.int64, device=x.device), empty, empty
+    if ex is not None:
+        with ex:
+            lens, mel, mel_post = run()
+        counts = [(lambda s: s.stop - s.start)(shard_slice(x.shape[0], r, world)) for r in range(world)]
+        shapes = (counts, ex.lengths())
+    else:
+        lens, mel, mel_post = run()
+        shapes = None
     b_cap = -(-x.shape[0] // world)                      # ceil: the largest shard of shard_slice
-    post_all, lens_all = gather_variable_mels(mel_post, lens, group, dst, b_cap)
+    post_all, lens_all = gather_variable_mels(mel_post, lens, group, dst, b_cap, shapes)
     if not gather_mel:
         mel_all = None
     elif mel is mel_post or mel.data_ptr() == mel_post.data_ptr():
         mel_all = post_all
     else:
-        mel_all, _ = gather_variable_mels(mel, lens, group, dst, b_cap)
+        mel_all, _ = gather_variable_mels(mel, lens, group, dst, b_cap, shapes)
     return {'mel': mel_all, 'mel_post': post_all, 'mel_lens': lens_all}
