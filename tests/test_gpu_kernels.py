@@ -719,3 +719,35 @@ def test_program_set_seq_len_reuses_plans():
         exact.close()
     with pytest.raises(AssertionError):
         big.set_seq_len(65)
+
+
+@pytest.mark.parametrize('cell,H,B,mode', [('gru', 256, 33, 'cluster'), ('lstm', 512, 64, 'l2'), ('gru', 64, 17, 'cluster')])
+def test_recurrence_repeatability_stress(cell, H, B, mode, monkeypatch):
+    """Race evidence for the hand-off protocols (compute-sanitizer is closed on this pool, profiles/r2_sanitizer.txt): 20
+    back-to-back runs of one plan -- eager launches first, CUDA-graph replays after -- are bit-identical.  A hand-off
+    that is consumed early, lost or double-delivered changes h_t; the step count (150) gives it ~6000 chances per run."""
+    monkeypatch.setenv('FTB_RNN_HANDOFF', mode)
+    L, In = 150, 64
+    gen = torch.Generator().manual_seed(H + B)
+    rnn = (torch.nn.GRU if cell == 'gru' else torch.nn.LSTM)(In, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    packed = pk.PackedRnn(rnn.to(DEV))
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    a, _ = _fill(prog, 'x', In, gen)
+    xp = prog.buf('xp', packed.ih.n)
+    out = prog.buf('h', 2 * H)
+    prog.gemm(a, packed.ih, xp, round_out=False)
+    prog.rnn([(packed, xp, out, 0)])
+    assert prog.info[-1]['handoff'] == mode
+    first = None
+    for i in range(20):
+        out.zero_()
+        prog.run()
+        torch.cuda.synchronize()
+        got = prog.view('h').clone()
+        assert bool(torch.isfinite(got).all())
+        if first is None:
+            first = got
+        assert torch.equal(got, first), f'run {i} differs'
