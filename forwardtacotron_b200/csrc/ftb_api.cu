@@ -54,6 +54,7 @@ extern "C" int ftb_destroy(ftb_handle h) {
   if (!h) return FTB_E_ARG;
   for (auto& kv : h->gemm_plans) gemm_plan_free(kv.second);
   for (auto& kv : h->rnn_plans) rnn_plan_free(kv.second);
+  for (auto& kv : h->tail_plans) tail_plan_free(kv.second);
   delete h;
   return 0;
 }
@@ -154,5 +155,44 @@ extern "C" int ftb_rnn_plan_destroy(ftb_handle h, int plan) {
   if (it == h->rnn_plans.end()) return FTB_E_PLAN;
   rnn_plan_free(it->second);
   h->rnn_plans.erase(it);
+  return 0;
+}
+
+extern "C" int ftb_cbhg_tail_plan_create(ftb_handle h, const ftb_cbhg_tail_problem* problem, int* plan_out) {
+  if (!h || !plan_out) return FTB_E_ARG;
+  DeviceScope scope(h->device);
+  TailPlan plan;
+  const int rc = tail_plan_build(problem, h->num_sms, &plan);
+  if (rc) { tail_plan_free(plan); return rc; }
+  const int id = h->next_plan++;
+  h->tail_plans[id] = plan;
+  *plan_out = id;
+  return 0;
+}
+
+extern "C" int ftb_cbhg_tail_plan_run(ftb_handle h, int plan, void* stream) {
+  if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
+  auto it = h->tail_plans.find(plan);
+  if (it == h->tail_plans.end()) return FTB_E_PLAN;
+  h->launches += 1;
+  return tail_plan_launch(it->second, h->num_sms, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ftb_cbhg_tail_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream) {
+  if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
+  auto it = h->tail_plans.find(plan);
+  if (it == h->tail_plans.end()) return FTB_E_PLAN;
+  return tail_plan_set_geometry(it->second, seq_len, seq_stride, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ftb_cbhg_tail_plan_destroy(ftb_handle h, int plan) {
+  if (!h) return FTB_E_ARG;
+  DeviceScope scope(h->device);
+  auto it = h->tail_plans.find(plan);
+  if (it == h->tail_plans.end()) return FTB_E_PLAN;
+  tail_plan_free(it->second);
+  h->tail_plans.erase(it);
   return 0;
 }

@@ -782,7 +782,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D row-major [rows, cols] fp32 or fp16 (leading dimension ld elements), box {128 bytes, box_rows}, 128B swizzle.
-static int make_map(CUtensorMap* m, const void* base, long long rows, int cols, int ld, int box_rows, bool f16) {
+int tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int cols, int ld, int box_rows, bool f16) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return FTB_E_DRIVER;
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
@@ -870,9 +870,9 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     d.cap_rows = q.rows;
     d.tile_base = tile_base;
     tile_base += (pair ? (d.m_tiles + 1) / 2 : d.m_tiles) * d.n_tiles;
-    int rc = make_map(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
+    int rc = tensor_map_2d(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
     if (rc) return rc;
-    rc = make_map(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, pair ? q.bn / 2 : q.bn, a16);
+    rc = tensor_map_2d(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, pair ? q.bn / 2 : q.bn, a16);
     if (rc) return rc;
     const long long e = q.rows * q.n;
     if (e > simt_elems) simt_elems = e;

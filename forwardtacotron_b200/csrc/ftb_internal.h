@@ -61,6 +61,34 @@ int gemm_plan_launch(const GemmPlan& plan, int impl, int num_sms, cudaStream_t s
 int gemm_plan_set_geometry(GemmPlan& plan, int seq_len, int seq_stride, cudaStream_t stream);
 void gemm_plan_free(GemmPlan& plan);
 
+// 2-D row-major [rows, cols] fp32 or fp16 tensor map (leading dimension ld elements), box {128 bytes, box_rows}, 128B swizzle
+int tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int cols, int ld, int box_rows, bool f16);
+
+// ------------------------------------------------------------------ fused CBHG tail (ftb_tail.cu)
+struct alignas(128) TailProblemDev {
+  CUtensorMap tm_a;      // proj2 output  [rows, cin]          fp16, box {64, 128}
+  CUtensorMap tm_wpre;   // pre_highway   [256, cin]           fp16, box {64, 256}
+  CUtensorMap tm_whw;    // highways      [nh * 512, 256]      fp16, box {64, 256}  (pack_highway layout, bn = 256)
+  CUtensorMap tm_wih;    // W_ih          [ih_chunks*256, 256] fp16, box {64, 256}
+  const float* b_hw;     // [nh][512] = b1 | b2
+  const float* b_ih;     // [n_ih]
+  void* out;             // x-projection [rows, out_ld] fp32 or fp16
+  long long rows, cap_rows;
+  int batch, seq_len, seq_stride;
+  int m_tiles, n_highways, kb_in, n_ih, ih_chunks, out_ld, out_f16;
+};
+
+struct TailPlan {
+  TailProblemDev* dev = nullptr;
+  TailProblemDev host{};
+  int cap_tiles = 0;
+};
+
+int tail_plan_build(const ftb_cbhg_tail_problem* q, int num_sms, TailPlan* plan);
+int tail_plan_launch(const TailPlan& plan, int num_sms, cudaStream_t stream);
+int tail_plan_set_geometry(TailPlan& plan, int seq_len, int seq_stride, cudaStream_t stream);
+void tail_plan_free(TailPlan& plan);
+
 // ------------------------------------------------------------------ recurrences (ftb_rnn.cu)
 struct RnnProblemDev {
   const float* xproj;
@@ -126,4 +154,5 @@ struct ftb_context {
   int next_plan = 1;
   std::map<int, ftb::GemmPlan> gemm_plans;
   std::map<int, ftb::RnnPlan> rnn_plans;
+  std::map<int, ftb::TailPlan> tail_plans;
 };

@@ -29,6 +29,8 @@ F16_OPERANDS = _F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
 # W_hh, exact gates): raw duration error ~1e-5 instead of ~3e-3, so the rounded durations (common_layers.py:21) match
 # the reference's except within ~1e-4 of a .5 tie.  FTB_PRECISE_DUR=0 restores the single-fp16 path (diagnostic).
 PRECISE_DUR = os.environ.get('FTB_PRECISE_DUR', '1') != '0'
+# pre_highway -> highways -> W_ih of a CBHG as ONE persistent kernel (ftb_tail.cu) instead of six GEMM launches
+FUSED_TAIL = os.environ.get('FTB_FUSED_TAIL', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -101,6 +103,7 @@ class Program:
         self.steps: List[Callable[[], None]] = []
         self._gemm_plans: List[int] = []
         self._rnn_plans: List[int] = []
+        self._tail_plans: List[int] = []
         self._pending: List[rt.GemmProblem] = []
         self._glue: list = []                         # queued embeddings / predictor heads: one batched launch per kind
         self._keep: list = []                         # tensors the plans point into
@@ -156,6 +159,8 @@ class Program:
             self.h.gemm_set_geometry(plan, seq_len, g.stride)
         for plan in self._rnn_plans:
             self.h.rnn_set_geometry(plan, seq_len, g.stride)
+        for plan in self._tail_plans:
+            self.h.tail_set_geometry(plan, seq_len, g.stride)
         valid = g.batch * seq_len
         for i in self.info:
             if 'flops_row' in i:
@@ -299,6 +304,35 @@ class Program:
                           'flops_row': flops / valid, 'bytes_row': (nbytes - wbytes) / valid, 'bytes_fixed': wbytes,
                           'steps': g.seq_len, 'problems': len(specs), **self.h.rnn_info(plan)})
 
+    def cbhg_tail(self, a: torch.Tensor, c: 'CbhgPack', xp: torch.Tensor):
+        """pre_highway -> highways -> W_ih projection of one CBHG as ONE fused launch (include/ftb200.h, K2f):
+        a = conv_project2's fp16 operand copy [rows, proj2.n], xp = the x-projection buffer (fp32 or fp16)."""
+        self.flush()
+        g = self.geo
+        w_pre = c.pre_highway.w16[0]                                             # [256, cin]
+        w_hw = torch.cat([w.w16[0] for w in c.highways], dim=0).contiguous()      # [nh * 512, 256]
+        b_hw = torch.cat([w.bias0 for w in c.highways]).contiguous()              # [nh * 512]
+        w_ih, b_ih = c.rnn.ih.w16[0], c.rnn.ih.bias0
+        p = rt.CbhgTailProblem()
+        p.a, p.lda, p.cin, p.channels = a.data_ptr(), a.shape[1], c.pre_highway.cin, c.channels
+        p.w_pre, p.n_highways, p.w_hw, p.b_hw = w_pre.data_ptr(), len(c.highways), w_hw.data_ptr(), b_hw.data_ptr()
+        p.w_ih, p.b_ih, p.n_ih = w_ih.data_ptr(), b_ih.data_ptr(), c.rnn.ih.n
+        p.out, p.out_ld, p.out_f16 = xp.data_ptr(), xp.shape[1], int(xp.dtype == torch.float16)
+        p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
+        plan = self.h.tail_plan(p)
+        self._tail_plans.append(plan)
+        self._keep += [a, w_pre, w_hw, b_hw, w_ih, b_ih, xp]
+        self.steps.append(lambda plan=plan: self.h.tail_run(plan))
+        valid = g.batch * g.seq_len
+        ch = c.channels
+        per_row = 2.0 * (c.pre_highway.cin * ch + len(c.highways) * 2 * ch * ch + ch * c.rnn.ih.n)
+        wbytes = 2.0 * (w_pre.numel() + w_hw.numel() + w_ih.numel())
+        brow = 2.0 * c.pre_highway.cin + xp.element_size() * c.rnn.ih.n
+        self.info.append({'kind': 'gemm', 'label': self._label or 'cbhg_tail', 'flops': per_row * valid,
+                          'flops_f16': per_row * valid, 'bytes': brow * valid + wbytes, 'problems': 2 + len(c.highways),
+                          'flops_row': per_row, 'flops_f16_row': per_row, 'bytes_row': brow, 'bytes_fixed': wbytes,
+                          'cta_pairs': False, 'slots': (g.rows + 127) // 128, 'fused_tail': True})
+
     def call(self, fn: Callable[[], None], label: str = 'glue', nbytes: float = 0.0):
         self.flush()
         self._baked_len = True
@@ -367,6 +401,9 @@ class Program:
             self.h.gemm_destroy(p)
         for p in self._rnn_plans:
             self.h.rnn_destroy(p)
+        for p in self._tail_plans:
+            self.h.tail_destroy(p)
+        self._tail_plans = []
         self._graphs = {}
         self._gemm_plans, self._rnn_plans, self.steps = [], [], []
 
@@ -416,10 +453,6 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
     f16s = _F16_OPERANDS and c.proj2.n % 8 == 0 and ch % 8 == 0
     sdt = torch.float16 if f16s else torch.float32
     p2 = prog.buf(f'{tag}.proj2', c.proj2.n, sdt)
-    hw = [prog.buf(f'{tag}.hw0', ch, sdt), prog.buf(f'{tag}.hw1', ch, sdt)]
-    # unrounded twins of the highway activations: the residual term (1-g)*x uses full fp32 values, only the
-    # GEMM operand copy is tf32-rounded
-    hwf = [prog.buf(f'{tag}.hw0_full', ch), prog.buf(f'{tag}.hw1_full', ch)]
     xp = prog.buf(f'{tag}.xproj', c.rnn.ih.n, torch.float16 if (xproj_f16 and c.rnn.ih.n % 8 == 0) else torch.float32)
     levels = []
 
@@ -442,6 +475,19 @@ def cbhg_levels(prog: Program, tag: str, c: CbhgPack, x: torch.Tensor, out: torc
                                                    split_out=chain_split)))
     levels.append(named('proj2', lambda: prog.gemm(p1, c.proj2, p2, split_in=chain_split,         # :111-114
                                                    residual=x_full if x_full is not None else x)))
+    if (FUSED_TAIL and f16s and ch == 256 and c.pre_highway.cin % 8 == 0 and c.rnn.ih.n % 16 == 0
+            and all(w.bn == 256 for w in c.highways)):
+        # :118-123 (W_ih half) as one fused launch: the highway activations never leave the SM
+        def l_tail():
+            prog.label(f'{tag}.tail')
+            prog.cbhg_tail(p2, c, xp)
+            prog.label('')
+        levels.append(l_tail)
+        return levels, (c.rnn, xp, out, out_col0)
+    hw = [prog.buf(f'{tag}.hw0', ch, sdt), prog.buf(f'{tag}.hw1', ch, sdt)]
+    # unrounded twins of the highway activations: the residual term (1-g)*x uses full fp32 values, only the
+    # GEMM operand copy is tf32-rounded
+    hwf = [prog.buf(f'{tag}.hw0_full', ch), prog.buf(f'{tag}.hw1_full', ch)]
     levels.append(named('pre_highway', lambda: prog.gemm(p2, c.pre_highway, hw[0], out_full=hwf[0])))   # :118
     for i, w in enumerate(c.highways):                                                            # :119-120
         levels.append(named(f'highway{i}', lambda i=i, w=w: prog.gemm(

@@ -38,6 +38,13 @@ class RnnProblem(C.Structure):
                 ('out_f16', C.c_int32), ('x_f16', C.c_int32), ('precise', C.c_int32)]
 
 
+class CbhgTailProblem(C.Structure):
+    _fields_ = [('a', _fp), ('lda', C.c_int32), ('cin', C.c_int32), ('channels', C.c_int32), ('w_pre', _fp),
+                ('n_highways', C.c_int32), ('w_hw', _fp), ('b_hw', _fp), ('w_ih', _fp), ('b_ih', _fp),
+                ('n_ih', C.c_int32), ('out', _fp), ('out_ld', C.c_int32), ('out_f16', C.c_int32),
+                ('batch', C.c_int32), ('seq_len', C.c_int32), ('seq_stride', C.c_int32)]
+
+
 class EmbedItem(C.Structure):
     _fields_ = [('tok', _fp), ('table', _fp), ('e1', C.c_int32),
                 ('tok2', _fp), ('table2', _fp), ('e2', C.c_int32),
@@ -69,6 +76,8 @@ class LrGatherArgs(C.Structure):
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
            'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy', 'ftb_gemm_plan_info',
            'ftb_gemm_plan_set_geometry', 'ftb_rnn_plan_set_geometry',
+           'ftb_cbhg_tail_plan_create', 'ftb_cbhg_tail_plan_run', 'ftb_cbhg_tail_plan_set_geometry',
+           'ftb_cbhg_tail_plan_destroy',
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
            'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
@@ -97,6 +106,10 @@ def load_library() -> C.CDLL:
     lib.ftb_gemm_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_gemm_plan_set_geometry.argtypes = [_fp, C.c_int, C.c_int, C.c_int, _fp]
     lib.ftb_rnn_plan_set_geometry.argtypes = [_fp, C.c_int, C.c_int, C.c_int, _fp]
+    lib.ftb_cbhg_tail_plan_create.argtypes = [_fp, C.POINTER(CbhgTailProblem), C.POINTER(C.c_int)]
+    lib.ftb_cbhg_tail_plan_run.argtypes = [_fp, C.c_int, _fp]
+    lib.ftb_cbhg_tail_plan_set_geometry.argtypes = [_fp, C.c_int, C.c_int, C.c_int, _fp]
+    lib.ftb_cbhg_tail_plan_destroy.argtypes = [_fp, C.c_int]
     lib.ftb_rnn_plan_create.argtypes = [_fp, C.POINTER(RnnProblem), C.c_int, C.POINTER(C.c_int)]
     lib.ftb_rnn_plan_run.argtypes = [_fp, C.c_int, _fp]
     lib.ftb_rnn_plan_destroy.argtypes = [_fp, C.c_int]
@@ -182,6 +195,20 @@ class Handle:
 
     def rnn_set_geometry(self, plan: int, seq_len: int, stride: int):
         self.check(self.lib.ftb_rnn_plan_set_geometry(self.h, plan, seq_len, stride, self.stream()))
+
+    def tail_plan(self, problem: CbhgTailProblem) -> int:
+        pid = C.c_int()
+        self.check(self.lib.ftb_cbhg_tail_plan_create(self.h, C.byref(problem), C.byref(pid)))
+        return pid.value
+
+    def tail_run(self, plan: int):
+        self.check(self.lib.ftb_cbhg_tail_plan_run(self.h, plan, self.stream()))
+
+    def tail_set_geometry(self, plan: int, seq_len: int, stride: int):
+        self.check(self.lib.ftb_cbhg_tail_plan_set_geometry(self.h, plan, seq_len, stride, self.stream()))
+
+    def tail_destroy(self, plan: int):
+        self.check(self.lib.ftb_cbhg_tail_plan_destroy(self.h, plan))
 
     def gemm_destroy(self, plan: int):
         self.check(self.lib.ftb_gemm_plan_destroy(self.h, plan))

@@ -135,6 +135,36 @@ int ftb_gemm_plan_info(ftb_handle h, int plan, int* cta_pairs, int* tiles);
 int ftb_gemm_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream);
 
 /* ------------------------------------------------------------------------------------
+ * K2f  fused row-local tail of a CBHG: pre_highway -> highways -> W_ih projection in ONE persistent kernel
+ *
+ * Replaces: `self.pre_highway(x)` (models/common_layers.py:118), `for h in self.highways: x = h(x)` (:119-120,
+ * HighwayNetwork.forward :35-40) and the W_ih x + b_ih half of `self.rnn(x)` (:123).  Every layer maps row r to row r,
+ * so a 128-row tile runs the whole chain on one SM: the activation tile stays in shared memory as an fp16 operand copy
+ * plus an fp16 remainder (their sum is the residual term of the highway), weights stream through a TMA ring, and only
+ * the x-projection is written to HBM.  Same arithmetic as the K1/K2 problems it replaces (fp16 operands, fp32
+ * accumulation, fp32 epilogue).
+ *   a      fp16 [rows, lda]: conv_project2 output + residual (the FTB_F_OUT_F16 operand copy), cin <= 256 columns
+ *   w_pre  fp16 [256][cin]                 pre_highway.weight (no bias)
+ *   w_hw   fp16 [n_highways][512][256]     per layer: [W1 rows | W2 rows] of units 0..127, then of units 128..255
+ *   b_hw   fp32 [n_highways][512]          per layer: b1 (256) | b2 (256)
+ *   w_ih   fp16 [n_ih rounded up to 256][256], b_ih fp32 [n_ih]: both directions, n_ih = 2 * 3 * H
+ *   out    [rows, out_ld] fp32, or fp16 when out_f16 != 0 (ftb_rnn_problem.x_f16); only rows with t < seq_len
+ * ------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* a; int32_t lda, cin;
+  int32_t channels;                 /* highway width: 256 */
+  const void* w_pre;
+  int32_t n_highways; const void* w_hw; const float* b_hw;
+  const void* w_ih; const float* b_ih; int32_t n_ih;
+  void* out; int32_t out_ld, out_f16;
+  int32_t batch, seq_len, seq_stride;
+} ftb_cbhg_tail_problem;
+int ftb_cbhg_tail_plan_create(ftb_handle h, const ftb_cbhg_tail_problem* problem, int* plan_out);
+int ftb_cbhg_tail_plan_run(ftb_handle h, int plan, void* stream);
+int ftb_cbhg_tail_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_stride, void* stream);
+int ftb_cbhg_tail_plan_destroy(ftb_handle h, int plan);
+
+/* ------------------------------------------------------------------------------------
  * K3/K4  persistent bidirectional GRU / LSTM recurrence
  *
  * Replaces: the time loop of nn.GRU (common_layers.py:123; forward_tacotron.py:37) and

@@ -751,3 +751,61 @@ def test_recurrence_repeatability_stress(cell, H, B, mode, monkeypatch):
         if first is None:
             first = got
         assert torch.equal(got, first), f'run {i} differs'
+
+
+@pytest.mark.parametrize('B,L,cin,x16', [(3, 130, 256, False), (2, 300, 80, True), (1, 50, 256, True)])
+def test_cbhg_tail_fused_matches_unfused_chain(B, L, cin, x16, monkeypatch):
+    """K2f (ftb_cbhg_tail_*): pre_highway -> 4 highways -> W_ih projection in ONE kernel against (a) the same chain as six
+    K1/K2 launches and (b) a float64 restatement of common_layers.py:118-123 on the same fp16 operands."""
+    from forwardtacotron_b200.models.common_layers import CBHG
+    torch.manual_seed(B * 100 + L)
+    m = CBHG(K=2, in_channels=cin, channels=256, proj_channels=[256, cin], num_highways=4, dropout=0.0).to(DEV).eval()
+    with torch.no_grad():
+        for h in m.highways:
+            h.W1.bias.normal_(0, 0.3)
+            h.W2.bias.normal_(0, 0.3)
+    from forwardtacotron_b200.models import _accel
+    pack = _accel.pack_cbhg(m)
+    gen = torch.Generator().manual_seed(L)
+    v = torch.randn(B, L, cin, generator=gen).to(torch.float16)
+    xdt = torch.float16 if x16 else torch.float32
+    outs = {}
+    for fused in (True, False):
+        monkeypatch.setattr(eng, 'FUSED_TAIL', fused)
+        prog = eng.Program(_handle(), eng.Geometry(B, L))
+        g = prog.geo
+        a = prog.buf('a', cin, torch.float16)
+        a.view(g.batch, g.stride, cin)[:, :L] = v.to(DEV)
+        xp = prog.buf('xp', pack.rnn.ih.n, xdt)
+        if fused:
+            prog.cbhg_tail(a, pack, xp)
+        else:
+            hw = [prog.buf('h0', 256, torch.float16), prog.buf('h1', 256, torch.float16)]
+            hwf = [prog.buf('h0f', 256), prog.buf('h1f', 256)]
+            prog.gemm(a, pack.pre_highway, hw[0], out_full=hwf[0])
+            prog.flush()
+            for i, w in enumerate(pack.highways):
+                prog.gemm(hw[i & 1], w, hw[(i + 1) & 1], epilogue=rt.EPI_HIGHWAY, residual=hwf[i & 1],
+                          out_full=hwf[(i + 1) & 1])
+                prog.flush()
+            prog.gemm(hw[0], pack.rnn.ih, xp, round_out=False)
+        for _ in range(2):
+            prog.run()
+        torch.cuda.synchronize()
+        outs[fused] = prog.view('xp').float().cpu()
+        assert float(xp.view(g.batch, g.stride, -1)[:, L:].float().abs().max()) == 0.0     # gap rows untouched
+    # float64 restatement on the same operands
+    x = v.double() @ pack.pre_highway.w16[0].double().cpu().t()
+    for h in m.highways:
+        xq = x.to(torch.float16).double()
+        x1 = xq @ h.W1.weight.detach().half().double().cpu().t() + h.W1.bias.detach().double().cpu()
+        x2 = xq @ h.W2.weight.detach().half().double().cpu().t() + h.W2.bias.detach().double().cpu()
+        gte = torch.sigmoid(x2)
+        x = gte * x1.clamp_min(0) + (1 - gte) * x
+    w_ih = torch.cat([m.rnn.weight_ih_l0, m.rnn.weight_ih_l0_reverse]).detach().half().double().cpu()
+    b_ih = torch.cat([m.rnn.bias_ih_l0, m.rnn.bias_ih_l0_reverse]).detach().double().cpu()
+    ref = x.to(torch.float16).double() @ w_ih.t() + b_ih
+    tol = 2e-3 if x16 else 5e-4
+    assert max_abs(outs[True], ref) < tol * max(1.0, float(ref.abs().max())), max_abs(outs[True], ref)
+    assert max_abs(outs[False], ref) < tol * max(1.0, float(ref.abs().max()))
+    assert max_abs(outs[True], outs[False]) < tol * max(1.0, float(ref.abs().max()))
