@@ -46,6 +46,9 @@ extern "C" int ftb_create(int device, ftb_handle* out) {
   ftb_context* c = new ftb_context();
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
+  ce = cudaMalloc(&c->err_word, sizeof(int));
+  if (ce == cudaSuccess) ce = cudaMemset(c->err_word, 0, sizeof(int));
+  if (ce != cudaSuccess) { cudaFree(c->err_word); delete c; return static_cast<int>(ce); }
   *out = c;
   return 0;
 }
@@ -55,6 +58,7 @@ extern "C" int ftb_destroy(ftb_handle h) {
   for (auto& kv : h->gemm_plans) gemm_plan_free(kv.second);
   for (auto& kv : h->rnn_plans) rnn_plan_free(kv.second);
   for (auto& kv : h->tail_plans) tail_plan_free(kv.second);
+  cudaFree(h->err_word);
   delete h;
   return 0;
 }

@@ -91,14 +91,20 @@ add_layernorm_kernel(const float* __restrict__ x, const float* __restrict__ res,
 __global__ void __launch_bounds__(256)
 posenc_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, const float* __restrict__ x_in,
               const float* __restrict__ pe, const float* __restrict__ scale_ptr, int e, int batch, int seq_len,
-              int seq_stride, float* __restrict__ out, float* __restrict__ out_full, int round) {
+              int seq_stride, float* __restrict__ out, float* __restrict__ out_full, int round, int table_rows,
+              int* __restrict__ err) {
   const int lane = threadIdx.x & 31;
   const long long row = blockIdx.x * 8ll + (threadIdx.x >> 5);
   if (row >= static_cast<long long>(batch) * seq_len) return;
   const int b = static_cast<int>(row / seq_len), t = static_cast<int>(row % seq_len);
   const long long off = (static_cast<long long>(b) * seq_stride + t) * e;
   const float sc = __ldg(scale_ptr);
-  const float* src = tok ? (table + tok[row] * e) : (x_in + off);
+  long long id = tok ? tok[row] : 0;
+  if (tok && (id < 0 || id >= table_rows)) {       // nn.Embedding would raise IndexError: clamp + flag (see ftb_misc.cu)
+    if (err) atomicOr(err, 1);
+    id = 0;
+  }
+  const float* src = tok ? (table + id * e) : (x_in + off);
   const float* per = pe + static_cast<long long>(t) * e;
   for (int c = lane; c < e; c += 32) {
     const float v = src[c] + sc * per[c];
@@ -403,13 +409,13 @@ extern "C" int ftb_add_layernorm(ftb_handle h, const float* x, const float* res,
 
 extern "C" int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, const float* x_in, const float* pe,
                           const float* scale_ptr, int e, int batch, int seq_len, int seq_stride, float* out,
-                          float* out_full, int round_tf32, void* stream) {
+                          float* out_full, int round_tf32, int table_rows, void* stream) {
   if (!h || !pe || !scale_ptr || !out || e < 1 || batch < 1 || seq_len < 1) return FTB_E_ARG;
-  if (tok ? !table : !x_in) return FTB_E_ARG;
+  if (tok ? (!table || table_rows < 1) : !x_in) return FTB_E_ARG;
   if (round_tf32 == 3 && (e % 8)) return FTB_E_SHAPE;
   const long long rows = static_cast<long long>(batch) * seq_len;
   posenc_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      tok, table, x_in, pe, scale_ptr, e, batch, seq_len, seq_stride, out, out_full, round_tf32);
+      tok, table, x_in, pe, scale_ptr, e, batch, seq_len, seq_stride, out, out_full, round_tf32, table_rows, h->err_word);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }

@@ -151,6 +151,8 @@ struct ftb_context {
   int device = 0;
   int num_sms = 0;
   int64_t launches = 0;
+  int* err_word = nullptr;    // device word: bit 0 = a token / class id outside its embedding table (set by the embedding
+                              // kernels, handed to the host through meta[3] of the next ftb_lr_scan and cleared there)
   int next_plan = 1;
   std::map<int, ftb::GemmPlan> gemm_plans;
   std::map<int, ftb::RnnPlan> rnn_plans;

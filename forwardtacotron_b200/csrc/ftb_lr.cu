@@ -17,7 +17,7 @@ constexpr int SCAN_THREADS = 1024;
 // L2-resident) so no grid-wide dependency is needed.
 __global__ void __launch_bounds__(SCAN_THREADS)
 lr_scan_kernel(float* __restrict__ dur, int batch, int T, int apply_fallback, int32_t* __restrict__ cum,
-               int32_t* __restrict__ lens, int32_t* __restrict__ meta) {
+               int32_t* __restrict__ lens, int32_t* __restrict__ meta, int* __restrict__ err) {
   __shared__ long long red[32];
   __shared__ int warp_tot[32];
   __shared__ int carry_s;
@@ -88,7 +88,12 @@ lr_scan_kernel(float* __restrict__ dur, int batch, int T, int apply_fallback, in
     lens[b] = len;
     atomicMax(meta + 0, len);
     atomicAdd(meta + 2, len);
-    if (b == 0) meta[1] = flag;
+    if (b == 0) {
+      meta[1] = flag;
+      // error word of the embedding kernels that ran before this scan on the stream (bit 0: id outside its table):
+      // handed over in meta[3] and cleared for the next call
+      meta[3] = err ? atomicExch(err, 0) : 0;
+    }
   }
 }
 
@@ -234,7 +239,7 @@ extern "C" int ftb_lr_scan(ftb_handle h, float* dur, int batch, int T, int apply
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t ce = cudaMemsetAsync(meta, 0, 4 * sizeof(int32_t), st);
   if (ce != cudaSuccess) return static_cast<int>(ce);
-  lr_scan_kernel<<<batch, SCAN_THREADS, 0, st>>>(dur, batch, T, apply_fallback, cum, lens, meta);
+  lr_scan_kernel<<<batch, SCAN_THREADS, 0, st>>>(dur, batch, T, apply_fallback, cum, lens, meta, h->err_word);
   const long long n = static_cast<long long>(batch) * T;
   int blocks = static_cast<int>((n + 255) / 256);
   if (blocks > 1184) blocks = 1184;
@@ -335,7 +340,7 @@ extern "C" int ftb_lr_regulate_static(ftb_handle h, const float* x, int x_stride
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t ce = cudaMemsetAsync(meta, 0, 4 * sizeof(int32_t), st);
   if (ce != cudaSuccess) return static_cast<int>(ce);
-  lr_scan_kernel<<<batch, SCAN_THREADS, 0, st>>>(dur, batch, T, apply_fallback, cum, lens, meta);
+  lr_scan_kernel<<<batch, SCAN_THREADS, 0, st>>>(dur, batch, T, apply_fallback, cum, lens, meta, h->err_word);
   const long long n = static_cast<long long>(batch) * T;
   int blocks = static_cast<int>((n + 255) / 256);
   if (blocks > 1184) blocks = 1184;

@@ -25,16 +25,27 @@ __device__ __forceinline__ void embed_store(float* out, long long i, float v, in
   }
 }
 
+// nn.Embedding raises IndexError for an id outside [0, rows) (forward_tacotron.py:31,210); here the id is clamped to row 0
+// (no out-of-bounds read) and bit 0 of the handle's error word is set -- generate() reads it with the scan result.
+__device__ __forceinline__ long long checked_row(long long id, int rows, int* err) {
+  if (id < 0 || id >= rows) {
+    if (err) atomicOr(err, 1);
+    return 0;
+  }
+  return id;
+}
+
 __device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
                                            const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
                                            const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
-                                           float* __restrict__ out, int out_ld, int mode) {
+                                           float* __restrict__ out, int out_ld, int mode, int rows1, int rows2,
+                                           int* __restrict__ err) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);          // batch * T < 2^31 (checked by the callers)
   if (row >= batch * T) return;
   const int b = row / T, t = row - b * T;
   const long long o = (static_cast<long long>(b) * seq_stride + t) * out_ld;
-  const float* s1 = table + tok[row] * e1;
+  const float* s1 = table + checked_row(tok[row], rows1, err) * e1;
   const int seg = out_ld / 3;
   if (mode != 3 && e2 == 0 && e3 == 0 && (e1 & 3) == 0 && (out_ld & 3) == 0 &&
       ((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0) {
@@ -55,7 +66,7 @@ __device__ __forceinline__ void embed_rows(const int64_t* __restrict__ tok, cons
   }
   for (int c = lane; c < e1; c += 32) embed_store(out, o + c, s1[c], mode, seg);
   if (e2 > 0) {
-    const float* s2 = table2 + tok2[row] * e2;
+    const float* s2 = table2 + checked_row(tok2[row], rows2, err) * e2;
     for (int c = lane; c < e2; c += 32) embed_store(out, o + e1 + c, s2[c], mode, seg);
   }
   if (e3 > 0) {
@@ -68,16 +79,16 @@ __global__ void __launch_bounds__(256)
 embed_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, int e1,
              const int64_t* __restrict__ tok2, const float* __restrict__ table2, int e2,
              const float* __restrict__ extra, int e3, int batch, int T, int seq_stride,
-             float* __restrict__ out, int out_ld, int mode) {
-  embed_rows(tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, mode);
+             float* __restrict__ out, int out_ld, int mode, int rows1, int rows2, int* __restrict__ err) {
+  embed_rows(tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, mode, rows1, rows2, err);
 }
 
 struct EmbedBatch { ftb_embed_item item[FTB_MAX_GLUE_ITEMS]; };
 __global__ void __launch_bounds__(256)
-embed_batch_kernel(const __grid_constant__ EmbedBatch args, int batch, int T, int seq_stride) {
+embed_batch_kernel(const __grid_constant__ EmbedBatch args, int batch, int T, int seq_stride, int* __restrict__ err) {
   const ftb_embed_item& it = args.item[blockIdx.y];
   embed_rows(it.tok, it.table, it.e1, it.tok2, it.table2, it.e2, it.extra, it.e3, batch, T, seq_stride, it.out, it.out_ld,
-             it.round_tf32);
+             it.round_tf32, it.rows1, it.rows2, err);
 }
 
 __device__ __forceinline__ void rowdot_rows(const float* __restrict__ x, int x_ld, int k, const float* __restrict__ w,
@@ -152,8 +163,8 @@ using namespace ftb;
 
 extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1, const int64_t* tok2,
                          const float* table2, int e2, const float* extra, int e3, int batch, int T, int seq_stride,
-                         float* out, int out_ld, int round_tf32, void* stream) {
-  if (!h || !tok || !table || !out || e1 < 1 || batch < 1 || T < 1) return FTB_E_ARG;
+                         float* out, int out_ld, int round_tf32, int rows1, int rows2, void* stream) {
+  if (!h || !tok || !table || !out || e1 < 1 || batch < 1 || T < 1 || rows1 < 1 || (e2 > 0 && rows2 < 1)) return FTB_E_ARG;
   if (e2 > 0 && (!tok2 || !table2)) return FTB_E_ARG;
   if (e3 > 0 && !extra) return FTB_E_ARG;
   if (seq_stride < T || round_tf32 < 0 || round_tf32 > 3) return FTB_E_ARG;
@@ -161,7 +172,7 @@ extern "C" int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, i
   const long long rows = static_cast<long long>(batch) * T;
   if (rows > 0x7fffffffll) return FTB_E_ARG;
   embed_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, round_tf32);
+      tok, table, e1, tok2, table2, e2, extra, e3, batch, T, seq_stride, out, out_ld, round_tf32, rows1, rows2, h->err_word);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }
@@ -172,7 +183,7 @@ extern "C" int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int ni
   EmbedBatch args{};
   for (int i = 0; i < nitems; ++i) {
     const ftb_embed_item& q = items[i];
-    if (!q.tok || !q.table || !q.out || q.e1 < 1) return FTB_E_ARG;
+    if (!q.tok || !q.table || !q.out || q.e1 < 1 || q.rows1 < 1 || (q.e2 > 0 && q.rows2 < 1)) return FTB_E_ARG;
     if (q.e2 > 0 && (!q.tok2 || !q.table2)) return FTB_E_ARG;
     if (q.e3 > 0 && !q.extra) return FTB_E_ARG;
     if (q.round_tf32 < 0 || q.round_tf32 > 3) return FTB_E_ARG;
@@ -182,7 +193,7 @@ extern "C" int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int ni
   const long long rows = static_cast<long long>(batch) * T;
   if (rows > 0x7fffffffll) return FTB_E_ARG;
   embed_batch_kernel<<<dim3(static_cast<unsigned>((rows + 7) / 8), nitems), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      args, batch, T, seq_stride);
+      args, batch, T, seq_stride, h->err_word);
   h->launches += 1;
   return static_cast<int>(cudaGetLastError());
 }

@@ -29,6 +29,8 @@ F16_OPERANDS = _F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
 # W_hh, exact gates): raw duration error ~1e-5 instead of ~3e-3, so the rounded durations (common_layers.py:21) match
 # the reference's except within ~1e-4 of a .5 tie.  FTB_PRECISE_DUR=0 restores the single-fp16 path (diagnostic).
 PRECISE_DUR = os.environ.get('FTB_PRECISE_DUR', '1') != '0'
+# FFT-block attention on the tensor cores with split-precision operands (ftb_attn.cu); FTB_TC_ATTENTION=0: fp32 SIMT kernel
+TC_ATTENTION = os.environ.get('FTB_TC_ATTENTION', '1') != '0'
 # pre_highway -> highways -> W_ih of a CBHG as ONE persistent kernel (ftb_tail.cu) instead of six GEMM launches
 FUSED_TAIL = os.environ.get('FTB_FUSED_TAIL', '1') != '0'
 

@@ -202,6 +202,10 @@ def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
     if scan_hook is not None:
         scan_hook(meta, lens)
     ev.synchronize()
+    if int(host[3]) != 0:
+        # what nn.Embedding raises in the reference (forward_tacotron.py:31,210) for an id outside its table; the
+        # kernels clamped the id instead of reading out of bounds, the outputs of this call are meaningless
+        raise IndexError('index out of range in self: a token / class id lies outside its embedding table')
     return cum, lens, int(host[0]), int(host[2])
 
 
@@ -281,7 +285,10 @@ def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torc
     opw, opdt = (3, torch.float16) if PR else (1, torch.float32)
     rmode = 3 if PR else True
     assert not PR or (x.dtype == torch.float16 and x.shape[1] == 3 * E and x_full is not None)
-    qkv = prog.buf(f'{tag}.qkv', 3 * E)
+    # head widths 64 / 128 (FastPitch): attention on the tensor cores (ftb_mha_split) over the in_proj output written as a
+    # split [hi | lo | hi] fp16 operand; other widths (MultiFastPitch: 192 / 196 / 256) keep the fp32 SIMT kernel
+    tc_attn = eng.TC_ATTENTION and (E // tp.heads) in (64, 128) and E % tp.heads == 0
+    qkv = prog.buf(f'{tag}.qkv16', 9 * E, torch.float16) if tc_attn else prog.buf(f'{tag}.qkv', 3 * E)
     att = prog.buf(f'{tag}.att', opw * E, opdt)
     y = prog.buf(f'{tag}.blk_y', E)
     x1 = prog.buf(f'{tag}.x1', opw * E, opdt)
@@ -306,9 +313,10 @@ def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torc
         dstf = None if i == n - 1 else xsf[1]
         last = tp.norm if i == n - 1 else (None, None)
         levels.append(named(f'l{i}.in_proj', lambda l=l, src=src: prog.gemm(src, l.in_proj, qkv, round_out=False,
-                                                                            split_in=PR)))
+                                                                            split_in=PR, split_out=tc_attn)))
         levels.append(lambda l=l: prog.call(
-            lambda: h.mha(qkv, E, tp.heads, key_tok, g.batch, g.seq_len, g.stride, att, round_tf32=rmode),
+            lambda: (h.mha_split if tc_attn else h.mha)(qkv, E, tp.heads, key_tok, g.batch, g.seq_len, g.stride, att,
+                                                        round_tf32=rmode),
             label=f'{tag}.mha', nbytes=4.0 * g.batch * g.seq_len * 4 * E))
         levels.append(named(f'l{i}.out_proj', lambda l=l, srcf=srcf: prog.gemm(att, l.out_proj, y, residual=srcf,
                                                                                round_out=False, split_in=PR)))

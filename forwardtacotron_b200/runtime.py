@@ -49,7 +49,7 @@ class EmbedItem(C.Structure):
     _fields_ = [('tok', _fp), ('table', _fp), ('e1', C.c_int32),
                 ('tok2', _fp), ('table2', _fp), ('e2', C.c_int32),
                 ('extra', _fp), ('e3', C.c_int32),
-                ('out', _fp), ('out_ld', C.c_int32), ('round_tf32', C.c_int32)]
+                ('out', _fp), ('out_ld', C.c_int32), ('round_tf32', C.c_int32), ('rows1', C.c_int32), ('rows2', C.c_int32)]
 
 
 class RowdotItem(C.Structure):
@@ -81,7 +81,7 @@ SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
            'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
-           'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha']
+           'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha', 'ftb_mha_split']
 
 _lib = None
 
@@ -121,15 +121,16 @@ def load_library() -> C.CDLL:
     lib.ftb_lr_regulate_static.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
                                            _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_embed.argtypes = [_fp, _fp, _fp, C.c_int, _fp, _fp, C.c_int, _fp, C.c_int,
-                              C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, _fp]
+                              C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, C.c_int, _fp]
     lib.ftb_rowdot.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, _fp, C.c_int, C.c_float,
                                C.c_int, C.c_int, C.c_int, _fp, _fp]
     lib.ftb_argmax_lastdim.argtypes = [_fp, _fp, C.c_int64, C.c_int, _fp, _fp]
     lib.ftb_add_layernorm.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp,
                                       C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int, _fp]
     lib.ftb_posenc.argtypes = [_fp, _fp, _fp, _fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
-                               _fp, _fp, C.c_int, _fp]
+                               _fp, _fp, C.c_int, C.c_int, _fp]
     lib.ftb_mha.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
+    lib.ftb_mha_split.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
     _lib = lib
     return lib
 
@@ -269,7 +270,8 @@ class Handle:
         # split fp16 [hi | lo | hi] / fp16 operand copy / tf32-rounded / as stored
         mode = 3 if int(round_tf32) == 3 else (2 if out.dtype == torch.float16 else int(round_tf32))
         self.check(self.lib.ftb_embed(self.h, ptr(tok), ptr(table), e1, ptr(tok2), ptr(table2), e2, ptr(extra), e3,
-                                      batch, T, stride, ptr(out), out_ld, mode, self.stream()))
+                                      batch, T, stride, ptr(out), out_ld, mode, table.shape[0],
+                                      table2.shape[0] if table2 is not None else 0, self.stream()))
 
     def embed_batch(self, items, batch, T, stride):
         """items: [(tok, table, out, tok2, table2, extra, round_tf32)] -> ONE launch (include/ftb200.h: ftb_embed_batch)."""
@@ -280,6 +282,7 @@ class Handle:
             a.extra, a.e3 = ptr(extra), (extra.shape[1] if extra is not None else 0)
             a.out, a.out_ld = ptr(out), out.shape[1]
             a.round_tf32 = 3 if int(round_tf32) == 3 else (2 if out.dtype == torch.float16 else int(round_tf32))
+            a.rows1, a.rows2 = table.shape[0], (table2.shape[0] if table2 is not None else 0)
         self.check(self.lib.ftb_embed_batch(self.h, arr, len(items), batch, T, stride, self.stream()))
 
     def rowdot_batch(self, items, batch, T, stride):
@@ -304,7 +307,13 @@ class Handle:
 
     def posenc(self, tok, table, x_in, pe, scale, e, batch, L, stride, out, round_tf32=True, out_full=None):
         self.check(self.lib.ftb_posenc(self.h, ptr(tok), ptr(table), ptr(x_in), ptr(pe), ptr(scale), e, batch, L,
-                                       stride, ptr(out), ptr(out_full), int(round_tf32), self.stream()))
+                                       stride, ptr(out), ptr(out_full), int(round_tf32),
+                                       table.shape[0] if table is not None else 0, self.stream()))
+
+    def mha_split(self, qkv16, e, heads, key_tok, batch, L, stride, out, round_tf32=True):
+        """Tensor-core attention on the split in_proj output (include/ftb200.h: ftb_mha_split)."""
+        self.check(self.lib.ftb_mha_split(self.h, ptr(qkv16), e, heads, ptr(key_tok), batch, L, stride, ptr(out),
+                                          int(round_tf32), self.stream()))
 
     def mha(self, qkv, e, heads, key_tok, batch, L, stride, out, round_tf32=True):
         self.check(self.lib.ftb_mha(self.h, ptr(qkv), e, heads, ptr(key_tok), batch, L, stride, ptr(out),

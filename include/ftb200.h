@@ -229,7 +229,9 @@ int ftb_rnn_plan_set_geometry(ftb_handle h, int plan, int seq_len, int seq_strid
  * ftb_lr_scan : clamps dur in place (dur[dur<0]=0), applies the batch-global fallback,
  *               rep = trunc(dur + 0.5f) (fp32 add), per-sentence inclusive scan.
  *               Outputs cum [batch, T] int32, lens [batch] int32, and meta[0] = max len,
- *               meta[1] = fallback flag, meta[2] = total frames (host reads meta once).
+ *               meta[1] = fallback flag, meta[2] = total frames, meta[3] = the handle's error word (bit 0: an
+ *               embedding kernel since the last scan saw an id outside its table -- nn.Embedding raises IndexError
+ *               there; the kernels clamp the id to row 0 instead of reading out of bounds) (host reads meta once).
  * ftb_lr_gather: out[b*out_stride + m, :] = src(b, idx) for m < lens[b], where
  *               src(b,t) = x[b*x_stride + t, :C1] ++ extra[b, :C2]  (speaker embedding tail)
  *                          + ps*(wp (*) pitch)[t] + es*(we (*) energy)[t]   (3-tap, zero padded)
@@ -291,7 +293,8 @@ int ftb_lr_regulate_static(ftb_handle h, const float* x, int x_stride /*rows per
 int ftb_embed(ftb_handle h, const int64_t* tok, const float* table, int e1,
               const int64_t* tok2, const float* table2, int e2,
               const float* extra, int e3,
-              int batch, int T, int seq_stride, float* out, int out_ld, int round_tf32, void* stream);
+              int batch, int T, int seq_stride, float* out, int out_ld, int round_tf32,
+              int rows1 /* rows of table */, int rows2 /* rows of table2 */, void* stream);
 
 /* Predictor head: y[b,t,o] = (dot(x[b*seq_stride+t, :k], w[o,:]) + bias[o]) / alpha
  * (self.lin + `/ alpha`, forward_tacotron.py:38-39).  n_out <= 4.  y is dense [batch, T, n_out]. */
@@ -309,6 +312,7 @@ typedef struct {
   const float* extra; int32_t e3;
   float* out; int32_t out_ld;
   int32_t round_tf32;      /* as ftb_embed */
+  int32_t rows1, rows2;    /* rows of table / table2: ids outside [0, rows) set the error word (ftb_lr_scan meta[3]) */
 } ftb_embed_item;
 int ftb_embed_batch(ftb_handle h, const ftb_embed_item* items, int nitems, int batch, int T, int seq_stride, void* stream);
 
@@ -342,12 +346,21 @@ int ftb_add_layernorm(ftb_handle h, const float* x, const float* res, int ld, in
  * tok == null: in-place x += scale*pe over an existing activation (post-LR postnet input). */
 int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, const float* x_in, const float* pe,
                const float* scale_ptr, int e, int batch, int seq_len, int seq_stride,
-               float* out, float* out_full, int round_tf32, void* stream);
+               float* out, float* out_full, int round_tf32, int table_rows /* rows of `table` (ids are checked) */,
+               void* stream);
 
 /* 2..8-head self attention over qkv [rows, 3e] (packed in_proj output), softmax over keys with
  * optional key padding (tok[b,s] == 0 masked, common_layers.py:232-233); out [rows, e]. */
 int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const int64_t* key_tok,
             int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
+
+/* The same attention on the TENSOR CORES with split-precision operands (head width 64 or 128, else FTB_E_SHAPE -> use
+ * ftb_mha): qkv16 is the in_proj output as written by a FTB_F_OUT_SPLIT problem, fp16 [rows, 9e] = [hi | lo | hi] column
+ * blocks of width 3e; both contractions run as three fp16 mma.sync products on hi / lo pairs (Qh Kh + Qh Kl + Ql Kh,
+ * Ph Vh + Ph Vl + Pl Vh) with fp32 accumulation and an fp32 online softmax, i.e. ~2^-20 relative operand precision --
+ * FastPitch's parity margin does not allow single-pass fp16 / tf32 scores.  out / round_tf32 as ftb_mha. */
+int ftb_mha_split(ftb_handle h, const void* qkv16, int e, int heads, const int64_t* key_tok,
+                  int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
 
 #ifdef __cplusplus
 }

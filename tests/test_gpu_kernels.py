@@ -809,3 +809,40 @@ def test_cbhg_tail_fused_matches_unfused_chain(B, L, cin, x16, monkeypatch):
     assert max_abs(outs[True], ref) < tol * max(1.0, float(ref.abs().max())), max_abs(outs[True], ref)
     assert max_abs(outs[False], ref) < tol * max(1.0, float(ref.abs().max()))
     assert max_abs(outs[True], outs[False]) < tol * max(1.0, float(ref.abs().max()))
+
+
+@pytest.mark.parametrize('D,heads,B,L,masked', [(64, 2, 3, 70, True), (128, 2, 2, 130, False), (128, 2, 2, 333, True),
+                                                (64, 2, 1, 64, False)])
+def test_mha_tensor_core_split_precision(D, heads, B, L, masked):
+    """ftb_mha_split (mma.sync on hi / lo fp16 operand pairs, fp32 online softmax) against float64 attention on operands
+    that are NOT pre-rounded: 3e-6 -- a single-fp16 product of the same operands is off by ~1e-3."""
+    E = D * heads
+    gen = torch.Generator().manual_seed(D + L)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    qkv = torch.randn(B, L, 3 * E, generator=gen) * 1.5
+    buf = prog.buf('qkv16', 9 * E, torch.float16)
+    buf.view(g.batch, g.stride, 9 * E)[:, :L] = _split3(qkv).to(DEV)
+    out = prog.buf('att', E)
+    out3 = prog.buf('att3', 3 * E, torch.float16)
+    tok = None
+    if masked:
+        tok = torch.randint(1, 50, (B, L), generator=gen)
+        for b in range(B):
+            tok[b, L - 3 * b - 2:] = 0
+        tok = tok.to(DEV)
+    h = _handle()
+    h.mha_split(buf, E, heads, tok, B, L, g.stride, out, round_tf32=False)
+    h.mha_split(buf, E, heads, tok, B, L, g.stride, out3, round_tf32=3)
+    torch.cuda.synchronize()
+    q, k, v = [t.double().view(B, L, heads, D).transpose(1, 2) for t in qkv.chunk(3, dim=-1)]
+    s = q @ k.transpose(-1, -2) / D ** 0.5
+    if masked:
+        s = s.masked_fill((tok.cpu() == 0)[:, None, None, :], float('-inf'))
+    ref = (torch.softmax(s, dim=-1) @ v).transpose(1, 2).reshape(B, L, E)
+    got = prog.view('att').cpu().double()
+    assert max_abs(got, ref) < 3e-6 * max(1.0, float(ref.abs().max())), max_abs(got, ref)
+    o3 = prog.view('att3').cpu()
+    assert torch.equal(o3[..., :E], o3[..., 2 * E:])
+    assert max_abs(o3[..., :E].double() + o3[..., E:2 * E].double(), ref) < 4e-6 * max(1.0, float(ref.abs().max()))
+    assert float(out.view(g.batch, g.stride, -1)[:, L:].abs().max()) == 0.0

@@ -436,3 +436,20 @@ def test_generate_reuses_programs_across_lengths():
         progs = model.__dict__['_accel']['programs']
     assert sum(1 for k in progs if k[0] == 'tok') == 1
     assert sum(1 for k in progs if k[0] == 'frame') <= 3
+
+
+@pytest.mark.parametrize('tag', ['forward_tacotron', 'fast_pitch'])
+def test_token_ids_outside_the_embedding_table_raise(tag):
+    """nn.Embedding raises IndexError for an id outside [0, num_chars); the kernels clamp the id (no
+    out-of-bounds read) and flag it, generate() raises the reference's exception -- and the next, valid call is clean."""
+    model = _model(tag, synthetic_sd(tag, 1))
+    good = synth.synth_tokens(2, 19, seed=1).to(DEV)
+    for bad_id in (135, 10 ** 6, -1):
+        bad = good.clone()
+        bad[1, 7] = bad_id
+        with pytest.raises(IndexError):
+            model.generate(bad)
+    a = model.generate(good)
+    b = model.generate(good)
+    torch.cuda.synchronize()
+    assert torch.equal(a['mel_post'], b['mel_post']) and bool(torch.isfinite(a['mel_post']).all())
