@@ -81,7 +81,7 @@ SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
            'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
-           'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha', 'ftb_mha_split']
+           'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha', 'ftb_mha_split', 'ftb_stft', 'ftb_istft', 'ftb_gl_update']
 
 _lib = None
 
@@ -131,6 +131,9 @@ def load_library() -> C.CDLL:
                                _fp, _fp, C.c_int, C.c_int, _fp]
     lib.ftb_mha.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
     lib.ftb_mha_split.argtypes = [_fp, _fp, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, _fp]
+    lib.ftb_stft.argtypes = [_fp, _fp, C.c_int, C.c_int64, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp]
+    lib.ftb_istft.argtypes = [_fp, _fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp, C.c_int64, _fp]
+    lib.ftb_gl_update.argtypes = [_fp, _fp, _fp, _fp, _fp, C.c_int64, C.c_float, _fp]
     _lib = lib
     return lib
 
@@ -309,6 +312,18 @@ class Handle:
         self.check(self.lib.ftb_posenc(self.h, ptr(tok), ptr(table), ptr(x_in), ptr(pe), ptr(scale), e, batch, L,
                                        stride, ptr(out), ptr(out_full), int(round_tf32),
                                        table.shape[0] if table is not None else 0, self.stream()))
+
+    def stft(self, y, y_len, window, tw, n_fft, hop, frames, spec):
+        self.check(self.lib.ftb_stft(self.h, ptr(y), y_len, y.shape[1], ptr(window), ptr(tw), n_fft, hop, y.shape[0],
+                                     frames, ptr(spec), self.stream()))
+
+    def istft(self, spec, window, tw, n_fft, hop, frames, frame_buf, y):
+        self.check(self.lib.ftb_istft(self.h, ptr(spec), ptr(window), ptr(tw), n_fft, hop, y.shape[0], frames,
+                                      ptr(frame_buf), ptr(y), y.shape[1], self.stream()))
+
+    def gl_update(self, mag, rebuilt, tprev, nxt, momentum):
+        self.check(self.lib.ftb_gl_update(self.h, ptr(mag), ptr(rebuilt), ptr(tprev), ptr(nxt), mag.numel(),
+                                          float(momentum), self.stream()))
 
     def mha_split(self, qkv16, e, heads, key_tok, batch, L, stride, out, round_tf32=True):
         """Tensor-core attention on the split in_proj output (include/ftb200.h: ftb_mha_split)."""

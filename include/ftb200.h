@@ -362,6 +362,27 @@ int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const int64_t* key
 int ftb_mha_split(ftb_handle h, const void* qkv16, int e, int heads, const int64_t* key_tok,
                   int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * K9  mel -> waveform: the transforms of fast Griffin-Lim
+ *
+ * Replaces: the loop of librosa.core.griffinlim as called by DSP.griffinlim (utils/dsp.py:89-93: n_iter = 32,
+ * hop_length, win_length = n_fft = 1024, librosa defaults momentum 0.99 / Hann window / centred frames).  librosa is a
+ * third-party dependency that is absent from /root/reference; the entries restate its published algorithm.
+ *   window    fp32 [n_fft] (periodic Hann); twiddles fp32 [n_fft/2][2] = exp(-2 pi i k / n_fft)
+ *   ftb_stft  y [batch, y_stride] (valid samples [0, y_len)), centred frames, zero padding -> spec [batch, frames,
+ *             n_fft/2 + 1][2] (interleaved complex)
+ *   ftb_istft spec -> window * irfft per frame (frame_buf [batch, frames, n_fft], scratch) -> overlap-add, divided by
+ *             the window sum-square, trimmed to hop * (frames - 1) samples -> y [batch, y_stride]
+ *   ftb_gl_update  a = rebuilt - momentum/(1+momentum) * tprev; a /= |a| + tiny; next = mag * a; tprev <- rebuilt
+ * n_fft: a power of two in [64, 2048].
+ * ------------------------------------------------------------------------------------ */
+int ftb_stft(ftb_handle h, const float* y, int y_len, int64_t y_stride, const float* window, const float* twiddles,
+             int n_fft, int hop, int batch, int frames, float* spec, void* stream);
+int ftb_istft(ftb_handle h, const float* spec, const float* window, const float* twiddles, int n_fft, int hop,
+              int batch, int frames, float* frame_buf, float* y, int64_t y_stride, void* stream);
+int ftb_gl_update(ftb_handle h, const float* mag, const float* rebuilt, float* tprev, float* next, int64_t count,
+                  float momentum, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
