@@ -271,6 +271,10 @@ def run_ours(args, rank, world, local_rank):
         semb = make_speaker(w['batch'])[sl].contiguous().to(dev) if multi else None
     x_dev = x_pin.to(dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+    # --vary: a different token batch on every step (8 in rotation), so with spread durations the regulated length M
+    # changes from call to call like it does with real text (the cached-shape replay is the best case)
+    pool = [make_tokens(B, T, rank, step=i).to(dev) for i in range(8)] if args.vary else None
+    seen_m, calls = set(), [0]
 
     def generate(x):
         return model.generate(x, semb, alpha=alpha) if multi else model.generate(x, alpha=alpha)
@@ -284,6 +288,13 @@ def run_ours(args, rank, world, local_rank):
         out = generate(x_dev)
     torch.cuda.synchronize(dev)
     frames = int((out['dur'] + 0.5).long().sum())                        # valid mel frames per step (this rank)
+    if pool is not None:       # every batch of the rotation once (builds / re-points the programs); frames = their mean
+        fl = []
+        for xb in pool:
+            o = generate(xb)
+            fl.append(int((o['dur'] + 0.5).long().sum()))
+        torch.cuda.synchronize(dev)
+        frames = sum(fl) / len(fl)
     M = out['mel'].shape[2]
     host_out = torch.empty(out['mel_post'].shape, dtype=torch.float32).pin_memory()
     b_cap = w['batch'] if w['scaling'] == 'weak' else -(-w['batch'] // world)
@@ -306,7 +317,12 @@ def run_ours(args, rank, world, local_rank):
         return float(t.item())
 
     def step_resident():
-        generate(x_dev)
+        if pool is None:
+            generate(x_dev)
+        else:
+            o = generate(pool[calls[0] % len(pool)])
+            calls[0] += 1
+            seen_m.add(o['mel'].shape[2])
 
     exchange = par.LengthExchange(dev) if world > 1 else None
     d2h_stream = torch.cuda.Stream(dev) if world > 1 else None
@@ -501,6 +517,8 @@ def run_ours(args, rank, world, local_rank):
                     'host_cpus_rank0': numa},
             'e2e': {'value': total_frames * args.steps / (ms_e2e / 1e3), 'unit': UNIT,
                     'h2d_bytes_per_step': x_pin.numel() * 8, 'd2h_bytes_per_step': host_out.numel() * 4},
+            'inputs': ('one token batch replayed every step' if pool is None else
+                       f'8 token batches in rotation (--vary): regulated lengths seen {sorted(seen_m)}'),
             'gpu_launches': int(launches), 'clocks': clk, 'roofline': roof, 'roofline_by_kernel': by_kernel,
             'kernel_ms_sum': round(sum(k['ms'] for k, _ in kernels), 4),
             'kernels': [k for k, _ in kernels]}
@@ -524,6 +542,8 @@ def main():
                     help="'fallback': as-is random init -> every duration 2 (forward_tacotron.py:176-177); "
                          "'spread': duration head shifted so durations vary (SURVEY §8d regime B)")
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--vary', action='store_true',
+                    help='a different token batch every step (with --durations spread the regulated length M varies)')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))

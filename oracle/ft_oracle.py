@@ -121,8 +121,8 @@ def batch_norm_conv(sd: SD, p: str, x: torch.Tensor, relu: bool) -> torch.Tensor
         y = F.relu(y)
     mean, var = sd[p + '.bnorm.running_mean'], sd[p + '.bnorm.running_var']
     gamma, beta = sd[p + '.bnorm.weight'], sd[p + '.bnorm.bias']
-    scale = gamma / torch.sqrt(var + 1e-5)
-    return (y - mean[None, :, None]) * scale[None, :, None] + beta[None, :, None]
+    # nn.BatchNorm1d in eval mode (common_layers.py:57): the same fused ATen op the reference's module calls
+    return F.batch_norm(y, mean, var, gamma, beta, False, 0.0, 1e-5)
 
 
 def highway(sd: SD, p: str, x: torch.Tensor) -> torch.Tensor:

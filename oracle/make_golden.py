@@ -266,5 +266,7 @@ if __name__ == '__main__':
         mfp_case('mfp_pad_b3_t28', 3, 28, seed=9, patched=True, with_pad=True, alpha=1.25)
         ft_forward_case('ft_forward_b4_t26', 4, 26, seed=10)
         fp_forward_case('fp_forward_b4_t26', 4, 26, seed=11)
+        mft_forward_case('mft_forward_b4_t26', 4, 26, seed=12)
+        mfp_forward_case('mfp_forward_b4_t26', 4, 26, seed=13)
     with open(os.path.join(OUT, 'PROVENANCE.txt'), 'w') as f:
         f.write(f'generated by oracle/make_golden.py from {REF}\ntorch {torch.__version__}\n')

@@ -846,3 +846,49 @@ def test_mha_tensor_core_split_precision(D, heads, B, L, masked):
     assert torch.equal(o3[..., :E], o3[..., 2 * E:])
     assert max_abs(o3[..., :E].double() + o3[..., E:2 * E].double(), ref) < 4e-6 * max(1.0, float(ref.abs().max()))
     assert float(out.view(g.batch, g.stride, -1)[:, L:].abs().max()) == 0.0
+
+
+def test_length_regulator_projection_branch_vs_oracle():
+    """K6 fused into K5's source read (a.pitch != null): x + ps * Conv1d(1->C,3)(pitch) + es * Conv1d(1->C,3)(energy)
+    (forward_tacotron.py:214-220) with the speaker tail appended (multi_forward_tacotron.py:280-282), then the gather --
+    against the oracle's cond_projection + LengthRegulator on the same tensors, plus the idx / pad-row contract."""
+    B, T, C1, C2 = 5, 37, 64, 16
+    gen = torch.Generator().manual_seed(12)
+    x = torch.randn(B, T, C1, generator=gen)
+    extra = torch.randn(B, C2, generator=gen)
+    pitch, energy = torch.randn(B, T, generator=gen), torch.randn(B, T, generator=gen)
+    C = C1 + C2
+    sd = {'p.weight': torch.randn(C, 1, 3, generator=gen) * 0.3, 'p.bias': torch.randn(C, generator=gen) * 0.1,
+          'e.weight': torch.randn(C, 1, 3, generator=gen) * 0.3, 'e.bias': torch.randn(C, generator=gen) * 0.1}
+    ps, es = 0.7, 1.3
+    dur = torch.rand(B, T, generator=gen) * 4 - 0.5
+    h = _handle()
+    dd = dur.to(DEV).contiguous()
+    cum = torch.empty((B, T), dtype=torch.int32, device=DEV)
+    lens = torch.empty((B,), dtype=torch.int32, device=DEV)
+    meta = torch.empty((4,), dtype=torch.int32, device=DEV)
+    h.lr_scan(dd, B, T, False, cum, lens, meta)
+    M = int(meta.cpu()[0])
+    out = torch.full((B, M, C), 7.0, device=DEV)
+    idx = torch.empty((B, M), dtype=torch.int32, device=DEV)
+    keep = [t.to(DEV).contiguous() for t in (x, extra, pitch, energy, sd['p.weight'].reshape(C, 3), sd['p.bias'],
+                                             sd['e.weight'].reshape(C, 3), sd['e.bias'])]
+    a = rt.LrGatherArgs()
+    a.x, a.x_stride, a.x_ld, a.c1 = keep[0].data_ptr(), T, C1, C1
+    a.extra, a.c2 = keep[1].data_ptr(), C2
+    a.pitch, a.energy = keep[2].data_ptr(), keep[3].data_ptr()
+    a.wp, a.bp, a.ps = keep[4].data_ptr(), keep[5].data_ptr(), ps
+    a.we, a.be, a.es = keep[6].data_ptr(), keep[7].data_ptr(), es
+    a.cum, a.lens, a.batch, a.T, a.M = cum.data_ptr(), lens.data_ptr(), B, T, M
+    a.out, a.out_stride, a.out_ld, a.idx, a.round_tf32 = out.data_ptr(), M, C, idx.data_ptr(), 0
+    h.lr_gather(a)
+    torch.cuda.synchronize()
+    src = torch.cat([x, extra[:, None, :].expand(-1, T, -1)], dim=2)
+    src = src + O.cond_projection(sd, 'p', pitch[:, None, :]) * ps + O.cond_projection(sd, 'e', energy[:, None, :]) * es
+    ref, idx_ref, lens_ref, _ = O.length_regulate_np(src.numpy(), dur.numpy())
+    assert ref.shape == (B, M, C)
+    assert np.array_equal(idx.cpu().numpy(), idx_ref) and np.array_equal(lens.cpu().numpy(), lens_ref)
+    got = out.cpu().numpy()
+    assert np.abs(got - ref).max() < 2e-6                     # fp32 adds in the reference's order; conv summation order may differ
+    for b in range(B):
+        assert np.all(got[b, lens_ref[b]:] == 0.0)
