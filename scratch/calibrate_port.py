@@ -25,19 +25,24 @@ ref = ForwardTacotron(num_chars=135, n_mels=80, **kw).eval()
 ref.load_state_dict(sd)
 
 
-def timed(fn, n=3):
-    fn()
-    ts = []
-    for _ in range(n):
-        t0 = time.perf_counter(); out = fn(); ts.append(time.perf_counter() - t0)
-    return out, sum(ts) / len(ts)
+def once(fn):
+    t0 = time.perf_counter()
+    out = fn()
+    return out, time.perf_counter() - t0
 
 
+# The two programs ALTERNATE (port, reference, port, ...): timing one after the other in blocks picks up the drift of a
+# shared host (a first version of this script reported 1.56x for what alternation shows to be 1.0x).
 O.use_library_rnn(True)
-o_port, t_port = timed(lambda: O.ft_generate(sd, x))
-O.use_library_rnn(False)
+tp, tr = [], []
 with torch.no_grad():
-    o_ref, t_ref = timed(lambda: ref.generate(x))
+    once(lambda: O.ft_generate(sd, x)); once(lambda: ref.generate(x))          # warm-up
+    for _ in range(5):
+        o_port, a = once(lambda: O.ft_generate(sd, x))
+        o_ref, b = once(lambda: ref.generate(x))
+        tp.append(a); tr.append(b)
+O.use_library_rnn(False)
+t_port, t_ref = sum(tp) / len(tp), sum(tr) / len(tr)
 frames = int(o_port['mel_lens'].sum())
 err = float((o_port['mel_post'] - o_ref['mel_post']).abs().max())
 print(f'batch {batch} x 200, {threads} threads: reference generate() {t_ref * 1e3:.1f} ms ({frames / t_ref:.0f} frames/s), '
