@@ -713,7 +713,9 @@ __device__ __forceinline__ float simt_acc(const GemmProblemDev* p, long long r, 
   float acc = 0.0f;
   for (int tap = 0; tap < p->taps; ++tap) {
     const long long ra = r + p->tap0 + tap;
-    if (ra < 0 || ra >= p->rows) continue;
+    // (folded problems, FTB_F_TAPS_IN_K: `a` starts FTB_FOLD_LEAD_ROWS zero rows early, tap0 is shifted by as much, and
+    //  the single tap walks taps*cin contiguous elements = the original rows, so the same loop below covers them)
+    if (ra < 0 || ra >= p->rows + ((p->flags & FTB_F_TAPS_IN_K) ? FTB_FOLD_LEAD_ROWS : 0)) continue;
     if (p->flags & FTB_F_A_F16) {
       const __half* a = reinterpret_cast<const __half*>(p->a) + ra * p->lda;
       const __half* w = reinterpret_cast<const __half*>(p->w) + (static_cast<long long>(tap) * p->w_tap_rows + wrow) * p->cin;
@@ -817,7 +819,7 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
       const int kel = (q.flags & FTB_F_A_F16) ? 2 * BK : BK;
       const double t = static_cast<double>((q.rows + BM - 1) / BM) * ((q.n + q.bn - 1) / q.bn);
       tiles += t;
-      kiters += t * q.taps * ((q.cin + kel - 1) / kel);
+      kiters += t * ((q.flags & FTB_F_TAPS_IN_K) ? (q.taps * q.cin + kel - 1) / kel : q.taps * ((q.cin + kel - 1) / kel));
     }
     pair = tiles > 0.0 && kiters / tiles >= GEMM_PAIR_MIN_KITERS;
   }
@@ -851,6 +853,8 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     } else if (q.epilogue != FTB_EPI_AFFINE && q.epilogue != FTB_EPI_MAXPOOL) {
       return FTB_E_ARG;
     }
+    const bool fold = (q.flags & FTB_F_TAPS_IN_K) != 0;
+    if (fold && (!a16 || q.lda != q.cin || q.taps > FTB_FOLD_LEAD_ROWS || q.tap0 < -FTB_FOLD_LEAD_ROWS || q.tap0 > 0)) return FTB_E_ARG;
     d.a = static_cast<const float*>(q.a); d.w = static_cast<const float*>(q.w); d.bias0 = q.bias0; d.scale = q.scale; d.shift = q.shift;
     d.residual = q.residual; d.out = static_cast<float*>(q.out); d.out_t = q.out_t; d.out_full = q.out_full;
     if (q.out_full && (!q.out || !aligned16(q.out_full))) return FTB_E_ALIGN;
@@ -870,10 +874,30 @@ int gemm_plan_build(const ftb_gemm_problem* problems, int nproblems, GemmPlan* p
     d.cap_rows = q.rows;
     d.tile_base = tile_base;
     tile_base += (pair ? (d.m_tiles + 1) / 2 : d.m_tiles) * d.n_tiles;
-    int rc = tensor_map_2d(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
-    if (rc) return rc;
-    rc = tensor_map_2d(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, pair ? q.bn / 2 : q.bn, a16);
-    if (rc) return rc;
+    int rc;
+    if (fold) {
+      // Taps folded into K (FTB_F_TAPS_IN_K): ONE tap over an overlapping-row view of A.  Virtual row v starts at real row
+      // v - LEAD of `a` (the LEAD zero rows in front of `a` make v >= 0 for every output row) and extends over taps*cin
+      // contiguous elements, i.e. the real rows v - LEAD .. v - LEAD + taps - 1; columns past taps*cin and virtual rows
+      // past the end are zero-filled by TMA, and the rows behind the last sentence are gap rows (zero) anyway.
+      const int kext = q.taps * q.cin;
+      const __half* base = static_cast<const __half*>(q.a) - static_cast<long long>(FTB_FOLD_LEAD_ROWS) * q.lda;
+      d.a = reinterpret_cast<const float*>(base);
+      d.tap0 = q.tap0 + FTB_FOLD_LEAD_ROWS;
+      d.taps = 1;
+      d.cin = kext;
+      d.kblocks = (kext + d.kelems - 1) / d.kelems;
+      d.lda = q.lda;                                  // real row pitch (the SIMT cross-check walks the same memory)
+      rc = tensor_map_2d(&d.tm_a, base, q.rows + FTB_FOLD_LEAD_ROWS - q.taps + 1, kext, q.lda, BM, true);
+      if (rc) return rc;
+      rc = tensor_map_2d(&d.tm_w, q.w, q.w_tap_rows, kext, kext, pair ? q.bn / 2 : q.bn, true);
+      if (rc) return rc;
+    } else {
+      rc = tensor_map_2d(&d.tm_a, q.a, q.rows, q.cin, q.lda, BM, a16);
+      if (rc) return rc;
+      rc = tensor_map_2d(&d.tm_w, q.w, static_cast<long long>(q.taps) * q.w_tap_rows, q.cin, q.cin, pair ? q.bn / 2 : q.bn, a16);
+      if (rc) return rc;
+    }
     const long long e = q.rows * q.n;
     if (e > simt_elems) simt_elems = e;
   }

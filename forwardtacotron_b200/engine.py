@@ -29,10 +29,16 @@ F16_OPERANDS = _F16_OPERANDS = os.environ.get('FTB_F16_OPERANDS', '1') != '0'
 # W_hh, exact gates): raw duration error ~1e-5 instead of ~3e-3, so the rounded durations (common_layers.py:21) match
 # the reference's except within ~1e-4 of a .5 tie.  FTB_PRECISE_DUR=0 restores the single-fp16 path (diagnostic).
 PRECISE_DUR = os.environ.get('FTB_PRECISE_DUR', '1') != '0'
+# Debug guard: after every program of generate() / forward(), check the activation buffers for inf / NaN and for fp16
+# operand copies near the end of fp16's range (Program.check_range; synchronises, off by default)
+CHECK_RANGE = os.environ.get('FTB_CHECK_RANGE', '0') == '1'
 # FFT-block attention on the tensor cores with split-precision operands (ftb_attn.cu); FTB_TC_ATTENTION=0: fp32 SIMT kernel
 TC_ATTENTION = os.environ.get('FTB_TC_ATTENTION', '1') != '0'
 # pre_highway -> highways -> W_ih of a CBHG as ONE persistent kernel (ftb_tail.cu) instead of six GEMM launches
 FUSED_TAIL = os.environ.get('FTB_FUSED_TAIL', '1') != '0'
+# taps folded into the reduction for convolutions over a channel count that fills a 128-byte swizzle row badly (the
+# postnet bank over the 80-channel mel: 48 k-blocks instead of 72, FTB_F_TAPS_IN_K); FTB_FOLD_TAPS=0 disables
+FOLD_TAPS = os.environ.get('FTB_FOLD_TAPS', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -40,7 +46,8 @@ def _tile_cost(q) -> float:
     each for kind::tf32) against the epilogue of its bn/32 chunks (two warp sets drain alternate tiles), plus the
     per-tile fixed cost."""
     kelems = 64 if (q.flags & rt.F_A_F16) else 32           # channels per 128-byte k-block
-    mma = q.taps * ((q.cin + kelems - 1) // kelems) * 2.0 * q.bn
+    kblocks = (q.taps * q.cin + kelems - 1) // kelems if (q.flags & rt.F_TAPS_IN_K) else q.taps * ((q.cin + kelems - 1) // kelems)
+    mma = kblocks * 2.0 * q.bn
     epi = (q.bn / 32.0) * 1800.0 / 2.0
     return max(mma, epi) + 1500.0
 
@@ -109,6 +116,7 @@ class Program:
         self._pending: List[rt.GemmProblem] = []
         self._glue: list = []                         # queued embeddings / predictor heads: one batched launch per kind
         self._keep: list = []                         # tensors the plans point into
+        self._lead: Dict[int, int] = {}               # data_ptr of a padded-flat buffer -> zero rows in front of it
         self.info: List[dict] = []                    # per step: kind, label, algorithmic flops / bytes
         self._label = ''
         # CUDA graph of the launch list: captured on the second run() (the first one runs eagerly so one-time
@@ -119,11 +127,14 @@ class Program:
         self._eager_runs = 0
 
     # ---- buffers ---------------------------------------------------------------------------
-    def buf(self, name: str, cols: int, dtype=torch.float32) -> torch.Tensor:
+    def buf(self, name: str, cols: int, dtype=torch.float32, lead: int = 0) -> torch.Tensor:
         """Zero-initialised [rows, cols] activation; gap rows are never written so they stay zero.  fp16 buffers are
-        GEMM-to-GEMM operands (FTB_F_OUT_F16 producer, FTB_F_A_F16 consumer)."""
+        GEMM-to-GEMM operands (FTB_F_OUT_F16 producer, FTB_F_A_F16 consumer).  `lead`: zero rows kept IN FRONT of the
+        buffer in the same allocation (what a FTB_F_TAPS_IN_K consumer reads for the taps left of the first sentence)."""
         if name not in self.bufs:
-            self.bufs[name] = torch.zeros((self.geo.cap_rows, cols), dtype=dtype, device=self.device)
+            full = torch.zeros((lead + self.geo.cap_rows, cols), dtype=dtype, device=self.device)
+            self.bufs[name] = full[lead:]
+            self._lead[self.bufs[name].data_ptr()] = lead
             self._flat.append(name)
         b = self.bufs[name]
         assert b.shape[1] == cols and b.dtype == dtype, (name, b.shape, cols, b.dtype)
@@ -138,6 +149,21 @@ class Program:
             if -1 in shape:
                 self.bufs.dyn[name] = tuple(shape)
         return self.bufs[name]
+
+    def check_range(self, where: str = '') -> None:
+        """Debug guard (FTB_CHECK_RANGE=1, called by the models after a program ran; it synchronises): the fp16 operand
+        copies are stored without saturation, so a checkpoint whose activations leave fp16's range (|x| > 65504 -- unbounded
+        post-ReLU BatchNorm outputs can) turns into inf silently.  Raises naming the first buffer that holds a non-finite
+        value or has used more than ~90 % of the fp16 range (FTB_F16_OPERANDS=0 runs every layer on tf32 operands)."""
+        for name in self._flat:
+            b = dict.__getitem__(self.bufs, name)
+            v = b[:self.geo.rows]
+            if not bool(torch.isfinite(v).all()):
+                raise RuntimeError(f'{where}: activation buffer {name!r} ({b.dtype}) holds inf / NaN -- activations outside '
+                                   'the fp16 operand range?  FTB_F16_OPERANDS=0 keeps tf32 operands')
+            if b.dtype == torch.float16 and float(v.abs().max()) > 6.0e4:
+                raise RuntimeError(f'{where}: fp16 operand buffer {name!r} reaches |x| = {float(v.abs().max()):.3g} '
+                                   '(limit 65504): FTB_F16_OPERANDS=0 keeps tf32 operands')
 
     def view(self, name: str) -> torch.Tensor:
         """[batch, seq_len, C] view of a padded-flat buffer (valid rows only) at the current geometry."""
@@ -192,11 +218,18 @@ class Program:
             p.cin = cin if cin is not None else w.cin
             assert p.cin == w.cin and p.cin <= a.shape[1], (p.cin, w.cin, a.shape)
             wt = w.w16 if a16 else w.w
+        # taps folded into K: dense fp16 rows with zero lead rows in front, a channel count that wastes swizzle rows
+        fold = (FOLD_TAPS and a16 and not split_in and 1 < w.taps <= rt.FOLD_LEAD_ROWS and a.shape[1] == w.cin
+                and w.cin % 64 != 0 and self._lead.get(a.data_ptr(), 0) >= rt.FOLD_LEAD_ROWS
+                and -(-(w.taps * w.cin) // 64) < w.taps * -(-w.cin // 64))
+        if fold:
+            wt = w.w16f
         assert not split_out or (o16 and out.shape[1] % 24 == 0 and out_col0 + w.n <= out.shape[1] // 3)
         p.w, p.taps, p.tap0, p.w_tap_rows = wt.data_ptr(), w.taps, w.tap0, w.n_pad
         p.n, p.bn, p.epilogue = w.n, w.bn, epilogue
         p.flags = ((rt.F_RELU if w.relu else 0) | (rt.F_ROUND if round_out and not o16 else 0) |
-                   (rt.F_A_F16 if a16 else 0) | (rt.F_OUT_F16 if o16 else 0) | (rt.F_OUT_SPLIT if split_out else 0))
+                   (rt.F_A_F16 if a16 else 0) | (rt.F_OUT_F16 if o16 else 0) | (rt.F_OUT_SPLIT if split_out else 0) |
+                   (rt.F_TAPS_IN_K if fold else 0))
         assert not o16 or epilogue != rt.EPI_MAXPOOL or (residual is None and out_t is None and out_full is None)
         p.bias0, p.scale, p.shift = rt.ptr(w.bias0), rt.ptr(w.scale), rt.ptr(w.shift)
         assert residual is None or residual.dtype == torch.float32, 'the residual term reads the fp32 twin'
@@ -354,6 +387,9 @@ class Program:
         replay (a 20-launch program otherwise leaves the SMs idle between its short kernels)."""
         # baked into kernel arguments of a captured graph: launch-time scalars, and (glue kernels only -- the GEMM and
         # recurrence kernels read their geometry from the device records) the sequence length
+        if CHECK_RANGE:
+            self.run_eager()
+            return self.check_range('forwardtacotron_b200 (FTB_CHECK_RANGE=1)')
         key = (getattr(self, 'alpha', None), self.geo.seq_len if self._baked_len else None)
         if not self.use_graph:
             return self.run_eager()

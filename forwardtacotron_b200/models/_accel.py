@@ -54,6 +54,13 @@ class AcceleratedMixin:
             if st is not None:
                 for prog in list(st['programs'].values()):
                     prog.close()
+            # Some packs alias the parameters themselves (embedding tables, predictor heads, the pitch / energy
+            # projections) and the kernels read them with 16-byte vector loads: a parameter that is a view at an odd
+            # offset of a larger buffer would be read from the wrong address.  torch allocations are 512-byte aligned.
+            for name, t in list(self.named_parameters()) + list(self.named_buffers()):
+                if t.is_floating_point() and t.data_ptr() % 16:
+                    raise RuntimeError(f'parameter {name!r} is not 16-byte aligned (a view into a larger buffer?): '
+                                       'clone it or lay the buffer out in 16-byte steps')
             handle = rt.Handle.get(device)
             st = {'sig': sig, 'device': device, 'handle': handle, 'packs': self._build_packs(),
                   'programs': OrderedDict()}
@@ -112,7 +119,8 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     odt = torch.float16 if eng.F16_OPERANDS else torch.float32
     hl = prog.buf('lstm.h', 2 * lstm.hidden, odt)
     # channels-last mel: only the postnet bank's operand (the residual uses mel_cl_full): fp16 copy
-    mel_cl = prog.buf('mel_cl', n_mels, torch.float16 if (eng.F16_OPERANDS and n_mels % 8 == 0) else torch.float32)
+    mel_cl = prog.buf('mel_cl', n_mels, torch.float16 if (eng.F16_OPERANDS and n_mels % 8 == 0) else torch.float32,
+                      lead=rt.FOLD_LEAD_ROWS)       # zero rows in front: the postnet bank folds its taps into K
     mel = prog.dense('mel', (batch, n_mels, -1))
     mel_post = prog.dense('mel_post', (batch, n_mels, -1))
     post = prog.buf('postnet.h', 2 * packs['postnet'].rnn.hidden, odt)
@@ -183,10 +191,27 @@ scan_hook = None
 _PINNED_META = {}
 
 
-def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
-    """Runs K5's scan on `dur` (clamped / fallback-filled IN PLACE like the reference) and reads the
-    three integers the host needs (max length, fallback flag, total frames): the one D2H sync of generate(), through a
-    pinned buffer and an event (the host waits for the 16-byte copy, not for a stream drain)."""
+class PendingScan:
+    """K5's scan enqueued, its 16-byte result on the way to pinned host memory: `finish()` waits for that copy."""
+
+    def __init__(self, cum, lens, host, event):
+        self.cum, self.lens, self.host, self.event = cum, lens, host, event
+
+    def finish(self):
+        self.event.synchronize()
+        host = self.host
+        if int(host[3]) != 0:
+            # what nn.Embedding raises in the reference (forward_tacotron.py:31,210) for an id outside its table; the
+            # kernels clamped the id instead of reading out of bounds, the outputs of this call are meaningless
+            raise IndexError('index out of range in self: a token / class id lies outside its embedding table')
+        return self.cum, self.lens, int(host[0]), int(host[2])
+
+
+def length_regulate_begin(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool) -> PendingScan:
+    """Enqueues K5's scan on `dur` (clamped / fallback-filled IN PLACE like the reference) and the copy of the three
+    integers the host needs (max length, fallback flag, total frames) into a pinned buffer, followed by an event: the one
+    D2H of generate().  The caller keeps enqueueing work that does not depend on the regulated length (the pitch / energy
+    callbacks) and calls `finish()` when it needs M -- the host then waits for the 16-byte copy, not for a stream drain."""
     B, T = dur.shape
     dev = dur.device
     cum = torch.empty((B, T), dtype=torch.int32, device=dev)
@@ -201,12 +226,12 @@ def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
     ev.record(torch.cuda.current_stream(dev))
     if scan_hook is not None:
         scan_hook(meta, lens)
-    ev.synchronize()
-    if int(host[3]) != 0:
-        # what nn.Embedding raises in the reference (forward_tacotron.py:31,210) for an id outside its table; the
-        # kernels clamped the id instead of reading out of bounds, the outputs of this call are meaningless
-        raise IndexError('index out of range in self: a token / class id lies outside its embedding table')
-    return cum, lens, int(host[0]), int(host[2])
+    return PendingScan(cum, lens, host, ev)
+
+
+def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
+    """length_regulate_begin(...).finish(): (cum, lens, M, total frames)."""
+    return length_regulate_begin(handle, dur, apply_fallback).finish()
 
 
 def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program, prog: eng.Program,

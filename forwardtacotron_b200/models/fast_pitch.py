@@ -209,9 +209,11 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
             prog.alpha = float(alpha)
             prog.run()
             dur_hat = prog.bufs['dur.y'].clone()
-            scan = _accel.length_regulate(st['handle'], dur_hat, apply_fallback=True)      # :176-177 (+ LR clamp)
+            pending = _accel.length_regulate_begin(st['handle'], dur_hat, apply_fallback=True)      # :176-177 (+ LR clamp)
+            # the callbacks do not depend on the regulated length: they are enqueued while the scan result travels to the host
             pitch_hat = pitch_function(prog.bufs['pitch.y'].clone().unsqueeze(1))
             energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
+            scan = pending.finish()
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
 
     def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:

@@ -53,7 +53,9 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                  rnn_dims: int, prenet_dims: int, prenet_k: int, postnet_num_highways: int,
                  prenet_dropout: float, postnet_dims: int, postnet_k: int, prenet_num_highways: int,
                  postnet_dropout: float, n_mels: int, padding_value=-11.5129):
+        ctor_kwargs = {k: v for k, v in locals().items() if k not in ('self', '__class__')}
         super().__init__()
+        self._ctor_kwargs = ctor_kwargs            # forwardtacotron_b200.jit.script() rebuilds the module from these
         self.rnn_dims = rnn_dims
         self.padding_value = padding_value
         self.n_mels = n_mels
@@ -193,9 +195,11 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             prog.alpha = float(alpha)
             prog.run()
             dur_hat = prog.bufs['dur.y'].clone()                               # [B,T]  (dur_pred(x)/alpha).squeeze(2)
-            scan = _accel.length_regulate(st['handle'], dur_hat, apply_fallback=True)   # :176-177 (+ LR clamp)
+            pending = _accel.length_regulate_begin(st['handle'], dur_hat, apply_fallback=True)   # :176-177 (+ LR clamp)
+            # the callbacks do not depend on the regulated length: they are enqueued while the scan result travels to the host
             pitch_hat = pitch_function(prog.bufs['pitch.y'].clone().unsqueeze(1))       # [B,1,T]
             energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
+            scan = pending.finish()
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
 
     def generate_jit(self, x: torch.Tensor, alpha: float = 1.0, beta: float = 1.0) -> Dict[str, torch.Tensor]:

@@ -290,9 +290,11 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             prog.run()
             pitch_cond_hat = prog.bufs['pitch_cond'].clone()                   # [B,T] int64
             dur_hat = prog.bufs['dur.y'].reshape(B, T).clone()
-            scan = _accel.length_regulate(st['handle'], dur_hat, apply_fallback=True)   # :254-255 (+ LR clamp)
+            pending = _accel.length_regulate_begin(st['handle'], dur_hat, apply_fallback=True)   # :254-255 (+ LR clamp)
+            # the callbacks do not depend on the regulated length: they are enqueued while the scan result travels to the host
             pitch_hat = pitch_function(prog.bufs['pitch.y'].reshape(B, 1, T).clone())
             energy_hat = energy_function(prog.bufs['energy.y'].reshape(B, 1, T).clone())
+            scan = pending.finish()
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, pitch_cond_hat, scan)
 
     def _forward_eval(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:

@@ -47,6 +47,7 @@ class PackedGemm:
         self._w16 = None
         self.w_src = None            # unrounded fp32 copy of `w`; kept only by packs built with split=True
         self._w16s = None
+        self._w16f = None
 
     @property
     def w16(self) -> torch.Tensor:
@@ -57,6 +58,14 @@ class PackedGemm:
             self._w16 = self.w.to(torch.float16).contiguous()
         return self._w16
 
+
+    @property
+    def w16f(self) -> torch.Tensor:
+        """The fp16 weight with the taps FOLDED into the reduction (FTB_F_TAPS_IN_K): [n_pad][taps*cin], column
+        j*cin + c = tap j, channel c -- the operand of ONE tap over an overlapping-row view of a dense activation."""
+        if self._w16f is None:
+            self._w16f = self.w16.permute(1, 0, 2).reshape(self.n_pad, self.taps * self.cin).contiguous()
+        return self._w16f
 
     @property
     def w16s(self) -> torch.Tensor:

@@ -14,7 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libftb200.so')
 
 EPI_AFFINE, EPI_MAXPOOL, EPI_HIGHWAY = 0, 1, 2
-F_RELU, F_ROUND, F_A_F16, F_OUT_F16, F_OUT_SPLIT = 1, 2, 4, 8, 16
+F_RELU, F_ROUND, F_A_F16, F_OUT_F16, F_OUT_SPLIT, F_TAPS_IN_K = 1, 2, 4, 8, 16, 32
+FOLD_LEAD_ROWS = 8
 CELL_GRU, CELL_LSTM = 0, 1
 SEQ_GAP = 8          # zero rows between sentences in the padded-flat layout (>= largest conv reach)
 

@@ -85,8 +85,17 @@ enum { FTB_EPI_AFFINE = 0, FTB_EPI_MAXPOOL = 1, FTB_EPI_HIGHWAY = 2 };
  *                [W_hi | W_hi | W_lo] along K (cin = 3 seg, FTB_F_A_F16) then accumulates hi*W_hi + lo*W_hi + hi*W_lo: the
  *                product at ~2^-20 relative operand precision instead of 2^-11, on the same kind::f16 MMAs.  Used for
  *                the DURATION predictor, whose output is rounded to integers (forward_tacotron.py:174-177,
- *                common_layers.py:18-21): an operand error of 2^-11 moves durations across the .5 boundary.           */
-enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2, FTB_F_A_F16 = 4, FTB_F_OUT_F16 = 8, FTB_F_OUT_SPLIT = 16 };
+ *                common_layers.py:18-21): an operand error of 2^-11 moves durations across the .5 boundary.
+ * FTB_F_TAPS_IN_K: (with FTB_F_A_F16, taps <= 8) the taps are folded into the reduction: `a` is DENSE (lda == cin) and at
+ *                least 8 zero rows PRECEDE it in the same allocation (like the 8 gap rows that follow every sentence),
+ *                so the `taps` rows r + tap0 .. r + tap0 + taps - 1 are one contiguous run of taps*cin elements, and `w`
+ *                is packed [w_tap_rows][taps*cin] (column j*cin + c = tap j, channel c).  The kernel then reads A through an
+ *                overlapping-row tensor map (row stride cin, row extent taps*cin) and runs ONE tap over K = taps*cin:
+ *                ceil(taps*cin/64) k-blocks instead of taps*ceil(cin/64).  For channel counts that fill a 128-byte
+ *                swizzle row badly -- the CBHG postnet's bank over the 80-channel mel (common_layers.py:97-99): 48
+ *                k-blocks instead of 72 for its eight kernel sizes.  Same sums, same operands, same rounding.        */
+enum { FTB_F_RELU = 1, FTB_F_ROUND_TF32 = 2, FTB_F_A_F16 = 4, FTB_F_OUT_F16 = 8, FTB_F_OUT_SPLIT = 16, FTB_F_TAPS_IN_K = 32 };
+#define FTB_FOLD_LEAD_ROWS 8
 
 typedef struct {
   const void* a;         /* [rows, lda] activations: fp32 tf32-rounded by their producer, or fp16 (A_F16) */

@@ -41,4 +41,11 @@ if 'conv_gemm_tc_pair_kernel' in out:
     for k in ('launches_per_step', 'dram_bytes_per_step', 'us_serialised'):
         base[k] += pr[k]
     base['pair_launches_per_step'] = pr['launches_per_step']
+# the fused CBHG tail (cbhg_tail_kernel) is part of the conv/linear GEMM family bench.py reports under conv_gemm_tc_kernel
+if 'cbhg_tail_kernel' in out and 'conv_gemm_tc_kernel' in out:
+    tl = out['cbhg_tail_kernel']
+    base = out['conv_gemm_tc_kernel']
+    for k in ('launches_per_step', 'dram_bytes_per_step', 'us_serialised'):
+        base[k] += tl[k]
+    base['tail_launches_per_step'] = tl['launches_per_step']
 json.dump(out, open(f'profiles/{tag}_traffic.json', 'w'), indent=1)

@@ -121,6 +121,70 @@ def test_conv_fp16_operands(B, L, cin, cout, k, relu, pool, in16, out16):
     prog.h.impl = 0
 
 
+@pytest.mark.parametrize('B,L,cin,cout,k,pool', [
+    (3, 70, 80, 256, 8, True),          # the postnet bank's widest conv: 10 k-blocks instead of 16, pooled (halo row -1)
+    (2, 130, 80, 256, 5, True),         # odd k, crosses an M-tile boundary
+    (1, 300, 80, 256, 2, False),        # even k (asymmetric trim): 3 k-blocks instead of 4
+    (2, 50, 72, 48, 3, False),          # K = 216: tail of the last k-block zero-filled, half chunk (bn = 48)
+])
+def test_conv_taps_folded_into_k(B, L, cin, cout, k, pool):
+    """FTB_F_TAPS_IN_K: ONE tap over an overlapping-row tensor map of a dense fp16 activation with zero lead rows
+    (common_layers.py:97-99 over the 80-channel mel).  Checked against float64 torch, the SIMT cross-check kernel and --
+    bit for bit -- the unfolded problem on the same operands (same products, same k order inside a tap... the sums differ
+    only by fp32 association, so that comparison is to 1e-5)."""
+    gen = torch.Generator().manual_seed(B * 10 + L + k)
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    v = torch.randn(B, L, cin, generator=gen).to(torch.float16)
+    a = prog.buf('a', cin, torch.float16, lead=rt.FOLD_LEAD_ROWS)
+    a.view(g.batch, g.stride, cin)[:, :L] = v.to(DEV)
+    a2 = prog.buf('a_nolead', cin, torch.float16)                      # same values, no lead rows: stays unfolded
+    a2.copy_(a)
+    w = torch.randn(cout, cin, k, generator=gen) / (cin * k) ** 0.5
+    gamma, beta = torch.rand(cout, generator=gen) + 0.5, torch.randn(cout, generator=gen) * 0.1
+    mean, var = torch.randn(cout, generator=gen) * 0.1, torch.rand(cout, generator=gen) + 0.5
+    packed = pk.pack_bn_conv(w.to(DEV), gamma.to(DEV), beta.to(DEV), mean.to(DEV), var.to(DEV), True)
+    out = prog.buf('out', cout, torch.float16)
+    out2 = prog.buf('out_unfolded', cout, torch.float16)
+    epi = rt.EPI_MAXPOOL if pool else rt.EPI_AFFINE
+    prog.gemm(a, packed, out, epilogue=epi, round_out=False)
+    assert prog._pending[-1].flags & rt.F_TAPS_IN_K
+    prog.flush()
+    prog.gemm(a2, packed, out2, epilogue=epi, round_out=False)
+    assert not (prog._pending[-1].flags & rt.F_TAPS_IN_K)
+    prog.flush()
+    w_used = packed.w16.cpu().double()[:, :cout, :].permute(1, 2, 0)
+    y = _conv_ref(v.double(), w_used, k).clamp_min(0)
+    sc = (gamma / torch.sqrt(var + 1e-5)).double()
+    ref = y * sc + (beta.double() - mean.double() * sc)
+    if pool:
+        ref = F.max_pool1d(ref.transpose(1, 2), kernel_size=2, stride=1, padding=1)[:, :, :L].transpose(1, 2)
+    tol = 2e-4 + float(ref.abs().max()) * 2.0 ** -11
+    for impl in (1, 0):
+        out.zero_(); out2.zero_()
+        prog.h.impl = impl
+        prog.run()
+        torch.cuda.synchronize()
+        got = prog.view('out').cpu().double()
+        assert max_abs(got, ref) < tol, f'impl={impl}'
+        assert max_abs(got, prog.view('out_unfolded').cpu().double()) < 1e-5 + float(ref.abs().max()) * 2.0 ** -10, f'impl={impl}'
+        assert float(out.view(g.batch, g.stride, cout)[:, L:].abs().max()) == 0.0
+    prog.h.impl = 0
+    # another length inside the same capacity: the folded view needs no re-encoding
+    L2 = L - 7
+    prog.set_seq_len(L2)
+    a.zero_()
+    a[:g.rows].view(g.batch, g.stride, cin)[:, :L2] = v[:, :L2].to(DEV)
+    out.zero_()
+    prog.run()
+    torch.cuda.synchronize()
+    y2 = _conv_ref(v[:, :L2].double(), w_used, k).clamp_min(0)
+    ref2 = y2 * sc + (beta.double() - mean.double() * sc)
+    if pool:
+        ref2 = F.max_pool1d(ref2.transpose(1, 2), kernel_size=2, stride=1, padding=1)[:, :, :L2].transpose(1, 2)
+    assert max_abs(prog.view('out').cpu().double(), ref2) < tol
+
+
 def test_bank_maxpool_matches_reference_semantics():
     """conv bank (k=1..6) + MaxPool1d(2,1,1)[:L] fused epilogue vs torch ops (common_layers.py:97-105)."""
     B, L, cin, ch, K = 2, 200, 64, 64, 6

@@ -362,6 +362,51 @@ def test_forward_tacotron_generate_jit_twin():
         model.generate_jit(x)
 
 
+def test_forward_tacotron_torchscript_export(tmp_path):
+    """README.md:159-171 "Export Model with TorchScript": the scripted module (forwardtacotron_b200.jit.script, one
+    registered operator over the C-ABI kernels) gives generate_jit's result bit for bit, before and after a
+    torch.jit.save / torch.jit.load round trip, and moves with .to(device) like any module."""
+    from forwardtacotron_b200 import jit as ftb_jit
+    model = init_tts_model(default_config('forward_tacotron'))
+    model.load_state_dict(synth.synth_state_dict(model.state_dict(), seed=6))
+    model = model.eval()
+    scripted = ftb_jit.script(model).to(DEV)
+    model = model.to(DEV)
+    x = synth.synth_tokens(2, 21, seed=6).to(DEV)
+    want = model.generate_jit(x, alpha=0.9, beta=1.2)
+    got = scripted.generate_jit(x, 0.9, 1.2)
+    assert set(got) == set(want)
+    for k in ('dur', 'pitch', 'energy', 'mel', 'mel_post'):
+        assert got[k].shape == want[k].shape, k
+        assert torch.equal(got[k], want[k]), (k, float((got[k] - want[k]).abs().max()))
+    path = str(tmp_path / 'tts.ts')
+    torch.jit.save(scripted, path)
+    loaded = torch.jit.load(path, map_location=DEV)
+    again = loaded.generate_jit(x, 0.9, 1.2)
+    for k in want:
+        assert torch.equal(again[k], want[k]), k
+    y = loaded.generate_jit(torch.ones((1, 5), dtype=torch.int64, device=DEV))       # the README's dummy call
+    assert y['mel_post'].shape[:2] == (1, 80) and torch.isfinite(y['mel_post']).all()
+
+
+def test_fp16_operand_range_guard(monkeypatch):
+    """FTB_CHECK_RANGE=1 (engine.Program.check_range): the fp16 operand copies are stored without saturation, so a
+    checkpoint whose activations leave fp16's range must be caught by the debug guard instead of turning into inf
+    silently; a normal checkpoint passes the same guard with unchanged results."""
+    from forwardtacotron_b200 import engine as eng
+    sd = synthetic_sd('forward_tacotron', 3)
+    x = synth.synth_tokens(2, 19, seed=3).to(DEV)
+    base = _model('forward_tacotron', sd).generate(x)
+    monkeypatch.setattr(eng, 'CHECK_RANGE', True)
+    checked = _model('forward_tacotron', sd).generate(x)
+    for k in ('mel', 'mel_post', 'dur'):
+        assert torch.equal(checked[k], base[k]), k
+    big = dict(sd)
+    big['prenet.conv_project1.bnorm.weight'] = sd['prenet.conv_project1.bnorm.weight'] * 1.0e6
+    with pytest.raises(RuntimeError, match='fp16|inf'):
+        _model('forward_tacotron', big).generate(x)
+
+
 def test_forward_tacotron_all_zero_durations_raise():
     """dur_hat <= 0 everywhere with the integer fallback NOT triggered cannot happen in generate() (the fallback fills
     2.0, forward_tacotron.py:176-177); the teacher-forced entry with all-zero durations has nothing to synthesise."""

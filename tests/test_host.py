@@ -97,3 +97,39 @@ def test_training_forward_shapes():
     assert out['mel'].shape == (2, 80, 20) and out['mel_post'].shape == (2, 80, 20)
     assert out['dur'].shape == (2, 10) and out['pitch'].shape == (2, 1, 10) and out['energy'].shape == (2, 1, 10)
     assert model.get_step() == 1
+
+
+def test_torchscript_export_scripts_and_refuses_cpu(tmp_path):
+    """forwardtacotron_b200.jit.script (README.md:159-171): the module scripts, its exported generate_jit is ONE call of
+    the registered ftb200::generate_jit operator, the file round-trips, the rebuilt model aliases the flat weight buffer
+    with an identical state_dict -- and a CPU call raises instead of falling back."""
+    from forwardtacotron_b200 import jit as ftb_jit
+    model = init_tts_model(default_config('forward_tacotron')).eval()
+    scripted = ftb_jit.script(model)
+    assert 'ftb200::generate_jit' in str(scripted.generate_jit.graph)
+    path = str(tmp_path / 'tts.ts')
+    torch.jit.save(scripted, path)
+    loaded = torch.jit.load(path)
+    rebuilt = ftb_jit._rebuild(loaded.flat, loaded.spec)
+    sd0, sd1 = model.state_dict(), rebuilt.state_dict()
+    assert list(sd0) == list(sd1) and all(torch.equal(sd0[k], sd1[k]) and sd0[k].dtype == sd1[k].dtype for k in sd0)
+    lo, hi = loaded.flat.data_ptr(), loaded.flat.data_ptr() + loaded.flat.numel() * 4
+    assert all(lo <= p.data_ptr() < hi for p in rebuilt.parameters())
+    with pytest.raises(Exception, match='no CPU path'):
+        loaded.generate_jit(torch.ones((1, 5), dtype=torch.int64))
+    with pytest.raises(TypeError):
+        ftb_jit.script(init_tts_model(default_config('fast_pitch')))
+
+
+def test_misaligned_parameter_is_refused():
+    """Packs alias some parameters and the kernels read them with 16-byte vector loads: a parameter that is a view at an
+    odd offset of a larger buffer must be refused loudly (found by the TorchScript export, whose weights are views of one
+    flat buffer -- it lays them out in 256-byte steps)."""
+    model = init_tts_model(default_config('forward_tacotron')).eval()
+    w = model.dur_pred.lin.weight
+    big = torch.zeros(w.numel() + 1)
+    big[1:] = w.detach().reshape(-1)
+    model.dur_pred.lin.weight = torch.nn.Parameter(big[1:].view(w.shape), requires_grad=False)
+    assert model.dur_pred.lin.weight.data_ptr() % 16 != 0
+    with pytest.raises(RuntimeError, match='16-byte aligned'):
+        model._accel_state(torch.device('cpu'))
