@@ -223,6 +223,9 @@ mha_tc_kernel(const __half* __restrict__ qkv16, int e, const int64_t* __restrict
         *reinterpret_cast<uint32_t*>(o) = hi;
         *reinterpret_cast<uint32_t*>(o + e) = lo;
         *reinterpret_cast<uint32_t*>(o + 2 * e) = hi;
+      } else if (round == 2) {
+        const __half2 hh = __floats2half2_rn(a, c2);
+        *reinterpret_cast<uint32_t*>(reinterpret_cast<__half*>(out) + row * e + col) = *reinterpret_cast<const uint32_t*>(&hh);
       } else {
         if (round) { a = round_tf32(a); c2 = round_tf32(c2); }
         *reinterpret_cast<float2*>(out + row * e + col) = make_float2(a, c2);

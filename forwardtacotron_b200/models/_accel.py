@@ -297,6 +297,19 @@ class TransformerPack:
         self.max_len = self.pe.shape[0]
 
 
+def transformer_operand(tp: TransformerPack):
+    """(column multiplier, dtype, round mode) of the GEMM-operand buffers of one ForwardTransformer: the split
+    [hi | lo | hi] fp16 form for a precise (duration) transformer, else the plain fp16 operand copy (kind::f16 MMAs: twice
+    the tensor rate and half the operand bytes of tf32 for the same 11-bit significand; LayerNorm outputs, attention
+    outputs and ReLU'd conv1 outputs sit well inside fp16's range), else fp32 rounded to tf32 (FTB_F16_OPERANDS=0 or widths
+    that are not multiples of 8).  The residual stream keeps its fp32 twins either way."""
+    if tp.precise:
+        return 3, torch.float16, 3
+    if eng.F16_OPERANDS and tp.d_model % 8 == 0 and tp.layers[0].conv1.n % 8 == 0:
+        return 1, torch.float16, 2
+    return 1, torch.float32, True
+
+
 def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torch.Tensor, out: torch.Tensor,
                        key_tok: Optional[torch.Tensor], round_final: bool = True,
                        x_full: Optional[torch.Tensor] = None):
@@ -307,9 +320,8 @@ def transformer_levels(prog: eng.Program, tag: str, tp: TransformerPack, x: torc
     E = tp.d_model
     F = tp.layers[0].conv1.n
     PR = tp.precise                              # GEMM operands are [hi | lo | hi] fp16 buffers of 3x the width
-    opw, opdt = (3, torch.float16) if PR else (1, torch.float32)
-    rmode = 3 if PR else True
-    assert not PR or (x.dtype == torch.float16 and x.shape[1] == 3 * E and x_full is not None)
+    opw, opdt, rmode = transformer_operand(tp)
+    assert x.dtype == opdt and x.shape[1] == opw * E and (opdt == torch.float32 or x_full is not None), (tag, x.dtype, x.shape)
     # head widths 64 / 128 (FastPitch): attention on the tensor cores (ftb_mha_split) over the in_proj output written as a
     # split [hi | lo | hi] fp16 operand; other widths (MultiFastPitch: 192 / 196 / 256) keep the fp32 SIMT kernel
     tc_attn = eng.TC_ATTENTION and (E // tp.heads) in (64, 128) and E % tp.heads == 0

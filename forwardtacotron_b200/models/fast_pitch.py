@@ -146,11 +146,12 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
 
         def add_transformer(tag, tp, table, key_tok):
             E = tp.d_model
-            x0 = prog.buf(f'{tag}.x', 3 * E, torch.float16) if tp.precise else prog.buf(f'{tag}.x', E)
+            opw, opdt, rmode = _accel.transformer_operand(tp)
+            x0 = prog.buf(f'{tag}.x', opw * E, opdt)
             x0f = prog.buf(f'{tag}.x_full', E)
             out = prog.buf(f'{tag}.out', E)
             prog.call(lambda: h.posenc(tok, table, None, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0,
-                                       round_tf32=3 if tp.precise else True, out_full=x0f),
+                                       round_tf32=rmode, out_full=x0f),
                       label=f'{tag}.embed+posenc')                      # embedding + x + scale*pe (:143-145)
             branches.append(_accel.transformer_levels(prog, tag, tp, x0, out, key_tok, round_final=False, x_full=x0f))
             return out
@@ -180,11 +181,12 @@ class FastPitch(nn.Module, _accel.AcceleratedMixin):
         prog = eng.Program(h, geo)
         E = tp.d_model
         lr = prog.buf('lr', E)
-        x0 = prog.buf('postnet.x', E)
+        opw, opdt, rmode = _accel.transformer_operand(tp)
+        x0 = prog.buf('postnet.x', opw * E, opdt)
         x0f = prog.buf('postnet.x_full', E)
         out = prog.buf('postnet.out', E)
         mel = prog.dense('mel', (batch, self.n_mels, -1))
-        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0, out_full=x0f),
+        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0, round_tf32=rmode, out_full=x0f),
                   label='postnet.posenc')
         frame_tok = prog.dense('frame_tok', (batch, -1), torch.int64) if masked else None
         eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, frame_tok, x_full=x0f)])

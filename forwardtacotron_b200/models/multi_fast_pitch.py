@@ -199,14 +199,15 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
             """concat [table[tok], ctable[pcond], semb] -> + scale*pe -> transformer levels."""
             E = tp.d_model
             cat = prog.buf(f'{tag}.cat', E)
-            x0 = prog.buf(f'{tag}.x', 3 * E, torch.float16) if tp.precise else prog.buf(f'{tag}.x', E)
+            opw, opdt, rmode = _accel.transformer_operand(tp)
+            x0 = prog.buf(f'{tag}.x', opw * E, opdt)
             x0f = prog.buf(f'{tag}.x_full', E)
             out = prog.buf(f'{tag}.out', E)
             prog.call(lambda: h.embed(tok, table, cat, E, batch, geo.seq_len, geo.stride,
                                       tok2=pcond if ctable is not None else None, table2=ctable, extra=semb,
                                       round_tf32=False), label=f'{tag}.embed')
             prog.call(lambda: h.posenc(None, None, cat, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0,
-                                       round_tf32=3 if tp.precise else True, out_full=x0f),
+                                       round_tf32=rmode, out_full=x0f),
                       label=f'{tag}.posenc')
             return out, _accel.transformer_levels(prog, tag, tp, x0, out, key_tok, round_final=False, x_full=x0f)
 
@@ -253,11 +254,12 @@ class MultiFastPitch(nn.Module, _accel.AcceleratedMixin):
         prog = eng.Program(h, geo)
         E = tp.d_model
         lr = prog.buf('lr', E)
-        x0 = prog.buf('postnet.x', E)
+        opw, opdt, rmode = _accel.transformer_operand(tp)
+        x0 = prog.buf('postnet.x', opw * E, opdt)
         x0f = prog.buf('postnet.x_full', E)
         out = prog.buf('postnet.out', E)
         mel = prog.dense('mel', (batch, self.n_mels, -1))
-        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0, out_full=x0f),
+        prog.call(lambda: h.posenc(None, None, lr, tp.pe, tp.scale, E, batch, geo.seq_len, geo.stride, x0, round_tf32=rmode, out_full=x0f),
                   label='postnet.posenc')
         frame_tok = prog.dense('frame_tok', (batch, -1), torch.int64) if masked else None
         eng.run_levels(prog, [_accel.transformer_levels(prog, 'postnet', tp, x0, out, frame_tok, x_full=x0f)])

@@ -362,6 +362,9 @@ int ftb_posenc(ftb_handle h, const int64_t* tok, const float* table, const float
  * optional key padding (tok[b,s] == 0 masked, common_layers.py:232-233); out [rows, e]. */
 int ftb_mha(ftb_handle h, const float* qkv, int e, int heads, const int64_t* key_tok,
             int batch, int seq_len, int seq_stride, float* out, int round_tf32, void* stream);
+/* round_tf32 of ftb_add_layernorm / ftb_posenc / ftb_mha / ftb_mha_split, as for ftb_embed: 0 = fp32 as computed, 1 = fp32
+ * rounded to tf32, 2 = `out` is an fp16 array with the row stride of the fp32 form (ld resp. e halves; e % 8 == 0): the
+ * operand copy a FTB_F_A_F16 problem reads, 3 = the split [hi | lo | hi] fp16 form (row stride 3e halves). */
 
 /* The same attention on the TENSOR CORES with split-precision operands (head width 64 or 128, else FTB_E_SHAPE -> use
  * ftb_mha): qkv16 is the in_proj output as written by a FTB_F_OUT_SPLIT problem, fp16 [rows, 9e] = [hi | lo | hi] column

@@ -564,6 +564,81 @@ def test_mha_matches_torch(D, heads, B, L, masked):
     assert max_abs(prog.view('att').cpu().double(), want) < 2e-5
 
 
+@pytest.mark.parametrize('E,chained,with_res', [
+    (128, False, False),     # FastPitch predictors: one float4 per lane
+    (256, True, False),      # FastPitch pre / postnet, last layer chained with the transformer's final norm
+    (384, False, True),      # three float4 per lane, residual operand
+    (392, True, True),       # MultiFastPitch width: tail of the last chunk predicated
+    (1000, False, False),    # eight chunks per lane
+    (102, False, True),      # e % 4 != 0: the scalar kernel
+])
+def test_add_layernorm_all_output_forms(E, chained, with_res):
+    """K7 through the C ABI vs float64 torch LayerNorm (common_layers.py:177,184,209): fp32 as computed, tf32-rounded, the
+    fp16 operand copy (mode 2) and the split [hi | lo | hi] form (mode 3), with the unrounded twin next to each."""
+    gen = torch.Generator().manual_seed(E)
+    B, L = 3, 45
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    x, x_ref = _fill(prog, 'x', E, gen)
+    res, res_ref = _fill(prog, 'res', E, gen) if with_res else (None, None)
+    g1, b1 = (torch.rand(E, generator=gen) + 0.5).to(DEV), (torch.randn(E, generator=gen) * 0.1).to(DEV)
+    g2, b2 = ((torch.rand(E, generator=gen) + 0.5).to(DEV), (torch.randn(E, generator=gen) * 0.1).to(DEV)) if chained else (None, None)
+    v = x_ref + (res_ref if with_res else 0.0)
+    want = F.layer_norm(v, (E,), g1.cpu().double(), b1.cpu().double(), 1e-5)
+    if chained:
+        want = F.layer_norm(want, (E,), g2.cpu().double(), b2.cpu().double(), 1e-5)
+    h = _handle()
+    modes = [0, 1] + ([2, 3] if E % 8 == 0 else [])
+    for mode in modes:
+        cols, dt = {0: (E, torch.float32), 1: (E, torch.float32), 2: (E, torch.float16), 3: (3 * E, torch.float16)}[mode]
+        out = prog.buf(f'out{mode}', cols, dt)
+        full = prog.buf(f'full{mode}', E)
+        h.add_layernorm(x, res, E, E, g1, b1, g2, b2, B, L, g.stride, out, round_tf32=mode, out_full=full)
+        torch.cuda.synchronize()
+        assert max_abs(prog.view(f'full{mode}').cpu().double(), want) < 2e-5, mode
+        o = prog.view(f'out{mode}').cpu()
+        f32 = prog.view(f'full{mode}').cpu()
+        if mode == 0:
+            assert torch.equal(o, f32)
+        elif mode == 1:
+            assert torch.equal(o, pk.round_tf32(f32))
+        elif mode == 2:
+            assert torch.equal(o, f32.to(torch.float16))
+        else:
+            hi = f32.to(torch.float16)
+            assert torch.equal(o[..., :E], hi) and torch.equal(o[..., 2 * E:], hi)
+            assert torch.equal(o[..., E:2 * E], (f32 - hi.float()).to(torch.float16))
+        assert float(out.view(g.batch, g.stride, -1)[:, L:].abs().max()) == 0.0
+
+
+def test_fft_glue_fp16_operand_outputs():
+    """Mode 2 (plain fp16 operand copy) of ftb_posenc / ftb_mha / ftb_mha_split equals fp16(mode 0) bit for bit."""
+    gen = torch.Generator().manual_seed(11)
+    B, L, E, heads = 2, 70, 256, 2
+    prog = eng.Program(_handle(), eng.Geometry(B, L))
+    g = prog.geo
+    h = _handle()
+    xin, _ = _fill(prog, 'xin', E, gen)
+    pe = torch.randn(L + 5, E, generator=gen).to(DEV)
+    scale = torch.tensor([0.7], device=DEV)
+    p32, p16 = prog.buf('p32', E), prog.buf('p16', E, torch.float16)
+    h.posenc(None, None, xin, pe, scale, E, B, L, g.stride, p32, round_tf32=False)
+    h.posenc(None, None, xin, pe, scale, E, B, L, g.stride, p16, round_tf32=2)
+    qkv, _ = _fill(prog, 'qkv', 3 * E, gen)
+    a32, a16 = prog.buf('a32', E), prog.buf('a16', E, torch.float16)
+    h.mha(qkv, E, heads, None, B, L, g.stride, a32, round_tf32=False)
+    h.mha(qkv, E, heads, None, B, L, g.stride, a16, round_tf32=2)
+    q3 = prog.buf('qkv16', 9 * E, torch.float16)
+    q3.view(g.batch, g.stride, 9 * E)[:, :L] = _split3(prog.view('qkv').cpu()).to(DEV)
+    s32, s16 = prog.buf('s32', E), prog.buf('s16', E, torch.float16)
+    h.mha_split(q3, E, heads, None, B, L, g.stride, s32, round_tf32=False)
+    h.mha_split(q3, E, heads, None, B, L, g.stride, s16, round_tf32=2)
+    torch.cuda.synchronize()
+    for a, b in (('p32', 'p16'), ('a32', 'a16'), ('s32', 's16')):
+        assert torch.equal(prog.view(a).to(torch.float16), prog.view(b)), a
+        assert float(prog.bufs[b].view(g.batch, g.stride, -1)[:, L:].abs().max()) == 0.0
+
+
 def test_embed_and_heads_batched_match_single_and_torch():
     """ftb_embed_batch / ftb_rowdot_batch == the single-item entry points == torch (forward_tacotron.py:31,38-39)."""
     h = _handle()
