@@ -352,6 +352,24 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
           for (int j = 0; j < 4; ++j) acs[PR ? i : 0][j] = 0.0f;
       }
       const __half* hrow = h_s + (par * SL + kq * KB) * TILE + fr * U + 8 * q;
+      if (!PR && nbv <= 8) {
+        // at most 8 sentences in this unit (a 4-sentence shard of a long article, a single request): the second n-tile
+        // (columns 8-15) holds no sentence; its partial sums stay at the zeros they were initialised with and no gate
+        // thread reads them, so half of the step's HMMAs and shared-memory operand reads are skipped
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb) {
+          const uint4 h0 = *reinterpret_cast<const uint4*>(hrow + kb * TILE);
+          mma_f16_16x8x16(acc[0], wfrag[kb * 2 + 0], h0.x, h0.y);
+          mma_f16_16x8x16(acc[1], wfrag[kb * 2 + 1], h0.z, h0.w);
+        }
+        float* pk1 = p_s + static_cast<size_t>(kq) * NB * S;
+        const int col1 = 2 * q, row1 = rs * 16 + fr;
+        pk1[col1 * S + row1] = acc[0][0] + acc[1][0];
+        pk1[(col1 + 1) * S + row1] = acc[0][1] + acc[1][1];
+        pk1[col1 * S + row1 + 8] = acc[0][2] + acc[1][2];
+        pk1[(col1 + 1) * S + row1 + 8] = acc[0][3] + acc[1][3];
+        return;
+      }
 #pragma unroll
       for (int kb = 0; kb < KB; ++kb) {
         const uint4 h0 = *reinterpret_cast<const uint4*>(hrow + kb * TILE);
