@@ -412,13 +412,17 @@ def run_ours(args, rank, world, local_rank):
         # per-launch device times of the two programs (buffers still hold the last step's data)
         st = model.__dict__['_accel']
         per = {}
-        for key in (('tok', B, T), ('frame', B, M)):
-            prog = model.program_for(*key)
+        tok_prog = model.program_for('tok', B, T)
+        timed_progs = [('tok', 'tok', tok_prog)]
+        if getattr(tok_prog, 'xprog', None) is not None:        # the BiLSTM's x-projection per phoneme (token geometry)
+            timed_progs.append(('tok', 'tokx', tok_prog.xprog))
+        timed_progs.append(('frame', 'frame', model.program_for('frame', B, M)))
+        for side, name, prog in timed_progs:
             for rep in range(4):
                 flush.zero_()
                 for i, (info, ms) in enumerate(prog.run_timed()):
                     if rep:
-                        e = per.setdefault((key[0], i), {'info': info, 'ms': 0.0})
+                        e = per.setdefault((side, name, i), {'info': info, 'ms': 0.0})
                         e['ms'] += ms / 3.0
         # K5/K6 (length regulator) are launched by generate() itself, outside the two programs: time them with
         # events around the C-ABI calls of three more generate() calls
@@ -444,7 +448,7 @@ def run_ours(args, rank, world, local_rank):
         return
 
     kernels = []
-    for (side, i), e in per.items():
+    for (side, _name, i), e in per.items():
         info, ms = e['info'], e['ms']
         k = {'side': side, 'label': info['label'], 'kind': info['kind'], 'ms': round(ms, 4)}
         if info['kind'] == 'gemm':
@@ -458,12 +462,20 @@ def run_ours(args, rank, world, local_rank):
             k['handoff'] = info.get('handoff')
             k['kernel_launches'] = info.get('kernel_launches')
         kernels.append((k, info))
-    lr_buf = model.program_for('frame', B, M).bufs['lr']
-    C = lr_buf.shape[1]
-    # bytes the gather really moves: fp32 source rows + durations + the regulated rows in the dtype the product path
-    # writes (fp16 operand copy for the BiLSTM's W_ih GEMM: 2 bytes per element, not SURVEY 8d's fp32 figure)
-    lr_bytes = {'lr_gather': 4.0 * B * T * C + 4.0 * B * T + float(lr_buf.element_size()) * B * M * C,
-                'lr_scan': 2 * 4.0 * B * T}
+    frame_prog = model.program_for('frame', B, M)
+    if 'lr' in frame_prog.bufs:
+        lr_buf = frame_prog.bufs['lr']
+        C = lr_buf.shape[1]
+        # bytes the gather really moves: fp32 source rows + durations + the regulated rows in the dtype the product path
+        # writes (fp16 operand copy for the BiLSTM's W_ih GEMM: 2 bytes per element, not SURVEY 8d's fp32 figure)
+        lr_bytes = {'lr_gather': 4.0 * B * T * C + 4.0 * B * T + float(lr_buf.element_size()) * B * M * C,
+                    'lr_scan': 2 * 4.0 * B * T}
+    else:
+        # per-phoneme x-projection: the regulated sequence is never written.  `lr_gather` is the identity regulator
+        # (fp32 prenet rows + projection adds -> fp16 operand rows, T of them per sentence), `lr_index` the frame -> row map
+        C = tok_prog.xprog.bufs['h_tok'].shape[1]
+        lr_bytes = {'lr_gather': 4.0 * B * T * C + 2.0 * B * T * C, 'lr_scan': 2 * 4.0 * B * T,
+                    'lr_index': 4.0 * B * T + 4.0 * B * M}
     for name, ms in lr_ms.items():
         k = {'side': 'lr', 'label': name, 'kind': 'glue', 'ms': round(ms, 4),
              'gbs': round(lr_bytes[name] / ms / 1e6, 1), 'note': 'event-timed around the C-ABI call (includes launch gaps)'}

@@ -96,6 +96,7 @@ struct RnnProblemDev {
   const float* b_hh;
   float* out;
   __half* hx;            // fp16 exchange tensor [2][seq_len][batch][hidden], sentinel-armed before each run
+  const int* x_idx;      // optional [batch, seq_len] frame -> absolute row of xproj (ftb_rnn_problem.x_idx) or null
   const int* lens;       // optional [batch] valid lengths (packed-sequence semantics) or null
   float pad_value;       // value of out[b, t >= lens[b]]
   int out_f16;           // `out` holds fp16 (the operand copy of a following FTB_F_A_F16 problem)

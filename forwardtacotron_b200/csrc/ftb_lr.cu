@@ -229,9 +229,40 @@ lr_gather_kernel(const GatherArgs g, int token_blocks) {
   }
 }
 
+// Frame -> phoneme map without the copy: one thread per frame, binary search in the sentence's inclusive cumsum.
+__global__ void __launch_bounds__(256)
+lr_index_kernel(const int32_t* __restrict__ cum, const int32_t* __restrict__ lens, int batch, int T, int M,
+                int row_stride, int pad_row, int32_t* __restrict__ idx) {
+  const long long i = blockIdx.x * 256ll + threadIdx.x;
+  if (i >= static_cast<long long>(batch) * M) return;
+  const int b = static_cast<int>(i / M), m = static_cast<int>(i - static_cast<long long>(b) * M);
+  int t = pad_row;
+  if (m < min(lens[b], M)) {
+    const int32_t* c = cum + static_cast<long long>(b) * T;
+    int lo = 0, hi = T - 1;                          // first t with cum[t] > m (exists: m < lens[b] = cum[T-1])
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (c[mid] > m) hi = mid; else lo = mid + 1;
+    }
+    t = b * row_stride + lo;
+  }
+  idx[i] = t;
+}
+
 }  // namespace ftb
 
 using namespace ftb;
+
+extern "C" int ftb_lr_index(ftb_handle h, const int32_t* cum, const int32_t* lens, int batch, int T, int M,
+                            int row_stride, int pad_row, int32_t* idx, void* stream) {
+  if (!h || !cum || !lens || !idx || batch < 1 || T < 1 || M < 0 || row_stride < 0) return FTB_E_ARG;
+  if (M == 0) return 0;
+  const long long n = static_cast<long long>(batch) * M;
+  lr_index_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      cum, lens, batch, T, M, row_stride, pad_row, idx);
+  h->launches += 1;
+  return static_cast<int>(cudaGetLastError());
+}
 
 extern "C" int ftb_lr_scan(ftb_handle h, float* dur, int batch, int T, int apply_fallback, int32_t* cum,
                            int32_t* lens, int32_t* meta, void* stream) {

@@ -179,7 +179,12 @@ struct RnnTiling {
 // CL = false: h handed between CTAs through L2 (in-band sentinel polling; cooperative launch).
 // CL = true : the SL CTAs of one (direction, batch group) unit sit in one thread-block cluster and push h_t
 //             straight into each other's shared memory (st.async + mbarrier complete_tx); see the header.
-template <int G, int H, bool CL, bool PR = false>
+// XI: the x-projection rows are read through ftb_rnn_problem.x_idx (the LengthRegulator folded into this read).  A
+// compile-time switch: the same code as a run-time branch cost every recurrence of the step 7 % (a few more live
+// registers in a kernel that sits at the 128-register cap).  Instantiated for the problems that use it: LSTM-512.
+// ONE (cluster hand-off): the unit holds at most 8 sentences, so only the first MMA n-tile (columns 0-7) is computed.
+// Also compile-time, for the same reason; instantiated for the frame-side recurrences (LSTM-512, GRU-256).
+template <int G, int H, bool CL, bool PR = false, bool XI = false, bool ONE = false>
 __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* smem) {
   using T = RnnTiling<G, H, CL, PR>;
   constexpr int U = T::U, NB = T::NB, KS = T::KS, WARPS = T::WARPS, KW = T::KW, KB = T::KB, NBG = T::NBG;
@@ -263,14 +268,25 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
   char* x_dst = reinterpret_cast<char*>(x_s) + (xb * XSTR + xg_ * U + xpart * xce) * xesz;
   const int x_stage = NB * XSTR * xesz;             // bytes per ring stage
   // running pointers (strength-reduced: the per-step 64-bit index math sat on the latency chain of the gate phase)
-  const long long x_step = (dir ? -static_cast<long long>(2 * GH) : static_cast<long long>(2 * GH)) * xesz;
-  const char* x_pf = x_src + static_cast<size_t>(dir ? L - 1 : 0) * (2 * GH) * xesz;
+  // XI: step t of sentence b reads row x_idx[b, t] (an absolute row) of a per-PHONEME x-projection; the running pointer
+  // walks the index row, and the index of the NEXT prefetch is loaded one prefetch ahead (a whole time step of slack), so
+  // the dependent address never waits on the chain.  Row offsets are 32-bit products (x-projections below 4 GB).
+  const long long x_step = XI ? (dir ? -1ll : 1ll) * static_cast<long long>(sizeof(int))
+                              : (dir ? -static_cast<long long>(2 * GH) : static_cast<long long>(2 * GH)) * xesz;
+  const char* x_pf = XI ? reinterpret_cast<const char*>(p.x_idx + static_cast<size_t>(b0 + (xv ? xb : 0)) * L + (dir ? L - 1 : 0))
+                        : x_src + static_cast<size_t>(dir ? L - 1 : 0) * (2 * GH) * xesz;
+  const char* xi_base = reinterpret_cast<const char*>(p.xproj) + static_cast<size_t>(dir * GH + xg_ * H + u0 + xpart * xce) * xesz;
+  const unsigned xi_rowbytes = static_cast<unsigned>(2 * GH * xesz);
+  unsigned xi_next = (XI && xv) ? static_cast<unsigned>(__ldg(reinterpret_cast<const int*>(x_pf))) : 0u;
   int pf_step = 0;
   auto prefetch_x = [&]() {                         // x rows of step `pf_step` -> ring slot pf_step % XS
-    if (xv && pf_step < L) cp_async16(x_dst + (pf_step & (RNN_XS - 1)) * x_stage, x_pf);
+    if (xv && pf_step < L)
+      cp_async16(x_dst + (pf_step & (RNN_XS - 1)) * x_stage,
+                 XI ? xi_base + static_cast<size_t>(xi_next) * xi_rowbytes : x_pf);
     cp_async_commit();
     x_pf += x_step;
     ++pf_step;
+    if (XI && xv && pf_step < L) xi_next = static_cast<unsigned>(__ldg(reinterpret_cast<const int*>(x_pf)));
   };
   // W_hh and the biases above are weights; the x-projection is the previous kernel's output
   pdl_wait();
@@ -352,7 +368,7 @@ __device__ void rnn_cta(const RnnProblemDev& p, int local_cta, unsigned char* sm
           for (int j = 0; j < 4; ++j) acs[PR ? i : 0][j] = 0.0f;
       }
       const __half* hrow = h_s + (par * SL + kq * KB) * TILE + fr * U + 8 * q;
-      if (!PR && nbv <= 8) {
+      if (ONE) {
         // at most 8 sentences in this unit (a 4-sentence shard of a long article, a single request): the second n-tile
         // (columns 8-15) holds no sentence; its partial sums stay at the zeros they were initialised with and no gate
         // thread reads them, so half of the step's HMMAs and shared-memory operand reads are skipped
@@ -648,14 +664,26 @@ __device__ __forceinline__ void rnn_dispatch(const RnnProblemDev& p, int local, 
       return;
     }
   }
+  // sentences in this CTA's unit (rnn_cta derives the same numbers): units of <= 8 take the one-n-tile form
+  const int unit_b0 = p.b_begin + ((local / p.slices) % p.bgroups) * RNN_NB;
+  const bool one = CL && (p.b_end - unit_b0) <= 8;
   if (p.cell == FTB_CELL_LSTM) {
-    if (p.hidden == 512) rnn_cta<4, 512, CL>(p, local, smem);
+    if (p.hidden == 512 && p.x_idx) {
+      if constexpr (CL) { if (one) { rnn_cta<4, 512, true, false, true, true>(p, local, smem); return; } }
+      rnn_cta<4, 512, CL, false, true>(p, local, smem);
+    } else if (p.hidden == 512) {
+      if constexpr (CL) { if (one) { rnn_cta<4, 512, true, false, false, true>(p, local, smem); return; } }
+      rnn_cta<4, 512, CL>(p, local, smem);
+    }
     else if (p.hidden == 256) rnn_cta<4, 256, CL>(p, local, smem);
     else if (p.hidden == 128) rnn_cta<4, 128, CL>(p, local, smem);
     else rnn_cta<4, 64, CL>(p, local, smem);
   } else {
     if (p.hidden == 512) rnn_cta<3, 512, CL>(p, local, smem);
-    else if (p.hidden == 256) rnn_cta<3, 256, CL>(p, local, smem);
+    else if (p.hidden == 256) {
+      if constexpr (CL) { if (one) { rnn_cta<3, 256, true, false, false, true>(p, local, smem); return; } }
+      rnn_cta<3, 256, CL>(p, local, smem);
+    }
     else if (p.hidden == 128) rnn_cta<3, 128, CL>(p, local, smem);
     else rnn_cta<3, 64, CL>(p, local, smem);
   }
@@ -762,6 +790,7 @@ static int rnn_place(const ftb_rnn_problem* problems, const std::vector<int>& wh
       RnnProblemDev d{};
       d.xproj = q.xproj; d.w_hh = q.w_hh; d.b_hh = q.b_hh; d.out = q.out; d.hx = nullptr;
       d.lens = q.lens; d.pad_value = q.pad_value; d.out_f16 = q.out_f16; d.x_f16 = q.x_f16;
+      d.x_idx = q.x_idx;
       d.precise = (cluster && q.precise) ? 1 : 0;
       d.cell = q.cell; d.hidden = q.hidden; d.batch = q.batch; d.seq_len = q.seq_len;
       d.seq_stride = q.seq_stride; d.out_ld = q.out_ld; d.out_col0 = q.out_col0;
@@ -801,6 +830,7 @@ int rnn_plan_build(const ftb_rnn_problem* problems, int nproblems, int num_sms, 
     if (q.hidden != 64 && q.hidden != 128 && q.hidden != 256 && q.hidden != 512) return FTB_E_SHAPE;
     if (q.batch < 1 || q.seq_len < 1 || q.seq_stride < q.seq_len) return FTB_E_ARG;
     if ((q.out_ld % 4) != 0 || (q.out_col0 % 4) != 0 || (reinterpret_cast<uintptr_t>(q.out) & 15u)) return FTB_E_ALIGN;
+    if (q.x_idx && (q.cell != FTB_CELL_LSTM || q.hidden != 512 || q.precise)) return FTB_E_SHAPE;   // instantiated for LSTM-512
     if (q.hidden / RNN_U > max_slices) max_slices = q.hidden / RNN_U;
     if (q.precise) {
       // split-precision recurrence: GRU, H <= 128, fp32 x-projection and output, cluster hand-off only

@@ -39,6 +39,10 @@ FUSED_TAIL = os.environ.get('FTB_FUSED_TAIL', '1') != '0'
 # taps folded into the reduction for convolutions over a channel count that fills a 128-byte swizzle row badly (the
 # postnet bank over the 80-channel mel: 48 k-blocks instead of 72, FTB_F_TAPS_IN_K); FTB_FOLD_TAPS=0 disables
 FOLD_TAPS = os.environ.get('FTB_FOLD_TAPS', '1') != '0'
+# The BiLSTM's x-projection computed once per PHONEME and read through the LengthRegulator's frame -> phoneme map
+# (ftb_rnn_problem.x_idx): the regulated sequence is never written and W_ih runs over T instead of M rows.
+# FTB_XPROJ_TOKENS=0 restores the materialised LengthRegulator output + frame-level projection.
+XPROJ_TOKENS = os.environ.get('FTB_XPROJ_TOKENS', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -309,13 +313,19 @@ class Program:
                               **self.h.gemm_info(plan)})
 
     def rnn(self, specs, lens: Optional[torch.Tensor] = None, pad_value: float = 0.0):
-        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0) run by one plan (cluster or cooperative launches).
-        `lens` (int32 [batch], device): packed-sequence semantics for every problem of the launch."""
+        """specs: list of (PackedRnn, xproj buffer, out buffer, out_col0[, xmap]) run by one plan (cluster or cooperative
+        launches).  `lens` (int32 [batch], device): packed-sequence semantics for every problem of the launch.
+        xmap = x_idx int32 [batch, cap] (absolute rows of xproj): the problem reads its x-projection rows through the
+        LengthRegulator's frame -> row map (ftb_rnn_problem.x_idx, ftb_lr_index)."""
         self.flush()
         g = self.geo
         probs = []
-        for r, xproj, out, col0 in specs:
+        specs = [tuple(sp) + (None,) * (5 - len(sp)) for sp in specs]
+        for r, xproj, out, col0, xmap in specs:
             p = rt.RnnProblem()
+            if xmap is not None:
+                p.x_idx = xmap.data_ptr()
+                self._keep.append(xmap)
             p.cell, p.hidden = r.cell, r.hidden
             p.batch, p.seq_len, p.seq_stride = g.batch, g.seq_len, g.stride
             p.xproj, p.w_hh, p.b_hh = xproj.data_ptr(), r.w_hh.data_ptr(), r.b_hh.data_ptr()
@@ -330,11 +340,11 @@ class Program:
         self._rnn_plans.append(plan)
         self.steps.append(lambda plan=plan: self.h.rnn_run(plan))
         valid = g.batch * g.seq_len
-        flops = sum(2.0 * 2 * valid * r.hidden * (4 if r.cell else 3) * r.hidden for r, _, _, _ in specs)
+        flops = sum(2.0 * 2 * valid * r.hidden * (4 if r.cell else 3) * r.hidden for r, *_ in specs)
         # x-projection read + h write per step, W_hh once
         nbytes = sum(4.0 * valid * (2 * (4 if r.cell else 3) * r.hidden + 2 * r.hidden) + 4.0 * r.w_hh.numel()
-                     for r, _, _, _ in specs)
-        wbytes = sum(4.0 * r.w_hh.numel() for r, _, _, _ in specs)
+                     for r, *_ in specs)
+        wbytes = sum(4.0 * r.w_hh.numel() for r, *_ in specs)
         self.info.append({'kind': 'rnn', 'label': self._label or 'rnn', 'flops': flops, 'bytes': nbytes,
                           'flops_row': flops / valid, 'bytes_row': (nbytes - wbytes) / valid, 'bytes_fixed': wbytes,
                           'steps': g.seq_len, 'problems': len(specs), **self.h.rnn_info(plan)})
@@ -435,6 +445,9 @@ class Program:
         return [(i, a.elapsed_time(b)) for i, (a, b) in zip(self.info, evs)]
 
     def close(self):
+        xp = self.__dict__.pop('xprog', None)          # a token program's companion (models/_accel.token_x_program)
+        if xp is not None:
+            xp.close()
         for p in self._gemm_plans:
             self.h.gemm_destroy(p)
         for p in self._rnn_plans:

@@ -83,6 +83,11 @@ class AcceleratedMixin:
             progs[ckey] = prog
             while len(progs) > self.MAX_PROGRAMS * 2:
                 _, old = progs.popitem(last=False)
+                # frame programs read the x-projection buffer of the token program they were built for
+                for dep in getattr(old, 'dependents', ()):
+                    d = progs.pop(dep, None)
+                    if d is not None:
+                        d.close()
                 old.close()
         prog.set_seq_len(seq_len)
         return prog
@@ -90,7 +95,15 @@ class AcceleratedMixin:
     def program_for(self, kind: str, batch: int, seq_len: int):
         """The cached program that served (kind, batch, seq_len), or None (tests, bench.py)."""
         st = self.__dict__.get('_accel')
-        return None if st is None else st['programs'].get((kind, batch, eng.capacity_bucket(seq_len)))
+        if st is None:
+            return None
+        bucket = eng.capacity_bucket(seq_len)
+        prog = st['programs'].get((kind, batch, bucket))
+        if prog is None:            # frame programs are keyed '<kind>@<token program>' (frame_program below): latest match
+            for (k, b, c), p in reversed(list(st['programs'].items())):
+                if k.startswith(kind + '@') and b == batch and c == bucket:
+                    return p
+        return prog
 
     @staticmethod
     def _check_tokens(x: torch.Tensor):
@@ -101,19 +114,103 @@ class AcceleratedMixin:
             raise RuntimeError(f'generate(): x must be int64 [batch, tokens], got {x.dtype} {tuple(x.shape)}')
 
 
+def token_x_supported(packs: dict, in_channels: int) -> bool:
+    """The BiLSTM's x-projection once per PHONEME (engine.XPROJ_TOKENS): the fp16 operand / fp16 x-projection path."""
+    return bool(eng.XPROJ_TOKENS and eng.F16_OPERANDS and eng.X16 and in_channels % 8 == 0 and packs['lstm'].ih.n % 8 == 0)
+
+
+def token_x_program(handle: rt.Handle, packs: dict, tok_prog: eng.Program, in_channels: int) -> eng.Program:
+    """The token program's companion (built on first use, same capacity): 'h_tok' = prenet output + pitch / energy
+    projection adds (+ speaker tail) per PHONEME as the fp16 operand, and the W_ih half of self.lstm over it
+    (forward_tacotron.py:214-224 with the LengthRegulator hoisted behind the projection: W_ih x + b_ih is a per-row map,
+    so it commutes with the regulator's row repetition, common_layers.py:21).  Row cap_rows of 'xproj' holds b_ih, the
+    projection of the regulator's zero padding (common_layers.py:23)."""
+    xp = getattr(tok_prog, 'xprog', None)
+    if xp is None:
+        geo = eng.Geometry(tok_prog.geo.batch, tok_prog.geo.cap)
+        xp = eng.Program(handle, geo)
+        lstm: pk.PackedRnn = packs['lstm']
+        h_tok = xp.buf('h_tok', in_channels, torch.float16)
+        xproj = xp.dense('xproj', (geo.cap_rows + 1, lstm.ih.n), torch.float16)
+        xproj[geo.cap_rows] = lstm.ih.bias0.to(torch.float16)
+        xp.label('lstm_ih')
+        xp.gemm(h_tok, lstm.ih, xproj, round_out=False)
+        xp.flush()
+        xp.label('')
+        xp.pad_row = geo.cap_rows
+        xp.ident = {}
+        tok_prog.xprog = xp
+        tok_prog.dependents = set()
+    xp.set_seq_len(tok_prog.geo.seq_len)
+    return xp
+
+
+def token_xproj(handle: rt.Handle, packs: dict, tok_prog: eng.Program, pre: torch.Tensor, extra: Optional[torch.Tensor],
+                c2: int, pitch_hat: torch.Tensor, energy_hat: torch.Tensor, pitch_strength: float,
+                energy_strength: float) -> None:
+    """Enqueue the per-phoneme x-projection of the BiLSTM.  Nothing here depends on the regulated length, so generate()
+    calls it BEFORE it waits for the LengthRegulator scan: the GEMM runs while the scan result travels to the host."""
+    B, T = tok_prog.geo.batch, tok_prog.geo.seq_len
+    C1 = pre.shape[1]
+    xp = token_x_program(handle, packs, tok_prog, C1 + c2)
+    ident = xp.ident.get(T)
+    if ident is None:                                  # the identity regulator: one frame per phoneme
+        if len(xp.ident) > 4:
+            xp.ident.clear()
+        cum = torch.arange(1, T + 1, dtype=torch.int32, device=pre.device).expand(B, T).contiguous()
+        ident = xp.ident[T] = (cum, torch.full((B,), T, dtype=torch.int32, device=pre.device))
+    g = _gather_args(packs, tok_prog, pre, extra, c2, pitch_hat, energy_hat, pitch_strength, energy_strength)
+    g.cum, g.lens = ident[0].data_ptr(), ident[1].data_ptr()
+    g.batch, g.T, g.M = B, T, T
+    h_tok = xp.bufs['h_tok']
+    g.out, g.out_stride, g.out_ld = h_tok.data_ptr(), xp.geo.stride, h_tok.shape[1]
+    g.idx, g.round_tf32 = None, 2
+    g._keep = g._keep + [ident]
+    handle.lr_gather(g)
+    xp.run()
+    tok_prog.x_token = (pitch_hat, energy_hat)
+
+
+def frame_program(model, st: dict, kind: str, tok_prog: eng.Program, batch: int, M: int, in_channels: int, n_mels: int,
+                  packed_pad_value: Optional[float] = None) -> eng.Program:
+    """The cached frame-side program for (kind, batch, M).  With the per-phoneme x-projection its BiLSTM reads the
+    'xproj' buffer of `tok_prog`'s companion program, so it is keyed by that token program too and leaves the cache
+    with it (AcceleratedMixin._program)."""
+    packs, h = st['packs'], st['handle']
+    if not token_x_supported(packs, in_channels):
+        return model._program(st, (kind, batch, M), lambda M: build_frame_program(h, packs, batch, M, in_channels, n_mels,
+                                                                                  packed_pad_value))
+    xp = token_x_program(h, packs, tok_prog, in_channels)
+    key_kind = f'{kind}@{id(tok_prog)}'
+    prog = model._program(st, (key_kind, batch, M), lambda M: build_frame_program(h, packs, batch, M, in_channels, n_mels,
+                                                                                  packed_pad_value, xprog=xp))
+    tok_prog.dependents.add((key_kind, batch, eng.capacity_bucket(M)))
+    return prog
+
+
 def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_channels: int, n_mels: int,
-                        packed_pad_value: Optional[float] = None):
+                        packed_pad_value: Optional[float] = None, xprog: Optional[eng.Program] = None):
     """LR output [B,M,C] -> BiLSTM -> lin -> CBHG postnet -> post_proj
-    (forward_tacotron.py:224-231).  Returns the Program; the LR gather writes prog.buf('lr').
+    (forward_tacotron.py:224-231).  Returns the Program; the LR gather writes prog.buf('lr') -- or, with `xprog` (the
+    per-phoneme x-projection, token_x_program), nothing is gathered at all: the BiLSTM reads xprog's 'xproj' rows through
+    the frame -> row map the caller writes into prog.bufs['x_idx'] (ftb_lr_index).
     `packed_pad_value` != None: the BiLSTM runs with pack_padded_sequence semantics over the int32 lengths the
     caller writes into prog.bufs['mel_len'] (eval-mode forward(batch), forward_tacotron.py:147-152)."""
     geo = eng.Geometry(batch, M)
     prog = eng.Program(handle, geo)
     lstm: pk.PackedRnn = packs['lstm']
-    # the regulated sequence feeds only the W_ih GEMM: fp16 operand copy (K5 writes it directly)
-    x = prog.buf('lr', in_channels, torch.float16 if (eng.F16_OPERANDS and in_channels % 8 == 0) else torch.float32)
     x16 = eng.X16 and eng.F16_OPERANDS and lstm.ih.n % 8 == 0
-    xp = prog.buf('lstm.xproj', lstm.ih.n, torch.float16 if x16 else torch.float32)
+    if xprog is not None:
+        prog.dense('x_idx', (batch, -1), torch.int32)
+        xmap = dict.__getitem__(prog.bufs, 'x_idx')                     # the storage: [batch, M] dense at its head
+        xp = dict.__getitem__(xprog.bufs, 'xproj')
+        prog._keep.append(xprog)
+        x = None
+    else:
+        xmap = None
+        # the regulated sequence feeds only the W_ih GEMM: fp16 operand copy (K5 writes it directly)
+        x = prog.buf('lr', in_channels, torch.float16 if (eng.F16_OPERANDS and in_channels % 8 == 0) else torch.float32)
+        xp = prog.buf('lstm.xproj', lstm.ih.n, torch.float16 if x16 else torch.float32)
     # the recurrences hand h_t on in fp16, so their layer outputs are fp16-exact: `lin` and `post_proj` (their only
     # readers) take them as fp16 operands
     odt = torch.float16 if eng.F16_OPERANDS else torch.float32
@@ -125,15 +222,16 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
     mel_post = prog.dense('mel_post', (batch, n_mels, -1))
     post = prog.buf('postnet.h', 2 * packs['postnet'].rnn.hidden, odt)
 
-    prog.label('lstm_ih')
-    prog.gemm(x, lstm.ih, xp, round_out=False)                    # W_ih half of self.lstm (:224)
+    if x is not None:
+        prog.label('lstm_ih')
+        prog.gemm(x, lstm.ih, xp, round_out=False)                # W_ih half of self.lstm (:224)
     prog.label('lstm')
     if packed_pad_value is None:
-        prog.rnn([(lstm, xp, hl, 0)])
+        prog.rnn([(lstm, xp, hl, 0, xmap)])
     else:
         mel_len = prog.dense('mel_len', (batch,), torch.int32)
         # the padded rows feed the `lin` GEMM: keep the pad value tf32-exact like every other operand
-        prog.rnn([(lstm, xp, hl, 0)], lens=mel_len, pad_value=float(pk.round_tf32(torch.tensor([packed_pad_value]))[0]))
+        prog.rnn([(lstm, xp, hl, 0, xmap)], lens=mel_len, pad_value=float(pk.round_tf32(torch.tensor([packed_pad_value]))[0]))
     prog.label('lin')
     mel_full = prog.buf('mel_cl_full', n_mels)
     prog.gemm(hl, packs['lin'], mel_cl, out_t=mel, out_full=mel_full)   # self.lin + transpose (:226-227)
@@ -234,15 +332,11 @@ def length_regulate(handle: rt.Handle, dur: torch.Tensor, apply_fallback: bool):
     return length_regulate_begin(handle, dur, apply_fallback).finish()
 
 
-def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program, prog: eng.Program,
-                          pre: torch.Tensor, extra: Optional[torch.Tensor], c2: int, dur_hat: torch.Tensor,
-                          pitch_hat: torch.Tensor, energy_hat: torch.Tensor, cum: torch.Tensor, lens: torch.Tensor,
-                          M: int, pitch_strength: float, energy_strength: float,
-                          round_tf32: bool = True) -> Dict[str, torch.Tensor]:
-    """K5/K6 gather (projection adds + optional speaker tail fused into the source read) into the frame
-    program's 'lr' buffer, then the frame-side launches; returns the reference's result dict
-    (forward_tacotron.py:214-233)."""
-    B, T = dur_hat.shape
+def _gather_args(packs: dict, tok_prog: eng.Program, pre: torch.Tensor, extra: Optional[torch.Tensor], c2: int,
+                 pitch_hat: torch.Tensor, energy_hat: torch.Tensor, pitch_strength: float,
+                 energy_strength: float) -> rt.LrGatherArgs:
+    """Source side of K5/K6's gather: prenet rows, speaker tail, the pitch / energy projection adds."""
+    B, T = tok_prog.geo.batch, tok_prog.geo.seq_len
     pitch = pitch_hat.reshape(B, T).to(torch.float32).contiguous()
     energy = energy_hat.reshape(B, T).to(torch.float32).contiguous()
     C1 = pre.shape[1]
@@ -253,12 +347,35 @@ def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program,
     (wp, bp), (we, be) = packs['pitch_proj'], packs['energy_proj']
     g.wp, g.bp, g.ps = wp.data_ptr(), bp.data_ptr(), pitch_strength
     g.we, g.be, g.es = we.data_ptr(), be.data_ptr(), energy_strength
-    g.cum, g.lens = cum.data_ptr(), lens.data_ptr()
-    g.batch, g.T, g.M = B, T, M
-    lr = prog.bufs['lr']
-    g.out, g.out_stride, g.out_ld = lr.data_ptr(), prog.geo.stride, lr.shape[1]
-    g.idx, g.round_tf32 = None, (2 if lr.dtype == torch.float16 else int(round_tf32))
-    handle.lr_gather(g)
+    g._keep = [pitch, energy]
+    return g
+
+
+def gather_and_run_frames(handle: rt.Handle, packs: dict, tok_prog: eng.Program, prog: eng.Program,
+                          pre: torch.Tensor, extra: Optional[torch.Tensor], c2: int, dur_hat: torch.Tensor,
+                          pitch_hat: torch.Tensor, energy_hat: torch.Tensor, cum: torch.Tensor, lens: torch.Tensor,
+                          M: int, pitch_strength: float, energy_strength: float,
+                          round_tf32: bool = True) -> Dict[str, torch.Tensor]:
+    """K5/K6 gather (projection adds + optional speaker tail fused into the source read) into the frame
+    program's 'lr' buffer, then the frame-side launches; returns the reference's result dict
+    (forward_tacotron.py:214-233).  Frame programs built on the per-phoneme x-projection (build_frame_program(xprog=))
+    get the frame -> row map instead of the gathered rows."""
+    B, T = dur_hat.shape
+    if 'x_idx' in prog.bufs:
+        xt = getattr(tok_prog, 'x_token', None)
+        if xt is None or xt[0] is not pitch_hat or xt[1] is not energy_hat:       # not enqueued ahead of the scan wait
+            token_xproj(handle, packs, tok_prog, pre, extra, c2, pitch_hat, energy_hat, pitch_strength, energy_strength)
+        tok_prog.x_token = None
+        xp = tok_prog.xprog
+        handle.lr_index(cum, lens, B, T, M, prog.bufs['x_idx'], row_stride=xp.geo.stride, pad_row=xp.pad_row)
+    else:
+        g = _gather_args(packs, tok_prog, pre, extra, c2, pitch_hat, energy_hat, pitch_strength, energy_strength)
+        g.cum, g.lens = cum.data_ptr(), lens.data_ptr()
+        g.batch, g.T, g.M = B, T, M
+        lr = prog.bufs['lr']
+        g.out, g.out_stride, g.out_ld = lr.data_ptr(), prog.geo.stride, lr.shape[1]
+        g.idx, g.round_tf32 = None, (2 if lr.dtype == torch.float16 else int(round_tf32))
+        handle.lr_gather(g)
     prog.run()
     mel = prog.bufs['mel'].clone()
     mel_post = prog.bufs['mel_post'].clone() if 'mel_post' in prog.bufs else mel

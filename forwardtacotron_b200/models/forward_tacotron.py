@@ -199,6 +199,11 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             # the callbacks do not depend on the regulated length: they are enqueued while the scan result travels to the host
             pitch_hat = pitch_function(prog.bufs['pitch.y'].clone().unsqueeze(1))       # [B,1,T]
             energy_hat = energy_function(prog.bufs['energy.y'].clone().unsqueeze(1))
+            pre = prog.bufs['prenet.h']
+            if _accel.token_x_supported(st['packs'], pre.shape[1]):
+                # the BiLSTM's x-projection per phoneme does not depend on the regulated length either
+                _accel.token_xproj(st['handle'], st['packs'], prog, pre, None, 0, pitch_hat, energy_hat,
+                                   float(self.pitch_strength), float(self.energy_strength))
             scan = pending.finish()
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, scan)
 
@@ -236,8 +241,8 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError(f'forward(): mel_len must lie in [1, {M_lr}] (the regulated length), as '
                                'pack_padded_sequence requires (forward_tacotron.py:147)')
         pre = tok.bufs['prenet.h']
-        prog = self._program(st, ('frame_packed', B, M), lambda M: _accel.build_frame_program(
-            st['handle'], st['packs'], B, M, pre.shape[1], self.n_mels, packed_pad_value=float(self.padding_value)))
+        prog = _accel.frame_program(self, st, 'frame_packed', tok, B, M, pre.shape[1], self.n_mels,
+                                    packed_pad_value=float(self.padding_value))
         prog.bufs['mel_len'].copy_(mel_len)
         out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, pre, None, 0, dur,
                                            batch['pitch'].to(x.device), batch['energy'].to(x.device), cum, lens, M,
@@ -269,7 +274,7 @@ class ForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError('generate(): all rounded durations are zero -- nothing to synthesise')
         pre = tok_prog.bufs['prenet.h']
         C = pre.shape[1]
-        prog = self._program(st, ('frame', B, M), lambda M: _accel.build_frame_program(h, packs, B, M, C, self.n_mels))
+        prog = _accel.frame_program(self, st, 'frame', tok_prog, B, M, C, self.n_mels)
         return _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, None, 0, dur_hat, pitch_hat, energy_hat,
                                             cum, lens, M, float(self.pitch_strength), float(self.energy_strength))
 

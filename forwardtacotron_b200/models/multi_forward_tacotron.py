@@ -294,6 +294,11 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             # the callbacks do not depend on the regulated length: they are enqueued while the scan result travels to the host
             pitch_hat = pitch_function(prog.bufs['pitch.y'].reshape(B, 1, T).clone())
             energy_hat = energy_function(prog.bufs['energy.y'].reshape(B, 1, T).clone())
+            pre, C2 = prog.bufs['prenet.h'], self.speaker_emb_dims
+            if _accel.token_x_supported(st['packs'], pre.shape[1] + C2):
+                # the BiLSTM's x-projection per phoneme does not depend on the regulated length either
+                _accel.token_xproj(st['handle'], st['packs'], prog, pre, prog.bufs['semb'], C2, pitch_hat, energy_hat,
+                                   float(self.pitch_strength), float(self.energy_strength))
             scan = pending.finish()
             return self._mel_from_prenet(st, prog, dur_hat, pitch_hat, energy_hat, pitch_cond_hat, scan)
 
@@ -325,8 +330,8 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
                                'pack_padded_sequence requires (multi_forward_tacotron.py:222)')
         pre = tok.bufs['prenet.h']
         C1, C2 = pre.shape[1], self.speaker_emb_dims
-        prog = self._program(st, ('frame_packed', B, M), lambda M: _accel.build_frame_program(
-            st['handle'], st['packs'], B, M, C1 + C2, self.n_mels, packed_pad_value=float(self.padding_value)))
+        prog = _accel.frame_program(self, st, 'frame_packed', tok, B, M, C1 + C2, self.n_mels,
+                                    packed_pad_value=float(self.padding_value))
         prog.bufs['mel_len'].copy_(mel_len)
         out = _accel.gather_and_run_frames(st['handle'], st['packs'], tok, prog, pre, tok.bufs['semb'], C2, dur,
                                            batch['pitch'].to(x.device), batch['energy'].to(x.device), cum, lens, M,
@@ -360,8 +365,7 @@ class MultiForwardTacotron(nn.Module, _accel.AcceleratedMixin):
             raise RuntimeError('generate(): all rounded durations are zero -- nothing to synthesise')
         pre = tok_prog.bufs['prenet.h']
         C1, C2 = pre.shape[1], self.speaker_emb_dims
-        prog = self._program(st, ('frame', B, M),
-                             lambda M: _accel.build_frame_program(h, packs, B, M, C1 + C2, self.n_mels))
+        prog = _accel.frame_program(self, st, 'frame', tok_prog, B, M, C1 + C2, self.n_mels)
         out = _accel.gather_and_run_frames(h, packs, tok_prog, prog, pre, tok_prog.bufs['semb'], C2, dur_hat,
                                            pitch_hat, energy_hat, cum, lens, M,
                                            float(self.pitch_strength), float(self.energy_strength))

@@ -36,7 +36,8 @@ class RnnProblem(C.Structure):
     _fields_ = [('cell', C.c_int32), ('hidden', C.c_int32), ('batch', C.c_int32), ('seq_len', C.c_int32),
                 ('seq_stride', C.c_int32), ('xproj', _fp), ('w_hh', _fp), ('b_hh', _fp), ('out', _fp),
                 ('out_ld', C.c_int32), ('out_col0', C.c_int32), ('lens', _fp), ('pad_value', C.c_float),
-                ('out_f16', C.c_int32), ('x_f16', C.c_int32), ('precise', C.c_int32)]
+                ('out_f16', C.c_int32), ('x_f16', C.c_int32), ('precise', C.c_int32),
+                ('x_idx', _fp)]
 
 
 class CbhgTailProblem(C.Structure):
@@ -80,7 +81,7 @@ SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_
            'ftb_cbhg_tail_plan_create', 'ftb_cbhg_tail_plan_run', 'ftb_cbhg_tail_plan_set_geometry',
            'ftb_cbhg_tail_plan_destroy',
            'ftb_rnn_plan_create', 'ftb_rnn_plan_run', 'ftb_rnn_plan_destroy', 'ftb_rnn_plan_info',
-           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
+           'ftb_lr_scan', 'ftb_lr_gather', 'ftb_lr_index', 'ftb_lr_regulate_static', 'ftb_embed', 'ftb_rowdot', 'ftb_embed_batch', 'ftb_rowdot_batch',
            'ftb_argmax_lastdim',
            'ftb_add_layernorm', 'ftb_posenc', 'ftb_mha', 'ftb_mha_split', 'ftb_stft', 'ftb_istft', 'ftb_gl_update']
 
@@ -119,6 +120,7 @@ def load_library() -> C.CDLL:
     lib.ftb_rnn_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_lr_scan.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_lr_gather.argtypes = [_fp, C.POINTER(LrGatherArgs), _fp]
+    lib.ftb_lr_index.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp]
     lib.ftb_lr_regulate_static.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
                                            _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_embed.argtypes = [_fp, _fp, _fp, C.c_int, _fp, _fp, C.c_int, _fp, C.c_int,
@@ -258,6 +260,12 @@ class Handle:
 
     def lr_gather(self, args: LrGatherArgs):
         self._timed('lr_gather', lambda: self.check(self.lib.ftb_lr_gather(self.h, C.byref(args), self.stream())))
+
+    def lr_index(self, cum, lens, batch, T, M, idx, row_stride=0, pad_row=-1):
+        """Frame -> row map of the LengthRegulator (dense int32 [batch, M]): b * row_stride + phoneme, `pad_row` for the
+        padded frames (defaults: the bare frame -> phoneme map, -1 = padded)."""
+        self._timed('lr_index', lambda: self.check(self.lib.ftb_lr_index(
+            self.h, ptr(cum), ptr(lens), batch, T, M, int(row_stride), int(pad_row), ptr(idx), self.stream())))
 
     def lr_regulate_static(self, x, x_stride, c, dur, batch, T, apply_fallback, M, out, out_stride,
                            idx=None, lens_out=None, meta_out=None):

@@ -215,6 +215,14 @@ typedef struct {
                             instead of 2^-11), the gates use ex2/rcp instead of tanh.approx, `out` receives the
                             unrounded fp32 h_t.  For the duration predictors, whose output is rounded to integers
                             (forward_tacotron.py:174-177); needs the cluster hand-off (else FTB_E_RESIDENT)      */
+  const int32_t* x_idx;  /* optional [batch, seq_len] (dense, row stride = seq_len): step t of sentence b reads row
+                            x_idx[b, t] of `xproj` (an absolute row index, >= 0) instead of row b * seq_stride + t.
+                            With it the recurrence consumes the LengthRegulator's output WITHOUT it ever being
+                            written: W_ih x + b_ih is a per-row map, so it commutes with the regulator's row
+                            repetition (common_layers.py:21) -- `xproj` is then computed once per PHONEME (half the
+                            projection work at two frames per phoneme), x_idx is the frame -> row map ftb_lr_index
+                            writes, and the padded frames (common_layers.py:23) point at one extra row that holds
+                            b_ih, the projection of a zero row.  null = rows b * seq_stride + t as described above  */
 } ftb_rnn_problem;
 
 #define FTB_MAX_RNN_PROBLEMS 8
@@ -264,6 +272,15 @@ typedef struct {
   int32_t round_tf32;                             /* 0 as computed, 1 tf32-rounded, 2 = `out` is fp16 (out_ld in halves) */
 } ftb_lr_gather_args;
 int ftb_lr_gather(ftb_handle h, const ftb_lr_gather_args* args, void* stream);
+/* Frame -> row map of LengthRegulator.forward (common_layers.py:21: repeat_interleave(x[i], rep)): with t = the token
+ * whose frames include m (cum[b, t-1] <= m < cum[b, t]; cum = the inclusive cumsum ftb_lr_scan wrote),
+ *   idx[b, m] = b * row_stride + t     for m < lens[b]
+ *   idx[b, m] = pad_row                for the padded frames m >= lens[b] (pad_sequence, common_layers.py:23)
+ * idx is dense [batch, M].  row_stride = 0, pad_row = -1 gives the bare frame -> phoneme map; row_stride = the token
+ * stride of a padded-flat buffer gives absolute rows: the map ftb_lr_gather applies, without the copy -- the input of
+ * ftb_rnn_problem.x_idx. */
+int ftb_lr_index(ftb_handle h, const int32_t* cum, const int32_t* lens, int batch, int T, int M, int row_stride,
+                 int pad_row, int32_t* idx, void* stream);
 
 /* No-allocation LengthRegulator: ftb_lr_scan + ftb_lr_gather (fp32 output, no projection / speaker tail) as ONE call
  * whose intermediates (cum, lens, meta) live in a file-scope `static __device__` array of the library instead of

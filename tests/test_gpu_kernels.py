@@ -639,6 +639,100 @@ def test_fft_glue_fp16_operand_outputs():
         assert float(prog.bufs[b].view(g.batch, g.stride, -1)[:, L:].abs().max()) == 0.0
 
 
+@pytest.mark.parametrize('tag', ['zero_row', 'ties', 'all2'])
+def test_lr_index_matches_reference_map(tag):
+    """ftb_lr_index: the frame -> phoneme map of LengthRegulator.forward (common_layers.py:21-23) without the copy, on
+    the reference goldens' durations (ties, zero durations, a zero-length sentence): bit-exact against the numpy oracle's
+    idx (itself pinned to the reference's output on these files), and in its absolute-row form."""
+    g = load_golden(f'lr_{tag}')
+    h = _handle()
+    dur = torch.from_numpy(g['dur']).to(DEV).contiguous()
+    B, T = dur.shape
+    _, idx_ref, lens_ref, _ = O.length_regulate_np(g['x'], g['dur'])
+    want = torch.from_numpy(idx_ref).to(torch.int32)
+    M = want.shape[1]
+    cum = torch.empty((B, T), dtype=torch.int32, device=DEV)
+    lens = torch.empty((B,), dtype=torch.int32, device=DEV)
+    meta = torch.empty((4,), dtype=torch.int32, device=DEV)
+    h.lr_scan(dur, B, T, False, cum, lens, meta)
+    idx = torch.full((B, M), -7, dtype=torch.int32, device=DEV)
+    h.lr_index(cum, lens, B, T, M, idx)
+    torch.cuda.synchronize()
+    assert torch.equal(idx.cpu(), want)
+    h.lr_index(cum, lens, B, T, M, idx, row_stride=T + 8, pad_row=B * (T + 8))
+    torch.cuda.synchronize()
+    rows = torch.where(want >= 0, want + torch.arange(B, dtype=torch.int32)[:, None] * (T + 8),
+                       torch.full_like(want, B * (T + 8)))
+    assert torch.equal(idx.cpu(), rows)
+    # gathering the source rows through the map reproduces the reference's LengthRegulator output bit for bit
+    x = torch.from_numpy(g['x'])
+    src = torch.cat([torch.nn.functional.pad(x, (0, 0, 0, 8)).reshape(B * (T + 8), -1), torch.zeros(1, x.shape[2])])
+    assert np.array_equal(src[idx.cpu().long()].numpy().view(np.uint32), g['out'].view(np.uint32))
+
+
+@pytest.mark.parametrize('cell,H,B,T', [('lstm', 512, 5, 23), ('lstm', 512, 40, 9), ('lstm', 512, 20, 17)])
+def test_recurrence_reads_x_through_the_regulator_map(cell, H, B, T, monkeypatch):
+    """ftb_rnn_problem.x_idx: the recurrence over the regulated sequence, its x-projection computed once per PHONEME and
+    read through the frame -> row map (pad frames -> the b_ih row), is BIT-IDENTICAL to the recurrence over the
+    materialised LengthRegulator output with a frame-level projection -- for both hand-off protocols."""
+    gen = torch.Generator().manual_seed(3 * H + B)
+    In = 64
+    rnn = (torch.nn.GRU if cell == 'gru' else torch.nn.LSTM)(In, H, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for p in rnn.parameters():
+            p.copy_((torch.rand(p.shape, generator=gen) * 2 - 1) / H ** 0.5)
+    packed = pk.PackedRnn(rnn.to(DEV))
+    h = _handle()
+    dur = (torch.rand(B, T, generator=gen) * 4 - 0.5).to(DEV).contiguous()
+    dur[B // 2, T // 2:] = 0.0                                         # a short sentence: padded frames behind it
+    cum = torch.empty((B, T), dtype=torch.int32, device=DEV)
+    lens = torch.empty((B,), dtype=torch.int32, device=DEV)
+    meta = torch.empty((4,), dtype=torch.int32, device=DEV)
+    h.lr_scan(dur, B, T, False, cum, lens, meta)
+    M = int(meta.cpu()[0])
+    xv = torch.randn(B, T, In, generator=gen).to(torch.float16)
+    results = {}
+    for mode in ('cluster', 'l2'):
+        monkeypatch.setenv('FTB_RNN_HANDOFF', mode)
+        # (a) per-phoneme projection + map
+        tokp = eng.Program(h, eng.Geometry(B, T))
+        a = tokp.buf('a', In, torch.float16)
+        a.view(B, tokp.geo.stride, In)[:, :T] = xv.to(DEV)
+        xproj = tokp.dense('xproj', (tokp.geo.cap_rows + 1, packed.ih.n), torch.float16)
+        xproj[tokp.geo.cap_rows] = packed.ih.bias0.to(torch.float16)
+        tokp.gemm(a, packed.ih, xproj, round_out=False)
+        tokp.flush()
+        tokp.run()
+        fr = eng.Program(h, eng.Geometry(B, M))
+        fr.dense('x_idx', (B, -1), torch.int32)
+        h.lr_index(cum, lens, B, T, M, fr.bufs['x_idx'], row_stride=tokp.geo.stride, pad_row=tokp.geo.cap_rows)
+        out_a = fr.buf('h', 2 * H, torch.float16)
+        fr.rnn([(packed, xproj, out_a, 0, dict.__getitem__(fr.bufs, 'x_idx'))])
+        fr.run()
+        # (b) materialised regulator output + frame-level projection
+        fr2 = eng.Program(h, eng.Geometry(B, M))
+        lr = fr2.buf('lr', In, torch.float16)
+        g = rt.LrGatherArgs()
+        g.x, g.x_stride, g.x_ld, g.c1, g.c2 = a.data_ptr(), tokp.geo.stride, In, In, 0
+        xf = a.float()                                                  # the gather reads fp32 rows
+        g.x = xf.data_ptr()
+        g.cum, g.lens, g.batch, g.T, g.M = cum.data_ptr(), lens.data_ptr(), B, T, M
+        g.out, g.out_stride, g.out_ld, g.idx, g.round_tf32 = lr.data_ptr(), fr2.geo.stride, In, None, 2
+        h.lr_gather(g)
+        xp2 = fr2.buf('xp', packed.ih.n, torch.float16)
+        out_b = fr2.buf('h', 2 * H, torch.float16)
+        fr2.gemm(lr, packed.ih, xp2, round_out=False)
+        fr2.rnn([(packed, xp2, out_b, 0)])
+        fr2.run()
+        torch.cuda.synchronize()
+        assert fr.h.rnn_info(fr._rnn_plans[0])['handoff'] == mode
+        assert torch.equal(fr.view('h'), fr2.view('h')), mode
+        results[mode] = fr.view('h').clone()
+        for pr in (tokp, fr, fr2):
+            pr.close()
+    assert torch.equal(results['cluster'], results['l2'])
+
+
 def test_embed_and_heads_batched_match_single_and_torch():
     """ftb_embed_batch / ftb_rowdot_batch == the single-item entry points == torch (forward_tacotron.py:31,38-39)."""
     h = _handle()

@@ -90,8 +90,13 @@ def test_forward_tacotron_generate_vs_reference_golden(name):
     _mel_checked(model, (x,), out, g, ties)
 
 
-def test_generate_mel_teacher_forced_intermediates():
-    """Stage-level check with the reference's own dur/pitch/energy (decouples rounding ties) + taps."""
+@pytest.mark.parametrize('tokens_x', [True, False])
+def test_generate_mel_teacher_forced_intermediates(tokens_x, monkeypatch):
+    """Stage-level check with the reference's own dur/pitch/energy (decouples rounding ties) + taps.  tokens_x: the
+    BiLSTM's x-projection per phoneme, read through the frame -> row map (the LengthRegulator's output is never written:
+    its tap is rebuilt from the per-phoneme rows and the map); False: the materialised LengthRegulator output."""
+    from forwardtacotron_b200 import engine as eng
+    monkeypatch.setattr(eng, 'XPROJ_TOKENS', tokens_x)
     g = load_golden('ft_spread_b3_t40')
     sd = synthetic_sd('forward_tacotron', int(g['seed']))
     model = _model('forward_tacotron', sd)
@@ -106,7 +111,18 @@ def test_generate_mel_teacher_forced_intermediates():
     frame = model.program_for('frame', B, M)
     assert rel_l2(tok.view('prenet.proj1').cpu(), g['tap_prenet_conv_project1'].transpose(0, 2, 1)) < 1e-3
     assert rel_l2(tok.view('prenet.h').cpu(), g['tap_prenet']) < 1e-3
-    assert rel_l2(frame.view('lr').cpu(), g['tap_lr']) < 1e-3
+    if tokens_x:
+        assert 'lr' not in frame.bufs
+        xp = tok.xprog
+        idx = frame.bufs['x_idx'].cpu().long()                                   # [B, M] absolute rows, pad row = cap_rows
+        rows = torch.cat([xp.bufs['h_tok'].float().cpu(), torch.zeros(1, xp.bufs['h_tok'].shape[1])])[:xp.pad_row + 1]
+        rows[xp.pad_row] = 0.0
+        lr = rows[idx]                                                           # what the regulator would have written
+        want_idx = torch.from_numpy(g['tap_lr']).abs().sum(-1) > 0               # padded frames are zero rows
+        assert torch.equal(idx != xp.pad_row, want_idx)
+        assert rel_l2(lr, g['tap_lr']) < 1e-3
+    else:
+        assert rel_l2(frame.view('lr').cpu(), g['tap_lr']) < 1e-3
     assert rel_l2(frame.view('lstm.h').cpu(), g['tap_lstm']) < 1e-3
     assert rel_l2(frame.view('postnet.h').cpu(), g['tap_postnet']) < 1e-3
     for k in ('mel', 'mel_post'):
