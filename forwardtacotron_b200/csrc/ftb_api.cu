@@ -58,12 +58,49 @@ extern "C" int ftb_destroy(ftb_handle h) {
   for (auto& kv : h->gemm_plans) gemm_plan_free(kv.second);
   for (auto& kv : h->rnn_plans) rnn_plan_free(kv.second);
   for (auto& kv : h->tail_plans) tail_plan_free(kv.second);
+  for (auto& kv : h->graphs) cudaGraphExecDestroy(kv.second);
   cudaFree(h->err_word);
   delete h;
   return 0;
 }
 
 extern "C" int64_t ftb_launch_count(ftb_handle h) { return h ? h->launches : -1; }
+
+extern "C" int ftb_graph_capture_begin(ftb_handle h, void* stream) {
+  if (!h || !stream) return FTB_E_ARG;             // the legacy default stream cannot be captured
+  return static_cast<int>(cudaStreamBeginCapture(static_cast<cudaStream_t>(stream), cudaStreamCaptureModeThreadLocal));
+}
+
+extern "C" int ftb_graph_capture_end(ftb_handle h, void* stream, int* graph_out) {
+  if (!h || !stream || !graph_out) return FTB_E_ARG;
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(static_cast<cudaStream_t>(stream), &graph);
+  if (ce != cudaSuccess) { cudaGetLastError(); return static_cast<int>(ce); }
+  cudaGraphExec_t exec = nullptr;
+  ce = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ce != cudaSuccess) { cudaGetLastError(); return static_cast<int>(ce); }
+  const int id = h->next_plan++;
+  h->graphs[id] = exec;
+  *graph_out = id;
+  return 0;
+}
+
+extern "C" int ftb_graph_launch(ftb_handle h, int graph, void* stream) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->graphs.find(graph);
+  if (it == h->graphs.end()) return FTB_E_PLAN;
+  return static_cast<int>(cudaGraphLaunch(it->second, static_cast<cudaStream_t>(stream)));
+}
+
+extern "C" int ftb_graph_destroy(ftb_handle h, int graph) {
+  if (!h) return FTB_E_ARG;
+  auto it = h->graphs.find(graph);
+  if (it == h->graphs.end()) return FTB_E_PLAN;
+  cudaGraphExecDestroy(it->second);
+  h->graphs.erase(it);
+  return 0;
+}
 
 extern "C" int ftb_gemm_plan_create(ftb_handle h, const ftb_gemm_problem* problems, int nproblems, int* plan_out) {
   if (!h || !plan_out) return FTB_E_ARG;

@@ -158,4 +158,5 @@ struct ftb_context {
   std::map<int, ftb::GemmPlan> gemm_plans;
   std::map<int, ftb::RnnPlan> rnn_plans;
   std::map<int, ftb::TailPlan> tail_plans;
+  std::map<int, cudaGraphExec_t> graphs;
 };

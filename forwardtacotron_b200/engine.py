@@ -43,6 +43,8 @@ FOLD_TAPS = os.environ.get('FTB_FOLD_TAPS', '1') != '0'
 # (ftb_rnn_problem.x_idx): the regulated sequence is never written and W_ih runs over T instead of M rows.
 # FTB_XPROJ_TOKENS=0 restores the materialised LengthRegulator output + frame-level projection.
 XPROJ_TOKENS = os.environ.get('FTB_XPROJ_TOKENS', '1') != '0'
+# CUDA graphs through the library's own stream capture (ftb_graph_*); FTB_NATIVE_GRAPHS=0: torch.cuda.CUDAGraph
+NATIVE_GRAPHS = os.environ.get('FTB_NATIVE_GRAPHS', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -128,6 +130,7 @@ class Program:
         self.use_graph = os.environ.get('FTB_CUDA_GRAPHS', '1') != '0'
         self._graphs: Dict[tuple, object] = {}        # (launch-time scalars, seq_len) -> captured graph
         self._baked_len = False                       # a glue kernel takes seq_len as a kernel ARGUMENT
+        self._torch_steps = False                     # a step runs torch operators (see call())
         self._eager_runs = 0
 
     # ---- buffers ---------------------------------------------------------------------------
@@ -378,9 +381,13 @@ class Program:
                           'flops_row': per_row, 'flops_f16_row': per_row, 'bytes_row': brow, 'bytes_fixed': wbytes,
                           'cta_pairs': False, 'slots': (g.rows + 127) // 128, 'fused_tail': True})
 
-    def call(self, fn: Callable[[], None], label: str = 'glue', nbytes: float = 0.0):
+    def call(self, fn: Callable[[], None], label: str = 'glue', nbytes: float = 0.0, torch_ops: bool = False):
+        """A step that is not a plan: a C-ABI call, or (torch_ops) torch operators -- those allocate through torch's
+        caching allocator, so a program that holds one is captured with torch.cuda.graph instead of the library's own
+        stream capture."""
         self.flush()
         self._baked_len = True
+        self._torch_steps = self._torch_steps or torch_ops
         self.steps.append(fn)
         self.info.append({'kind': 'glue', 'label': label, 'flops': 0.0, 'bytes': nbytes})
 
@@ -406,7 +413,7 @@ class Program:
         graph = self._graphs.get(key)
         if graph is not None:
             self.h.replayed_launches += self._launches_per_run     # kernels inside the replayed graph
-            return graph.replay()
+            return self.h.graph_launch(graph) if isinstance(graph, int) else graph.replay()
         if self._eager_runs < 1:
             self._eager_runs += 1
             n0 = self.h.launch_count()
@@ -414,11 +421,16 @@ class Program:
             self._launches_per_run = self.h.launch_count() - n0
             return
         try:
-            graph = torch.cuda.CUDAGraph()
             side = torch.cuda.Stream(self.device)
             side.wait_stream(torch.cuda.current_stream(self.device))
-            with torch.cuda.graph(graph, stream=side):
-                self.run_eager()
+            if self._torch_steps or not NATIVE_GRAPHS:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=side):
+                    self.run_eager()
+            else:
+                # the library's own stream capture (ftb_graph_*): a torch.cuda.CUDAGraph replay prepends two one-element
+                # fill kernels for its generator state (~8 us of stream time, three replays per generate())
+                graph = self.h.graph_capture(self.run_eager, side)
             torch.cuda.current_stream(self.device).wait_stream(side)
         except Exception as exc:                              # capture unsupported: stay on eager launches
             import warnings
@@ -426,9 +438,12 @@ class Program:
             self.use_graph = False
             return self.run_eager()
         while len(self._graphs) >= 8:                         # a few distinct lengths / scalars stay captured
-            self._graphs.pop(next(iter(self._graphs)))
+            old = self._graphs.pop(next(iter(self._graphs)))
+            if isinstance(old, int):
+                self.h.graph_destroy(old)
         self._graphs[key] = graph
-        return graph.replay()          # (the capture pass already counted these launches once in the C counter)
+        # (the capture pass already counted these launches once in the C counter)
+        return self.h.graph_launch(graph) if isinstance(graph, int) else graph.replay()
 
     def run_timed(self):
         """Like run(), with a CUDA-event pair around every launch on the current stream.
@@ -455,6 +470,9 @@ class Program:
         for p in self._tail_plans:
             self.h.tail_destroy(p)
         self._tail_plans = []
+        for g in self._graphs.values():
+            if isinstance(g, int):
+                self.h.graph_destroy(g)
         self._graphs = {}
         self._gemm_plans, self._rnn_plans, self.steps = [], [], []
 

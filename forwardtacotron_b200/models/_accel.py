@@ -267,7 +267,7 @@ def build_frame_program(handle: rt.Handle, packs: dict, batch: int, M: int, in_c
                 sp[:, L:] = 0
         seg = pk.ceil_to(n_mels, 8)
         mel_split = prog.buf('mel_split', 3 * seg, torch.float16) if packs['postnet'].bank[0].w_src is not None else None
-        prog.call(fix_pad_rows, label='lin.pad_rows')
+        prog.call(fix_pad_rows, label='lin.pad_rows', torch_ops=True)
     else:
         mel_split = None
     prog.label('')

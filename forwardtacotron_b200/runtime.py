@@ -76,6 +76,7 @@ class LrGatherArgs(C.Structure):
 
 # every symbol include/ftb200.h declares (tests check that the .so exports all of them)
 SYMBOLS = ['ftb_version', 'ftb_error_string', 'ftb_create', 'ftb_destroy', 'ftb_launch_count',
+           'ftb_graph_capture_begin', 'ftb_graph_capture_end', 'ftb_graph_launch', 'ftb_graph_destroy',
            'ftb_gemm_plan_create', 'ftb_gemm_plan_run', 'ftb_gemm_plan_destroy', 'ftb_gemm_plan_info',
            'ftb_gemm_plan_set_geometry', 'ftb_rnn_plan_set_geometry',
            'ftb_cbhg_tail_plan_create', 'ftb_cbhg_tail_plan_run', 'ftb_cbhg_tail_plan_set_geometry',
@@ -120,6 +121,10 @@ def load_library() -> C.CDLL:
     lib.ftb_rnn_plan_info.argtypes = [_fp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.ftb_lr_scan.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
     lib.ftb_lr_gather.argtypes = [_fp, C.POINTER(LrGatherArgs), _fp]
+    lib.ftb_graph_capture_begin.argtypes = [_fp, _fp]
+    lib.ftb_graph_capture_end.argtypes = [_fp, _fp, C.POINTER(C.c_int)]
+    lib.ftb_graph_launch.argtypes = [_fp, C.c_int, _fp]
+    lib.ftb_graph_destroy.argtypes = [_fp, C.c_int]
     lib.ftb_lr_index.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _fp, _fp]
     lib.ftb_lr_regulate_static.argtypes = [_fp, _fp, C.c_int, C.c_int, C.c_int, _fp, C.c_int, C.c_int, C.c_int, C.c_int,
                                            _fp, C.c_int, C.c_int, _fp, _fp, _fp, _fp]
@@ -253,6 +258,27 @@ class Handle:
         fn()
         b.record()
         self.timing.append((name, a, b))
+
+    def graph_capture(self, fn, stream: 'torch.cuda.Stream') -> int:
+        """Run fn() with `stream` current and under capture; returns the id of the instantiated graph."""
+        with torch.cuda.stream(stream):
+            self.check(self.lib.ftb_graph_capture_begin(self.h, C.c_void_p(stream.cuda_stream)))
+            try:
+                fn()
+            except Exception:
+                gid = C.c_int(0)
+                if self.lib.ftb_graph_capture_end(self.h, C.c_void_p(stream.cuda_stream), C.byref(gid)) == 0:
+                    self.lib.ftb_graph_destroy(self.h, gid.value)
+                raise
+            gid = C.c_int(0)
+            self.check(self.lib.ftb_graph_capture_end(self.h, C.c_void_p(stream.cuda_stream), C.byref(gid)))
+        return gid.value
+
+    def graph_launch(self, gid: int):
+        self.check(self.lib.ftb_graph_launch(self.h, gid, self.stream()))
+
+    def graph_destroy(self, gid: int):
+        self.lib.ftb_graph_destroy(self.h, gid)
 
     def lr_scan(self, dur, batch, T, apply_fallback, cum, lens, meta):
         self._timed('lr_scan', lambda: self.check(self.lib.ftb_lr_scan(

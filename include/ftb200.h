@@ -49,6 +49,17 @@ int ftb_destroy(ftb_handle h);
 /* number of kernels launched through this handle since creation (bench.py's gpu_launches) */
 int64_t ftb_launch_count(ftb_handle h);
 
+/* Launch lists as CUDA graphs (plumbing; no counterpart in the reference, whose modules launch eagerly).  Everything the
+ * entry points of this header enqueue on `stream` between ftb_graph_capture_begin and ftb_graph_capture_end -- the
+ * cluster / cooperative launches of a recurrence plan and their side-stream forks included -- becomes one executable
+ * graph; ftb_graph_launch replays it on any stream.  Capture mode is thread-local; `stream` must not be the legacy
+ * default stream.  (torch.cuda.CUDAGraph does the same but prepends two one-element fill kernels to every replay for its
+ * random-number generator state: ~8 us of stream time per replay, three replays per generate().) */
+int ftb_graph_capture_begin(ftb_handle h, void* stream);
+int ftb_graph_capture_end(ftb_handle h, void* stream, int* graph_out);
+int ftb_graph_launch(ftb_handle h, int graph, void* stream);
+int ftb_graph_destroy(ftb_handle h, int graph);
+
 /* ------------------------------------------------------------------------------------
  * K1/K2  implicit-GEMM convolution / linear with fused epilogue   (tcgen05 + TMEM + TMA)
  *
