@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libftb200.so')
-SOURCES = ['ftb_api.cu', 'ftb_gemm.cu', 'ftb_rnn.cu', 'ftb_lr.cu', 'ftb_misc.cu', 'ftb_fft.cu', 'ftb_tail.cu', 'ftb_attn.cu', 'ftb_gl.cu']
+SOURCES = ['ftb_api.cu', 'ftb_gemm.cu', 'ftb_rnn.cu', 'ftb_lr.cu', 'ftb_misc.cu', 'ftb_fft.cu', 'ftb_tail.cu', 'ftb_attn.cu', 'ftb_attn5.cu', 'ftb_gl.cu']
 HEADERS = ['ftb_internal.h', 'ftb_ptx.cuh', os.path.join('..', '..', 'include', 'ftb200.h')]
 # fast-math is deliberately NOT enabled: the gate math needs accurate expf/tanhf.
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',

@@ -11,6 +11,7 @@
 // mma.sync.m16n8k16 (legacy tensor-core path): the operands of both products are produced by the same thread in
 // registers (P) or change every tile (K, V) and the M tile is 16 rows per warp, which is what this instruction is for;
 // a tcgen05 version would need P staged through shared memory per key tile.
+#include <cstdlib>
 #include <cuda_fp16.h>
 
 #include "ftb_internal.h"
@@ -250,6 +251,7 @@ extern "C" int ftb_mha_split(ftb_handle h, const void* qkv16, int e, int heads, 
   dim3 grid((seq_len + 63) / 64, heads, batch);
   cudaError_t ce = cudaSuccess;
   static bool attr64 = false, attr128 = false;
+  static const bool tc5 = [] { const char* v = getenv("FTB_ATTN_TC5"); return !(v && v[0] == '0'); }();
   if (d == 64) {
     if (!attr64) {
       ce = cudaFuncSetAttribute(mha_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, mha_tc_smem<64>());
@@ -258,6 +260,10 @@ extern "C" int ftb_mha_split(ftb_handle h, const void* qkv16, int e, int heads, 
     }
     mha_tc_kernel<64><<<grid, 128, mha_tc_smem<64>(), st>>>(static_cast<const __half*>(qkv16), e, key_tok, seq_len,
                                                             seq_stride, out, round_tf32);
+  } else if (d == 128 && tc5) {
+    // head width 128 (FastPitch pre / postnet): the tcgen05 kernel (ftb_attn5.cu); FTB_ATTN_TC5=0 keeps mma.sync
+    const int rc = mha_tc5_launch(qkv16, e, heads, key_tok, batch, seq_len, seq_stride, out, round_tf32, st);
+    if (rc) return rc;
   } else if (d == 128) {
     if (!attr128) {
       ce = cudaFuncSetAttribute(mha_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, mha_tc_smem<128>());

@@ -63,6 +63,9 @@ void gemm_plan_free(GemmPlan& plan);
 
 // 2-D row-major [rows, cols] fp32 or fp16 tensor map (leading dimension ld elements), box {128 bytes, box_rows}, 128B swizzle
 int tensor_map_2d(CUtensorMap* m, const void* base, long long rows, int cols, int ld, int box_rows, bool f16);
+// K8u (ftb_attn5.cu): split-precision attention on tcgen05, head width 128
+int mha_tc5_launch(const void* qkv16, int e, int heads, const int64_t* key_tok, int batch, int seq_len, int seq_stride,
+                   float* out, int round, cudaStream_t st);
 
 // ------------------------------------------------------------------ fused CBHG tail (ftb_tail.cu)
 struct alignas(128) TailProblemDev {
