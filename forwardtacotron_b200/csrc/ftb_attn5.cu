@@ -10,12 +10,15 @@
 //   warp 1      : MMA issuer     S[128 q x 64 keys] into one of two TMEM buffers (24 x tcgen05.mma M128 N64 K16, all K-major);
 //                                O[128 q x 128 d] += P V (12 x M128 N128 K16; A = the P tile the softmax warps wrote to shared
 //                                memory, B = the V tile as loaded: keys x d with d contiguous = an MN-major operand)
-//   warps 2..5  : softmax        thread = query row = TMEM lane: row max / row sum need no shuffles
+//   warps 2..9  : softmax        thread = (query row = TMEM lane, 32 of the tile's 64 keys): row shift / row sum need no shuffles
 //
-// TWO PASSES over the keys instead of an online softmax: pass 1 computes S and keeps the row maxima, pass 2 computes S again
-// (same instructions, same bits), P = exp2(S - max), O += P V.  The accumulator O then never has to be rescaled -- in TMEM
-// that would be a load / multiply / store round trip of 128 x 128 fp32 per key tile -- at the price of the S product twice,
-// which at tcgen05 rates is the cheap side: 24 + 24 + 12 MMAs per key tile against the 384 HMMAs per warp of the old kernel.
+// TWO PASSES over the keys instead of an online softmax: pass 1 keeps a row-wise shift m, pass 2 computes S, P =
+// exp2(S - m), O += P V.  The accumulator O then never has to be rescaled -- in TMEM that would be a load / multiply / store
+// round trip of 128 x 128 fp32 per key tile.  softmax is invariant under the shift, so m need not be the exact maximum:
+// pass 1 runs the Qh Kh^T product alone (8 MMAs and the K hi boxes per tile; its maximum is within ~1e-2 of the true one,
+// which only has to keep exp2 in range), pass 2 the three products: 8 + 24 + 12 MMAs per key tile against the 384 HMMAs per
+// warp of the old kernel.  Two softmax warpgroups split the 64 keys of a tile (both read the same TMEM lanes); their
+// partial row sums and shifts meet in shared memory.
 #include <cuda_fp16.h>
 
 #include "ftb_internal.h"
@@ -31,7 +34,7 @@ constexpr int A5_KBOX = A5_KT * 128;         // one [64 rows x 64 fp16] box: 8 K
 constexpr int A5_Q_BYTES = 4 * A5_QBOX;      // Q hi (d 0-63, d 64-127), Q lo (same)
 constexpr int A5_STAGE = 8 * A5_KBOX;        // K hi (2 boxes), K lo (2), V hi (2), V lo (2): 64 KB
 constexpr int A5_P_BYTES = 2 * A5_QBOX;      // P hi, P lo: [128 q x 64 keys] each
-constexpr int A5_THREADS = 192;
+constexpr int A5_THREADS = 320;            // producer, MMA issuer, 2 softmax warpgroups of 4 warps
 
 struct A5Smem {
   uint64_t q_full;
@@ -41,6 +44,7 @@ struct A5Smem {
   uint64_t o_full;
   uint32_t tmem_base;
   uint32_t pad;
+  float xch[2][A5_QT];                       // row shift (pass 1) / row sum (pass 2) of each softmax warpgroup
 };
 constexpr int A5_SMEM_BYTES = A5_Q_BYTES + 2 * A5_STAGE + A5_P_BYTES + static_cast<int>(sizeof(A5Smem)) + 1024;
 static_assert(A5_SMEM_BYTES <= 232448, "over the 227 KB shared-memory limit");
@@ -85,9 +89,9 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
     mbar_init(&sm->q_full, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&sm->kv_full[i], 1); mbar_init(&sm->kv_empty[i], 1);
-      mbar_init(&sm->s_full[i], 1); mbar_init(&sm->s_empty[i], 4);
+      mbar_init(&sm->s_full[i], 1); mbar_init(&sm->s_empty[i], 8);
     }
-    mbar_init(&sm->p_full, 4);
+    mbar_init(&sm->p_full, 8);
     mbar_init(&sm->p_free, 1);
     mbar_init(&sm->o_full, 1);
     fence_mbar_init();
@@ -111,9 +115,9 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
           const int stage = it & 1;
           mbar_wait(&sm->kv_empty[stage], ((it >> 1) & 1u) ^ 1u);
           uint8_t* st = kv_s + stage * A5_STAGE;
-          mbar_expect_tx(&sm->kv_full[stage], (pass ? 8 : 4) * A5_KBOX);
+          mbar_expect_tx(&sm->kv_full[stage], (pass ? 8 : 2) * A5_KBOX);
           const int r = row0 + j * A5_KT;
-          for (int half = 0; half < 2; ++half)
+          for (int half = 0; half < (pass ? 2 : 1); ++half)                  // pass 1: the hi boxes of K alone
             for (int box = 0; box < 2; ++box)
               tma_load_2d(st + (half * 2 + box) * A5_KBOX, &tm_kv, &sm->kv_full[stage], col_k + half * lo_off + box * 64, r);
           if (pass) {
@@ -132,12 +136,11 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       const uint32_t idesc_o = umma_idesc_f16(A5_QT, A5_D) | (1u << 16);        // B (the V tile) is MN-major
       const uint32_t q_base = smem_u32(q_s), p_base = smem_u32(p_s);
       // S[sb] = Qh Kh^T + Qh Kl^T + Ql Kh^T over d = 2 boxes x 4 k-steps of 16
-      auto issue_s = [&](int sb, int stage) {
+      auto issue_s = [&](int sb, int stage, int nprod) {
         const uint32_t k_base = smem_u32(kv_s + stage * A5_STAGE);
         const uint32_t d_tmem = tmem_base + sb * A5_KT;
         uint32_t acc = 0;
-#pragma unroll
-        for (int prod = 0; prod < 3; ++prod) {
+        for (int prod = 0; prod < nprod; ++prod) {
           const uint32_t qa = q_base + (prod == 2 ? 2 * A5_QBOX : 0);           // Q lo for the third product
           const uint32_t kb = k_base + (prod == 1 ? 2 * A5_KBOX : 0);           // K lo for the second
 #pragma unroll
@@ -170,13 +173,13 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       };
       mbar_wait(&sm->q_full, 0);
       uint32_t it = 0, sit = 0;
-      // ---- pass 1: S only (the softmax warps keep the row maxima)
+      // ---- pass 1: Qh Kh^T only (the softmax warps keep a row shift)
       for (int j = 0; j < n_tiles; ++j, ++it, ++sit) {
         const int stage = it & 1, sb = sit & 1;
         mbar_wait(&sm->kv_full[stage], (it >> 1) & 1u);
         mbar_wait(&sm->s_empty[sb], ((sit >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        issue_s(sb, stage);
+        issue_s(sb, stage, 1);
         umma_commit(&sm->kv_empty[stage]);
         umma_commit(&sm->s_full[sb]);
       }
@@ -187,7 +190,7 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
           mbar_wait(&sm->kv_full[stage], (it >> 1) & 1u);
           mbar_wait(&sm->s_empty[sb], ((sit >> 1) & 1u) ^ 1u);
           tc_fence_after();
-          issue_s(sb, stage);
+          issue_s(sb, stage, 3);
           umma_commit(&sm->s_full[sb]);
           ++it; ++sit;
         }
@@ -205,79 +208,72 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
     }
   } else {
     // ================================ softmax =====================================
+    // warps 2..5 = warpgroup 0 (keys 0-31 of every tile), warps 6..9 = warpgroup 1 (keys 32-63); warp w of either group reads
+    // TMEM lane quarter w % 4.  A thread owns one query row and 32 keys per tile.
     const int w = warp & 3;                                 // TMEM lane quarter of this warp
+    const int wg = (warp - 2) >> 2;                         // softmax warpgroup = key half
     const int row = w * 32 + lane;                          // query row of the tile = TMEM lane
-    const uint32_t tlane = tmem_base + (static_cast<uint32_t>(w * 32) << 16);
+    const uint32_t tlane = tmem_base + (static_cast<uint32_t>(w * 32) << 16) + wg * 32;
     const float scale_log2 = rsqrtf(static_cast<float>(A5_D)) * 1.4426950408889634f;
     const int64_t* tok = key_tok ? key_tok + static_cast<long long>(b) * seq_len : nullptr;
-    auto key_mask = [&](int j, unsigned& m0, unsigned& m1) {  // bit i of m0 / m1: key j*64 + i / + 32 + i takes part
-      const int k0 = j * A5_KT + lane, k1 = k0 + 32;
-      bool ok0 = k0 < seq_len, ok1 = k1 < seq_len;
-      if (tok) { if (ok0) ok0 = tok[k0] != 0; if (ok1) ok1 = tok[k1] != 0; }
-      m0 = __ballot_sync(0xffffffffu, ok0);
-      m1 = __ballot_sync(0xffffffffu, ok1);
+    auto key_mask = [&](int j) {                            // bit i: key j*64 + 32*wg + i takes part
+      const int k = j * A5_KT + wg * 32 + lane;
+      bool ok = k < seq_len;
+      if (tok && ok) ok = tok[k] != 0;
+      return __ballot_sync(0xffffffffu, ok);
     };
     uint32_t sit = 0;
     float mx = -INFINITY;
-    // ---- pass 1: row maxima
+    // ---- pass 1: row shift (the maximum of the hi x hi product)
     for (int j = 0; j < n_tiles; ++j, ++sit) {
       const int sb = sit & 1;
-      unsigned m0, m1;
-      key_mask(j, m0, m1);
+      const unsigned mk = key_mask(j);
       mbar_wait(&sm->s_full[sb], (sit >> 1) & 1u);
       tc_fence_after();
-      float v0[32], v1[32];
-      tmem_ld_32x32(tlane + sb * A5_KT, v0);
-      tmem_ld_32x32(tlane + sb * A5_KT + 32, v1);
+      float v[32];
+      tmem_ld_32x32(tlane + sb * A5_KT, v);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm->s_empty[sb]);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        if ((m0 >> i) & 1u) mx = fmaxf(mx, v0[i]);
-        if ((m1 >> i) & 1u) mx = fmaxf(mx, v1[i]);
-      }
+      for (int i = 0; i < 32; ++i)
+        if ((mk >> i) & 1u) mx = fmaxf(mx, v[i]);
     }
+    sm->xch[wg][row] = mx;
+    named_bar_sync(1, 256);                                 // the eight softmax warps
+    mx = fmaxf(mx, sm->xch[wg ^ 1][row]);
     const float mu = (mx == -INFINITY) ? 0.0f : mx * scale_log2;
-    // ---- pass 2: P = exp2(S * scale - max) as hi / lo fp16 into the swizzled K-major P tile
+    named_bar_sync(1, 256);                                 // everyone has read the shifts: xch is reused for the sums
+    // ---- pass 2: P = exp2(S * scale - shift) as hi / lo fp16 into the swizzled K-major P tile
     float l_sum = 0.0f;
     uint8_t* p_hi = p_s;
     uint8_t* p_lo = p_s + A5_QBOX;
     const uint32_t prow = static_cast<uint32_t>((row >> 3) * 1024 + (row & 7) * 128);
     for (int j = 0; j < n_tiles; ++j, ++sit) {
       const int sb = sit & 1;
-      unsigned m0, m1;
-      key_mask(j, m0, m1);
+      const unsigned mk = key_mask(j);
       mbar_wait(&sm->s_full[sb], (sit >> 1) & 1u);
       tc_fence_after();
-      float v[2][32];
-      tmem_ld_32x32(tlane + sb * A5_KT, v[0]);
-      tmem_ld_32x32(tlane + sb * A5_KT + 32, v[1]);
+      float v[32];
+      tmem_ld_32x32(tlane + sb * A5_KT, v);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm->s_empty[sb]);
 #pragma unroll
-      for (int hf = 0; hf < 2; ++hf) {
-        const unsigned mk = hf ? m1 : m0;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float p = ((mk >> i) & 1u) ? exp2f(fmaf(v[hf][i], scale_log2, -mu)) : 0.0f;
-          v[hf][i] = p;
-          l_sum += p;
-        }
+      for (int i = 0; i < 32; ++i) {
+        const float p = ((mk >> i) & 1u) ? exp2f(fmaf(v[i], scale_log2, -mu)) : 0.0f;
+        v[i] = p;
+        l_sum += p;
       }
       if (j >= 1) mbar_wait(&sm->p_free, static_cast<uint32_t>(j - 1) & 1u);      // P V of the previous tile has retired
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {                          // 16-byte chunk c = keys 8c .. 8c+7 of this row
+      for (int c = 0; c < 4; ++c) {                          // 16-byte chunk 4*wg + c = keys 32*wg + 8c .. + 7 of this row
         uint32_t h[4], l[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int k = 8 * c + 2 * i;
-          a5_split2(v[k >> 5][k & 31], v[(k + 1) >> 5][(k + 1) & 31], &h[i], &l[i]);
-        }
-        const uint32_t off = prow + ((static_cast<uint32_t>(c) ^ static_cast<uint32_t>(row & 7)) << 4);
+        for (int i = 0; i < 4; ++i) a5_split2(v[8 * c + 2 * i], v[8 * c + 2 * i + 1], &h[i], &l[i]);
+        const uint32_t off = prow + ((static_cast<uint32_t>(4 * wg + c) ^ static_cast<uint32_t>(row & 7)) << 4);
         *reinterpret_cast<uint4*>(p_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
         *reinterpret_cast<uint4*>(p_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
       }
@@ -285,16 +281,20 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm->p_full);
     }
-    // ---- O / l -> out
+    sm->xch[wg][row] = l_sum;
+    named_bar_sync(1, 256);
+    l_sum += sm->xch[wg ^ 1][row];
+    // ---- O / l -> out: warpgroup wg stores d columns [64 wg, 64 wg + 64)
     mbar_wait(&sm->o_full, 0);
     tc_fence_after();
     const int t = q0 + row;
     const float inv = 1.0f / l_sum;
     const long long orow = static_cast<long long>(row0) + t;
+    const uint32_t olane = tmem_base + (static_cast<uint32_t>(w * 32) << 16) + 2 * A5_KT;
 #pragma unroll
-    for (int c = 0; c < A5_D / 32; ++c) {
+    for (int c = 2 * wg; c < 2 * wg + 2; ++c) {
       float o[32];
-      tmem_ld_32x32(tlane + 2 * A5_KT + c * 32, o);
+      tmem_ld_32x32(olane + c * 32, o);
       tmem_ld_wait();
       if (t < seq_len) {
         const int col = head * A5_D + c * 32;
