@@ -32,13 +32,14 @@ constexpr int A5_D = 128;                    // head width
 constexpr int A5_QBOX = A5_QT * 128;         // one [128 rows x 64 fp16] box: 16 KB
 constexpr int A5_KBOX = A5_KT * 128;         // one [64 rows x 64 fp16] box: 8 KB
 constexpr int A5_Q_BYTES = 4 * A5_QBOX;      // Q hi (d 0-63, d 64-127), Q lo (same)
-constexpr int A5_STAGE = 8 * A5_KBOX;        // K hi (2 boxes), K lo (2), V hi (2), V lo (2): 64 KB
+constexpr int A5_STAGE = 4 * A5_KBOX;        // one ring slot: hi (2 boxes) + lo (2 boxes) of a K tile, or of a V tile: 32 KB
 constexpr int A5_P_BYTES = 2 * A5_QBOX;      // P hi, P lo: [128 q x 64 keys] each
-constexpr int A5_THREADS = 320;            // producer, MMA issuer, 2 softmax warpgroups of 4 warps
+constexpr int A5_THREADS = 352;            // K producer, MMA issuer, 2 softmax warpgroups of 4 warps, V producer
 
 struct A5Smem {
   uint64_t q_full;
-  uint64_t kv_full[2], kv_empty[2];
+  uint64_t k_full[2], k_empty[2];            // K ring: a slot is free once the S MMAs that read it have retired
+  uint64_t v_full[2], v_empty[2];            // V ring: ... once the P V MMAs have (a tile later), so K runs ahead of V
   uint64_t s_full[2], s_empty[2];
   uint64_t p_full, p_free;
   uint64_t o_full;
@@ -46,7 +47,7 @@ struct A5Smem {
   uint32_t pad;
   float xch[2][A5_QT];                       // row shift (pass 1) / row sum (pass 2) of each softmax warpgroup
 };
-constexpr int A5_SMEM_BYTES = A5_Q_BYTES + 2 * A5_STAGE + A5_P_BYTES + static_cast<int>(sizeof(A5Smem)) + 1024;
+constexpr int A5_SMEM_BYTES = A5_Q_BYTES + 4 * A5_STAGE + A5_P_BYTES + static_cast<int>(sizeof(A5Smem)) + 1024;
 static_assert(A5_SMEM_BYTES <= 232448, "over the 227 KB shared-memory limit");
 
 // MN-major shared-memory descriptor, 128B swizzle (cute::UMMA canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte
@@ -76,8 +77,9 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
   extern __shared__ uint8_t a5_smem_raw[];
   uint8_t* smem = a5_smem_raw + ((1024u - (smem_u32(a5_smem_raw) & 1023u)) & 1023u);
   uint8_t* q_s = smem;                                   // [hi0 | hi1 | lo0 | lo1]
-  uint8_t* kv_s = smem + A5_Q_BYTES;                     // 2 stages x [Kh0 Kh1 Kl0 Kl1 Vh0 Vh1 Vl0 Vl1]
-  uint8_t* p_s = kv_s + 2 * A5_STAGE;                    // [P hi | P lo]
+  uint8_t* k_s = smem + A5_Q_BYTES;                      // 2 slots x [Kh0 Kh1 Kl0 Kl1]
+  uint8_t* v_s = k_s + 2 * A5_STAGE;                     // 2 slots x [Vh0 Vh1 Vl0 Vl1]
+  uint8_t* p_s = v_s + 2 * A5_STAGE;                     // [P hi | P lo]
   A5Smem* sm = reinterpret_cast<A5Smem*>(p_s + A5_P_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * A5_QT, head = blockIdx.y, b = blockIdx.z;
@@ -88,7 +90,8 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
   if (warp == 0 && lane == 0) {
     mbar_init(&sm->q_full, 1);
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&sm->kv_full[i], 1); mbar_init(&sm->kv_empty[i], 1);
+      mbar_init(&sm->k_full[i], 1); mbar_init(&sm->k_empty[i], 1);
+      mbar_init(&sm->v_full[i], 1); mbar_init(&sm->v_empty[i], 1);
       mbar_init(&sm->s_full[i], 1); mbar_init(&sm->s_empty[i], 8);
     }
     mbar_init(&sm->p_full, 8);
@@ -112,21 +115,29 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       uint32_t it = 0;
       for (int pass = 0; pass < 2; ++pass) {
         for (int j = 0; j < n_tiles; ++j, ++it) {
-          const int stage = it & 1;
-          mbar_wait(&sm->kv_empty[stage], ((it >> 1) & 1u) ^ 1u);
-          uint8_t* st = kv_s + stage * A5_STAGE;
-          mbar_expect_tx(&sm->kv_full[stage], (pass ? 8 : 2) * A5_KBOX);
-          const int r = row0 + j * A5_KT;
+          const int slot = it & 1;
+          mbar_wait(&sm->k_empty[slot], ((it >> 1) & 1u) ^ 1u);
+          uint8_t* st = k_s + slot * A5_STAGE;
+          mbar_expect_tx(&sm->k_full[slot], (pass ? 4 : 2) * A5_KBOX);
           for (int half = 0; half < (pass ? 2 : 1); ++half)                  // pass 1: the hi boxes of K alone
             for (int box = 0; box < 2; ++box)
-              tma_load_2d(st + (half * 2 + box) * A5_KBOX, &tm_kv, &sm->kv_full[stage], col_k + half * lo_off + box * 64, r);
-          if (pass) {
-            for (int half = 0; half < 2; ++half)
-              for (int box = 0; box < 2; ++box)
-                tma_load_2d(st + (4 + half * 2 + box) * A5_KBOX, &tm_kv, &sm->kv_full[stage],
-                            col_v + half * lo_off + box * 64, r);
-          }
+              tma_load_2d(st + (half * 2 + box) * A5_KBOX, &tm_kv, &sm->k_full[slot], col_k + half * lo_off + box * 64,
+                          row0 + j * A5_KT);
         }
+      }
+    }
+  } else if (warp == 10) {
+    // ================================ TMA producer of V (pass 2) ===================
+    if (lane == 0) {
+      for (int j = 0; j < n_tiles; ++j) {
+        const int slot = j & 1;
+        mbar_wait(&sm->v_empty[slot], ((j >> 1) & 1u) ^ 1u);
+        uint8_t* st = v_s + slot * A5_STAGE;
+        mbar_expect_tx(&sm->v_full[slot], 4 * A5_KBOX);
+        for (int half = 0; half < 2; ++half)
+          for (int box = 0; box < 2; ++box)
+            tma_load_2d(st + (half * 2 + box) * A5_KBOX, &tm_kv, &sm->v_full[slot], col_v + half * lo_off + box * 64,
+                        row0 + j * A5_KT);
       }
     }
   } else if (warp == 1) {
@@ -137,7 +148,7 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       const uint32_t q_base = smem_u32(q_s), p_base = smem_u32(p_s);
       // S[sb] = Qh Kh^T + Qh Kl^T + Ql Kh^T over d = 2 boxes x 4 k-steps of 16
       auto issue_s = [&](int sb, int stage, int nprod) {
-        const uint32_t k_base = smem_u32(kv_s + stage * A5_STAGE);
+        const uint32_t k_base = smem_u32(k_s + stage * A5_STAGE);
         const uint32_t d_tmem = tmem_base + sb * A5_KT;
         uint32_t acc = 0;
         for (int prod = 0; prod < nprod; ++prod) {
@@ -154,7 +165,7 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       };
       // O += Ph Vh + Ph Vl + Pl Vh over the 64 keys of the tile = 4 k-steps of 16
       auto issue_pv = [&](int stage, bool first) {
-        const uint32_t v_base = smem_u32(kv_s + stage * A5_STAGE) + 4 * A5_KBOX;
+        const uint32_t v_base = smem_u32(v_s + stage * A5_STAGE);
         const uint32_t d_tmem = tmem_base + 2 * A5_KT;
         uint32_t acc = first ? 0u : 1u;
 #pragma unroll
@@ -175,33 +186,35 @@ mha_tc5_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__
       uint32_t it = 0, sit = 0;
       // ---- pass 1: Qh Kh^T only (the softmax warps keep a row shift)
       for (int j = 0; j < n_tiles; ++j, ++it, ++sit) {
-        const int stage = it & 1, sb = sit & 1;
-        mbar_wait(&sm->kv_full[stage], (it >> 1) & 1u);
+        const int slot = it & 1, sb = sit & 1;
+        mbar_wait(&sm->k_full[slot], (it >> 1) & 1u);
         mbar_wait(&sm->s_empty[sb], ((sit >> 1) & 1u) ^ 1u);
         tc_fence_after();
-        issue_s(sb, stage, 1);
-        umma_commit(&sm->kv_empty[stage]);
+        issue_s(sb, slot, 1);
+        umma_commit(&sm->k_empty[slot]);
         umma_commit(&sm->s_full[sb]);
       }
       // ---- pass 2: S(j) first, then P V of the previous tile (the softmax of tile j runs meanwhile)
       for (int j = 0; j <= n_tiles; ++j) {
         if (j < n_tiles) {
-          const int stage = it & 1, sb = sit & 1;
-          mbar_wait(&sm->kv_full[stage], (it >> 1) & 1u);
+          const int slot = it & 1, sb = sit & 1;
+          mbar_wait(&sm->k_full[slot], (it >> 1) & 1u);
           mbar_wait(&sm->s_empty[sb], ((sit >> 1) & 1u) ^ 1u);
           tc_fence_after();
-          issue_s(sb, stage, 3);
+          issue_s(sb, slot, 3);
+          umma_commit(&sm->k_empty[slot]);
           umma_commit(&sm->s_full[sb]);
           ++it; ++sit;
         }
         if (j >= 1) {
           const uint32_t pj = static_cast<uint32_t>(j - 1);
-          const int pstage = (n_tiles + j - 1) & 1;                             // ring slot of tile j-1 of pass 2
+          const int vslot = pj & 1;
+          mbar_wait(&sm->v_full[vslot], (pj >> 1) & 1u);
           mbar_wait(&sm->p_full, pj & 1u);
           tc_fence_after();
-          issue_pv(pstage, pj == 0);
+          issue_pv(vslot, pj == 0);
           umma_commit(&sm->p_free);
-          umma_commit(&sm->kv_empty[pstage]);
+          umma_commit(&sm->v_empty[vslot]);
         }
       }
       umma_commit(&sm->o_full);
