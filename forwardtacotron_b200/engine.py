@@ -45,6 +45,9 @@ FOLD_TAPS = os.environ.get('FTB_FOLD_TAPS', '1') != '0'
 XPROJ_TOKENS = os.environ.get('FTB_XPROJ_TOKENS', '1') != '0'
 # CUDA graphs through the library's own stream capture (ftb_graph_*); FTB_NATIVE_GRAPHS=0: torch.cuda.CUDAGraph
 NATIVE_GRAPHS = os.environ.get('FTB_NATIVE_GRAPHS', '1') != '0'
+# Independent glue launches of one level (the attention / LayerNorm calls of the four token-side transformers of FastPitch)
+# on parallel streams, forked from and joined to the program's stream (parallel branches of its CUDA graph)
+PARALLEL_GLUE = os.environ.get('FTB_PARALLEL_GLUE', '1') != '0'
 
 
 def _tile_cost(q) -> float:
@@ -131,6 +134,7 @@ class Program:
         self._graphs: Dict[tuple, object] = {}        # (launch-time scalars, seq_len) -> captured graph
         self._baked_len = False                       # a glue kernel takes seq_len as a kernel ARGUMENT
         self._torch_steps = False                     # a step runs torch operators (see call())
+        self._sides: list = []                        # (stream, fork event, join event) of the parallel glue steps
         self._eager_runs = 0
 
     # ---- buffers ---------------------------------------------------------------------------
@@ -389,7 +393,43 @@ class Program:
         self._baked_len = True
         self._torch_steps = self._torch_steps or torch_ops
         self.steps.append(fn)
-        self.info.append({'kind': 'glue', 'label': label, 'flops': 0.0, 'bytes': nbytes})
+        self.info.append({'kind': 'glue', 'label': label, 'flops': 0.0, 'bytes': nbytes, 'call': not torch_ops})
+
+    # ---- levels: the steps queued between begin_level() and end_level() are independent of each other ----------
+    def begin_level(self):
+        self.flush()
+        self._level_mark = len(self.steps)
+
+    def end_level(self):
+        """Close a level (run_levels).  When it consists of two or more C-ABI call steps -- one per branch: the attention
+        or LayerNorm launches of independent transformers, each a few microseconds of work on a fraction of the SMs --
+        they become ONE step that runs them on parallel streams."""
+        self.flush()
+        n0 = getattr(self, '_level_mark', len(self.steps))
+        infos = self.info[n0:]
+        if not (PARALLEL_GLUE and len(infos) >= 2 and all(i.get('call') for i in infos)):
+            return
+        fns = self.steps[n0:]
+        del self.steps[n0:], self.info[n0:]
+        while len(self._sides) < len(fns) - 1:
+            self._sides.append((torch.cuda.Stream(self.device), torch.cuda.Event(), torch.cuda.Event()))
+        sides = self._sides[:len(fns) - 1]
+
+        def run(fns=fns, sides=sides):
+            main = torch.cuda.current_stream(self.device)
+            fork = sides[0][1]
+            fork.record(main)
+            for fn, (st, _, done) in zip(fns[1:], sides):
+                st.wait_event(fork)
+                with torch.cuda.stream(st):
+                    fn()
+                    done.record(st)
+            fns[0]()
+            for _, _, done in sides:
+                main.wait_event(done)
+        self.steps.append(run)
+        self.info.append({'kind': 'glue', 'label': ' | '.join(i['label'] for i in infos), 'flops': 0.0,
+                          'bytes': sum(i['bytes'] for i in infos), 'parallel': len(fns)})
 
     def label(self, text: str):
         self._label = text
@@ -634,7 +674,8 @@ def run_levels(prog: Program, branches: List[list]):
     """Queue level i of every branch, flush, then level i+1, ...  (branches are independent)."""
     depth = max(len(b) for b in branches)
     for i in range(depth):
+        prog.begin_level()
         for b in branches:
             if i < len(b):
                 b[i]()
-        prog.flush()
+        prog.end_level()
