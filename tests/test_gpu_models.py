@@ -496,7 +496,31 @@ def test_generate_reuses_programs_across_lengths():
         _mel_checked(model, (x.to(DEV),), out, ref, _check_durations(out['dur'], ref['dur']))
         progs = model.__dict__['_accel']['programs']
     assert sum(1 for k in progs if k[0] == 'tok') == 1
-    assert sum(1 for k in progs if k[0] == 'frame') <= 3
+    assert 1 <= sum(1 for k in progs if k[0].startswith('frame')) <= 3
+
+
+def test_program_cache_eviction_takes_dependent_frame_programs_along():
+    """Frame programs read the x-projection buffer of the token program they were built for (models/_accel.frame_program):
+    when the LRU cache drops a token program its frame programs go with it, and a later call with the evicted shape
+    rebuilds both and reproduces its first result bit for bit."""
+    sd = synthetic_sd('forward_tacotron', 2)
+    model = _model('forward_tacotron', sd)
+    first = {}
+    for B in (1, 2, 3, 4, 5, 6):                       # 6 x (token + frame program) > the 8-entry cache
+        x = synth.synth_tokens(B, 21, seed=B).to(DEV)
+        first[B] = (x, model.generate(x))
+    progs = model.__dict__['_accel']['programs']
+    assert len(progs) <= 2 * model.MAX_PROGRAMS
+    live_tok = {id(p) for k, p in progs.items() if k[0] == 'tok'}
+    for k in progs:
+        if k[0].startswith('frame@'):
+            assert int(k[0].split('@')[1]) in live_tok, 'a frame program outlived its token program'
+    for B in (1, 2, 6):
+        x, want = first[B]
+        got = model.generate(x)
+        torch.cuda.synchronize()
+        for key in ('mel', 'mel_post', 'dur'):
+            assert torch.equal(got[key], want[key]), (B, key)
 
 
 @pytest.mark.parametrize('tag', ['forward_tacotron', 'fast_pitch'])
