@@ -143,7 +143,7 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
   // phase-B base pointers: row (r_warp + sub), column n0 + 4*part; +32 columns per chunk, +4 rows per i8
   const long long orow = (c.r_warp + sub) * c.out_ld + c.n0 + 4 * part;
   // fp16 output next to a residual / unrounded twin / transposed output: phase-B layout, 8-byte stores of 4 halves
-  constexpr bool O16_FAST = OUT16 && !RES && !FULL && !OUTT && !SPLIT;
+  constexpr bool O16_FAST = OUT16 && !RES && !FULL && !OUTT;     // (SPLIT included: hi / lo / hi as 16-byte row segments)
   float* optr = c.out ? c.out + orow : nullptr;
   __half* hptr = (OUT16 && !O16_FAST) ? c.out16 + orow : nullptr;
   float* fptr = FULL ? c.out_full + orow : nullptr;
@@ -255,7 +255,24 @@ __device__ __forceinline__ void epi_affine_tile(const EpiCtx& c) {
               t = __floats2half2_rn(y0.z, y0.w); pk.y = *reinterpret_cast<const uint32_t*>(&t);
               t = __floats2half2_rn(y1.x, y1.y); pk.z = *reinterpret_cast<const uint32_t*>(&t);
               t = __floats2half2_rn(y1.z, y1.w); pk.w = *reinterpret_cast<const uint32_t*>(&t);
-              *reinterpret_cast<uint4*>(o16 + static_cast<long long>(h * 16 + i2 * 8) * c.out_ld + c0) = pk;
+              __half* dst = o16 + static_cast<long long>(h * 16 + i2 * 8) * c.out_ld + c0;
+              *reinterpret_cast<uint4*>(dst) = pk;
+              if (SPLIT) {
+                // FTB_F_OUT_SPLIT: [hi | lo | hi] column blocks of width out_ld / 3 -- the K-concatenated operand of a
+                // split-precision consumer (weights packed as [W_hi | W_hi | W_lo]): hi*W_hi + lo*W_hi + hi*W_lo
+                const float yv[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+                const uint32_t hw[4] = {pk.x, pk.y, pk.z, pk.w};
+                uint32_t lw[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hw[u]));
+                  const __half2 r = __floats2half2_rn(yv[2 * u] - f.x, yv[2 * u + 1] - f.y);
+                  lw[u] = *reinterpret_cast<const uint32_t*>(&r);
+                }
+                const int seg = c.out_ld / 3;
+                *reinterpret_cast<uint4*>(dst + seg) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+                *reinterpret_cast<uint4*>(dst + 2 * seg) = pk;
+              }
             }
           }
         }
