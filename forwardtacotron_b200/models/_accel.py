@@ -116,7 +116,10 @@ class AcceleratedMixin:
 
 def token_x_supported(packs: dict, in_channels: int) -> bool:
     """The BiLSTM's x-projection once per PHONEME (engine.XPROJ_TOKENS): the fp16 operand / fp16 x-projection path."""
-    return bool(eng.XPROJ_TOKENS and eng.F16_OPERANDS and eng.X16 and in_channels % 8 == 0 and packs['lstm'].ih.n % 8 == 0)
+    lstm = packs['lstm']
+    # (the indexed x read of the recurrence kernel is instantiated for the LSTM of 512 units, rnn_dims of both yaml configs)
+    return bool(eng.XPROJ_TOKENS and eng.F16_OPERANDS and eng.X16 and in_channels % 8 == 0 and lstm.ih.n % 8 == 0
+                and lstm.cell == 1 and lstm.hidden == 512)
 
 
 def token_x_program(handle: rt.Handle, packs: dict, tok_prog: eng.Program, in_channels: int) -> eng.Program:

@@ -499,6 +499,29 @@ def test_generate_reuses_programs_across_lengths():
     assert 1 <= sum(1 for k in progs if k[0].startswith('frame')) <= 3
 
 
+def test_forward_tacotron_other_rnn_width_takes_the_materialised_regulator_path():
+    """The per-phoneme x-projection of the BiLSTM is instantiated for rnn_dims = 512 (both yaml configs).  Another width
+    falls back to the materialised LengthRegulator output + frame-level projection (models/_accel.token_x_supported) and
+    still matches the oracle."""
+    cfg = default_config('forward_tacotron')
+    cfg['forward_tacotron']['model']['rnn_dims'] = 256
+    model = init_tts_model(cfg)
+    sd = synth.synth_state_dict(model.state_dict(), seed=9)
+    model.load_state_dict(sd)
+    model = model.to(DEV).eval()
+    x = synth.synth_tokens(3, 23, seed=9)
+    O.use_library_rnn(True)
+    try:
+        ref = O.ft_generate(sd, x)
+    finally:
+        O.use_library_rnn(False)
+    out = model.generate(x.to(DEV))
+    torch.cuda.synchronize()
+    frame = model.program_for('frame', 3, out['mel'].shape[2])
+    assert frame is not None and 'lr' in frame.bufs and 'x_idx' not in frame.bufs
+    _mel_checked(model, (x.to(DEV),), out, ref, _check_durations(out['dur'], ref['dur']))
+
+
 def test_program_cache_eviction_takes_dependent_frame_programs_along():
     """Frame programs read the x-projection buffer of the token program they were built for (models/_accel.frame_program):
     when the LRU cache drops a token program its frame programs go with it, and a later call with the evicted shape
