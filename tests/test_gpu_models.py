@@ -35,7 +35,7 @@ DUR_WINDOW = 2e-4      # the documented .5-tie window, in frames: 
 
 
 # MultiFastPitch's duration predictor is four FFT blocks of width 392 (K = 3 * 3528 per conv1 MMA chain): the tensor
-# core's fp32 accumulator truncates instead of rounding, a bias that grows with K (scratch/debug_mfp_dur.py: 1e-4 per
+# core's fp32 accumulator truncates instead of rounding, a bias that grows with K (scratch/mfp_dur_layer_errors.py: 1e-4 per
 # unit-scale activation after four layers although every operand is split to ~2^-20), so its raw durations agree to
 # 2.4e-4 and its window is wider.
 DUR_WINDOW_MFP = 5e-4
