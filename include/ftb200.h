@@ -233,7 +233,9 @@ typedef struct {
                             repetition (common_layers.py:21) -- `xproj` is then computed once per PHONEME (half the
                             projection work at two frames per phoneme), x_idx is the frame -> row map ftb_lr_index
                             writes, and the padded frames (common_layers.py:23) point at one extra row that holds
-                            b_ih, the projection of a zero row.  null = rows b * seq_stride + t as described above  */
+                            b_ih, the projection of a zero row.  null = rows b * seq_stride + t as described above.
+                            Instantiated for the LSTM of 512 hidden units (the BiLSTM of both reference configs,
+                            forward_tacotron.py:224); other problems return FTB_E_SHAPE                          */
 } ftb_rnn_problem;
 
 #define FTB_MAX_RNN_PROBLEMS 8
